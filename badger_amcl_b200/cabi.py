@@ -1,0 +1,370 @@
+"""ctypes binding of include/bamcl.h (libbamcl_cuda.so). Thin: numpy in, numpy out, errors raise.
+
+This is plumbing for tests/ and bench.py; the product boundary is the C ABI itself. If the library has not
+been built, or there is no CUDA device, construction fails loudly -- there is no CPU fallback.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libbamcl_cuda.so")
+
+MODEL_BEAM, MODEL_LF, MODEL_LF_PROB, MODEL_LF_GOMPERTZ = 0, 1, 2, 3
+
+
+class BamclError(RuntimeError):
+    pass
+
+
+class PlanarModel(C.Structure):
+    _fields_ = [("model_type", C.c_int), ("max_beams", C.c_int), ("z_hit", C.c_double), ("z_short", C.c_double),
+                ("z_max", C.c_double), ("z_rand", C.c_double), ("sigma_hit", C.c_double), ("lambda_short", C.c_double),
+                ("gompertz_a", C.c_double), ("gompertz_b", C.c_double), ("gompertz_c", C.c_double),
+                ("input_shift", C.c_double), ("input_scale", C.c_double), ("output_shift", C.c_double),
+                ("do_beamskip", C.c_int), ("beam_skip_distance", C.c_double), ("beam_skip_threshold", C.c_double),
+                ("beam_skip_error_threshold", C.c_double), ("off_map_factor", C.c_double),
+                ("non_free_space_factor", C.c_double), ("non_free_space_radius", C.c_double),
+                ("scanner_pose", C.c_double * 3)]
+
+
+class ResampleParams(C.Structure):
+    _fields_ = [("resample_systematic", C.c_int), ("min_samples", C.c_int), ("max_samples", C.c_int),
+                ("pop_err", C.c_double), ("pop_z", C.c_double), ("w_diff", C.c_double), ("dist_threshold", C.c_double),
+                ("convergence_threshold", C.c_double), ("drand48_state", C.c_uint64), ("random_poses", C.c_void_p),
+                ("n_random_poses", C.c_long)]
+
+
+class ResampleResult(C.Structure):
+    _fields_ = [("sample_count", C.c_int), ("leaf_count", C.c_int), ("node_count", C.c_int), ("cluster_count", C.c_int),
+                ("converged", C.c_int), ("random_poses_used", C.c_int), ("status_flags", C.c_int), ("reserved", C.c_int),
+                ("drand48_state", C.c_uint64), ("mean", C.c_double * 3), ("cov", C.c_double * 5)]
+
+
+def planar_model(model_type=MODEL_LF, max_beams=60, z_hit=0.95, z_short=0.1, z_max=0.05, z_rand=0.05, sigma_hit=0.2,
+                 lambda_short=0.1, gompertz=(1.0, 1.0, 1.0, 0.0, 1.0, 0.0), do_beamskip=False, beam_skip_distance=0.5,
+                 beam_skip_threshold=0.3, beam_skip_error_threshold=0.9, off_map_factor=1.0, non_free_space_factor=1.0,
+                 non_free_space_radius=0.0, scanner_pose=(0.0, 0.0, 0.0)):
+    """Defaults are the reference node's (node_2d.cpp:49-76)."""
+    p = PlanarModel()
+    p.model_type, p.max_beams = model_type, max_beams
+    p.z_hit, p.z_short, p.z_max, p.z_rand, p.sigma_hit, p.lambda_short = z_hit, z_short, z_max, z_rand, sigma_hit, lambda_short
+    (p.gompertz_a, p.gompertz_b, p.gompertz_c, p.input_shift, p.input_scale, p.output_shift) = gompertz
+    p.do_beamskip = int(do_beamskip)
+    p.beam_skip_distance, p.beam_skip_threshold, p.beam_skip_error_threshold = (
+        beam_skip_distance, beam_skip_threshold, beam_skip_error_threshold)
+    p.off_map_factor, p.non_free_space_factor, p.non_free_space_radius = (
+        off_map_factor, non_free_space_factor, non_free_space_radius)
+    p.scanner_pose[:] = scanner_pose
+    return p
+
+
+_lib = None
+
+# every symbol include/bamcl.h declares: (restype, argtypes)
+_D, _I, _L, _P, _F = C.c_double, C.c_int, C.c_long, C.c_void_p, C.c_float
+SIGNATURES = {
+    "bamcl_last_error": (C.c_char_p, []),
+    "bamcl_version": (_I, []),
+    "bamcl_ctx_create": (_I, [_I, _P]),
+    "bamcl_ctx_destroy": (_I, [_P]),
+    "bamcl_ctx_sync": (_I, [_P]),
+    "bamcl_ctx_stream": (_P, [_P]),
+    "bamcl_timer_start": (_I, [_P]),
+    "bamcl_timer_stop_ms": (_I, [_P, _P]),
+    "bamcl_ctx_launch_count": (_L, [_P]),
+    "bamcl_ctx_flush_l2": (_I, [_P]),
+    "bamcl_map2d_create": (_I, [_P, _I, _I, _D, _F, _F, _P]),
+    "bamcl_map2d_destroy": (_I, [_P]),
+    "bamcl_map2d_set_cells": (_I, [_P, _P, _L]),
+    "bamcl_map2d_build_distances": (_I, [_P, _D]),
+    "bamcl_map2d_upload_distances": (_I, [_P, _P, _L, _D]),
+    "bamcl_map2d_download_distances": (_I, [_P, _P, _L]),
+    "bamcl_map2d_calc_range": (_I, [_P, _P, _P, _P, _L, _D, _P, _P]),
+    "bamcl_pf_create": (_I, [_P, _I, _I, _P]),
+    "bamcl_pf_destroy": (_I, [_P]),
+    "bamcl_pf_upload_samples": (_I, [_P, _P, _L]),
+    "bamcl_pf_download_samples": (_I, [_P, _P, _L]),
+    "bamcl_pf_sample_count": (_I, [_P, _P]),
+    "bamcl_pf_upload_weights": (_I, [_P, _P, _L]),
+    "bamcl_pf_download_weights": (_I, [_P, _P, _L]),
+    "bamcl_pf_score_planar": (_I, [_P, _P, _P, _P, _P, _I, _D, _I, _P]),
+    "bamcl_pf_normalise": (_I, [_P, _D]),
+    "bamcl_pf_update_planar": (_I, [_P, _P, _P, _P, _P, _I, _D, _I, _P]),
+    "bamcl_pf_stage_scan": (_I, [_P, _P, _P, _P, _P, _I, _D]),
+    "bamcl_pf_update_planar_staged": (_I, [_P, _P, _I, _P]),
+    "bamcl_pf_cdf": (_I, [_P, _P, _L]),
+    "bamcl_pf_resample": (_I, [_P, _P, _P]),
+    "bamcl_pf_init_stats": (_I, [_P, _P]),
+    "bamcl_pf_resample_sources": (_I, [_P, _P, _L]),
+    "bamcl_pf_sample_clusters": (_I, [_P, _P, _L]),
+    "bamcl_pf_cluster_stats": (_I, [_P, _P, _I]),
+    "bamcl_resample_limit": (_I, [_I, _I, _I, _D, _D]),
+}
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise BamclError("%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                             "(no CPU fallback exists)" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError here = the library does not export what bamcl.h declares
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise BamclError("bamcl error %d: %s" % (rc, lib().bamcl_last_error().decode()))
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    def __init__(self, device=0):
+        self.L = lib()
+        h = C.c_void_p()
+        _check(self.L.bamcl_ctx_create(device, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            self.L.bamcl_ctx_destroy(self.h)
+            self.h = None
+
+    def sync(self):
+        _check(self.L.bamcl_ctx_sync(self.h))
+
+    def stream(self):
+        return self.L.bamcl_ctx_stream(self.h)
+
+    def timer_start(self):
+        _check(self.L.bamcl_timer_start(self.h))
+
+    def timer_stop_ms(self):
+        ms = C.c_float()
+        _check(self.L.bamcl_timer_stop_ms(self.h, C.byref(ms)))
+        return ms.value
+
+    def launch_count(self):
+        return self.L.bamcl_ctx_launch_count(self.h)
+
+    def flush_l2(self):
+        _check(self.L.bamcl_ctx_flush_l2(self.h))
+
+
+class Map2D:
+    """OccupancyMap (include/amcl/map/occupancy_map.h:57-81) on the device."""
+
+    def __init__(self, ctx, cells, resolution, origin=(0.0, 0.0)):
+        self.ctx, self.L = ctx, ctx.L
+        cells = np.ascontiguousarray(cells, np.int8)
+        self.size_y, self.size_x = cells.shape
+        self.resolution = float(resolution)
+        h = C.c_void_p()
+        _check(self.L.bamcl_map2d_create(ctx.h, self.size_x, self.size_y, resolution, origin[0], origin[1], C.byref(h)))
+        self.h = h
+        if cells.size:
+            _check(self.L.bamcl_map2d_set_cells(self.h, _p(cells), cells.size))
+
+    def close(self):
+        if self.h:
+            self.L.bamcl_map2d_destroy(self.h)
+            self.h = None
+
+    def build_distances(self, max_distance):
+        _check(self.L.bamcl_map2d_build_distances(self.h, max_distance))
+
+    def upload_distances(self, dist, max_distance):
+        d = np.ascontiguousarray(dist, np.float32)
+        _check(self.L.bamcl_map2d_upload_distances(self.h, _p(d), d.size, max_distance))
+
+    def download_distances(self):
+        out = np.empty((self.size_y, self.size_x), np.float32)
+        _check(self.L.bamcl_map2d_download_distances(self.h, _p(out), out.size))
+        return out
+
+    def calc_range(self, ox, oy, oa, max_range, with_steps=False):
+        ox, oy, oa = (np.ascontiguousarray(np.broadcast_to(a, np.shape(oa)), np.float64) for a in (ox, oy, oa))
+        out = np.empty(len(oa))
+        steps = C.c_long(0)
+        _check(self.L.bamcl_map2d_calc_range(self.h, _p(ox), _p(oy), _p(oa), len(oa), max_range, _p(out), C.byref(steps)))
+        return (out, steps.value) if with_steps else out
+
+
+class ParticleFilter:
+    """Device side of ParticleFilter (include/amcl/pf/particle_filter.h:96-130). The scalar bookkeeping the
+    reference keeps in the class (w_slow_/w_fast_, current_set_, converged_) lives in the host C++ mirror
+    (badger_amcl_b200/host); this wrapper re-states just enough of it for tests and the bench."""
+
+    def __init__(self, ctx, min_samples, max_samples, alpha_slow=0.001, alpha_fast=0.1, conv_thresh=95.0,
+                 systematic=True, pop_err=0.01, pop_z=0.99):
+        self.ctx, self.L = ctx, ctx.L
+        self.min_samples, self.max_samples = min_samples, max_samples
+        self.alpha_slow, self.alpha_fast, self.conv_thresh = alpha_slow, alpha_fast, conv_thresh
+        self.systematic, self.pop_err, self.pop_z = systematic, pop_err, pop_z
+        self.w_slow = self.w_fast = 0.0
+        self.converged = False
+        self.drand48_state = 0
+        self.random_poses = np.zeros((0, 3))
+        self.random_next = 0
+        self.last = None
+        h = C.c_void_p()
+        _check(self.L.bamcl_pf_create(ctx.h, min_samples, max_samples, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            self.L.bamcl_pf_destroy(self.h)
+            self.h = None
+
+    # -- sample exchange
+    def sample_count(self):
+        n = C.c_int()
+        _check(self.L.bamcl_pf_sample_count(self.h, C.byref(n)))
+        return n.value
+
+    def upload_samples(self, aos):
+        a = np.ascontiguousarray(aos, np.float64)
+        assert a.ndim == 2 and a.shape[1] == 4
+        _check(self.L.bamcl_pf_upload_samples(self.h, _p(a), len(a)))
+
+    def samples(self):
+        out = np.empty((self.sample_count(), 4))
+        _check(self.L.bamcl_pf_download_samples(self.h, _p(out), len(out)))
+        return out
+
+    def upload_weights(self, w):
+        w = np.ascontiguousarray(w, np.float64)
+        _check(self.L.bamcl_pf_upload_weights(self.h, _p(w), len(w)))
+
+    def weights(self):
+        out = np.empty(self.sample_count())
+        _check(self.L.bamcl_pf_download_weights(self.h, _p(out), len(out)))
+        return out
+
+    def init_with_poses(self, poses):
+        """initWithPoseFn (particle_filter.cpp:136-162): max_samples poses, weights 1/max_samples, kd-tree +
+        cluster statistics, averages reset, not converged."""
+        poses = np.asarray(poses, np.float64)
+        n = self.max_samples
+        aos = np.empty((n, 4))
+        aos[:, :3] = poses[np.arange(n) % len(poses)]
+        aos[:, 3] = 1.0 / n
+        self.upload_samples(aos)
+        self.w_slow = self.w_fast = 0.0
+        self.converged = False
+        res = ResampleResult()
+        _check(self.L.bamcl_pf_init_stats(self.h, C.byref(res)))
+        self.last = res
+        return res
+
+    # -- sensor update
+    def score_planar(self, map2d, model, ranges, angles, range_max):
+        """PlanarScanner::applyModelToSampleSet: returns the total; weights stay un-normalised."""
+        ranges = np.ascontiguousarray(ranges, np.float64)
+        angles = np.ascontiguousarray(angles, np.float64)
+        total = C.c_double()
+        _check(self.L.bamcl_pf_score_planar(self.h, map2d.h, C.byref(model), _p(ranges), _p(angles), len(ranges),
+                                            range_max, int(self.converged), C.byref(total)))
+        return total.value
+
+    def normalise(self, total):
+        _check(self.L.bamcl_pf_normalise(self.h, total))
+
+    def _averages(self, total):
+        """particle_filter.cpp:237-257 (w_avg is the same sequential sum as the total, divided by the count)"""
+        if total > 0.0:
+            w_avg = total / self.sample_count()
+            self.w_slow = w_avg if self.w_slow == 0.0 else self.w_slow + self.alpha_slow * (w_avg - self.w_slow)
+            self.w_fast = w_avg if self.w_fast == 0.0 else self.w_fast + self.alpha_fast * (w_avg - self.w_fast)
+
+    def update_sensor(self, map2d, model, ranges, angles, range_max):
+        """PlanarScanner::updateSensor -> ParticleFilter::updateSensor, fused on the device."""
+        if model.max_beams < 2:
+            return False
+        ranges = np.ascontiguousarray(ranges, np.float64)
+        angles = np.ascontiguousarray(angles, np.float64)
+        total = C.c_double()
+        _check(self.L.bamcl_pf_update_planar(self.h, map2d.h, C.byref(model), _p(ranges), _p(angles), len(ranges),
+                                             range_max, int(self.converged), C.byref(total)))
+        self._averages(total.value)
+        self.last_total = total.value
+        return True
+
+    def stage_scan(self, map2d, model, ranges, angles, range_max):
+        ranges = np.ascontiguousarray(ranges, np.float64)
+        angles = np.ascontiguousarray(angles, np.float64)
+        _check(self.L.bamcl_pf_stage_scan(self.h, map2d.h, C.byref(model), _p(ranges), _p(angles), len(ranges), range_max))
+
+    def update_staged(self, map2d, want_total=True):
+        total = C.c_double()
+        _check(self.L.bamcl_pf_update_planar_staged(self.h, map2d.h, int(self.converged),
+                                                    C.byref(total) if want_total else None))
+        if want_total:
+            self._averages(total.value)
+            return total.value
+        return None
+
+    # -- resampling
+    def cdf(self):
+        out = np.empty(self.sample_count() + 1)
+        _check(self.L.bamcl_pf_cdf(self.h, _p(out), len(out)))
+        return out
+
+    def srand48(self, seed):
+        self.drand48_state = ((seed & 0xFFFFFFFF) << 16) | 0x330E
+
+    def set_random_poses(self, poses):
+        self.random_poses = np.ascontiguousarray(poses, np.float64)
+        self.random_next = 0
+
+    def resample_limit(self, k):
+        return self.L.bamcl_resample_limit(k, self.min_samples, self.max_samples, self.pop_err, self.pop_z)
+
+    def update_resample(self, w_diff=None):
+        """ParticleFilter::updateResample (particle_filter.cpp:423-471)."""
+        if w_diff is None:
+            with np.errstate(divide="ignore", invalid="ignore"):
+                w_diff = float(1.0 - np.float64(self.w_fast) / np.float64(self.w_slow))
+            if w_diff < 0.0:
+                w_diff = 0.0
+        rp = self.random_poses[self.random_next:]
+        prm = ResampleParams(int(self.systematic), self.min_samples, self.max_samples, self.pop_err, self.pop_z, w_diff,
+                             0.5, self.conv_thresh, self.drand48_state, _p(rp) if len(rp) else None, len(rp))
+        res = ResampleResult()
+        _check(self.L.bamcl_pf_resample(self.h, C.byref(prm), C.byref(res)))
+        self.drand48_state = res.drand48_state
+        self.random_next += res.random_poses_used
+        if w_diff > 0.0:
+            self.w_slow = self.w_fast = 0.0
+        self.converged = bool(res.converged)
+        self.last = res
+        return res
+
+    def resample_sources(self):
+        out = np.empty(self.sample_count(), np.int32)
+        _check(self.L.bamcl_pf_resample_sources(self.h, _p(out), len(out)))
+        return out
+
+    def sample_clusters(self):
+        out = np.empty(self.sample_count(), np.int32)
+        _check(self.L.bamcl_pf_sample_clusters(self.h, _p(out), len(out)))
+        return out
+
+    def cluster_stats(self):
+        n = self.last.cluster_count
+        out = np.empty((n, 10))
+        _check(self.L.bamcl_pf_cluster_stats(self.h, _p(out), n))
+        return out
+
+    def set_stats(self):
+        r = self.last
+        return np.array(list(r.mean) + list(r.cov))

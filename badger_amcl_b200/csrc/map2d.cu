@@ -1,0 +1,361 @@
+// OccupancyMap device object: cell upload, distance-cache build (exact capped EDT, K-e2), cache
+// upload/download, batched calcRange. Reference: src/amcl/map/occupancy_map.cpp.
+#include <cmath>
+#include <cstring>
+#include <cstdlib>
+
+#include "map2d.cuh"
+
+using namespace bamcl;
+
+namespace
+{
+constexpr int kFarG = 0xFFFF;  // "no obstacle within the radius along this column"
+
+// ---- K-e2 phase 1: per column i, distance (in cells, along j) to the nearest occupied cell, capped.
+// One thread per column; adjacent threads touch adjacent addresses of every row (coalesced).
+__global__ void k_edt_columns(const int8_t* __restrict__ cells, uint16_t* __restrict__ g, int size_x, int size_y,
+                              int radius)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= size_x)
+    return;
+  int d = kFarG;
+  for (int j = 0; j < size_y; j++)
+  {
+    const size_t idx = (size_t)j * size_x + i;
+    d = (cells[idx] == 1) ? 0 : (d >= radius ? kFarG : d + 1);
+    g[idx] = (uint16_t)d;
+  }
+  d = kFarG;
+  for (int j = size_y - 1; j >= 0; j--)
+  {
+    const size_t idx = (size_t)j * size_x + i;
+    d = (cells[idx] == 1) ? 0 : (d >= radius ? kFarG : d + 1);
+    if (d < g[idx])
+      g[idx] = (uint16_t)d;
+  }
+}
+
+// ---- K-e2 phase 2: per cell, k = min over |di| <= radius of di^2 + g(i+di, j)^2. A block owns a row
+// segment; the g row (with halo) is staged in shared memory once and read 2*radius+1 times.
+// Writes the float cache with the reference's value formula and the tiled u16 field.
+template <int BLOCK>
+__global__ void k_edt_rows(const uint16_t* __restrict__ g, float* __restrict__ dist, uint16_t* __restrict__ kmap,
+                           int size_x, int size_y, int tiles_x, int layout, int radius, double resolution, float far_value)
+{
+  extern __shared__ uint16_t s_g[];  // BLOCK + 2*radius
+  const int j = blockIdx.y;
+  const int i0 = blockIdx.x * BLOCK;
+  const int span = BLOCK + 2 * radius;
+  for (int t = threadIdx.x; t < span; t += BLOCK)
+  {
+    const int i = i0 - radius + t;
+    s_g[t] = (i >= 0 && i < size_x) ? g[(size_t)j * size_x + i] : (uint16_t)kFarG;
+  }
+  __syncthreads();
+  const int i = i0 + threadIdx.x;
+  if (i >= size_x)
+    return;
+  const int r2 = radius * radius;
+  int best = r2 + 1;
+  for (int d = -radius; d <= radius; d++)
+  {
+    const int gv = s_g[threadIdx.x + radius + d];
+    if (gv != kFarG)
+    {
+      const int k2 = d * d + gv * gv;
+      best = min(best, k2);
+    }
+  }
+  // occupancy_map.cpp:229-232: accepted iff sqrt(di^2+dj^2) <= cell_radius, stored as float(distance * res)
+  float v = far_value;
+  int k = r2 + 1;
+  if (best <= r2)
+  {
+    v = (float)(sqrt((double)best) * resolution);
+    k = best;
+  }
+  dist[(size_t)j * size_x + i] = v;
+  kmap[tiled_offset(i, j, tiles_x, layout)] = (uint16_t)(k * 8);
+}
+
+// ---- uploaded cache -> tiled u16 field. A value is canonical if it is (float)(sqrt(k)*res) for an
+// integer k <= radius^2, or equals the far value.
+__global__ void k_index_uploaded(const float* __restrict__ dist, uint16_t* __restrict__ kmap, int size_x, int size_y,
+                                 int tiles_x, int layout, int radius, double resolution, float far_value, int* __restrict__ bad)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y;
+  if (i >= size_x)
+    return;
+  const float d = dist[(size_t)j * size_x + i];
+  const int r2 = radius * radius;
+  int k = r2 + 1;
+  if (d != far_value)
+  {
+    const double c = (double)d / resolution;
+    const long kk = llrint(c * c);
+    bool ok = false;
+    for (long t = kk - 1; t <= kk + 1 && !ok; t++)
+      if (t >= 0 && t <= r2 && (float)(sqrt((double)t) * resolution) == d)
+      {
+        k = (int)t;
+        ok = true;
+      }
+    if (!ok)
+      atomicAdd(bad, 1);
+  }
+  kmap[tiled_offset(i, j, tiles_x, layout)] = (uint16_t)(k * 8);
+}
+
+// ---- "not free" bit fields for the ray march: bit (i & 31) of word [j][i >> 5] (rows) and
+// bit (j & 31) of word [i][j >> 5] (columns).
+__global__ void k_blocked_bits(const int8_t* __restrict__ cells, uint32_t* __restrict__ rows, uint32_t* __restrict__ cols,
+                               int size_x, int size_y, int row_words, int col_words)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y;
+  const bool blocked = (i < size_x) ? (cells[(size_t)j * size_x + i] != -1) : true;
+  const unsigned m = __ballot_sync(0xffffffffu, blocked);
+  if ((threadIdx.x & 31) == 0 && (i >> 5) < row_words)
+    rows[(size_t)j * row_words + (i >> 5)] = m;
+  if (blocked && i < size_x)
+    atomicOr(&cols[(size_t)i * col_words + (j >> 5)], 1u << (j & 31));
+}
+
+// ---- calcRange (occupancy_map.cpp:257-364), one thread per ray, the reference's own cell walk.
+__global__ void k_calc_range(const int8_t* __restrict__ cells, int size_x, int size_y, double resolution, float ox_f,
+                             float oy_f, const double* __restrict__ ox, const double* __restrict__ oy,
+                             const double* __restrict__ oa, long n, double max_range, double* __restrict__ out,
+                             unsigned long long* __restrict__ steps_total)
+{
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n)
+    return;
+  int x0 = world_to_cell(ox[t], ox_f, resolution, size_x);
+  int y0 = world_to_cell(oy[t], oy_f, resolution, size_y);
+  int x1 = world_to_cell(ox[t] + max_range * cos(oa[t]), ox_f, resolution, size_x);
+  int y1 = world_to_cell(oy[t] + max_range * sin(oa[t]), oy_f, resolution, size_y);
+  unsigned long long steps = 0;
+  double r = max_range;
+  if (!(x0 == x1 && y0 == y1))
+  {
+    const bool steep = abs(y1 - y0) > abs(x1 - x0);
+    if (steep)
+    {
+      int tmp = x0; x0 = y0; y0 = tmp;
+      tmp = x1; x1 = y1; y1 = tmp;
+    }
+    const int deltax = abs(x1 - x0), deltay = abs(y1 - y0);
+    const int xstep = (x0 < x1) ? 1 : -1, ystep = (y0 < y1) ? 1 : -1;
+    int error = 0, x = x0, y = y0;
+    for (;;)
+    {
+      const int cx = steep ? y : x, cy = steep ? x : y;
+      steps++;
+      const bool valid = cx >= 0 && cx < size_x && cy >= 0 && cy < size_y;
+      if (!valid || cells[(size_t)cy * size_x + cx] != -1)
+      {
+        r = sqrt((double)((x - x0) * (x - x0) + (y - y0) * (y - y0))) * resolution;
+        break;
+      }
+      if (x == x1 + xstep)
+        break;
+      x += xstep;
+      error += deltay;
+      if (2 * error >= deltax)
+      {
+        y += ystep;
+        error -= deltax;
+      }
+    }
+  }
+  out[t] = r;
+  if (steps_total)
+    atomicAdd(steps_total, steps);
+}
+}  // namespace
+
+// the reference loop tests the start cell, then steps until x == x1 + xstep *after* testing; the kernel
+// above tests the cell at x1 + xstep too (the reference's while condition is checked before the step, so
+// the last tested x is x1 + xstep) -- see the parity test against the oracle.
+
+static int build_blocked_bits(bamcl_map2d* m)
+{
+  bamcl_ctx* ctx = m->ctx;
+  m->row_words = (m->size_x + 31) / 32;
+  m->col_words = (m->size_y + 31) / 32;
+  BAMCL_TRY(m->blocked_rows.reserve(sizeof(uint32_t) * (size_t)m->row_words * m->size_y));
+  BAMCL_TRY(m->blocked_cols.reserve(sizeof(uint32_t) * (size_t)m->col_words * m->size_x));
+  BAMCL_CUDA_OK(cudaMemsetAsync(m->blocked_cols.p, 0, sizeof(uint32_t) * (size_t)m->col_words * m->size_x, ctx->stream));
+  dim3 grid((m->row_words * 32 + 255) / 256, m->size_y);
+  BAMCL_LAUNCH(ctx, k_blocked_bits, grid, 256, 0, m->cells.as<int8_t>(), m->blocked_rows.as<uint32_t>(),
+               m->blocked_cols.as<uint32_t>(), m->size_x, m->size_y, m->row_words, m->col_words);
+  return BAMCL_OK;
+}
+
+extern "C" {
+
+int bamcl_map2d_create(bamcl_ctx* ctx, int size_x, int size_y, double resolution, float origin_x, float origin_y,
+                       bamcl_map2d** out)
+{
+  if (!ctx || !out || size_x < 0 || size_y < 0 || !(resolution > 0.0))
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_create: bad arguments");
+  bamcl_map2d* m = new bamcl_map2d();
+  m->ctx = ctx;
+  m->size_x = size_x;
+  m->size_y = size_y;
+  m->resolution = resolution;
+  m->origin_x = origin_x;
+  m->origin_y = origin_y;
+  m->tiles_x = (size_x + 7) / 8;
+  m->tiles_y = (size_y + 7) / 8;
+  if (const char* e = getenv("BAMCL_LAYOUT"))  // layout experiments (profiles/), default 0
+    m->layout = atoi(e) % 3;
+  *out = m;
+  return BAMCL_OK;
+}
+
+int bamcl_map2d_destroy(bamcl_map2d* m)
+{
+  if (!m)
+    return BAMCL_OK;
+  cudaStreamSynchronize(m->ctx->stream);
+  m->cells.release();
+  m->dist.release();
+  m->kmap.release();
+  m->blocked_rows.release();
+  m->blocked_cols.release();
+  delete m;
+  return BAMCL_OK;
+}
+
+int bamcl_map2d_set_cells(bamcl_map2d* m, const int8_t* cells, long n)
+{
+  if (!m || !cells || n != (long)m->size_x * m->size_y)
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_set_cells: need size_x*size_y cells");
+  if (n == 0)
+    return BAMCL_OK;
+  BAMCL_TRY(m->cells.reserve((size_t)n));
+  BAMCL_CUDA_OK(cudaMemcpyAsync(m->cells.p, cells, (size_t)n, cudaMemcpyHostToDevice, m->ctx->stream));
+  m->has_cells = true;
+  BAMCL_TRY(build_blocked_bits(m));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(m->ctx->stream));
+  return BAMCL_OK;
+}
+
+static int prepare_cache(bamcl_map2d* m, double max_distance)
+{
+  const size_t n = (size_t)m->size_x * m->size_y;
+  m->max_distance = max_distance;
+  m->cell_radius = (int)std::floor(max_distance / m->resolution);
+  // the field stores k*8 (the byte offset into the f64 value table) in 16 bits
+  if (((long)m->cell_radius * m->cell_radius + 2) * 8 > 65535)
+    return set_error(BAMCL_E_UNSUPPORTED, "max_distance/resolution = %d cells exceeds the u16 field (90 cells)",
+                     m->cell_radius);
+  BAMCL_TRY(m->dist.reserve(sizeof(float) * n));
+  BAMCL_TRY(m->kmap.reserve(sizeof(uint16_t) * (size_t)m->tiles_x * m->tiles_y * 64));
+  // cells of partial edge tiles that lie outside the map are never read; keep them defined anyway
+  BAMCL_CUDA_OK(cudaMemsetAsync(m->kmap.p, 0xFF, sizeof(uint16_t) * (size_t)m->tiles_x * m->tiles_y * 64, m->ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_map2d_build_distances(bamcl_map2d* m, double max_distance)
+{
+  if (!m)
+    return set_error(BAMCL_E_ARG, "null map");
+  if (!m->has_cells)
+    return set_error(BAMCL_E_STATE, "bamcl_map2d_build_distances: set_cells first");
+  m->max_distance = max_distance;
+  if (max_distance == 0.0)  // occupancy_map.cpp:141-145: nothing is built
+    return BAMCL_OK;
+  BAMCL_TRY(prepare_cache(m, max_distance));
+  bamcl_ctx* ctx = m->ctx;
+  const size_t n = (size_t)m->size_x * m->size_y;
+  DevBuf g;
+  BAMCL_TRY(g.reserve(sizeof(uint16_t) * n));
+  BAMCL_LAUNCH(ctx, k_edt_columns, (m->size_x + 127) / 128, 128, 0, m->cells.as<int8_t>(), g.as<uint16_t>(), m->size_x,
+               m->size_y, m->cell_radius);
+  constexpr int BLOCK = 256;
+  dim3 grid((m->size_x + BLOCK - 1) / BLOCK, m->size_y);
+  const size_t smem = sizeof(uint16_t) * (size_t)(BLOCK + 2 * m->cell_radius);
+  BAMCL_LAUNCH(ctx, k_edt_rows<BLOCK>, grid, BLOCK, smem, g.as<uint16_t>(), m->dist.as<float>(), m->kmap.as<uint16_t>(),
+               m->size_x, m->size_y, m->tiles_x, m->layout, m->cell_radius, m->resolution, (float)max_distance);
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  g.release();
+  m->has_dist = true;
+  m->version++;
+  return BAMCL_OK;
+}
+
+int bamcl_map2d_upload_distances(bamcl_map2d* m, const float* distances, long n, double max_distance)
+{
+  if (!m || !distances || n != (long)m->size_x * m->size_y || !(max_distance > 0.0))
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_upload_distances: bad arguments");
+  BAMCL_TRY(prepare_cache(m, max_distance));
+  bamcl_ctx* ctx = m->ctx;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(m->dist.p, distances, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+  DevBuf bad;
+  BAMCL_TRY(bad.reserve(sizeof(int)));
+  BAMCL_CUDA_OK(cudaMemsetAsync(bad.p, 0, sizeof(int), ctx->stream));
+  dim3 grid((m->size_x + 255) / 256, m->size_y);
+  BAMCL_LAUNCH(ctx, k_index_uploaded, grid, 256, 0, m->dist.as<float>(), m->kmap.as<uint16_t>(), m->size_x, m->size_y,
+               m->tiles_x, m->layout, m->cell_radius, m->resolution, (float)max_distance, bad.as<int>());
+  int h_bad = 0;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(&h_bad, bad.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  bad.release();
+  if (h_bad != 0)
+  {
+    m->has_dist = false;
+    return set_error(BAMCL_E_UNSUPPORTED,
+                     "%d cached distances are not of the form float(sqrt(k)*resolution) or float(max_distance)", h_bad);
+  }
+  m->has_dist = true;
+  m->version++;
+  return BAMCL_OK;
+}
+
+int bamcl_map2d_download_distances(bamcl_map2d* m, float* out, long n)
+{
+  if (!m || !out || n != (long)m->size_x * m->size_y)
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_download_distances: bad arguments");
+  if (!m->has_dist)
+    return set_error(BAMCL_E_STATE, "no distance cache has been built or uploaded");
+  BAMCL_CUDA_OK(cudaMemcpyAsync(out, m->dist.p, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, m->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(m->ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_map2d_calc_range(bamcl_map2d* m, const double* ox, const double* oy, const double* oa, long n,
+                           double max_range, double* ranges_out, long* steps_total_or_null)
+{
+  if (!m || !ox || !oy || !oa || !ranges_out || n < 0)
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_calc_range: bad arguments");
+  if (!m->has_cells)
+    return set_error(BAMCL_E_STATE, "bamcl_map2d_calc_range: set_cells first");
+  if (n == 0)
+    return BAMCL_OK;
+  bamcl_ctx* ctx = m->ctx;
+  DevBuf buf;
+  BAMCL_TRY(buf.reserve(sizeof(double) * 4 * (size_t)n + sizeof(unsigned long long)));
+  double* d = buf.as<double>();
+  unsigned long long* d_steps = reinterpret_cast<unsigned long long*>(d + 4 * n);
+  BAMCL_CUDA_OK(cudaMemcpyAsync(d, ox, sizeof(double) * n, cudaMemcpyHostToDevice, ctx->stream));
+  BAMCL_CUDA_OK(cudaMemcpyAsync(d + n, oy, sizeof(double) * n, cudaMemcpyHostToDevice, ctx->stream));
+  BAMCL_CUDA_OK(cudaMemcpyAsync(d + 2 * n, oa, sizeof(double) * n, cudaMemcpyHostToDevice, ctx->stream));
+  BAMCL_CUDA_OK(cudaMemsetAsync(d_steps, 0, sizeof(unsigned long long), ctx->stream));
+  BAMCL_LAUNCH(ctx, k_calc_range, (unsigned)((n + 127) / 128), 128, 0, m->cells.as<int8_t>(), m->size_x, m->size_y,
+               m->resolution, m->origin_x, m->origin_y, d, d + n, d + 2 * n, n, max_range, d + 3 * n, d_steps);
+  unsigned long long h_steps = 0;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(ranges_out, d + 3 * n, sizeof(double) * n, cudaMemcpyDeviceToHost, ctx->stream));
+  BAMCL_CUDA_OK(cudaMemcpyAsync(&h_steps, d_steps, sizeof(h_steps), cudaMemcpyDeviceToHost, ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  buf.release();
+  if (steps_total_or_null)
+    *steps_total_or_null = (long)h_steps;
+  return BAMCL_OK;
+}
+
+}  // extern "C"

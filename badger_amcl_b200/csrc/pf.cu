@@ -1,0 +1,327 @@
+// ParticleFilter device object: sample-set storage, host<->device sample exchange, weight total and
+// normalisation, and the update entry points. Reference: src/amcl/pf/particle_filter.cpp:38-98, 223-267.
+#include <cmath>
+#include <cstring>
+
+#include "pf.cuh"
+
+using namespace bamcl;
+
+namespace bamcl
+{
+int stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
+               const double* angles, int range_count, double range_max);
+int launch_score(bamcl_pf* pf, bamcl_map2d* map);
+}  // namespace bamcl
+
+namespace
+{
+__global__ void k_aos_to_soa(const double4* __restrict__ aos, double* __restrict__ x, double* __restrict__ y,
+                             double* __restrict__ th, double* __restrict__ w, int n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  const double4 s = aos[i];
+  x[i] = s.x;
+  y[i] = s.y;
+  th[i] = s.z;
+  w[i] = s.w;
+}
+__global__ void k_soa_to_aos(double4* __restrict__ aos, const double* __restrict__ x, const double* __restrict__ y,
+                             const double* __restrict__ th, const double* __restrict__ w, int n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  aos[i] = make_double4(x[i], y[i], th[i], w[i]);
+}
+__global__ void k_fill(double* __restrict__ p, double v, int n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    p[i] = v;
+}
+
+// ---- deterministic weight total: fixed-shape two-level tree (block partials, then one block).
+constexpr int RED_BLOCK = 256;
+constexpr int RED_ITEMS = 8;
+__global__ void __launch_bounds__(RED_BLOCK) k_sum_partials(const double* __restrict__ w, int n, double* __restrict__ partials)
+{
+  __shared__ double s[RED_BLOCK / 32];
+  const int base = blockIdx.x * RED_BLOCK * RED_ITEMS;
+  double v = 0.0;
+#pragma unroll
+  for (int t = 0; t < RED_ITEMS; t++)
+  {
+    const int i = base + t * RED_BLOCK + threadIdx.x;
+    if (i < n)
+      v += w[i];
+  }
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0)
+    s[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x < 32)
+  {
+    double t = threadIdx.x < RED_BLOCK / 32 ? s[threadIdx.x] : 0.0;
+    t = warp_sum(t);
+    if (threadIdx.x == 0)
+      partials[blockIdx.x] = t;
+  }
+}
+__global__ void __launch_bounds__(1024) k_sum_final(const double* __restrict__ partials, int m, double* __restrict__ total)
+{
+  __shared__ double s[32];
+  double v = 0.0;
+  for (int i = threadIdx.x; i < m; i += 1024)
+    v += partials[i];
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0)
+    s[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x < 32)
+  {
+    double t = s[threadIdx.x];
+    t = warp_sum(t);
+    if (threadIdx.x == 0)
+      *total = t;
+  }
+}
+
+// ---- ParticleFilter::updateSensor, particle_filter.cpp:237-266
+__global__ void k_normalise(double* __restrict__ w, int n, const double* __restrict__ total_p)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  const double total = *total_p;
+  if (total > 0.0)
+    w[i] = w[i] / total;
+  else
+    w[i] = 1.0 / n;
+}
+}  // namespace
+
+namespace bamcl
+{
+int pf_reduce_total(bamcl_pf* pf, double* d_total)
+{
+  SampleSet& set = pf->sets[pf->current];
+  const int n = set.sample_count;
+  const int blocks = (n + RED_BLOCK * RED_ITEMS - 1) / (RED_BLOCK * RED_ITEMS);
+  BAMCL_TRY(pf->partials.reserve(sizeof(double) * (size_t)(blocks + 1)));
+  if (blocks > 0)
+    BAMCL_LAUNCH(pf->ctx, k_sum_partials, blocks, RED_BLOCK, 0, set.w.as<double>(), n, pf->partials.as<double>());
+  BAMCL_LAUNCH(pf->ctx, k_sum_final, 1, 1024, 0, pf->partials.as<double>(), blocks, d_total);
+  return BAMCL_OK;
+}
+}  // namespace bamcl
+
+static int read_scalar(bamcl_pf* pf, int slot, double* out)
+{
+  BAMCL_CUDA_OK(cudaMemcpyAsync(pf->h_scalars.as<double>() + slot, pf->scalars.as<double>() + slot, sizeof(double),
+                                cudaMemcpyDeviceToHost, pf->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+  *out = pf->h_scalars.as<double>()[slot];
+  return BAMCL_OK;
+}
+
+extern "C" {
+
+int bamcl_pf_create(bamcl_ctx* ctx, int min_samples, int max_samples, bamcl_pf** out)
+{
+  if (!ctx || !out || max_samples <= 0 || min_samples < 0)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_create: bad arguments");
+  bamcl_pf* pf = new bamcl_pf();
+  pf->ctx = ctx;
+  pf->min_samples = min_samples;
+  pf->max_samples = max_samples;
+  const size_t bytes = sizeof(double) * (size_t)max_samples;
+  for (int j = 0; j < 2; j++)
+  {
+    SampleSet& s = pf->sets[j];
+    BAMCL_TRY(s.x.reserve(bytes));
+    BAMCL_TRY(s.y.reserve(bytes));
+    BAMCL_TRY(s.th.reserve(bytes));
+    BAMCL_TRY(s.w.reserve(bytes));
+    BAMCL_TRY(s.label.reserve(sizeof(int) * (size_t)max_samples));
+    // particle_filter.cpp:69-79: max_samples samples at the origin with weight 1/max_samples
+    s.sample_count = max_samples;
+    BAMCL_CUDA_OK(cudaMemsetAsync(s.x.p, 0, bytes, ctx->stream));
+    BAMCL_CUDA_OK(cudaMemsetAsync(s.y.p, 0, bytes, ctx->stream));
+    BAMCL_CUDA_OK(cudaMemsetAsync(s.th.p, 0, bytes, ctx->stream));
+    BAMCL_LAUNCH(ctx, k_fill, (max_samples + 255) / 256, 256, 0, s.w.as<double>(), 1.0 / max_samples, max_samples);
+  }
+  BAMCL_TRY(pf->scalars.reserve(sizeof(double) * 64));
+  BAMCL_TRY(pf->h_scalars.reserve(sizeof(double) * 64));
+  BAMCL_CUDA_OK(cudaMemsetAsync(pf->scalars.p, 0, sizeof(double) * 64, ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  *out = pf;
+  return BAMCL_OK;
+}
+
+int bamcl_pf_destroy(bamcl_pf* pf)
+{
+  if (!pf)
+    return BAMCL_OK;
+  cudaStreamSynchronize(pf->ctx->stream);
+  for (int j = 0; j < 2; j++)
+  {
+    SampleSet& s = pf->sets[j];
+    s.x.release();
+    s.y.release();
+    s.th.release();
+    s.w.release();
+    s.label.release();
+    s.cluster_stats.release();
+  }
+  pf->scan.beams.release();
+  pf->scan.table.release();
+  pf->scan.ranges.release();
+  pf->scan.angles.release();
+  pf->scalars.release();
+  pf->h_scalars.release();
+  pf->h_stage.release();
+  pf->d_stage.release();
+  pf->partials.release();
+  pf->cdf.release();
+  pf->src.release();
+  pf->scratch.release();
+  pf->scratch2.release();
+  pf->random_poses.release();
+  delete pf;
+  return BAMCL_OK;
+}
+
+int bamcl_pf_upload_samples(bamcl_pf* pf, const double* aos, long n)
+{
+  if (!pf || !aos || n < 0 || n > pf->max_samples)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_upload_samples: need 0 <= n <= max_samples");
+  SampleSet& s = pf->sets[pf->current];
+  s.sample_count = (int)n;
+  if (n == 0)
+    return BAMCL_OK;
+  bamcl_ctx* ctx = pf->ctx;
+  BAMCL_TRY(pf->d_stage.reserve(sizeof(double) * 4 * (size_t)n));
+  BAMCL_CUDA_OK(cudaMemcpyAsync(pf->d_stage.p, aos, sizeof(double) * 4 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+  BAMCL_LAUNCH(ctx, k_aos_to_soa, (unsigned)((n + 255) / 256), 256, 0, pf->d_stage.as<double4>(), s.x.as<double>(),
+               s.y.as<double>(), s.th.as<double>(), s.w.as<double>(), (int)n);
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_pf_download_samples(bamcl_pf* pf, double* aos, long n)
+{
+  if (!pf || !aos)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_download_samples: bad arguments");
+  SampleSet& s = pf->sets[pf->current];
+  if (n != s.sample_count)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_download_samples: n must equal sample_count (%d)", s.sample_count);
+  if (n == 0)
+    return BAMCL_OK;
+  bamcl_ctx* ctx = pf->ctx;
+  BAMCL_TRY(pf->d_stage.reserve(sizeof(double) * 4 * (size_t)n));
+  BAMCL_LAUNCH(ctx, k_soa_to_aos, (unsigned)((n + 255) / 256), 256, 0, pf->d_stage.as<double4>(), s.x.as<double>(),
+               s.y.as<double>(), s.th.as<double>(), s.w.as<double>(), (int)n);
+  BAMCL_CUDA_OK(cudaMemcpyAsync(aos, pf->d_stage.p, sizeof(double) * 4 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_pf_sample_count(bamcl_pf* pf, int* n)
+{
+  if (!pf || !n)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_sample_count: bad arguments");
+  *n = pf->sets[pf->current].sample_count;
+  return BAMCL_OK;
+}
+
+int bamcl_pf_upload_weights(bamcl_pf* pf, const double* w, long n)
+{
+  if (!pf || !w || n != pf->sets[pf->current].sample_count)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_upload_weights: n must equal sample_count");
+  BAMCL_CUDA_OK(cudaMemcpyAsync(pf->sets[pf->current].w.p, w, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, pf->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_pf_download_weights(bamcl_pf* pf, double* w, long n)
+{
+  if (!pf || !w || n != pf->sets[pf->current].sample_count)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_download_weights: n must equal sample_count");
+  BAMCL_CUDA_OK(cudaMemcpyAsync(w, pf->sets[pf->current].w.p, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, pf->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_pf_stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
+                        const double* angles, int range_count, double range_max)
+{
+  return stage_scan(pf, map, model, ranges, angles, range_count, range_max);
+}
+
+int bamcl_pf_score_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
+                          const double* angles, int range_count, double range_max, int converged, double* total_out)
+{
+  (void)converged;
+  if (!total_out)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_score_planar: total_out is required");
+  BAMCL_TRY(stage_scan(pf, map, model, ranges, angles, range_count, range_max));
+  if (model->max_beams < 2)  // planar_scanner.cpp:144
+  {
+    *total_out = 0.0;
+    return BAMCL_OK;
+  }
+  BAMCL_TRY(launch_score(pf, map));
+  BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
+  return read_scalar(pf, 0, total_out);
+}
+
+int bamcl_pf_normalise(bamcl_pf* pf, double total)
+{
+  if (!pf)
+    return set_error(BAMCL_E_ARG, "null pf");
+  SampleSet& s = pf->sets[pf->current];
+  if (s.sample_count == 0)
+    return BAMCL_OK;
+  pf->h_scalars.as<double>()[1] = total;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(pf->scalars.as<double>() + 1, pf->h_scalars.as<double>() + 1, sizeof(double),
+                                cudaMemcpyHostToDevice, pf->ctx->stream));
+  BAMCL_LAUNCH(pf->ctx, k_normalise, (s.sample_count + 255) / 256, 256, 0, s.w.as<double>(), s.sample_count,
+               pf->scalars.as<double>() + 1);
+  BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_pf_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out_or_null)
+{
+  (void)converged;
+  if (!pf || !map)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_update_planar_staged: bad arguments");
+  SampleSet& s = pf->sets[pf->current];
+  if (pf->scan.valid && pf->scan.model.max_beams < 2)  // updateSensor returns false, nothing happens (:128)
+  {
+    if (total_out_or_null)
+      *total_out_or_null = 0.0;
+    return BAMCL_OK;
+  }
+  BAMCL_TRY(launch_score(pf, map));
+  BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
+  if (s.sample_count > 0)
+    BAMCL_LAUNCH(pf->ctx, k_normalise, (s.sample_count + 255) / 256, 256, 0, s.w.as<double>(), s.sample_count,
+                 pf->scalars.as<double>());
+  if (total_out_or_null)
+    return read_scalar(pf, 0, total_out_or_null);
+  return BAMCL_OK;
+}
+
+int bamcl_pf_update_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
+                           const double* angles, int range_count, double range_max, int converged,
+                           double* total_out)
+{
+  BAMCL_TRY(stage_scan(pf, map, model, ranges, angles, range_count, range_max));
+  return bamcl_pf_update_planar_staged(pf, map, converged, total_out);
+}
+
+}  // extern "C"

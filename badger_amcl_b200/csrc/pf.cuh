@@ -1,0 +1,61 @@
+// ParticleFilter device state: two SoA sample sets + per-set kd-tree/cluster state + staged scan.
+#pragma once
+#include "common.cuh"
+#include "map2d.cuh"
+
+namespace bamcl
+{
+// One sample set (PFSampleSet, particle_filter.h:68-87) in SoA form.
+struct SampleSet
+{
+  DevBuf x, y, th, w;  // f64[max_samples]
+  int sample_count = 0;
+  // kd-tree histogram of this set as built at its creation (resample or init), pf_kdtree.cpp
+  int leaf_count = 0, node_count = 0, cluster_count = 0;
+  DevBuf label;          // int32[max_samples]: cluster label of every sample
+  DevBuf cluster_stats;  // f64[10 * cluster_count]
+  size_t cluster_cap = 0;
+};
+
+// Scan staged for the scoring kernel: valid beams only, in cell units.
+struct StagedScan
+{
+  bool valid = false;
+  bamcl_planar_model model;
+  int n_beams = 0;      // beams that survive the step / max-range / NaN filter
+  int n_slots = 0;      // beam_ind slots (prob model with beam skipping)
+  DevBuf beams;         // double2[n_beams]: (r cos b, r sin b) / resolution
+  DevBuf table;         // f64[table_n]: per-k model value
+  int table_n = 0;
+  double range_max = 0.0;
+  uint64_t map_version = 0;
+  // raw copies for the beam model
+  DevBuf ranges, angles;
+  int range_count = 0, step = 1;
+};
+}  // namespace bamcl
+
+struct bamcl_pf
+{
+  bamcl_ctx* ctx = nullptr;
+  int min_samples = 0, max_samples = 0;
+  bamcl::SampleSet sets[2];
+  int current = 0;
+  bamcl::StagedScan scan;
+  bamcl::DevBuf scalars;   // small device scratch for totals etc.
+  bamcl::PinBuf h_scalars; // pinned mirror
+  bamcl::PinBuf h_stage;   // pinned staging for uploads
+  bamcl::DevBuf d_stage;   // device staging (AoS <-> SoA)
+  bamcl::DevBuf partials;  // block partial sums
+  // resample scratch
+  bamcl::DevBuf cdf;       // f64[max_samples + 1]
+  bamcl::DevBuf src;       // int32[max_samples]
+  bamcl::DevBuf scratch;   // generic scratch, grown on demand
+  bamcl::DevBuf scratch2;
+  bamcl::DevBuf random_poses;
+};
+
+namespace bamcl
+{
+int pf_reduce_total(bamcl_pf* pf, double* d_total);  // deterministic sum of the current set's weights -> device scalar
+}

@@ -1,0 +1,405 @@
+// K-a: likelihood-field scoring of every particle against a planar scan (+ coordAdd + recalcWeight), and
+// the scan staging that feeds it. Reference: src/amcl/sensors/planar_scanner.cpp:141-164, 236-323,
+// 325-533, 552-640, 642-682, 693-701.
+//
+// Design (B200): the scan is staged once per call as the list of beams that survive the reference's
+// step / max-range / NaN filter, in cell units: (r cos b, r sin b) / resolution. A beam's end point for a
+// particle is then a 2x2 rotation in FP64 (4 DFMA; FP32 would flip ~2e-4 of the cell look-ups, SURVEY
+// H5) + a round-down magic add for the floor. The per-cell value comes from two small look-ups:
+//   k   = tiled u16 field (squared cell distance to the nearest obstacle), 32 MB for 4000^2 -> L2 resident
+//   val = table[k] in shared memory, built on the host with glibc's exp/log in the reference's own
+//         expression order (so every per-beam term is bit-identical to the reference's pz^3 / pz / log pz)
+// A warp owns a batch of PB particles and walks the beams in passes of 32*BPL: lane l holds BPL beams in
+// registers (adjacent lanes = adjacent beams = neighbouring cells -> shared sectors), particle data is
+// broadcast from shared memory, partial sums stay in registers until the batch ends.
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "pf.cuh"
+
+using namespace bamcl;
+
+namespace
+{
+constexpr int PB = 16;    // particles per warp batch
+constexpr int BPL = 4;    // beams per lane per pass
+constexpr int WARPS = 8;  // warps per block
+constexpr int PASS_BEAMS = 32 * BPL;
+
+struct ScoreArgs
+{
+  const double* x;
+  const double* y;
+  const double* th;
+  double* w;
+  int n;
+  const double2* beams;
+  int n_beams;
+  const double* table;
+  int table_n;
+  const uint16_t* kmap;
+  int tiles_x, size_x, size_y;
+  const int8_t* cells;
+  const float* dist;
+  double resolution;
+  float origin_x, origin_y;
+  double scan_x, scan_y, cos_sa, sin_sa;  // scanner mount (planar_scanner_pose_)
+  int model;
+  double gompertz_a, gompertz_b, gompertz_c, input_shift, input_scale, output_shift;
+  double off_map_factor, non_free_space_factor, non_free_space_radius;
+};
+
+template <bool TAIL, int LAYOUT>
+__device__ __forceinline__ void score_pass(const ScoreArgs& a, const unsigned char* __restrict__ tab, const double4* stash,
+                                           int beam0, int lane, double (&acc)[PB])
+{
+  double bx[BPL], by[BPL];
+  bool live[BPL];
+#pragma unroll
+  for (int q = 0; q < BPL; q++)
+  {
+    const int b = beam0 + q * 32 + lane;
+    live[q] = !TAIL || b < a.n_beams;
+    const double2 v = live[q] ? __ldg(&a.beams[b]) : make_double2(0.0, 0.0);
+    bx[q] = v.x;
+    by[q] = v.y;
+  }
+  const int k_off = (a.table_n - 1) * 8;
+#pragma unroll
+  for (int g = 0; g < PB; g++)
+  {
+    const double4 p = stash[g];  // cos, sin, X, Y (cell units, +0.5 and +size/2 folded in)
+#pragma unroll
+    for (int q = 0; q < BPL; q++)
+    {
+      const double gx = fma(p.x, bx[q], fma(-p.y, by[q], p.z));
+      const double gy = fma(p.y, bx[q], fma(p.x, by[q], p.w));
+      const int ix = floor_to_int(gx);
+      const int iy = floor_to_int(gy);
+      const bool inb = ((unsigned)ix < (unsigned)a.size_x) && ((unsigned)iy < (unsigned)a.size_y);
+      int k = k_off;
+      if (inb)
+        k = __ldg(&a.kmap[tiled_offset_t<LAYOUT>(ix, iy, a.tiles_x)]);
+      const double v = *reinterpret_cast<const double*>(tab + k);  // the field holds byte offsets
+      if (!TAIL || live[q])
+        acc[g] += v;
+    }
+  }
+}
+
+template <bool SMEM_TAB, int LAYOUT>
+__global__ void __launch_bounds__(WARPS * 32) k_score_lf(const ScoreArgs a)
+{
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  double4* s_stash = reinterpret_cast<double4*>(s_raw);                       // [WARPS][PB]
+  double* s_tab = reinterpret_cast<double*>(s_raw + sizeof(double4) * WARPS * PB);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (SMEM_TAB)
+  {
+    for (int t = threadIdx.x; t < a.table_n; t += blockDim.x)
+      s_tab[t] = a.table[t];
+    __syncthreads();
+  }
+  const unsigned char* tab = reinterpret_cast<const unsigned char*>(SMEM_TAB ? s_tab : a.table);
+  double4* stash = s_stash + warp * PB;
+  const int n_batches = (a.n + PB - 1) / PB;
+  const int warps_total = gridDim.x * WARPS;
+  const int n_full = a.n_beams / PASS_BEAMS;
+
+  for (int batch = blockIdx.x * WARPS + warp; batch < n_batches; batch += warps_total)
+  {
+    // ---- prologue: lane l < PB prepares particle batch*PB + l
+    const int idx = batch * PB + lane;
+    const bool mine = lane < PB && idx < a.n;
+    double w = 0.0, factor = 1.0;
+    if (lane < PB)
+    {
+      const int src = min(idx, a.n - 1);
+      const double px = a.x[src], py = a.y[src], pth = a.th[src];
+      w = a.w[src];
+      double s, c;
+      sincos(pth, &s, &c);
+      // coordAdd, planar_scanner.cpp:693-701 (the angle is only used through its sine and cosine)
+      const double sx = px + a.scan_x * c - a.scan_y * s;
+      const double sy = py + a.scan_x * s + a.scan_y * c;
+      const double c2 = c * a.cos_sa - s * a.sin_sa;
+      const double s2 = s * a.cos_sa + c * a.sin_sa;
+      double4 st;
+      st.x = c2;
+      st.y = s2;
+      st.z = (sx - (double)a.origin_x) / a.resolution + 0.5 + (double)(a.size_x / 2);
+      st.w = (sy - (double)a.origin_y) / a.resolution + 0.5 + (double)(a.size_y / 2);
+      stash[lane] = st;
+      // recalcWeight, planar_scanner.cpp:642-682 (uses the robot pose, not the scanner pose)
+      const int ci = world_to_cell(px, a.origin_x, a.resolution, a.size_x);
+      const int cj = world_to_cell(py, a.origin_y, a.resolution, a.size_y);
+      if (!(ci >= 0 && ci < a.size_x && cj >= 0 && cj < a.size_y))
+        factor = a.off_map_factor;
+      else if (a.cells[(size_t)cj * a.size_x + ci] != -1)
+        factor = a.non_free_space_factor;
+      else
+      {
+        const double distance = (double)a.dist[(size_t)cj * a.size_x + ci];
+        if (distance < a.non_free_space_radius)
+        {
+          const double delta_d = distance / a.non_free_space_radius;
+          factor = a.non_free_space_factor + delta_d * (1.0 - a.non_free_space_factor);
+        }
+      }
+    }
+    __syncwarp();
+
+    // ---- beams
+    double acc[PB];
+#pragma unroll
+    for (int g = 0; g < PB; g++)
+      acc[g] = 0.0;
+    for (int pass = 0; pass < n_full; pass++)
+      score_pass<false, LAYOUT>(a, tab, stash, pass * PASS_BEAMS, lane, acc);
+    if (n_full * PASS_BEAMS < a.n_beams)
+      score_pass<true, LAYOUT>(a, tab, stash, n_full * PASS_BEAMS, lane, acc);
+
+    // ---- reduce the PB partial sums across lanes; lane g keeps particle g's sum
+    double sum = 0.0;
+#pragma unroll
+    for (int g = 0; g < PB; g++)
+    {
+      const double v = warp_sum(acc[g]);
+      if (lane == g)
+        sum = v;
+    }
+    __syncwarp();
+
+    // ---- epilogue: model-specific combination + map factor
+    if (mine)
+    {
+      double p;
+      if (a.model == BAMCL_PLANAR_LF)
+        p = 1.0 + sum;  // planar_scanner.cpp:259,315
+      else if (a.model == BAMCL_PLANAR_LF_GOMPERTZ)
+      {
+        if (a.n_beams > 0)  // :624-633
+        {
+          p = sum / a.n_beams;
+          p = p * a.input_scale + a.input_shift;  // applyGompertz :540-550
+          p = a.gompertz_a * exp(-1.0 * a.gompertz_b * exp(-1.0 * a.gompertz_c * p));
+          p += a.output_shift;
+        }
+        else
+          p = 1.0;
+      }
+      else
+        p = exp(sum);  // :477
+      w *= p;
+      w *= factor;  // 1.0 where the reference leaves the weight alone (same value)
+      a.w[idx] = w;
+    }
+  }
+}
+}  // namespace
+
+// =============================================================================================
+// host side: scan staging
+// =============================================================================================
+namespace bamcl
+{
+// value of the model's per-beam term for a cached distance z, in the reference's expression order
+static double lf_term(const bamcl_planar_model& m, double z, double range_max)
+{
+  const double z_hit_denom = 2 * m.sigma_hit * m.sigma_hit;
+  double pz = 0.0;
+  if (m.model_type == BAMCL_PLANAR_LF)
+  {
+    const double z_rand_mult = 1.0 / range_max;
+    pz += m.z_hit * std::exp(-(z * z) / z_hit_denom);
+    pz += m.z_rand * z_rand_mult;
+    return pz * pz * pz;
+  }
+  if (m.model_type == BAMCL_PLANAR_LF_GOMPERTZ)
+  {
+    pz += m.z_hit * std::exp(-(z * z) / z_hit_denom);
+    pz += m.z_rand;
+    return pz;
+  }
+  const double z_rand_mult = 1.0 / range_max;
+  pz += m.z_hit * std::exp(-(z * z) / z_hit_denom);
+  pz += m.z_rand * z_rand_mult;
+  return std::log(pz);
+}
+
+int stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
+               const double* angles, int range_count, double range_max)
+{
+  StagedScan& sc = pf->scan;
+  sc.valid = false;
+  if (!pf || !map || !model || range_count < 0 || (range_count > 0 && (!ranges || !angles)))
+    return set_error(BAMCL_E_ARG, "stage_scan: bad arguments");
+  if (!map->has_dist)  // every planar model reads the cache through recalcWeight
+    return set_error(BAMCL_E_STATE, "the map has no distance cache (updateDistancesLUT / upload_distances first)");
+  sc.model = *model;
+  sc.range_max = range_max;
+  sc.map_version = map->version;
+  sc.range_count = range_count;
+  if (model->max_beams < 2)  // planar_scanner.cpp:128,144: nothing is applied
+  {
+    sc.n_beams = 0;
+    sc.valid = true;
+    return BAMCL_OK;
+  }
+  bamcl_ctx* ctx = pf->ctx;
+  const int type = model->model_type;
+  int step;
+  if (type == BAMCL_PLANAR_LF_PROB)
+    step = (int)std::ceil(range_count / static_cast<double>(model->max_beams));  // :339
+  else
+    step = (range_count - 1) / (model->max_beams - 1);  // :193,:265,:578
+  if (type == BAMCL_PLANAR_BEAM)
+  {
+    if (step < 1)  // the reference never terminates here
+      return set_error(BAMCL_E_ARG, "beam model needs range_count-1 >= max_beams-1 (reference loops forever)");
+  }
+  else if (step < 1)
+    step = 1;
+  sc.step = step;
+  if (type == BAMCL_PLANAR_LF_PROB && model->do_beamskip)
+    return set_error(BAMCL_E_UNSUPPORTED, "likelihood_field_prob with beam skipping is not implemented on the device yet");
+
+  if (type == BAMCL_PLANAR_BEAM)
+  {
+    BAMCL_TRY(sc.ranges.reserve(sizeof(double) * (size_t)(range_count + 1)));
+    BAMCL_TRY(sc.angles.reserve(sizeof(double) * (size_t)(range_count + 1)));
+    BAMCL_CUDA_OK(cudaMemcpyAsync(sc.ranges.p, ranges, sizeof(double) * range_count, cudaMemcpyHostToDevice, ctx->stream));
+    BAMCL_CUDA_OK(cudaMemcpyAsync(sc.angles.p, angles, sizeof(double) * range_count, cudaMemcpyHostToDevice, ctx->stream));
+    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    sc.valid = true;
+    return BAMCL_OK;
+  }
+
+  // beams that the reference integrates (:271-282), in cell units
+  const size_t max_beams = (size_t)(range_count / step + 2);
+  BAMCL_TRY(pf->h_stage.reserve(sizeof(double) * 2 * max_beams + sizeof(double) * 70000));
+  double* hb = pf->h_stage.as<double>();
+  int nb = 0;
+  for (int i = 0; i < range_count; i += step)
+  {
+    const double obs_range = ranges[i], obs_bearing = angles[i];
+    if (obs_range >= range_max)
+      continue;
+    if (obs_range != obs_range)
+      continue;
+    hb[2 * nb] = obs_range * std::cos(obs_bearing) / map->resolution;
+    hb[2 * nb + 1] = obs_range * std::sin(obs_bearing) / map->resolution;
+    nb++;
+  }
+  sc.n_beams = nb;
+  // value table over k = squared cell distance; [r2+1] = in-map cell beyond the radius; [r2+2] = off the map
+  const int r2 = map->cell_radius * map->cell_radius;
+  const int tn = r2 + 3;
+  double* ht = hb + 2 * max_beams;
+  for (int k = 0; k <= r2; k++)
+    ht[k] = lf_term(*model, (double)(float)(std::sqrt((double)k) * map->resolution), range_max);
+  ht[r2 + 1] = lf_term(*model, (double)(float)map->max_distance, range_max);
+  if (type == BAMCL_PLANAR_LF_PROB)
+  {
+    // :350,:443: off-map beams use exp(-max^2/denom) with the un-narrowed max distance
+    const double z_hit_denom = 2 * model->sigma_hit * model->sigma_hit;
+    const double max_dist_prob = std::exp(-(map->max_distance * map->max_distance) / z_hit_denom);
+    double pz = 0.0;
+    pz += model->z_hit * max_dist_prob;
+    pz += model->z_rand * (1.0 / range_max);
+    ht[r2 + 2] = std::log(pz);
+  }
+  else
+    ht[r2 + 2] = lf_term(*model, map->max_distance, range_max);  // :298,:613: z = getMaxDistanceToObject()
+  sc.table_n = tn;
+  BAMCL_TRY(sc.beams.reserve(sizeof(double) * 2 * (size_t)(nb + 1)));
+  BAMCL_TRY(sc.table.reserve(sizeof(double) * (size_t)tn));
+  if (nb > 0)
+    BAMCL_CUDA_OK(cudaMemcpyAsync(sc.beams.p, hb, sizeof(double) * 2 * nb, cudaMemcpyHostToDevice, ctx->stream));
+  BAMCL_CUDA_OK(cudaMemcpyAsync(sc.table.p, ht, sizeof(double) * tn, cudaMemcpyHostToDevice, ctx->stream));
+  // the pinned staging buffer is reused by the next call: wait for the copies
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  sc.valid = true;
+  return BAMCL_OK;
+}
+
+int launch_beam_model(bamcl_pf* pf, bamcl_map2d* map);  // score_beam.cu
+
+// enqueue the scoring of the current set with the staged scan (no synchronisation)
+int launch_score(bamcl_pf* pf, bamcl_map2d* map)
+{
+  StagedScan& sc = pf->scan;
+  if (!sc.valid)
+    return set_error(BAMCL_E_STATE, "no scan staged");
+  if (sc.map_version != map->version)
+    return set_error(BAMCL_E_STATE, "the map's distance cache changed after the scan was staged");
+  SampleSet& set = pf->sets[pf->current];
+  if (set.sample_count == 0 || sc.model.max_beams < 2)
+    return BAMCL_OK;
+  if (sc.model.model_type == BAMCL_PLANAR_BEAM)
+    return launch_beam_model(pf, map);
+  bamcl_ctx* ctx = pf->ctx;
+  ScoreArgs a;
+  a.x = set.x.as<double>();
+  a.y = set.y.as<double>();
+  a.th = set.th.as<double>();
+  a.w = set.w.as<double>();
+  a.n = set.sample_count;
+  a.beams = sc.beams.as<double2>();
+  a.n_beams = sc.n_beams;
+  a.table = sc.table.as<double>();
+  a.table_n = sc.table_n;
+  a.kmap = map->kmap.as<uint16_t>();
+  a.tiles_x = map->tiles_x;
+  a.size_x = map->size_x;
+  a.size_y = map->size_y;
+  a.cells = map->cells.as<int8_t>();
+  a.dist = map->dist.as<float>();
+  a.resolution = map->resolution;
+  a.origin_x = map->origin_x;
+  a.origin_y = map->origin_y;
+  a.scan_x = sc.model.scanner_pose[0];
+  a.scan_y = sc.model.scanner_pose[1];
+  a.cos_sa = std::cos(sc.model.scanner_pose[2]);
+  a.sin_sa = std::sin(sc.model.scanner_pose[2]);
+  a.model = sc.model.model_type;
+  a.gompertz_a = sc.model.gompertz_a;
+  a.gompertz_b = sc.model.gompertz_b;
+  a.gompertz_c = sc.model.gompertz_c;
+  a.input_shift = sc.model.input_shift;
+  a.input_scale = sc.model.input_scale;
+  a.output_shift = sc.model.output_shift;
+  a.off_map_factor = sc.model.off_map_factor;
+  a.non_free_space_factor = sc.model.non_free_space_factor;
+  a.non_free_space_radius = sc.model.non_free_space_radius;
+
+  const int n_batches = (a.n + PB - 1) / PB;
+  int blocks = (n_batches + WARPS - 1) / WARPS;
+  const int max_blocks = kNumSMs * 2;
+  if (blocks > max_blocks)
+    blocks = max_blocks;
+  const size_t stash_bytes = sizeof(double4) * WARPS * PB;
+  const size_t tab_bytes = sizeof(double) * (size_t)a.table_n;
+  const bool smem_tab = tab_bytes <= 40 * 1024;
+#define BAMCL_SCORE_CASE(L)                                                                          \
+  if (smem_tab)                                                                                      \
+    BAMCL_LAUNCH(ctx, (k_score_lf<true, L>), blocks, WARPS * 32, stash_bytes + tab_bytes, a);        \
+  else                                                                                               \
+    BAMCL_LAUNCH(ctx, (k_score_lf<false, L>), blocks, WARPS * 32, stash_bytes, a);
+  if (map->layout == 0)
+  {
+    BAMCL_SCORE_CASE(0)
+  }
+  else if (map->layout == 1)
+  {
+    BAMCL_SCORE_CASE(1)
+  }
+  else
+  {
+    BAMCL_SCORE_CASE(2)
+  }
+#undef BAMCL_SCORE_CASE
+  return BAMCL_OK;
+}
+}  // namespace bamcl

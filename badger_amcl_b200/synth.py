@@ -158,3 +158,12 @@ class Drand48:
 
     def state(self):
         return self.x
+
+
+def reference_test_map():
+    """The 100 x 150 map of the reference's own testOccupancyMapDistances (test/test_badger_amcl.cpp:131-154)."""
+    cells = np.full((150, 100), FREE, np.int8)
+    cells[3:12, 1] = UNKNOWN
+    cells[10, 5:14] = OCCUPIED
+    cells[15, 5:14] = OCCUPIED
+    return cells

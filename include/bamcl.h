@@ -1,0 +1,177 @@
+/* include/bamcl.h -- C ABI of libbamcl_cuda.so (sm_100a), the device side of the badger_amcl hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types. The host
+ * C++ classes that mirror the reference API (badger_amcl_b200/host/amcl/...) and the Python test/bench
+ * binding (badger_amcl_b200/cabi.py) call ONLY these entry points. Each entry cites the reference
+ * interface it replaces (paths relative to /root/reference).
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative BAMCL_E_* code otherwise; bamcl_last_error() gives text
+ *  - host buffers are caller-owned; device buffers are owned by the handles
+ *  - particles on the host side are the reference's AoS PFSample {double pose[3]; double weight} = 4 doubles
+ *    (particle_filter.h:41-49); on the device they are SoA (x, y, theta, w as separate f64 arrays)
+ *  - all work is enqueued on the context's stream; functions that return scalars synchronise that stream
+ *  - there is no CPU fallback: without a CUDA device every entry point fails with BAMCL_E_CUDA
+ */
+#ifndef BAMCL_H
+#define BAMCL_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BAMCL_OK 0
+#define BAMCL_E_CUDA -1       /* CUDA runtime error (text in bamcl_last_error) */
+#define BAMCL_E_ARG -2        /* invalid argument / precondition of the reference violated */
+#define BAMCL_E_UNSUPPORTED -3 /* input outside what the device path represents (e.g. non-canonical cache) */
+#define BAMCL_E_STATE -4      /* call order violated (e.g. scoring before a distance cache exists) */
+
+typedef struct bamcl_ctx bamcl_ctx;
+typedef struct bamcl_map2d bamcl_map2d;
+typedef struct bamcl_map3d bamcl_map3d;
+typedef struct bamcl_pf bamcl_pf;
+
+const char* bamcl_last_error(void);
+int bamcl_version(void);
+
+/* ---- context: one per GPU (one process per GPU in multi-GPU runs) */
+int bamcl_ctx_create(int device, bamcl_ctx** out);
+int bamcl_ctx_destroy(bamcl_ctx* ctx);
+int bamcl_ctx_sync(bamcl_ctx* ctx);
+/* cudaStream_t of the context (for event timing / NCCL on the same stream) */
+void* bamcl_ctx_stream(bamcl_ctx* ctx);
+/* CUDA-event stopwatch on the context's stream */
+int bamcl_timer_start(bamcl_ctx* ctx);
+int bamcl_timer_stop_ms(bamcl_ctx* ctx, float* ms);
+/* kernels launched by this library through this context since creation (bench.py "gpu_launches") */
+long bamcl_ctx_launch_count(bamcl_ctx* ctx);
+/* write a buffer larger than L2 (bench hygiene between timed iterations) */
+int bamcl_ctx_flush_l2(bamcl_ctx* ctx);
+
+/* ---- OccupancyMap (include/amcl/map/occupancy_map.h:57-81) */
+/* ctor + setSize + setOrigin (occupancy_map.cpp:30-57) */
+int bamcl_map2d_create(bamcl_ctx* ctx, int size_x, int size_y, double resolution, float origin_x, float origin_y,
+                       bamcl_map2d** out);
+int bamcl_map2d_destroy(bamcl_map2d* m);
+/* setCellState for every cell (occupancy_map.cpp:112-115); cells[i + j*size_x] in {-1 free, 0 unknown, +1 occupied} */
+int bamcl_map2d_set_cells(bamcl_map2d* m, const int8_t* cells, long n);
+/* updateDistancesLUT (occupancy_map.cpp:138-160): builds the distance cache on the device as the EXACT capped
+ * Euclidean distance transform with the reference's value formula (the reference's heap-order
+ * brushfire is >= this in a few % of cells and cannot be reproduced in parallel). */
+int bamcl_map2d_build_distances(bamcl_map2d* m, double max_distance);
+/* install a precomputed distance cache (e.g. the reference's own brushfire result); values must be of the
+ * form (float)(sqrt(k)*resolution), k integer, or (float)max_distance -- what updateDistancesLUT can produce */
+int bamcl_map2d_upload_distances(bamcl_map2d* m, const float* distances, long n, double max_distance);
+/* distances_lut_ readback (getDistanceToObject, occupancy_map.cpp:64-73) */
+int bamcl_map2d_download_distances(bamcl_map2d* m, float* out, long n);
+/* calcRange (occupancy_map.cpp:257-364) for a batch of rays; steps_total_or_null gets the number of cells tested */
+int bamcl_map2d_calc_range(bamcl_map2d* m, const double* ox, const double* oy, const double* oa, long n,
+                           double max_range, double* ranges_out, long* steps_total_or_null);
+
+/* ---- PlanarScanner (include/amcl/sensors/planar_scanner.h:62-96) */
+enum
+{
+  BAMCL_PLANAR_BEAM = 0,       /* setModelBeam :64 */
+  BAMCL_PLANAR_LF = 1,         /* setModelLikelihoodField :66 */
+  BAMCL_PLANAR_LF_PROB = 2,    /* setModelLikelihoodFieldProb :69 */
+  BAMCL_PLANAR_LF_GOMPERTZ = 3 /* setModelLikelihoodFieldGompertz :73 */
+};
+typedef struct
+{
+  int model_type;
+  int max_beams; /* init :62 */
+  double z_hit, z_short, z_max, z_rand, sigma_hit, lambda_short;
+  double gompertz_a, gompertz_b, gompertz_c, input_shift, input_scale, output_shift;
+  int do_beamskip;
+  double beam_skip_distance, beam_skip_threshold, beam_skip_error_threshold;
+  double off_map_factor, non_free_space_factor, non_free_space_radius; /* setMapFactors :82 */
+  double scanner_pose[3];                                              /* setPlanarScannerPose :93 */
+} bamcl_planar_model;
+
+/* ---- ParticleFilter (include/amcl/pf/particle_filter.h:96-130) */
+/* ctor (particle_filter.cpp:38-98): two sample sets of max_samples, uniform weights 1/max_samples */
+int bamcl_pf_create(bamcl_ctx* ctx, int min_samples, int max_samples, bamcl_pf** out);
+int bamcl_pf_destroy(bamcl_pf* pf);
+/* current set <- host AoS (what initWithPoseFn/initWithGaussian/Odom::updateAction write through
+ * getCurrentSet()); sets sample_count = n */
+int bamcl_pf_upload_samples(bamcl_pf* pf, const double* aos, long n);
+int bamcl_pf_download_samples(bamcl_pf* pf, double* aos, long n);
+int bamcl_pf_sample_count(bamcl_pf* pf, int* n);
+/* weights only (n doubles) */
+int bamcl_pf_upload_weights(bamcl_pf* pf, const double* w, long n);
+int bamcl_pf_download_weights(bamcl_pf* pf, double* w, long n);
+
+/* PlanarScanner::applyModelToSampleSet (planar_scanner.cpp:141-164) on the current set: the four models
+ * (:168,:236,:325,:552), coordAdd (:693) and recalcWeight (:642) in one launch. `converged` is
+ * set->converged (beam skipping, :361). total_out receives the returned total (synchronises). */
+int bamcl_pf_score_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
+                          const double* angles, int range_count, double range_max, int converged, double* total_out);
+/* ParticleFilter::updateSensor after the sensor model returned `total` (particle_filter.cpp:237-266):
+ * w /= total, or 1/n each if total <= 0. */
+int bamcl_pf_normalise(bamcl_pf* pf, double total);
+/* fused PlanarScanner::updateSensor (planar_scanner.cpp:125-137): score + total + normalise with no host
+ * round trip in between; total_out as above (w_avg of :240-248 is total / sample_count). */
+int bamcl_pf_update_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
+                           const double* angles, int range_count, double range_max, int converged,
+                           double* total_out);
+/* Same, with the scan already staged on the device by bamcl_pf_stage_scan (bench "inputs resident in HBM"). */
+int bamcl_pf_stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
+                        const double* angles, int range_count, double range_max);
+int bamcl_pf_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out_or_null);
+
+/* sequential CDF c[0..n] of the current set's weights exactly as particle_filter.cpp:280-285 rounds it */
+int bamcl_pf_cdf(bamcl_pf* pf, double* c_out, long n_plus_1);
+
+typedef struct
+{
+  int resample_systematic;  /* setResampleModel :100 (1 = PF_RESAMPLE_SYSTEMATIC) */
+  int min_samples, max_samples;
+  double pop_err, pop_z;    /* setPopulationSizeParameters :121 */
+  double w_diff;            /* max(0, 1 - w_fast/w_slow), particle_filter.cpp:438-440 */
+  double dist_threshold;    /* 0.5, particle_filter.cpp:60 */
+  double convergence_threshold; /* global_localization_convergence_threshold_ */
+  /* drand48 contract: the host hands over the generator state; the device consumes draws
+   * exactly like the reference (1 draw for systematic, :309; 2 per output for multinomial, :385,:393)
+   * and returns the advanced state. */
+  uint64_t drand48_state;
+  /* poses returned by random_pose_fn_ (:320,:387), in call order; n_random_poses available */
+  const double* random_poses;
+  long n_random_poses;
+} bamcl_resample_params;
+
+typedef struct
+{
+  int sample_count;       /* set_b->sample_count */
+  int leaf_count;         /* set_b->kdtree->getLeafCount() (pf_kdtree.cpp:92) */
+  int node_count;         /* number of kd-tree nodes = occupied pose bins */
+  int cluster_count;      /* set->cluster_count */
+  int converged;          /* updateConverged (particle_filter.cpp:170-220) */
+  int random_poses_used;
+  int status_flags;       /* bit0: a systematic target fell at/after c[P] (reference would hang) */
+  int reserved;
+  uint64_t drand48_state; /* generator state after the draws */
+  double mean[3];         /* set->mean */
+  double cov[5];          /* set->cov (0,0) (0,1) (1,0) (1,1) (2,2) */
+} bamcl_resample_result;
+
+/* ParticleFilter::updateResample (particle_filter.cpp:423-471): KLD-adaptive systematic (:269) or
+ * multinomial (:356) resampling into the other set, kd-tree histogram (pf_kdtree.cpp:49-150), clustering
+ * (:58-76,:169-194), cluster/set statistics (particle_filter.cpp:505-636), set swap, updateConverged. */
+int bamcl_pf_resample(bamcl_pf* pf, const bamcl_resample_params* params, bamcl_resample_result* result);
+/* kd-tree + cluster statistics of the CURRENT set as initWithPoseFn/initWithGaussian compute them
+ * (particle_filter.cpp:106-162): fills leaf_count, node_count, cluster_count, mean, cov. */
+int bamcl_pf_init_stats(bamcl_pf* pf, bamcl_resample_result* result);
+/* source index in the previous set of every sample of the last resample (-1 = random pose) */
+int bamcl_pf_resample_sources(bamcl_pf* pf, int* src, long n);
+/* cluster label of every sample of the current set (PFKDTree::getCluster, pf_kdtree.cpp:79-90) */
+int bamcl_pf_sample_clusters(bamcl_pf* pf, int* labels, long n);
+/* per cluster 10 doubles: count, weight, mean[3], cov(0,0),(0,1),(1,0),(1,1),(2,2) (getClusterStats :639) */
+int bamcl_pf_cluster_stats(bamcl_pf* pf, double* out, int max_clusters);
+/* resampleLimit (particle_filter.cpp:475-502), host arithmetic exposed for parity tests */
+int bamcl_resample_limit(int k, int min_samples, int max_samples, double pop_err, double pop_z);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

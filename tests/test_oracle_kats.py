@@ -106,24 +106,13 @@ def test_occupancy_map_conversions_kat(oracle_built, backend):
     assert m.world_to_map(.05, .1) == (1, 2)
 
 
-def _kat_map():
-    cells = np.full((150, 100), synth.FREE, np.int8)
-    for x in range(100):
-        for y in range(150):
-            if x == 1 and 2 < y < 12:
-                cells[y, x] = synth.UNKNOWN
-            elif 4 < x < 14 and y in (10, 15):
-                cells[y, x] = synth.OCCUPIED
-    return cells
-
-
 @pytest.mark.parametrize("backend", BACKENDS)
 def test_occupancy_map_distances_kat(oracle_built, backend):
     """test_badger_amcl.cpp:131-171"""
     O = oracle_built
     _skip_if_no_ref(O, backend)
     res = 0.05
-    cells = _kat_map()
+    cells = synth.reference_test_map()
     origin = (100 // 2 * res, 150 // 2 * res)
     m = (O.PortMap2D if backend == "port" else O.RefMap2D)(cells, res, origin)
     assert m.is_valid(0, 0) and not m.is_valid(-1, 5) and m.is_valid(99, 149)

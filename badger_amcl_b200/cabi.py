@@ -101,6 +101,7 @@ SIGNATURES = {
     "bamcl_pf_sample_clusters": (_I, [_P, _P, _L]),
     "bamcl_pf_cluster_stats": (_I, [_P, _P, _I]),
     "bamcl_resample_limit": (_I, [_I, _I, _I, _D, _D]),
+    "bamcl_systematic_targets": (_I, [_D, _D, _L, _P]),
 }
 
 

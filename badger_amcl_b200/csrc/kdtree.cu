@@ -1,0 +1,709 @@
+// K-d3/K-d4: the pose histogram "kd-tree" of a sample set, its KLD leaf count, cluster labels and the cluster /
+// set statistics. Reference: src/amcl/pf/pf_kdtree.cpp:49-194, src/amcl/pf/particle_filter.cpp:170-220, 505-636.
+//
+// What the reference's insertion-order BST observably produces:
+//   * one node per distinct integer key floor(pose / (0.5, 0.5, 10 deg)), in order of first occurrence;
+//   * leaf_count = number of nodes that no later key was ever routed through. A node fixes its pivot dimension
+//     from the first foreign key that reaches it (largest |delta|, lowest dimension on ties) and routes by
+//     key[pivot] > node.key[pivot];
+//   * cluster labels = connected components under the 26-neighbourhood, numbered by their earliest node.
+// Device construction: a hash table gives every distinct key its first-occurrence sample index; a scan turns
+// that into creation-order node ids; the tree is then grown for ALL keys at once, one level per step (every
+// key still travelling sits at the node it has reached; the smallest id among the keys at a node is that node's
+// first foreign key, the smallest id per side becomes the child) inside one cooperative kernel; components
+// come from a lock-free union-find that always hooks the larger root under the smaller, so a root is its
+// component's earliest node and ranking the roots reproduces the reference's numbering.
+#include <cooperative_groups.h>
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstring>
+
+#include "pf.cuh"
+#include "scan.cuh"
+
+namespace cg = cooperative_groups;
+using namespace bamcl;
+
+namespace
+{
+constexpr unsigned long long EMPTY_KEY = ~0ull;
+constexpr int NONE = INT_MAX;
+constexpr int ROW = 10;  // per cluster: count, weight, m0, m1, m2, m3, c00, c01, c10, c11
+
+struct TreeOut
+{
+  int K;     // nodes
+  int C;     // clusters
+  int leaf;  // childless nodes
+  int conv;  // samples within dist_threshold of the mean
+  int err;   // bit0 key out of the packed range, bit1 cluster rows exhausted
+  int level_flags[3];
+  int levels;
+  int pad;
+  double set_sums[12];  // weight, m0..m3, c00..c11, count, sum x, sum y
+};
+
+__host__ __device__ __forceinline__ unsigned long long pack_key(int kx, int ky, int kt)
+{
+  return (unsigned long long)(unsigned)(kx + (1 << 20)) | ((unsigned long long)(unsigned)(ky + (1 << 20)) << 21) |
+         ((unsigned long long)(unsigned)(kt + (1 << 21)) << 42);
+}
+__device__ __forceinline__ void unpack_key(unsigned long long k, int* kx, int* ky, int* kt)
+{
+  *kx = (int)(k & 0x1FFFFF) - (1 << 20);
+  *ky = (int)((k >> 21) & 0x1FFFFF) - (1 << 20);
+  *kt = (int)((k >> 42) & 0x3FFFFF) - (1 << 21);
+}
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z)
+{
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+  return z ^ (z >> 31);
+}
+
+// ---- 1. distinct keys and their first occurrence
+__global__ void __launch_bounds__(256) k_hash_insert(const double* __restrict__ x, const double* __restrict__ y,
+                                                     const double* __restrict__ th, int n, double cx, double cy, double ct,
+                                                     unsigned long long* __restrict__ hkeys, int* __restrict__ hfirst,
+                                                     unsigned hmask, int* __restrict__ slot_out, TreeOut* out)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  // pf_kdtree.cpp:51-54
+  const double fx = floor(x[i] / cx), fy = floor(y[i] / cy), ft = floor(th[i] / ct);
+  if (!(fabs(fx) < 1048575.0) || !(fabs(fy) < 1048575.0) || !(fabs(ft) < 2097151.0))
+  {
+    atomicOr(&out->err, 1);
+    slot_out[i] = 0;
+    return;
+  }
+  const unsigned long long key = pack_key((int)fx, (int)fy, (int)ft);
+  unsigned s = (unsigned)mix64(key) & hmask;
+  for (;;)
+  {
+    const unsigned long long cur = hkeys[s];
+    if (cur == key)
+      break;
+    if (cur == EMPTY_KEY)
+    {
+      const unsigned long long old = atomicCAS(&hkeys[s], EMPTY_KEY, key);
+      if (old == EMPTY_KEY || old == key)
+        break;
+    }
+    s = (s + 1) & hmask;
+  }
+  atomicMin(&hfirst[s], i);
+  slot_out[i] = (int)s;
+}
+
+__global__ void __launch_bounds__(256) k_flag_first(const int* __restrict__ slot, const int* __restrict__ hfirst,
+                                                    int* __restrict__ flag, int n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    flag[i] = hfirst[slot[i]] == i ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(256) k_make_nodes(const int* __restrict__ slot, const int* __restrict__ hfirst,
+                                                    const int* __restrict__ rank, const unsigned long long* __restrict__ hkeys,
+                                                    int* __restrict__ hnode, unsigned long long* __restrict__ nkey,
+                                                    int* __restrict__ nfirst, int n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  const int s = slot[i];
+  if (hfirst[s] != i)
+    return;
+  const int id = rank[i];
+  nkey[id] = hkeys[s];
+  nfirst[id] = i;
+  hnode[s] = id;
+}
+
+// ---- 2. the tree, one level per step
+struct TreeArgs
+{
+  TreeOut* out;
+  const unsigned long long* nkey;
+  int* cur;       // node a key currently sits at, -1 once it has become a tree node itself
+  int* child;     // [2 * K]
+  int* first_at;  // smallest id among the keys that reached a node = its first foreign key
+  signed char* side;
+  int* parent;  // union-find forest for the clustering step, initialised here
+};
+
+__global__ void __launch_bounds__(256) k_tree_build(const TreeArgs a)
+{
+  cg::grid_group grid = cg::this_grid();
+  const int K = a.out->K;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+  for (int v = tid; v < K; v += nth)
+  {
+    a.child[2 * v] = a.child[2 * v + 1] = NONE;
+    a.first_at[v] = (v == 0 && K > 1) ? 1 : NONE;
+    a.cur[v] = v == 0 ? -1 : 0;
+    a.parent[v] = v;
+  }
+  grid.sync();
+  int level = 0;
+  for (;;)
+  {
+    // every travelling key picks its side at the node it sits at (pf_kdtree.cpp:131-150)
+    for (int v = tid; v < K; v += nth)
+    {
+      const int u = a.cur[v];
+      if (u < 0)
+        continue;
+      const int f = a.first_at[u];
+      int ku[3], kf[3], kv[3];
+      unpack_key(a.nkey[u], &ku[0], &ku[1], &ku[2]);
+      unpack_key(a.nkey[f], &kf[0], &kf[1], &kf[2]);
+      unpack_key(a.nkey[v], &kv[0], &kv[1], &kv[2]);
+      int pivot = 0, max_split = 0;
+#pragma unroll
+      for (int d = 0; d < 3; d++)
+      {
+        const int split = abs(kf[d] - ku[d]);
+        if (split > max_split)
+        {
+          max_split = split;
+          pivot = d;
+        }
+      }
+      const int sd = kv[pivot] > ku[pivot] ? 1 : 0;
+      a.side[v] = (signed char)sd;
+      atomicMin(&a.child[2 * u + sd], v);
+    }
+    grid.sync();
+    bool any = false;
+    for (int v = tid; v < K; v += nth)
+    {
+      const int u = a.cur[v];
+      if (u < 0)
+        continue;
+      const int c = a.child[2 * u + a.side[v]];
+      if (c == v)
+        a.cur[v] = -1;
+      else
+      {
+        a.cur[v] = c;
+        atomicMin(&a.first_at[c], v);
+        any = true;
+      }
+    }
+    if (any)
+      a.out->level_flags[level % 3] = 1;
+    grid.sync();
+    const int more = *((volatile int*)&a.out->level_flags[level % 3]);
+    if (tid == 0)
+      a.out->level_flags[(level + 1) % 3] = 0;
+    level++;
+    if (!more)
+      break;
+  }
+  int cnt = 0;
+  for (int v = tid; v < K; v += nth)
+    cnt += (a.child[2 * v] == NONE && a.child[2 * v + 1] == NONE) ? 1 : 0;
+  cnt = warp_sum_i(cnt);
+  if ((threadIdx.x & 31) == 0 && cnt)
+    atomicAdd(&a.out->leaf, cnt);
+  if (tid == 0)
+    a.out->levels = level;
+}
+
+// ---- 3. connected components (pf_kdtree.cpp:58-76, 169-194)
+__device__ __forceinline__ int uf_find(int* parent, int v)
+{
+  int cur = *((volatile int*)&parent[v]);
+  if (cur != v)
+  {
+    int prev = v, next;
+    while (cur > (next = *((volatile int*)&parent[cur])))
+    {
+      parent[prev] = next;
+      prev = cur;
+      cur = next;
+    }
+  }
+  return cur;
+}
+__device__ __forceinline__ void uf_union(int* parent, int a, int b)
+{
+  int ra = uf_find(parent, a), rb = uf_find(parent, b);
+  bool repeat;
+  do
+  {
+    repeat = false;
+    if (ra != rb)
+    {
+      int ret;
+      if (ra < rb)
+      {
+        if ((ret = atomicCAS(&parent[rb], rb, ra)) != rb)
+        {
+          rb = ret;
+          repeat = true;
+        }
+      }
+      else
+      {
+        if ((ret = atomicCAS(&parent[ra], ra, rb)) != ra)
+        {
+          ra = ret;
+          repeat = true;
+        }
+      }
+    }
+  } while (repeat);
+}
+
+__global__ void __launch_bounds__(256) k_cc_union(const TreeOut* __restrict__ out, const unsigned long long* __restrict__ nkey,
+                                                  const unsigned long long* __restrict__ hkeys, const int* __restrict__ hnode,
+                                                  unsigned hmask, int* parent, int n_max)
+{
+  const int K = out->K;
+  // one thread per (node, neighbour offset in the positive half space): 13 offsets
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int v = (int)(t / 13);
+  const int o = (int)(t % 13) + 14;  // offsets 14..26 of the 27 = lexicographically after (0,0,0)
+  if (v >= K || v >= n_max)
+    return;
+  int kx, ky, kt;
+  unpack_key(nkey[v], &kx, &ky, &kt);
+  const int dx = o / 9 - 1, dy = (o % 9) / 3 - 1, dt = (o % 9) % 3 - 1;
+  const int nx = kx + dx, ny = ky + dy, nt = kt + dt;
+  if (abs(nx) >= (1 << 20) - 1 || abs(ny) >= (1 << 20) - 1 || abs(nt) >= (1 << 21) - 1)
+    return;
+  const unsigned long long key = pack_key(nx, ny, nt);
+  unsigned s = (unsigned)mix64(key) & hmask;
+  for (;;)
+  {
+    const unsigned long long cur = hkeys[s];
+    if (cur == EMPTY_KEY)
+      return;
+    if (cur == key)
+      break;
+    s = (s + 1) & hmask;
+  }
+  uf_union(parent, v, hnode[s]);
+}
+
+__global__ void __launch_bounds__(256) k_cc_roots(const TreeOut* __restrict__ out, int* parent, int* __restrict__ is_root,
+                                                  int n)
+{
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n)
+    return;
+  const int K = out->K;
+  if (v >= K)
+  {
+    is_root[v] = 0;
+    return;
+  }
+  const int r = uf_find(parent, v);
+  parent[v] = r;
+  is_root[v] = r == v ? 1 : 0;
+}
+
+// ---- 4. labels + statistics (particle_filter.cpp:505-636)
+struct StatsArgs
+{
+  const double *x, *y, *th, *w;
+  int n;
+  const int* slot;
+  const int* hnode;
+  const int* parent;
+  const int* cid;
+  int* label;
+  double* rows;  // [cap][ROW]
+  int cap;
+  TreeOut* out;
+};
+constexpr int ST_BLOCK = 256;
+constexpr int ST_CHUNKS = 8;  // chunks of 32 samples per warp
+
+__device__ __forceinline__ void flush_rows(double* rows, int cap, int label, const double (&v)[ROW], TreeOut* out)
+{
+  if (label < 0)
+    return;
+  if (label >= cap)
+  {
+    atomicOr(&out->err, 2);
+    return;
+  }
+#pragma unroll
+  for (int q = 0; q < ROW; q++)
+    atomicAdd(&rows[(size_t)label * ROW + q], v[q]);
+}
+
+__global__ void __launch_bounds__(ST_BLOCK) k_labels_stats(const StatsArgs a)
+{
+  __shared__ double s_set[ST_BLOCK / 32][12];
+  __shared__ double s_open[ST_BLOCK / 32][ROW];
+  __shared__ int s_open_label[ST_BLOCK / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int warp_base = (blockIdx.x * (ST_BLOCK / 32) + warp) * (32 * ST_CHUNKS);
+  double setv[12];
+#pragma unroll
+  for (int q = 0; q < 12; q++)
+    setv[q] = 0.0;
+  double open[ROW];
+#pragma unroll
+  for (int q = 0; q < ROW; q++)
+    open[q] = 0.0;
+  int open_label = -1;  // warp-uniform
+  for (int ch = 0; ch < ST_CHUNKS; ch++)
+  {
+    const int i = warp_base + ch * 32 + lane;
+    const bool live = i < a.n;
+    int label = -1;
+    double v[ROW];
+#pragma unroll
+    for (int q = 0; q < ROW; q++)
+      v[q] = 0.0;
+    if (live)
+    {
+      const int node = a.hnode[a.slot[i]];
+      label = a.cid[a.parent[node]];
+      a.label[i] = label;
+      const double px = a.x[i], py = a.y[i], pt = a.th[i], pw = a.w[i];
+      double sn, cs;
+      sincos(pt, &sn, &cs);
+      v[0] = 1.0;
+      v[1] = pw;
+      v[2] = pw * px;
+      v[3] = pw * py;
+      v[4] = pw * cs;
+      v[5] = pw * sn;
+      v[6] = pw * px * px;
+      v[7] = pw * px * py;
+      v[8] = pw * py * px;
+      v[9] = pw * py * py;
+      setv[0] += pw;
+      setv[1] += v[2];
+      setv[2] += v[3];
+      setv[3] += v[4];
+      setv[4] += v[5];
+      setv[5] += v[6];
+      setv[6] += v[7];
+      setv[7] += v[8];
+      setv[8] += v[9];
+      setv[9] += 1.0;
+      setv[10] += px;
+      setv[11] += py;
+    }
+    const unsigned live_mask = __ballot_sync(0xffffffffu, live);
+    if (live_mask == 0)
+      break;
+    const int first_label = __shfl_sync(0xffffffffu, label, __ffs(live_mask) - 1);
+    const bool uniform = __all_sync(0xffffffffu, !live || label == first_label);
+    if (uniform && (open_label == first_label || open_label < 0))
+    {
+      open_label = first_label;
+#pragma unroll
+      for (int q = 0; q < ROW; q++)
+        open[q] += v[q];
+      continue;
+    }
+    // mixed chunk: one warp reduction per distinct label
+    unsigned todo = live_mask;
+    while (todo)
+    {
+      const int lead = __ffs(todo) - 1;
+      const int lab = __shfl_sync(0xffffffffu, label, lead);
+      const bool mine = live && label == lab;
+      double r[ROW];
+#pragma unroll
+      for (int q = 0; q < ROW; q++)
+        r[q] = warp_sum(mine ? v[q] : 0.0);
+      if (lab == open_label)
+      {
+        if (lane == 0)
+        {
+#pragma unroll
+          for (int q = 0; q < ROW; q++)
+            open[q] += r[q];
+        }
+      }
+      else if (lane == 0)
+        flush_rows(a.rows, a.cap, lab, r, a.out);
+      todo &= ~__ballot_sync(0xffffffffu, mine);
+    }
+  }
+  // warp totals
+#pragma unroll
+  for (int q = 0; q < ROW; q++)
+    open[q] = warp_sum(open[q]);
+#pragma unroll
+  for (int q = 0; q < 12; q++)
+    setv[q] = warp_sum(setv[q]);
+  if (lane == 0)
+  {
+#pragma unroll
+    for (int q = 0; q < ROW; q++)
+      s_open[warp][q] = open[q];
+    s_open_label[warp] = open_label;
+#pragma unroll
+    for (int q = 0; q < 12; q++)
+      s_set[warp][q] = setv[q];
+  }
+  __syncthreads();
+  if (warp == 0)
+  {
+    // merge the warps' open rows that share a label (normally all of them)
+    if (lane < 12)
+    {
+      double t = 0.0;
+      for (int k = 0; k < ST_BLOCK / 32; k++)
+        t += s_set[k][lane];
+      atomicAdd(&a.out->set_sums[lane], t);
+    }
+    if (lane < ROW)
+    {
+      for (int k = 0; k < ST_BLOCK / 32; k++)
+      {
+        const int lab = s_open_label[k];
+        if (lab < 0)
+          continue;
+        bool seen = false;
+        for (int k2 = 0; k2 < k; k2++)
+          seen |= s_open_label[k2] == lab;
+        if (seen)
+          continue;
+        double t = 0.0;
+        for (int k2 = k; k2 < ST_BLOCK / 32; k2++)
+          if (s_open_label[k2] == lab)
+            t += s_open[k2][lane];
+        if (lab >= a.cap)
+          atomicOr(&a.out->err, 2);
+        else
+          atomicAdd(&a.rows[(size_t)lab * ROW + lane], t);
+      }
+    }
+  }
+}
+
+// updateConverged (particle_filter.cpp:170-220)
+__global__ void __launch_bounds__(256) k_converged_count(const double* __restrict__ x, const double* __restrict__ y, int n,
+                                                         double dist_threshold, TreeOut* out)
+{
+  const double mean_x = out->set_sums[10] / n, mean_y = out->set_sums[11] / n;
+  int cnt = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    cnt += (fabs(x[i] - mean_x) <= dist_threshold && fabs(y[i] - mean_y) <= dist_threshold) ? 1 : 0;
+  cnt = warp_sum_i(cnt);
+  if ((threadIdx.x & 31) == 0 && cnt)
+    atomicAdd(&out->conv, cnt);
+}
+
+// normalizeCluster (particle_filter.cpp:548-562) -> count, weight, mean[3], cov(0,0),(0,1),(1,0),(1,1),(2,2)
+__global__ void __launch_bounds__(256) k_cluster_finalize(const TreeOut* __restrict__ out, const double* __restrict__ rows,
+                                                          int cap, double* __restrict__ stats)
+{
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int C = min(out->C, cap);
+  if (c >= C)
+    return;
+  const double* r = rows + (size_t)c * ROW;
+  double* o = stats + (size_t)c * 10;
+  const double weight = r[1];
+  const double mean0 = r[2] / weight, mean1 = r[3] / weight;
+  o[0] = r[0];
+  o[1] = weight;
+  o[2] = mean0;
+  o[3] = mean1;
+  o[4] = atan2(r[5], r[4]);
+  o[5] = r[6] / weight - mean0 * mean0;
+  o[6] = r[7] / weight - mean0 * mean1;
+  o[7] = r[8] / weight - mean1 * mean0;
+  o[8] = r[9] / weight - mean1 * mean1;
+  o[9] = -2 * log(sqrt(r[4] * r[4] + r[5] * r[5]));
+}
+}  // namespace
+
+namespace bamcl
+{
+static int coop_blocks_for(bamcl_pf* pf)
+{
+  if (pf->coop_blocks == 0)
+  {
+    int per_sm = 0, sms = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tree_build, 256, 0) != cudaSuccess || per_sm < 1)
+      per_sm = 1;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, pf->ctx->device) != cudaSuccess || sms < 1)
+      sms = kNumSMs;
+    pf->coop_blocks = per_sm * sms;
+  }
+  return pf->coop_blocks;
+}
+
+int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, double convergence_threshold,
+                         bamcl_resample_result* res)
+{
+  bamcl_ctx* ctx = pf->ctx;
+  SampleSet& set = pf->sets[set_index];
+  const int n = set.sample_count;
+  set.leaf_count = set.node_count = set.cluster_count = 0;
+  if (n <= 0)
+    return BAMCL_OK;
+  // hash capacity: power of two >= 2n
+  size_t H = 1024;
+  while (H < (size_t)n * 2)
+    H <<= 1;
+  const unsigned hmask = (unsigned)(H - 1);
+  BAMCL_TRY(pf->t_hkeys.reserve(sizeof(unsigned long long) * H));
+  BAMCL_TRY(pf->t_hfirst.reserve(sizeof(int) * H));
+  BAMCL_TRY(pf->t_hnode.reserve(sizeof(int) * H));
+  const size_t cap_n = (size_t)pf->max_samples;
+  BAMCL_TRY(pf->t_slot.reserve(sizeof(int) * cap_n));
+  BAMCL_TRY(pf->t_flag.reserve(sizeof(int) * cap_n));
+  BAMCL_TRY(pf->t_nkey.reserve(sizeof(unsigned long long) * cap_n));
+  BAMCL_TRY(pf->t_cur.reserve(sizeof(int) * cap_n));
+  BAMCL_TRY(pf->t_child.reserve(sizeof(int) * 2 * cap_n));
+  BAMCL_TRY(pf->t_first_at.reserve(sizeof(int) * cap_n));
+  BAMCL_TRY(pf->t_side.reserve(cap_n));
+  BAMCL_TRY(pf->t_parent.reserve(sizeof(int) * cap_n));
+  BAMCL_TRY(pf->t_cid.reserve(sizeof(int) * cap_n));
+  BAMCL_TRY(pf->t_nfirst.reserve(sizeof(int) * cap_n));
+  BAMCL_TRY(pf->t_scan.reserve(sizeof(int) * scan_scratch_ints((long)cap_n)));
+  BAMCL_TRY(pf->t_out.reserve(sizeof(TreeOut)));
+  BAMCL_TRY(pf->t_hout.reserve(sizeof(TreeOut)));
+  if (pf->t_cluster_cap == 0)
+    pf->t_cluster_cap = 4096;
+  TreeOut* out = pf->t_out.as<TreeOut>();
+  TreeOut* h_out = pf->t_hout.as<TreeOut>();
+  const int blocks_n = (n + 255) / 256;
+  // cell sizes exactly as pf_kdtree.cpp:35-37 writes them
+  const double cx = 0.50, cy = 0.50, ct = (10 * M_PI / 180);
+
+  for (int attempt = 0; attempt < 2; attempt++)
+  {
+    BAMCL_TRY(pf->t_sums.reserve(sizeof(double) * ROW * pf->t_cluster_cap));
+    BAMCL_TRY(set.cluster_stats.reserve(sizeof(double) * 10 * pf->t_cluster_cap));
+    BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_hkeys.p, 0xFF, sizeof(unsigned long long) * H, ctx->stream));
+    BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_hfirst.p, 0x7F, sizeof(int) * H, ctx->stream));
+    BAMCL_CUDA_OK(cudaMemsetAsync(out, 0, sizeof(TreeOut), ctx->stream));
+    BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_sums.p, 0, sizeof(double) * ROW * pf->t_cluster_cap, ctx->stream));
+    BAMCL_LAUNCH(ctx, k_hash_insert, blocks_n, 256, 0, set.x.as<double>(), set.y.as<double>(), set.th.as<double>(), n, cx, cy,
+                 ct, pf->t_hkeys.as<unsigned long long>(), pf->t_hfirst.as<int>(), hmask, pf->t_slot.as<int>(), out);
+    BAMCL_LAUNCH(ctx, k_flag_first, blocks_n, 256, 0, pf->t_slot.as<int>(), pf->t_hfirst.as<int>(), pf->t_flag.as<int>(), n);
+    BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_flag.as<int>(), pf->t_flag.as<int>(), n, pf->t_scan.as<int>(), &out->K));
+    BAMCL_LAUNCH(ctx, k_make_nodes, blocks_n, 256, 0, pf->t_slot.as<int>(), pf->t_hfirst.as<int>(), pf->t_flag.as<int>(),
+                 pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), pf->t_nkey.as<unsigned long long>(),
+                 pf->t_nfirst.as<int>(), n);
+    {
+      TreeArgs ta;
+      ta.out = out;
+      ta.nkey = pf->t_nkey.as<unsigned long long>();
+      ta.cur = pf->t_cur.as<int>();
+      ta.child = pf->t_child.as<int>();
+      ta.first_at = pf->t_first_at.as<int>();
+      ta.side = pf->t_side.as<signed char>();
+      ta.parent = pf->t_parent.as<int>();
+      int blocks = std::min(coop_blocks_for(pf), std::max(1, (n + 511) / 512));
+      void* args[] = {&ta};
+      BAMCL_CUDA_OK(cudaLaunchCooperativeKernel((void*)k_tree_build, dim3(blocks), dim3(256), args, 0, ctx->stream));
+      ctx->launches++;
+    }
+    {
+      const long threads = (long)n * 13;
+      BAMCL_LAUNCH(ctx, k_cc_union, (unsigned)((threads + 255) / 256), 256, 0, out, pf->t_nkey.as<unsigned long long>(),
+                   pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), hmask, pf->t_parent.as<int>(), n);
+    }
+    BAMCL_LAUNCH(ctx, k_cc_roots, blocks_n, 256, 0, out, pf->t_parent.as<int>(), pf->t_cid.as<int>(), n);
+    BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_cid.as<int>(), pf->t_cid.as<int>(), n, pf->t_scan.as<int>(), &out->C));
+    {
+      StatsArgs sa;
+      sa.x = set.x.as<double>();
+      sa.y = set.y.as<double>();
+      sa.th = set.th.as<double>();
+      sa.w = set.w.as<double>();
+      sa.n = n;
+      sa.slot = pf->t_slot.as<int>();
+      sa.hnode = pf->t_hnode.as<int>();
+      sa.parent = pf->t_parent.as<int>();
+      sa.cid = pf->t_cid.as<int>();
+      sa.label = set.label.as<int>();
+      sa.rows = pf->t_sums.as<double>();
+      sa.cap = (int)pf->t_cluster_cap;
+      sa.out = out;
+      const int per_block = ST_BLOCK * ST_CHUNKS;
+      BAMCL_LAUNCH(ctx, k_labels_stats, (n + per_block - 1) / per_block, ST_BLOCK, 0, sa);
+    }
+    BAMCL_LAUNCH(ctx, k_converged_count, std::min(blocks_n, kNumSMs * 8), 256, 0, set.x.as<double>(), set.y.as<double>(), n,
+                 dist_threshold, out);
+    BAMCL_LAUNCH(ctx, k_cluster_finalize, (unsigned)((pf->t_cluster_cap + 255) / 256), 256, 0, out, pf->t_sums.as<double>(),
+                 (int)pf->t_cluster_cap, set.cluster_stats.as<double>());
+    BAMCL_CUDA_OK(cudaMemcpyAsync(h_out, out, sizeof(TreeOut), cudaMemcpyDeviceToHost, ctx->stream));
+    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    if (h_out->err & 1)
+      return set_error(BAMCL_E_UNSUPPORTED, "a pose is outside the kd-tree key range (|x|,|y| < 5e5 m, |theta| < 3.6e5 rad)");
+    if ((h_out->err & 2) || (size_t)h_out->C > pf->t_cluster_cap)
+    {
+      // more clusters than rows: grow and redo (rare: only widely scattered sets have thousands of components)
+      size_t want = pf->t_cluster_cap;
+      while (want < (size_t)h_out->C)
+        want <<= 1;
+      pf->t_cluster_cap = want;
+      continue;
+    }
+    break;
+  }
+  set.leaf_count = h_out->leaf;
+  set.node_count = h_out->K;
+  set.cluster_count = h_out->C;
+  pf->tree_levels = h_out->levels;
+  // computeSetStats (particle_filter.cpp:612-628)
+  const double* s = h_out->set_sums;
+  const double weight = s[0];
+  res->mean[0] = s[1] / weight;
+  res->mean[1] = s[2] / weight;
+  res->mean[2] = std::atan2(s[4], s[3]);
+  res->cov[0] = s[5] / weight - res->mean[0] * res->mean[0];
+  res->cov[1] = s[6] / weight - res->mean[0] * res->mean[1];
+  res->cov[2] = s[7] / weight - res->mean[1] * res->mean[0];
+  res->cov[3] = s[8] / weight - res->mean[1] * res->mean[1];
+  res->cov[4] = -2 * std::log(std::sqrt(s[3] * s[3] + s[4] * s[4]));
+  res->leaf_count = h_out->leaf;
+  res->node_count = h_out->K;
+  res->cluster_count = h_out->C;
+  // updateConverged :206-219 (percentage in float, as the reference computes it)
+  const double percent = static_cast<float>(h_out->conv) / static_cast<float>(n) * 100;
+  res->converged = percent >= convergence_threshold ? 1 : 0;
+  return BAMCL_OK;
+}
+}  // namespace bamcl
+
+extern "C" {
+
+int bamcl_pf_sample_clusters(bamcl_pf* pf, int* labels, long n)
+{
+  if (!pf || !labels || n != pf->sets[pf->current].sample_count)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_sample_clusters: n must equal sample_count");
+  if (n == 0)
+    return BAMCL_OK;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(labels, pf->sets[pf->current].label.p, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost,
+                                pf->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_pf_cluster_stats(bamcl_pf* pf, double* out, int max_clusters)
+{
+  if (!pf || !out || max_clusters < 0)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_cluster_stats: bad arguments");
+  bamcl::SampleSet& set = pf->sets[pf->current];
+  const int c = std::min(max_clusters, set.cluster_count);
+  if (c == 0)
+    return BAMCL_OK;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(out, set.cluster_stats.p, sizeof(double) * 10 * (size_t)c, cudaMemcpyDeviceToHost,
+                                pf->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+  return BAMCL_OK;
+}
+
+}  // extern "C"

@@ -53,7 +53,24 @@ struct bamcl_pf
   bamcl::DevBuf scratch;   // generic scratch, grown on demand
   bamcl::DevBuf scratch2;
   bamcl::DevBuf random_poses;
+  bamcl::DevBuf seg_buf;   // systematic target segments
+  // kd-tree / clustering workspace (kdtree.cu), shared by both sets
+  bamcl::DevBuf t_hkeys, t_hfirst, t_hnode;                 // hash table over pose bins
+  bamcl::DevBuf t_slot, t_flag;                             // per sample
+  bamcl::DevBuf t_nkey, t_cur, t_child, t_first_at, t_side; // per node (creation order)
+  bamcl::DevBuf t_parent, t_cid, t_nfirst;
+  bamcl::DevBuf t_scan, t_out, t_sums;
+  bamcl::PinBuf t_hout;
+  size_t t_cluster_cap = 0;
+  int coop_blocks = 0;
+  int tree_levels = 0;      // levels the last tree build needed (diagnostics)
 };
+
+namespace bamcl
+{
+// device int flags of the resampler: bit0 target beyond the CDF, bit1 unsupported value
+inline int* pf_flags(bamcl_pf* pf) { return reinterpret_cast<int*>(pf->scalars.as<double>() + 32); }
+}
 
 namespace bamcl
 {

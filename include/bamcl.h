@@ -168,6 +168,9 @@ int bamcl_pf_resample_sources(bamcl_pf* pf, int* src, long n);
 int bamcl_pf_sample_clusters(bamcl_pf* pf, int* labels, long n);
 /* per cluster 10 doubles: count, weight, mean[3], cov(0,0),(0,1),(1,0),(1,1),(2,2) (getClusterStats :639) */
 int bamcl_pf_cluster_stats(bamcl_pf* pf, double* out, int max_clusters);
+/* the systematic target sequence of particle_filter.cpp:309,337-341 (target = start; target += delta; wrap above
+ * 1.0) in the closed per-binade form the device uses; host arithmetic, exposed for parity tests (no GPU needed) */
+int bamcl_systematic_targets(double start, double delta, long n, double* out);
 /* resampleLimit (particle_filter.cpp:475-502), host arithmetic exposed for parity tests */
 int bamcl_resample_limit(int k, int min_samples, int max_samples, double pop_err, double pop_z);
 

@@ -1,0 +1,184 @@
+"""GPU parity: the KLD resampler (K-d1..d4) vs the oracle.
+
+Staged as SURVEY H1b describes: the device resampler is fed the ORACLE's normalised weights, kd-tree state and
+drand48 draw and must return bit-identical CDF entries, source indices, sample_count, leaf count, node count and
+cluster labels; means / covariances within 1e-6 (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+
+from badger_amcl_b200 import synth
+
+pytestmark = pytest.mark.gpu
+RES = 0.05
+STAT_RTOL = 1e-6
+
+
+@pytest.fixture(scope="module")
+def env(oracle_built):
+    from badger_amcl_b200 import cabi
+    ctx = cabi.Context(0)
+    cells = synth.make_grid(2000, 2000, seed=7)
+    truth = synth.pick_truth_pose(cells, RES, seed=5)
+    yield dict(O=oracle_built, cabi=cabi, ctx=ctx, cells=cells, truth=truth)
+    ctx.close()
+
+
+def _weights(kind, n, rng):
+    if kind == "uniform":
+        return np.full(n, 1.0 / n)
+    if kind == "random":
+        w = rng.random(n)
+    elif kind == "heavy":
+        w = np.exp(rng.normal(0.0, 6.0, n))
+    elif kind == "zeros":
+        w = rng.random(n)
+        w[: n // 3] = 0.0
+        w[rng.random(n) < 0.3] = 0.0
+        if not w.any():
+            w[-1] = 1.0
+    elif kind == "dominant":
+        w = rng.random(n) * 1e-12
+        w[n // 2] = 1.0
+    elif kind == "ties":
+        # dyadic weights whose low bits sit exactly half way between neighbours of the running sum
+        w = (rng.integers(1, 8, n) * 2.0 + 1.0) * 2.0 ** -60 + rng.integers(0, 3, n) * 2.0 ** -20
+        return w  # deliberately not normalised: exact dyadic arithmetic
+    elif kind == "increasing":
+        w = np.exp(np.linspace(-40.0, 0.0, n))
+    else:
+        raise ValueError(kind)
+    return w / w.sum()
+
+
+@pytest.mark.parametrize("kind", ["uniform", "random", "heavy", "zeros", "dominant", "ties", "increasing"])
+@pytest.mark.parametrize("n", [1, 5, 2047, 2048, 2049, 5000, 100000, 1000000])
+def test_cdf_is_the_sequential_fp64_prefix_sum(env, kind, n):
+    """particle_filter.cpp:280-285: c[i+1] = c[i] + w[i], one rounding at a time"""
+    O, cabi = env["O"], env["cabi"]
+    rng = np.random.default_rng(n * 7 + len(kind))
+    w = _weights(kind, n, rng)
+    aos = np.zeros((n, 4))
+    aos[:, 3] = w
+    port = O.PortPF(1, n)
+    port.set_samples(aos)
+    want = port.cdf()
+    pf = cabi.ParticleFilter(env["ctx"], 1, n)
+    pf.upload_samples(aos)
+    got = pf.cdf()
+    bad = np.nonzero(got != want)[0]
+    assert bad.size == 0, "first mismatch at %d: %r vs %r (%d total)" % (bad[0], got[bad[0]], want[bad[0]], bad.size)
+    pf.close()
+
+
+def _assert_same_resample(pf, port, r, check_labels=True):
+    assert r.sample_count == port.sample_count()
+    assert np.array_equal(pf.resample_sources(), port.resample_sources())
+    got, want = pf.samples(), port.samples()
+    assert np.array_equal(got[:, :3], want[:, :3])
+    assert np.array_equal(got[:, 3], want[:, 3])
+    assert r.leaf_count == port.leaf_count()
+    assert r.node_count == port.node_count()
+    assert r.cluster_count == port.cluster_count()
+    assert bool(r.converged) == port.is_converged()
+    if check_labels:
+        assert np.array_equal(pf.sample_clusters(), port.sample_clusters())
+    assert np.allclose(pf.set_stats(), port.set_stats(), rtol=STAT_RTOL, atol=1e-9)
+    gs, ws = pf.cluster_stats(), port.cluster_stats()
+    assert gs.shape == ws.shape
+    assert np.array_equal(gs[:, 0], ws[:, 0])
+    assert np.allclose(gs[:, 1:], ws[:, 1:], rtol=STAT_RTOL, atol=1e-9)
+
+
+@pytest.mark.parametrize("cloud", ["global", "tracking"])
+def test_update_resample_sequence_matches_oracle(env, cloud):
+    """C1: 5k particles x 60 beams, (updateSensor, updateSensor, updateResample) x 3 with the oracle's weights"""
+    O, cabi = env["O"], env["cabi"]
+    n = 5000
+    cells, truth = env["cells"], env["truth"]
+    pm = O.PortMap2D(cells, RES)
+    pm.set_distances(pm.exact_edt(2.0), 2.0)
+    poses = (synth.uniform_free_poses(cells, RES, n, seed=1) if cloud == "global"
+             else synth.gaussian_poses(truth, n, seed=2))
+    ranges, angles = synth.make_scan(cells, RES, truth, n_beams=60)
+    model = O.planar_model(model_type=1, max_beams=60, scanner_pose=(0.1, 0.0, 0.0))
+    port = O.PortPF(100, n)
+    port.init_with_poses(poses)
+    port.srand48(4242)
+    pf = cabi.ParticleFilter(env["ctx"], 100, n)
+    r0 = pf.init_with_poses(poses)
+    pf.srand48(4242)
+    assert r0.leaf_count == port.leaf_count() and r0.node_count == port.node_count()
+    assert r0.cluster_count == port.cluster_count()
+    assert np.array_equal(pf.sample_clusters(), port.sample_clusters())
+    assert np.allclose(pf.set_stats(), port.set_stats(), rtol=STAT_RTOL, atol=1e-9)
+    for _ in range(3):
+        for _ in range(2):
+            port.update_sensor(pm, model, ranges, angles, 30.0)
+        pf.upload_weights(port.samples()[:, 3])
+        pf.w_slow, pf.w_fast = port.averages()
+        port.update_resample()
+        r = pf.update_resample()
+        _assert_same_resample(pf, port, r)
+    pf.close()
+
+
+def test_resample_with_random_pose_injection(env):
+    """w_diff > 0 (particle_filter.cpp:297-306, 317-327): random poses first, averages reset"""
+    O, cabi = env["O"], env["cabi"]
+    n = 4000
+    cells, truth = env["cells"], env["truth"]
+    poses = synth.gaussian_poses(truth, n, seed=3)
+    rnd = synth.uniform_free_poses(cells, RES, n, seed=9)
+    rng = np.random.default_rng(5)
+    w = rng.random(n)
+    w /= w.sum()
+    port = O.PortPF(500, n)
+    port.init_with_poses(poses)
+    aos = np.concatenate([poses, w[:, None]], axis=1)
+    port.set_samples(aos)
+    port.set_averages(0.010, 0.007)
+    port.set_random_poses(rnd)
+    port.srand48(99)
+    pf = cabi.ParticleFilter(env["ctx"], 500, n)
+    pf.init_with_poses(poses)
+    pf.upload_samples(aos)
+    pf.w_slow, pf.w_fast = 0.010, 0.007
+    pf.set_random_poses(rnd)
+    pf.srand48(99)
+    port.update_resample()
+    r = pf.update_resample()
+    assert r.random_poses_used == port.L.orc_pf_random_poses_used(port.h) > 0
+    _assert_same_resample(pf, port, r)
+    assert (pf.w_slow, pf.w_fast) == port.averages() == (0.0, 0.0)
+    pf.close()
+
+
+@pytest.mark.parametrize("n,cloud", [(100000, "global"), (100000, "tracking"), (1000000, "global")])
+def test_large_resample_matches_oracle(env, n, cloud):
+    """C3 sizes: synthetic heavy-tailed weights on global / tracking clouds, two consecutive resamples"""
+    O, cabi = env["O"], env["cabi"]
+    cells, truth = env["cells"], env["truth"]
+    poses = (synth.uniform_free_poses(cells, RES, n, seed=1) if cloud == "global"
+             else synth.gaussian_poses(truth, n, seed=2))
+    rng = np.random.default_rng(n)
+    port = O.PortPF(n // 10, n)
+    port.init_with_poses(poses)
+    port.srand48(7)
+    pf = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    r0 = pf.init_with_poses(poses)
+    pf.srand48(7)
+    assert r0.leaf_count == port.leaf_count() and r0.node_count == port.node_count()
+    for _ in range(2):
+        m = port.sample_count()
+        w = np.exp(rng.normal(0.0, 2.0, m))
+        w /= w.sum()
+        s = port.samples()
+        s[:, 3] = w
+        port.set_samples(s)
+        port.set_averages(1.0, 1.0)
+        pf.upload_weights(w)
+        pf.w_slow = pf.w_fast = 1.0
+        port.update_resample()
+        r = pf.update_resample()
+        _assert_same_resample(pf, port, r, check_labels=(n <= 100000))
+    pf.close()

@@ -292,8 +292,10 @@ __global__ void __launch_bounds__(256) k_cc_union(const TreeOut* __restrict__ ou
   uf_union(parent, v, hnode[s]);
 }
 
-__global__ void __launch_bounds__(256) k_cc_roots(const TreeOut* __restrict__ out, int* parent, int* __restrict__ is_root,
-                                                  int n)
+// Read-only find: a compressing find here would race with other threads' finds (a stale intermediate ancestor
+// written over an already final root), so the final roots go to a separate array.
+__global__ void __launch_bounds__(256) k_cc_roots(const TreeOut* __restrict__ out, const int* __restrict__ parent,
+                                                  int* __restrict__ root, int* __restrict__ is_root, int n)
 {
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= n)
@@ -304,8 +306,10 @@ __global__ void __launch_bounds__(256) k_cc_roots(const TreeOut* __restrict__ ou
     is_root[v] = 0;
     return;
   }
-  const int r = uf_find(parent, v);
-  parent[v] = r;
+  int r = v, up;
+  while ((up = parent[r]) != r)
+    r = up;
+  root[v] = r;
   is_root[v] = r == v ? 1 : 0;
 }
 
@@ -614,7 +618,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       BAMCL_LAUNCH(ctx, k_cc_union, (unsigned)((threads + 255) / 256), 256, 0, out, pf->t_nkey.as<unsigned long long>(),
                    pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), hmask, pf->t_parent.as<int>(), n);
     }
-    BAMCL_LAUNCH(ctx, k_cc_roots, blocks_n, 256, 0, out, pf->t_parent.as<int>(), pf->t_cid.as<int>(), n);
+    BAMCL_LAUNCH(ctx, k_cc_roots, blocks_n, 256, 0, out, pf->t_parent.as<int>(), pf->t_cur.as<int>(), pf->t_cid.as<int>(), n);
     BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_cid.as<int>(), pf->t_cid.as<int>(), n, pf->t_scan.as<int>(), &out->C));
     {
       StatsArgs sa;
@@ -625,7 +629,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       sa.n = n;
       sa.slot = pf->t_slot.as<int>();
       sa.hnode = pf->t_hnode.as<int>();
-      sa.parent = pf->t_parent.as<int>();
+      sa.parent = pf->t_cur.as<int>();  // final roots (k_cc_roots)
       sa.cid = pf->t_cid.as<int>();
       sa.label = set.label.as<int>();
       sa.rows = pf->t_sums.as<double>();

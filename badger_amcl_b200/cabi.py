@@ -75,6 +75,9 @@ SIGNATURES = {
     "bamcl_timer_stop_ms": (_I, [_P, _P]),
     "bamcl_ctx_launch_count": (_L, [_P]),
     "bamcl_ctx_flush_l2": (_I, [_P]),
+    "bamcl_host_alloc": (_I, [C.c_size_t, _P]),
+    "bamcl_host_free": (_I, [_P]),
+    "bamcl_pf_last_score_ms": (_I, [_P, _P]),
     "bamcl_map2d_create": (_I, [_P, _I, _I, _D, _F, _F, _P]),
     "bamcl_map2d_destroy": (_I, [_P]),
     "bamcl_map2d_set_cells": (_I, [_P, _P, _L]),
@@ -159,6 +162,20 @@ class Context:
 
     def flush_l2(self):
         _check(self.L.bamcl_ctx_flush_l2(self.h))
+
+
+def pinned_array(shape, dtype=np.float64):
+    """numpy array over page-locked host memory from bamcl_host_alloc (kept alive by the array's base)."""
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = C.c_void_p()
+    _check(lib().bamcl_host_alloc(max(n, 1), C.byref(p)))
+    buf = (C.c_char * max(n, 1)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    _PINNED.append((p, buf))
+    return arr
+
+
+_PINNED = []  # pinned blocks live for the life of the process (bench / tests only)
 
 
 class Map2D:
@@ -267,6 +284,19 @@ class ParticleFilter:
         self.last = res
         return res
 
+    def init_with_current(self):
+        """kd-tree + cluster statistics of the samples already on the device (bamcl_pf_init_stats)."""
+        res = ResampleResult()
+        _check(self.L.bamcl_pf_init_stats(self.h, C.byref(res)))
+        self.converged = False
+        self.last = res
+        return res
+
+    def download_samples_into(self, out):
+        """current set -> caller's (n, 4) float64 buffer (e.g. a pinned_array slice)"""
+        assert out.dtype == np.float64 and out.flags.c_contiguous and out.shape[1] == 4
+        _check(self.L.bamcl_pf_download_samples(self.h, _p(out), len(out)))
+
     # -- sensor update
     def score_planar(self, map2d, model, ranges, angles, range_max):
         """PlanarScanner::applyModelToSampleSet: returns the total; weights stay un-normalised."""
@@ -276,6 +306,11 @@ class ParticleFilter:
         _check(self.L.bamcl_pf_score_planar(self.h, map2d.h, C.byref(model), _p(ranges), _p(angles), len(ranges),
                                             range_max, int(self.converged), C.byref(total)))
         return total.value
+
+    def last_score_ms(self):
+        ms = C.c_float()
+        _check(self.L.bamcl_pf_last_score_ms(self.h, C.byref(ms)))
+        return ms.value
 
     def normalise(self, total):
         _check(self.L.bamcl_pf_normalise(self.h, total))

@@ -97,6 +97,21 @@ int bamcl_timer_stop_ms(bamcl_ctx* ctx, float* ms)
   return BAMCL_OK;
 }
 
+int bamcl_host_alloc(size_t bytes, void** out)
+{
+  if (!out || bytes == 0)
+    return set_error(BAMCL_E_ARG, "bamcl_host_alloc: bad arguments");
+  BAMCL_CUDA_OK(cudaMallocHost(out, bytes));
+  return BAMCL_OK;
+}
+
+int bamcl_host_free(void* p)
+{
+  if (p)
+    BAMCL_CUDA_OK(cudaFreeHost(p));
+  return BAMCL_OK;
+}
+
 long bamcl_ctx_launch_count(bamcl_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
 int bamcl_ctx_flush_l2(bamcl_ctx* ctx)

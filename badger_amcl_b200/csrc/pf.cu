@@ -153,6 +153,8 @@ int bamcl_pf_create(bamcl_ctx* ctx, int min_samples, int max_samples, bamcl_pf**
     BAMCL_CUDA_OK(cudaMemsetAsync(s.th.p, 0, bytes, ctx->stream));
     BAMCL_LAUNCH(ctx, k_fill, (max_samples + 255) / 256, 256, 0, s.w.as<double>(), 1.0 / max_samples, max_samples);
   }
+  BAMCL_CUDA_OK(cudaEventCreate(&pf->score_ev0));
+  BAMCL_CUDA_OK(cudaEventCreate(&pf->score_ev1));
   BAMCL_TRY(pf->scalars.reserve(sizeof(double) * 64));
   BAMCL_TRY(pf->h_scalars.reserve(sizeof(double) * 64));
   BAMCL_CUDA_OK(cudaMemsetAsync(pf->scalars.p, 0, sizeof(double) * 64, ctx->stream));
@@ -196,6 +198,10 @@ int bamcl_pf_destroy(bamcl_pf* pf)
                            &pf->t_out, &pf->t_sums})
     b->release();
   pf->t_hout.release();
+  if (pf->score_ev0)
+    cudaEventDestroy(pf->score_ev0);
+  if (pf->score_ev1)
+    cudaEventDestroy(pf->score_ev1);
   delete pf;
   return BAMCL_OK;
 }
@@ -282,6 +288,17 @@ int bamcl_pf_score_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_mod
   BAMCL_TRY(launch_score(pf, map));
   BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
   return read_scalar(pf, 0, total_out);
+}
+
+int bamcl_pf_last_score_ms(bamcl_pf* pf, float* ms)
+{
+  if (!pf || !ms)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_last_score_ms: bad arguments");
+  if (!pf->score_timed)
+    return set_error(BAMCL_E_STATE, "no scoring kernel has been launched yet");
+  BAMCL_CUDA_OK(cudaEventSynchronize(pf->score_ev1));
+  BAMCL_CUDA_OK(cudaEventElapsedTime(ms, pf->score_ev0, pf->score_ev1));
+  return BAMCL_OK;
 }
 
 int bamcl_pf_normalise(bamcl_pf* pf, double total)

@@ -63,6 +63,8 @@ struct bamcl_pf
   bamcl::PinBuf t_hout;
   size_t t_cluster_cap = 0;
   int coop_blocks = 0;
+  cudaEvent_t score_ev0 = nullptr, score_ev1 = nullptr;  // around the last scoring kernel (bamcl_pf_last_score_ms)
+  bool score_timed = false;
   int tree_levels = 0;      // levels the last tree build needed (diagnostics)
 };
 

@@ -188,7 +188,10 @@ int launch_beam_model(bamcl_pf* pf, bamcl_map2d* map)
   int blocks = (a.n + 7) / 8;
   if (blocks > kNumSMs * 8)
     blocks = kNumSMs * 8;
+  BAMCL_CUDA_OK(cudaEventRecord(pf->score_ev0, ctx->stream));
   BAMCL_LAUNCH(ctx, k_score_beam, blocks, 256, 0, a);
+  BAMCL_CUDA_OK(cudaEventRecord(pf->score_ev1, ctx->stream));
+  pf->score_timed = true;
   return BAMCL_OK;
 }
 }  // namespace bamcl

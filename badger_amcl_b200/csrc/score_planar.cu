@@ -382,6 +382,7 @@ int launch_score(bamcl_pf* pf, bamcl_map2d* map)
   const size_t stash_bytes = sizeof(double4) * WARPS * PB;
   const size_t tab_bytes = sizeof(double) * (size_t)a.table_n;
   const bool smem_tab = tab_bytes <= 40 * 1024;
+  BAMCL_CUDA_OK(cudaEventRecord(pf->score_ev0, ctx->stream));
 #define BAMCL_SCORE_CASE(L)                                                                          \
   if (smem_tab)                                                                                      \
     BAMCL_LAUNCH(ctx, (k_score_lf<true, L>), blocks, WARPS * 32, stash_bytes + tab_bytes, a);        \
@@ -400,6 +401,8 @@ int launch_score(bamcl_pf* pf, bamcl_map2d* map)
     BAMCL_SCORE_CASE(2)
   }
 #undef BAMCL_SCORE_CASE
+  BAMCL_CUDA_OK(cudaEventRecord(pf->score_ev1, ctx->stream));
+  pf->score_timed = true;
   return BAMCL_OK;
 }
 }  // namespace bamcl

@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""bench.py -- the badger_amcl hot path on B200: likelihood-field update + KLD-adaptive systematic resample.
+
+One "step" = PlanarScanner::updateSensor (planar_scanner.cpp:125 -> particle_filter.cpp:223) followed by
+ParticleFilter::updateResample (particle_filter.cpp:423) over ONE set of P particles and one B-beam scan on a
+W x W occupancy grid (BASELINE.json metric: "particle-beam evals/sec; update+resample ms at 1M particles").
+Default workload = north_star's target case: P = 1 000 000 global-uniform particles x 1080 beams, 4000^2 grid,
+0.05 m cells, node-default model parameters, min_samples = P/10, max_samples = P.
+
+  value   evals/s with the particle set, map and scan resident in HBM (device-timed, CUDA events on the
+          library's stream; the set is restored and L2 flushed between steps, outside the timed region)
+  e2e     the same step through the C ABI with HOST buffers: pinned AoS particle upload + scan staging +
+          update + resample + AoS download of the resampled set and the result struct, all inside the timer
+  roofline   dominant kernel (k_score_lf) alone: algorithmic bytes P*B*4 + P*40 + B*16 / its
+             CUDA-event duration vs MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline   the reference's own translation units (oracle/_ref, kind "reference") or the C restatement
+                 (kind "port") on a bounded particle prefix, one thread (the reference is single-threaded)
+
+`--impl reference` times that CPU path alone. N > 1 (torchrun): every rank runs the step on its own shard of
+N*P particles against a replicated map (weak scaling); see DESIGN.md "multi-GPU" for what is exchanged.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+RES = 0.05
+RANGE_MAX = 30.0
+METRIC = "particle-beam evals/sec (likelihood-field update + KLD resample)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--particles", type=int, default=1000000, help="particles per GPU")
+    ap.add_argument("--beams", type=int, default=1080)
+    ap.add_argument("--map", type=int, default=4000, help="grid is map x map cells")
+    ap.add_argument("--cpu-particles", type=int, default=0, help="particle prefix for the CPU baseline (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def workload_name(a):
+    return "lf_update+kld_systematic_resample P=%d/gpu B=%d grid=%dx%d res=%.2f" % (a.particles, a.beams, a.map, a.map, RES)
+
+
+def make_inputs(a, rank=0):
+    """Synthetic world of SURVEY 8(d): rooms grid, scan ray-cast from a truth pose, global-uniform particles."""
+    from badger_amcl_b200 import synth
+    cells = synth.make_grid(a.map, a.map, seed=7)
+    truth = synth.pick_truth_pose(cells, RES, seed=5)
+    ranges, angles = synth.make_scan(cells, RES, truth, n_beams=a.beams)
+    poses = synth.uniform_free_poses(cells, RES, a.particles, seed=1 + rank)
+    return cells, truth, ranges, angles, poses
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampling (nvidia-smi during the timed region)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 6:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own code (oracle/_ref) or the C restatement (oracle/liboracle.so)
+# ------------------------------------------------------------------------------------------------
+class CpuArm:
+    """updateSensor + updateResample of the reference on the host, one thread (the reference has no threads)."""
+
+    def __init__(self, a, cells, ranges, angles, poses, n_cpu):
+        try:
+            import resource
+            resource.setrlimit(resource.RLIMIT_STACK, (resource.RLIM_INFINITY, resource.RLIM_INFINITY))
+        except Exception:
+            pass
+        from oracle import oracle as O  # bench.py's cpu legs are the one product-side place allowed to run oracle/
+        self.O, self.n = O, n_cpu
+        self.kind = "reference" if O.have_ref() else "port"
+        self.ranges, self.angles = ranges, angles
+        self.poses = np.ascontiguousarray(poses[:n_cpu])
+        self.model = O.planar_model(model_type=1, max_beams=a.beams, scanner_pose=(0.1, 0.0, 0.0))
+        self.valid = int((ranges < RANGE_MAX).sum())
+        if self.kind == "reference":
+            self.map = O.RefMap2D(cells, RES)
+            self.map.update_distances(2.0)  # the reference's own brushfire (setup, untimed)
+            self.scanner = O.RefScanner2D(self.map, self.model)
+            self.pf = O.RefPF(max(1, n_cpu // 10), n_cpu)
+        else:
+            self.map = O.PortMap2D(cells, RES)
+            self.map.update_distances(2.0)
+            self.pf = O.PortPF(max(1, n_cpu // 10), n_cpu)
+
+    def step(self):
+        """returns (update_s, resample_s)"""
+        self.pf.init_with_poses(self.poses)  # restore the set + its kd-tree (untimed)
+        self.pf.srand48(12345)
+        t0 = time.perf_counter()
+        if self.kind == "reference":
+            self.pf.update_sensor(self.scanner, self.ranges, self.angles, RANGE_MAX)
+        else:
+            self.pf.update_sensor(self.map, self.model, self.ranges, self.angles, RANGE_MAX)
+        t1 = time.perf_counter()
+        self.pf.update_resample()
+        t2 = time.perf_counter()
+        return t1 - t0, t2 - t1
+
+
+def run_reference_arm(a):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return 0
+    steps, warm = a.steps, a.warmup
+    # bounded sample: about 120 s of single-thread work over all steps at ~220 ns per particle-beam
+    n_cpu = a.cpu_particles or int(min(50000, max(2000, 120.0 / ((steps + warm) * a.beams * 220e-9))))
+    n_cpu = min(n_cpu, a.particles)
+    cells, truth, ranges, angles, poses = make_inputs(a)
+    arm = CpuArm(a, cells, ranges, angles, poses, n_cpu)
+    for _ in range(warm):
+        arm.step()
+    ts = [arm.step() for _ in range(steps)]
+    up, rs = float(np.mean([t[0] for t in ts])), float(np.mean([t[1] for t in ts]))
+    value = n_cpu * arm.valid / (up + rs)
+    sample = "first %d of %d particles x %d beams (valid %d), update %.1f ms + resample %.1f ms per step" % (
+        n_cpu, a.particles, a.beams, arm.valid, up * 1e3, rs * 1e3)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": a.gpus, "steps": steps,
+            "warmup": warm, "ms_per_step": (up + rs) * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "timing": "host perf_counter, single thread"},
+            "cpu_baseline": {"value": value, "unit": "evals/s", "cores": 1, "kind": arm.kind, "sample": sample,
+                             "host_cores_available": os.cpu_count()},
+            "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def run_b200_arm(a):
+    rank, local_rank, world = dist_env()
+    from badger_amcl_b200 import cabi
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = cabi.Context(local_rank)
+    cells, truth, ranges, angles, poses = make_inputs(a, rank)
+    P, B = a.particles, a.beams
+    valid = int((ranges < RANGE_MAX).sum())
+    m = cabi.Map2D(ctx, cells, RES)
+    ctx.timer_start()
+    m.build_distances(2.0)
+    edt_ms = ctx.timer_stop_ms()
+    model = cabi.planar_model(model_type=cabi.MODEL_LF, max_beams=B, scanner_pose=(0.1, 0.0, 0.0))
+    pf = cabi.ParticleFilter(ctx, P // 10, P)
+    aos = cabi.pinned_array((P, 4))
+    aos[:, :3] = poses
+    aos[:, 3] = 1.0 / P
+    out_aos = cabi.pinned_array((P, 4))
+    pf.srand48(12345)
+
+    def restore():
+        pf.upload_samples(aos)
+        pf.init_with_current()  # kd-tree of the set being resampled (particle_filter.cpp:292 reads its leaf count)
+        pf.w_slow = pf.w_fast = 0.0
+
+    def barrier():
+        ctx.sync()
+        if dist is not None:
+            dist.barrier()
+
+    # ---- resident: scan staged once, set restored outside the timed region
+    pf.stage_scan(m, model, ranges, angles, RANGE_MAX)
+
+    def step_resident():
+        restore()
+        ctx.flush_l2()
+        ctx.sync()
+        ctx.timer_start()
+        pf.update_staged(m, want_total=True)
+        t_up = ctx.timer_stop_ms()
+        k_ms = pf.last_score_ms()
+        ctx.timer_start()
+        r = pf.update_resample()
+        t_rs = ctx.timer_stop_ms()
+        return t_up, t_rs, k_ms, r
+
+    def step_e2e():
+        restore()
+        ctx.flush_l2()
+        ctx.sync()
+        t0 = time.perf_counter()
+        ctx.timer_start()
+        pf.upload_samples(aos)                                   # H2D: P x 32 B AoS from pinned host memory
+        pf.update_sensor(m, model, ranges, angles, RANGE_MAX)    # H2D: scan; D2H: total
+        r = pf.update_resample()                                 # D2H: result struct
+        n = r.sample_count
+        pf.download_samples_into(out_aos[:n])                    # D2H: n x 32 B AoS
+        ms = ctx.timer_stop_ms()
+        wall = (time.perf_counter() - t0) * 1e3
+        return max(ms, wall), n
+
+    for _ in range(a.warmup):
+        step_resident()
+    launches0 = ctx.launch_count()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    rows = [step_resident() for _ in range(a.steps)]
+    barrier()
+    launches_timed = ctx.launch_count() - launches0
+    up = float(np.sum([r[0] for r in rows]))
+    rs = float(np.sum([r[1] for r in rows]))
+    k_ms = float(np.mean([r[2] for r in rows]))
+    last = rows[-1][3]
+    for _ in range(max(1, a.warmup // 2)):
+        step_e2e()
+    barrier()
+    e_rows = [step_e2e() for _ in range(a.steps)]
+    barrier()
+    clocks = sampler.stop()
+    e_ms = float(np.sum([r[0] for r in e_rows]))
+    n_out = int(e_rows[-1][1])
+
+    total_ms, e_total_ms = up + rs, e_ms
+    if dist is not None:
+        import torch
+        t = torch.tensor([total_ms, e_total_ms, up, rs, k_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, e_total_ms, up, rs, k_ms = [float(v) for v in t.tolist()]
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
+
+    evals = float(P) * valid * world
+    value = evals * a.steps / (total_ms * 1e-3)
+    e_value = evals * a.steps / (e_total_ms * 1e-3)
+    peak, peak_src = measured_peaks()
+    algo_bytes = float(P) * valid * 4 + float(P) * 40 + B * 16
+    achieved = algo_bytes / (k_ms * 1e-3) / 1e9
+    line = {"metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "valid_beams": valid, "model": "likelihood_field",
+                       "resample": "kld systematic, min=P/10 max=P, kld_err 0.01 kld_z 0.99",
+                       "parallelism": "particle shards x%d, map+scan replicated" % world,
+                       "l2": "flushed (256 MiB write) before every timed step",
+                       "update_ms": up / a.steps, "resample_ms": rs / a.steps, "edt_build_ms": edt_ms,
+                       "resampled_count": int(last.sample_count), "kld_leaf_count": int(last.leaf_count),
+                       "clusters": int(last.cluster_count)},
+            "e2e": {"value": e_value, "unit": "evals/s", "ms_per_step": e_total_ms / a.steps,
+                    "h2d_bytes_per_step": int(P * 32 + 2 * B * 8), "d2h_bytes_per_step": int(n_out * 32 + 8 + 96)},
+            "gpu_launches": int(launches_timed),
+            "roofline": {"kernel": "k_score_lf", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "kernel_ms": k_ms, "peak_source": peak_src,
+                         "algorithmic_bytes": algo_bytes},
+            "clocks": clocks}
+    if not a.no_cpu_baseline and world >= 1:
+        n_cpu = a.cpu_particles or min(P, 20000)
+        arm = CpuArm(a, cells, ranges, angles, poses, n_cpu)
+        arm.step()
+        cu, cr = arm.step()
+        line["cpu_baseline"] = {"value": n_cpu * arm.valid / (cu + cr), "unit": "evals/s", "cores": 1, "kind": arm.kind,
+                                "sample": "first %d of %d particles x %d beams: update %.1f ms + resample %.1f ms, 1 thread"
+                                          % (n_cpu, P, B, cu * 1e3, cr * 1e3),
+                                "host_cores_available": os.cpu_count()}
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        return run_reference_arm(a)
+    return run_b200_arm(a)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -15,6 +15,7 @@
  */
 #ifndef BAMCL_H
 #define BAMCL_H
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -48,6 +49,11 @@ int bamcl_timer_stop_ms(bamcl_ctx* ctx, float* ms);
 long bamcl_ctx_launch_count(bamcl_ctx* ctx);
 /* write a buffer larger than L2 (bench hygiene between timed iterations) */
 int bamcl_ctx_flush_l2(bamcl_ctx* ctx);
+
+/* page-locked host memory for the caller's sample / scan buffers (the host mirror of PFSampleSet::samples,
+ * particle_filter.h:72, lives in such a buffer so uploads and downloads run at full PCIe rate) */
+int bamcl_host_alloc(size_t bytes, void** out);
+int bamcl_host_free(void* p);
 
 /* ---- OccupancyMap (include/amcl/map/occupancy_map.h:57-81) */
 /* ctor + setSize + setOrigin (occupancy_map.cpp:30-57) */
@@ -119,6 +125,10 @@ int bamcl_pf_update_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_mo
 int bamcl_pf_stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
                         const double* angles, int range_count, double range_max);
 int bamcl_pf_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out_or_null);
+
+/* device duration of the most recent scoring kernel launch alone (CUDA events around that launch on the
+ * context's stream); bench.py's roofline figure */
+int bamcl_pf_last_score_ms(bamcl_pf* pf, float* ms);
 
 /* sequential CDF c[0..n] of the current set's weights exactly as particle_filter.cpp:280-285 rounds it */
 int bamcl_pf_cdf(bamcl_pf* pf, double* c_out, long n_plus_1);

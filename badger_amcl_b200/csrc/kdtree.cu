@@ -18,6 +18,7 @@
 #include <algorithm>
 #include <climits>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "pf.cuh"
@@ -41,6 +42,8 @@ struct TreeOut
   int err;   // bit0 key out of the packed range, bit1 cluster rows exhausted
   int level_flags[3];
   int levels;
+  int fast_ok;        // the bucketed shared-memory build (tree_fast.cuh) produced the leaf count
+  int bucket_levels;  // deepest bucket subtree of that build
   int pad;
   double set_sums[12];  // weight, m0..m3, c00..c11, count, sum x, sum y
 };
@@ -136,9 +139,14 @@ struct TreeArgs
   int* parent;  // union-find forest for the clustering step, initialised here
 };
 
+#include "tree_fast.cuh"
+
+// General level-synchronous build over the whole grid: only runs when the fast path gave up.
 __global__ void __launch_bounds__(256) k_tree_build(const TreeArgs a)
 {
   cg::grid_group grid = cg::this_grid();
+  if (a.out->fast_ok)
+    return;
   const int K = a.out->K;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
   for (int v = tid; v < K; v += nth)
@@ -574,6 +582,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
   BAMCL_TRY(pf->t_cid.reserve(sizeof(int) * cap_n));
   BAMCL_TRY(pf->t_nfirst.reserve(sizeof(int) * cap_n));
   BAMCL_TRY(pf->t_scan.reserve(sizeof(int) * scan_scratch_ints((long)cap_n)));
+  BAMCL_TRY(pf->t_fast.reserve(sizeof(int) * (3 * M_TOP + 2 * (N_BUCKETS + 1))));
   BAMCL_TRY(pf->t_out.reserve(sizeof(TreeOut)));
   BAMCL_TRY(pf->t_hout.reserve(sizeof(TreeOut)));
   if (pf->t_cluster_cap == 0)
@@ -599,6 +608,46 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
     BAMCL_LAUNCH(ctx, k_make_nodes, blocks_n, 256, 0, pf->t_slot.as<int>(), pf->t_hfirst.as<int>(), pf->t_flag.as<int>(),
                  pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), pf->t_nkey.as<unsigned long long>(),
                  pf->t_nfirst.as<int>(), n);
+    static const bool force_general = getenv("BAMCL_TREE_GENERAL") != nullptr;  // tests: exercise k_tree_build
+    if (!force_general)
+    {
+      FastArgs fa;
+      int* small = pf->t_fast.as<int>();
+      fa.out = out;
+      fa.nkey = pf->t_nkey.as<unsigned long long>();
+      fa.tpivot = small;
+      fa.tchild = small + M_TOP;
+      fa.bcount = small + 3 * M_TOP;
+      fa.boff = fa.bcount + N_BUCKETS + 1;
+      fa.bslot = pf->t_cur.as<int>();
+      fa.bpos = pf->t_first_at.as<int>();
+      fa.bids = pf->t_child.as<int>();
+      fa.parent = pf->t_parent.as<int>();
+      const int per = 28;  // bytes of shared memory per key in k_fast_top / k_fast_bucket
+      static bool attr_done = false;
+      if (!attr_done)
+      {
+        BAMCL_CUDA_OK(cudaFuncSetAttribute(k_fast_top, cudaFuncAttributeMaxDynamicSharedMemorySize, 24 * M_TOP));
+        BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_M, FAST_CAP_S, 512>),
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, per * FAST_CAP_M));
+        BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_L, FAST_CAP_M, 1024>),
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, per * FAST_CAP_L));
+        attr_done = true;
+      }
+      const int walk_blocks = std::max(1, std::min(kNumSMs * 8, (n + 255) / 256));
+      BAMCL_LAUNCH(ctx, k_fast_top, 1, 1024, 24 * M_TOP, fa);
+      BAMCL_LAUNCH(ctx, k_fast_descend, walk_blocks, 256, 0, fa);
+      BAMCL_LAUNCH(ctx, k_fast_offsets, 1, 1024, 0, fa);
+      if (n > M_TOP)
+        BAMCL_LAUNCH(ctx, k_fast_scatter, walk_blocks, 256, 0, fa);
+      const int bucket_blocks = 2 * std::min(n, M_TOP);
+      BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_S, 0, 256>), bucket_blocks, 256, per * FAST_CAP_S, fa);
+      if (n > M_TOP + FAST_CAP_S)
+      {
+        BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_M, FAST_CAP_S, 512>), bucket_blocks, 512, per * FAST_CAP_M, fa);
+        BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_L, FAST_CAP_M, 1024>), bucket_blocks, 1024, per * FAST_CAP_L, fa);
+      }
+    }
     {
       TreeArgs ta;
       ta.out = out;
@@ -660,7 +709,8 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
   set.leaf_count = h_out->leaf;
   set.node_count = h_out->K;
   set.cluster_count = h_out->C;
-  pf->tree_levels = h_out->levels;
+  pf->tree_levels = h_out->levels + h_out->bucket_levels;
+  pf->tree_fast = h_out->fast_ok;
   // computeSetStats (particle_filter.cpp:612-628)
   const double* s = h_out->set_sums;
   const double weight = s[0];

@@ -195,7 +195,7 @@ int bamcl_pf_destroy(bamcl_pf* pf)
   pf->seg_buf.release();
   for (bamcl::DevBuf* b : {&pf->t_hkeys, &pf->t_hfirst, &pf->t_hnode, &pf->t_slot, &pf->t_flag, &pf->t_nkey, &pf->t_cur,
                            &pf->t_child, &pf->t_first_at, &pf->t_side, &pf->t_parent, &pf->t_cid, &pf->t_nfirst, &pf->t_scan,
-                           &pf->t_out, &pf->t_sums})
+                           &pf->t_out, &pf->t_sums, &pf->t_fast})
     b->release();
   pf->t_hout.release();
   if (pf->score_ev0)

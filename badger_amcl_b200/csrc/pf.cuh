@@ -59,7 +59,8 @@ struct bamcl_pf
   bamcl::DevBuf t_slot, t_flag;                             // per sample
   bamcl::DevBuf t_nkey, t_cur, t_child, t_first_at, t_side; // per node (creation order)
   bamcl::DevBuf t_parent, t_cid, t_nfirst;
-  bamcl::DevBuf t_scan, t_out, t_sums;
+  bamcl::DevBuf t_scan, t_out, t_sums, t_fast;
+  int tree_fast = 0;        // the last tree build used the bucketed shared-memory path
   bamcl::PinBuf t_hout;
   size_t t_cluster_cap = 0;
   int coop_blocks = 0;

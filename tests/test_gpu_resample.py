@@ -182,3 +182,24 @@ def test_large_resample_matches_oracle(env, n, cloud):
         r = pf.update_resample()
         _assert_same_resample(pf, port, r, check_labels=(n <= 100000))
     pf.close()
+
+
+@pytest.mark.parametrize("order", ["random", "sorted_x"])
+@pytest.mark.parametrize("n", [1, 2, 300, 2048, 2049, 5000, 60000])
+def test_kdtree_leaf_count_paths(env, n, order):
+    """pf_kdtree.cpp:97-150: leaf / node counts and cluster labels of initWithPoseFn's tree. 'sorted_x' makes the
+    tree a chain so one bucket of the bucketed build overflows and the general grid kernel takes over."""
+    O, cabi = env["O"], env["cabi"]
+    cells = env["cells"]
+    poses = synth.uniform_free_poses(cells, RES, n, seed=11)
+    if order == "sorted_x":
+        if n > 20000:
+            pytest.skip("a 60k-deep chain is minutes of level steps")
+        poses = poses[np.argsort(poses[:, 0], kind="stable")]
+    port = O.PortPF(1, n)
+    port.init_with_poses(poses)
+    pf = cabi.ParticleFilter(env["ctx"], 1, n)
+    r = pf.init_with_poses(poses)
+    assert (r.leaf_count, r.node_count, r.cluster_count) == (port.leaf_count(), port.node_count(), port.cluster_count())
+    assert np.array_equal(pf.sample_clusters(), port.sample_clusters())
+    pf.close()

@@ -421,7 +421,10 @@ __global__ void __launch_bounds__(ST_BLOCK) k_labels_stats(const StatsArgs a)
         open[q] += v[q];
       continue;
     }
-    // mixed chunk: one warp reduction per distinct label
+    // mixed chunk: one warp reduction per distinct label. The first label seen becomes the warp's open row, so a
+    // dominant cluster is accumulated in registers instead of hammering one row with atomics.
+    if (open_label < 0)
+      open_label = first_label;
     unsigned todo = live_mask;
     while (todo)
     {

@@ -78,6 +78,7 @@ SIGNATURES = {
     "bamcl_host_alloc": (_I, [C.c_size_t, _P]),
     "bamcl_host_free": (_I, [_P]),
     "bamcl_pf_last_score_ms": (_I, [_P, _P]),
+    "bamcl_pf_set_exact_terms": (_I, [_P, _I]),
     "bamcl_map2d_create": (_I, [_P, _I, _I, _D, _F, _F, _P]),
     "bamcl_map2d_destroy": (_I, [_P]),
     "bamcl_map2d_set_cells": (_I, [_P, _P, _L]),
@@ -306,6 +307,9 @@ class ParticleFilter:
         _check(self.L.bamcl_pf_score_planar(self.h, map2d.h, C.byref(model), _p(ranges), _p(angles), len(ranges),
                                             range_max, int(self.converged), C.byref(total)))
         return total.value
+
+    def set_exact_terms(self, exact):
+        _check(self.L.bamcl_pf_set_exact_terms(self.h, int(exact)))
 
     def last_score_ms(self):
         ms = C.c_float()

@@ -126,6 +126,13 @@ __device__ __forceinline__ double warp_sum(double v)
     v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+__device__ __forceinline__ long long warp_sum_ll(long long v)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+    v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
 __device__ __forceinline__ int warp_sum_i(int v)
 {
 #pragma unroll

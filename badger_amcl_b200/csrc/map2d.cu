@@ -42,7 +42,8 @@ __global__ void k_edt_columns(const int8_t* __restrict__ cells, uint16_t* __rest
 // Writes the float cache with the reference's value formula and the tiled u16 field.
 template <int BLOCK>
 __global__ void k_edt_rows(const uint16_t* __restrict__ g, float* __restrict__ dist, uint16_t* __restrict__ kmap,
-                           int size_x, int size_y, int tiles_x, int layout, int radius, double resolution, float far_value)
+                           const uint16_t* __restrict__ rank_of_k, int size_x, int size_y, int tiles_x, int layout, int radius,
+                           double resolution, float far_value)
 {
   extern __shared__ uint16_t s_g[];  // BLOCK + 2*radius
   const int j = blockIdx.y;
@@ -77,13 +78,14 @@ __global__ void k_edt_rows(const uint16_t* __restrict__ g, float* __restrict__ d
     k = best;
   }
   dist[(size_t)j * size_x + i] = v;
-  kmap[tiled_offset(i, j, tiles_x, layout)] = (uint16_t)(k * 8);
+  kmap[tiled_offset(i, j, tiles_x, layout)] = rank_of_k[k];
 }
 
 // ---- uploaded cache -> tiled u16 field. A value is canonical if it is (float)(sqrt(k)*res) for an
 // integer k <= radius^2, or equals the far value.
-__global__ void k_index_uploaded(const float* __restrict__ dist, uint16_t* __restrict__ kmap, int size_x, int size_y,
-                                 int tiles_x, int layout, int radius, double resolution, float far_value, int* __restrict__ bad)
+__global__ void k_index_uploaded(const float* __restrict__ dist, uint16_t* __restrict__ kmap,
+                                 const uint16_t* __restrict__ rank_of_k, int size_x, int size_y, int tiles_x, int layout,
+                                 int radius, double resolution, float far_value, int* __restrict__ bad)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int j = blockIdx.y;
@@ -103,10 +105,13 @@ __global__ void k_index_uploaded(const float* __restrict__ dist, uint16_t* __res
         k = (int)t;
         ok = true;
       }
-    if (!ok)
+    if (!ok || rank_of_k[k] == 0xFFFF)  // not a value the brushfire can produce (k must be a sum of two squares)
+    {
       atomicAdd(bad, 1);
+      k = r2 + 1;
+    }
   }
-  kmap[tiled_offset(i, j, tiles_x, layout)] = (uint16_t)(k * 8);
+  kmap[tiled_offset(i, j, tiles_x, layout)] = rank_of_k[k];
 }
 
 // ---- "not free" bit fields for the ray march: bit (i & 31) of word [j][i >> 5] (rows) and
@@ -211,7 +216,8 @@ int bamcl_map2d_create(bamcl_ctx* ctx, int size_x, int size_y, double resolution
   m->origin_y = origin_y;
   m->tiles_x = (size_x + 7) / 8;
   m->tiles_y = (size_y + 7) / 8;
-  if (const char* e = getenv("BAMCL_LAYOUT"))  // layout experiments (profiles/), default 0
+  m->layout = 1;
+  if (const char* e = getenv("BAMCL_LAYOUT"))  // layout experiments (profiles/), default 1
     m->layout = atoi(e) % 3;
   *out = m;
   return BAMCL_OK;
@@ -225,6 +231,7 @@ int bamcl_map2d_destroy(bamcl_map2d* m)
   m->cells.release();
   m->dist.release();
   m->kmap.release();
+  m->rank_of_k.release();
   m->blocked_rows.release();
   m->blocked_cols.release();
   delete m;
@@ -250,10 +257,30 @@ static int prepare_cache(bamcl_map2d* m, double max_distance)
   const size_t n = (size_t)m->size_x * m->size_y;
   m->max_distance = max_distance;
   m->cell_radius = (int)std::floor(max_distance / m->resolution);
-  // the field stores k*8 (the byte offset into the f64 value table) in 16 bits
-  if (((long)m->cell_radius * m->cell_radius + 2) * 8 > 65535)
-    return set_error(BAMCL_E_UNSUPPORTED, "max_distance/resolution = %d cells exceeds the u16 field (90 cells)",
+  if (m->cell_radius > 250)
+    return set_error(BAMCL_E_UNSUPPORTED, "max_distance/resolution = %d cells exceeds the u16 field (250 cells)",
                      m->cell_radius);
+  // The field stores the RANK of k = di^2 + dj^2 among the values a brushfire can produce (sums of two squares
+  // <= radius^2, about 0.28 * radius^2 of them), then one rank for "in the map but beyond the radius". The
+  // scoring kernels index their per-scan value tables with it.
+  {
+    const int r2 = m->cell_radius * m->cell_radius;
+    std::vector<uint16_t> rank((size_t)r2 + 2, (uint16_t)0xFFFF);
+    std::vector<char> rep((size_t)r2 + 1, 0);
+    for (int a = 0; a <= m->cell_radius; a++)
+      for (int b = a; a * a + b * b <= r2; b++)
+        rep[a * a + b * b] = 1;
+    m->rep_k.clear();
+    for (int k = 0; k <= r2; k++)
+      if (rep[k])
+      {
+        rank[k] = (uint16_t)m->rep_k.size();
+        m->rep_k.push_back(k);
+      }
+    rank[r2 + 1] = (uint16_t)m->rep_k.size();
+    BAMCL_TRY(m->rank_of_k.reserve(sizeof(uint16_t) * rank.size()));
+    BAMCL_CUDA_OK(cudaMemcpy(m->rank_of_k.p, rank.data(), sizeof(uint16_t) * rank.size(), cudaMemcpyHostToDevice));
+  }
   BAMCL_TRY(m->dist.reserve(sizeof(float) * n));
   BAMCL_TRY(m->kmap.reserve(sizeof(uint16_t) * (size_t)m->tiles_x * m->tiles_y * 64));
   // cells of partial edge tiles that lie outside the map are never read; keep them defined anyway
@@ -281,7 +308,7 @@ int bamcl_map2d_build_distances(bamcl_map2d* m, double max_distance)
   dim3 grid((m->size_x + BLOCK - 1) / BLOCK, m->size_y);
   const size_t smem = sizeof(uint16_t) * (size_t)(BLOCK + 2 * m->cell_radius);
   BAMCL_LAUNCH(ctx, k_edt_rows<BLOCK>, grid, BLOCK, smem, g.as<uint16_t>(), m->dist.as<float>(), m->kmap.as<uint16_t>(),
-               m->size_x, m->size_y, m->tiles_x, m->layout, m->cell_radius, m->resolution, (float)max_distance);
+               m->rank_of_k.as<uint16_t>(), m->size_x, m->size_y, m->tiles_x, m->layout, m->cell_radius, m->resolution, (float)max_distance);
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
   g.release();
   m->has_dist = true;
@@ -300,8 +327,8 @@ int bamcl_map2d_upload_distances(bamcl_map2d* m, const float* distances, long n,
   BAMCL_TRY(bad.reserve(sizeof(int)));
   BAMCL_CUDA_OK(cudaMemsetAsync(bad.p, 0, sizeof(int), ctx->stream));
   dim3 grid((m->size_x + 255) / 256, m->size_y);
-  BAMCL_LAUNCH(ctx, k_index_uploaded, grid, 256, 0, m->dist.as<float>(), m->kmap.as<uint16_t>(), m->size_x, m->size_y,
-               m->tiles_x, m->layout, m->cell_radius, m->resolution, (float)max_distance, bad.as<int>());
+  BAMCL_LAUNCH(ctx, k_index_uploaded, grid, 256, 0, m->dist.as<float>(), m->kmap.as<uint16_t>(), m->rank_of_k.as<uint16_t>(),
+               m->size_x, m->size_y, m->tiles_x, m->layout, m->cell_radius, m->resolution, (float)max_distance, bad.as<int>());
   int h_bad = 0;
   BAMCL_CUDA_OK(cudaMemcpyAsync(&h_bad, bad.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));

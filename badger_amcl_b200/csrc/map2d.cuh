@@ -12,12 +12,14 @@ struct bamcl_map2d
   // row-major, index = i + j*size_x (occupancy_map.cpp:107-110)
   bamcl::DevBuf cells;  // int8: -1 free, 0 unknown, +1 occupied
   bamcl::DevBuf dist;   // float distance cache (distances_lut_)
-  // Tiled field for the particle x beam gathers: one u16 per cell holding k = di^2 + dj^2 of the nearest
-  // obstacle (the cached distance is (float)(sqrt(k)*resolution), occupancy_map.cpp:125,229-232) or
-  // k_far = radius^2 + 1 for cells beyond the radius. 8x8-cell tiles = one 128 B line; inside a tile
+  // Tiled field for the particle x beam gathers: one u16 per cell holding the rank of k = di^2 + dj^2 of the
+  // nearest obstacle (the cached distance is (float)(sqrt(k)*resolution), occupancy_map.cpp:125,229-232) or
+  // rep_k.size() for cells beyond the radius. 8x8-cell tiles = one 128 B line; inside a tile
   // four 4x4 blocks = one 32 B sector each, so a scan's end points (which trace wall contours) share
   // sectors in every direction.
   bamcl::DevBuf kmap;
+  bamcl::DevBuf rank_of_k;  // u16[radius^2 + 2]: k -> rank (0xFFFF = not a sum of two squares)
+  std::vector<int> rep_k;   // rank -> k for the representable k <= radius^2 (host copy, for the value tables)
   int tiles_x = 0, tiles_y = 0;
   int cell_radius = 0;  // floor(max_distance / resolution), occupancy_map.cpp:125
   double max_distance = 0.0;

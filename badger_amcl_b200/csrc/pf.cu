@@ -180,6 +180,7 @@ int bamcl_pf_destroy(bamcl_pf* pf)
   }
   pf->scan.beams.release();
   pf->scan.table.release();
+  pf->scan.table_q.release();
   pf->scan.ranges.release();
   pf->scan.angles.release();
   pf->scalars.release();
@@ -288,6 +289,14 @@ int bamcl_pf_score_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_mod
   BAMCL_TRY(launch_score(pf, map));
   BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
   return read_scalar(pf, 0, total_out);
+}
+
+int bamcl_pf_set_exact_terms(bamcl_pf* pf, int exact)
+{
+  if (!pf)
+    return set_error(BAMCL_E_ARG, "null pf");
+  pf->exact_terms = exact != 0;
+  return BAMCL_OK;
 }
 
 int bamcl_pf_last_score_ms(bamcl_pf* pf, float* ms)

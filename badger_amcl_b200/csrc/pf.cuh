@@ -27,6 +27,8 @@ struct StagedScan
   DevBuf beams;         // double2[n_beams]: (r cos b, r sin b) / resolution
   DevBuf table;         // f64[table_n]: per-k model value
   int table_n = 0;
+  DevBuf table_q;       // int32[table_n]: round(table * 2^q_shift), -1 shift = unusable
+  int q_shift = -1;
   double range_max = 0.0;
   uint64_t map_version = 0;
   // raw copies for the beam model
@@ -66,6 +68,7 @@ struct bamcl_pf
   int coop_blocks = 0;
   cudaEvent_t score_ev0 = nullptr, score_ev1 = nullptr;  // around the last scoring kernel (bamcl_pf_last_score_ms)
   bool score_timed = false;
+  bool exact_terms = false;  // bamcl_pf_set_exact_terms
   int tree_levels = 0;      // levels the last tree build needed (diagnostics)
 };
 

@@ -13,7 +13,9 @@
 // registers (adjacent lanes = adjacent beams = neighbouring cells -> shared sectors), particle data is
 // broadcast from shared memory, partial sums stay in registers until the batch ends.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <type_traits>
 #include <vector>
 
 #include "pf.cuh"
@@ -24,6 +26,7 @@ namespace
 {
 constexpr int PB = 16;    // particles per warp batch
 constexpr int BPL = 4;    // beams per lane per pass
+constexpr int GB = 4;     // particles per gather batch (GB * BPL loads in flight per lane)
 constexpr int WARPS = 8;  // warps per block
 constexpr int PASS_BEAMS = 32 * BPL;
 
@@ -38,6 +41,8 @@ struct ScoreArgs
   int n_beams;
   const double* table;
   int table_n;
+  const int* table_q;  // round(table * 2^q_shift) for the fixed-point path
+  double q_scale_inv;  // 2^-q_shift
   const uint16_t* kmap;
   int tiles_x, size_x, size_y;
   const int8_t* cells;
@@ -50,9 +55,15 @@ struct ScoreArgs
   double off_map_factor, non_free_space_factor, non_free_space_radius;
 };
 
-template <bool TAIL, int LAYOUT>
-__device__ __forceinline__ void score_pass(const ScoreArgs& a, const unsigned char* __restrict__ tab, const double4* stash,
-                                           int beam0, int lane, double (&acc)[PB])
+// TABLE: 2 = shared memory, 16 interleaved copies (entry r, copy c at double index r*16 + c; lane l reads copy
+// l & 15, so both half-warps of a 64-bit load are bank-conflict free whatever the ranks are); 1 = one copy in
+// shared memory; 0 = global memory.
+//         3 = shared memory, 32 interleaved copies of the table in 32-bit fixed point (entry r, copy l at int
+//             index r*32 + l: one wavefront per warp load); terms are summed as integers, so a particle's sum
+//             does not depend on the order or grouping of its beams.
+template <bool TAIL, int LAYOUT, int TABLE, typename Acc>
+__device__ __forceinline__ void score_pass(const ScoreArgs& a, const double* __restrict__ tab, const double4* stash,
+                                           int beam0, int lane, Acc (&acc)[PB])
 {
   double bx[BPL], by[BPL];
   bool live[BPL];
@@ -65,43 +76,91 @@ __device__ __forceinline__ void score_pass(const ScoreArgs& a, const unsigned ch
     bx[q] = v.x;
     by[q] = v.y;
   }
-  const int k_off = (a.table_n - 1) * 8;
+  const unsigned k_off = (unsigned)(a.table_n - 1);  // rank of "off the map"
+  const unsigned copy = TABLE == 2 ? (unsigned)(lane & 15) : 0u;
+  // GB particles x BPL beams = 16 gathers are issued back to back before the first one is consumed: the field
+  // lives in L2 (random poses leave nothing for L1), so a warp must keep many loads in flight to hide its latency.
 #pragma unroll
-  for (int g = 0; g < PB; g++)
+  for (int g0 = 0; g0 < PB; g0 += GB)
   {
-    const double4 p = stash[g];  // cos, sin, X, Y (cell units, +0.5 and +size/2 folded in)
+    unsigned kk[GB][BPL];
 #pragma unroll
-    for (int q = 0; q < BPL; q++)
+    for (int gg = 0; gg < GB; gg++)
     {
-      const double gx = fma(p.x, bx[q], fma(-p.y, by[q], p.z));
-      const double gy = fma(p.y, bx[q], fma(p.x, by[q], p.w));
-      const int ix = floor_to_int(gx);
-      const int iy = floor_to_int(gy);
-      const bool inb = ((unsigned)ix < (unsigned)a.size_x) && ((unsigned)iy < (unsigned)a.size_y);
-      int k = k_off;
-      if (inb)
-        k = __ldg(&a.kmap[tiled_offset_t<LAYOUT>(ix, iy, a.tiles_x)]);
-      const double v = *reinterpret_cast<const double*>(tab + k);  // the field holds byte offsets
-      if (!TAIL || live[q])
-        acc[g] += v;
+      const double4 p = stash[g0 + gg];  // cos, sin, X, Y (cell units, +0.5 and +size/2 folded in)
+#pragma unroll
+      for (int q = 0; q < BPL; q++)
+      {
+        const double gx = fma(p.x, bx[q], fma(-p.y, by[q], p.z));
+        const double gy = fma(p.y, bx[q], fma(p.x, by[q], p.w));
+        const int ix = floor_to_int(gx);
+        const int iy = floor_to_int(gy);
+        const bool inb = ((unsigned)ix < (unsigned)a.size_x) && ((unsigned)iy < (unsigned)a.size_y);
+        unsigned k = k_off;
+        if (inb)
+          k = __ldg(&a.kmap[tiled_offset_t<LAYOUT>(ix, iy, a.tiles_x)]);
+        kk[gg][q] = k;
+      }
+    }
+    if (TABLE == 3)
+    {
+      const int* tabq = reinterpret_cast<const int*>(tab);
+#pragma unroll
+      for (int gg = 0; gg < GB; gg++)
+      {
+        int part = 0;  // BPL terms fit 32 bits by construction of q_shift
+#pragma unroll
+        for (int q = 0; q < BPL; q++)
+        {
+          const int v = tabq[(kk[gg][q] << 5) | (unsigned)lane];
+          part += (!TAIL || live[q]) ? v : 0;
+        }
+        acc[g0 + gg] += part;
+      }
+    }
+    else
+    {
+#pragma unroll
+      for (int gg = 0; gg < GB; gg++)
+#pragma unroll
+        for (int q = 0; q < BPL; q++)
+        {
+          const unsigned k = kk[gg][q];
+          const double v = TABLE == 2 ? tab[(k << 4) | copy] : tab[k];
+          if (!TAIL || live[q])
+            acc[g0 + gg] += v;
+        }
     }
   }
 }
 
-template <bool SMEM_TAB, int LAYOUT>
+template <int TABLE, int LAYOUT>
 __global__ void __launch_bounds__(WARPS * 32) k_score_lf(const ScoreArgs a)
 {
   extern __shared__ __align__(16) unsigned char s_raw[];
   double4* s_stash = reinterpret_cast<double4*>(s_raw);                       // [WARPS][PB]
   double* s_tab = reinterpret_cast<double*>(s_raw + sizeof(double4) * WARPS * PB);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (SMEM_TAB)
+  if (TABLE == 3)
+  {
+    int* s_q = reinterpret_cast<int*>(s_tab);
+    for (int t = threadIdx.x; t < a.table_n * 32; t += blockDim.x)
+      s_q[t] = a.table_q[t >> 5];
+    __syncthreads();
+  }
+  else if (TABLE == 2)
+  {
+    for (int t = threadIdx.x; t < a.table_n * 16; t += blockDim.x)
+      s_tab[t] = a.table[t >> 4];
+    __syncthreads();
+  }
+  else if (TABLE == 1)
   {
     for (int t = threadIdx.x; t < a.table_n; t += blockDim.x)
       s_tab[t] = a.table[t];
     __syncthreads();
   }
-  const unsigned char* tab = reinterpret_cast<const unsigned char*>(SMEM_TAB ? s_tab : a.table);
+  const double* tab = TABLE != 0 ? s_tab : a.table;
   double4* stash = s_stash + warp * PB;
   const int n_batches = (a.n + PB - 1) / PB;
   const int warps_total = gridDim.x * WARPS;
@@ -151,21 +210,26 @@ __global__ void __launch_bounds__(WARPS * 32) k_score_lf(const ScoreArgs a)
     __syncwarp();
 
     // ---- beams
-    double acc[PB];
+    typedef typename std::conditional<TABLE == 3, long long, double>::type Acc;
+    Acc acc[PB];
 #pragma unroll
     for (int g = 0; g < PB; g++)
-      acc[g] = 0.0;
+      acc[g] = 0;
     for (int pass = 0; pass < n_full; pass++)
-      score_pass<false, LAYOUT>(a, tab, stash, pass * PASS_BEAMS, lane, acc);
+      score_pass<false, LAYOUT, TABLE, Acc>(a, tab, stash, pass * PASS_BEAMS, lane, acc);
     if (n_full * PASS_BEAMS < a.n_beams)
-      score_pass<true, LAYOUT>(a, tab, stash, n_full * PASS_BEAMS, lane, acc);
+      score_pass<true, LAYOUT, TABLE, Acc>(a, tab, stash, n_full * PASS_BEAMS, lane, acc);
 
     // ---- reduce the PB partial sums across lanes; lane g keeps particle g's sum
     double sum = 0.0;
 #pragma unroll
     for (int g = 0; g < PB; g++)
     {
-      const double v = warp_sum(acc[g]);
+      double v;
+      if (TABLE == 3)
+        v = (double)warp_sum_ll((long long)acc[g]) * a.q_scale_inv;  // exact: |total| < 2^53, power-of-two scale
+      else
+        v = warp_sum((double)acc[g]);
       if (lane == g)
         sum = v;
     }
@@ -278,7 +342,7 @@ int stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, 
 
   // beams that the reference integrates (:271-282), in cell units
   const size_t max_beams = (size_t)(range_count / step + 2);
-  BAMCL_TRY(pf->h_stage.reserve(sizeof(double) * 2 * max_beams + sizeof(double) * 70000));
+  BAMCL_TRY(pf->h_stage.reserve(sizeof(double) * 2 * max_beams + sizeof(double) * 100000));
   double* hb = pf->h_stage.as<double>();
   int nb = 0;
   for (int i = 0; i < range_count; i += step)
@@ -293,13 +357,14 @@ int stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, 
     nb++;
   }
   sc.n_beams = nb;
-  // value table over k = squared cell distance; [r2+1] = in-map cell beyond the radius; [r2+2] = off the map
-  const int r2 = map->cell_radius * map->cell_radius;
-  const int tn = r2 + 3;
+  // value table over the rank of k = squared cell distance (map2d.cuh); [n_rep] = in-map cell beyond the
+  // radius; [n_rep + 1] = off the map
+  const int n_rep = (int)map->rep_k.size();
+  const int tn = n_rep + 2;
   double* ht = hb + 2 * max_beams;
-  for (int k = 0; k <= r2; k++)
-    ht[k] = lf_term(*model, (double)(float)(std::sqrt((double)k) * map->resolution), range_max);
-  ht[r2 + 1] = lf_term(*model, (double)(float)map->max_distance, range_max);
+  for (int r = 0; r < n_rep; r++)
+    ht[r] = lf_term(*model, (double)(float)(std::sqrt((double)map->rep_k[r]) * map->resolution), range_max);
+  ht[n_rep] = lf_term(*model, (double)(float)map->max_distance, range_max);
   if (type == BAMCL_PLANAR_LF_PROB)
   {
     // :350,:443: off-map beams use exp(-max^2/denom) with the un-narrowed max distance
@@ -308,10 +373,32 @@ int stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, 
     double pz = 0.0;
     pz += model->z_hit * max_dist_prob;
     pz += model->z_rand * (1.0 / range_max);
-    ht[r2 + 2] = std::log(pz);
+    ht[n_rep + 1] = std::log(pz);
   }
   else
-    ht[r2 + 2] = lf_term(*model, map->max_distance, range_max);  // :298,:613: z = getMaxDistanceToObject()
+    ht[n_rep + 1] = lf_term(*model, map->max_distance, range_max);  // :298,:613: z = getMaxDistanceToObject()
+  // fixed-point copy: the largest shift that keeps BPL terms inside 32 bits; unusable if a term is not finite
+  {
+    double maxabs = 0.0;
+    bool finite = true;
+    for (int r = 0; r < tn; r++)
+    {
+      finite = finite && std::isfinite(ht[r]);
+      maxabs = std::max(maxabs, std::fabs(ht[r]));
+    }
+    int* hq = reinterpret_cast<int*>(ht + tn);
+    sc.q_shift = -1;
+    if (finite && maxabs > 0.0 && maxabs < 1e6)
+    {
+      int e;
+      std::frexp(maxabs * BPL, &e);  // maxabs * BPL < 2^e
+      sc.q_shift = 30 - e;
+      for (int r = 0; r < tn; r++)
+        hq[r] = (int)std::llrint(std::ldexp(ht[r], sc.q_shift));
+      BAMCL_TRY(sc.table_q.reserve(sizeof(int) * (size_t)tn));
+      BAMCL_CUDA_OK(cudaMemcpyAsync(sc.table_q.p, hq, sizeof(int) * tn, cudaMemcpyHostToDevice, ctx->stream));
+    }
+  }
   sc.table_n = tn;
   BAMCL_TRY(sc.beams.reserve(sizeof(double) * 2 * (size_t)(nb + 1)));
   BAMCL_TRY(sc.table.reserve(sizeof(double) * (size_t)tn));
@@ -350,6 +437,8 @@ int launch_score(bamcl_pf* pf, bamcl_map2d* map)
   a.n_beams = sc.n_beams;
   a.table = sc.table.as<double>();
   a.table_n = sc.table_n;
+  a.table_q = sc.table_q.as<int>();
+  a.q_scale_inv = std::ldexp(1.0, -sc.q_shift);
   a.kmap = map->kmap.as<uint16_t>();
   a.tiles_x = map->tiles_x;
   a.size_x = map->size_x;
@@ -376,18 +465,37 @@ int launch_score(bamcl_pf* pf, bamcl_map2d* map)
 
   const int n_batches = (a.n + PB - 1) / PB;
   int blocks = (n_batches + WARPS - 1) / WARPS;
-  const int max_blocks = kNumSMs * 2;
+  static const int per_sm = getenv("BAMCL_SCORE_CTAS") ? atoi(getenv("BAMCL_SCORE_CTAS")) : 4;
+  const int max_blocks = kNumSMs * per_sm;
   if (blocks > max_blocks)
     blocks = max_blocks;
   const size_t stash_bytes = sizeof(double4) * WARPS * PB;
   const size_t tab_bytes = sizeof(double) * (size_t)a.table_n;
-  const bool smem_tab = tab_bytes <= 40 * 1024;
+  // bamcl_pf_set_exact_terms(pf, 1) / BAMCL_EXACT_TERMS=1 keeps every per-beam term a bit-exact f64 (modes 2/1/0); the default fixed-point table
+  // is within 2^-28 relative of the largest term per beam (DESIGN.md "K-a").
+  static const bool env_exact = getenv("BAMCL_EXACT_TERMS") != nullptr && atoi(getenv("BAMCL_EXACT_TERMS")) != 0;
+  const bool exact_terms = env_exact || pf->exact_terms;
+  const bool can_fixed = sc.q_shift >= 0 && !exact_terms && tab_bytes * 16 <= 64 * 1024;
+  const int table_mode = can_fixed ? 3 : tab_bytes * 16 <= 64 * 1024 ? 2 : tab_bytes <= 40 * 1024 ? 1 : 0;
+  const size_t smem_bytes = stash_bytes + (table_mode >= 2 ? tab_bytes * 16 : table_mode == 1 ? tab_bytes : 0);
   BAMCL_CUDA_OK(cudaEventRecord(pf->score_ev0, ctx->stream));
-#define BAMCL_SCORE_CASE(L)                                                                          \
-  if (smem_tab)                                                                                      \
-    BAMCL_LAUNCH(ctx, (k_score_lf<true, L>), blocks, WARPS * 32, stash_bytes + tab_bytes, a);        \
-  else                                                                                               \
-    BAMCL_LAUNCH(ctx, (k_score_lf<false, L>), blocks, WARPS * 32, stash_bytes, a);
+#define BAMCL_SCORE_CASE(L)                                                                              \
+  if (table_mode == 3)                                                                                   \
+  {                                                                                                      \
+    BAMCL_CUDA_OK(cudaFuncSetAttribute((k_score_lf<3, L>), cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                       (int)(stash_bytes + 64 * 1024)));                                 \
+    BAMCL_LAUNCH(ctx, (k_score_lf<3, L>), blocks, WARPS * 32, smem_bytes, a);                            \
+  }                                                                                                      \
+  else if (table_mode == 2)                                                                                   \
+  {                                                                                                      \
+    BAMCL_CUDA_OK(cudaFuncSetAttribute((k_score_lf<2, L>), cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                       (int)(stash_bytes + 64 * 1024)));                                 \
+    BAMCL_LAUNCH(ctx, (k_score_lf<2, L>), blocks, WARPS * 32, smem_bytes, a);                            \
+  }                                                                                                      \
+  else if (table_mode == 1)                                                                              \
+    BAMCL_LAUNCH(ctx, (k_score_lf<1, L>), blocks, WARPS * 32, smem_bytes, a);                            \
+  else                                                                                                   \
+    BAMCL_LAUNCH(ctx, (k_score_lf<0, L>), blocks, WARPS * 32, smem_bytes, a);
   if (map->layout == 0)
   {
     BAMCL_SCORE_CASE(0)

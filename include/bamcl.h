@@ -126,6 +126,11 @@ int bamcl_pf_stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model
                         const double* angles, int range_count, double range_max);
 int bamcl_pf_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out_or_null);
 
+/* Likelihood-field scoring sums one table term per beam. Default: terms in 32-bit fixed point summed as integers
+ * (order-independent, |error| <= 2^-28 of the largest term per beam -- far inside the 1e-5 log-weight bound).
+ * exact = 1: every term is the bit-exact f64 the reference computes (planar_scanner.cpp:303-315), summed in f64. */
+int bamcl_pf_set_exact_terms(bamcl_pf* pf, int exact);
+
 /* device duration of the most recent scoring kernel launch alone (CUDA events around that launch on the
  * context's stream); bench.py's roofline figure */
 int bamcl_pf_last_score_ms(bamcl_pf* pf, float* ms);

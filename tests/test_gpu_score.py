@@ -1,8 +1,9 @@
 """GPU parity: K-a / K-b scoring kernels vs the oracle on the same seeded inputs.
 
 Tolerance (BASELINE.json north_star): per-particle log-weights within 1e-5 relative. The kernels are far
-tighter in practice (identical cells, host-built per-cell terms), so a 1e-9 relative bound on the weights
-themselves is asserted as well; it would catch a flipped cell look-up."""
+tighter in practice (identical cells, host-built per-cell terms): in exact-term mode a 1e-9 relative bound on the
+weights themselves is asserted as well (it would catch a flipped cell look-up); in the default fixed-point mode
+the bound is the worst case of the 32-bit term quantisation, 2e-5 (typically 1e-7)."""
 import numpy as np
 import pytest
 
@@ -59,9 +60,10 @@ MODELS = {
 }
 
 
+@pytest.mark.parametrize("terms", ["fixed", "exact"])
 @pytest.mark.parametrize("name", list(MODELS))
 @pytest.mark.parametrize("n_beams", [60, 1080])
-def test_apply_model_matches_oracle(env, name, n_beams):
+def test_apply_model_matches_oracle(env, name, n_beams, terms):
     """applyModelToSampleSet: un-normalised weights and the returned total (C1 shape: 5k x 60; and 1080 beams)"""
     O, cabi = env["O"], env["cabi"]
     n = 5000 if n_beams == 60 else 1500
@@ -75,11 +77,13 @@ def test_apply_model_matches_oracle(env, name, n_beams):
     samples = _samples(env, n)
     want_total, want_w = env["pm"].apply(O.planar_model(**kw), ranges, angles, 30.0, samples)
     pf = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    pf.set_exact_terms(terms == "exact")
     pf.upload_samples(samples)
     got_total = pf.score_planar(env["m"], cabi.planar_model(**kw), ranges, angles, 30.0)
     got_w = pf.weights()
-    assert_weights_close(got_w, want_w)
-    assert abs(got_total - want_total) <= 1e-12 * abs(want_total)
+    exact = terms == "exact" or name == "beam"
+    assert_weights_close(got_w, want_w, rtol=1e-9 if exact else 2e-5)
+    assert abs(got_total - want_total) <= (1e-12 if exact else 2e-5) * abs(want_total)
     pf.close()
 
 
@@ -93,6 +97,7 @@ def test_fused_update_matches_oracle_sequence(env):
     port = O.PortPF(n // 10, n)
     port.init_with_poses(poses)
     pf = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    pf.set_exact_terms(True)
     aos = np.concatenate([poses, np.full((n, 1), 1.0 / n)], axis=1)
     pf.upload_samples(aos)
     for _ in range(2):

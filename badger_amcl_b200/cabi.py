@@ -29,6 +29,27 @@ class PlanarModel(C.Structure):
                 ("scanner_pose", C.c_double * 3)]
 
 
+class CloudModel(C.Structure):
+    _fields_ = [("model_type", C.c_int), ("max_beams", C.c_int), ("z_hit", C.c_double), ("z_rand", C.c_double),
+                ("sigma_hit", C.c_double), ("gompertz_a", C.c_double), ("gompertz_b", C.c_double),
+                ("gompertz_c", C.c_double), ("input_shift", C.c_double), ("input_scale", C.c_double),
+                ("output_shift", C.c_double), ("off_map_factor", C.c_double), ("mount_translation", C.c_double * 3),
+                ("mount_rotation", C.c_double * 4)]
+
+
+def cloud_model(model_type=0, max_beams=4096, z_hit=0.95, z_rand=0.05, sigma_hit=0.2,
+                gompertz=(1.0, 1.0, 1.0, 0.0, 1.0, 0.0), off_map_factor=1.0, mount_translation=(0.0, 0.0, 0.0),
+                mount_rotation=(0.0, 0.0, 0.0, 1.0)):
+    """Defaults are the reference node's (node_3d.cpp:58-94)."""
+    p = CloudModel()
+    p.model_type, p.max_beams, p.z_hit, p.z_rand, p.sigma_hit = model_type, max_beams, z_hit, z_rand, sigma_hit
+    (p.gompertz_a, p.gompertz_b, p.gompertz_c, p.input_shift, p.input_scale, p.output_shift) = gompertz
+    p.off_map_factor = off_map_factor
+    p.mount_translation[:] = mount_translation
+    p.mount_rotation[:] = mount_rotation
+    return p
+
+
 class ResampleParams(C.Structure):
     _fields_ = [("resample_systematic", C.c_int), ("min_samples", C.c_int), ("max_samples", C.c_int),
                 ("pop_err", C.c_double), ("pop_z", C.c_double), ("w_diff", C.c_double), ("dist_threshold", C.c_double),
@@ -86,6 +107,17 @@ SIGNATURES = {
     "bamcl_map2d_upload_distances": (_I, [_P, _P, _L, _D]),
     "bamcl_map2d_download_distances": (_I, [_P, _P, _L]),
     "bamcl_map2d_calc_range": (_I, [_P, _P, _P, _P, _L, _D, _P, _P]),
+    "bamcl_map3d_create": (_I, [_P, _D, _D, _P, _L, _P]),
+    "bamcl_map3d_destroy": (_I, [_P]),
+    "bamcl_map3d_get_bounds": (_I, [_P, _P, _P]),
+    "bamcl_map3d_set_bounds": (_I, [_P, _P, _P]),
+    "bamcl_map3d_build_distances": (_I, [_P]),
+    "bamcl_map3d_upload_distances": (_I, [_P, _P, _L]),
+    "bamcl_map3d_download_distances": (_I, [_P, _P, _L]),
+    "bamcl_pf_score_cloud": (_I, [_P, _P, _P, _P, _L, _P]),
+    "bamcl_pf_update_cloud": (_I, [_P, _P, _P, _P, _L, _P]),
+    "bamcl_pf_stage_cloud": (_I, [_P, _P, _P, _P, _L]),
+    "bamcl_pf_update_cloud_staged": (_I, [_P, _P, _P]),
     "bamcl_pf_create": (_I, [_P, _I, _I, _P]),
     "bamcl_pf_destroy": (_I, [_P]),
     "bamcl_pf_upload_samples": (_I, [_P, _P, _L]),
@@ -218,6 +250,49 @@ class Map2D:
         return (out, steps.value) if with_steps else out
 
 
+class Map3D:
+    """OctoMap (include/amcl/map/octomap.h:61-81) on the device; `keys` = occupied leaf keys (n, 3)."""
+
+    def __init__(self, ctx, resolution, keys, max_distance):
+        self.ctx, self.L = ctx, ctx.L
+        keys = np.ascontiguousarray(keys, np.int32)
+        h = C.c_void_p()
+        _check(self.L.bamcl_map3d_create(ctx.h, resolution, max_distance, _p(keys), len(keys), C.byref(h)))
+        self.h = h
+        self.resolution, self.max_distance = resolution, max_distance
+
+    def close(self):
+        if self.h:
+            self.L.bamcl_map3d_destroy(self.h)
+            self.h = None
+
+    def bounds(self):
+        mn, mx = (C.c_int * 3)(), (C.c_int * 3)()
+        _check(self.L.bamcl_map3d_get_bounds(self.h, mn, mx))
+        return np.array(mn[:]), np.array(mx[:])
+
+    def shape(self):
+        mn, mx = self.bounds()
+        return tuple(int(v) for v in (mx - mn + 1)[::-1])  # (D, H, W)
+
+    def set_bounds(self, mn, mx):
+        a, b = (C.c_double * 2)(*mn), (C.c_double * 2)(*mx)
+        _check(self.L.bamcl_map3d_set_bounds(self.h, a, b))
+
+    def build_distances(self):
+        _check(self.L.bamcl_map3d_build_distances(self.h))
+
+    def upload_distances(self, field):
+        f = np.ascontiguousarray(field, np.uint8)
+        assert f.shape == self.shape()
+        _check(self.L.bamcl_map3d_upload_distances(self.h, _p(f), f.size))
+
+    def download_distances(self):
+        out = np.empty(self.shape(), np.uint8)
+        _check(self.L.bamcl_map3d_download_distances(self.h, _p(out), out.size))
+        return out
+
+
 class ParticleFilter:
     """Device side of ParticleFilter (include/amcl/pf/particle_filter.h:96-130). The scalar bookkeeping the
     reference keeps in the class (w_slow_/w_fast_, current_set_, converged_) lives in the host C++ mirror
@@ -348,6 +423,37 @@ class ParticleFilter:
         total = C.c_double()
         _check(self.L.bamcl_pf_update_planar_staged(self.h, map2d.h, int(self.converged),
                                                     C.byref(total) if want_total else None))
+        if want_total:
+            self._averages(total.value)
+            return total.value
+        return None
+
+    # -- 3-D sensor update
+    def score_cloud(self, map3d, model, points):
+        """PointCloudScanner::applyModelToSampleSet: returns the total; weights stay un-normalised."""
+        pts = np.ascontiguousarray(points, np.float32)
+        total = C.c_double()
+        _check(self.L.bamcl_pf_score_cloud(self.h, map3d.h, C.byref(model), _p(pts), len(pts), C.byref(total)))
+        return total.value
+
+    def update_sensor_cloud(self, map3d, model, points):
+        """PointCloudScanner::updateSensor -> ParticleFilter::updateSensor, fused on the device."""
+        if model.max_beams < 2:
+            return False
+        pts = np.ascontiguousarray(points, np.float32)
+        total = C.c_double()
+        _check(self.L.bamcl_pf_update_cloud(self.h, map3d.h, C.byref(model), _p(pts), len(pts), C.byref(total)))
+        self._averages(total.value)
+        self.last_total = total.value
+        return True
+
+    def stage_cloud(self, map3d, model, points):
+        pts = np.ascontiguousarray(points, np.float32)
+        _check(self.L.bamcl_pf_stage_cloud(self.h, map3d.h, C.byref(model), _p(pts), len(pts)))
+
+    def update_cloud_staged(self, map3d, want_total=True):
+        total = C.c_double()
+        _check(self.L.bamcl_pf_update_cloud_staged(self.h, map3d.h, C.byref(total) if want_total else None))
         if want_total:
             self._averages(total.value)
             return total.value

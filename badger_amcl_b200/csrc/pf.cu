@@ -118,7 +118,22 @@ int pf_reduce_total(bamcl_pf* pf, double* d_total)
 }
 }  // namespace bamcl
 
-static int read_scalar(bamcl_pf* pf, int slot, double* out)
+namespace bamcl
+{
+int pf_normalise_by_device_total(bamcl_pf* pf)
+{
+  SampleSet& s = pf->sets[pf->current];
+  if (s.sample_count > 0)
+    BAMCL_LAUNCH(pf->ctx, k_normalise, (s.sample_count + 255) / 256, 256, 0, s.w.as<double>(), s.sample_count,
+                 pf->scalars.as<double>());
+  return BAMCL_OK;
+}
+int pf_read_scalar(bamcl_pf* pf, int slot, double* out);
+}  // namespace bamcl
+
+static int read_scalar(bamcl_pf* pf, int slot, double* out) { return bamcl::pf_read_scalar(pf, slot, out); }
+
+int bamcl::pf_read_scalar(bamcl_pf* pf, int slot, double* out)
 {
   BAMCL_CUDA_OK(cudaMemcpyAsync(pf->h_scalars.as<double>() + slot, pf->scalars.as<double>() + slot, sizeof(double),
                                 cudaMemcpyDeviceToHost, pf->ctx->stream));
@@ -183,6 +198,8 @@ int bamcl_pf_destroy(bamcl_pf* pf)
   pf->scan.table_q.release();
   pf->scan.ranges.release();
   pf->scan.angles.release();
+  for (bamcl::DevBuf* b : {&pf->cloud.xyz, &pf->cloud.px, &pf->cloud.py, &pf->cloud.pz, &pf->cloud.table})
+    b->release();
   pf->scalars.release();
   pf->h_scalars.release();
   pf->h_stage.release();

@@ -35,6 +35,16 @@ struct StagedScan
   DevBuf ranges, angles;
   int range_count = 0, step = 1;
 };
+// Point cloud staged for the 3-D scoring kernel.
+struct StagedCloud
+{
+  bool valid = false;
+  bamcl_cloud_model model;
+  int n_points = 0;
+  DevBuf xyz, px, py, pz;  // packed upload + SoA split (f32, sensor frame)
+  DevBuf table;            // f64[257]: per-quantum model value, [256] = outside the map
+  uint64_t map_version = 0;
+};
 }  // namespace bamcl
 
 struct bamcl_pf
@@ -44,6 +54,7 @@ struct bamcl_pf
   bamcl::SampleSet sets[2];
   int current = 0;
   bamcl::StagedScan scan;
+  bamcl::StagedCloud cloud;
   bamcl::DevBuf scalars;   // small device scratch for totals etc.
   bamcl::PinBuf h_scalars; // pinned mirror
   bamcl::PinBuf h_stage;   // pinned staging for uploads
@@ -81,4 +92,6 @@ inline int* pf_flags(bamcl_pf* pf) { return reinterpret_cast<int*>(pf->scalars.a
 namespace bamcl
 {
 int pf_reduce_total(bamcl_pf* pf, double* d_total);  // deterministic sum of the current set's weights -> device scalar
+int pf_read_scalar(bamcl_pf* pf, int slot, double* out);  // device scalar slot -> host (synchronises)
+int pf_normalise_by_device_total(bamcl_pf* pf);           // w /= scalars[0] (or 1/n), particle_filter.cpp:237-266
 }

@@ -167,3 +167,58 @@ def reference_test_map():
     cells[10, 5:14] = OCCUPIED
     cells[15, 5:14] = OCCUPIED
     return cells
+
+
+# ---------------------------------------------------------------------------------------------
+# 3-D world: floor plane + wall slabs + clutter as occupied octree leaf keys
+# ---------------------------------------------------------------------------------------------
+def make_voxel_world(size_x=400, size_y=400, size_z=60, seed=3, wall_every=100, clutter=0.003):
+    """Occupied leaf keys (n, 3) int32 of a room world: floor at k = 0, walls of full height every `wall_every`
+    voxels with door gaps, random clutter in the lower third. Keys are centred on the origin in x / y."""
+    rng = np.random.default_rng(seed)
+    occ = np.zeros((size_z, size_y, size_x), bool)
+    occ[0] = True
+    jj, ii = np.meshgrid(np.arange(size_y), np.arange(size_x), indexing="ij")
+    door = ((ii // 9 + jj // 13) % 4) == 0
+    wall = (((ii % wall_every) == 0) | ((jj % wall_every) == 0)) & ~door
+    wall[0, :] = wall[-1, :] = True
+    wall[:, 0] = wall[:, -1] = True
+    occ[:, wall] = True
+    low = max(1, size_z // 3)
+    occ[1:low] |= rng.random((low - 1, size_y, size_x)) < clutter
+    k, j, i = np.nonzero(occ)
+    keys = np.stack([i - size_x // 2, j - size_y // 2, k], axis=1).astype(np.int32)
+    return keys
+
+
+def make_cloud(keys, resolution, truth_pose, n_points=4096, mount=(0.2, 0.0, 1.5), max_range=20.0, seed=4, noise=0.01):
+    """Sensor-frame cloud (n, 3) float32: occupied voxel centres seen from the sensor at the truth pose (within
+    max_range, no occlusion test -- the scorer does not need one), sub-sampled to n_points, plus noise."""
+    rng = np.random.default_rng(seed)
+    c = (keys.astype(np.float64) + 0.5) * resolution
+    x, y, th = truth_pose
+    cs, sn = math.cos(th), math.sin(th)
+    sx = x + cs * mount[0] - sn * mount[1]
+    sy = y + sn * mount[0] + cs * mount[1]
+    sz = mount[2]
+    d = c - np.array([sx, sy, sz])
+    near = np.nonzero((d ** 2).sum(1) < max_range ** 2)[0]
+    pick = near[rng.permutation(len(near))[:n_points]]
+    pick.sort()
+    d = d[pick]
+    # world -> sensor frame (yaw only; the mount's small pitch is ignored by the generator)
+    px = cs * d[:, 0] + sn * d[:, 1]
+    py = -sn * d[:, 0] + cs * d[:, 1]
+    pts = np.stack([px, py, d[:, 2]], axis=1) + rng.normal(0.0, noise, (len(d), 3))
+    if len(pts) < n_points:  # small worlds: repeat with fresh noise
+        reps = -(-n_points // max(1, len(pts)))
+        pts = np.concatenate([pts + rng.normal(0.0, noise, pts.shape) for _ in range(reps)])[:n_points]
+    return np.ascontiguousarray(pts, np.float32)
+
+
+def rpy_quaternion(roll, pitch, yaw):
+    """tf2::Quaternion::setRPY (x, y, z, w)"""
+    hr, hp, hy = roll * 0.5, pitch * 0.5, yaw * 0.5
+    cr, sr, cp, sp, cy, sy = math.cos(hr), math.sin(hr), math.cos(hp), math.sin(hp), math.cos(hy), math.sin(hy)
+    return (sr * cp * cy - cr * sp * sy, cr * sp * cy + sr * cp * sy, cr * cp * sy - sr * sp * cy,
+            cr * cp * cy + sr * sp * sy)

@@ -75,6 +75,41 @@ int bamcl_map2d_download_distances(bamcl_map2d* m, float* out, long n);
 int bamcl_map2d_calc_range(bamcl_map2d* m, const double* ox, const double* oy, const double* oa, long n,
                            double max_range, double* ranges_out, long* steps_total_or_null);
 
+/* ---- OctoMap (include/amcl/map/octomap.h:61-81) */
+/* ctor + initFromOctree (octomap.cpp:30-74). The octomap::OcTree argument becomes the list of its occupied leaves
+ * as integer keys (leaf centre = (key + 0.5) * resolution, octomap's keyToCoord), 3 ints per leaf. */
+int bamcl_map3d_create(bamcl_ctx* ctx, double resolution, double max_distance, const int* keys, long n_keys,
+                       bamcl_map3d** out);
+int bamcl_map3d_destroy(bamcl_map3d* m);
+/* getMinMaxCells (octomap.h:75): inclusive voxel bounds after cropping */
+int bamcl_map3d_get_bounds(bamcl_map3d* m, int mn[3], int mx[3]);
+/* setMapBounds (octomap.cpp:128-150): crop x/y to [mn - max_distance, mx + max_distance] and rebuild the cache */
+int bamcl_map3d_set_bounds(bamcl_map3d* m, const double mn[2], const double mx[2]);
+/* updateDistancesLUT (octomap.cpp:174-207) as the EXACT quantised distance transform
+ * floor(min(d, max) / max * 255) (the reference's FIFO brushfire differs in a few voxels per million) */
+int bamcl_map3d_build_distances(bamcl_map3d* m);
+/* install / read the cache as a dense u8 field over the bounds, x fastest, then y, then z
+ * (getDistanceToObject(i, j, k) = field * max_distance / 255, octomap.cpp:336-350) */
+int bamcl_map3d_upload_distances(bamcl_map3d* m, const uint8_t* dense, long n);
+int bamcl_map3d_download_distances(bamcl_map3d* m, uint8_t* out, long n);
+
+/* ---- PointCloudScanner (include/amcl/sensors/point_cloud_scanner.h:59-78) */
+enum
+{
+  BAMCL_CLOUD_PLAIN = 0,   /* setPointCloudModel :61 */
+  BAMCL_CLOUD_GOMPERTZ = 1 /* setPointCloudModelGompertz :62 */
+};
+typedef struct
+{
+  int model_type;
+  int max_beams; /* init :59 */
+  double z_hit, z_rand, sigma_hit;
+  double gompertz_a, gompertz_b, gompertz_c, input_shift, input_scale, output_shift;
+  double off_map_factor;       /* setMapFactors :73 (the non-free-space factors are unused in 3-D) */
+  double mount_translation[3]; /* setPointCloudScannerToFootprintTF :76 (geometry_msgs::Transform) */
+  double mount_rotation[4];    /* quaternion x, y, z, w */
+} bamcl_cloud_model;
+
 /* ---- PlanarScanner (include/amcl/sensors/planar_scanner.h:62-96) */
 enum
 {
@@ -125,6 +160,19 @@ int bamcl_pf_update_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_mo
 int bamcl_pf_stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
                         const double* angles, int range_count, double range_max);
 int bamcl_pf_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out_or_null);
+
+/* PointCloudScanner::applyModelToSampleSet (point_cloud_scanner.cpp:111-129) on the current set: per-particle
+ * cloud transform (getMapCloud :231-248), calcPointCloudModel / Gompertz (:132-203) and recalcWeight (:205-229)
+ * in one launch. points_xyz = PointCloudData::points_ (point_cloud_scanner.h:50) as packed float x, y, z in the
+ * sensor frame. */
+int bamcl_pf_score_cloud(bamcl_pf* pf, bamcl_map3d* map, const bamcl_cloud_model* model, const float* points_xyz,
+                         long n_points, double* total_out);
+/* fused PointCloudScanner::updateSensor (:92-102): score + total + normalise */
+int bamcl_pf_update_cloud(bamcl_pf* pf, bamcl_map3d* map, const bamcl_cloud_model* model, const float* points_xyz,
+                          long n_points, double* total_out);
+int bamcl_pf_stage_cloud(bamcl_pf* pf, bamcl_map3d* map, const bamcl_cloud_model* model, const float* points_xyz,
+                         long n_points);
+int bamcl_pf_update_cloud_staged(bamcl_pf* pf, bamcl_map3d* map, double* total_out_or_null);
 
 /* Likelihood-field scoring sums one table term per beam. Default: terms in 32-bit fixed point summed as integers
  * (order-independent, |error| <= 2^-28 of the largest term per beam -- far inside the 1e-5 log-weight bound).

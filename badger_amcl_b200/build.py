@@ -32,6 +32,31 @@ def build(force=False, verbose=False):
     return OUT
 
 
+HOST = os.path.join(HERE, "host")
+HOST_LIB = os.path.join(HERE, "libbadger_amcl.so")
+HOST_TEST = os.path.join(HOST, "test", "test_host_api")
+CXX = os.environ.get("CXX", "g++")
+
+
+def build_host(force=False):
+    """libbadger_amcl.so: the C++ mirror of the reference's class API (host/include/amcl/...) over the C ABI, and
+    the test driver that runs the reference's own unit tests against it. Plain g++: no CUDA in these sources."""
+    srcs = sorted(glob.glob(os.path.join(HOST, "src", "*.cpp")))
+    hdrs = glob.glob(os.path.join(HOST, "include", "amcl", "*", "*.h")) + glob.glob(os.path.join(HOST, "include", "amcl", "*.h"))
+    inc = ["-I", os.path.join(HOST, "include"), "-I", os.path.join(HERE, "..", "include")]
+    common = [CXX, "-std=c++17", "-O2", "-fPIC", "-ffp-contract=off", "-Wall"] + inc
+    def stale(out, deps):
+        return force or not os.path.exists(out) or any(os.path.getmtime(d) > os.path.getmtime(out) for d in deps)
+    if stale(HOST_LIB, srcs + hdrs + [OUT]):
+        subprocess.check_call(common + ["-shared", "-o", HOST_LIB] + srcs + ["-L", HERE, "-lbamcl_cuda", "-Wl,-rpath,$ORIGIN"])
+    test_src = os.path.join(HOST, "test", "test_host_api.cpp")
+    if stale(HOST_TEST, [test_src, HOST_LIB] + hdrs):
+        subprocess.check_call(common + ["-o", HOST_TEST, test_src, "-L", HERE, "-lbadger_amcl", "-lbamcl_cuda",
+                                        "-Wl,-rpath,$ORIGIN/../.."])
+    return HOST_LIB
+
+
 if __name__ == "__main__":
     build(force=True, verbose="-v" in sys.argv)
+    build_host(force=True)
     print(OUT)

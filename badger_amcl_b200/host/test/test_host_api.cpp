@@ -1,0 +1,326 @@
+// The reference's own unit tests (test/test_badger_amcl.cpp:51-171: testPfKdtree, testOctoMapConversions,
+// testOccupancyMapConversions, testOccupancyMapDistances) run against the host mirror of the class API, plus a
+// "flow" mode that drives scan -> updateSensor -> updateResample through the same classes on inputs read from a
+// file, so tests/ can compare the outputs with the oracle on identical bytes. No gtest/ROS on the box: a few
+// macros stand in for EXPECT_*.
+//   test_host_api kats
+//   test_host_api flow <in.bin> <out.bin>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "amcl/map/occupancy_map.h"
+#include "amcl/map/octomap.h"
+#include "amcl/pf/particle_filter.h"
+#include "amcl/pf/pdf_gaussian.h"
+#include "amcl/sensors/planar_scanner.h"
+#include "amcl/sensors/point_cloud_scanner.h"
+
+static int g_failed = 0;
+#define EXPECT_TRUE(c)                                                  \
+  do                                                                    \
+  {                                                                     \
+    if (!(c))                                                           \
+    {                                                                   \
+      std::printf("FAILED %s:%d: %s\n", __FILE__, __LINE__, #c);        \
+      g_failed++;                                                       \
+    }                                                                   \
+  } while (0)
+#define EXPECT_EQ(a, b) EXPECT_TRUE((a) == (b))
+// gtest's EXPECT_DOUBLE_EQ: within 4 ulps
+static bool almostEqual(double a, double b)
+{
+  if (a == b)
+    return true;
+  long long ia, ib;
+  std::memcpy(&ia, &a, 8);
+  std::memcpy(&ib, &b, 8);
+  if ((ia < 0) != (ib < 0))
+    return false;
+  return std::llabs(ia - ib) <= 4;
+}
+#define EXPECT_DOUBLE_EQ(a, b) EXPECT_TRUE(almostEqual((a), (b)))
+
+static void testPfKdtree()
+{
+  badger_amcl::PFKDTree pf_kdtree;
+  EXPECT_EQ(pf_kdtree.getLeafCount(), 0);
+  Eigen::Vector3d pose(1, 1, 1);
+  double value = 0.0;
+  pf_kdtree.insertPose(pose, value);
+  EXPECT_EQ(pf_kdtree.getLeafCount(), 1);
+  pf_kdtree.clearKDTree();
+  EXPECT_EQ(pf_kdtree.getLeafCount(), 0);
+  pf_kdtree.insertPose(pose, value);
+  EXPECT_EQ(pf_kdtree.getCluster(pose), -1);
+  pf_kdtree.cluster();
+  EXPECT_EQ(pf_kdtree.getCluster(pose), 0);
+  Eigen::Vector3d pose2(0, 1, 1);
+  Eigen::Vector3d pose3(3, 0, 0);
+  pf_kdtree.insertPose(pose2, value);
+  pf_kdtree.insertPose(pose3, value);
+  pf_kdtree.cluster();
+  EXPECT_EQ(pf_kdtree.getCluster(pose), 0);
+  EXPECT_EQ(pf_kdtree.getCluster(pose2), 1);
+  EXPECT_EQ(pf_kdtree.getCluster(pose3), 2);
+  EXPECT_EQ(pf_kdtree.getLeafCount(), 2);
+  Eigen::Vector3d pose4(0.5, 1, 1);
+  pf_kdtree.insertPose(pose4, value);
+  pf_kdtree.cluster();
+  EXPECT_EQ(pf_kdtree.getCluster(pose), 0);
+  EXPECT_EQ(pf_kdtree.getCluster(pose2), 0);
+  EXPECT_EQ(pf_kdtree.getCluster(pose3), 1);
+  EXPECT_EQ(pf_kdtree.getCluster(pose4), 0);
+  EXPECT_EQ(pf_kdtree.getLeafCount(), 2);
+}
+
+static void testOctoMapConversions()
+{
+  badger_amcl::OctoMap octomap(0.05, false);
+  std::vector<int> rtn_vec_map(2);
+  std::vector<double> rtn_vec_world(2);
+  std::vector<int> map_coords_2d = {1, 2};
+  std::vector<double> world_coords_2d = {.05, .1};
+  octomap.convertMapToWorld(map_coords_2d, &rtn_vec_world);
+  octomap.convertWorldToMap(world_coords_2d, &rtn_vec_map);
+  for (size_t i = 0; i < world_coords_2d.size(); i++)
+    EXPECT_DOUBLE_EQ(world_coords_2d[i], rtn_vec_world[i]);
+  EXPECT_EQ(map_coords_2d, rtn_vec_map);
+  std::vector<int> map_coords_3d = {3, 5, -1};
+  std::vector<double> world_coords_3d{.15, .25, -.05};
+  rtn_vec_world.resize(3);
+  rtn_vec_map.resize(3);
+  octomap.convertMapToWorld(map_coords_3d, &rtn_vec_world);
+  octomap.convertWorldToMap(world_coords_3d, &rtn_vec_map);
+  for (size_t i = 0; i < world_coords_3d.size(); i++)
+    EXPECT_DOUBLE_EQ(world_coords_3d[i], rtn_vec_world[i]);
+  EXPECT_EQ(map_coords_3d, rtn_vec_map);
+}
+
+static void testOccupancyMapConversions()
+{
+  badger_amcl::OccupancyMap occupancy_map(0.05);
+  std::vector<int> rtn_vec_map(2);
+  std::vector<double> rtn_vec_world(2);
+  std::vector<int> map_coords = {1, 2};
+  std::vector<double> world_coords = {.05, .1};
+  occupancy_map.convertMapToWorld(map_coords, &rtn_vec_world);
+  occupancy_map.convertWorldToMap(world_coords, &rtn_vec_map);
+  for (size_t i = 0; i < world_coords.size(); i++)
+    EXPECT_DOUBLE_EQ(world_coords[i], rtn_vec_world[i]);
+  EXPECT_EQ(map_coords, rtn_vec_map);
+}
+
+static void testOccupancyMapDistances()
+{
+  double resolution = 0.05;
+  badger_amcl::OccupancyMap occupancy_map(resolution);
+  std::vector<int> size_vec = {100, 150};
+  occupancy_map.setSize(size_vec);
+  EXPECT_EQ(occupancy_map.getSize(), size_vec);
+  double x_origin = size_vec[0] / 2 * resolution, y_origin = size_vec[1] / 2 * resolution;
+  occupancy_map.setOrigin(pcl::PointXYZ(x_origin, y_origin, 0.0));
+  for (int x = 0; x < size_vec[0]; x++)
+    for (int y = 0; y < size_vec[1]; y++)
+    {
+      unsigned int index = occupancy_map.computeCellIndex(x, y);
+      badger_amcl::MapCellState state;
+      if (x == 1 and y > 2 and y < 12)
+        state = badger_amcl::MapCellState::CELL_UNKNOWN;
+      else if (x > 4 and x < 14 and (y == 10 or y == 15))
+        state = badger_amcl::MapCellState::CELL_OCCUPIED;
+      else
+        state = badger_amcl::MapCellState::CELL_FREE;
+      occupancy_map.setCellState(index, state);
+      EXPECT_EQ(occupancy_map.getCellState(x, y), state);
+    }
+  EXPECT_TRUE(occupancy_map.isValid({0, 0}));
+  EXPECT_TRUE(not occupancy_map.isValid({-1, 5}));
+  EXPECT_TRUE(occupancy_map.isValid({99, 149}));
+  EXPECT_TRUE(not occupancy_map.isValid({100, 150}));
+  EXPECT_TRUE(not occupancy_map.isValid({149, 99}));
+  occupancy_map.updateDistancesLUT(0.3);
+  EXPECT_EQ(occupancy_map.getCellState(0, 0), badger_amcl::MapCellState::CELL_FREE);
+  EXPECT_EQ(occupancy_map.getCellState(1, 3), badger_amcl::MapCellState::CELL_UNKNOWN);
+  EXPECT_EQ(occupancy_map.getCellState(5, 10), badger_amcl::MapCellState::CELL_OCCUPIED);
+  double range = occupancy_map.calcRange(0, 0, 0, 0);
+  EXPECT_DOUBLE_EQ(range, 0.0);
+  range = occupancy_map.calcRange(0.05, 0, 1.5708, 0.5);
+  EXPECT_DOUBLE_EQ(range, 0.15);
+  // the cache itself: occupied cells are 0, cells beyond the radius hold max_distance (occupancy_map.cpp:147-153)
+  EXPECT_EQ(occupancy_map.getDistanceToObject(5, 10), 0.0f);
+  EXPECT_EQ(occupancy_map.getDistanceToObject(50, 100), 0.3f);
+  EXPECT_EQ(occupancy_map.getDistanceToObject(-3, 0), 0.3f);
+  EXPECT_TRUE(occupancy_map.isDistancesLUTCreated());
+}
+
+static void testDrand48Contract()
+{
+  // POSIX drand48 KAT; PDFGaussian::draw consumes it exactly like pdf_gaussian.cpp:77-97
+  srand48(12345);
+  EXPECT_EQ(drand48(), 0.22532851279629895);
+  EXPECT_EQ(drand48(), 0.919183068533556);
+  srand48(7);
+  const double a = badger_amcl::PDFGaussian::draw(2.0);
+  srand48(7);
+  const double b = badger_amcl::PDFGaussian::draw(2.0);
+  EXPECT_EQ(a, b);
+  EXPECT_TRUE(std::isfinite(a));
+}
+
+// ------------------------------------------------------------------------------------------ flow mode
+struct Reader
+{
+  std::vector<unsigned char> buf;
+  size_t pos = 0;
+  template <typename T>
+  void get(T* out, size_t n)
+  {
+    std::memcpy(out, &buf[pos], sizeof(T) * n);
+    pos += sizeof(T) * n;
+  }
+};
+
+static int flow(const char* in_path, const char* out_path)
+{
+  Reader rd;
+  {
+    FILE* f = std::fopen(in_path, "rb");
+    if (!f)
+      return 2;
+    std::fseek(f, 0, SEEK_END);
+    rd.buf.resize((size_t)std::ftell(f));
+    std::fseek(f, 0, SEEK_SET);
+    if (std::fread(rd.buf.data(), 1, rd.buf.size(), f) != rd.buf.size())
+      return 2;
+    std::fclose(f);
+  }
+  int hdr[9];
+  double par[3];
+  rd.get(hdr, 9);
+  rd.get(par, 3);
+  const int size_x = hdr[1], size_y = hdr[2], n = hdr[3], n_beams = hdr[4], min_samples = hdr[5], model_type = hdr[6],
+            systematic = hdr[7], seed = hdr[8];
+  const double resolution = par[0], max_dist = par[1], range_max = par[2];
+  std::vector<int8_t> cells((size_t)size_x * size_y);
+  rd.get(cells.data(), cells.size());
+  auto data = std::make_shared<badger_amcl::PlanarData>();
+  data->range_count_ = n_beams;
+  data->range_max_ = range_max;
+  data->ranges_.resize(n_beams);
+  data->angles_.resize(n_beams);
+  rd.get(data->ranges_.data(), n_beams);
+  rd.get(data->angles_.data(), n_beams);
+  std::vector<double> poses((size_t)3 * n);
+  rd.get(poses.data(), poses.size());
+
+  // Node2D::convertMap + initFromNewMap (node_2d.cpp:223-295): map, scanner model, particle filter
+  auto map = std::make_shared<badger_amcl::OccupancyMap>(resolution);
+  map->setSize({size_x, size_y});
+  map->setOrigin(pcl::PointXYZ(0.0, 0.0, 0.0));
+  for (int j = 0; j < size_y; j++)
+    for (int i = 0; i < size_x; i++)
+      map->setCellState(map->computeCellIndex(i, j), (badger_amcl::MapCellState)cells[(size_t)j * size_x + i]);
+  badger_amcl::PlanarScanner scanner;
+  scanner.init(n_beams, map);
+  if (model_type == badger_amcl::PLANAR_MODEL_LIKELIHOOD_FIELD_GOMPERTZ)
+    scanner.setModelLikelihoodFieldGompertz(0.95, 0.05, 0.2, max_dist, 1.0, 2.0, 6.0, -0.2, 1.3, 0.05);
+  else if (model_type == badger_amcl::PLANAR_MODEL_BEAM)
+  {
+    map->updateDistancesLUT(max_dist);  // the beam model reads the cache through recalcWeight
+    scanner.setModelBeam(0.95, 0.1, 0.05, 0.05, 0.2, 0.1);
+  }
+  else
+    scanner.setModelLikelihoodField(0.95, 0.05, 0.2, max_dist);
+  scanner.setPlanarScannerPose(Eigen::Vector3d(0.1, 0.0, 0.0));
+  size_t next_pose = 0;
+  auto pose_fn = [&]() {
+    const size_t k = (next_pose++) % (size_t)n;
+    return Eigen::Vector3d(poses[3 * k], poses[3 * k + 1], poses[3 * k + 2]);
+  };
+  auto random_pose_fn = [&]() { return Eigen::Vector3d(drand48() * 10.0 - 5.0, drand48() * 10.0 - 5.0, drand48() * 6.28 - 3.14); };
+  auto pf = std::make_shared<badger_amcl::ParticleFilter>(min_samples, n, 0.001, 0.1, 95.0, random_pose_fn);
+  pf->setResampleModel(systematic ? badger_amcl::PF_RESAMPLE_SYSTEMATIC : badger_amcl::PF_RESAMPLE_MULTINOMIAL);
+  pf->setPopulationSizeParameters(0.01, 0.99);
+  pf->initWithPoseFn(pose_fn);
+  srand48(seed);
+
+  FILE* out = std::fopen(out_path, "wb");
+  if (!out)
+    return 2;
+  auto put = [&](const double* p, size_t k) { std::fwrite(p, sizeof(double), k, out); };
+  {
+    auto set = pf->peekCurrentSet();
+    const double head[3] = {(double)set->sample_count, (double)set->kdtree->getLeafCount(), (double)set->cluster_count};
+    put(head, 3);
+  }
+  for (int round = 0; round < 2; round++)
+  {
+    for (int u = 0; u < 2; u++)  // resample_interval = 2 (node_2d.cpp:69)
+    {
+      EXPECT_TRUE(scanner.updateSensor(pf, data));
+      if (round == 0 && u == 0)
+      {
+        auto set = pf->peekCurrentSet();
+        std::vector<double> w((size_t)set->sample_count);
+        for (int i = 0; i < set->sample_count; i++)
+          w[(size_t)i] = set->samples[(size_t)i].weight;
+        put(w.data(), w.size());
+      }
+    }
+    pf->updateResample();
+    auto set = pf->peekCurrentSet();
+    const double st[12] = {(double)set->sample_count, (double)set->kdtree->getLeafCount(), (double)set->cluster_count,
+                           (double)set->converged,    set->mean[0],  set->mean[1],  set->mean[2],  set->cov(0, 0),
+                           set->cov(0, 1),            set->cov(1, 0), set->cov(1, 1), set->cov(2, 2)};
+    put(st, 12);
+    put(reinterpret_cast<const double*>(set->samples.data()), (size_t)4 * set->sample_count);
+    // max-weight cluster read-out as Node2D::getMaxWeightPose does (node_2d.cpp:588-617)
+    double best_w = -1.0;
+    Eigen::Vector3d best(0, 0, 0);
+    for (int c = 0; c < set->cluster_count; c++)
+    {
+      double w;
+      Eigen::Vector3d mean;
+      EXPECT_TRUE(pf->getClusterStats(c, &w, &mean));
+      if (w > best_w)
+      {
+        best_w = w;
+        best = mean;
+      }
+    }
+    const double bp[4] = {best_w, best[0], best[1], best[2]};
+    put(bp, 4);
+    // a motion-model style edit through the mutable set (odom.cpp:107-121), so the next round re-uploads
+    auto mset = pf->getCurrentSet();
+    for (int i = 0; i < mset->sample_count; i++)
+      mset->samples[(size_t)i].pose[0] += 0.01;
+  }
+  std::fclose(out);
+  return g_failed ? 1 : 0;
+}
+
+int main(int argc, char** argv)
+{
+  const std::string mode = argc > 1 ? argv[1] : "kats";
+  try
+  {
+    if (mode == "flow" && argc == 4)
+      return flow(argv[2], argv[3]);
+    testPfKdtree();
+    testOctoMapConversions();
+    testOccupancyMapConversions();
+    testOccupancyMapDistances();
+    testDrand48Contract();
+  }
+  catch (const std::exception& e)
+  {
+    std::printf("EXCEPTION: %s\n", e.what());
+    return 3;
+  }
+  std::printf("%s: %d failed\n", mode.c_str(), g_failed);
+  return g_failed ? 1 : 0;
+}

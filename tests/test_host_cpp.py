@@ -1,0 +1,98 @@
+"""The C++ host mirror of the reference's class API (badger_amcl_b200/host): the reference's own unit tests
+(test/test_badger_amcl.cpp:51-171) and a scan -> updateSensor -> updateResample flow, driven through
+OccupancyMap / PlanarScanner / ParticleFilter exactly as Node2D drives them, compared with the oracle."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+from badger_amcl_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+RES = 0.05
+
+
+@pytest.fixture(scope="module")
+def exe():
+    from badger_amcl_b200 import build
+    build.build()
+    build.build_host()
+    return build.HOST_TEST
+
+
+def test_host_library_builds_and_fails_loudly_without_a_gpu(exe):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    p = subprocess.run([exe, "kats"], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 3
+    assert "no CPU fallback" in p.stdout
+
+
+@pytest.mark.gpu
+def test_reference_unit_tests_pass_on_the_host_mirror(exe):
+    p = subprocess.run([exe, "kats"], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert "0 failed" in p.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cloud", ["global", "tracking"])
+def test_flow_through_the_class_api_matches_oracle(exe, oracle_built, tmp_path, cloud):
+    O = oracle_built
+    n, n_beams, seed = 5000, 60, 4242
+    cells = synth.make_grid(600, 500, seed=7, wall_every=100)
+    truth = synth.pick_truth_pose(cells, RES, seed=5)
+    ranges, angles = synth.make_scan(cells, RES, truth, n_beams=n_beams)
+    poses = (synth.uniform_free_poses(cells, RES, n, seed=1) if cloud == "global"
+             else synth.gaussian_poses(truth, n, seed=2))
+    fin, fout = str(tmp_path / "in.bin"), str(tmp_path / "out.bin")
+    with open(fin, "wb") as f:
+        f.write(struct.pack("<9i", 0x414D434C, cells.shape[1], cells.shape[0], n, n_beams, n // 10, 1, 1, seed))
+        f.write(struct.pack("<3d", RES, 2.0, 30.0))
+        f.write(np.ascontiguousarray(cells, np.int8).tobytes())
+        f.write(np.ascontiguousarray(ranges, np.float64).tobytes())
+        f.write(np.ascontiguousarray(angles, np.float64).tobytes())
+        f.write(np.ascontiguousarray(poses, np.float64).tobytes())
+    env = dict(os.environ, BAMCL_EXACT_TERMS="1")
+    p = subprocess.run([exe, "flow", fin, fout], capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0, p.stdout + p.stderr
+    got = np.fromfile(fout, np.float64)
+
+    pm = O.PortMap2D(cells, RES)
+    pm.set_distances(pm.exact_edt(2.0), 2.0)
+    model = O.planar_model(model_type=1, max_beams=n_beams, scanner_pose=(0.1, 0.0, 0.0))
+    port = O.PortPF(n // 10, n)
+    port.init_with_poses(poses)
+    port.srand48(seed)
+    pos = 0
+    assert tuple(got[:3]) == (n, port.leaf_count(), port.cluster_count())
+    pos = 3
+    for rnd in range(2):
+        for u in range(2):
+            port.update_sensor(pm, model, ranges, angles, 30.0)
+            if rnd == 0 and u == 0:
+                w = got[pos:pos + n]
+                pos += n
+                assert np.allclose(w, port.samples()[:, 3], rtol=1e-9, atol=0.0)
+        port.update_resample()
+        m = port.sample_count()
+        st = got[pos:pos + 12]
+        pos += 12
+        assert (int(st[0]), int(st[1]), int(st[2]), bool(st[3])) == (m, port.leaf_count(), port.cluster_count(),
+                                                                     port.is_converged())
+        assert np.allclose(st[4:12], port.set_stats(), rtol=1e-6, atol=1e-9)
+        s = got[pos:pos + 4 * m].reshape(m, 4)
+        pos += 4 * m
+        assert np.array_equal(s, port.samples())  # same source indices => identical poses, weights 1/m
+        best = got[pos:pos + 4]
+        pos += 4
+        cs = port.cluster_stats()
+        k = int(np.argmax(cs[:, 1]))
+        assert np.allclose(best, [cs[k, 1], cs[k, 2], cs[k, 3], cs[k, 4]], rtol=1e-6, atol=1e-9)
+        moved = port.samples()
+        moved[:, 0] += 0.01
+        port.set_samples(moved)
+    assert pos == len(got)

@@ -130,6 +130,7 @@ SIGNATURES = {
     "bamcl_pf_update_planar": (_I, [_P, _P, _P, _P, _P, _I, _D, _I, _P]),
     "bamcl_pf_stage_scan": (_I, [_P, _P, _P, _P, _P, _I, _D]),
     "bamcl_pf_update_planar_staged": (_I, [_P, _P, _I, _P]),
+    "bamcl_pf_score_planar_staged": (_I, [_P, _P, _I, _P]),
     "bamcl_pf_cdf": (_I, [_P, _P, _L]),
     "bamcl_pf_resample": (_I, [_P, _P, _P]),
     "bamcl_pf_init_stats": (_I, [_P, _P]),
@@ -138,6 +139,14 @@ SIGNATURES = {
     "bamcl_pf_cluster_stats": (_I, [_P, _P, _I]),
     "bamcl_resample_limit": (_I, [_I, _I, _I, _D, _D]),
     "bamcl_systematic_targets": (_I, [_D, _D, _L, _P]),
+    "bamcl_pf_set_window": (_I, [_P, _L, _L]),
+    "bamcl_pf_shard_cdf": (_I, [_P, _D, _P]),
+    "bamcl_systematic_plan": (_I, [_D, _D, _L, _P, _I, _P, _I, _P]),
+    "bamcl_pf_shard_select": (_I, [_P, _D, _D, _L, _L, _L, _L, _P, _P]),
+    "bamcl_pf_shard_install": (_I, [_P, _P, _L, _P, _P]),
+    "bamcl_pf_leaf_count": (_I, [_P, _P]),
+    "bamcl_pf_upload_window_samples": (_I, [_P, _P, _L, _L]),
+    "bamcl_pf_download_window_samples": (_I, [_P, _P, _L, _L]),
 }
 
 

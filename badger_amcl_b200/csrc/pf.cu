@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(1024) k_sum_final(const double* __restrict__ p
 }
 
 // ---- ParticleFilter::updateSensor, particle_filter.cpp:237-266
-__global__ void k_normalise(double* __restrict__ w, int n, const double* __restrict__ total_p)
+__global__ void k_normalise(double* __restrict__ w, int n, const double* __restrict__ total_p, int n_set)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n)
@@ -99,7 +99,7 @@ __global__ void k_normalise(double* __restrict__ w, int n, const double* __restr
   if (total > 0.0)
     w[i] = w[i] / total;
   else
-    w[i] = 1.0 / n;
+    w[i] = 1.0 / n_set;  // the whole set's count (a sharded filter normalises only its window)
 }
 }  // namespace
 
@@ -108,11 +108,12 @@ namespace bamcl
 int pf_reduce_total(bamcl_pf* pf, double* d_total)
 {
   SampleSet& set = pf->sets[pf->current];
-  const int n = set.sample_count;
+  const int n = pf_win_cnt(pf);
   const int blocks = (n + RED_BLOCK * RED_ITEMS - 1) / (RED_BLOCK * RED_ITEMS);
   BAMCL_TRY(pf->partials.reserve(sizeof(double) * (size_t)(blocks + 1)));
   if (blocks > 0)
-    BAMCL_LAUNCH(pf->ctx, k_sum_partials, blocks, RED_BLOCK, 0, set.w.as<double>(), n, pf->partials.as<double>());
+    BAMCL_LAUNCH(pf->ctx, k_sum_partials, blocks, RED_BLOCK, 0, set.w.as<double>() + pf_win_off(pf), n,
+                 pf->partials.as<double>());
   BAMCL_LAUNCH(pf->ctx, k_sum_final, 1, 1024, 0, pf->partials.as<double>(), blocks, d_total);
   return BAMCL_OK;
 }
@@ -123,9 +124,9 @@ namespace bamcl
 int pf_normalise_by_device_total(bamcl_pf* pf)
 {
   SampleSet& s = pf->sets[pf->current];
-  if (s.sample_count > 0)
-    BAMCL_LAUNCH(pf->ctx, k_normalise, (s.sample_count + 255) / 256, 256, 0, s.w.as<double>(), s.sample_count,
-                 pf->scalars.as<double>());
+  if (pf_win_cnt(pf) > 0)
+    BAMCL_LAUNCH(pf->ctx, k_normalise, (pf_win_cnt(pf) + 255) / 256, 256, 0, s.w.as<double>() + pf_win_off(pf),
+                 pf_win_cnt(pf), pf->scalars.as<double>(), s.sample_count);
   return BAMCL_OK;
 }
 int pf_read_scalar(bamcl_pf* pf, int slot, double* out);
@@ -230,6 +231,7 @@ int bamcl_pf_upload_samples(bamcl_pf* pf, const double* aos, long n)
     return set_error(BAMCL_E_ARG, "bamcl_pf_upload_samples: need 0 <= n <= max_samples");
   SampleSet& s = pf->sets[pf->current];
   s.sample_count = (int)n;
+  pf->win_cnt = -1;  // a new set: back to the whole-set window
   if (n == 0)
     return BAMCL_OK;
   bamcl_ctx* ctx = pf->ctx;
@@ -237,6 +239,38 @@ int bamcl_pf_upload_samples(bamcl_pf* pf, const double* aos, long n)
   BAMCL_CUDA_OK(cudaMemcpyAsync(pf->d_stage.p, aos, sizeof(double) * 4 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
   BAMCL_LAUNCH(ctx, k_aos_to_soa, (unsigned)((n + 255) / 256), 256, 0, pf->d_stage.as<double4>(), s.x.as<double>(),
                s.y.as<double>(), s.th.as<double>(), s.w.as<double>(), (int)n);
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_pf_upload_window_samples(bamcl_pf* pf, const double* aos, long offset, long n)
+{
+  if (!pf || !aos || offset < 0 || n < 0 || offset + n > pf->sets[pf->current].sample_count)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_upload_window_samples: [offset, offset + n) must lie inside the current set");
+  if (n == 0)
+    return BAMCL_OK;
+  SampleSet& s = pf->sets[pf->current];
+  bamcl_ctx* ctx = pf->ctx;
+  BAMCL_TRY(pf->d_stage.reserve(sizeof(double) * 4 * (size_t)n));
+  BAMCL_CUDA_OK(cudaMemcpyAsync(pf->d_stage.p, aos, sizeof(double) * 4 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+  BAMCL_LAUNCH(ctx, k_aos_to_soa, (unsigned)((n + 255) / 256), 256, 0, pf->d_stage.as<double4>(), s.x.as<double>() + offset,
+               s.y.as<double>() + offset, s.th.as<double>() + offset, s.w.as<double>() + offset, (int)n);
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_pf_download_window_samples(bamcl_pf* pf, double* aos, long offset, long n)
+{
+  if (!pf || !aos || offset < 0 || n < 0 || offset + n > pf->sets[pf->current].sample_count)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_download_window_samples: [offset, offset + n) must lie inside the current set");
+  if (n == 0)
+    return BAMCL_OK;
+  SampleSet& s = pf->sets[pf->current];
+  bamcl_ctx* ctx = pf->ctx;
+  BAMCL_TRY(pf->d_stage.reserve(sizeof(double) * 4 * (size_t)n));
+  BAMCL_LAUNCH(ctx, k_soa_to_aos, (unsigned)((n + 255) / 256), 256, 0, pf->d_stage.as<double4>(), s.x.as<double>() + offset,
+               s.y.as<double>() + offset, s.th.as<double>() + offset, s.w.as<double>() + offset, (int)n);
+  BAMCL_CUDA_OK(cudaMemcpyAsync(aos, pf->d_stage.p, sizeof(double) * 4 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
   return BAMCL_OK;
 }
@@ -332,13 +366,13 @@ int bamcl_pf_normalise(bamcl_pf* pf, double total)
   if (!pf)
     return set_error(BAMCL_E_ARG, "null pf");
   SampleSet& s = pf->sets[pf->current];
-  if (s.sample_count == 0)
+  if (s.sample_count == 0 || pf_win_cnt(pf) == 0)
     return BAMCL_OK;
   pf->h_scalars.as<double>()[1] = total;
   BAMCL_CUDA_OK(cudaMemcpyAsync(pf->scalars.as<double>() + 1, pf->h_scalars.as<double>() + 1, sizeof(double),
                                 cudaMemcpyHostToDevice, pf->ctx->stream));
-  BAMCL_LAUNCH(pf->ctx, k_normalise, (s.sample_count + 255) / 256, 256, 0, s.w.as<double>(), s.sample_count,
-               pf->scalars.as<double>() + 1);
+  BAMCL_LAUNCH(pf->ctx, k_normalise, (pf_win_cnt(pf) + 255) / 256, 256, 0, s.w.as<double>() + pf_win_off(pf),
+               pf_win_cnt(pf), pf->scalars.as<double>() + 1, s.sample_count);
   BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
   return BAMCL_OK;
 }
@@ -357,12 +391,27 @@ int bamcl_pf_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged,
   }
   BAMCL_TRY(launch_score(pf, map));
   BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
-  if (s.sample_count > 0)
-    BAMCL_LAUNCH(pf->ctx, k_normalise, (s.sample_count + 255) / 256, 256, 0, s.w.as<double>(), s.sample_count,
-                 pf->scalars.as<double>());
+  if (pf_win_cnt(pf) > 0)
+    BAMCL_LAUNCH(pf->ctx, k_normalise, (pf_win_cnt(pf) + 255) / 256, 256, 0, s.w.as<double>() + pf_win_off(pf),
+                 pf_win_cnt(pf), pf->scalars.as<double>(), s.sample_count);
   if (total_out_or_null)
     return read_scalar(pf, 0, total_out_or_null);
   return BAMCL_OK;
+}
+
+int bamcl_pf_score_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out)
+{
+  (void)converged;
+  if (!pf || !map || !total_out)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_score_planar_staged: bad arguments");
+  if (pf->scan.valid && pf->scan.model.max_beams < 2)
+  {
+    *total_out = 0.0;
+    return BAMCL_OK;
+  }
+  BAMCL_TRY(launch_score(pf, map));
+  BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
+  return read_scalar(pf, 0, total_out);
 }
 
 int bamcl_pf_update_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,

@@ -81,12 +81,19 @@ struct bamcl_pf
   bool score_timed = false;
   bool exact_terms = false;  // bamcl_pf_set_exact_terms
   int tree_levels = 0;      // levels the last tree build needed (diagnostics)
+  // Sharded filter (multi-GPU): every rank holds the whole set; scoring, totals, normalisation and the
+  // CDF work on this rank's window [win_off, win_off + win_cnt) of the current set. win_cnt < 0 = whole set.
+  long win_off = 0;
+  int win_cnt = -1;
 };
 
 namespace bamcl
 {
 // device int flags of the resampler: bit0 target beyond the CDF, bit1 unsupported value
 inline int* pf_flags(bamcl_pf* pf) { return reinterpret_cast<int*>(pf->scalars.as<double>() + 32); }
+// this rank's window of the current set
+inline long pf_win_off(const bamcl_pf* pf) { return pf->win_cnt < 0 ? 0 : pf->win_off; }
+inline int pf_win_cnt(const bamcl_pf* pf) { return pf->win_cnt < 0 ? pf->sets[pf->current].sample_count : pf->win_cnt; }
 }
 
 namespace bamcl
@@ -94,4 +101,5 @@ namespace bamcl
 int pf_reduce_total(bamcl_pf* pf, double* d_total);  // deterministic sum of the current set's weights -> device scalar
 int pf_read_scalar(bamcl_pf* pf, int slot, double* out);  // device scalar slot -> host (synchronises)
 int pf_normalise_by_device_total(bamcl_pf* pf);           // w /= scalars[0] (or 1/n), particle_filter.cpp:237-266
+int pf_build_cdf(bamcl_pf* pf, double c0 = 0.0);           // exact sequential CDF of the window, starting at c0
 }

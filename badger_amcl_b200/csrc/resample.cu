@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tile_sums(const double* __res
 
 // one block: approximate start value of every tile and the fast/slow decision
 __global__ void __launch_bounds__(1024) k_cdf_classify(const double* __restrict__ sums, int n_tiles, int n,
-                                                       double* __restrict__ starts, int* __restrict__ tile_e)
+                                                       double* __restrict__ starts, int* __restrict__ tile_e, double c0)
 {
   __shared__ double s_part[1024];
   __shared__ double s_total;
@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(1024) k_cdf_classify(const double* __restrict_
   __syncthreads();
   if (threadIdx.x == 0)
   {
-    double run = 0.0;
+    double run = c0;  // value of the CDF before the first element (0 unless this is a later shard of a sharded set)
     for (int i = 0; i < 1024; i++)
     {
       const double t = s_part[i];
@@ -233,6 +233,7 @@ struct CdfArgs
   double* incl;
   int* counter;
   int* flags;  // bit1: unsupported value (subnormal running sum / inconsistent binade)
+  double c0;   // c[0]: 0, or the exact end value of the previous shard (sharded filter)
 };
 
 // exact inclusive value of tile t-1, by warp 0
@@ -256,7 +257,7 @@ __device__ double cdf_lookback(const CdfArgs& a, int t)
     __threadfence();
     Fn F;
     F.d0 = F.d1 = 0;
-    double base = 0.0;
+    double base = a.c0;  // "tile -1" ends at c[0]
     if (jj >= 0)
     {
       if (st == ST_AGG)
@@ -310,7 +311,7 @@ __global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tiles(const CdfArgs a)
   for (int k = 0; k < CDF_ITEMS; k++)
     wv[k] = (idx0 + k < a.n) ? a.w[idx0 + k] : 0.0;
   if (t == 0 && threadIdx.x == 0)
-    a.c[0] = 0.0;
+    a.c[0] = a.c0;
   const int e_fast = a.tile_e[t];
   const bool last_thread = threadIdx.x == CDF_BLOCK - 1;
 
@@ -368,7 +369,7 @@ __global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tiles(const CdfArgs a)
   // ---- slow tile: needs the exact start value first
   if (threadIdx.x < 32)
   {
-    const double v = (t == 0) ? 0.0 : cdf_lookback(a, t);
+    const double v = (t == 0) ? a.c0 : cdf_lookback(a, t);
     if (threadIdx.x == 0)
       s_val = v;
   }
@@ -725,16 +726,18 @@ int build_target_segments(double start, double delta, long long n, std::vector<T
 
 namespace bamcl
 {
-// c[0..n] of the current set -> pf->cdf (device), exact sequential rounding
-int pf_build_cdf(bamcl_pf* pf)
+// c[0..n] of the current set's window -> pf->cdf (device), exact sequential rounding, c[0] = c0
+int pf_build_cdf(bamcl_pf* pf, double c0)
 {
   SampleSet& set = pf->sets[pf->current];
-  const int n = set.sample_count;
+  const int n = pf_win_cnt(pf);
+  const double* w = set.w.as<double>() + pf_win_off(pf);
   bamcl_ctx* ctx = pf->ctx;
   BAMCL_TRY(pf->cdf.reserve(sizeof(double) * ((size_t)n + 1)));
   if (n == 0)
   {
-    BAMCL_CUDA_OK(cudaMemsetAsync(pf->cdf.p, 0, sizeof(double), ctx->stream));
+    BAMCL_CUDA_OK(cudaMemcpyAsync(pf->cdf.p, &c0, sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     return BAMCL_OK;
   }
   const int tiles = (n + CDF_TILE - 1) / CDF_TILE;
@@ -752,10 +755,11 @@ int pf_build_cdf(bamcl_pf* pf)
   int* flags = pf_flags(pf);
   BAMCL_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int) * ((size_t)tiles + 2), ctx->stream));
   BAMCL_CUDA_OK(cudaMemsetAsync(flags, 0, sizeof(int), ctx->stream));
-  BAMCL_LAUNCH(ctx, k_cdf_tile_sums, tiles, CDF_BLOCK, 0, set.w.as<double>(), n, sums);
-  BAMCL_LAUNCH(ctx, k_cdf_classify, 1, 1024, 0, sums, tiles, n, starts, tile_e);
+  BAMCL_LAUNCH(ctx, k_cdf_tile_sums, tiles, CDF_BLOCK, 0, w, n, sums);
+  BAMCL_LAUNCH(ctx, k_cdf_classify, 1, 1024, 0, sums, tiles, n, starts, tile_e, c0);
   CdfArgs a;
-  a.w = set.w.as<double>();
+  a.w = w;
+  a.c0 = c0;
   a.n = n;
   a.c = pf->cdf.as<double>();
   a.tile_e = tile_e;
@@ -845,6 +849,8 @@ int bamcl_pf_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resa
   if (!(prm->w_diff >= 0.0))  // NaN when no sensor update preceded the resample
     return set_error(BAMCL_E_STATE, "bamcl_pf_resample: w_diff is NaN/negative (updateSensor must succeed first)");
   memset(res, 0, sizeof(*res));
+  if (pf->win_cnt >= 0)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_resample: a shard window is set; use the bamcl_pf_shard_* phases");
   if (!prm->resample_systematic)
     return resample_multinomial(pf, prm, res);
 
@@ -947,6 +953,270 @@ int bamcl_pf_resample_sources(bamcl_pf* pf, int* src, long n)
     return set_error(BAMCL_E_ARG, "bamcl_pf_resample_sources: n must equal sample_count after a resample");
   BAMCL_CUDA_OK(cudaMemcpyAsync(src, pf->src.p, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, pf->ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+  return BAMCL_OK;
+}
+
+}  // extern "C"
+
+// =============================================================================================
+// Sharded filter: the phases of resampleSystematic split at the points where ranks exchange data.
+// Global order is rank-major, so every order-dependent reference semantic (sequential CDF, target sequence,
+// first-occurrence order of pose bins) is the single-set one. Rank r owns the window [off, off + cnt) of the
+// current set; c_local[0] = exact end value of rank r-1's CDF, so the concatenation of the local CDFs IS the
+// reference's c[0..P].
+// =============================================================================================
+namespace
+{
+struct ShardSelArgs
+{
+  const double* c;  // cnt + 1, global values
+  int P;            // window size
+  long off;         // window offset = global index of local particle 0
+  const double *ax, *ay, *ath;  // window base
+  double* out3;     // global AoS buffer, row = output slot, 3 doubles (x, y, theta)
+  int* src_out;     // optional: global source index per output slot
+  long k_begin, k_end, row0;  // outputs [k_begin, k_end) of the systematic sequence; row = row0 + k
+  const TargetSeg* segs;
+  int n_segs;
+  int* flags;
+};
+
+__global__ void __launch_bounds__(256) k_select_shard(const ShardSelArgs a)
+{
+  __shared__ TargetSeg s_segs[MAX_SEGS];
+  for (int i = threadIdx.x; i < a.n_segs; i += blockDim.x)
+    s_segs[i] = a.segs[i];
+  __syncthreads();
+  const long long k = a.k_begin + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= a.k_end)
+    return;
+  int lo = 0, hi = a.n_segs - 1;
+  while (lo < hi)
+  {
+    const int mid = (lo + hi + 1) >> 1;
+    if (s_segs[mid].k0 <= k)
+      lo = mid;
+    else
+      hi = mid - 1;
+  }
+  const TargetSeg sg = s_segs[lo];
+  const double target = scalbn((double)(sg.m0 + (k - sg.k0) * sg.d), sg.eu);
+  int L = 0, H = a.P;
+  while (L < H)
+  {
+    const int mid = (L + H) >> 1;
+    if (__ldg(&a.c[mid + 1]) <= target)
+      L = mid + 1;
+    else
+      H = mid;
+  }
+  int j = L;
+  if (j >= a.P)
+  {
+    // only the rank that owns the end of the CDF is given such targets (bamcl_systematic_plan): SURVEY Q10
+    atomicOr(a.flags, 1);
+    const double top = a.c[a.P];
+    int l2 = 0, h2 = a.P;
+    while (l2 < h2)
+    {
+      const int mid = (l2 + h2) >> 1;
+      if (a.c[mid + 1] < top)
+        l2 = mid + 1;
+      else
+        h2 = mid;
+    }
+    j = min(l2, a.P - 1);
+  }
+  const long long row = a.row0 + k;
+  a.out3[3 * row] = a.ax[j];
+  a.out3[3 * row + 1] = a.ay[j];
+  a.out3[3 * row + 2] = a.ath[j];
+  if (a.src_out)
+    a.src_out[row] = (int)(a.off + j);
+}
+
+__global__ void k_aos3_to_soa(const double* __restrict__ in3, double* __restrict__ x, double* __restrict__ y,
+                              double* __restrict__ th, double* __restrict__ w, double weight, int n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  x[i] = in3[3 * (size_t)i];
+  y[i] = in3[3 * (size_t)i + 1];
+  th[i] = in3[3 * (size_t)i + 2];
+  w[i] = weight;
+}
+}  // namespace
+
+extern "C" {
+
+int bamcl_pf_set_window(bamcl_pf* pf, long offset, long count)
+{
+  if (!pf)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_set_window: null pf");
+  const int n = pf->sets[pf->current].sample_count;
+  if (count < 0)
+  {
+    pf->win_off = 0;
+    pf->win_cnt = -1;
+    return BAMCL_OK;
+  }
+  if (offset < 0 || offset + count > n)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_set_window: [%ld, %ld) is outside the set of %d samples", offset, offset + count, n);
+  pf->win_off = offset;
+  pf->win_cnt = (int)count;
+  return BAMCL_OK;
+}
+
+int bamcl_pf_shard_cdf(bamcl_pf* pf, double c0, double* end_out)
+{
+  if (!pf || !end_out)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_cdf: bad arguments");
+  if (!(c0 >= 0.0))
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_cdf: c0 must be >= 0");
+  BAMCL_TRY(pf_build_cdf(pf, c0));
+  const int n = pf_win_cnt(pf);
+  int flags = 0;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(end_out, pf->cdf.as<double>() + n, sizeof(double), cudaMemcpyDeviceToHost, pf->ctx->stream));
+  if (n > 0)
+    BAMCL_CUDA_OK(cudaMemcpyAsync(&flags, pf_flags(pf), sizeof(int), cudaMemcpyDeviceToHost, pf->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+  if (flags & 2)
+    return set_error(BAMCL_E_UNSUPPORTED, "CDF: a running sum left the supported range (subnormal or non-finite weights)");
+  return BAMCL_OK;
+}
+
+int bamcl_systematic_plan(double start, double delta, long n, const double* bounds, int n_ranks, long* runs, int max_runs,
+                          int* n_runs)
+{
+  if (!bounds || !runs || !n_runs || n_ranks < 1 || n < 0 || max_runs < 1)
+    return set_error(BAMCL_E_ARG, "bamcl_systematic_plan: bad arguments");
+  for (int r = 0; r < n_ranks; r++)
+    if (!(bounds[r] <= bounds[r + 1]))
+      return set_error(BAMCL_E_ARG, "bamcl_systematic_plan: bounds must be non-decreasing");
+  std::vector<TargetSeg> segs;
+  if (n > 0 && build_target_segments(start, delta, n, segs) != 0)
+    return set_error(BAMCL_E_UNSUPPORTED, "target sequence needs more than %d binade segments", MAX_SEGS);
+  int last_mass = -1;  // last rank that holds weight: owner of targets at/after the end of the CDF
+  for (int r = 0; r < n_ranks; r++)
+    if (bounds[r] < bounds[r + 1])
+      last_mass = r;
+  if (last_mass < 0 && n > 0)
+    return set_error(BAMCL_E_STATE, "bamcl_systematic_plan: the CDF is empty (all weights zero)");
+  int cnt = 0;
+  for (size_t s = 0; s < segs.size(); s++)
+  {
+    const long long k0 = segs[s].k0, k1 = (s + 1 < segs.size()) ? segs[s + 1].k0 : (long long)n;
+    auto value = [&](long long k) { return std::ldexp((double)(segs[s].m0 + (k - k0) * segs[s].d), segs[s].eu); };
+    long long prev_cut = k0;
+    for (int i = 1; i <= n_ranks + 1; i++)
+    {
+      // keys in [prev_cut, cut) have exactly i-1 of bounds[1..G] <= target
+      long long cut = k1;
+      if (i <= n_ranks)
+      {
+        long long lo = prev_cut, hi = k1;  // first k with value(k) >= bounds[i]
+        while (lo < hi)
+        {
+          const long long mid = lo + (hi - lo) / 2;
+          if (value(mid) >= bounds[i])
+            hi = mid;
+          else
+            lo = mid + 1;
+        }
+        cut = lo;
+      }
+      if (cut > prev_cut)
+      {
+        const int owner = (i - 1 < n_ranks) ? i - 1 : last_mass;
+        if (cnt > 0 && runs[3 * (cnt - 1) + 2] == owner && runs[3 * (cnt - 1) + 1] == prev_cut)
+          runs[3 * (cnt - 1) + 1] = cut;
+        else
+        {
+          if (cnt >= max_runs)
+            return set_error(BAMCL_E_ARG, "bamcl_systematic_plan: more than %d runs", max_runs);
+          runs[3 * cnt] = prev_cut;
+          runs[3 * cnt + 1] = cut;
+          runs[3 * cnt + 2] = owner;
+          cnt++;
+        }
+      }
+      prev_cut = cut;
+    }
+  }
+  *n_runs = cnt;
+  return BAMCL_OK;
+}
+
+int bamcl_pf_shard_select(bamcl_pf* pf, double start, double delta, long n_sys, long row0, long k_begin, long k_end,
+                          double* out_aos3_dev, int* src_out_dev_or_null)
+{
+  if (!pf || !out_aos3_dev || k_begin < 0 || k_end > n_sys || k_begin > k_end)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_select: bad arguments");
+  if (k_begin == k_end)
+    return BAMCL_OK;
+  const int P = pf_win_cnt(pf);
+  if (P <= 0)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_shard_select: this rank's window is empty but it was given outputs");
+  bamcl_ctx* ctx = pf->ctx;
+  SampleSet& set_a = pf->sets[pf->current];
+  std::vector<TargetSeg> segs;
+  if (build_target_segments(start, delta, n_sys, segs) != 0)
+    return set_error(BAMCL_E_UNSUPPORTED, "target sequence needs more than %d binade segments", MAX_SEGS);
+  BAMCL_TRY(pf->h_stage.reserve(sizeof(TargetSeg) * MAX_SEGS));
+  BAMCL_TRY(pf->seg_buf.reserve(sizeof(TargetSeg) * MAX_SEGS));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));  // the pinned segment buffer may still feed an earlier copy
+  memcpy(pf->h_stage.p, segs.data(), sizeof(TargetSeg) * segs.size());
+  BAMCL_CUDA_OK(cudaMemcpyAsync(pf->seg_buf.p, pf->h_stage.p, sizeof(TargetSeg) * segs.size(), cudaMemcpyHostToDevice,
+                                ctx->stream));
+  ShardSelArgs a;
+  a.c = pf->cdf.as<double>();
+  a.P = P;
+  a.off = pf_win_off(pf);
+  a.ax = set_a.x.as<double>() + a.off;
+  a.ay = set_a.y.as<double>() + a.off;
+  a.ath = set_a.th.as<double>() + a.off;
+  a.out3 = out_aos3_dev;
+  a.src_out = src_out_dev_or_null;
+  a.k_begin = k_begin;
+  a.k_end = k_end;
+  a.row0 = row0;
+  a.segs = pf->seg_buf.as<TargetSeg>();
+  a.n_segs = (int)segs.size();
+  a.flags = pf_flags(pf);
+  const long long cnt = k_end - k_begin;
+  BAMCL_LAUNCH(ctx, k_select_shard, (unsigned)((cnt + 255) / 256), 256, 0, a);
+  return BAMCL_OK;
+}
+
+int bamcl_pf_shard_install(bamcl_pf* pf, const double* aos3_dev, long n, const bamcl_resample_params* prm,
+                           bamcl_resample_result* res)
+{
+  if (!pf || !aos3_dev || !prm || !res || n <= 0 || n > pf->max_samples)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_install: bad arguments");
+  memset(res, 0, sizeof(*res));
+  bamcl_ctx* ctx = pf->ctx;
+  SampleSet& set_b = pf->sets[1 - pf->current];
+  BAMCL_LAUNCH(ctx, k_aos3_to_soa, (unsigned)((n + 255) / 256), 256, 0, aos3_dev, set_b.x.as<double>(), set_b.y.as<double>(),
+               set_b.th.as<double>(), set_b.w.as<double>(), 1.0 / (double)n, (int)n);
+  set_b.sample_count = (int)n;
+  pf->current = 1 - pf->current;
+  pf->win_off = 0;
+  pf->win_cnt = -1;
+  BAMCL_TRY(build_tree_and_stats(pf, pf->current, prm->dist_threshold, prm->convergence_threshold, res));
+  int flags = 0;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(&flags, pf_flags(pf), sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  res->sample_count = (int)n;
+  res->status_flags = flags & 1;
+  return BAMCL_OK;
+}
+
+int bamcl_pf_leaf_count(bamcl_pf* pf, int* leaf_count)
+{
+  if (!pf || !leaf_count)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_leaf_count: bad arguments");
+  *leaf_count = pf->sets[pf->current].leaf_count;
   return BAMCL_OK;
 }
 

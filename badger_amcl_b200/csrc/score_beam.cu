@@ -159,11 +159,11 @@ int launch_beam_model(bamcl_pf* pf, bamcl_map2d* map)
   BAMCL_CUDA_OK(cudaMemcpyAsync(sc.beams.p, hb, sizeof(double) * 4 * n_used, cudaMemcpyHostToDevice, ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
   BeamArgs a;
-  a.x = set.x.as<double>();
-  a.y = set.y.as<double>();
-  a.th = set.th.as<double>();
-  a.w = set.w.as<double>();
-  a.n = set.sample_count;
+  a.x = set.x.as<double>() + pf_win_off(pf);
+  a.y = set.y.as<double>() + pf_win_off(pf);
+  a.th = set.th.as<double>() + pf_win_off(pf);
+  a.w = set.w.as<double>() + pf_win_off(pf);
+  a.n = pf_win_cnt(pf);
   a.ranges = sc.ranges.as<double>();
   a.beam = sc.beams.as<double4>();
   a.n_used = n_used;

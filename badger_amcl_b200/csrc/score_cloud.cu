@@ -362,11 +362,11 @@ int launch_score_cloud(bamcl_pf* pf, bamcl_map3d* map)
     return BAMCL_OK;
   bamcl_ctx* ctx = pf->ctx;
   CloudArgs a;
-  a.x = set.x.as<double>();
-  a.y = set.y.as<double>();
-  a.th = set.th.as<double>();
-  a.w = set.w.as<double>();
-  a.n = set.sample_count;
+  a.x = set.x.as<double>() + pf_win_off(pf);
+  a.y = set.y.as<double>() + pf_win_off(pf);
+  a.th = set.th.as<double>() + pf_win_off(pf);
+  a.w = set.w.as<double>() + pf_win_off(pf);
+  a.n = pf_win_cnt(pf);
   a.px = sc.px.as<float>();
   a.py = sc.py.as<float>();
   a.pz = sc.pz.as<float>();

@@ -428,11 +428,11 @@ int launch_score(bamcl_pf* pf, bamcl_map2d* map)
     return launch_beam_model(pf, map);
   bamcl_ctx* ctx = pf->ctx;
   ScoreArgs a;
-  a.x = set.x.as<double>();
-  a.y = set.y.as<double>();
-  a.th = set.th.as<double>();
-  a.w = set.w.as<double>();
-  a.n = set.sample_count;
+  a.x = set.x.as<double>() + pf_win_off(pf);
+  a.y = set.y.as<double>() + pf_win_off(pf);
+  a.th = set.th.as<double>() + pf_win_off(pf);
+  a.w = set.w.as<double>() + pf_win_off(pf);
+  a.n = pf_win_cnt(pf);
   a.beams = sc.beams.as<double2>();
   a.n_beams = sc.n_beams;
   a.table = sc.table.as<double>();

@@ -1,0 +1,231 @@
+"""Sharded particle filter: ONE global sample set resampled exactly like the reference's single set
+(particle_filter.cpp:223-267, 269-354, 423-471), with the particles scored on G GPUs (one process per GPU).
+
+Global order is rank-major, so the order-dependent reference semantics are the single-set ones:
+
+  update    rank r scores its window [r*P/G, (r+1)*P/G); local totals are all-gathered and summed in rank order;
+            every rank normalises its window by the global total (particle_filter.cpp:237-266)
+  resample  the sequential CDF is chained over ranks (rank r starts at rank r-1's exact end value), the systematic
+            target sequence is planned on the host (bamcl_systematic_plan: which rank's window holds the source of
+            each output slot), each rank selects for its runs into a global (n x 3) buffer, the runs are broadcast,
+            and every rank installs the new set and builds the global pose-bin tree / clusters / statistics
+            (replicated: the KLD leaf count and the cluster numbering are properties of the global insertion order)
+
+`ShardedFilter` holds the host logic and talks to torch.distributed (NCCL on the GPUs, gloo in the CPU tests); the
+device phases live behind an *engine*: `CudaEngine` here (the C ABI); tests/ plug in a checker-based engine to
+exercise the host logic without a GPU. No engine here computes on the CPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import cabi
+
+
+def drand48_next(state):
+    return (0x5DEECE66D * state + 0xB) & ((1 << 48) - 1)
+
+
+def shard_bounds(n, world):
+    """contiguous rank-major partition of n samples: rank r owns [b[r], b[r+1])"""
+    return [(n * r) // world for r in range(world + 1)]
+
+
+def systematic_plan(start, delta, n, bounds):
+    """runs (k_begin, k_end, rank) of output slots by the rank whose CDF range holds the target (host arithmetic)"""
+    b = np.ascontiguousarray(bounds, np.float64)
+    g = len(b) - 1
+    max_runs = 4 * g + 2048
+    runs = np.zeros((max_runs, 3), np.int64)
+    n_runs = C.c_int()
+    cabi._check(cabi.lib().bamcl_systematic_plan(start, delta, n, cabi._p(b), g, cabi._p(runs), max_runs, C.byref(n_runs)))
+    return [tuple(int(v) for v in runs[i]) for i in range(n_runs.value)]
+
+
+class CudaEngine:
+    """device phases of the sharded filter through the C ABI (include/bamcl.h, "sharded filter")"""
+
+    def __init__(self, pf, map2d, device):
+        import torch
+        self.torch, self.pf, self.map, self.L = torch, pf, map2d, pf.L
+        self.device = torch.device("cuda", device)
+        self.buf = torch.empty((pf.max_samples, 3), dtype=torch.float64, device=self.device)
+        self.src = None
+
+    def want_sources(self):
+        self.src = self.torch.full((self.pf.max_samples,), -1, dtype=self.torch.int32, device=self.device)
+
+    def scalar_tensor(self, v=0.0):
+        return self.torch.tensor([v], dtype=self.torch.float64, device=self.device)
+
+    def sample_count(self):
+        return self.pf.sample_count()
+
+    def leaf_count(self):
+        k = C.c_int()
+        cabi._check(self.L.bamcl_pf_leaf_count(self.pf.h, C.byref(k)))
+        return k.value
+
+    def set_window(self, off, cnt):
+        cabi._check(self.L.bamcl_pf_set_window(self.pf.h, off, cnt))
+
+    def score(self):
+        total = C.c_double()
+        cabi._check(self.L.bamcl_pf_score_planar_staged(self.pf.h, self.map.h, int(self.pf.converged), C.byref(total)))
+        return total.value
+
+    def normalise(self, total):
+        self.pf.normalise(total)
+
+    def shard_cdf(self, c0):
+        end = C.c_double()
+        cabi._check(self.L.bamcl_pf_shard_cdf(self.pf.h, c0, C.byref(end)))
+        return end.value
+
+    def put_random(self, poses):
+        if len(poses):
+            self.buf[:len(poses)].copy_(self.torch.from_numpy(np.ascontiguousarray(poses, np.float64)))
+
+    def select(self, start, delta, n_sys, row0, kb, ke):
+        src = C.c_void_p(self.src.data_ptr()) if self.src is not None else None
+        cabi._check(self.L.bamcl_pf_shard_select(self.pf.h, start, delta, n_sys, row0, kb, ke,
+                                                 C.c_void_p(self.buf.data_ptr()), src))
+
+    def before_exchange(self):
+        self.pf.ctx.sync()  # selections were enqueued on the library's stream; NCCL runs on torch's
+
+    def after_exchange(self):
+        self.torch.cuda.current_stream(self.device).synchronize()
+
+    def install(self, n, prm):
+        res = cabi.ResampleResult()
+        cabi._check(self.L.bamcl_pf_shard_install(self.pf.h, C.c_void_p(self.buf.data_ptr()), n, C.byref(prm), C.byref(res)))
+        return res
+
+
+class ShardedFilter:
+    """ParticleFilter::updateSensor / updateResample over a rank-major sharded set. `dist` is torch.distributed (an
+    initialised default group) or None for a single rank."""
+
+    def __init__(self, engine, rank, world, dist, min_samples, max_samples, alpha_slow=0.001, alpha_fast=0.1,
+                 conv_thresh=95.0, pop_err=0.01, pop_z=0.99):
+        self.e, self.rank, self.world, self.dist = engine, rank, world, dist
+        self.min_samples, self.max_samples = min_samples, max_samples
+        self.alpha_slow, self.alpha_fast, self.conv_thresh = alpha_slow, alpha_fast, conv_thresh
+        self.pop_err, self.pop_z = pop_err, pop_z
+        self.w_slow = self.w_fast = 0.0
+        self.drand48_state = 0
+        self.random_poses = np.zeros((0, 3))
+        self.random_next = 0
+        self.last = None
+        self.last_plan = None
+        self.converged = False
+
+    def srand48(self, seed):
+        self.drand48_state = ((seed & 0xFFFFFFFF) << 16) | 0x330E
+
+    def set_random_poses(self, poses):
+        self.random_poses = np.ascontiguousarray(poses, np.float64)
+        self.random_next = 0
+
+    # -- windows
+    def window(self):
+        b = shard_bounds(self.e.sample_count(), self.world)
+        return b[self.rank], b[self.rank + 1] - b[self.rank]
+
+    def apply_window(self):
+        off, cnt = self.window()
+        self.e.set_window(off, cnt)
+
+    # -- exchanges
+    def _all_gather_scalar(self, v):
+        if self.dist is None or self.world == 1:
+            return [v]
+        t = self.e.scalar_tensor(v)
+        out = [self.e.scalar_tensor() for _ in range(self.world)]
+        self.dist.all_gather(out, t)
+        return [float(o.item()) for o in out]
+
+    def _chain_cdf(self):
+        """bounds[0..G]: rank r's CDF starts at the exact end value of rank r-1's (particle_filter.cpp:280-285)"""
+        bounds = [0.0]
+        for r in range(self.world):
+            if r == self.rank:
+                end = self.e.shard_cdf(bounds[r])
+            else:
+                end = 0.0
+            if self.dist is not None and self.world > 1:
+                t = self.e.scalar_tensor(end)
+                self.dist.broadcast(t, src=r)
+                end = float(t.item())
+            bounds.append(end)
+        return bounds
+
+    # -- ParticleFilter::updateSensor (particle_filter.cpp:223-267) with PlanarScanner::applyModelToSampleSet
+    def update_sensor(self):
+        self.apply_window()
+        local = self.e.score()
+        totals = self._all_gather_scalar(local)
+        total = 0.0
+        for t in totals:  # rank order = sample order of the partial sums
+            total += t
+        self.e.normalise(total)
+        if total > 0.0:
+            w_avg = total / self.e.sample_count()
+            self.w_slow = w_avg if self.w_slow == 0.0 else self.w_slow + self.alpha_slow * (w_avg - self.w_slow)
+            self.w_fast = w_avg if self.w_fast == 0.0 else self.w_fast + self.alpha_fast * (w_avg - self.w_fast)
+        self.last_total = total
+        return total
+
+    # -- ParticleFilter::updateResample, systematic (particle_filter.cpp:423-471, 269-354)
+    def update_resample(self, w_diff=None):
+        if w_diff is None:
+            with np.errstate(divide="ignore", invalid="ignore"):
+                w_diff = float(1.0 - np.float64(self.w_fast) / np.float64(self.w_slow))
+            if w_diff < 0.0:
+                w_diff = 0.0
+        if not w_diff >= 0.0:
+            raise RuntimeError("updateResample before any successful updateSensor (w_diff is NaN, SURVEY Q11)")
+        self.apply_window()
+        bounds = self._chain_cdf()
+        # :291-306
+        new_count = cabi.lib().bamcl_resample_limit(self.e.leaf_count(), self.min_samples, self.max_samples,
+                                                   self.pop_err, self.pop_z)
+        if w_diff > 0.0:
+            new_count = int(new_count * (1.0 + w_diff))
+            new_count = min(new_count, self.max_samples)
+        n_rand = int(w_diff * new_count)
+        n_sys = new_count - n_rand
+        rp = self.random_poses[self.random_next:self.random_next + n_rand]
+        if len(rp) < n_rand:
+            raise RuntimeError("%d random poses needed, %d supplied" % (n_rand, len(rp)))
+        self.e.put_random(rp)
+        # :309-310
+        state = drand48_next(self.drand48_state)
+        start = float(np.ldexp(np.float64(state), -48))
+        delta = 1.0 / n_sys if n_sys > 0 else 0.0
+        runs = systematic_plan(start, delta, n_sys, bounds) if n_sys > 0 else []
+        for kb, ke, r in runs:
+            if r == self.rank:
+                self.e.select(start, delta, n_sys, n_rand, kb, ke)
+        self.e.before_exchange()
+        if self.dist is not None and self.world > 1:
+            for kb, ke, r in runs:
+                self.dist.broadcast(self.e.buf[n_rand + kb:n_rand + ke], src=r)
+                if self.e.src is not None:
+                    self.dist.broadcast(self.e.src[n_rand + kb:n_rand + ke], src=r)
+        self.e.after_exchange()
+        prm = cabi.ResampleParams(1, self.min_samples, self.max_samples, self.pop_err, self.pop_z, w_diff, 0.5,
+                                  self.conv_thresh, self.drand48_state, None, 0)
+        res = self.e.install(new_count, prm)
+        res.random_poses_used = n_rand
+        res.drand48_state = state
+        self.drand48_state = state
+        self.random_next += n_rand
+        if w_diff > 0.0:
+            self.w_slow = self.w_fast = 0.0
+        self.converged = bool(res.converged)
+        if hasattr(self.e, "pf"):
+            self.e.pf.converged = self.converged
+        self.last, self.last_plan, self.last_bounds = res, runs, bounds
+        return res

@@ -204,6 +204,15 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic(kernel):
+    """dram bytes read + written per launch of `kernel`, from the committed ncu --set full capture (profiles/)"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return float(json.load(f)[kernel]["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def run_b200_arm(a):
     rank, local_rank, world = dist_env()
     from badger_amcl_b200 import cabi
@@ -214,25 +223,37 @@ def run_b200_arm(a):
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = cabi.Context(local_rank)
-    cells, truth, ranges, angles, poses = make_inputs(a, rank)
+    # ONE global set of world * P particles (weak scaling: P per GPU); map and scan replicated on every rank
     P, B = a.particles, a.beams
+    PT = P * world
+    ga = argparse.Namespace(**vars(a))
+    ga.particles = PT
+    cells, truth, ranges, angles, poses = make_inputs(ga)
     valid = int((ranges < RANGE_MAX).sum())
     m = cabi.Map2D(ctx, cells, RES)
     ctx.timer_start()
     m.build_distances(2.0)
     edt_ms = ctx.timer_stop_ms()
     model = cabi.planar_model(model_type=cabi.MODEL_LF, max_beams=B, scanner_pose=(0.1, 0.0, 0.0))
-    pf = cabi.ParticleFilter(ctx, P // 10, P)
-    aos = cabi.pinned_array((P, 4))
+    pf = cabi.ParticleFilter(ctx, PT // 10, PT)
+    aos = cabi.pinned_array((PT, 4))
     aos[:, :3] = poses
-    aos[:, 3] = 1.0 / P
-    out_aos = cabi.pinned_array((P, 4))
+    aos[:, 3] = 1.0 / PT
+    out_aos = cabi.pinned_array((PT, 4))
     pf.srand48(12345)
+    sf = None
+    if world > 1:
+        from badger_amcl_b200 import sharded
+        sf = sharded.ShardedFilter(sharded.CudaEngine(pf, m, local_rank), rank, world, dist, PT // 10, PT)
+        sf.srand48(12345)
+    off0, cnt0 = (PT * rank) // world, (PT * (rank + 1)) // world - (PT * rank) // world
 
     def restore():
         pf.upload_samples(aos)
         pf.init_with_current()  # kd-tree of the set being resampled (particle_filter.cpp:292 reads its leaf count)
         pf.w_slow = pf.w_fast = 0.0
+        if sf is not None:
+            sf.w_slow = sf.w_fast = 0.0
 
     def barrier():
         ctx.sync()
@@ -245,30 +266,46 @@ def run_b200_arm(a):
     def step_resident():
         restore()
         ctx.flush_l2()
-        ctx.sync()
+        barrier()
         ctx.timer_start()
-        pf.update_staged(m, want_total=True)
+        if sf is None:
+            pf.update_staged(m, want_total=True)
+        else:
+            sf.update_sensor()       # score this rank's window, all-gather the totals, normalise
         t_up = ctx.timer_stop_ms()
         k_ms = pf.last_score_ms()
         ctx.timer_start()
-        r = pf.update_resample()
+        r = pf.update_resample() if sf is None else sf.update_resample()
         t_rs = ctx.timer_stop_ms()
         return t_up, t_rs, k_ms, r
 
     def step_e2e():
         restore()
         ctx.flush_l2()
-        ctx.sync()
+        barrier()
         t0 = time.perf_counter()
         ctx.timer_start()
-        pf.upload_samples(aos)                                   # H2D: P x 32 B AoS from pinned host memory
-        pf.update_sensor(m, model, ranges, angles, RANGE_MAX)    # H2D: scan; D2H: total
-        r = pf.update_resample()                                 # D2H: result struct
-        n = r.sample_count
-        pf.download_samples_into(out_aos[:n])                    # D2H: n x 32 B AoS
+        if sf is None:
+            pf.upload_samples(aos)                                   # H2D: P x 32 B AoS from pinned host memory
+            pf.update_sensor(m, model, ranges, angles, RANGE_MAX)    # H2D: scan; D2H: total
+            r = pf.update_resample()                                 # D2H: result struct
+            n = r.sample_count
+            pf.download_samples_into(out_aos[:n])                    # D2H: n x 32 B AoS
+            moved = n
+        else:
+            # every rank moves ITS window: upload P x 32 B, stage the scan, sharded update + resample, download its
+            # share of the new set
+            cabi._check(pf.L.bamcl_pf_upload_window_samples(pf.h, cabi._p(aos[off0:off0 + cnt0]), off0, cnt0))
+            pf.stage_scan(m, model, ranges, angles, RANGE_MAX)
+            sf.update_sensor()
+            r = sf.update_resample()
+            n = r.sample_count
+            o, c = sf.window()
+            cabi._check(pf.L.bamcl_pf_download_window_samples(pf.h, cabi._p(out_aos[o:o + c]), o, c))
+            moved = c
         ms = ctx.timer_stop_ms()
         wall = (time.perf_counter() - t0) * 1e3
-        return max(ms, wall), n
+        return max(ms, wall), moved
 
     for _ in range(a.warmup):
         step_resident()
@@ -303,30 +340,36 @@ def run_b200_arm(a):
             dist.destroy_process_group()
         return 0
 
-    evals = float(P) * valid * world
+    evals = float(PT) * valid
     value = evals * a.steps / (total_ms * 1e-3)
     e_value = evals * a.steps / (e_total_ms * 1e-3)
     peak, peak_src = measured_peaks()
-    algo_bytes = float(P) * valid * 4 + float(P) * 40 + B * 16
+    algo_bytes = float(cnt0) * valid * 4 + float(cnt0) * 40 + B * 16   # one launch scores this rank's window
     achieved = algo_bytes / (k_ms * 1e-3) / 1e9
+    par = ("single GPU" if world == 1 else
+           "ONE global set of %d particles, rank-major windows x%d; map+scan replicated; weight totals all-gathered, "
+           "exact CDF chained over ranks, systematic select by source rank, pose runs broadcast, pose-bin tree "
+           "replicated" % (PT, world))
     line = {"metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(a), "valid_beams": valid, "model": "likelihood_field",
+                       "global_particles": PT,
                        "resample": "kld systematic, min=P/10 max=P, kld_err 0.01 kld_z 0.99",
-                       "parallelism": "particle shards x%d, map+scan replicated" % world,
+                       "parallelism": par,
                        "l2": "flushed (256 MiB write) before every timed step",
                        "update_ms": up / a.steps, "resample_ms": rs / a.steps, "edt_build_ms": edt_ms,
                        "resampled_count": int(last.sample_count), "kld_leaf_count": int(last.leaf_count),
                        "clusters": int(last.cluster_count)},
             "e2e": {"value": e_value, "unit": "evals/s", "ms_per_step": e_total_ms / a.steps,
-                    "h2d_bytes_per_step": int(P * 32 + 2 * B * 8), "d2h_bytes_per_step": int(n_out * 32 + 8 + 96)},
+                    "h2d_bytes_per_step": int(cnt0 * 32 + 2 * B * 8) * world,
+                    "d2h_bytes_per_step": int(n_out * 32 + 8 + 96) * world},
             "gpu_launches": int(launches_timed),
             "roofline": {"kernel": "k_score_lf", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "kernel_ms": k_ms, "peak_source": peak_src,
-                         "algorithmic_bytes": algo_bytes},
+                         "frac": achieved / peak, "traffic": ncu_traffic("k_score_lf") if world == 1 else None,
+                         "kernel_ms": k_ms, "peak_source": peak_src, "algorithmic_bytes": algo_bytes},
             "clocks": clocks}
-    if not a.no_cpu_baseline and world >= 1:
+    if not a.no_cpu_baseline and world == 1:
         n_cpu = a.cpu_particles or min(P, 20000)
         arm = CpuArm(a, cells, ranges, angles, poses, n_cpu)
         arm.step()

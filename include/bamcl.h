@@ -160,6 +160,8 @@ int bamcl_pf_update_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_mo
 int bamcl_pf_stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
                         const double* angles, int range_count, double range_max);
 int bamcl_pf_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out_or_null);
+/* applyModelToSampleSet only (no normalisation) with the staged scan: the sharded filter normalises by the GLOBAL total */
+int bamcl_pf_score_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out);
 
 /* PointCloudScanner::applyModelToSampleSet (point_cloud_scanner.cpp:111-129) on the current set: per-particle
  * cloud transform (getMapCloud :231-248), calcPointCloudModel / Gompertz (:132-203) and recalcWeight (:205-229)
@@ -236,6 +238,41 @@ int bamcl_pf_cluster_stats(bamcl_pf* pf, double* out, int max_clusters);
 int bamcl_systematic_targets(double start, double delta, long n, double* out);
 /* resampleLimit (particle_filter.cpp:475-502), host arithmetic exposed for parity tests */
 int bamcl_resample_limit(int k, int min_samples, int max_samples, double pop_err, double pop_z);
+
+/* ---- sharded filter (multi-GPU, one process per GPU) ------------------------------------
+ * The reference resamples ONE global set (particle_filter.cpp:269-354). With G ranks the global order is
+ * rank-major: rank r scores, normalises and builds the CDF of its window [offset, offset + count) of the set;
+ * every rank holds the whole set (poses of foreign windows are only read by the pose-bin tree). The host layer
+ * moves the scalars and poses between ranks (NCCL on bamcl_ctx_stream(); badger_amcl_b200/sharded.py):
+ *   score (window) -> local totals all-gathered, summed in rank order -> bamcl_pf_normalise(global total)
+ *   bamcl_pf_shard_cdf(c0 = end of rank r-1) chained over ranks -> bounds[0..G]
+ *   bamcl_systematic_plan -> which rank's window holds the source of every output slot (runs of slots)
+ *   bamcl_pf_shard_select for this rank's runs -> rows of a global (n x 3) device buffer; runs broadcast
+ *   bamcl_pf_shard_install: buffer -> the other sample set (weights 1/n), pose-bin tree, clusters, statistics. */
+/* window of the current set this rank works on; count < 0 = whole set (single-GPU behaviour) */
+int bamcl_pf_set_window(bamcl_pf* pf, long offset, long count);
+/* exact sequential CDF of the window with c[0] = c0 (particle_filter.cpp:280-285 continued from the previous
+ * rank's last value); end_out = c[count] */
+int bamcl_pf_shard_cdf(bamcl_pf* pf, double c0, double* end_out);
+/* host arithmetic: for the systematic target sequence (start, delta, n) of particle_filter.cpp:309,337-341 and the
+ * ranks' CDF bounds[0..n_ranks], the runs (k_begin, k_end, rank) of output slots whose source lies in each rank's
+ * window; targets at/after bounds[n_ranks] go to the last rank that holds weight. */
+int bamcl_systematic_plan(double start, double delta, long n, const double* bounds, int n_ranks, long* runs, int max_runs,
+                          int* n_runs);
+/* particle_filter.cpp:326-351 for outputs [k_begin, k_end) of n_sys: pose of the selected window particle ->
+ * out_aos3_dev[(row0 + k) * 3 ..] (device pointer), global source index -> src_out_dev_or_null[row0 + k]. Enqueued on
+ * the context's stream; needs bamcl_pf_shard_cdf first. */
+int bamcl_pf_shard_select(bamcl_pf* pf, double start, double delta, long n_sys, long row0, long k_begin, long k_end,
+                          double* out_aos3_dev, int* src_out_dev_or_null);
+/* particle_filter.cpp:343-346,448-470 on every rank: the n gathered poses become the new current set (weights 1/n),
+ * then pose-bin tree, clusters, statistics, updateConverged as in bamcl_pf_resample; clears the window. */
+int bamcl_pf_shard_install(bamcl_pf* pf, const double* aos3_dev, long n, const bamcl_resample_params* params,
+                           bamcl_resample_result* result);
+/* host AoS <-> the samples [offset, offset + n) of the current set (a rank's window); sample_count is unchanged */
+int bamcl_pf_upload_window_samples(bamcl_pf* pf, const double* aos, long offset, long n);
+int bamcl_pf_download_window_samples(bamcl_pf* pf, double* aos, long offset, long n);
+/* getLeafCount of the current set's tree (pf_kdtree.cpp:92), as of its last resample / init */
+int bamcl_pf_leaf_count(bamcl_pf* pf, int* leaf_count);
 
 #ifdef __cplusplus
 }

@@ -540,6 +540,55 @@ __global__ void __launch_bounds__(256) k_cluster_finalize(const TreeOut* __restr
 }
 }  // namespace
 
+namespace
+{
+// the bucketed shared-memory leaf count (tree_fast.cuh) with a top tree of M_TOP keys
+template <int M_TOP>
+int launch_fast_tree(bamcl_pf* pf, TreeOut* out, int n)
+{
+  bamcl_ctx* ctx = pf->ctx;
+  constexpr int N_BUCKETS = 2 * M_TOP;
+  FastArgs fa;
+  int* small = pf->t_fast.as<int>();
+  fa.out = out;
+  fa.nkey = pf->t_nkey.as<unsigned long long>();
+  fa.tpivot = small;
+  fa.tchild = small + M_TOP;
+  fa.bcount = small + 3 * M_TOP;
+  fa.boff = fa.bcount + N_BUCKETS + 1;
+  fa.bslot = pf->t_cur.as<int>();
+  fa.bpos = pf->t_first_at.as<int>();
+  fa.bids = pf->t_child.as<int>();
+  fa.parent = pf->t_parent.as<int>();
+  const int per = 28;  // bytes of shared memory per key in k_fast_top / k_fast_bucket
+  static bool attr_done = false;
+  if (!attr_done)
+  {
+    BAMCL_CUDA_OK(cudaFuncSetAttribute(k_fast_top<M_TOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 24 * M_TOP));
+    BAMCL_CUDA_OK(cudaFuncSetAttribute(k_fast_descend<M_TOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 17 * M_TOP));
+    BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_M, FAST_CAP_S, 512, M_TOP>),
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, per * FAST_CAP_M));
+    BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_L, FAST_CAP_M, 1024, M_TOP>),
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, per * FAST_CAP_L));
+    attr_done = true;
+  }
+  const int walk_blocks = std::max(1, std::min(kNumSMs * (M_TOP > 4096 ? 1 : 8), (n + 255) / 256));
+  BAMCL_LAUNCH(ctx, k_fast_top<M_TOP>, 1, 1024, 24 * M_TOP, fa);
+  BAMCL_LAUNCH(ctx, k_fast_descend<M_TOP>, walk_blocks, 256, 17 * M_TOP, fa);
+  BAMCL_LAUNCH(ctx, k_fast_offsets<M_TOP>, 1, 1024, 0, fa);
+  if (n > M_TOP)
+    BAMCL_LAUNCH(ctx, k_fast_scatter<M_TOP>, walk_blocks, 256, 0, fa);
+  const int bucket_blocks = 2 * std::min(n, M_TOP);
+  BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_S, 0, 256, M_TOP>), bucket_blocks, 256, per * FAST_CAP_S, fa);
+  if (n > M_TOP + FAST_CAP_S)
+  {
+    BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_M, FAST_CAP_S, 512, M_TOP>), bucket_blocks, 512, per * FAST_CAP_M, fa);
+    BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_L, FAST_CAP_M, 1024, M_TOP>), bucket_blocks, 1024, per * FAST_CAP_L, fa);
+  }
+  return BAMCL_OK;
+}
+}  // namespace
+
 namespace bamcl
 {
 static int coop_blocks_for(bamcl_pf* pf)
@@ -585,7 +634,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
   BAMCL_TRY(pf->t_cid.reserve(sizeof(int) * cap_n));
   BAMCL_TRY(pf->t_nfirst.reserve(sizeof(int) * cap_n));
   BAMCL_TRY(pf->t_scan.reserve(sizeof(int) * scan_scratch_ints((long)cap_n)));
-  BAMCL_TRY(pf->t_fast.reserve(sizeof(int) * (3 * M_TOP + 2 * (N_BUCKETS + 1))));
+  BAMCL_TRY(pf->t_fast.reserve(sizeof(int) * (3 * M_TOP_LARGE + 2 * (2 * M_TOP_LARGE + 1))));
   BAMCL_TRY(pf->t_out.reserve(sizeof(TreeOut)));
   BAMCL_TRY(pf->t_hout.reserve(sizeof(TreeOut)));
   if (pf->t_cluster_cap == 0)
@@ -614,42 +663,10 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
     static const bool force_general = getenv("BAMCL_TREE_GENERAL") != nullptr;  // tests: exercise k_tree_build
     if (!force_general)
     {
-      FastArgs fa;
-      int* small = pf->t_fast.as<int>();
-      fa.out = out;
-      fa.nkey = pf->t_nkey.as<unsigned long long>();
-      fa.tpivot = small;
-      fa.tchild = small + M_TOP;
-      fa.bcount = small + 3 * M_TOP;
-      fa.boff = fa.bcount + N_BUCKETS + 1;
-      fa.bslot = pf->t_cur.as<int>();
-      fa.bpos = pf->t_first_at.as<int>();
-      fa.bids = pf->t_child.as<int>();
-      fa.parent = pf->t_parent.as<int>();
-      const int per = 28;  // bytes of shared memory per key in k_fast_top / k_fast_bucket
-      static bool attr_done = false;
-      if (!attr_done)
-      {
-        BAMCL_CUDA_OK(cudaFuncSetAttribute(k_fast_top, cudaFuncAttributeMaxDynamicSharedMemorySize, 24 * M_TOP));
-        BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_M, FAST_CAP_S, 512>),
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, per * FAST_CAP_M));
-        BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_L, FAST_CAP_M, 1024>),
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, per * FAST_CAP_L));
-        attr_done = true;
-      }
-      const int walk_blocks = std::max(1, std::min(kNumSMs * 8, (n + 255) / 256));
-      BAMCL_LAUNCH(ctx, k_fast_top, 1, 1024, 24 * M_TOP, fa);
-      BAMCL_LAUNCH(ctx, k_fast_descend, walk_blocks, 256, 0, fa);
-      BAMCL_LAUNCH(ctx, k_fast_offsets, 1, 1024, 0, fa);
-      if (n > M_TOP)
-        BAMCL_LAUNCH(ctx, k_fast_scatter, walk_blocks, 256, 0, fa);
-      const int bucket_blocks = 2 * std::min(n, M_TOP);
-      BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_S, 0, 256>), bucket_blocks, 256, per * FAST_CAP_S, fa);
-      if (n > M_TOP + FAST_CAP_S)
-      {
-        BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_M, FAST_CAP_S, 512>), bucket_blocks, 512, per * FAST_CAP_M, fa);
-        BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_L, FAST_CAP_M, 1024>), bucket_blocks, 1024, per * FAST_CAP_L, fa);
-      }
+      if (n > 1500000)
+        BAMCL_TRY((launch_fast_tree<M_TOP_LARGE>(pf, out, n)));
+      else
+        BAMCL_TRY((launch_fast_tree<M_TOP_SMALL>(pf, out, n)));
     }
     {
       TreeArgs ta;

@@ -17,8 +17,9 @@
 // give up (TreeOut::fast_ok stays 0) and k_tree_build does the work instead.
 #pragma once
 
-constexpr int M_TOP = 2048;        // keys in the top tree
-constexpr int N_BUCKETS = 2 * M_TOP;
+// keys in the top tree: the largest bucket holds about ln(M_TOP) / M_TOP of the keys, so sets beyond ~1.5M samples
+// (sharded filter: every rank builds the global tree) take the large top tree to stay inside FAST_CAP_L.
+constexpr int M_TOP_SMALL = 2048, M_TOP_LARGE = 8192;
 constexpr int FAST_CAP_S = 512, FAST_CAP_M = 2048, FAST_CAP_L = 6144;
 
 __device__ __forceinline__ int pivot_dim(unsigned long long ku, unsigned long long kf)
@@ -111,8 +112,10 @@ struct FastArgs
 };
 
 // ---- 1. top tree (one CTA)
+template <int M_TOP>
 __global__ void __launch_bounds__(1024) k_fast_top(const FastArgs a)
 {
+  constexpr int N_BUCKETS = 2 * M_TOP;
   extern __shared__ __align__(16) unsigned char s_raw[];
   unsigned long long* key = reinterpret_cast<unsigned long long*>(s_raw);
   int* cur = reinterpret_cast<int*>(key + M_TOP);
@@ -145,11 +148,13 @@ __global__ void __launch_bounds__(1024) k_fast_top(const FastArgs a)
 }
 
 // ---- 2. every later key finds its bucket
+template <int M_TOP>
 __global__ void __launch_bounds__(256) k_fast_descend(const FastArgs a)
 {
-  __shared__ unsigned long long s_key[M_TOP];
-  __shared__ int s_child[2 * M_TOP];
-  __shared__ signed char s_pivot[M_TOP];
+  extern __shared__ __align__(16) unsigned char s_raw[];  // 17 * M_TOP bytes
+  unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_raw);
+  int* s_child = reinterpret_cast<int*>(s_key + M_TOP);
+  signed char* s_pivot = reinterpret_cast<signed char*>(s_child + 2 * M_TOP);
   const int K = a.out->K;
   const int m = min(K, M_TOP);
   for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < K; v += gridDim.x * blockDim.x)
@@ -191,8 +196,10 @@ __global__ void __launch_bounds__(256) k_fast_descend(const FastArgs a)
 }
 
 // ---- 3. bucket offsets (one CTA) and the grouping scatter
+template <int M_TOP>
 __global__ void __launch_bounds__(1024) k_fast_offsets(const FastArgs a)
 {
+  constexpr int N_BUCKETS = 2 * M_TOP;
   __shared__ int s_warp[32];
   __shared__ int s_over;
   constexpr int PER = N_BUCKETS / 1024;
@@ -247,6 +254,7 @@ __global__ void __launch_bounds__(1024) k_fast_offsets(const FastArgs a)
   }
 }
 
+template <int M_TOP>
 __global__ void __launch_bounds__(256) k_fast_scatter(const FastArgs a)
 {
   const int K = a.out->K;
@@ -257,7 +265,7 @@ __global__ void __launch_bounds__(256) k_fast_scatter(const FastArgs a)
 }
 
 // ---- 4. one CTA per bucket: sort by creation index, grow the subtree, count its childless nodes
-template <int CAP, int CAP_BELOW, int THREADS>
+template <int CAP, int CAP_BELOW, int THREADS, int M_TOP>
 __global__ void __launch_bounds__(THREADS) k_fast_bucket(const FastArgs a)
 {
   extern __shared__ __align__(16) unsigned char s_raw[];

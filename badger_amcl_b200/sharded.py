@@ -16,6 +16,8 @@ device phases live behind an *engine*: `CudaEngine` here (the C ABI); tests/ plu
 exercise the host logic without a GPU. No engine here computes on the CPU.
 """
 import ctypes as C
+import os
+import time
 
 import numpy as np
 
@@ -186,8 +188,16 @@ class ShardedFilter:
                 w_diff = 0.0
         if not w_diff >= 0.0:
             raise RuntimeError("updateResample before any successful updateSensor (w_diff is NaN, SURVEY Q11)")
+        tm = [time.perf_counter()] if os.environ.get("BAMCL_SHARD_TIMING") else None
+
+        def mark():
+            if tm is not None:
+                self.e.before_exchange()
+                tm.append(time.perf_counter())
+
         self.apply_window()
         bounds = self._chain_cdf()
+        mark()
         # :291-306
         new_count = cabi.lib().bamcl_resample_limit(self.e.leaf_count(), self.min_samples, self.max_samples,
                                                    self.pop_err, self.pop_z)
@@ -209,15 +219,22 @@ class ShardedFilter:
             if r == self.rank:
                 self.e.select(start, delta, n_sys, n_rand, kb, ke)
         self.e.before_exchange()
+        mark()
         if self.dist is not None and self.world > 1:
             for kb, ke, r in runs:
                 self.dist.broadcast(self.e.buf[n_rand + kb:n_rand + ke], src=r)
                 if self.e.src is not None:
                     self.dist.broadcast(self.e.src[n_rand + kb:n_rand + ke], src=r)
         self.e.after_exchange()
+        mark()
         prm = cabi.ResampleParams(1, self.min_samples, self.max_samples, self.pop_err, self.pop_z, w_diff, 0.5,
                                   self.conv_thresh, self.drand48_state, None, 0)
         res = self.e.install(new_count, prm)
+        mark()
+        if tm is not None and self.rank == 0:
+            d = [1e3 * (b - a) for a, b in zip(tm, tm[1:])]
+            print("[shard timing ms] cdf-chain %.3f plan+select %.3f exchange %.3f install+tree %.3f runs %d" %
+                  (d[0], d[1], d[2], d[3], len(runs)), flush=True)
         res.random_poses_used = n_rand
         res.drand48_state = state
         self.drand48_state = state

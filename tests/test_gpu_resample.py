@@ -203,3 +203,17 @@ def test_kdtree_leaf_count_paths(env, n, order):
     assert (r.leaf_count, r.node_count, r.cluster_count) == (port.leaf_count(), port.node_count(), port.cluster_count())
     assert np.array_equal(pf.sample_clusters(), port.sample_clusters())
     pf.close()
+
+
+def test_kdtree_leaf_count_large_top_tree(env):
+    """sets beyond 1.5M samples (a sharded filter's global set) use the 8192-key top tree of tree_fast.cuh"""
+    O, cabi = env["O"], env["cabi"]
+    n = 2200000
+    poses = synth.uniform_free_poses(env["cells"], RES, n, seed=21)
+    port = O.PortPF(1, n)
+    port.init_with_poses(poses)
+    pf = cabi.ParticleFilter(env["ctx"], 1, n)
+    r = pf.init_with_poses(poses)
+    assert (r.leaf_count, r.node_count) == (port.leaf_count(), port.node_count())
+    assert r.cluster_count == port.cluster_count()
+    pf.close()

@@ -661,7 +661,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
                  pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), pf->t_nkey.as<unsigned long long>(),
                  pf->t_nfirst.as<int>(), n);
     static const bool force_general = getenv("BAMCL_TREE_GENERAL") != nullptr;  // tests: exercise k_tree_build
-    if (!force_general)
+    if (!force_general && !pf->force_general_tree)
     {
       if (n > 1500000)
         BAMCL_TRY((launch_fast_tree<M_TOP_LARGE>(pf, out, n)));

@@ -1,9 +1,235 @@
-// Multinomial KLD resampling (particle_filter.cpp:356-420) -- placeholder until the device version lands.
+// K-d (multinomial): KLD-adaptive multinomial resampling. Reference: src/amcl/pf/particle_filter.cpp:356-420.
+//
+// The reference draws one output at a time -- drand48() < w_diff ? random pose : (r = drand48(); linear search
+// c[i] <= r < c[i+1]) -- inserts it into set_b's pose-bin tree and stops as soon as the output count exceeds
+// resampleLimit(leaf count so far) (:416). Parallel form, for w_diff == 0 (two draws per output, the first one
+// unused because `drand48() < 0` is never true):
+//   1. exact sequential CDF (resample.cu);
+//   2. all max_samples candidate outputs at once: output k uses draw 2k+2 of the generator, reached by the LCG's
+//      skip-ahead (X_j = A^j X_0 + C_j mod 2^48), and the same upper_bound as the systematic select;
+//   3. the pose-bin tree of ALL candidates (general build, which keeps every node's first foreign key). A node is
+//      a leaf from its creation until its first child is created, so after m insertions
+//         leaf(m) = #{nodes created by a sample < m} - #{nodes whose first child was created by a sample < m}
+//      (SURVEY H2): two +-1 events per node on the sample time line and one prefix sum;
+//   4. the smallest m with m > resampleLimit(leaf(m)), else max_samples: the new set is the first m candidates;
+//   5. tree, clusters and statistics of those m samples as for any new set.
+// w_diff > 0 interleaves random_pose_fn_() -- host code that itself calls drand48 (node.cpp:831,837) -- with the
+// resampler's draws one output at a time; that order cannot be reproduced from the device and is refused.
+#include <cmath>
+#include <cstring>
+
 #include "pf.cuh"
+#include "scan.cuh"
+
+using namespace bamcl;
+
 namespace bamcl
 {
-int resample_multinomial(bamcl_pf*, const bamcl_resample_params*, bamcl_resample_result*)
+int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, double convergence_threshold,
+                         bamcl_resample_result* result);  // kdtree.cu
+}
+
+namespace
 {
-  return set_error(BAMCL_E_UNSUPPORTED, "multinomial resampling is not implemented on the device yet");
+constexpr unsigned long long LCG_A = 0x5DEECE66DULL, LCG_C = 0xBULL, LCG_MASK = (1ULL << 48) - 1;
+constexpr int NONE = INT_MAX;
+
+// state after j steps from x0
+__host__ __device__ inline unsigned long long lcg_skip(unsigned long long x0, unsigned long long j)
+{
+  unsigned long long a = LCG_A, c = LCG_C, A = 1, C = 0;  // x -> A x + C
+  while (j)
+  {
+    if (j & 1)
+    {
+      A = (A * a) & LCG_MASK;
+      C = (C * a + c) & LCG_MASK;
+    }
+    c = ((a + 1) * c) & LCG_MASK;
+    a = (a * a) & LCG_MASK;
+    j >>= 1;
+  }
+  return (A * x0 + C) & LCG_MASK;
+}
+
+struct MultiArgs
+{
+  const double* c;  // P + 1
+  int P;
+  const double *ax, *ay, *ath;
+  double *bx, *by, *bth, *bw;
+  int* src;
+  int n;
+  unsigned long long state0;
+  int* flags;
+};
+
+__global__ void __launch_bounds__(256) k_select_multinomial(const MultiArgs a)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= a.n)
+    return;
+  const unsigned long long x = lcg_skip(a.state0, 2ull * (unsigned long long)k + 2ull);
+  const double r = scalbn((double)x, -48);  // drand48: X / 2^48, exact
+  int L = 0, H = a.P;  // first i with c[i] <= r < c[i+1] == number of entries of c[1..P] that are <= r
+  while (L < H)
+  {
+    const int mid = (L + H) >> 1;
+    if (__ldg(&a.c[mid + 1]) <= r)
+      L = mid + 1;
+    else
+      H = mid;
+  }
+  int j = L;
+  if (j >= a.P)
+  {
+    // r >= c[P]: the reference's search runs off the end and copies samples[P] (:391-403); flagged, last particle
+    // with weight taken
+    atomicOr(a.flags, 1);
+    const double top = a.c[a.P];
+    int l2 = 0, h2 = a.P;
+    while (l2 < h2)
+    {
+      const int mid = (l2 + h2) >> 1;
+      if (a.c[mid + 1] < top)
+        l2 = mid + 1;
+      else
+        h2 = mid;
+    }
+    j = min(l2, a.P - 1);
+  }
+  a.src[k] = j;
+  a.bx[k] = a.ax[j];
+  a.by[k] = a.ay[j];
+  a.bth[k] = a.ath[j];
+  a.bw[k] = 1.0;
+}
+
+// +1 at the sample that created node v, -1 at the sample that created v's first child
+__global__ void k_leaf_events(const int* __restrict__ nfirst, const int* __restrict__ first_at, int K, int* __restrict__ ev)
+{
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= K)
+    return;
+  atomicAdd(&ev[nfirst[v]], 1);
+  const int f = first_at[v];
+  if (f != NONE)
+    atomicAdd(&ev[nfirst[f]], -1);
+}
+
+// particle_filter.cpp:475-502 on the device (same operations in the same order; the library is built without FMA
+// contraction)
+__device__ __forceinline__ int d_resample_limit(int k, int min_samples, int max_samples, double pop_err, double pop_z)
+{
+  if (k <= 1)
+    return max_samples;
+  const double kd = (double)k;
+  const double a = 1;
+  const double b = 2 / (9 * (kd - 1));
+  const double c = sqrt(2 / (9 * (kd - 1))) * pop_z;
+  const double x = a - b + c;
+  const int n = (int)ceil((k - 1) / (2 * pop_err) * x * x * x);
+  if (n < min_samples)
+    return min_samples;
+  if (n > max_samples)
+    return max_samples;
+  return n;
+}
+
+// leaf_before[m] = leaf count after m insertions; the first m with m > resampleLimit(leaf) stops the loop (:416)
+__global__ void k_find_stop(const int* __restrict__ leaf_before, int n, int min_samples, int max_samples, double pop_err,
+                            double pop_z, int* __restrict__ stop)
+{
+  const int m = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  if (m > n)
+    return;
+  if (m > d_resample_limit(leaf_before[m], min_samples, max_samples, pop_err, pop_z))
+    atomicMin(stop, m);
+}
+
+__global__ void k_fill_f64(double* __restrict__ p, double v, int n)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    p[i] = v;
+}
+}  // namespace
+
+namespace bamcl
+{
+int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res)
+{
+  if (prm->w_diff > 0.0)
+    return set_error(BAMCL_E_UNSUPPORTED,
+                     "multinomial resampling with w_diff > 0 interleaves random_pose_fn_() with the resampler's drand48 "
+                     "draws one output at a time (particle_filter.cpp:385-387); use the systematic model");
+  bamcl_ctx* ctx = pf->ctx;
+  SampleSet& set_a = pf->sets[pf->current];
+  SampleSet& set_b = pf->sets[1 - pf->current];
+  const int P = set_a.sample_count;
+  const int n = prm->max_samples;
+  if (P <= 0)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_resample: the current set is empty");
+  BAMCL_TRY(pf_build_cdf(pf));
+  BAMCL_TRY(pf->src.reserve(sizeof(int) * (size_t)pf->max_samples));
+  MultiArgs a;
+  a.c = pf->cdf.as<double>();
+  a.P = P;
+  a.ax = set_a.x.as<double>();
+  a.ay = set_a.y.as<double>();
+  a.ath = set_a.th.as<double>();
+  a.bx = set_b.x.as<double>();
+  a.by = set_b.y.as<double>();
+  a.bth = set_b.th.as<double>();
+  a.bw = set_b.w.as<double>();
+  a.src = pf->src.as<int>();
+  a.n = n;
+  a.state0 = prm->drand48_state;
+  a.flags = pf_flags(pf);
+  BAMCL_LAUNCH(ctx, k_select_multinomial, (n + 255) / 256, 256, 0, a);
+
+  // tree of all candidates with every node's first foreign key kept (general build)
+  set_b.sample_count = n;
+  pf->current = 1 - pf->current;
+  pf->force_general_tree = true;
+  bamcl_resample_result all;
+  memset(&all, 0, sizeof(all));
+  const int rc = build_tree_and_stats(pf, pf->current, prm->dist_threshold, prm->convergence_threshold, &all);
+  pf->force_general_tree = false;
+  if (rc != BAMCL_OK)
+    return rc;
+  const int K = all.node_count;
+  // events on the sample time line, prefix sum, first stopping point
+  BAMCL_TRY(pf->scratch.reserve(sizeof(int) * ((size_t)n + 8)));
+  BAMCL_TRY(pf->scratch2.reserve(sizeof(int) * (scan_scratch_ints((long)n + 1) + 8)));
+  int* ev = pf->scratch.as<int>();
+  int* stop = pf->scratch2.as<int>();
+  int* scan_scratch = stop + 4;
+  const int sentinel = INT_MAX;
+  BAMCL_CUDA_OK(cudaMemsetAsync(ev, 0, sizeof(int) * ((size_t)n + 1), ctx->stream));
+  BAMCL_CUDA_OK(cudaMemcpyAsync(stop, &sentinel, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+  BAMCL_LAUNCH(ctx, k_leaf_events, (K + 255) / 256, 256, 0, pf->t_nfirst.as<int>(), pf->t_first_at.as<int>(), K, ev);
+  BAMCL_TRY(exclusive_scan_i32(ctx, ev, ev, (long)n + 1, scan_scratch, stop + 1));
+  BAMCL_LAUNCH(ctx, k_find_stop, (n + 255) / 256, 256, 0, ev, n, prm->min_samples, prm->max_samples, prm->pop_err,
+               prm->pop_z, stop);
+  int h_stop = 0;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(&h_stop, stop, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  const int count = h_stop < n ? h_stop : n;
+
+  // the new set: the first `count` candidates, weights 1/count (:404-405 then :457-462)
+  set_b.sample_count = count;
+  BAMCL_LAUNCH(ctx, k_fill_f64, (count + 255) / 256, 256, 0, set_b.w.as<double>(), 1.0 / (double)count, count);
+  BAMCL_TRY(build_tree_and_stats(pf, pf->current, prm->dist_threshold, prm->convergence_threshold, res));
+  int flags = 0;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(&flags, pf_flags(pf), sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  if (flags & 2)
+    return set_error(BAMCL_E_UNSUPPORTED, "resample: a CDF running sum left the supported range");
+  res->sample_count = count;
+  res->random_poses_used = 0;
+  res->status_flags = flags & 1;
+  res->drand48_state = lcg_skip(prm->drand48_state, 2ull * (unsigned long long)count);
+  return BAMCL_OK;
 }
 }  // namespace bamcl

@@ -328,7 +328,8 @@ int bamcl_pf_stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model
 int bamcl_pf_score_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
                           const double* angles, int range_count, double range_max, int converged, double* total_out)
 {
-  (void)converged;
+  if (pf)
+    pf->set_converged = converged;
   if (!total_out)
     return set_error(BAMCL_E_ARG, "bamcl_pf_score_planar: total_out is required");
   BAMCL_TRY(stage_scan(pf, map, model, ranges, angles, range_count, range_max));
@@ -379,7 +380,8 @@ int bamcl_pf_normalise(bamcl_pf* pf, double total)
 
 int bamcl_pf_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out_or_null)
 {
-  (void)converged;
+  if (pf)
+    pf->set_converged = converged;
   if (!pf || !map)
     return set_error(BAMCL_E_ARG, "bamcl_pf_update_planar_staged: bad arguments");
   SampleSet& s = pf->sets[pf->current];
@@ -401,7 +403,8 @@ int bamcl_pf_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged,
 
 int bamcl_pf_score_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out)
 {
-  (void)converged;
+  if (pf)
+    pf->set_converged = converged;
   if (!pf || !map || !total_out)
     return set_error(BAMCL_E_ARG, "bamcl_pf_score_planar_staged: bad arguments");
   if (pf->scan.valid && pf->scan.model.max_beams < 2)

@@ -1,5 +1,7 @@
 // ParticleFilter device state: two SoA sample sets + per-set kd-tree/cluster state + staged scan.
 #pragma once
+#include <vector>
+
 #include "common.cuh"
 #include "map2d.cuh"
 
@@ -34,6 +36,14 @@ struct StagedScan
   // raw copies for the beam model
   DevBuf ranges, angles;
   int range_count = 0, step = 1;
+  // beam skipping (planar_scanner.cpp:361-529): slot (beam_ind) of every staged beam, the staged beams on the host,
+  // "cached distance < beam_skip_distance" per table rank, and device scratch for the agreement counts / the
+  // beams that survive the mask
+  std::vector<int> beam_slot;
+  std::vector<double> h_beams;
+  DevBuf agree;      // u8[table_n]
+  DevBuf skip_count; // int32[n_beams]
+  DevBuf beams_sel;  // double2[n_beams]
 };
 // Point cloud staged for the 3-D scoring kernel.
 struct StagedCloud
@@ -79,6 +89,12 @@ struct bamcl_pf
   int coop_blocks = 0;
   cudaEvent_t score_ev0 = nullptr, score_ev1 = nullptr;  // around the last scoring kernel (bamcl_pf_last_score_ms)
   bool score_timed = false;
+  // temp_obs_ bookkeeping of the beam-skipping model (planar_scanner.h:160-164): rows written per slot since the last
+  // clearTempData (planar_scanner.cpp:684-690); the values themselves are recomputed, never stored
+  std::vector<int> skip_written;
+  int skip_max_obs = 0, skip_max_samples = 0;
+  bool force_general_tree = false;  // keep every node's first foreign key (multinomial.cu needs t_first_at)
+  int set_converged = 0;     // set->converged as handed to the last scoring entry point
   bool exact_terms = false;  // bamcl_pf_set_exact_terms
   int tree_levels = 0;      // levels the last tree build needed (diagnostics)
   // Sharded filter (multi-GPU): every rank holds the whole set; scoring, totals, normalisation and the

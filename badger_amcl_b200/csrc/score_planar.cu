@@ -261,6 +261,65 @@ __global__ void __launch_bounds__(WARPS * 32) k_score_lf(const ScoreArgs a)
     }
   }
 }
+
+// ---- beam skipping, pass 1 (planar_scanner.cpp:398-451): per staged beam, the number of particles whose end point
+// lies on the map within beam_skip_distance of an obstacle. Lane l loads particle l of a group of 32; the group's
+// particles are then broadcast one by one and the lanes stride over the beams. Counts are kept per CTA in shared
+// memory and flushed once.
+__global__ void __launch_bounds__(256) k_skip_count(const ScoreArgs a, const unsigned char* __restrict__ agree,
+                                                    int* __restrict__ counts, int layout)
+{
+  extern __shared__ int s_cnt[];
+  for (int b = threadIdx.x; b < a.n_beams; b += blockDim.x)
+    s_cnt[b] = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+  const unsigned k_off = (unsigned)(a.table_n - 1);
+  for (int base = warp * 32; base < a.n; base += n_warps * 32)
+  {
+    const int idx = base + lane;
+    double4 st = make_double4(0.0, 0.0, 0.0, 0.0);
+    if (idx < a.n)
+    {
+      const double px = a.x[idx], py = a.y[idx], pth = a.th[idx];
+      double sn, cs;
+      sincos(pth, &sn, &cs);
+      const double sx = px + a.scan_x * cs - a.scan_y * sn;
+      const double sy = py + a.scan_x * sn + a.scan_y * cs;
+      st.x = cs * a.cos_sa - sn * a.sin_sa;
+      st.y = sn * a.cos_sa + cs * a.sin_sa;
+      st.z = (sx - (double)a.origin_x) / a.resolution + 0.5 + (double)(a.size_x / 2);
+      st.w = (sy - (double)a.origin_y) / a.resolution + 0.5 + (double)(a.size_y / 2);
+    }
+    const int live = min(32, a.n - base);
+    for (int g = 0; g < live; g++)
+    {
+      double4 p;
+      p.x = __shfl_sync(0xffffffffu, st.x, g);
+      p.y = __shfl_sync(0xffffffffu, st.y, g);
+      p.z = __shfl_sync(0xffffffffu, st.z, g);
+      p.w = __shfl_sync(0xffffffffu, st.w, g);
+      for (int b = lane; b < a.n_beams; b += 32)
+      {
+        const double2 v = __ldg(&a.beams[b]);
+        const double gx = fma(p.x, v.x, fma(-p.y, v.y, p.z));
+        const double gy = fma(p.y, v.x, fma(p.x, v.y, p.w));
+        const int ix = floor_to_int(gx), iy = floor_to_int(gy);
+        if (((unsigned)ix < (unsigned)a.size_x) && ((unsigned)iy < (unsigned)a.size_y))
+        {
+          const unsigned k = __ldg(&a.kmap[tiled_offset(ix, iy, a.tiles_x, layout)]);
+          if (k != k_off && agree[k])
+            atomicAdd(&s_cnt[b], 1);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < a.n_beams; b += blockDim.x)
+    if (s_cnt[b])
+      atomicAdd(&counts[b], s_cnt[b]);
+}
 }  // namespace
 
 // =============================================================================================
@@ -326,8 +385,6 @@ int stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, 
   else if (step < 1)
     step = 1;
   sc.step = step;
-  if (type == BAMCL_PLANAR_LF_PROB && model->do_beamskip)
-    return set_error(BAMCL_E_UNSUPPORTED, "likelihood_field_prob with beam skipping is not implemented on the device yet");
 
   if (type == BAMCL_PLANAR_BEAM)
   {
@@ -344,8 +401,9 @@ int stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, 
   const size_t max_beams = (size_t)(range_count / step + 2);
   BAMCL_TRY(pf->h_stage.reserve(sizeof(double) * 2 * max_beams + sizeof(double) * 100000));
   double* hb = pf->h_stage.as<double>();
-  int nb = 0;
-  for (int i = 0; i < range_count; i += step)
+  int nb = 0, slot = 0;
+  sc.beam_slot.clear();
+  for (int i = 0; i < range_count; i += step, slot++)
   {
     const double obs_range = ranges[i], obs_bearing = angles[i];
     if (obs_range >= range_max)
@@ -354,9 +412,12 @@ int stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, 
       continue;
     hb[2 * nb] = obs_range * std::cos(obs_bearing) / map->resolution;
     hb[2 * nb + 1] = obs_range * std::sin(obs_bearing) / map->resolution;
+    sc.beam_slot.push_back(slot);
     nb++;
   }
   sc.n_beams = nb;
+  sc.n_slots = slot;
+  sc.h_beams.assign(hb, hb + 2 * nb);
   // value table over the rank of k = squared cell distance (map2d.cuh); [n_rep] = in-map cell beyond the
   // radius; [n_rep + 1] = off the map
   const int n_rep = (int)map->rep_k.size();
@@ -405,6 +466,17 @@ int stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, 
   if (nb > 0)
     BAMCL_CUDA_OK(cudaMemcpyAsync(sc.beams.p, hb, sizeof(double) * 2 * nb, cudaMemcpyHostToDevice, ctx->stream));
   BAMCL_CUDA_OK(cudaMemcpyAsync(sc.table.p, ht, sizeof(double) * tn, cudaMemcpyHostToDevice, ctx->stream));
+  if (type == BAMCL_PLANAR_LF_PROB && model->do_beamskip)
+  {
+    // :448-451: an in-map beam agrees with the map when its cached distance is below beam_skip_distance
+    unsigned char* ha = reinterpret_cast<unsigned char*>(ht + tn) + sizeof(int) * (size_t)tn;
+    for (int r = 0; r < n_rep; r++)
+      ha[r] = (double)(float)(std::sqrt((double)map->rep_k[r]) * map->resolution) < model->beam_skip_distance ? 1 : 0;
+    ha[n_rep] = (double)(float)map->max_distance < model->beam_skip_distance ? 1 : 0;
+    ha[n_rep + 1] = 0;  // off the map: never counted
+    BAMCL_TRY(sc.agree.reserve((size_t)tn));
+    BAMCL_CUDA_OK(cudaMemcpyAsync(sc.agree.p, ha, (size_t)tn, cudaMemcpyHostToDevice, ctx->stream));
+  }
   // the pinned staging buffer is reused by the next call: wait for the copies
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
   sc.valid = true;
@@ -462,6 +534,87 @@ int launch_score(bamcl_pf* pf, bamcl_map2d* map)
   a.off_map_factor = sc.model.off_map_factor;
   a.non_free_space_factor = sc.model.non_free_space_factor;
   a.non_free_space_radius = sc.model.non_free_space_radius;
+
+  // ---- beam skipping (planar_scanner.cpp:361-395, 480-529): only for a converged set
+  if (sc.model.model_type == BAMCL_PLANAR_LF_PROB && sc.model.do_beamskip && pf->set_converged)
+  {
+    if (pf->win_cnt >= 0)
+      return set_error(BAMCL_E_UNSUPPORTED, "beam skipping on a sharded filter needs an all-reduce of the agreement counts");
+    const int max_beams = sc.model.max_beams, P = a.n, nb = sc.n_beams;
+    // clearTempData bookkeeping (:378-394, :684-690); temp_obs_ itself is never stored: its entries are recomputed
+    if (pf->skip_max_obs < max_beams || pf->skip_max_samples < P)
+    {
+      pf->skip_max_obs = max_beams;
+      pf->skip_max_samples = std::max(pf->skip_max_samples, P);
+      pf->skip_written.assign((size_t)max_beams, 0);
+    }
+    std::vector<int> counts((size_t)std::max(nb, 1), 0);
+    if (nb > 0)
+    {
+      BAMCL_TRY(sc.skip_count.reserve(sizeof(int) * (size_t)nb));
+      BAMCL_CUDA_OK(cudaMemsetAsync(sc.skip_count.p, 0, sizeof(int) * (size_t)nb, ctx->stream));
+      const int cblocks = std::max(1, std::min(kNumSMs * 4, (P + 255) / 256));
+      BAMCL_LAUNCH(ctx, k_skip_count, cblocks, 256, sizeof(int) * (size_t)nb, a, sc.agree.as<unsigned char>(),
+                   sc.skip_count.as<int>(), map->layout);
+      BAMCL_CUDA_OK(cudaMemcpyAsync(counts.data(), sc.skip_count.p, sizeof(int) * (size_t)nb, cudaMemcpyDeviceToHost,
+                                    ctx->stream));
+      BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    }
+    std::vector<int> obs_count((size_t)max_beams, 0);
+    std::vector<char> now((size_t)max_beams, 0);
+    for (int b = 0; b < nb; b++)
+    {
+      obs_count[sc.beam_slot[b]] = counts[b];
+      now[sc.beam_slot[b]] = 1;
+      pf->skip_written[sc.beam_slot[b]] = std::max(pf->skip_written[sc.beam_slot[b]], P);
+    }
+    int skipped = 0;
+    std::vector<char> mask((size_t)max_beams, 0);
+    for (int s = 0; s < max_beams; s++)  // :483-494
+    {
+      if ((obs_count[s] / static_cast<double>(P)) > sc.model.beam_skip_threshold)
+        mask[s] = 1;
+      else
+        skipped++;
+    }
+    const bool error = skipped >= (max_beams * sc.model.beam_skip_error_threshold);  // :502-510
+    bool zero_all = false;
+    if (error)
+    {
+      // every slot 0..max_beams-1 is integrated (:519-525). A slot this scan did not write still holds what an earlier
+      // scan left there: 0.0 if nothing ever did (log 0 = -inf: every weight becomes 0), else that scan's value.
+      for (int s = 0; s < max_beams; s++)
+        if (!now[s])
+        {
+          if (pf->skip_written[s] == 0)
+            zero_all = true;
+          else
+            return set_error(BAMCL_E_UNSUPPORTED,
+                             "beam skipping: the reference would integrate slot %d's stale temp_obs_ entry of an earlier "
+                             "scan (SURVEY Q12); the device recomputes entries and does not keep old scans", s);
+        }
+    }
+    if (zero_all)
+    {
+      BAMCL_CUDA_OK(cudaMemsetAsync(a.w, 0, sizeof(double) * (size_t)P, ctx->stream));  // w *= exp(-inf)
+      return BAMCL_OK;
+    }
+    // the beams that are integrated, in slot order
+    std::vector<double> sel;
+    sel.reserve(2 * (size_t)nb);
+    for (int b = 0; b < nb; b++)
+      if (error || mask[sc.beam_slot[b]])
+      {
+        sel.push_back(sc.h_beams[2 * b]);
+        sel.push_back(sc.h_beams[2 * b + 1]);
+      }
+    const int n_sel = (int)(sel.size() / 2);
+    BAMCL_TRY(sc.beams_sel.reserve(sizeof(double) * 2 * (size_t)(n_sel + 1)));
+    if (n_sel > 0)
+      BAMCL_CUDA_OK(cudaMemcpy(sc.beams_sel.p, sel.data(), sizeof(double) * 2 * (size_t)n_sel, cudaMemcpyHostToDevice));
+    a.beams = sc.beams_sel.as<double2>();
+    a.n_beams = n_sel;
+  }
 
   const int n_batches = (a.n + PB - 1) / PB;
   int blocks = (n_batches + WARPS - 1) / WARPS;

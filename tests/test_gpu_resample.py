@@ -217,3 +217,57 @@ def test_kdtree_leaf_count_large_top_tree(env):
     assert (r.leaf_count, r.node_count) == (port.leaf_count(), port.node_count())
     assert r.cluster_count == port.cluster_count()
     pf.close()
+
+
+@pytest.mark.parametrize("n,n_min,cloud", [(3000, 100, "global"), (3000, 100, "tracking"), (20000, 500, "global"),
+                                           (20000, 50, "tracking"), (1, 1, "tracking"), (2, 1, "global")])
+def test_multinomial_resample_matches_oracle(env, n, n_min, cloud):
+    """resampleMultinomial (particle_filter.cpp:356-420) with w_diff = 0: two draws per output, stop as soon as the
+    count exceeds resampleLimit(leaf count so far); indices, count, tree and the advanced drand48 state"""
+    O, cabi = env["O"], env["cabi"]
+    cells, truth = env["cells"], env["truth"]
+    poses = (synth.uniform_free_poses(cells, RES, n, seed=1) if cloud == "global"
+             else synth.gaussian_poses(truth, n, seed=2, sigma_xy=0.3))
+    rng = np.random.default_rng(n + n_min)
+    port = O.PortPF(n_min, n, systematic=False)
+    port.init_with_poses(poses)
+    port.srand48(31)
+    pf = cabi.ParticleFilter(env["ctx"], n_min, n, systematic=False)
+    pf.init_with_poses(poses)
+    pf.srand48(31)
+    for _ in range(2):
+        m = port.sample_count()
+        w = np.exp(rng.normal(0.0, 1.0, m))
+        w /= w.sum()
+        s = port.samples()
+        s[:, 3] = w
+        port.set_samples(s)
+        port.set_averages(1.0, 1.0)
+        pf.upload_weights(w)
+        pf.w_slow = pf.w_fast = 1.0
+        port.update_resample()
+        r = pf.update_resample()
+        _assert_same_resample(pf, port, r)
+    # both generators consumed the same number of draws: the next systematic start agrees
+    port.L.orc_pf_set_resample_model(port.h, 1)
+    pf.systematic = True
+    s = port.samples()
+    pf.w_slow = pf.w_fast = 1.0
+    port.set_averages(1.0, 1.0)
+    port.update_resample()
+    r = pf.update_resample()
+    assert np.array_equal(pf.resample_sources(), port.resample_sources())
+    pf.close()
+
+
+def test_multinomial_with_random_injection_is_refused(env):
+    cabi = env["cabi"]
+    n = 1000
+    poses = synth.gaussian_poses(env["truth"], n, seed=2)
+    pf = cabi.ParticleFilter(env["ctx"], 100, n, systematic=False)
+    pf.init_with_poses(poses)
+    pf.w_slow, pf.w_fast = 0.010, 0.007
+    pf.set_random_poses(poses)
+    with pytest.raises(cabi.BamclError):
+        pf.update_resample()
+    pf.close()

@@ -140,3 +140,79 @@ def test_scoring_needs_a_distance_cache(env):
         pf.score_planar(m, cabi.planar_model(), np.ones(60), np.linspace(-1, 1, 60), 30.0)
     pf.close()
     m.close()
+
+
+# ---- likelihood_field_prob with beam skipping (planar_scanner.cpp:361-529)
+def _skip_case(env, n, n_beams, cloud, dropouts=0.0, blockers=0):
+    ranges, angles = synth.make_scan(env["cells"], RES, env["truth"], n_beams=n_beams, dropouts=dropouts)
+    rng = np.random.default_rng(n_beams + blockers)
+    for i in rng.choice(n_beams, blockers, replace=False):  # "a person in front of the robot": shortened readings
+        ranges[i] = min(ranges[i], 29.0) * 0.45
+    poses = (synth.gaussian_poses(env["truth"], n, seed=3, sigma_xy=0.05, sigma_th=0.01) if cloud == "tracking"
+             else synth.uniform_free_poses(env["cells"], RES, n, seed=3))
+    w = np.random.default_rng(1).uniform(0.5, 1.5, n) / n
+    return ranges, angles, np.concatenate([poses, w[:, None]], axis=1)
+
+
+SKIP_KW = dict(model_type=2, do_beamskip=True, beam_skip_distance=0.5, beam_skip_threshold=0.3,
+               beam_skip_error_threshold=0.9, scanner_pose=(0.1, 0.0, 0.0))
+
+
+@pytest.mark.parametrize("case", ["mask", "mask_dropouts", "error_all_beams", "not_converged", "subsampled"])
+def test_beam_skipping_matches_oracle(env, case):
+    O, cabi = env["O"], env["cabi"]
+    n, n_beams = 3000, 180
+    kw = dict(SKIP_KW, max_beams=n_beams)
+    cloud, dropouts, blockers, converged = "tracking", 0.0, 25, 1
+    if case == "mask_dropouts":
+        dropouts = 0.05
+    if case == "error_all_beams":
+        # no beam reaches the agreement threshold: every beam is skipped -> all are integrated (:502-510)
+        cloud, blockers, kw["beam_skip_threshold"] = "global", 0, 0.995
+    if case == "not_converged":
+        converged = 0
+    if case == "subsampled":
+        kw["max_beams"] = 60
+    ranges, angles, samples = _skip_case(env, n, n_beams, cloud, dropouts, blockers)
+    st = O.port_lib().orc_planar_state_create()
+    pf = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    pf.set_exact_terms(True)
+    for rep in range(2):  # the second call runs with temp_obs_ already allocated
+        want_total, want_w = env["pm"].apply(O.planar_model(**kw), ranges, angles, 30.0, samples, converged=converged,
+                                             state=st)
+        pf.upload_samples(samples)
+        pf.converged = bool(converged)
+        got_total = pf.score_planar(env["m"], cabi.planar_model(**kw), ranges, angles, 30.0)
+        assert_weights_close(pf.weights(), want_w, rtol=1e-9)
+        assert abs(got_total - want_total) <= 1e-12 * abs(want_total)
+    if case in ("mask", "mask_dropouts", "subsampled"):
+        # the mask really dropped beams: the same scan without skipping weighs differently
+        plain_total, _ = env["pm"].apply(O.planar_model(**dict(kw, do_beamskip=False)), ranges, angles, 30.0, samples)
+        assert plain_total != want_total
+    O.port_lib().orc_planar_state_destroy(st)
+    pf.close()
+
+
+def test_beam_skipping_never_written_slots_zero_every_weight(env):
+    """in the integrate-everything case a slot no scan ever wrote holds 0.0 -> log 0 -> weight 0 -> total 0"""
+    O, cabi = env["O"], env["cabi"]
+    n, n_beams = 2000, 120
+    kw = dict(SKIP_KW, max_beams=n_beams, beam_skip_threshold=0.995)
+    ranges, angles, samples = _skip_case(env, n, n_beams, "global", dropouts=0.1)
+    st = O.port_lib().orc_planar_state_create()
+    want_total, want_w = env["pm"].apply(O.planar_model(**kw), ranges, angles, 30.0, samples, converged=1, state=st)
+    O.port_lib().orc_planar_state_destroy(st)
+    assert want_total == 0.0 and not want_w.any()
+    pf = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    pf.upload_samples(samples)
+    pf.converged = True
+    assert pf.score_planar(env["m"], cabi.planar_model(**kw), ranges, angles, 30.0) == 0.0
+    assert not pf.weights().any()
+    # a second scan that would integrate the first scan's stale entries is refused, not approximated
+    ranges2, angles2, _ = _skip_case(env, n, n_beams, "global", dropouts=0.0)
+    pf.upload_samples(samples)
+    pf.score_planar(env["m"], cabi.planar_model(**kw), ranges2, angles2, 30.0)  # writes every slot
+    pf.upload_samples(samples)
+    with pytest.raises(cabi.BamclError):
+        pf.score_planar(env["m"], cabi.planar_model(**kw), ranges, angles, 30.0)
+    pf.close()

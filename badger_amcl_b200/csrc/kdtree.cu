@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(256) k_flag_first(const int* __restrict__ slot
 __global__ void __launch_bounds__(256) k_make_nodes(const int* __restrict__ slot, const int* __restrict__ hfirst,
                                                     const int* __restrict__ rank, const unsigned long long* __restrict__ hkeys,
                                                     int* __restrict__ hnode, unsigned long long* __restrict__ nkey,
-                                                    int* __restrict__ nfirst, int n)
+                                                    int* __restrict__ nfirst, int* __restrict__ parent, int n)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n)
@@ -125,6 +125,7 @@ __global__ void __launch_bounds__(256) k_make_nodes(const int* __restrict__ slot
   nkey[id] = hkeys[s];
   nfirst[id] = i;
   hnode[s] = id;
+  parent[id] = id;  // union-find forest of the clustering step: every node its own root
 }
 
 // ---- 2. the tree, one level per step
@@ -136,7 +137,6 @@ struct TreeArgs
   int* child;     // [2 * K]
   int* first_at;  // smallest id among the keys that reached a node = its first foreign key
   signed char* side;
-  int* parent;  // union-find forest for the clustering step, initialised here
 };
 
 #include "tree_fast.cuh"
@@ -154,7 +154,6 @@ __global__ void __launch_bounds__(256) k_tree_build(const TreeArgs a)
     a.child[2 * v] = a.child[2 * v + 1] = NONE;
     a.first_at[v] = (v == 0 && K > 1) ? 1 : NONE;
     a.cur[v] = v == 0 ? -1 : 0;
-    a.parent[v] = v;
   }
   grid.sync();
   int level = 0;
@@ -224,13 +223,23 @@ __global__ void __launch_bounds__(256) k_tree_build(const TreeArgs a)
 }
 
 // ---- 3. connected components (pf_kdtree.cpp:58-76, 169-194)
+// CA = read the forest through L1 (ld.global.ca). A stale entry is an older parent pointer, which is still an ancestor
+// (roots only ever get hooked under smaller ids, compression only skips ancestors), and every hook is decided by an
+// atomicCAS on the true value, so staleness costs at most a retry; it spreads the reads of a large component's root
+// over the SMs' L1s instead of one L2 slice.
+template <bool CA>
+__device__ __forceinline__ int uf_load(const int* p)
+{
+  return CA ? __ldca(p) : *((const volatile int*)p);
+}
+template <bool CA>
 __device__ __forceinline__ int uf_find(int* parent, int v)
 {
-  int cur = *((volatile int*)&parent[v]);
+  int cur = uf_load<CA>(&parent[v]);
   if (cur != v)
   {
     int prev = v, next;
-    while (cur > (next = *((volatile int*)&parent[cur])))
+    while (cur > (next = uf_load<CA>(&parent[cur])))
     {
       parent[prev] = next;
       prev = cur;
@@ -239,9 +248,10 @@ __device__ __forceinline__ int uf_find(int* parent, int v)
   }
   return cur;
 }
+template <bool CA>
 __device__ __forceinline__ void uf_union(int* parent, int a, int b)
 {
-  int ra = uf_find(parent, a), rb = uf_find(parent, b);
+  int ra = uf_find<CA>(parent, a), rb = uf_find<CA>(parent, b);
   bool repeat;
   do
   {
@@ -269,6 +279,7 @@ __device__ __forceinline__ void uf_union(int* parent, int a, int b)
   } while (repeat);
 }
 
+template <bool CA>
 __global__ void __launch_bounds__(256) k_cc_union(const TreeOut* __restrict__ out, const unsigned long long* __restrict__ nkey,
                                                   const unsigned long long* __restrict__ hkeys, const int* __restrict__ hnode,
                                                   unsigned hmask, int* parent, int n_max)
@@ -297,7 +308,7 @@ __global__ void __launch_bounds__(256) k_cc_union(const TreeOut* __restrict__ ou
       break;
     s = (s + 1) & hmask;
   }
-  uf_union(parent, v, hnode[s]);
+  uf_union<CA>(parent, v, hnode[s]);
 }
 
 // Read-only find: a compressing find here would race with other threads' finds (a stale intermediate ancestor
@@ -559,7 +570,6 @@ int launch_fast_tree(bamcl_pf* pf, TreeOut* out, int n)
   fa.bslot = pf->t_cur.as<int>();
   fa.bpos = pf->t_first_at.as<int>();
   fa.bids = pf->t_child.as<int>();
-  fa.parent = pf->t_parent.as<int>();
   const int per = 28;  // bytes of shared memory per key in k_fast_top / k_fast_bucket
   static bool attr_done = false;
   if (!attr_done)
@@ -637,6 +647,13 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
   BAMCL_TRY(pf->t_fast.reserve(sizeof(int) * (3 * M_TOP_LARGE + 2 * (2 * M_TOP_LARGE + 1))));
   BAMCL_TRY(pf->t_out.reserve(sizeof(TreeOut)));
   BAMCL_TRY(pf->t_hout.reserve(sizeof(TreeOut)));
+  BAMCL_TRY(pf->t_root.reserve(sizeof(int) * cap_n));
+  if (!pf->aux_stream)
+  {
+    BAMCL_CUDA_OK(cudaStreamCreateWithFlags(&pf->aux_stream, cudaStreamNonBlocking));
+    BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_fork, cudaEventDisableTiming));
+    BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_join, cudaEventDisableTiming));
+  }
   if (pf->t_cluster_cap == 0)
     pf->t_cluster_cap = 4096;
   TreeOut* out = pf->t_out.as<TreeOut>();
@@ -659,37 +676,34 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
     BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_flag.as<int>(), pf->t_flag.as<int>(), n, pf->t_scan.as<int>(), &out->K));
     BAMCL_LAUNCH(ctx, k_make_nodes, blocks_n, 256, 0, pf->t_slot.as<int>(), pf->t_hfirst.as<int>(), pf->t_flag.as<int>(),
                  pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), pf->t_nkey.as<unsigned long long>(),
-                 pf->t_nfirst.as<int>(), n);
+                 pf->t_nfirst.as<int>(), pf->t_parent.as<int>(), n);
     static const bool force_general = getenv("BAMCL_TREE_GENERAL") != nullptr;  // tests: exercise k_tree_build
-    if (!force_general && !pf->force_general_tree)
+    const bool general_only = force_general || pf->force_general_tree;
+    // ---- fork: the cluster chain (needs only the nodes and the hash) goes to the auxiliary stream and overlaps the
+    // leaf-count chain on the main stream; both join before the result is copied back
+    cudaStream_t main_stream = ctx->stream;
+    BAMCL_CUDA_OK(cudaEventRecord(pf->ev_fork, main_stream));
+    BAMCL_CUDA_OK(cudaStreamWaitEvent(pf->aux_stream, pf->ev_fork, 0));
     {
-      if (n > 1500000)
-        BAMCL_TRY((launch_fast_tree<M_TOP_LARGE>(pf, out, n)));
-      else
-        BAMCL_TRY((launch_fast_tree<M_TOP_SMALL>(pf, out, n)));
-    }
-    {
-      TreeArgs ta;
-      ta.out = out;
-      ta.nkey = pf->t_nkey.as<unsigned long long>();
-      ta.cur = pf->t_cur.as<int>();
-      ta.child = pf->t_child.as<int>();
-      ta.first_at = pf->t_first_at.as<int>();
-      ta.side = pf->t_side.as<signed char>();
-      ta.parent = pf->t_parent.as<int>();
-      int blocks = std::min(coop_blocks_for(pf), std::max(1, (n + 511) / 512));
-      void* args[] = {&ta};
-      BAMCL_CUDA_OK(cudaLaunchCooperativeKernel((void*)k_tree_build, dim3(blocks), dim3(256), args, 0, ctx->stream));
-      ctx->launches++;
-    }
-    {
+      struct StreamSwap  // BAMCL_LAUNCH and the scan use ctx->stream; restored on every exit path
+      {
+        bamcl_ctx* c;
+        cudaStream_t keep;
+        ~StreamSwap() { c->stream = keep; }
+      } swap{ctx, main_stream};
+      ctx->stream = pf->aux_stream;
       const long threads = (long)n * 13;
-      BAMCL_LAUNCH(ctx, k_cc_union, (unsigned)((threads + 255) / 256), 256, 0, out, pf->t_nkey.as<unsigned long long>(),
-                   pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), hmask, pf->t_parent.as<int>(), n);
-    }
-    BAMCL_LAUNCH(ctx, k_cc_roots, blocks_n, 256, 0, out, pf->t_parent.as<int>(), pf->t_cur.as<int>(), pf->t_cid.as<int>(), n);
-    BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_cid.as<int>(), pf->t_cid.as<int>(), n, pf->t_scan.as<int>(), &out->C));
-    {
+      static const bool cc_volatile = getenv("BAMCL_CC_VOLATILE") != nullptr;  // A/B switch: forest reads bypass L1
+      if (cc_volatile)
+        BAMCL_LAUNCH(ctx, k_cc_union<false>, (unsigned)((threads + 255) / 256), 256, 0, out,
+                     pf->t_nkey.as<unsigned long long>(), pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), hmask,
+                     pf->t_parent.as<int>(), n);
+      else
+        BAMCL_LAUNCH(ctx, k_cc_union<true>, (unsigned)((threads + 255) / 256), 256, 0, out,
+                     pf->t_nkey.as<unsigned long long>(), pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), hmask,
+                     pf->t_parent.as<int>(), n);
+      BAMCL_LAUNCH(ctx, k_cc_roots, blocks_n, 256, 0, out, pf->t_parent.as<int>(), pf->t_root.as<int>(), pf->t_cid.as<int>(), n);
+      BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_cid.as<int>(), pf->t_cid.as<int>(), n, pf->t_scan.as<int>(), &out->C));
       StatsArgs sa;
       sa.x = set.x.as<double>();
       sa.y = set.y.as<double>();
@@ -698,7 +712,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       sa.n = n;
       sa.slot = pf->t_slot.as<int>();
       sa.hnode = pf->t_hnode.as<int>();
-      sa.parent = pf->t_cur.as<int>();  // final roots (k_cc_roots)
+      sa.parent = pf->t_root.as<int>();  // final roots (k_cc_roots)
       sa.cid = pf->t_cid.as<int>();
       sa.label = set.label.as<int>();
       sa.rows = pf->t_sums.as<double>();
@@ -706,11 +720,46 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       sa.out = out;
       const int per_block = ST_BLOCK * ST_CHUNKS;
       BAMCL_LAUNCH(ctx, k_labels_stats, (n + per_block - 1) / per_block, ST_BLOCK, 0, sa);
+      BAMCL_LAUNCH(ctx, k_converged_count, std::min(blocks_n, kNumSMs * 8), 256, 0, set.x.as<double>(), set.y.as<double>(), n,
+                   dist_threshold, out);
+      BAMCL_LAUNCH(ctx, k_cluster_finalize, (unsigned)((pf->t_cluster_cap + 255) / 256), 256, 0, out, pf->t_sums.as<double>(),
+                   (int)pf->t_cluster_cap, set.cluster_stats.as<double>());
+      BAMCL_CUDA_OK(cudaEventRecord(pf->ev_join, pf->aux_stream));
     }
-    BAMCL_LAUNCH(ctx, k_converged_count, std::min(blocks_n, kNumSMs * 8), 256, 0, set.x.as<double>(), set.y.as<double>(), n,
-                 dist_threshold, out);
-    BAMCL_LAUNCH(ctx, k_cluster_finalize, (unsigned)((pf->t_cluster_cap + 255) / 256), 256, 0, out, pf->t_sums.as<double>(),
-                 (int)pf->t_cluster_cap, set.cluster_stats.as<double>());
+    // ---- main stream: the leaf count
+    auto launch_general = [&]() -> int {
+      TreeArgs ta;
+      ta.out = out;
+      ta.nkey = pf->t_nkey.as<unsigned long long>();
+      ta.cur = pf->t_cur.as<int>();
+      ta.child = pf->t_child.as<int>();
+      ta.first_at = pf->t_first_at.as<int>();
+      ta.side = pf->t_side.as<signed char>();
+      int blocks = std::min(coop_blocks_for(pf), std::max(1, (n + 511) / 512));
+      void* args[] = {&ta};
+      BAMCL_CUDA_OK(cudaLaunchCooperativeKernel((void*)k_tree_build, dim3(blocks), dim3(256), args, 0, ctx->stream));
+      ctx->launches++;
+      return BAMCL_OK;
+    };
+    if (!general_only)
+    {
+      if (n > 1500000)
+        BAMCL_TRY((launch_fast_tree<M_TOP_LARGE>(pf, out, n)));
+      else
+        BAMCL_TRY((launch_fast_tree<M_TOP_SMALL>(pf, out, n)));
+    }
+    else
+      BAMCL_TRY(launch_general());
+    BAMCL_CUDA_OK(cudaStreamWaitEvent(main_stream, pf->ev_join, 0));
+    BAMCL_CUDA_OK(cudaMemcpyAsync(h_out, out, sizeof(TreeOut), cudaMemcpyDeviceToHost, ctx->stream));
+    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    if (!general_only && !h_out->fast_ok)
+    {
+      // a bucket outgrew shared memory (adversarial insertion order): the grid-synchronous build takes over
+      BAMCL_TRY(launch_general());
+      BAMCL_CUDA_OK(cudaMemcpyAsync(h_out, out, sizeof(TreeOut), cudaMemcpyDeviceToHost, ctx->stream));
+      BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    }
     BAMCL_CUDA_OK(cudaMemcpyAsync(h_out, out, sizeof(TreeOut), cudaMemcpyDeviceToHost, ctx->stream));
     BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     if (h_out->err & 1)

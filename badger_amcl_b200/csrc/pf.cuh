@@ -81,7 +81,10 @@ struct bamcl_pf
   bamcl::DevBuf t_hkeys, t_hfirst, t_hnode;                 // hash table over pose bins
   bamcl::DevBuf t_slot, t_flag;                             // per sample
   bamcl::DevBuf t_nkey, t_cur, t_child, t_first_at, t_side; // per node (creation order)
-  bamcl::DevBuf t_parent, t_cid, t_nfirst;
+  bamcl::DevBuf t_parent, t_cid, t_nfirst, t_root;
+  // the cluster chain (union-find, labels, statistics) runs on this stream next to the leaf-count chain
+  cudaStream_t aux_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bamcl::DevBuf t_scan, t_out, t_sums, t_fast;
   int tree_fast = 0;        // the last tree build used the bucketed shared-memory path
   bamcl::PinBuf t_hout;

@@ -108,7 +108,6 @@ struct FastArgs
   int* bslot;                      // [K] bucket of every key >= m
   int* bpos;                       // [K] arrival position inside the bucket
   int* bids;                       // [K] keys grouped by bucket
-  int* parent;                     // union-find forest for the clustering step, initialised here
 };
 
 // ---- 1. top tree (one CTA)
@@ -157,8 +156,6 @@ __global__ void __launch_bounds__(256) k_fast_descend(const FastArgs a)
   signed char* s_pivot = reinterpret_cast<signed char*>(s_child + 2 * M_TOP);
   const int K = a.out->K;
   const int m = min(K, M_TOP);
-  for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < K; v += gridDim.x * blockDim.x)
-    a.parent[v] = v;
   if (K <= M_TOP)
     return;
   for (int v = threadIdx.x; v < m; v += blockDim.x)

@@ -69,7 +69,8 @@ def _run_sharded(env, world, poses, weights_per_step, seed, n_min):
     n = len(poses)
 
     def rank_fn(rank, dist):
-        pf = cabi.ParticleFilter(env["ctx"], n_min, n)
+        ctx = cabi.Context(0)  # one context (stream) per rank, as in the one-process-per-GPU deployment
+        pf = cabi.ParticleFilter(ctx, n_min, n)
         pf.init_with_poses(poses)
         eng = sharded.CudaEngine(pf, env["map"], 0)
         eng.want_sources()
@@ -89,6 +90,7 @@ def _run_sharded(env, world, poses, weights_per_step, seed, n_min):
                             labels=pf.sample_clusters(), stats=np.array(list(res.mean) + list(res.cov)),
                             runs=list(f.last_plan)))
         pf.close()
+        ctx.close()
         return out
 
     return run_ranks(world, rank_fn)
@@ -153,7 +155,8 @@ def test_sharded_update_matches_the_unsharded_device_filter(env):
     one.close()
 
     def rank_fn(rank, dist):
-        pf = cabi.ParticleFilter(env["ctx"], n // 10, n)
+        ctx = cabi.Context(0)
+        pf = cabi.ParticleFilter(ctx, n // 10, n)
         pf.init_with_poses(poses)
         pf.stage_scan(env["map"], model, ranges, angles, 30.0)
         f = sharded.ShardedFilter(sharded.CudaEngine(pf, env["map"], 0), rank, world, dist, n // 10, n)
@@ -161,6 +164,7 @@ def test_sharded_update_matches_the_unsharded_device_filter(env):
         off, cnt = f.window()
         w = pf.weights()[off:off + cnt]
         pf.close()
+        ctx.close()
         return total, off, cnt, w
 
     got = run_ranks(world, rank_fn)

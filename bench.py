@@ -189,7 +189,7 @@ def run_reference_arm(a):
                              "host_cores_available": os.cpu_count()},
             "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -378,14 +378,27 @@ def run_b200_arm(a):
                                 "sample": "first %d of %d particles x %d beams: update %.1f ms + resample %.1f ms, 1 thread"
                                           % (n_cpu, P, B, cu * 1e3, cr * 1e3),
                                 "host_cores_available": os.cpu_count()}
-    print(json.dumps(line))
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
     return 0
 
 
+def emit(line):
+    """the ONE JSON line goes to the real stdout; everything else this process (or NCCL) prints went to stderr"""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
     a = parse_args()
+    # NCCL and friends write banners to fd 1 ("NCCL version ..."): keep stdout for the JSON line only
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         return run_reference_arm(a)
     return run_b200_arm(a)

@@ -131,6 +131,8 @@ SIGNATURES = {
     "bamcl_pf_stage_scan": (_I, [_P, _P, _P, _P, _P, _I, _D]),
     "bamcl_pf_update_planar_staged": (_I, [_P, _P, _I, _P]),
     "bamcl_pf_score_planar_staged": (_I, [_P, _P, _I, _P]),
+    "bamcl_pf_update_planar_host": (_I, [_P, _P, _P, _P, _P, _I, _D, _I, _P, _L, _P]),
+    "bamcl_pf_resample_host": (_I, [_P, _P, _P, _P, _L]),
     "bamcl_pf_cdf": (_I, [_P, _P, _L]),
     "bamcl_pf_resample": (_I, [_P, _P, _P]),
     "bamcl_pf_init_stats": (_I, [_P, _P]),
@@ -423,6 +425,21 @@ class ParticleFilter:
         self.last_total = total.value
         return True
 
+    def update_sensor_host(self, map2d, model, ranges, angles, range_max, aos):
+        """updateSensor with the particles still in host memory (n x 4 AoS, ideally a pinned_array): the upload is
+        pipelined with the scoring (bamcl_pf_update_planar_host)."""
+        if model.max_beams < 2:
+            return False
+        ranges = np.ascontiguousarray(ranges, np.float64)
+        angles = np.ascontiguousarray(angles, np.float64)
+        assert aos.dtype == np.float64 and aos.flags.c_contiguous and aos.ndim == 2 and aos.shape[1] == 4
+        total = C.c_double()
+        _check(self.L.bamcl_pf_update_planar_host(self.h, map2d.h, C.byref(model), _p(ranges), _p(angles), len(ranges),
+                                                  range_max, int(self.converged), _p(aos), len(aos), C.byref(total)))
+        self._averages(total.value)
+        self.last_total = total.value
+        return True
+
     def stage_scan(self, map2d, model, ranges, angles, range_max):
         ranges = np.ascontiguousarray(ranges, np.float64)
         angles = np.ascontiguousarray(angles, np.float64)
@@ -484,8 +501,9 @@ class ParticleFilter:
     def resample_limit(self, k):
         return self.L.bamcl_resample_limit(k, self.min_samples, self.max_samples, self.pop_err, self.pop_z)
 
-    def update_resample(self, w_diff=None):
-        """ParticleFilter::updateResample (particle_filter.cpp:423-471)."""
+    def update_resample(self, w_diff=None, out=None):
+        """ParticleFilter::updateResample (particle_filter.cpp:423-471). out = (cap x 4) float64 host buffer: the new
+        set is also copied there, overlapped with the tree / cluster build (bamcl_pf_resample_host)."""
         if w_diff is None:
             with np.errstate(divide="ignore", invalid="ignore"):
                 w_diff = float(1.0 - np.float64(self.w_fast) / np.float64(self.w_slow))
@@ -495,7 +513,11 @@ class ParticleFilter:
         prm = ResampleParams(int(self.systematic), self.min_samples, self.max_samples, self.pop_err, self.pop_z, w_diff,
                              0.5, self.conv_thresh, self.drand48_state, _p(rp) if len(rp) else None, len(rp))
         res = ResampleResult()
-        _check(self.L.bamcl_pf_resample(self.h, C.byref(prm), C.byref(res)))
+        if out is None:
+            _check(self.L.bamcl_pf_resample(self.h, C.byref(prm), C.byref(res)))
+        else:
+            assert out.dtype == np.float64 and out.flags.c_contiguous and out.ndim == 2 and out.shape[1] == 4
+            _check(self.L.bamcl_pf_resample_host(self.h, C.byref(prm), C.byref(res), _p(out), len(out)))
         self.drand48_state = res.drand48_state
         self.random_next += res.random_poses_used
         if w_diff > 0.0:

@@ -105,6 +105,43 @@ __global__ void k_normalise(double* __restrict__ w, int n, const double* __restr
 
 namespace bamcl
 {
+int pf_ensure_streams(bamcl_pf* pf)
+{
+  if (pf->aux_stream)
+    return BAMCL_OK;
+  BAMCL_CUDA_OK(cudaStreamCreateWithFlags(&pf->aux_stream, cudaStreamNonBlocking));
+  BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_fork, cudaEventDisableTiming));
+  BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_join, cudaEventDisableTiming));
+  BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_bucket_fork, cudaEventDisableTiming));
+  for (int i = 0; i < 2; i++)
+  {
+    BAMCL_CUDA_OK(cudaStreamCreateWithFlags(&pf->bucket_stream[i], cudaStreamNonBlocking));
+    BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_bucket_join[i], cudaEventDisableTiming));
+  }
+  BAMCL_CUDA_OK(cudaStreamCreateWithFlags(&pf->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 8; i++)
+    BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_copy[i], cudaEventDisableTiming));
+  return BAMCL_OK;
+}
+
+// current set -> host AoS, enqueued on the copy stream behind everything the main stream holds now; the caller
+// synchronises the copy stream before it lets the host read `aos`
+int pf_download_async(bamcl_pf* pf, double* aos, long n)
+{
+  BAMCL_TRY(pf_ensure_streams(pf));
+  SampleSet& s = pf->sets[pf->current];
+  BAMCL_TRY(pf->d_stage.reserve(sizeof(double) * 4 * (size_t)n));
+  BAMCL_CUDA_OK(cudaEventRecord(pf->ev_copy[0], pf->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamWaitEvent(pf->copy_stream, pf->ev_copy[0], 0));
+  k_soa_to_aos<<<(unsigned)((n + 255) / 256), 256, 0, pf->copy_stream>>>(pf->d_stage.as<double4>(), s.x.as<double>(),
+                                                                        s.y.as<double>(), s.th.as<double>(),
+                                                                        s.w.as<double>(), (int)n);
+  pf->ctx->launches++;
+  BAMCL_CUDA_OK(cudaGetLastError());
+  BAMCL_CUDA_OK(cudaMemcpyAsync(aos, pf->d_stage.p, sizeof(double) * 4 * (size_t)n, cudaMemcpyDeviceToHost, pf->copy_stream));
+  return BAMCL_OK;
+}
+
 int pf_reduce_total(bamcl_pf* pf, double* d_total)
 {
   SampleSet& set = pf->sets[pf->current];
@@ -223,6 +260,20 @@ int bamcl_pf_destroy(bamcl_pf* pf)
     cudaEventDestroy(pf->ev_fork);
   if (pf->ev_join)
     cudaEventDestroy(pf->ev_join);
+  for (int i = 0; i < 2; i++)
+  {
+    if (pf->bucket_stream[i])
+      cudaStreamDestroy(pf->bucket_stream[i]);
+    if (pf->ev_bucket_join[i])
+      cudaEventDestroy(pf->ev_bucket_join[i]);
+  }
+  if (pf->ev_bucket_fork)
+    cudaEventDestroy(pf->ev_bucket_fork);
+  if (pf->copy_stream)
+    cudaStreamDestroy(pf->copy_stream);
+  for (int i = 0; i < 8; i++)
+    if (pf->ev_copy[i])
+      cudaEventDestroy(pf->ev_copy[i]);
   if (pf->score_ev0)
     cudaEventDestroy(pf->score_ev0);
   if (pf->score_ev1)
@@ -421,6 +472,56 @@ int bamcl_pf_score_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, 
   BAMCL_TRY(launch_score(pf, map));
   BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
   return read_scalar(pf, 0, total_out);
+}
+
+int bamcl_pf_update_planar_host(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
+                                const double* angles, int range_count, double range_max, int converged, const double* aos,
+                                long n, double* total_out)
+{
+  if (!pf || !aos || n < 0 || n > pf->max_samples)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_update_planar_host: need 0 <= n <= max_samples");
+  const bool skip = model && model->model_type == BAMCL_PLANAR_LF_PROB && model->do_beamskip && converged;
+  constexpr int CHUNKS = 4;
+  if (n < 4 * 65536 || skip || (model && model->model_type == BAMCL_PLANAR_BEAM) || (model && model->max_beams < 2))
+  {
+    // small sets, and models that look at the whole set before weighting it: upload, then update
+    BAMCL_TRY(bamcl_pf_upload_samples(pf, aos, n));
+    return bamcl_pf_update_planar(pf, map, model, ranges, angles, range_count, range_max, converged, total_out);
+  }
+  BAMCL_TRY(stage_scan(pf, map, model, ranges, angles, range_count, range_max));
+  BAMCL_TRY(pf_ensure_streams(pf));
+  pf->set_converged = converged;
+  bamcl_ctx* ctx = pf->ctx;
+  SampleSet& s = pf->sets[pf->current];
+  s.sample_count = (int)n;
+  BAMCL_TRY(pf->d_stage.reserve(sizeof(double) * 4 * (size_t)n));
+  // the copy stream may only overwrite the staging buffer after the main stream's earlier readers are done
+  BAMCL_CUDA_OK(cudaEventRecord(pf->ev_copy[CHUNKS], ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamWaitEvent(pf->copy_stream, pf->ev_copy[CHUNKS], 0));
+  int rc = BAMCL_OK;
+  for (int c = 0; c < CHUNKS && rc == BAMCL_OK; c++)
+  {
+    const long off = n * c / CHUNKS, cnt = n * (c + 1) / CHUNKS - off;
+    double* d = pf->d_stage.as<double>() + 4 * off;
+    BAMCL_CUDA_OK(cudaMemcpyAsync(d, aos + 4 * off, sizeof(double) * 4 * (size_t)cnt, cudaMemcpyHostToDevice, pf->copy_stream));
+    BAMCL_CUDA_OK(cudaEventRecord(pf->ev_copy[c], pf->copy_stream));
+    BAMCL_CUDA_OK(cudaStreamWaitEvent(ctx->stream, pf->ev_copy[c], 0));
+    BAMCL_LAUNCH(ctx, k_aos_to_soa, (unsigned)((cnt + 255) / 256), 256, 0, reinterpret_cast<const double4*>(d),
+                 s.x.as<double>() + off, s.y.as<double>() + off, s.th.as<double>() + off, s.w.as<double>() + off, (int)cnt);
+    pf->win_off = off;  // score this chunk while the next one is on the bus
+    pf->win_cnt = (int)cnt;
+    rc = launch_score(pf, map);
+  }
+  pf->win_off = 0;
+  pf->win_cnt = -1;
+  if (rc != BAMCL_OK)
+    return rc;
+  BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
+  BAMCL_LAUNCH(ctx, k_normalise, (unsigned)((n + 255) / 256), 256, 0, s.w.as<double>(), (int)n, pf->scalars.as<double>(),
+               s.sample_count);
+  if (total_out)
+    return read_scalar(pf, 0, total_out);
+  return BAMCL_OK;
 }
 
 int bamcl_pf_update_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,

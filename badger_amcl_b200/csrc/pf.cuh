@@ -85,6 +85,12 @@ struct bamcl_pf
   // the cluster chain (union-find, labels, statistics) runs on this stream next to the leaf-count chain
   cudaStream_t aux_stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // copies of host sample buffers overlap the kernels (bamcl_pf_update_planar_host / bamcl_pf_resample_host)
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_copy[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  // the three bucket size classes of the leaf count run side by side
+  cudaStream_t bucket_stream[2] = {nullptr, nullptr};
+  cudaEvent_t ev_bucket_fork = nullptr, ev_bucket_join[2] = {nullptr, nullptr};
   bamcl::DevBuf t_scan, t_out, t_sums, t_fast;
   int tree_fast = 0;        // the last tree build used the bucketed shared-memory path
   bamcl::PinBuf t_hout;
@@ -120,5 +126,7 @@ namespace bamcl
 int pf_reduce_total(bamcl_pf* pf, double* d_total);  // deterministic sum of the current set's weights -> device scalar
 int pf_read_scalar(bamcl_pf* pf, int slot, double* out);  // device scalar slot -> host (synchronises)
 int pf_normalise_by_device_total(bamcl_pf* pf);           // w /= scalars[0] (or 1/n), particle_filter.cpp:237-266
+int pf_ensure_streams(bamcl_pf* pf);                      // side streams + events, created on first use
+int pf_download_async(bamcl_pf* pf, double* aos, long n); // current set -> host AoS on the copy stream (after the main stream's work so far)
 int pf_build_cdf(bamcl_pf* pf, double c0 = 0.0);           // exact sequential CDF of the window, starting at c0
 }

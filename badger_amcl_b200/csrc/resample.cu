@@ -840,7 +840,24 @@ int bamcl_pf_cdf(bamcl_pf* pf, double* c_out, long n_plus_1)
   return BAMCL_OK;
 }
 
+static int resample_impl(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res, double* aos_out,
+                         long aos_cap);
+
 int bamcl_pf_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res)
+{
+  return resample_impl(pf, prm, res, nullptr, 0);
+}
+
+int bamcl_pf_resample_host(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res, double* aos_out,
+                           long aos_capacity)
+{
+  if (!aos_out || aos_capacity < 0)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_resample_host: bad output buffer");
+  return resample_impl(pf, prm, res, aos_out, aos_capacity);
+}
+
+static int resample_impl(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res, double* aos_out,
+                         long aos_cap)
 {
   if (!pf || !prm || !res)
     return set_error(BAMCL_E_ARG, "bamcl_pf_resample: bad arguments");
@@ -852,7 +869,16 @@ int bamcl_pf_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resa
   if (pf->win_cnt >= 0)
     return set_error(BAMCL_E_STATE, "bamcl_pf_resample: a shard window is set; use the bamcl_pf_shard_* phases");
   if (!prm->resample_systematic)
-    return resample_multinomial(pf, prm, res);
+  {
+    BAMCL_TRY(resample_multinomial(pf, prm, res));
+    if (aos_out)
+    {
+      if (res->sample_count > aos_cap)
+        return set_error(BAMCL_E_ARG, "bamcl_pf_resample_host: %d samples do not fit the output buffer", res->sample_count);
+      return bamcl_pf_download_samples(pf, aos_out, res->sample_count);
+    }
+    return BAMCL_OK;
+  }
 
   bamcl_ctx* ctx = pf->ctx;
   SampleSet& set_a = pf->sets[pf->current];
@@ -921,8 +947,18 @@ int bamcl_pf_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resa
     BAMCL_LAUNCH(ctx, k_select, (new_count + 255) / 256, 256, 0, a);
   set_b.sample_count = new_count;
   pf->current = 1 - pf->current;
+  if (aos_out)
+  {
+    // the new set is final once k_select has run: its copy to the host overlaps the pose-bin tree and the clustering
+    if (new_count > aos_cap)
+      return set_error(BAMCL_E_ARG, "bamcl_pf_resample_host: %d samples do not fit the output buffer", new_count);
+    if (new_count > 0)
+      BAMCL_TRY(pf_download_async(pf, aos_out, new_count));
+  }
   // the pinned segment buffer is reused by later calls
   BAMCL_TRY(build_tree_and_stats(pf, pf->current, prm->dist_threshold, prm->convergence_threshold, res));
+  if (aos_out && new_count > 0)
+    BAMCL_CUDA_OK(cudaStreamSynchronize(pf->copy_stream));
   int flags = 0;
   BAMCL_CUDA_OK(cudaMemcpyAsync(&flags, pf_flags(pf), sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));

@@ -286,11 +286,12 @@ def run_b200_arm(a):
         t0 = time.perf_counter()
         ctx.timer_start()
         if sf is None:
-            pf.upload_samples(aos)                                   # H2D: P x 32 B AoS from pinned host memory
-            pf.update_sensor(m, model, ranges, angles, RANGE_MAX)    # H2D: scan; D2H: total
-            r = pf.update_resample()                                 # D2H: result struct
+            # H2D: P x 32 B AoS from pinned host memory (chunks, scored while the next chunk is on the bus) + the scan;
+            # D2H: total
+            pf.update_sensor_host(m, model, ranges, angles, RANGE_MAX, aos)
+            # D2H: result struct + n x 32 B AoS of the new set (copied while the pose-bin tree is built)
+            r = pf.update_resample(out=out_aos)
             n = r.sample_count
-            pf.download_samples_into(out_aos[:n])                    # D2H: n x 32 B AoS
             moved = n
         else:
             # every rank moves ITS window: upload P x 32 B, stage the scan, sharded update + resample, download its

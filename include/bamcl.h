@@ -156,6 +156,12 @@ int bamcl_pf_normalise(bamcl_pf* pf, double total);
 int bamcl_pf_update_planar(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
                            const double* angles, int range_count, double range_max, int converged,
                            double* total_out);
+/* The same update with the particles still in HOST memory (the state after Odom::updateAction wrote the poses through
+ * getCurrentSet(), odom.cpp:107-121): `aos` (n PFSample, page-locked for full PCIe rate) is uploaded in chunks and every
+ * chunk is scored while the next one is on the bus; then total + normalise as above. Sets sample_count = n. */
+int bamcl_pf_update_planar_host(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
+                                const double* angles, int range_count, double range_max, int converged, const double* aos,
+                                long n, double* total_out);
 /* Same, with the scan already staged on the device by bamcl_pf_stage_scan (bench "inputs resident in HBM"). */
 int bamcl_pf_stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
                         const double* angles, int range_count, double range_max);
@@ -224,6 +230,11 @@ typedef struct
  * multinomial (:356) resampling into the other set, kd-tree histogram (pf_kdtree.cpp:49-150), clustering
  * (:58-76,:169-194), cluster/set statistics (particle_filter.cpp:505-636), set swap, updateConverged. */
 int bamcl_pf_resample(bamcl_pf* pf, const bamcl_resample_params* params, bamcl_resample_result* result);
+/* updateResample that also hands the new set to the host (what a caller reads next through getCurrentSet()->samples,
+ * node.cpp:337-349): the device->host copy of the resampled AoS overlaps the pose-bin tree / clustering / statistics.
+ * aos_out holds aos_capacity PFSample; result->sample_count of them are written. */
+int bamcl_pf_resample_host(bamcl_pf* pf, const bamcl_resample_params* params, bamcl_resample_result* result, double* aos_out,
+                           long aos_capacity);
 /* kd-tree + cluster statistics of the CURRENT set as initWithPoseFn/initWithGaussian compute them
  * (particle_filter.cpp:106-162): fills leaf_count, node_count, cluster_count, mean, cov. */
 int bamcl_pf_init_stats(bamcl_pf* pf, bamcl_resample_result* result);

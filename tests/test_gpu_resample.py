@@ -271,3 +271,40 @@ def test_multinomial_with_random_injection_is_refused(env):
     with pytest.raises(cabi.BamclError):
         pf.update_resample()
     pf.close()
+
+
+def test_host_buffer_entry_points_equal_the_resident_ones(env):
+    """bamcl_pf_update_planar_host / bamcl_pf_resample_host (pipelined copies) == upload + update + resample + download"""
+    cabi = env["cabi"]
+    n = 400000  # above the chunking threshold
+    cells, truth = env["cells"], env["truth"]
+    m = cabi.Map2D(env["ctx"], cells, RES)
+    m.build_distances(2.0)
+    poses = synth.uniform_free_poses(cells, RES, n, seed=8)
+    ranges, angles = synth.make_scan(cells, RES, truth, n_beams=90)
+    model = cabi.planar_model(model_type=cabi.MODEL_LF, max_beams=90, scanner_pose=(0.1, 0.0, 0.0))
+    aos = cabi.pinned_array((n, 4))
+    aos[:, :3] = poses
+    aos[:, 3] = 1.0 / n
+    a = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    a.init_with_poses(poses)
+    a.srand48(5)
+    a.upload_samples(aos)
+    a.update_sensor(m, model, ranges, angles, 30.0)
+    wa = a.weights()
+    ra = a.update_resample()
+    sa = a.samples()
+    b = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    b.init_with_poses(poses)
+    b.srand48(5)
+    b.update_sensor_host(m, model, ranges, angles, 30.0, aos)
+    assert np.array_equal(b.weights(), wa)
+    out = cabi.pinned_array((n, 4))
+    rb = b.update_resample(out=out)
+    assert (rb.sample_count, rb.leaf_count, rb.node_count, rb.cluster_count) == (
+        ra.sample_count, ra.leaf_count, ra.node_count, ra.cluster_count)
+    assert np.array_equal(out[:rb.sample_count], sa)
+    assert np.array_equal(b.samples(), sa)
+    a.close()
+    b.close()
+    m.close()

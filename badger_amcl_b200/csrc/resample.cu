@@ -30,8 +30,14 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
 
 namespace
 {
-constexpr int CDF_BLOCK = 256;
-constexpr int CDF_ITEMS = 8;
+#ifndef CDF_BLOCK_THREADS
+#define CDF_BLOCK_THREADS 256
+#endif
+#ifndef CDF_ITEMS_PER_THREAD
+#define CDF_ITEMS_PER_THREAD 8
+#endif
+constexpr int CDF_BLOCK = CDF_BLOCK_THREADS;
+constexpr int CDF_ITEMS = CDF_ITEMS_PER_THREAD;
 constexpr int CDF_TILE = CDF_BLOCK * CDF_ITEMS;
 constexpr long long SAT = 1ll << 56;
 constexpr long long TWO53 = 1ll << 53;

@@ -24,10 +24,28 @@ using namespace bamcl;
 
 namespace
 {
-constexpr int PB = 16;    // particles per warp batch
-constexpr int BPL = 4;    // beams per lane per pass
-constexpr int GB = 4;     // particles per gather batch (GB * BPL loads in flight per lane)
-constexpr int WARPS = 8;  // warps per block
+// tuning knobs (overridable at build time for sweeps: BAMCL_EXTRA_NVCC="-DSCORE_BPL=8 ...")
+#ifndef SCORE_PB
+#define SCORE_PB 16
+#endif
+#ifndef SCORE_BPL
+#define SCORE_BPL 2
+#endif
+#ifndef SCORE_GB
+#define SCORE_GB 8
+#endif
+#ifndef SCORE_WARPS
+#define SCORE_WARPS 8
+#endif
+#ifdef SCORE_MINB
+#define SCORE_BOUNDS __launch_bounds__(SCORE_WARPS * 32, SCORE_MINB)
+#else
+#define SCORE_BOUNDS __launch_bounds__(SCORE_WARPS * 32)
+#endif
+constexpr int PB = SCORE_PB;        // particles per warp batch
+constexpr int BPL = SCORE_BPL;      // beams per lane per pass
+constexpr int GB = SCORE_GB;        // particles per gather batch (GB * BPL loads in flight per lane)
+constexpr int WARPS = SCORE_WARPS;  // warps per block
 constexpr int PASS_BEAMS = 32 * BPL;
 
 struct ScoreArgs
@@ -135,7 +153,7 @@ __device__ __forceinline__ void score_pass(const ScoreArgs& a, const double* __r
 }
 
 template <int TABLE, int LAYOUT>
-__global__ void __launch_bounds__(WARPS * 32) k_score_lf(const ScoreArgs a)
+__global__ void SCORE_BOUNDS k_score_lf(const ScoreArgs a)
 {
   extern __shared__ __align__(16) unsigned char s_raw[];
   double4* s_stash = reinterpret_cast<double4*>(s_raw);                       // [WARPS][PB]

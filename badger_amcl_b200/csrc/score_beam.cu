@@ -25,6 +25,8 @@ struct BeamArgs
   int step;
   const int8_t* cells;
   const float* dist;
+  const uint32_t *blocked_rows, *blocked_cols;  // 1-bit "not free" maps (row-major / column-major)
+  int row_words, col_words;
   int size_x, size_y;
   double resolution;
   float origin_x, origin_y;
@@ -34,37 +36,32 @@ struct BeamArgs
   double off_map_factor, non_free_space_factor, non_free_space_radius;
 };
 
-__device__ __forceinline__ double march(const BeamArgs& a, int x0, int y0, int x1, int y1)
+// OccupancyMap::calcRange (occupancy_map.cpp:257-364) inside the scorer: the reference's integer Bresenham walk, cell
+// by cell, so the first blocked cell -- and the returned range -- are the reference's. The cell test reads the 1-bit
+// "not free" maps (map2d.cu k_blocked_bits): bit (major & 31) of word [minor][major >> 5], the row-major copy for
+// x-major rays and the column-major copy for steep ones, so 32 consecutive steps along the major axis share one word,
+// which stays in a register until the walk leaves it.
+// State of one lane's walk along its current ray (the reference's loop variables, occupancy_map.cpp:300-360).
+struct RayWalk
 {
-  if (x0 == x1 && y0 == y1)
-    return a.range_max;
-  const bool steep = abs(y1 - y0) > abs(x1 - x0);
-  if (steep)
-  {
-    int t = x0; x0 = y0; y0 = t;
-    t = x1; x1 = y1; y1 = t;
-  }
-  const int deltax = abs(x1 - x0), deltay = abs(y1 - y0);
-  const int xstep = (x0 < x1) ? 1 : -1, ystep = (y0 < y1) ? 1 : -1;
-  const int xend = x1 + xstep;
-  int error = 0, x = x0, y = y0;
-  for (;;)
-  {
-    const int cx = steep ? y : x, cy = steep ? x : y;
-    const bool valid = ((unsigned)cx < (unsigned)a.size_x) && ((unsigned)cy < (unsigned)a.size_y);
-    if (!valid || a.cells[(size_t)cy * a.size_x + cx] != -1)
-      return sqrt((double)((x - x0) * (x - x0) + (y - y0) * (y - y0))) * a.resolution;
-    if (x == xend)
-      return a.range_max;
-    x += xstep;
-    error += deltay;
-    if (2 * error >= deltax)
-    {
-      y += ystep;
-      error -= deltax;
-    }
-  }
-}
+  // the reference's loop variables (x = major axis after the steep swap); err2 = 2 * error
+  int x, y, x0, y0, err2, dx, dy2, dx2, xstep, ystep;
+  int left;        // cells still to test before the walk leaves the grid along x or has tested x1 + xstep
+  int oob_at_end;  // running out of `left` means the next cell is off the grid (a hit) rather than "nothing hit"
+  int rowbase;     // y * words
+  int edge;        // (x & 31) value that starts a new word in walking direction
+  int steep;
+  int u;  // beam index, -1 = no ray
+};
+
+// Warp = one particle at a time; lanes = rays. Adjacent rays can differ 30x in length (one ends on the near wall, the
+// next runs through a door), so a lane that finishes its ray scores it and takes the particle's next unassigned beam
+// instead of idling until the longest ray of its group of 32 is done. Refills happen when at least REFILL_MIN lanes
+// are idle (the set-up and the scoring are ~10x a walk step, so they are batched), or when nothing else is running.
+#ifndef BEAM_REFILL_MIN
+#define BEAM_REFILL_MIN 8
+#endif
+constexpr int REFILL_MIN = BEAM_REFILL_MIN;
 
 __global__ void __launch_bounds__(256) k_score_beam(const BeamArgs a)
 {
@@ -80,25 +77,177 @@ __global__ void __launch_bounds__(256) k_score_beam(const BeamArgs a)
     const double sy = py + a.scan_x * s + a.scan_y * c;
     const double c2 = c * a.cos_sa - s * a.sin_sa;
     const double s2 = s * a.cos_sa + c * a.sin_sa;
-    const int x0 = world_to_cell(sx, a.origin_x, a.resolution, a.size_x);
-    const int y0 = world_to_cell(sy, a.origin_y, a.resolution, a.size_y);
+    const int px0 = world_to_cell(sx, a.origin_x, a.resolution, a.size_x);
+    const int py0 = world_to_cell(sy, a.origin_y, a.resolution, a.size_y);
     double acc = 0.0;
-    for (int u = lane; u < a.n_used; u += 32)
+    int next = 0;  // next unassigned beam (warp-uniform)
+    RayWalk r;
+    r.u = -1;
+    bool walking = false;  // this lane is inside a walk
+    double map_range = 0.0;
+    bool have_result = false;  // a finished ray waits to be scored
+    uint32_t cur_word = 0;
+    for (;;)
     {
-      const double4 b = a.beam[u];
-      const double obs_range = a.ranges[(size_t)u * a.step];
-      const double ca = c2 * b.x - s2 * b.y;  // cos(theta + bearing)
-      const double sa = s2 * b.x + c2 * b.y;
-      const int x1 = world_to_cell(sx + a.range_max * ca, a.origin_x, a.resolution, a.size_x);
-      const int y1 = world_to_cell(sy + a.range_max * sa, a.origin_y, a.resolution, a.size_y);
-      const double map_range = march(a, x0, y0, x1, y1);
-      const double z = obs_range - map_range;
-      double pz = 0.0;
-      pz += a.z_hit * exp(-(z * z) / a.z_hit_denom);  // :205
-      if (z < 0)
-        pz += b.z;  // :209
-      pz += b.w;    // :212-217 (exactly one of the two applies unless the range exceeds range_max)
-      acc += pz * pz * pz;
+      const unsigned busy = __ballot_sync(0xffffffffu, walking);
+      const int idle = 32 - __popc(busy);
+      if (next >= a.n_used && busy == 0)
+      {
+        // nothing left to hand out and nobody walks: score what is pending and stop
+        if (have_result)
+        {
+          const double4 b = a.beam[r.u];
+          const double z = a.ranges[(size_t)r.u * a.step] - map_range;
+          double pz = 0.0;
+          pz += a.z_hit * exp(-(z * z) / a.z_hit_denom);  // :205
+          if (z < 0)
+            pz += b.z;  // :209
+          pz += b.w;    // :212-217
+          acc += pz * pz * pz;
+          have_result = false;
+        }
+        break;
+      }
+      if ((next < a.n_used && idle >= REFILL_MIN) || busy == 0)
+      {
+        if (!walking)
+        {
+          if (have_result)
+          {
+            const double4 b = a.beam[r.u];
+            const double z = a.ranges[(size_t)r.u * a.step] - map_range;
+            double pz = 0.0;
+            pz += a.z_hit * exp(-(z * z) / a.z_hit_denom);
+            if (z < 0)
+              pz += b.z;
+            pz += b.w;
+            acc += pz * pz * pz;
+            have_result = false;
+          }
+          // idle lanes take consecutive beams
+          const unsigned idle_mask = ~busy;
+          const int my = next + __popc(idle_mask & ((1u << lane) - 1));
+          if (my < a.n_used)
+          {
+            const double4 b = a.beam[my];
+            const double ca = c2 * b.x - s2 * b.y;  // cos(theta + bearing)
+            const double sa = s2 * b.x + c2 * b.y;
+            int x0 = px0, y0 = py0;
+            int x1 = world_to_cell(sx + a.range_max * ca, a.origin_x, a.resolution, a.size_x);
+            int y1 = world_to_cell(sy + a.range_max * sa, a.origin_y, a.resolution, a.size_y);
+            r.u = my;
+            if (x0 == x1 && y0 == y1)  // occupancy_map.cpp:279-280
+            {
+              map_range = a.range_max;
+              have_result = true;
+            }
+            else
+            {
+              r.steep = abs(y1 - y0) > abs(x1 - x0);
+              if (r.steep)
+              {
+                int t = x0; x0 = y0; y0 = t;
+                t = x1; x1 = y1; y1 = t;
+              }
+              const int major_size = r.steep ? a.size_y : a.size_x, minor_size = r.steep ? a.size_x : a.size_y;
+              const int words = r.steep ? a.col_words : a.row_words;
+              r.x0 = x0;
+              r.y0 = y0;
+              r.dx = abs(x1 - x0);
+              r.dy2 = 2 * abs(y1 - y0);
+              r.dx2 = 2 * r.dx;
+              r.xstep = (x0 < x1) ? 1 : -1;
+              r.ystep = (y0 < y1) ? 1 : -1;
+              r.edge = r.xstep > 0 ? 0 : 31;
+              r.err2 = 0;
+              r.x = x0;
+              r.y = y0;
+              // cells x0 .. x1 + xstep are tested (dx + 2 of them); those with x off the grid count as hits
+              const int to_test = r.dx + 2;
+              const int in_grid = ((unsigned)x0 < (unsigned)major_size) ? (r.xstep > 0 ? major_size - x0 : x0 + 1) : 0;
+              r.left = min(to_test, in_grid);
+              r.oob_at_end = in_grid < to_test;
+              if ((unsigned)y0 >= (unsigned)minor_size || r.left == 0)
+              {
+                map_range = 0.0;  // the start cell itself is off the grid: hit at distance 0 (:315-332)
+                have_result = true;
+              }
+              else
+              {
+                r.rowbase = y0 * words;
+                cur_word = __ldg(&(r.steep ? a.blocked_cols : a.blocked_rows)[r.rowbase + (x0 >> 5)]);
+                walking = true;
+              }
+            }
+          }
+        }
+        next += idle;  // warp-uniform: every idle lane was offered a beam (those past the end stay idle)
+        if (next > a.n_used)
+          next = a.n_used;
+        continue;
+      }
+      // ---- one chunk of walk steps for the lanes that have a ray
+      if (walking)
+      {
+        const uint32_t* __restrict__ bits = r.steep ? a.blocked_cols : a.blocked_rows;
+        const int words = r.steep ? a.col_words : a.row_words;
+        const int minor_size = r.steep ? a.size_x : a.size_y;
+        int x = r.x, y = r.y, err2 = r.err2, left = r.left;
+        uint32_t word = cur_word;
+        // single-exit loop (no breaks): the lanes of a warp stay converged from one step to the next
+        int code = 0;  // 0 walking, 1 hit at (x, y), 2 nothing hit, 3 the next step leaves the grid along x
+#pragma unroll 1
+        for (int it = 0; it < 32 && code == 0; it++)
+        {
+          if ((word >> (x & 31)) & 1u)  // the cell is not free
+            code = 1;
+          else if (left == 1)  // that was the last testable cell
+            code = r.oob_at_end ? 3 : 2;
+          else
+          {
+            left--;
+            x += r.xstep;
+            err2 += r.dy2;
+            bool reload = (x & 31) == r.edge;
+            if (err2 >= r.dx)
+            {
+              y += r.ystep;
+              err2 -= r.dx2;
+              if ((unsigned)y >= (unsigned)minor_size)  // left the grid sideways: this cell is a hit
+                code = 1;
+              else
+              {
+                r.rowbase = y * words;
+                reload = true;
+              }
+            }
+            if (reload && code == 0)
+              word = __ldg(&bits[r.rowbase + (x >> 5)]);
+          }
+        }
+        if (code == 3)
+        {
+          // the walk steps once more and lands off the grid: a hit there (:340-358)
+          x += r.xstep;
+          err2 += r.dy2;
+          if (err2 >= r.dx)
+            y += r.ystep;
+          code = 1;
+        }
+        const bool done = code != 0, hit = code == 1;
+        r.x = x;
+        r.y = y;
+        r.err2 = err2;
+        r.left = left;
+        cur_word = word;
+        if (done)
+        {
+          const int ddx = x - r.x0, ddy = y - r.y0;
+          map_range = hit ? sqrt((double)(ddx * ddx + ddy * ddy)) * a.resolution : a.range_max;
+          walking = false;
+          have_result = true;
+        }
+      }
     }
     acc = warp_sum(acc);
     if (lane == 0)
@@ -170,6 +319,10 @@ int launch_beam_model(bamcl_pf* pf, bamcl_map2d* map)
   a.step = sc.step;
   a.cells = map->cells.as<int8_t>();
   a.dist = map->dist.as<float>();
+  a.blocked_rows = map->blocked_rows.as<uint32_t>();
+  a.blocked_cols = map->blocked_cols.as<uint32_t>();
+  a.row_words = map->row_words;
+  a.col_words = map->col_words;
   a.size_x = map->size_x;
   a.size_y = map->size_y;
   a.resolution = map->resolution;

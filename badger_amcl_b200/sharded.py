@@ -53,6 +53,7 @@ class CudaEngine:
         self.device = torch.device("cuda", device)
         self.buf = torch.empty((pf.max_samples, 3), dtype=torch.float64, device=self.device)
         self.src = None
+        self.pack = self.pack_src = self.gathered = self.gathered_src = None
 
     def want_sources(self):
         self.src = self.torch.full((self.pf.max_samples,), -1, dtype=self.torch.int32, device=self.device)
@@ -88,10 +89,36 @@ class CudaEngine:
         if len(poses):
             self.buf[:len(poses)].copy_(self.torch.from_numpy(np.ascontiguousarray(poses, np.float64)))
 
-    def select(self, start, delta, n_sys, row0, kb, ke):
-        src = C.c_void_p(self.src.data_ptr()) if self.src is not None else None
+    def select(self, start, delta, n_sys, row0, kb, ke, packed=False):
+        """outputs [kb, ke) -> rows row0 + k of the global buffer, or of this rank's packed send buffer"""
+        buf, src = (self.pack, self.pack_src) if packed else (self.buf, self.src)
+        srcp = C.c_void_p(src.data_ptr()) if src is not None else None
         cabi._check(self.L.bamcl_pf_shard_select(self.pf.h, start, delta, n_sys, row0, kb, ke,
-                                                 C.c_void_p(self.buf.data_ptr()), src))
+                                                 C.c_void_p(buf.data_ptr()), srcp))
+
+    def reserve_packed(self, maxc, world):
+        t = self.torch
+        if self.pack is None or self.pack.shape[0] < maxc:
+            self.pack = t.empty((maxc, 3), dtype=t.float64, device=self.device)
+            self.pack_src = t.empty((maxc,), dtype=t.int32, device=self.device) if self.src is not None else None
+        if self.gathered is None or self.gathered.shape[0] < world * maxc:
+            self.gathered = t.empty((world * maxc, 3), dtype=t.float64, device=self.device)
+            self.gathered_src = t.empty((world * maxc,), dtype=t.int32, device=self.device) if self.src is not None else None
+
+    def gather_packed(self, dist, maxc, world):
+        """every rank's packed rows -> gathered[r * maxc ...] (one all-gather instead of one broadcast per run)"""
+        pairs = [(self.gathered, self.pack)] + ([(self.gathered_src, self.pack_src)] if self.src is not None else [])
+        for out, inp in pairs:
+            out, inp = out[:world * maxc], inp[:maxc]
+            if getattr(dist, "get_backend", None) and dist.get_backend() == "nccl":
+                dist.all_gather_into_tensor(out, inp)
+            else:
+                dist.all_gather([out[r * maxc:(r + 1) * maxc] for r in range(world)], inp)
+
+    def unpack(self, r, maxc, off, row, cnt):
+        self.buf[row:row + cnt].copy_(self.gathered[r * maxc + off:r * maxc + off + cnt])
+        if self.src is not None:
+            self.src[row:row + cnt].copy_(self.gathered_src[r * maxc + off:r * maxc + off + cnt])
 
     def before_exchange(self):
         self.pf.ctx.sync()  # selections were enqueued on the library's stream; NCCL runs on torch's
@@ -122,6 +149,8 @@ class ShardedFilter:
         self.last = None
         self.last_plan = None
         self.converged = False
+        self.exchange = "allgather"  # or "broadcast": one broadcast per run of output slots
+        self.last_exchange = None
 
     def srand48(self, seed):
         self.drand48_state = ((seed & 0xFFFFFFFF) << 16) | 0x330E
@@ -144,9 +173,9 @@ class ShardedFilter:
         if self.dist is None or self.world == 1:
             return [v]
         t = self.e.scalar_tensor(v)
-        out = [self.e.scalar_tensor() for _ in range(self.world)]
-        self.dist.all_gather(out, t)
-        return [float(o.item()) for o in out]
+        flat = self.e.scalar_tensor().repeat(self.world)
+        self.dist.all_gather([flat[r:r + 1] for r in range(self.world)], t)
+        return [float(x) for x in flat.tolist()]  # one device->host copy
 
     def _chain_cdf(self):
         """bounds[0..G]: rank r's CDF starts at the exact end value of rank r-1's (particle_filter.cpp:280-285)"""
@@ -215,16 +244,41 @@ class ShardedFilter:
         start = float(np.ldexp(np.float64(state), -48))
         delta = 1.0 / n_sys if n_sys > 0 else 0.0
         runs = systematic_plan(start, delta, n_sys, bounds) if n_sys > 0 else []
+        # exchange: every rank needs the whole new set (the pose-bin tree is global). Balanced plans use ONE all-gather
+        # of packed per-rank rows; a plan where one rank sources most outputs (a converged filter) would pad that to
+        # world x its size, so it falls back to one broadcast per run.
+        counts = [0] * self.world
         for kb, ke, r in runs:
-            if r == self.rank:
-                self.e.select(start, delta, n_sys, n_rand, kb, ke)
-        self.e.before_exchange()
-        mark()
-        if self.dist is not None and self.world > 1:
+            counts[r] += ke - kb
+        maxc = max(counts) if counts else 0
+        gather = (self.dist is not None and self.world > 1 and self.exchange == "allgather" and maxc > 0 and
+                  maxc <= 2 * (-(-n_sys // self.world)) + 1024)
+        self.last_exchange = "allgather" if gather else "broadcast"
+        if gather:
+            self.e.reserve_packed(maxc, self.world)
+            off = 0
             for kb, ke, r in runs:
-                self.dist.broadcast(self.e.buf[n_rand + kb:n_rand + ke], src=r)
-                if self.e.src is not None:
-                    self.dist.broadcast(self.e.src[n_rand + kb:n_rand + ke], src=r)
+                if r == self.rank:
+                    self.e.select(start, delta, n_sys, off - kb, kb, ke, packed=True)
+                    off += ke - kb
+            self.e.before_exchange()
+            mark()
+            self.e.gather_packed(self.dist, maxc, self.world)
+            offs = [0] * self.world
+            for kb, ke, r in runs:
+                self.e.unpack(r, maxc, offs[r], n_rand + kb, ke - kb)
+                offs[r] += ke - kb
+        else:
+            for kb, ke, r in runs:
+                if r == self.rank:
+                    self.e.select(start, delta, n_sys, n_rand, kb, ke)
+            self.e.before_exchange()
+            mark()
+            if self.dist is not None and self.world > 1:
+                for kb, ke, r in runs:
+                    self.dist.broadcast(self.e.buf[n_rand + kb:n_rand + ke], src=r)
+                    if self.e.src is not None:
+                        self.dist.broadcast(self.e.src[n_rand + kb:n_rand + ke], src=r)
         self.e.after_exchange()
         mark()
         prm = cabi.ResampleParams(1, self.min_samples, self.max_samples, self.pop_err, self.pop_z, w_diff, 0.5,

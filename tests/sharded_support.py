@@ -113,14 +113,30 @@ class CheckerEngine:
         if len(poses):
             self.buf[:len(poses)] = self.torch.from_numpy(np.ascontiguousarray(poses))
 
-    def select(self, start, delta, n_sys, row0, kb, ke):
+    def select(self, start, delta, n_sys, row0, kb, ke, packed=False):
         from badger_amcl_b200 import cabi
         t = np.empty(n_sys)
         cabi._check(self.L.bamcl_systematic_targets(start, delta, n_sys, cabi._p(t)))
         j = np.searchsorted(self.c[1:], t[kb:ke], side="right")
         assert j.max() < self.cnt, "target beyond this rank's CDF"
-        self.buf[row0 + kb:row0 + ke] = self.torch.from_numpy(self.poses[self.off + j])
-        self.src[row0 + kb:row0 + ke] = self.torch.from_numpy((self.off + j).astype(np.int32))
+        buf, src = (self.pack, self.pack_src) if packed else (self.buf, self.src)
+        buf[row0 + kb:row0 + ke] = self.torch.from_numpy(self.poses[self.off + j])
+        src[row0 + kb:row0 + ke] = self.torch.from_numpy((self.off + j).astype(np.int32))
+
+    def reserve_packed(self, maxc, world):
+        t = self.torch
+        self.pack = t.zeros((maxc, 3), dtype=t.float64)
+        self.pack_src = t.zeros((maxc,), dtype=t.int32)
+        self.gathered = t.zeros((world * maxc, 3), dtype=t.float64)
+        self.gathered_src = t.zeros((world * maxc,), dtype=t.int32)
+
+    def gather_packed(self, dist, maxc, world):
+        for out, inp in ((self.gathered, self.pack), (self.gathered_src, self.pack_src)):
+            dist.all_gather([out[r * maxc:(r + 1) * maxc] for r in range(world)], inp[:maxc])
+
+    def unpack(self, r, maxc, off, row, cnt):
+        self.buf[row:row + cnt] = self.gathered[r * maxc + off:r * maxc + off + cnt]
+        self.src[row:row + cnt] = self.gathered_src[r * maxc + off:r * maxc + off + cnt]
 
     def before_exchange(self):
         pass

@@ -62,7 +62,7 @@ def test_sharded_cdf_chain_is_the_sequential_cdf(env, world, kind):
     pf.close()
 
 
-def _run_sharded(env, world, poses, weights_per_step, seed, n_min):
+def _run_sharded(env, world, poses, weights_per_step, seed, n_min, exchange="allgather"):
     from badger_amcl_b200 import sharded
     from sharded_support import run_ranks
     cabi = env["cabi"]
@@ -76,6 +76,7 @@ def _run_sharded(env, world, poses, weights_per_step, seed, n_min):
         eng.want_sources()
         f = sharded.ShardedFilter(eng, rank, world, dist, n_min, n)
         f.srand48(seed)
+        f.exchange = exchange
         out = []
         for w in weights_per_step:
             m = pf.sample_count()
@@ -88,7 +89,7 @@ def _run_sharded(env, world, poses, weights_per_step, seed, n_min):
             res = f.update_resample()
             out.append(dict(res=res, src=eng.src[:res.sample_count].cpu().numpy(), samples=pf.samples(),
                             labels=pf.sample_clusters(), stats=np.array(list(res.mean) + list(res.cov)),
-                            runs=list(f.last_plan)))
+                            runs=list(f.last_plan), exchange=f.last_exchange))
         pf.close()
         ctx.close()
         return out
@@ -96,9 +97,10 @@ def _run_sharded(env, world, poses, weights_per_step, seed, n_min):
     return run_ranks(world, rank_fn)
 
 
+@pytest.mark.parametrize("exchange", ["allgather", "broadcast"])
 @pytest.mark.parametrize("world", [2, 4])
 @pytest.mark.parametrize("n,cloud", [(5000, "global"), (100000, "tracking"), (100000, "global")])
-def test_sharded_resample_equals_the_oracles_single_set(env, world, n, cloud):
+def test_sharded_resample_equals_the_oracles_single_set(env, world, n, cloud, exchange):
     O = env["O"]
     cells, truth = env["cells"], env["truth"]
     poses = (synth.uniform_free_poses(cells, RES, n, seed=1) if cloud == "global"
@@ -121,7 +123,8 @@ def test_sharded_resample_equals_the_oracles_single_set(env, world, n, cloud):
         want.append(dict(count=port.sample_count(), src=port.resample_sources(), samples=port.samples(),
                          leaf=port.leaf_count(), nodes=port.node_count(), clusters=port.cluster_count(),
                          labels=port.sample_clusters(), stats=port.set_stats(), conv=port.is_converged()))
-    got = _run_sharded(env, world, poses, weights, 7, n // 10)
+    got = _run_sharded(env, world, poses, weights, 7, n // 10, exchange)
+    assert got[0][0]["exchange"] == exchange  # balanced weights: the all-gather path is really taken when asked for
     for rank in range(world):
         for step in range(2):
             g, w_ = got[rank][step], want[step]

@@ -63,6 +63,17 @@ class ResampleResult(C.Structure):
                 ("drand48_state", C.c_uint64), ("mean", C.c_double * 3), ("cov", C.c_double * 5)]
 
 
+ODOM_DIFF, ODOM_OMNI, ODOM_DIFF_CORRECTED, ODOM_OMNI_CORRECTED, ODOM_GAUSSIAN = 0, 1, 2, 3, 4  # odom.h:33-40
+
+
+class OdomModel(C.Structure):
+    _fields_ = [("model_type", C.c_int), ("alpha", C.c_double * 5)]
+
+
+class OdomData(C.Structure):
+    _fields_ = [("pose", C.c_double * 3), ("delta", C.c_double * 3), ("absolute_motion", C.c_double * 3)]
+
+
 def planar_model(model_type=MODEL_LF, max_beams=60, z_hit=0.95, z_short=0.1, z_max=0.05, z_rand=0.05, sigma_hit=0.2,
                  lambda_short=0.1, gompertz=(1.0, 1.0, 1.0, 0.0, 1.0, 0.0), do_beamskip=False, beam_skip_distance=0.5,
                  beam_skip_threshold=0.3, beam_skip_error_threshold=0.9, off_map_factor=1.0, non_free_space_factor=1.0,
@@ -147,6 +158,7 @@ SIGNATURES = {
     "bamcl_pf_shard_select": (_I, [_P, _D, _D, _L, _L, _L, _L, _P, _P]),
     "bamcl_pf_shard_install": (_I, [_P, _P, _L, _P, _P]),
     "bamcl_pf_leaf_count": (_I, [_P, _P]),
+    "bamcl_pf_update_action": (_I, [_P, _P, _P, C.c_uint64, _P]),
     "bamcl_pf_upload_window_samples": (_I, [_P, _P, _L, _L]),
     "bamcl_pf_download_window_samples": (_I, [_P, _P, _L, _L]),
 }
@@ -497,6 +509,16 @@ class ParticleFilter:
     def set_random_poses(self, poses):
         self.random_poses = np.ascontiguousarray(poses, np.float64)
         self.random_next = 0
+
+    def update_action(self, model_type, alpha, pose, delta, absolute_motion=(0.0, 0.0, 0.0)):
+        """Odom::updateAction (odom.cpp:74-311) on the device-resident current set; the Gaussian draws continue this
+        filter's drand48 stream (srand48 / the resampler's state)."""
+        al = list(alpha) + [0.0] * (5 - len(alpha))
+        m = OdomModel(int(model_type), (C.c_double * 5)(*al))
+        d = OdomData((C.c_double * 3)(*pose), (C.c_double * 3)(*delta), (C.c_double * 3)(*absolute_motion))
+        out = C.c_uint64()
+        _check(self.L.bamcl_pf_update_action(self.h, C.byref(m), C.byref(d), self.drand48_state, C.byref(out)))
+        self.drand48_state = out.value
 
     def resample_limit(self, k):
         return self.L.bamcl_resample_limit(k, self.min_samples, self.max_samples, self.pop_err, self.pop_z)

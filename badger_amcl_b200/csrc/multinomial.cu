@@ -18,6 +18,7 @@
 #include <cmath>
 #include <cstring>
 
+#include "lcg.cuh"
 #include "pf.cuh"
 #include "scan.cuh"
 
@@ -31,26 +32,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
 
 namespace
 {
-constexpr unsigned long long LCG_A = 0x5DEECE66DULL, LCG_C = 0xBULL, LCG_MASK = (1ULL << 48) - 1;
 constexpr int NONE = INT_MAX;
-
-// state after j steps from x0
-__host__ __device__ inline unsigned long long lcg_skip(unsigned long long x0, unsigned long long j)
-{
-  unsigned long long a = LCG_A, c = LCG_C, A = 1, C = 0;  // x -> A x + C
-  while (j)
-  {
-    if (j & 1)
-    {
-      A = (A * a) & LCG_MASK;
-      C = (C * a + c) & LCG_MASK;
-    }
-    c = ((a + 1) * c) & LCG_MASK;
-    a = (a * a) & LCG_MASK;
-    j >>= 1;
-  }
-  return (A * x0 + C) & LCG_MASK;
-}
 
 struct MultiArgs
 {

@@ -285,6 +285,33 @@ int bamcl_pf_download_window_samples(bamcl_pf* pf, double* aos, long offset, lon
 /* getLeafCount of the current set's tree (pf_kdtree.cpp:92), as of its last resample / init */
 int bamcl_pf_leaf_count(bamcl_pf* pf, int* leaf_count);
 
+/* ---- Odom (include/amcl/sensors/odom.h:33-86): the motion update, the step before scoring */
+#define BAMCL_ODOM_DIFF 0 /* OdomModelType, odom.h:33-40 */
+#define BAMCL_ODOM_OMNI 1
+#define BAMCL_ODOM_DIFF_CORRECTED 2
+#define BAMCL_ODOM_OMNI_CORRECTED 3
+#define BAMCL_ODOM_GAUSSIAN 4
+typedef struct bamcl_odom_model /* Odom::setModel, odom.cpp:63-72 */
+{
+  int model_type;
+  double alpha[5];
+} bamcl_odom_model;
+typedef struct bamcl_odom_data /* OdomData, odom.h:43-52 */
+{
+  double pose[3];            /* odometric pose */
+  double delta[3];           /* change in odometric pose */
+  double absolute_motion[3]; /* accumulated |motion| (gaussian model) */
+} bamcl_odom_data;
+/* Odom::updateAction (odom.cpp:74-311) on the device-resident current set: every sample is moved by the odometry
+ * delta plus three PDFGaussian::draw values (pdf_gaussian.cpp:77-97). The draws are the ones the reference would take
+ * from the process's drand48 stream in state `drand48_state` (48 bits): the polar rejection loop is evaluated for all
+ * attempts at once (generator skip-ahead + a prefix sum over the acceptances), so sample i gets accepted attempts
+ * 3i..3i+2 exactly as in the sequential loop. *drand48_state_out = the state after the last draw consumed (hand it to
+ * seed48 to keep the host stream in step). A draw of exactly 0.0 (probability 2^-48 each) would shift the pairing and is
+ * reported as BAMCL_E_UNSUPPORTED. On a sharded set every rank moves its whole replicated copy. Synchronises. */
+int bamcl_pf_update_action(bamcl_pf* pf, const bamcl_odom_model* model, const bamcl_odom_data* data,
+                           uint64_t drand48_state, uint64_t* drand48_state_out);
+
 #ifdef __cplusplus
 }
 #endif

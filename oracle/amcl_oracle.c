@@ -1017,6 +1017,105 @@ void orc_pf_set_samples(orc_pf* pf, const double* aos, long n)
 }
 double* orc_pf_samples_ptr(orc_pf* pf) { return pf->sets[pf->current_set].samples; }
 
+/* ====================================================================== Odom::updateAction */
+/* odom.cpp:318-321: angleDiff(a, b) = angles::shortest_angular_distance(b, a) = normalize_angle(a - b) */
+static double odom_angle_diff(double a, double b) { return orc_normalize_angle(a - b); }
+/* odom.cpp:145-148: distance of a rotation from the nearer of 0 and pi */
+static double odom_rot_noise(double rot)
+{
+  const double to_zero = fabs(odom_angle_diff(rot, 0.0)), to_pi = fabs(odom_angle_diff(rot, M_PI));
+  return to_pi < to_zero ? to_pi : to_zero;
+}
+
+void orc_pf_update_action(orc_pf* pf, orc_rng* rng, int model_type, const double* alpha, const double* pose,
+                          const double* delta, const double* absolute_motion)
+{
+  pf_set* set = &pf->sets[pf->current_set];
+  const double a1 = alpha[0], a2 = alpha[1], a3 = alpha[2], a4 = alpha[3], a5 = alpha[4];
+  const double old_theta = pose[2] - delta[2]; /* :83-85, only the heading of the old pose is used */
+  const double trans = sqrt(delta[0] * delta[0] + delta[1] * delta[1]);
+  const double rot = delta[2];
+  int i;
+  if (model_type == 1 || model_type == 3)
+  {
+    /* omni :88-123, omni corrected :171-206 (standard deviations instead of variances) */
+    double sd_trans = a3 * (trans * trans) + a1 * (rot * rot);
+    double sd_rot = a4 * (rot * rot) + a2 * (trans * trans);
+    double sd_strafe = a1 * (rot * rot) + a5 * (trans * trans);
+    if (model_type == 3)
+    {
+      sd_trans = sqrt(sd_trans);
+      sd_rot = sqrt(sd_rot);
+      sd_strafe = sqrt(sd_strafe);
+    }
+    for (i = 0; i < set->sample_count; i++)
+    {
+      double* s = &set->samples[4 * i];
+      const double bearing = odom_angle_diff(atan2(delta[1], delta[0]), old_theta) + s[2];
+      const double cb = cos(bearing), sb = sin(bearing);
+      const double trans_hat = trans + orc_gaussian_draw(rng, sd_trans);
+      const double rot_hat = rot + orc_gaussian_draw(rng, sd_rot);
+      const double strafe_hat = 0 + orc_gaussian_draw(rng, sd_strafe);
+      s[0] += (trans_hat * cb + strafe_hat * sb);
+      s[1] += (trans_hat * sb - strafe_hat * cb);
+      s[2] += rot_hat;
+    }
+  }
+  else if (model_type == 0 || model_type == 2)
+  {
+    /* diff :125-169, diff corrected :208-255 */
+    const double rot1 = trans < 0.01 ? 0.0 : odom_angle_diff(atan2(delta[1], delta[0]), old_theta);
+    const double rot2 = odom_angle_diff(delta[2], rot1);
+    const double n1 = odom_rot_noise(rot1), n2 = odom_rot_noise(rot2);
+    double sd_rot1 = a1 * n1 * n1 + a2 * trans * trans;
+    double sd_trans = a3 * trans * trans + a4 * n1 * n1 + a4 * n2 * n2;
+    double sd_rot2 = a1 * n2 * n2 + a2 * trans * trans;
+    if (model_type == 2)
+    {
+      sd_rot1 = sqrt(sd_rot1);
+      sd_trans = sqrt(sd_trans);
+      sd_rot2 = sqrt(sd_rot2);
+    }
+    for (i = 0; i < set->sample_count; i++)
+    {
+      double* s = &set->samples[4 * i];
+      const double rot1_hat = odom_angle_diff(rot1, orc_gaussian_draw(rng, sd_rot1));
+      const double trans_hat = trans - orc_gaussian_draw(rng, sd_trans);
+      const double rot2_hat = odom_angle_diff(rot2, orc_gaussian_draw(rng, sd_rot2));
+      const double heading = s[2] + rot1_hat;
+      s[0] += trans_hat * cos(heading);
+      s[1] += trans_hat * sin(heading);
+      s[2] += rot1_hat + rot2_hat;
+    }
+  }
+  else
+  {
+    /* gaussian :257-311: noise from the absolute motion since the last update, applied along the mid heading */
+    const double at2 = absolute_motion[0] * absolute_motion[0], as2 = absolute_motion[1] * absolute_motion[1],
+                 ar2 = absolute_motion[2] * absolute_motion[2];
+    const double sd_rot = sqrt(a1 * ar2 + a2 * at2);
+    const double sd_trans = sqrt(a3 * at2 + a4 * ar2);
+    const double sd_strafe = sqrt(a4 * ar2 + a5 * as2);
+    for (i = 0; i < set->sample_count; i++)
+    {
+      double* s = &set->samples[4 * i];
+      const double heading = s[2] + delta[2] / 2;
+      const double ch = cos(heading), sh = sin(heading);
+      const double bearing = odom_angle_diff(atan2(delta[1], delta[0]), old_theta) + s[2];
+      const double cb = cos(bearing), sb = sin(bearing);
+      const double trans_hat = orc_gaussian_draw(rng, sd_trans);
+      const double strafe_hat = orc_gaussian_draw(rng, sd_strafe);
+      const double rot_hat = orc_gaussian_draw(rng, sd_rot);
+      s[0] += (trans * cb);
+      s[1] += (trans * sb);
+      s[2] += rot;
+      s[0] += (trans_hat * ch + strafe_hat * sh);
+      s[1] += (trans_hat * sh - strafe_hat * ch);
+      s[2] += rot_hat;
+    }
+  }
+}
+
 /* ParticleFilter::updateSensor :237-266 */
 void orc_pf_normalise(orc_pf* pf, double total)
 {

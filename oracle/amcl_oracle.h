@@ -128,6 +128,12 @@ void orc_pf_get_set_stats(const orc_pf* pf, double* out8);      /* mean[3], cov0
 /* sequential CDF of the current set (:280-285); c has sample_count+1 entries */
 void orc_pf_cdf(const orc_pf* pf, double* c);
 
+/* ---- Odom::updateAction (sensors/odom.cpp:74-311): the motion update of the current set, drawing from rng.
+ * model_type = OdomModelType (odom.h:33-40): 0 diff, 1 omni, 2 diff corrected, 3 omni corrected, 4 gaussian;
+ * alpha[5]; pose / delta / absolute_motion = OdomData (odom.h:43-52). */
+void orc_pf_update_action(orc_pf* pf, orc_rng* rng, int model_type, const double* alpha, const double* pose,
+                          const double* delta, const double* absolute_motion);
+
 /* ---- OctoMap (map/octomap.cpp) */
 typedef struct orc_map3d orc_map3d;
 /* occupied leaves as integer keys (centre = (key + 0.5) * res, octomap's keyToCoord) */

@@ -98,6 +98,7 @@ def port_lib():
         L = C.CDLL(PORT_SO)
         D, I, L_, V, P = C.c_double, C.c_int, C.c_long, C.c_void_p, C.c_void_p
         sig = {
+            "orc_pf_update_action": (None, [P, P, I, P, P, P, P]),
             "orc_srand48": (None, [P, L_]), "orc_drand48": (D, [P]), "orc_gaussian_draw": (D, [P, D]),
             "orc_map2d_world_to_map": (None, [P, D, D, P, P]), "orc_map2d_map_to_world": (None, [P, I, I, P, P]),
             "orc_map2d_is_valid": (I, [P, I, I]), "orc_map2d_distance": (C.c_float, [P, I, I]),
@@ -153,6 +154,7 @@ def ref_lib():
         sig = {
             "ref_srand48": (None, [L_]), "ref_drand48": (D, []), "ref_seed48": (None, [P]), "ref_get_seed48": (None, [P]),
             "ref_gaussian_draw": (D, [D]),
+            "ref_pf_update_action": (None, [P, I, P, P, P, P]),
             "ref_map2d_create": (V, [D, I, I, F, F]), "ref_map2d_destroy": (None, [P]),
             "ref_map2d_set_cells": (None, [P, P, L_]), "ref_map2d_get_cell": (I, [P, I, I]),
             "ref_map2d_update_distances": (None, [P, D]), "ref_map2d_get_distances": (None, [P, P, L_]),
@@ -431,6 +433,11 @@ class PortPF(_PFBase):
     def update_resample(self):
         self.L.orc_pf_update_resample(self.h, C.byref(self.rng))
 
+    def update_action(self, model_type, alpha, pose, delta, absolute_motion=(0.0, 0.0, 0.0)):
+        """Odom::updateAction (odom.cpp:74-311) on the current set, drawing from this filter's drand48 stream"""
+        v = [np.ascontiguousarray(x, np.float64) for x in (alpha, pose, delta, absolute_motion)]
+        self.L.orc_pf_update_action(self.h, C.byref(self.rng), int(model_type), *[_ptr(x) for x in v])
+
     def resample_sources(self):
         out = np.empty(self.sample_count(), np.int32)
         self.L.orc_pf_get_resample_sources(self.h, _ptr(out))
@@ -517,6 +524,10 @@ class RefPF(_PFBase):
 
     def update_resample(self):
         self.L.ref_pf_update_resample(self.h)
+
+    def update_action(self, model_type, alpha, pose, delta, absolute_motion=(0.0, 0.0, 0.0)):
+        v = [np.ascontiguousarray(x, np.float64) for x in (alpha, pose, delta, absolute_motion)]
+        self.L.ref_pf_update_action(self.h, int(model_type), *[_ptr(x) for x in v])
 
     def resample_limit(self, k):
         return self.L.ref_pf_resample_limit(self.h, k)

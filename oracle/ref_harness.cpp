@@ -32,6 +32,7 @@
 #include "map/octomap.h"
 #include "pf/particle_filter.h"
 #include "pf/pf_kdtree.h"
+#include "sensors/odom.h"
 #include "sensors/planar_scanner.h"
 #undef private
 #undef protected
@@ -512,4 +513,27 @@ void ref_pf_get_set_stats(void* h, double* out)
   out[7] = set->cov(2, 2);
 }
 
+// ---------------------------------------------------------------- Odom::updateAction (sensors/odom.cpp:74-311)
+// model_type = OdomModelType (odom.h:33-40); the draws come from the process-global drand48 stream.
+void ref_pf_update_action(void* h, int model_type, const double* alpha, const double* pose, const double* delta,
+                          const double* absolute_motion)
+{
+  Odom odom;
+  odom.setModel(static_cast<OdomModelType>(model_type), alpha[0], alpha[1], alpha[2], alpha[3], alpha[4]);
+  std::shared_ptr<OdomData> data = std::make_shared<OdomData>();
+  for (int i = 0; i < 3; i++)
+  {
+    data->pose[i] = pose[i];
+    data->delta[i] = delta[i];
+    data->absolute_motion[i] = absolute_motion[i];
+  }
+  odom.updateAction(static_cast<PF*>(h)->pf, data);
+}
 }  // extern "C"
+
+// odom.cpp links against PDFGaussian::draw; its own translation unit (pf/pdf_gaussian.cpp) needs Eigen::EigenSolver and
+// cannot be compiled here, so the static member gets the restated body above.
+namespace badger_amcl
+{
+double PDFGaussian::draw(double sigma) { return ref_gaussian_draw(sigma); }
+}  // namespace badger_amcl

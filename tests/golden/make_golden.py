@@ -23,6 +23,12 @@ MODELS = {
 }
 
 
+MOTION_ALPHA = [0.2, 0.3, 0.25, 0.15, 0.1]
+MOTION_POSE = [1.0, 2.0, 0.7]
+MOTION_DELTAS = [[0.3, 0.1, 0.2], [0.001, 0.0, 1.5], [-0.4, 0.2, -3.0]]
+MOTION_ABS = [0.35, 0.05, 0.25]
+
+
 def world():
     cells = synth.make_grid(240, 200, seed=7, wall_every=60)
     truth = synth.pick_truth_pose(cells, RES, seed=5)
@@ -101,6 +107,20 @@ def main():
     m3.update_distances()
     mn, mx = m3.bounds()
     np.savez_compressed(os.path.join(HERE, "octomap_3d.npz"), keys=keys, field=m3.dense(), mn=np.array(mn), mx=np.array(mx))
+    # motion update (odom.cpp:74-311): five models x three odometry deltas on one small cloud, drand48 seeded per case;
+    # `next` = the drand48() value after the update (pins the number of draws consumed)
+    mposes = synth.gaussian_poses((1.5, -0.7, 0.4), 400, seed=9)
+    out = dict(poses=mposes, alpha=np.array(MOTION_ALPHA), pose=np.array(MOTION_POSE), deltas=np.array(MOTION_DELTAS),
+               absolute_motion=np.array(MOTION_ABS))
+    for mt in range(5):
+        for di, delta in enumerate(MOTION_DELTAS):
+            pf = O.RefPF(40, len(mposes))
+            pf.init_with_poses(mposes)
+            pf.srand48(100 + 10 * mt + di)
+            pf.update_action(mt, MOTION_ALPHA, MOTION_POSE, delta, MOTION_ABS)
+            out["m%d_d%d" % (mt, di)] = pf.samples()[:, :3]
+            out["m%d_d%d_next" % (mt, di)] = np.float64(O.ref_lib().ref_drand48())
+    np.savez_compressed(os.path.join(HERE, "motion.npz"), **out)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")

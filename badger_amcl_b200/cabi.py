@@ -159,6 +159,11 @@ SIGNATURES = {
     "bamcl_pf_shard_install": (_I, [_P, _P, _L, _P, _P]),
     "bamcl_pf_leaf_count": (_I, [_P, _P]),
     "bamcl_pf_update_action": (_I, [_P, _P, _P, C.c_uint64, _P]),
+    "bamcl_pf_max_weight_pose": (_I, [_P, _P, _P, _P]),
+    "bamcl_map2d_update_free_space": (_I, [_P, _D, _P]),
+    "bamcl_map2d_download_free_space": (_I, [_P, _P, _L]),
+    "bamcl_pf_init_uniform": (_I, [_P, _P, _D, _D, C.c_uint64, _P, _P]),
+    "bamcl_pose_covariance": (_I, [_P, _P]),
     "bamcl_pf_upload_window_samples": (_I, [_P, _P, _L, _L]),
     "bamcl_pf_download_window_samples": (_I, [_P, _P, _L, _L]),
 }
@@ -259,6 +264,18 @@ class Map2D:
     def upload_distances(self, dist, max_distance):
         d = np.ascontiguousarray(dist, np.float32)
         _check(self.L.bamcl_map2d_upload_distances(self.h, _p(d), d.size, max_distance))
+
+    def update_free_space(self, radius):
+        """Node2D::updateFreeSpaceIndices (node_2d.cpp:320-338) on the device; returns the number of free cells"""
+        n = C.c_long()
+        _check(self.L.bamcl_map2d_update_free_space(self.h, radius, C.byref(n)))
+        self.free_count = n.value
+        return n.value
+
+    def free_space(self):
+        out = np.empty((self.free_count, 2), np.int32)
+        _check(self.L.bamcl_map2d_download_free_space(self.h, _p(out), len(out)))
+        return out
 
     def download_distances(self):
         out = np.empty((self.size_y, self.size_x), np.float32)
@@ -380,6 +397,19 @@ class ParticleFilter:
         self.converged = False
         res = ResampleResult()
         _check(self.L.bamcl_pf_init_stats(self.h, C.byref(res)))
+        self.last = res
+        return res
+
+    def init_uniform(self, map2d, threshold=0.0, multiplier=0.0):
+        """initWithPoseFn(uniformPoseGenerator) on the device (particle_filter.cpp:136-162, node.cpp:823-868); the map's
+        free-space list must have been built (Map2D.update_free_space)"""
+        res = ResampleResult()
+        out = C.c_uint64()
+        _check(self.L.bamcl_pf_init_uniform(self.h, map2d.h, threshold, multiplier, self.drand48_state, C.byref(out),
+                                            C.byref(res)))
+        self.drand48_state = out.value
+        self.w_slow = self.w_fast = 0.0
+        self.converged = False
         self.last = res
         return res
 
@@ -563,6 +593,19 @@ class ParticleFilter:
         out = np.empty((n, 10))
         _check(self.L.bamcl_pf_cluster_stats(self.h, _p(out), n))
         return out
+
+    def max_weight_pose(self):
+        """Node2D::getMaxWeightPose (node_2d.cpp:588-617) -> (weight, pose[3], cluster index)"""
+        w, idx = C.c_double(), C.c_int()
+        pose = np.empty(3)
+        _check(self.L.bamcl_pf_max_weight_pose(self.h, C.byref(w), _p(pose), C.byref(idx)))
+        return w.value, pose, idx.value
+
+    def pose_covariance(self):
+        """the 6x6 covariance Node::updatePose publishes (node.cpp:381-395)"""
+        out = np.empty(36)
+        _check(self.L.bamcl_pose_covariance(C.byref(self.last), _p(out)))
+        return out.reshape(6, 6)
 
     def set_stats(self):
         r = self.last

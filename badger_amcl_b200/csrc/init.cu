@@ -1,0 +1,187 @@
+// Global localisation on the device: the free-space index list of Node2D::updateFreeSpaceIndices
+// (src/amcl/node/node_2d.cpp:320-338) and ParticleFilter::initWithPoseFn (src/amcl/pf/particle_filter.cpp:136-162)
+// fed by Node::uniformPoseGenerator / randomFreeSpacePose (src/amcl/node/node.cpp:823-868).
+//
+// The list is a stream compaction over the grid in the reference's order (i outer, j inner -- the transpose of the
+// cell storage). Every randomFreeSpacePose call takes exactly two drand48 values, and Node2D::scorePose always returns
+// 1.0 (it scores a copy of the fake sample, node_2d.cpp:310-313), so the de-weighting retry loop of
+// uniformPoseGenerator runs a fixed number r of extra generations per pose: pose s is generation (1 + r) s + r of the
+// stream and all poses are independent given the generator's skip-ahead (lcg.cuh).
+#include <cmath>
+#include <cstring>
+
+#include "lcg.cuh"
+#include "pf.cuh"
+#include "scan.cuh"
+
+using namespace bamcl;
+
+namespace bamcl
+{
+int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, double convergence_threshold,
+                         bamcl_resample_result* result);  // kdtree.cu
+}
+
+namespace
+{
+// t = i * size_y + j (the reference's loop order); cell storage is i + j * size_x
+__global__ void __launch_bounds__(256) k_free_flags(const signed char* __restrict__ cells, const float* __restrict__ dist,
+                                                    int size_x, int size_y, double radius, int* __restrict__ flag)
+{
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long)size_x * size_y)
+    return;
+  const int i = (int)(t / size_y), j = (int)(t % size_y);
+  const size_t c = (size_t)i + (size_t)j * size_x;
+  flag[t] = (cells[c] == -1 && (double)dist[c] > radius) ? 1 : 0;  // CELL_FREE and getDistanceToObject > radius
+}
+
+__global__ void __launch_bounds__(256) k_free_scatter(const signed char* __restrict__ cells, const float* __restrict__ dist,
+                                                      int size_x, int size_y, double radius, const int* __restrict__ pos,
+                                                      int2* __restrict__ out)
+{
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long)size_x * size_y)
+    return;
+  const int i = (int)(t / size_y), j = (int)(t % size_y);
+  const size_t c = (size_t)i + (size_t)j * size_x;
+  if (cells[c] == -1 && (double)dist[c] > radius)
+    out[pos[t]] = make_int2(i, j);
+}
+
+struct UniformArgs
+{
+  unsigned long long state0;
+  int n, per_pose;  // per_pose = 1 + r generations per returned pose; the last one is kept
+  const int2* free_ij;
+  long free_n;
+  int size_x, size_y;
+  double resolution, origin_x, origin_y;
+  double *x, *y, *th, *w;
+  double weight;
+};
+
+__global__ void __launch_bounds__(256) k_uniform_poses(const UniformArgs a)
+{
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= a.n)
+    return;
+  const unsigned long long gen = (unsigned long long)a.per_pose * (unsigned long long)s + (unsigned long long)(a.per_pose - 1);
+  const unsigned long long u = lcg_skip(a.state0, 2ull * gen + 1ull), v = lcg_next(u);
+  const double r1 = (double)u * 0x1p-48, r2 = (double)v * 0x1p-48;
+  const unsigned int k = (unsigned int)(r1 * (double)(size_t)a.free_n);  // node.cpp:831
+  const int2 c = a.free_ij[k];
+  a.x[s] = a.origin_x + (c.x - a.size_x / 2) * a.resolution;  // convertMapToWorld, occupancy_map.cpp:75-88
+  a.y[s] = a.origin_y + (c.y - a.size_y / 2) * a.resolution;
+  a.th[s] = r2 * 2 * M_PI - M_PI;  // node.cpp:837
+  a.w[s] = a.weight;
+}
+}  // namespace
+
+extern "C" int bamcl_map2d_update_free_space(bamcl_map2d* m, double non_free_space_radius, long* count_out)
+{
+  if (!m || !count_out)
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_update_free_space: null argument");
+  if (!m->has_cells || !m->has_dist)
+    return set_error(BAMCL_E_STATE, "bamcl_map2d_update_free_space: needs the cells and the distance cache "
+                                    "(node_2d.cpp:322-323)");
+  bamcl_ctx* ctx = m->ctx;
+  const long n = (long)m->size_x * m->size_y;
+  DevBuf flags, scratch;
+  int rc = flags.reserve(sizeof(int) * ((size_t)n + 2));
+  if (rc == BAMCL_OK)
+    rc = scratch.reserve(sizeof(int) * (scan_scratch_ints(n) + 8));
+  if (rc != BAMCL_OK)
+  {
+    flags.release();
+    scratch.release();
+    return rc;
+  }
+  int* total = scratch.as<int>();
+  const unsigned blocks = (unsigned)((n + 255) / 256);
+  auto body = [&]() -> int {
+    BAMCL_LAUNCH(ctx, k_free_flags, blocks, 256, 0, m->cells.as<signed char>(), m->dist.as<float>(), m->size_x, m->size_y,
+                 non_free_space_radius, flags.as<int>());
+    BAMCL_TRY(exclusive_scan_i32(ctx, flags.as<int>(), flags.as<int>(), n, total + 4, total));
+    int h_total = 0;
+    BAMCL_CUDA_OK(cudaMemcpyAsync(&h_total, total, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    BAMCL_TRY(m->free_ij.reserve(sizeof(int2) * (size_t)std::max(h_total, 1)));
+    BAMCL_LAUNCH(ctx, k_free_scatter, blocks, 256, 0, m->cells.as<signed char>(), m->dist.as<float>(), m->size_x, m->size_y,
+                 non_free_space_radius, flags.as<int>(), m->free_ij.as<int2>());
+    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    m->free_count = h_total;
+    return BAMCL_OK;
+  };
+  rc = body();
+  flags.release();
+  scratch.release();
+  if (rc != BAMCL_OK)
+    return rc;
+  *count_out = m->free_count;
+  return BAMCL_OK;
+}
+
+extern "C" int bamcl_map2d_download_free_space(bamcl_map2d* m, int* ij_out, long n)
+{
+  if (!m || !ij_out || m->free_count < 0 || n != m->free_count)
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_download_free_space: need free_count pairs (update_free_space first)");
+  if (n == 0)
+    return BAMCL_OK;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(ij_out, m->free_ij.p, sizeof(int2) * (size_t)n, cudaMemcpyDeviceToHost, m->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(m->ctx->stream));
+  return BAMCL_OK;
+}
+
+extern "C" int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double starting_weight_threshold,
+                                     double deweight_multiplier, uint64_t drand48_state, uint64_t* drand48_state_out,
+                                     bamcl_resample_result* res)
+{
+  if (!pf || !map || !drand48_state_out || !res)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_init_uniform: null argument");
+  if (map->free_count <= 0)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_init_uniform: the free-space list is empty or not built (node.cpp:826-830 "
+                                    "warns and returns an unset pose)");
+  // node.cpp:849-866 with scorePose == 1.0: generations thrown away per returned pose
+  long r = 0;
+  if (starting_weight_threshold > 0.0 && deweight_multiplier < 1.0 && deweight_multiplier >= 0.0)
+  {
+    double good = starting_weight_threshold;
+    while (1.0 < good)
+    {
+      good *= deweight_multiplier;
+      if (++r > 1000000)
+        return set_error(BAMCL_E_UNSUPPORTED, "bamcl_pf_init_uniform: more than 1e6 de-weighting retries per pose");
+    }
+  }
+  bamcl_ctx* ctx = pf->ctx;
+  pf->win_cnt = -1;
+  SampleSet& set = pf->sets[pf->current];
+  const int n = pf->max_samples;  // :147
+  UniformArgs a;
+  a.state0 = drand48_state & LCG_MASK;
+  a.n = n;
+  a.per_pose = (int)(1 + r);
+  a.free_ij = map->free_ij.as<int2>();
+  a.free_n = map->free_count;
+  a.size_x = map->size_x;
+  a.size_y = map->size_y;
+  a.resolution = map->resolution;
+  a.origin_x = (double)map->origin_x;
+  a.origin_y = (double)map->origin_y;
+  a.x = set.x.as<double>();
+  a.y = set.y.as<double>();
+  a.th = set.th.as<double>();
+  a.w = set.w.as<double>();
+  a.weight = 1.0 / (double)pf->max_samples;  // :152
+  BAMCL_LAUNCH(ctx, k_uniform_poses, (unsigned)((n + 255) / 256), 256, 0, a);
+  set.sample_count = n;
+  memset(res, 0, sizeof(*res));
+  BAMCL_TRY(build_tree_and_stats(pf, pf->current, 0.5, 1e300, res));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  res->sample_count = n;
+  res->converged = 0;  // initConverged, :163-167
+  *drand48_state_out = lcg_skip(a.state0, 2ull * (unsigned long long)(1 + r) * (unsigned long long)n);
+  res->drand48_state = *drand48_state_out;
+  return BAMCL_OK;
+}

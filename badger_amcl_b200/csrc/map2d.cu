@@ -234,6 +234,7 @@ int bamcl_map2d_destroy(bamcl_map2d* m)
   m->rank_of_k.release();
   m->blocked_rows.release();
   m->blocked_cols.release();
+  m->free_ij.release();
   delete m;
   return BAMCL_OK;
 }
@@ -313,6 +314,7 @@ int bamcl_map2d_build_distances(bamcl_map2d* m, double max_distance)
   g.release();
   m->has_dist = true;
   m->version++;
+  m->free_count = -1;  // the free-space list belongs to the previous cache
   return BAMCL_OK;
 }
 
@@ -341,6 +343,7 @@ int bamcl_map2d_upload_distances(bamcl_map2d* m, const float* distances, long n,
   }
   m->has_dist = true;
   m->version++;
+  m->free_count = -1;  // the free-space list belongs to the previous cache
   return BAMCL_OK;
 }
 

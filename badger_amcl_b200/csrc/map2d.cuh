@@ -27,6 +27,9 @@ struct bamcl_map2d
   // bit field "cell is not free" for the ray march, row-major and column-major copies
   bamcl::DevBuf blocked_rows, blocked_cols;
   int row_words = 0, col_words = 0;
+  // Node2D::updateFreeSpaceIndices (node_2d.cpp:320-338): (i, j) of the free cells far enough from obstacles, i-major
+  bamcl::DevBuf free_ij;
+  long free_count = -1;  // -1 = not built for the current cache
   uint64_t version = 0;  // bumped whenever the cache changes (scan staging keys on it)
   int layout = 0;        // tiled_offset layout (see below); fixed at creation
 };

@@ -312,6 +312,32 @@ typedef struct bamcl_odom_data /* OdomData, odom.h:43-52 */
 int bamcl_pf_update_action(bamcl_pf* pf, const bamcl_odom_model* model, const bamcl_odom_data* data,
                            uint64_t drand48_state, uint64_t* drand48_state_out);
 
+/* ---- global localisation */
+/* Node2D::updateFreeSpaceIndices (node_2d.cpp:320-338): the (i, j) of every CELL_FREE cell whose cached distance exceeds
+ * non_free_space_radius, in the reference's order (i outer, j inner), kept on the device; count_out =
+ * free_space_indices_.size(). Needs the cells and a distance cache. */
+int bamcl_map2d_update_free_space(bamcl_map2d* m, double non_free_space_radius, long* count_out);
+/* the list as n (i, j) int pairs (parity tests) */
+int bamcl_map2d_download_free_space(bamcl_map2d* m, int* ij_out, long n);
+/* ParticleFilter::initWithPoseFn (particle_filter.cpp:136-162) with Node::uniformPoseGenerator (node.cpp:847-868) as
+ * the pose function: max_samples poses drawn from the free-space list (randomFreeSpacePose, node.cpp:823-840: cell
+ * index = drand48() * size, heading = drand48() * 2 pi - pi), weights 1/max_samples, pose-bin tree, clusters and
+ * statistics; w_slow/w_fast reset is the caller's (:158). The de-weighting retry loop compares against
+ * Node2D::scorePose, which always returns 1.0 in the reference (it scores a copy, node_2d.cpp:310-313): with
+ * starting_weight_threshold > 1 every pose throws away a fixed number of generations, reproduced here.
+ * drand48_state in / out as for bamcl_pf_update_action. */
+int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double starting_weight_threshold, double deweight_multiplier,
+                          uint64_t drand48_state, uint64_t* drand48_state_out, bamcl_resample_result* result);
+
+/* ---- pose read-out */
+/* Node2D::getMaxWeightPose (node_2d.cpp:588-617): weight and mean pose of the first cluster with the greatest weight,
+ * from the cluster statistics of the last resample / init, reduced on the device (no download of the cluster table).
+ * Where the reference would index hyps[-1] (no cluster with positive weight) this returns BAMCL_E_STATE. */
+int bamcl_pf_max_weight_pose(bamcl_pf* pf, double* max_weight, double* pose3, int* cluster_index_or_null);
+/* covariance packing of Node::updatePose (node.cpp:381-395): the set's covariance (result->cov) into the row-major
+ * 6x6 of geometry_msgs/PoseWithCovariance: [0],[1],[6],[7] and [35] (COVARIANCE_AA, node.h:67); host arithmetic */
+int bamcl_pose_covariance(const bamcl_resample_result* result, double* cov36);
+
 #ifdef __cplusplus
 }
 #endif

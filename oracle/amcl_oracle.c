@@ -1017,6 +1017,51 @@ void orc_pf_set_samples(orc_pf* pf, const double* aos, long n)
 }
 double* orc_pf_samples_ptr(orc_pf* pf) { return pf->sets[pf->current_set].samples; }
 
+/* ====================================================================== global localisation helpers */
+/* node_2d.cpp:320-338 */
+long orc_map2d_free_space(const orc_map2d* m, double non_free_space_radius, int* ij_out)
+{
+  long n = 0;
+  int i, j;
+  for (i = 0; i < m->size_x; i++)
+    for (j = 0; j < m->size_y; j++)
+      if (m->cells[cell_index(m, i, j)] == -1 && orc_map2d_distance(m, i, j) > non_free_space_radius)
+      {
+        if (ij_out)
+        {
+          ij_out[2 * n] = i;
+          ij_out[2 * n + 1] = j;
+        }
+        n++;
+      }
+  return n;
+}
+/* node.cpp:823-840 */
+static void random_free_space_pose(const orc_map2d* m, const int* free_ij, long free_n, orc_rng* rng, double* p)
+{
+  const unsigned int k = orc_drand48(rng) * (size_t)free_n;
+  orc_map2d_map_to_world(m, free_ij[2 * k], free_ij[2 * k + 1], &p[0], &p[1]);
+  p[2] = orc_drand48(rng) * 2 * M_PI - M_PI;
+}
+/* node.cpp:847-868 with scorePose(p) == 1.0 */
+void orc_uniform_poses(const orc_map2d* m, const int* free_ij, long free_n, orc_rng* rng, double starting_weight_threshold,
+                       double deweight_multiplier, long n, double* poses3)
+{
+  long s;
+  for (s = 0; s < n; s++)
+  {
+    double good = starting_weight_threshold;
+    double* p = &poses3[3 * s];
+    random_free_space_pose(m, free_ij, free_n, rng, p);
+    if (good > 0.0 && deweight_multiplier < 1.0 && deweight_multiplier >= 0.0)
+      while (1.0 < good)
+      {
+        random_free_space_pose(m, free_ij, free_n, rng, p);
+        good *= deweight_multiplier;
+      }
+  }
+}
+
 /* ====================================================================== Odom::updateAction */
 /* odom.cpp:318-321: angleDiff(a, b) = angles::shortest_angular_distance(b, a) = normalize_angle(a - b) */
 static double odom_angle_diff(double a, double b) { return orc_normalize_angle(a - b); }

@@ -128,6 +128,16 @@ void orc_pf_get_set_stats(const orc_pf* pf, double* out8);      /* mean[3], cov0
 /* sequential CDF of the current set (:280-285); c has sample_count+1 entries */
 void orc_pf_cdf(const orc_pf* pf, double* c);
 
+/* ---- global localisation (node_2d.cpp:320-338, node.cpp:823-868). The node translation units are ROS nodes and cannot
+ * be compiled here: PARITY UNPINNED for these three helpers (no reference test or golden vector covers them). */
+/* Node2D::updateFreeSpaceIndices: free cells with cached distance > radius, i outer / j inner; ij_out = pairs, may be
+ * NULL to count only */
+long orc_map2d_free_space(const orc_map2d* m, double non_free_space_radius, int* ij_out);
+/* Node::uniformPoseGenerator n times (randomFreeSpacePose + the de-weighting retry loop with Node2D::scorePose == 1.0,
+ * which is what the reference's copy-of-the-sample bug makes it, node_2d.cpp:310-313) */
+void orc_uniform_poses(const orc_map2d* m, const int* free_ij, long free_n, orc_rng* rng, double starting_weight_threshold,
+                       double deweight_multiplier, long n, double* poses3);
+
 /* ---- Odom::updateAction (sensors/odom.cpp:74-311): the motion update of the current set, drawing from rng.
  * model_type = OdomModelType (odom.h:33-40): 0 diff, 1 omni, 2 diff corrected, 3 omni corrected, 4 gaussian;
  * alpha[5]; pose / delta / absolute_motion = OdomData (odom.h:43-52). */

@@ -99,6 +99,7 @@ def port_lib():
         D, I, L_, V, P = C.c_double, C.c_int, C.c_long, C.c_void_p, C.c_void_p
         sig = {
             "orc_pf_update_action": (None, [P, P, I, P, P, P, P]),
+            "orc_map2d_free_space": (L_, [P, D, P]), "orc_uniform_poses": (None, [P, P, L_, P, D, D, L_, P]),
             "orc_srand48": (None, [P, L_]), "orc_drand48": (D, [P]), "orc_gaussian_draw": (D, [P, D]),
             "orc_map2d_world_to_map": (None, [P, D, D, P, P]), "orc_map2d_map_to_world": (None, [P, I, I, P, P]),
             "orc_map2d_is_valid": (I, [P, I, I]), "orc_map2d_distance": (C.c_float, [P, I, I]),
@@ -221,6 +222,21 @@ class PortMap2D:
         self.L.orc_map2d_update_distances(C.byref(self.s), max_dist, _ptr(self.dist))
         self.s.distances, self.s.max_distance = _ptr(self.dist), max_dist
         return self.dist
+
+    def free_space(self, radius):
+        """Node2D::updateFreeSpaceIndices (node_2d.cpp:320-338) -> (n, 2) int32 of (i, j)"""
+        n = self.L.orc_map2d_free_space(C.byref(self.s), radius, None)
+        out = np.empty((n, 2), np.int32)
+        self.L.orc_map2d_free_space(C.byref(self.s), radius, _ptr(out))
+        return out
+
+    def uniform_poses(self, free_ij, rng, n, threshold=0.0, multiplier=0.0):
+        """n calls of Node::uniformPoseGenerator (node.cpp:847-868) drawing from rng (an oracle.Rng)"""
+        free_ij = np.ascontiguousarray(free_ij, np.int32)
+        out = np.empty((n, 3))
+        self.L.orc_uniform_poses(C.byref(self.s), _ptr(free_ij), len(free_ij), C.byref(rng), threshold, multiplier, n,
+                                 _ptr(out))
+        return out
 
     def exact_edt(self, max_dist):
         out = np.empty((self.size_y, self.size_x), np.float32)
@@ -383,6 +399,24 @@ class _PFBase:
         out = np.empty(8)
         self._get_set_stats(out)
         return out
+
+    def max_weight_pose(self):
+        """Node2D::getMaxWeightPose (node_2d.cpp:588-617) restated over getClusterStats: the first cluster whose weight
+        is strictly greater than every earlier one -> (weight, mean pose, index); index -1 where the reference would
+        read hyps[-1]. (node_2d.cpp is a ROS node and cannot be compiled here: parity unpinned for this helper.)"""
+        st = self.cluster_stats()
+        best, idx = 0.0, -1
+        for c in range(len(st)):
+            if st[c, 1] > best:
+                best, idx = st[c, 1], c
+        return best, (st[idx, 2:5].copy() if idx >= 0 else None), idx
+
+    def pose_covariance(self):
+        """Node::updatePose's packing of set->cov into the 6x6 message covariance (node.cpp:381-395)"""
+        s = self.set_stats()
+        cov = np.zeros((6, 6))
+        cov[0, 0], cov[0, 1], cov[1, 0], cov[1, 1], cov[5, 5] = s[3], s[4], s[5], s[6], s[7]
+        return cov
 
 
 class PortPF(_PFBase):

@@ -74,6 +74,24 @@ class OdomData(C.Structure):
     _fields_ = [("pose", C.c_double * 3), ("delta", C.c_double * 3), ("absolute_motion", C.c_double * 3)]
 
 
+def scan_from_laserscan(msg_ranges, msg_range_min, msg_range_max, angle_min, angle_increment, sensor_min_range=-1.0,
+                        sensor_max_range=-1.0):
+    """Node2D::updateLatestScanData (node_2d.cpp:534-560) -> (ranges f64, angles f64, range_max)"""
+    r = np.ascontiguousarray(msg_ranges, np.float32)
+    ranges, angles, rmax = np.empty(len(r)), np.empty(len(r)), C.c_double()
+    _check(lib().bamcl_scan_from_laserscan(_p(r), len(r), msg_range_min, msg_range_max, sensor_min_range, sensor_max_range,
+                                           angle_min, angle_increment, _p(ranges), _p(angles), C.byref(rmax)))
+    return ranges, angles, rmax.value
+
+
+def cloud_subsample(xyz, max_beams):
+    """Node3D::updateLatestScanData (node_3d.cpp:467-480): stride sub-sampling of an (n, 3) float32 cloud"""
+    xyz = np.ascontiguousarray(xyz, np.float32)
+    out, n = np.empty_like(xyz), C.c_long()
+    _check(lib().bamcl_cloud_subsample(_p(xyz), len(xyz), max_beams, _p(out), len(out), C.byref(n)))
+    return out[:n.value].copy()
+
+
 def planar_model(model_type=MODEL_LF, max_beams=60, z_hit=0.95, z_short=0.1, z_max=0.05, z_rand=0.05, sigma_hit=0.2,
                  lambda_short=0.1, gompertz=(1.0, 1.0, 1.0, 0.0, 1.0, 0.0), do_beamskip=False, beam_skip_distance=0.5,
                  beam_skip_threshold=0.3, beam_skip_error_threshold=0.9, off_map_factor=1.0, non_free_space_factor=1.0,
@@ -160,6 +178,11 @@ SIGNATURES = {
     "bamcl_pf_leaf_count": (_I, [_P, _P]),
     "bamcl_pf_update_action": (_I, [_P, _P, _P, C.c_uint64, _P]),
     "bamcl_pf_max_weight_pose": (_I, [_P, _P, _P, _P]),
+    "bamcl_map2d_from_occupancy_grid": (_I, [_P, _P, _I, _I, _D, _D, _D, _I, _P]),
+    "bamcl_map2d_download_cells": (_I, [_P, _P, _L]),
+    "bamcl_map2d_geometry": (_I, [_P, _P, _P, _P]),
+    "bamcl_scan_from_laserscan": (_I, [_P, _I, C.c_float, C.c_float, _D, _D, _D, _D, _P, _P, _P]),
+    "bamcl_cloud_subsample": (_I, [_P, _L, _I, _P, _L, _P]),
     "bamcl_map2d_update_free_space": (_I, [_P, _D, _P]),
     "bamcl_map2d_download_free_space": (_I, [_P, _P, _L]),
     "bamcl_pf_init_uniform": (_I, [_P, _P, _D, _D, C.c_uint64, _P, _P]),
@@ -252,6 +275,26 @@ class Map2D:
         self.h = h
         if cells.size:
             _check(self.L.bamcl_map2d_set_cells(self.h, _p(cells), cells.size))
+
+    @classmethod
+    def from_occupancy_grid(cls, ctx, data, resolution, origin_xy=(0.0, 0.0), scale_up=1):
+        """Node2D::convertMap (node_2d.cpp:265-295): data = (height, width) int8 OccupancyGrid payload"""
+        data = np.ascontiguousarray(data, np.int8)
+        self = cls.__new__(cls)
+        self.L, self.ctx = lib(), ctx
+        h = C.c_void_p()
+        _check(self.L.bamcl_map2d_from_occupancy_grid(ctx.h, _p(data), data.shape[1], data.shape[0], resolution,
+                                                      origin_xy[0], origin_xy[1], scale_up, C.byref(h)))
+        self.h = h
+        size, res, org = (C.c_int * 2)(), C.c_double(), (C.c_float * 2)()
+        _check(self.L.bamcl_map2d_geometry(self.h, size, C.byref(res), org))
+        self.size_x, self.size_y, self.resolution, self.origin = size[0], size[1], res.value, (org[0], org[1])
+        return self
+
+    def cells(self):
+        out = np.empty((self.size_y, self.size_x), np.int8)
+        _check(self.L.bamcl_map2d_download_cells(self.h, _p(out), out.size))
+        return out
 
     def close(self):
         if self.h:

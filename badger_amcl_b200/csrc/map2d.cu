@@ -389,3 +389,83 @@ int bamcl_map2d_calc_range(bamcl_map2d* m, const double* ox, const double* oy, c
 }
 
 }  // extern "C"
+
+// ---- Node2D::convertMap (src/amcl/node/node_2d.cpp:265-295): OccupancyGrid message -> cell states, with the integer
+// up-scaling done on the device so that only width x height bytes cross PCIe
+namespace
+{
+__global__ void __launch_bounds__(256) k_convert_grid(const signed char* __restrict__ data, int width, int scale, int size_x,
+                                                      int size_y, signed char* __restrict__ cells)
+{
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (long)size_x * size_y)
+    return;
+  const int y = (int)(t / size_x), x = (int)(t % size_x);
+  const signed char v = data[(size_t)(y / scale) * width + x / scale];
+  cells[t] = v == 0 ? -1 : (v == 100 ? 1 : 0);  // CELL_FREE / CELL_OCCUPIED / CELL_UNKNOWN (map.h)
+}
+}  // namespace
+
+extern "C" int bamcl_map2d_from_occupancy_grid(bamcl_ctx* ctx, const int8_t* data, int width, int height, double resolution,
+                                               double origin_x, double origin_y, int scale_up, bamcl_map2d** out)
+{
+  if (!ctx || !data || !out || width <= 0 || height <= 0 || scale_up < 1 || !(resolution > 0.0))
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_from_occupancy_grid: bad arguments");
+  if ((long)width * scale_up > 0x7fffffffl || (long)height * scale_up > 0x7fffffffl)
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_from_occupancy_grid: scaled size overflows int");
+  const double res = resolution / scale_up;  // :267
+  const int size_x = width * scale_up, size_y = height * scale_up;
+  const double x_origin = origin_x + (size_x / 2) * res;  // :275-276, narrowed to float by pcl::PointXYZ (:277)
+  const double y_origin = origin_y + (size_y / 2) * res;
+  bamcl_map2d* m = nullptr;
+  BAMCL_TRY(bamcl_map2d_create(ctx, size_x, size_y, res, (float)x_origin, (float)y_origin, &m));
+  auto body = [&]() -> int {
+    const size_t n = (size_t)size_x * size_y, n_msg = (size_t)width * height;
+    bamcl::DevBuf msg;
+    BAMCL_TRY(msg.reserve(n_msg));
+    int rc = m->cells.reserve(n);
+    if (rc == BAMCL_OK && cudaMemcpyAsync(msg.p, data, n_msg, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess)
+      rc = set_error(BAMCL_E_CUDA, "bamcl_map2d_from_occupancy_grid: upload failed");
+    if (rc == BAMCL_OK)
+    {
+      k_convert_grid<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(msg.as<signed char>(), width, scale_up, size_x,
+                                                                           size_y, m->cells.as<signed char>());
+      ctx->launches++;
+      m->has_cells = true;
+      rc = build_blocked_bits(m);
+    }
+    if (rc == BAMCL_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+      rc = set_error(BAMCL_E_CUDA, "bamcl_map2d_from_occupancy_grid: %s", cudaGetErrorString(cudaGetLastError()));
+    msg.release();
+    return rc;
+  };
+  const int rc = body();
+  if (rc != BAMCL_OK)
+  {
+    bamcl_map2d_destroy(m);
+    return rc;
+  }
+  *out = m;
+  return BAMCL_OK;
+}
+
+extern "C" int bamcl_map2d_download_cells(bamcl_map2d* m, int8_t* cells, long n)
+{
+  if (!m || !cells || !m->has_cells || n != (long)m->size_x * m->size_y)
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_download_cells: need size_x*size_y cells of a map that has them");
+  BAMCL_CUDA_OK(cudaMemcpyAsync(cells, m->cells.p, (size_t)n, cudaMemcpyDeviceToHost, m->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(m->ctx->stream));
+  return BAMCL_OK;
+}
+
+extern "C" int bamcl_map2d_geometry(bamcl_map2d* m, int* size_xy, double* resolution, float* origin_xy)
+{
+  if (!m || !size_xy || !resolution || !origin_xy)
+    return set_error(BAMCL_E_ARG, "bamcl_map2d_geometry: null argument");
+  size_xy[0] = m->size_x;
+  size_xy[1] = m->size_y;
+  *resolution = m->resolution;
+  origin_xy[0] = m->origin_x;
+  origin_xy[1] = m->origin_y;
+  return BAMCL_OK;
+}

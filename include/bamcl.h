@@ -312,6 +312,26 @@ typedef struct bamcl_odom_data /* OdomData, odom.h:43-52 */
 int bamcl_pf_update_action(bamcl_pf* pf, const bamcl_odom_model* model, const bamcl_odom_data* data,
                            uint64_t drand48_state, uint64_t* drand48_state_out);
 
+/* ---- scan / map ingestion */
+/* Node2D::convertMap (node_2d.cpp:265-295): nav_msgs/OccupancyGrid (data row-major, width x height, 0 free / 100
+ * occupied / anything else unknown) -> a map of (width x scale_up) x (height x scale_up) cells at resolution / scale_up
+ * with the origin moved to the map centre (:275-277, narrowed to float as pcl::PointXYZ does). The message bytes are
+ * uploaded once and expanded on the device. */
+int bamcl_map2d_from_occupancy_grid(bamcl_ctx* ctx, const int8_t* data, int width, int height, double resolution,
+                                    double origin_x, double origin_y, int scale_up, bamcl_map2d** out);
+/* cell states back to the host (-1 free, 0 unknown, +1 occupied; index = i + j*size_x), and the map's geometry */
+int bamcl_map2d_download_cells(bamcl_map2d* m, int8_t* cells, long n);
+int bamcl_map2d_geometry(bamcl_map2d* m, int* size_xy, double* resolution, float* origin_xy);
+/* Node2D::updateLatestScanData (node_2d.cpp:534-560): sensor_msgs/LaserScan ranges (float) -> PlanarData ranges_ /
+ * angles_ / range_max_ (double): min/max thresholds applied in float (:538-546), readings <= range_min mapped to
+ * range_max (:551-556), bearing = angle_min + i * angle_increment (:558). Host arithmetic, no GPU work. */
+int bamcl_scan_from_laserscan(const float* msg_ranges, int range_count, float msg_range_min, float msg_range_max,
+                              double sensor_min_range, double sensor_max_range, double angle_min, double angle_increment,
+                              double* ranges_out, double* angles_out, double* range_max_out);
+/* Node3D::updateLatestScanData (node_3d.cpp:467-480): every step-th point, step = max((count-1)/(max_beams-1), 1);
+ * xyz / xyz_out are packed float triples. Host arithmetic, no GPU work. */
+int bamcl_cloud_subsample(const float* xyz, long data_count, int max_beams, float* xyz_out, long capacity, long* n_out);
+
 /* ---- global localisation */
 /* Node2D::updateFreeSpaceIndices (node_2d.cpp:320-338): the (i, j) of every CELL_FREE cell whose cached distance exceeds
  * non_free_space_radius, in the reference's order (i outer, j inner), kept on the device; count_out =

@@ -786,3 +786,44 @@ def cloud_model(model_type=0, max_beams=4096, z_hit=0.95, z_rand=0.05, sigma_hit
     p.mount_translation[:] = mount_translation
     p.mount_rotation[:] = mount_rotation
     return p
+
+
+# ---------------------------------------------------------------- ingestion (node_2d.cpp / node_3d.cpp)
+# The node translation units are ROS nodes and cannot be compiled here: these numpy restatements are PARITY UNPINNED
+# (no reference test or golden vector covers them); they follow the cited lines statement by statement.
+def convert_map(data, resolution, origin_xy, scale_up=1):
+    """Node2D::convertMap (node_2d.cpp:265-295) -> (cells (size_y, size_x) int8, resolution, (origin_x, origin_y) f32)"""
+    data = np.asarray(data, np.int8)
+    height, width = data.shape
+    res = resolution / scale_up
+    size_x, size_y = width * scale_up, height * scale_up
+    ox = np.float32(origin_xy[0] + (size_x // 2) * res)
+    oy = np.float32(origin_xy[1] + (size_y // 2) * res)
+    cells = np.empty((size_y, size_x), np.int8)
+    for y in range(size_y):
+        row = data[y // scale_up]
+        v = row[np.arange(size_x) // scale_up]
+        cells[y] = np.where(v == 0, -1, np.where(v == 100, 1, 0))
+    return cells, res, (ox, oy)
+
+
+def scan_from_laserscan(msg_ranges, msg_range_min, msg_range_max, angle_min, angle_increment, sensor_min_range=-1.0,
+                        sensor_max_range=-1.0):
+    """Node2D::updateLatestScanData (node_2d.cpp:534-560); message fields are float32"""
+    r = np.asarray(msg_ranges, np.float32)
+    rmin_msg, rmax_msg = np.float32(msg_range_min), np.float32(msg_range_max)
+    range_max = float(min(rmax_msg, np.float32(sensor_max_range))) if sensor_max_range > 0.0 else float(rmax_msg)
+    range_min = float(max(rmin_msg, np.float32(sensor_min_range))) if sensor_min_range > 0.0 else float(rmin_msg)
+    ranges, angles = np.empty(len(r)), np.empty(len(r))
+    for i in range(len(r)):
+        ranges[i] = range_max if float(r[i]) <= range_min else float(r[i])
+        angles[i] = angle_min + (i * angle_increment)
+    return ranges, angles, range_max
+
+
+def cloud_subsample(xyz, max_beams):
+    """Node3D::updateLatestScanData (node_3d.cpp:467-480)"""
+    xyz = np.asarray(xyz, np.float32)
+    count = len(xyz)
+    step = max(int((count - 1) / (max_beams - 1)), 1)  # C integer division truncates toward zero
+    return xyz[0:count:step].copy()

@@ -85,6 +85,11 @@ public:
   std::shared_ptr<PFSampleSet> peekCurrentSet();  // up-to-date mirror, read-only contract
   bamcl_pf* deviceHandle() { return dev_; }
   void pushIfHostDirty();                         // upload the mirror if the caller may have modified it
+  void markDeviceModified()                       // a device operation changed the set: the host mirror is stale
+  {
+    host_valid_ = false;
+    host_dirty_ = false;
+  }
   int resampleLimit(int k);                       // particle_filter.cpp:475-502
   double slowAverage() const { return w_slow_; }
   double fastAverage() const { return w_fast_; }

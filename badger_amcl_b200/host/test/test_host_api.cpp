@@ -8,7 +8,9 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstdint>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -16,6 +18,7 @@
 #include "amcl/map/octomap.h"
 #include "amcl/pf/particle_filter.h"
 #include "amcl/pf/pdf_gaussian.h"
+#include "amcl/sensors/odom.h"
 #include "amcl/sensors/planar_scanner.h"
 #include "amcl/sensors/point_cloud_scanner.h"
 
@@ -303,6 +306,60 @@ static int flow(const char* in_path, const char* out_path)
   return g_failed ? 1 : 0;
 }
 
+// "odom" mode: initWithPoseFn + three Odom::updateAction calls (models from the input) through the mirror's class API;
+// writes the moved samples and the next drand48() value after every call
+static int odomFlow(const char* in_path, const char* out_path)
+{
+  FILE* f = std::fopen(in_path, "rb");
+  if (!f)
+    return 2;
+  int hdr[3];  // n, seed, number of updates
+  if (std::fread(hdr, sizeof(int), 3, f) != 3)
+    return 2;
+  const int n = hdr[0], seed = hdr[1], updates = hdr[2];
+  std::vector<double> poses((size_t)3 * n), par((size_t)15 * updates);  // per update: model, alpha[5], pose, delta, abs
+  if (std::fread(poses.data(), sizeof(double), poses.size(), f) != poses.size() ||
+      std::fread(par.data(), sizeof(double), par.size(), f) != par.size())
+    return 2;
+  std::fclose(f);
+  size_t next_pose = 0;
+  auto pose_fn = [&]() {
+    const size_t k = (next_pose++) % (size_t)n;
+    return Eigen::Vector3d(poses[3 * k], poses[3 * k + 1], poses[3 * k + 2]);
+  };
+  auto pf = std::make_shared<badger_amcl::ParticleFilter>(n / 10, n, 0.001, 0.1, 95.0, pose_fn);
+  pf->initWithPoseFn(pose_fn);
+  srand48(seed);
+  FILE* out = std::fopen(out_path, "wb");
+  if (!out)
+    return 2;
+  badger_amcl::Odom odom;
+  for (int u = 0; u < updates; u++)
+  {
+    const double* p = &par[(size_t)15 * u];
+    odom.setModel(static_cast<badger_amcl::OdomModelType>((int)p[0]), p[1], p[2], p[3], p[4], p[5]);
+    auto data = std::make_shared<badger_amcl::OdomData>();
+    for (int k = 0; k < 3; k++)
+    {
+      data->pose[k] = p[6 + k];
+      data->delta[k] = p[9 + k];
+      data->absolute_motion[k] = p[12 + k];
+    }
+    EXPECT_TRUE(odom.updateAction(pf, data));
+    auto set = pf->peekCurrentSet();
+    std::fwrite(set->samples.data(), sizeof(double), (size_t)4 * set->sample_count, out);
+    // peek at libc's stream without consuming it: the next value the host would draw
+    unsigned short zero[3] = {0, 0, 0};
+    unsigned short* prev = seed48(zero);
+    unsigned short saved[3] = {prev[0], prev[1], prev[2]};
+    seed48(saved);
+    const double state = (double)((uint64_t)saved[0] | ((uint64_t)saved[1] << 16) | ((uint64_t)saved[2] << 32));
+    std::fwrite(&state, sizeof(double), 1, out);
+  }
+  std::fclose(out);
+  return g_failed ? 1 : 0;
+}
+
 int main(int argc, char** argv)
 {
   const std::string mode = argc > 1 ? argv[1] : "kats";
@@ -310,6 +367,8 @@ int main(int argc, char** argv)
   {
     if (mode == "flow" && argc == 4)
       return flow(argv[2], argv[3]);
+    if (mode == "odom" && argc == 4)
+      return odomFlow(argv[2], argv[3]);
     testPfKdtree();
     testOctoMapConversions();
     testOccupancyMapConversions();

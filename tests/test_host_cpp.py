@@ -96,3 +96,35 @@ def test_flow_through_the_class_api_matches_oracle(exe, oracle_built, tmp_path, 
         moved[:, 0] += 0.01
         port.set_samples(moved)
     assert pos == len(got)
+
+
+@pytest.mark.gpu
+def test_odom_update_action_through_the_class_api_matches_oracle(exe, oracle_built, tmp_path):
+    """the mirror's Odom::updateAction (host/src/odom.cpp -> bamcl_pf_update_action) against the oracle's restatement of
+    odom.cpp:74-311: libc's drand48 state after every call bit-exact, poses to 1e-12 (device log / sincos)"""
+    O = oracle_built
+    n, seed = 4000, 99
+    poses = synth.gaussian_poses((1.0, -2.0, 0.5), n, seed=3)
+    updates = [(1, [0.2, 0.3, 0.25, 0.15, 0.1], [1.0, 2.0, 0.7], [0.3, 0.1, 0.2], [0.35, 0.05, 0.25]),
+               (2, [0.1, 0.2, 0.3, 0.1, 0.0], [1.3, 2.1, 0.9], [0.001, 0.0, 1.5], [0.0, 0.0, 0.0]),
+               (4, [0.2, 0.3, 0.25, 0.15, 0.1], [0.9, 2.3, -2.1], [-0.4, 0.2, -3.0], [0.45, 0.1, 3.0])]
+    fin, fout = str(tmp_path / "odom_in.bin"), str(tmp_path / "odom_out.bin")
+    with open(fin, "wb") as f:
+        f.write(struct.pack("<3i", n, seed, len(updates)))
+        f.write(np.ascontiguousarray(poses, np.float64).tobytes())
+        for mt, alpha, pose, delta, am in updates:
+            f.write(np.array([mt] + alpha + pose + delta + am, np.float64).tobytes())
+    p = subprocess.run([exe, "odom", fin, fout], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    got = np.fromfile(fout, np.float64).reshape(len(updates), 4 * n + 1)
+    port = O.PortPF(n // 10, n)
+    port.init_with_poses(poses)
+    port.srand48(seed)
+    for u, (mt, alpha, pose, delta, am) in enumerate(updates):
+        port.update_action(mt, alpha, pose, delta, am)
+        s = got[u, :4 * n].reshape(n, 4)
+        assert int(got[u, 4 * n]) == port.rng.x
+        assert np.abs(s[:, :3] - port.samples()[:, :3]).max() <= 1e-12
+        assert np.array_equal(s[:, 3], port.samples()[:, 3])
+        # continue from the device's poses so that rounding differences do not accumulate in the comparison
+        port.set_samples(s)

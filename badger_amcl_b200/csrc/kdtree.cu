@@ -716,7 +716,9 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       static const bool cc_volatile = getenv("BAMCL_CC_VOLATILE") != nullptr;  // A/B switch: forest reads bypass L1
       // (Measured and dropped: collecting the neighbour pairs first and uniting them in a second, dense launch. The
       // unions then all contend at once: 0.73 ms for ~1M pairs against 0.38 ms for this kernel with the unions spread
-      // over the probes.)
+      // over the probes. Also measured and dropped: one thread per node with its 13 probes issued together and its own
+      // root carried through the unions (the ECL-CC shape) -- resample 1.14 ms against 0.89 ms at 1M samples / 243k
+      // bins: 13x fewer threads leave the forest walks latency-bound.)
       if (cc_volatile)
         BAMCL_LAUNCH(ctx, k_cc_union<false>, (unsigned)((threads + 255) / 256), 256, 0, out,
                      pf->t_nkey.as<unsigned long long>(), pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), hmask,

@@ -327,6 +327,17 @@ def run_b200_arm(a):
     e_rows = [step_e2e() for _ in range(a.steps)]
     barrier()
     clocks = sampler.stop()
+    # the step before the path, reported beside the metric, not inside it
+    motion_ms = None
+    if sf is None:
+        pf.srand48(1)
+        ts = []
+        for _ in range(4):
+            ctx.sync()
+            ctx.timer_start()
+            pf.update_action(cabi.ODOM_DIFF_CORRECTED, [0.2, 0.2, 0.2, 0.2, 0.2], [1.0, 2.0, 0.7], [0.3, 0.1, 0.2])
+            ts.append(ctx.timer_stop_ms())
+        motion_ms = float(np.median(ts[1:]))
     e_ms = float(np.sum([r[0] for r in e_rows]))
     n_out = int(e_rows[-1][1])
 
@@ -361,7 +372,8 @@ def run_b200_arm(a):
                        "l2": "flushed (256 MiB write) before every timed step",
                        "update_ms": up / a.steps, "resample_ms": rs / a.steps, "edt_build_ms": edt_ms,
                        "resampled_count": int(last.sample_count), "kld_leaf_count": int(last.leaf_count),
-                       "clusters": int(last.cluster_count)},
+                       "clusters": int(last.cluster_count),
+                       "motion_update_ms_not_in_metric": motion_ms},
             "e2e": {"value": e_value, "unit": "evals/s", "ms_per_step": e_total_ms / a.steps,
                     "h2d_bytes_per_step": int(cnt0 * 32 + 2 * B * 8) * world,
                     "d2h_bytes_per_step": int(n_out * 32 + 8 + 96) * world},

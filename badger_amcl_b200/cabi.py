@@ -178,6 +178,7 @@ SIGNATURES = {
     "bamcl_pf_leaf_count": (_I, [_P, _P]),
     "bamcl_pf_update_action": (_I, [_P, _P, _P, C.c_uint64, _P]),
     "bamcl_pf_max_weight_pose": (_I, [_P, _P, _P, _P]),
+    "bamcl_pf_set_random_pose_source": (_I, [_P, _P, _D, _D]),
     "bamcl_map2d_from_occupancy_grid": (_I, [_P, _P, _I, _I, _D, _D, _D, _I, _P]),
     "bamcl_map2d_download_cells": (_I, [_P, _P, _L]),
     "bamcl_map2d_geometry": (_I, [_P, _P, _P, _P]),
@@ -455,6 +456,11 @@ class ParticleFilter:
         self.converged = False
         self.last = res
         return res
+
+    def set_random_pose_source(self, map2d, threshold=0.0, multiplier=0.0):
+        """random_pose_fn_ = Node::uniformPoseGenerator over map2d's free-space list (node.cpp:262-264, 847-868)"""
+        _check(self.L.bamcl_pf_set_random_pose_source(self.h, map2d.h if map2d is not None else None, threshold, multiplier))
+        self.device_pose_source = map2d is not None
 
     def init_with_current(self):
         """kd-tree + cluster statistics of the samples already on the device (bamcl_pf_init_stats)."""

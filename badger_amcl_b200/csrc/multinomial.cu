@@ -13,8 +13,12 @@
 //      (SURVEY H2): two +-1 events per node on the sample time line and one prefix sum;
 //   4. the smallest m with m > resampleLimit(leaf(m)), else max_samples: the new set is the first m candidates;
 //   5. tree, clusters and statistics of those m samples as for any new set.
-// w_diff > 0 interleaves random_pose_fn_() -- host code that itself calls drand48 (node.cpp:831,837) -- with the
-// resampler's draws one output at a time; that order cannot be reproduced from the device and is refused.
+// w_diff > 0 interleaves random_pose_fn_() with the resampler's draws one output at a time. The node's pose function is
+// Node::uniformPoseGenerator (node.cpp:262-264), which itself takes a fixed number g = 2 (1 + retries) of drand48
+// values per pose (init.cu). With bamcl_pf_set_random_pose_source the device replays that too: output k starts at
+// stream position p_k, p_0 = 0, p_{k+1} = p_k + (draw p_k + 1 < w_diff ? 1 + g : 2). All p_k at once by binary lifting:
+// next[p] for every position, level_{j+1} = level_j o level_j, and p_k = the composition of the levels of k's set bits
+// (powers of one function commute). Without a registered source (an arbitrary host callback) the case is refused.
 #include <cmath>
 #include <cstring>
 
@@ -44,6 +48,14 @@ struct MultiArgs
   int n;
   unsigned long long state0;
   int* flags;
+  // random-pose injection (w_diff > 0): stream position of every output, the free-space list and the map geometry
+  const int* pos;  // null: output k starts at position 2k
+  double w_diff;
+  int retries;  // generations thrown away per random pose (uniformPoseGenerator's de-weighting loop)
+  const int2* free_ij;
+  long free_n;
+  int size_x, size_y;
+  double resolution, origin_x, origin_y;
 };
 
 __global__ void __launch_bounds__(256) k_select_multinomial(const MultiArgs a)
@@ -51,8 +63,23 @@ __global__ void __launch_bounds__(256) k_select_multinomial(const MultiArgs a)
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= a.n)
     return;
-  const unsigned long long x = lcg_skip(a.state0, 2ull * (unsigned long long)k + 2ull);
-  const double r = scalbn((double)x, -48);  // drand48: X / 2^48, exact
+  const unsigned long long p = a.pos ? (unsigned long long)a.pos[k] : 2ull * (unsigned long long)k;
+  const unsigned long long x1 = lcg_skip(a.state0, p + 1ull);  // :385
+  if (a.w_diff > 0.0 && (double)x1 * 0x1p-48 < a.w_diff)
+  {
+    // random_pose_fn_() = the last of (1 + retries) randomFreeSpacePose generations (node.cpp:823-868)
+    const unsigned long long u = lcg_skip(a.state0, p + 2ull + 2ull * (unsigned long long)a.retries), v = lcg_next(u);
+    const unsigned int cell = (unsigned int)((double)u * 0x1p-48 * (double)(size_t)a.free_n);
+    const int2 c = a.free_ij[cell];
+    a.src[k] = -1;
+    a.bx[k] = a.origin_x + (c.x - a.size_x / 2) * a.resolution;
+    a.by[k] = a.origin_y + (c.y - a.size_y / 2) * a.resolution;
+    a.bth[k] = (double)v * 0x1p-48 * 2 * M_PI - M_PI;
+    a.bw[k] = 1.0;
+    return;
+  }
+  const unsigned long long x = lcg_next(x1);
+  const double r = scalbn((double)x, -48);  // drand48: X / 2^48, exact (:393)
   int L = 0, H = a.P;  // first i with c[i] <= r < c[i+1] == number of entries of c[1..P] that are <= r
   while (L < H)
   {
@@ -85,6 +112,43 @@ __global__ void __launch_bounds__(256) k_select_multinomial(const MultiArgs a)
   a.by[k] = a.ay[j];
   a.bth[k] = a.ath[j];
   a.bw[k] = 1.0;
+}
+
+// next[p] = stream position after the output that starts at p; positions >= n_pos collapse into the sentinel n_pos
+__global__ void __launch_bounds__(256) k_mn_next(unsigned long long state0, double w_diff, int token_random, int n_pos,
+                                                 int* __restrict__ next)
+{
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p > n_pos)
+    return;
+  if (p == n_pos)
+  {
+    next[p] = n_pos;
+    return;
+  }
+  const unsigned long long x = lcg_skip(state0, (unsigned long long)p + 1ull);
+  const long long q = (long long)p + ((double)x * 0x1p-48 < w_diff ? token_random : 2);
+  next[p] = q >= n_pos ? n_pos : (int)q;
+}
+__global__ void __launch_bounds__(256) k_mn_apply(int* __restrict__ cur, const int* __restrict__ level, int bit, int n)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n && ((k >> bit) & 1))
+    cur[k] = level[cur[k]];
+}
+__global__ void __launch_bounds__(256) k_mn_square(const int* __restrict__ in, int* __restrict__ out, int n)
+{
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < n)
+    out[p] = in[in[p]];
+}
+__global__ void __launch_bounds__(256) k_count_random(const int* __restrict__ src, int n, int* __restrict__ out)
+{
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool r = k < n && src[k] < 0;
+  const unsigned m = __ballot_sync(0xffffffffu, r);
+  if ((threadIdx.x & 31) == 0 && m)
+    atomicAdd(out, __popc(m));
 }
 
 // +1 at the sample that created node v, -1 at the sample that created v's first child
@@ -141,10 +205,23 @@ namespace bamcl
 {
 int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res)
 {
-  if (prm->w_diff > 0.0)
+  const bool inject = prm->w_diff > 0.0;
+  if (inject && (!pf->rp_map || pf->rp_map->free_count <= 0))
     return set_error(BAMCL_E_UNSUPPORTED,
                      "multinomial resampling with w_diff > 0 interleaves random_pose_fn_() with the resampler's drand48 "
-                     "draws one output at a time (particle_filter.cpp:385-387); use the systematic model");
+                     "draws one output at a time (particle_filter.cpp:385-387): register the node's pose function with "
+                     "bamcl_pf_set_random_pose_source (map with a free-space list), or use the systematic model");
+  long retries = 0;
+  if (inject && pf->rp_threshold > 0.0 && pf->rp_multiplier < 1.0 && pf->rp_multiplier >= 0.0)
+  {
+    double good = pf->rp_threshold;  // node.cpp:849-866 with scorePose == 1.0 (init.cu)
+    while (1.0 < good)
+    {
+      good *= pf->rp_multiplier;
+      if (++retries > 1000000)
+        return set_error(BAMCL_E_UNSUPPORTED, "resample: more than 1e6 de-weighting retries per random pose");
+    }
+  }
   bamcl_ctx* ctx = pf->ctx;
   SampleSet& set_a = pf->sets[pf->current];
   SampleSet& set_b = pf->sets[1 - pf->current];
@@ -166,8 +243,61 @@ int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
   a.bw = set_b.w.as<double>();
   a.src = pf->src.as<int>();
   a.n = n;
-  a.state0 = prm->drand48_state;
+  a.state0 = prm->drand48_state & LCG_MASK;
   a.flags = pf_flags(pf);
+  a.pos = nullptr;
+  a.w_diff = 0.0;
+  a.retries = 0;
+  a.free_ij = nullptr;
+  a.free_n = 0;
+  a.size_x = a.size_y = 0;
+  a.resolution = a.origin_x = a.origin_y = 0.0;
+  int* d_pos = nullptr;
+  if (inject)
+  {
+    // stream position of every output (and of "output n" = the draws n outputs consume) by binary lifting
+    const long long token = 1 + 2 * (1 + retries);
+    const long long worst = (long long)n * token + 2;
+    long long n_pos = (long long)std::ceil((double)n * (2.0 + prm->w_diff * (double)(token - 2)) * 1.05) + 4096 + token;
+    if (n_pos > worst)
+      n_pos = worst;
+    for (;;)
+    {
+      if (n_pos > 0x7ffffff0ll)
+        return set_error(BAMCL_E_UNSUPPORTED, "resample: drand48 stream positions exceed 2^31");
+      BAMCL_TRY(pf->mn_buf.reserve(sizeof(int) * ((size_t)(n + 1) + 2 * (size_t)(n_pos + 1) + 8)));
+      d_pos = pf->mn_buf.as<int>();
+      int* level[2] = {d_pos + n + 1, d_pos + n + 1 + n_pos + 1};
+      BAMCL_CUDA_OK(cudaMemsetAsync(d_pos, 0, sizeof(int) * ((size_t)n + 1), ctx->stream));
+      const unsigned pb = (unsigned)((n_pos + 1 + 255) / 256), kb = (unsigned)((n + 1 + 255) / 256);
+      BAMCL_LAUNCH(ctx, k_mn_next, pb, 256, 0, a.state0, prm->w_diff, (int)token, (int)n_pos, level[0]);
+      int bits = 0;
+      while ((1ll << bits) <= (long long)n)
+        bits++;
+      for (int j = 0; j < bits; j++)
+      {
+        BAMCL_LAUNCH(ctx, k_mn_apply, kb, 256, 0, d_pos, level[j & 1], j, n + 1);
+        if (j + 1 < bits)
+          BAMCL_LAUNCH(ctx, k_mn_square, pb, 256, 0, level[j & 1], level[(j + 1) & 1], (int)n_pos + 1);
+      }
+      int h_end = 0;
+      BAMCL_CUDA_OK(cudaMemcpyAsync(&h_end, d_pos + n, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+      BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+      if (h_end < n_pos || n_pos == worst)
+        break;
+      n_pos = worst;  // more random poses than the margin allowed for: the worst case always fits
+    }
+    a.pos = d_pos;
+    a.w_diff = prm->w_diff;
+    a.retries = (int)retries;
+    a.free_ij = pf->rp_map->free_ij.as<int2>();
+    a.free_n = pf->rp_map->free_count;
+    a.size_x = pf->rp_map->size_x;
+    a.size_y = pf->rp_map->size_y;
+    a.resolution = pf->rp_map->resolution;
+    a.origin_x = (double)pf->rp_map->origin_x;
+    a.origin_y = (double)pf->rp_map->origin_y;
+  }
   BAMCL_LAUNCH(ctx, k_select_multinomial, (n + 255) / 256, 256, 0, a);
 
   // tree of all candidates with every node's first foreign key kept (general build)
@@ -211,7 +341,31 @@ int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
   res->sample_count = count;
   res->random_poses_used = 0;
   res->status_flags = flags & 1;
-  res->drand48_state = lcg_skip(prm->drand48_state, 2ull * (unsigned long long)count);
+  unsigned long long consumed = 2ull * (unsigned long long)count;
+  if (inject)
+  {
+    int* d_cnt = stop + 2;
+    int h[2] = {0, 0};
+    BAMCL_CUDA_OK(cudaMemsetAsync(d_cnt, 0, sizeof(int), ctx->stream));
+    BAMCL_LAUNCH(ctx, k_count_random, (count + 255) / 256, 256, 0, pf->src.as<int>(), count, d_cnt);
+    BAMCL_CUDA_OK(cudaMemcpyAsync(&h[0], d_cnt, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    BAMCL_CUDA_OK(cudaMemcpyAsync(&h[1], d_pos + count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    res->random_poses_used = h[0];
+    consumed = (unsigned long long)h[1];
+  }
+  res->drand48_state = lcg_skip(a.state0, consumed);
   return BAMCL_OK;
 }
 }  // namespace bamcl
+
+extern "C" int bamcl_pf_set_random_pose_source(bamcl_pf* pf, bamcl_map2d* map_or_null, double starting_weight_threshold,
+                                               double deweight_multiplier)
+{
+  if (!pf)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_set_random_pose_source: null filter");
+  pf->rp_map = map_or_null;
+  pf->rp_threshold = starting_weight_threshold;
+  pf->rp_multiplier = deweight_multiplier;
+  return BAMCL_OK;
+}

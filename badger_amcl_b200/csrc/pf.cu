@@ -249,6 +249,7 @@ int bamcl_pf_destroy(bamcl_pf* pf)
   pf->scratch2.release();
   pf->random_poses.release();
   pf->seg_buf.release();
+  pf->mn_buf.release();
   for (bamcl::DevBuf* b : {&pf->t_hkeys, &pf->t_hfirst, &pf->t_hnode, &pf->t_slot, &pf->t_flag, &pf->t_nkey, &pf->t_cur,
                            &pf->t_child, &pf->t_first_at, &pf->t_side, &pf->t_parent, &pf->t_cid, &pf->t_nfirst, &pf->t_root, &pf->t_scan,
                            &pf->t_out, &pf->t_sums, &pf->t_fast})

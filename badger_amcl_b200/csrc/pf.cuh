@@ -77,6 +77,11 @@ struct bamcl_pf
   bamcl::DevBuf scratch2;
   bamcl::DevBuf random_poses;
   bamcl::DevBuf seg_buf;   // systematic target segments
+  // multinomial resampling with random-pose injection: stream positions of the outputs + jump tables (multinomial.cu)
+  bamcl::DevBuf mn_buf;
+  // random_pose_fn_ = Node::uniformPoseGenerator over this map's free-space list (bamcl_pf_set_random_pose_source)
+  bamcl_map2d* rp_map = nullptr;
+  double rp_threshold = 0.0, rp_multiplier = 0.0;
   // kd-tree / clustering workspace (kdtree.cu), shared by both sets
   bamcl::DevBuf t_hkeys, t_hfirst, t_hnode;                 // hash table over pose bins
   bamcl::DevBuf t_slot, t_flag;                             // per sample

@@ -349,6 +349,14 @@ int bamcl_map2d_download_free_space(bamcl_map2d* m, int* ij_out, long n);
 int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double starting_weight_threshold, double deweight_multiplier,
                           uint64_t drand48_state, uint64_t* drand48_state_out, bamcl_resample_result* result);
 
+/* random_pose_fn_ of the filter (particle_filter.h:128; the node wires in Node::uniformPoseGenerator, node.cpp:262-264):
+ * registers `map`'s free-space list (bamcl_map2d_update_free_space) and the generator's two parameters, so that
+ * multinomial resampling with w_diff > 0 (particle_filter.cpp:385-388) draws its random poses on the device from the
+ * same drand48 stream, in the reference's order. NULL map = no source (that case is then BAMCL_E_UNSUPPORTED). The map
+ * must outlive the filter or be unregistered first. */
+int bamcl_pf_set_random_pose_source(bamcl_pf* pf, bamcl_map2d* map_or_null, double starting_weight_threshold,
+                                    double deweight_multiplier);
+
 /* ---- pose read-out */
 /* Node2D::getMaxWeightPose (node_2d.cpp:588-617): weight and mean pose of the first cluster with the greatest weight,
  * from the cluster statistics of the last resample / init, reduced on the device (no download of the cluster table).

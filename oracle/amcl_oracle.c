@@ -841,6 +841,11 @@ struct orc_pf
   int converged;
   double* random_poses;
   long random_n, random_next;
+  /* alternative random_pose_fn_: Node::uniformPoseGenerator over a free-space list, drawing from the resampler's rng */
+  const orc_map2d* uniform_map;
+  const int* uniform_free_ij;
+  long uniform_free_n;
+  double uniform_threshold, uniform_multiplier;
   int* last_src;
 };
 
@@ -906,9 +911,28 @@ void orc_pf_set_random_poses(orc_pf* pf, const double* poses, long n)
   pf->random_next = 0;
 }
 long orc_pf_random_poses_used(const orc_pf* pf) { return pf->random_next; }
-static void random_pose(orc_pf* pf, double out[3])
+void orc_uniform_poses(const orc_map2d* m, const int* free_ij, long free_n, orc_rng* rng, double starting_weight_threshold,
+                       double deweight_multiplier, long n, double* poses3);
+void orc_pf_set_uniform_pose_source(orc_pf* pf, const orc_map2d* m, const int* free_ij, long free_n, double threshold,
+                                    double multiplier)
+{
+  pf->uniform_map = m;
+  pf->uniform_free_ij = free_ij;
+  pf->uniform_free_n = free_n;
+  pf->uniform_threshold = threshold;
+  pf->uniform_multiplier = multiplier;
+  pf->random_next = 0;
+}
+static void random_pose(orc_pf* pf, orc_rng* rng, double out[3])
 {
   out[0] = out[1] = out[2] = 0.0;
+  if (pf->uniform_map)
+  {
+    orc_uniform_poses(pf->uniform_map, pf->uniform_free_ij, pf->uniform_free_n, rng, pf->uniform_threshold,
+                      pf->uniform_multiplier, 1, out);
+    pf->random_next++;
+    return;
+  }
   if (pf->random_next < pf->random_n)
   {
     memcpy(out, &pf->random_poses[3 * pf->random_next], sizeof(double) * 3);
@@ -1255,7 +1279,7 @@ static double resample_systematic(orc_pf* pf, double w_diff, orc_rng* rng)
   for (i = 0; i < num_random; ++i)
   {
     double* sb = &set_b->samples[4 * i];
-    random_pose(pf, sb);
+    random_pose(pf, rng, sb);
     sb[3] = 1.0;
     total += sb[3];
     orc_kdtree_insert(set_b->kdtree, sb, sb[3]);
@@ -1313,7 +1337,7 @@ static double resample_multinomial(orc_pf* pf, double w_diff, orc_rng* rng)
     double* sb = &set_b->samples[4 * out];
     if (orc_drand48(rng) < w_diff)
     {
-      random_pose(pf, sb);
+      random_pose(pf, rng, sb);
       pf->last_src[out] = -1;
     }
     else

@@ -102,6 +102,10 @@ void orc_pf_set_population_params(orc_pf* pf, double pop_err, double pop_z); /* 
 void orc_pf_set_decay_rates(orc_pf* pf, double a_slow, double a_fast);       /* :657-661 */
 void orc_pf_set_random_poses(orc_pf* pf, const double* poses, long n);       /* queue behind random_pose_fn_ */
 long orc_pf_random_poses_used(const orc_pf* pf);
+/* random_pose_fn_ = Node::uniformPoseGenerator (node.cpp:847-868) over free_ij, drawing from the rng handed to
+ * orc_pf_update_resample -- what the node wires in (node.cpp:262-264); the caller keeps m and free_ij alive */
+void orc_pf_set_uniform_pose_source(orc_pf* pf, const orc_map2d* m, const int* free_ij, long free_n, double threshold,
+                                    double multiplier);
 void orc_pf_init_with_poses(orc_pf* pf, const double* poses, long n);        /* initWithPoseFn :136-162 */
 int orc_pf_sample_count(const orc_pf* pf);
 void orc_pf_get_samples(const orc_pf* pf, double* aos);

@@ -100,6 +100,7 @@ def port_lib():
         sig = {
             "orc_pf_update_action": (None, [P, P, I, P, P, P, P]),
             "orc_map2d_free_space": (L_, [P, D, P]), "orc_uniform_poses": (None, [P, P, L_, P, D, D, L_, P]),
+            "orc_pf_set_uniform_pose_source": (None, [P, P, P, L_, D, D]),
             "orc_srand48": (None, [P, L_]), "orc_drand48": (D, [P]), "orc_gaussian_draw": (D, [P, D]),
             "orc_map2d_world_to_map": (None, [P, D, D, P, P]), "orc_map2d_map_to_world": (None, [P, I, I, P, P]),
             "orc_map2d_is_valid": (I, [P, I, I]), "orc_map2d_distance": (C.c_float, [P, I, I]),
@@ -155,6 +156,7 @@ def ref_lib():
         sig = {
             "ref_srand48": (None, [L_]), "ref_drand48": (D, []), "ref_seed48": (None, [P]), "ref_get_seed48": (None, [P]),
             "ref_gaussian_draw": (D, [D]),
+            "ref_pf_set_uniform_pose_source": (None, [P, P, P, L_, D, D]),
             "ref_pf_update_action": (None, [P, I, P, P, P, P]),
             "ref_map2d_create": (V, [D, I, I, F, F]), "ref_map2d_destroy": (None, [P]),
             "ref_map2d_set_cells": (None, [P, P, L_]), "ref_map2d_get_cell": (I, [P, I, I]),
@@ -448,6 +450,12 @@ class PortPF(_PFBase):
         p = np.ascontiguousarray(poses, np.float64)
         self.L.orc_pf_init_with_poses(self.h, _ptr(p), len(p))
 
+    def set_uniform_pose_source(self, port_map, free_ij, threshold=0.0, multiplier=0.0):
+        """random_pose_fn_ = Node::uniformPoseGenerator over the map's free-space list (node.cpp:262-264, 847-868)"""
+        self._uni = (port_map, np.ascontiguousarray(free_ij, np.int32))  # kept alive: the C side stores the pointers
+        self.L.orc_pf_set_uniform_pose_source(self.h, C.byref(port_map.s), _ptr(self._uni[1]), len(self._uni[1]),
+                                              threshold, multiplier)
+
     def sample_count(self):
         return self.L.orc_pf_sample_count(self.h)
 
@@ -540,6 +548,11 @@ class RefPF(_PFBase):
     def init_with_poses(self, poses):
         p = np.ascontiguousarray(poses, np.float64)
         self.L.ref_pf_init_with_poses(self.h, _ptr(p), len(p))
+
+    def set_uniform_pose_source(self, ref_map, free_ij, threshold=0.0, multiplier=0.0):
+        f = np.ascontiguousarray(free_ij, np.int32)
+        self._uni = ref_map
+        self.L.ref_pf_set_uniform_pose_source(self.h, ref_map.h, _ptr(f), len(f), threshold, multiplier)
 
     def sample_count(self):
         return self.L.ref_pf_sample_count(self.h)

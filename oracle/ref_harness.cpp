@@ -68,6 +68,11 @@ struct PF
   // queue of poses handed out by random_pose_fn_ (x, y, theta triples), consumed in order
   std::vector<double> random_poses;
   size_t random_next = 0;
+  // alternative source: Node::uniformPoseGenerator restated (node.cpp:823-868; the node sources cannot be compiled
+  // here) over a free-space list, drawing from the process-global drand48 stream like the node's pose function does
+  std::shared_ptr<OccupancyMap> uniform_map;
+  std::vector<int> free_ij;
+  double uniform_threshold = 0.0, uniform_multiplier = 0.0;
 };
 }  // namespace
 
@@ -391,6 +396,27 @@ void* ref_pf_create(int min_samples, int max_samples, double alpha_slow, double 
   PF* h = new PF();
   h->pf = std::make_shared<ParticleFilter>(min_samples, max_samples, alpha_slow, alpha_fast, conv_thresh, [h]() {
     Eigen::Vector3d p(0.0, 0.0, 0.0);
+    if (h->uniform_map)
+    {
+      auto generate = [h, &p]() {
+        const unsigned int k = drand48() * (h->free_ij.size() / 2);
+        std::vector<double> w(2);
+        h->uniform_map->convertMapToWorld({h->free_ij[2 * k], h->free_ij[2 * k + 1]}, &w);
+        p[0] = w[0];
+        p[1] = w[1];
+        p[2] = drand48() * 2 * M_PI - M_PI;
+      };
+      double good = h->uniform_threshold;
+      generate();
+      if (good > 0.0 && h->uniform_multiplier < 1.0 && h->uniform_multiplier >= 0.0)
+        while (1.0 < good)  // scorePose(p) is always 1.0 in the reference (node_2d.cpp:310-313)
+        {
+          generate();
+          good *= h->uniform_multiplier;
+        }
+      h->random_next += 3;
+      return p;
+    }
     if (h->random_next + 3 <= h->random_poses.size())
     {
       p = Eigen::Vector3d(h->random_poses[h->random_next], h->random_poses[h->random_next + 1],
@@ -412,6 +438,15 @@ void ref_pf_set_random_poses(void* h, const double* poses, long n)
 {
   PF* p = static_cast<PF*>(h);
   p->random_poses.assign(poses, poses + 3 * n);
+  p->random_next = 0;
+}
+void ref_pf_set_uniform_pose_source(void* h, void* map2d, const int* free_ij, long n, double threshold, double multiplier)
+{
+  PF* p = static_cast<PF*>(h);
+  p->uniform_map = static_cast<Map2D*>(map2d)->m;
+  p->free_ij.assign(free_ij, free_ij + 2 * n);
+  p->uniform_threshold = threshold;
+  p->uniform_multiplier = multiplier;
   p->random_next = 0;
 }
 long ref_pf_random_poses_used(void* h) { return static_cast<long>(static_cast<PF*>(h)->random_next / 3); }

@@ -260,6 +260,52 @@ def test_multinomial_resample_matches_oracle(env, n, n_min, cloud):
     pf.close()
 
 
+@pytest.mark.parametrize("n,n_min,w_fast,thr,mult", [(3000, 100, 0.7, 0.0, 0.0), (20000, 500, 0.95, 3.0, 0.5),
+                                                     (20000, 50, 0.3, 0.0, 0.0), (1, 1, 0.5, 0.0, 0.0),
+                                                     (200000, 20000, 0.9, 1.5, 0.5), (5000, 100, 0.0, 0.0, 0.0)])
+def test_multinomial_with_device_pose_source_matches_oracle(env, n, n_min, w_fast, thr, mult):
+    """resampleMultinomial with w_diff = 1 - w_fast / w_slow > 0 (particle_filter.cpp:385-388) and the node's pose
+    function (uniformPoseGenerator over the free-space list, node.cpp:262-264) drawing from the same drand48 stream:
+    sources (-1 = random pose), poses, count, tree, clusters and the stream state, bit for bit"""
+    O, cabi = env["O"], env["cabi"]
+    cells = synth.make_grid(300, 200, seed=7, wall_every=60)
+    pm = O.PortMap2D(cells, RES, (0.5, -0.25))
+    pm.update_distances(2.0)
+    fs = pm.free_space(0.1)
+    m = cabi.Map2D(env["ctx"], cells, RES, origin=(0.5, -0.25))
+    m.upload_distances(pm.dist, 2.0)
+    assert m.update_free_space(0.1) == len(fs)
+    poses = synth.gaussian_poses((0.5, 0.3, 0.2), n, seed=2, sigma_xy=0.3)
+    rng = np.random.default_rng(n + n_min)
+    port = O.PortPF(n_min, n, systematic=False)
+    port.init_with_poses(poses)
+    port.set_uniform_pose_source(pm, fs, thr, mult)
+    port.srand48(31)
+    pf = cabi.ParticleFilter(env["ctx"], n_min, n, systematic=False)
+    pf.init_with_poses(poses)
+    pf.set_random_pose_source(m, thr, mult)
+    pf.srand48(31)
+    for _ in range(2):
+        k = port.sample_count()
+        w = np.exp(rng.normal(0.0, 1.0, k))
+        w /= w.sum()
+        s = port.samples()
+        s[:, 3] = w
+        port.set_samples(s)
+        port.set_averages(1.0, w_fast)
+        pf.upload_samples(s)
+        pf.w_slow, pf.w_fast = 1.0, w_fast
+        port.update_resample()
+        r = pf.update_resample()
+        _assert_same_resample(pf, port, r)
+        assert r.random_poses_used == int((port.resample_sources() < 0).sum())
+        assert pf.drand48_state == port.rng.x
+        if w_fast < 1.0 and n > 100:
+            assert r.random_poses_used > 0
+    pf.close()
+    m.close()
+
+
 def test_multinomial_with_random_injection_is_refused(env):
     cabi = env["cabi"]
     n = 1000

@@ -219,3 +219,43 @@ def test_octomap_lut_bit_exact(world):
     pm.set_bounds((0.5, 0.4), (2.0, 1.9))
     assert np.array_equal(rm.bounds()[0], pm.bounds()[0]) and np.array_equal(rm.bounds()[1], pm.bounds()[1])
     assert np.array_equal(rm.dense(), pm.dense())
+
+
+@pytest.mark.parametrize("systematic", [False, True])
+@pytest.mark.parametrize("thr,mult", [(0.0, 0.0), (3.0, 0.5)])
+def test_resample_with_the_nodes_pose_function_bit_exact(world, systematic, thr, mult):
+    """resampleMultinomial / resampleSystematic (particle_filter.cpp:269-420, UNMODIFIED in oracle/_ref) with w_diff > 0
+    and random_pose_fn_ = Node::uniformPoseGenerator drawing from the same drand48 stream (node.cpp:262-264,
+    823-868; restated in the harness and in the port): the interleaving of the resampler's and the generator's draws"""
+    O = world["O"]
+    cells = synth.make_grid(300, 200, seed=7, wall_every=60)
+    pm = O.PortMap2D(cells, 0.05)
+    pm.update_distances(2.0)
+    rm = O.RefMap2D(cells, 0.05)
+    rm.set_distances(pm.dist, 2.0)
+    fs = pm.free_space(0.1)
+    n = 3000
+    poses = synth.gaussian_poses((1.0, 0.5, 0.2), n, seed=1)
+    rng = np.random.default_rng(0)
+    a, b = O.PortPF(n // 10, n, systematic=systematic), O.RefPF(n // 10, n, systematic=systematic)
+    a.init_with_poses(poses)
+    b.init_with_poses(poses)
+    a.set_uniform_pose_source(pm, fs, thr, mult)
+    b.set_uniform_pose_source(rm, fs, thr, mult)
+    for step in range(2):
+        a.srand48(5 + step)
+        b.srand48(5 + step)
+        m = a.sample_count()
+        w = np.exp(rng.normal(0.0, 1.0, m))
+        s = a.samples()
+        s[:, 3] = w / w.sum()
+        a.set_samples(s)
+        b.set_samples(s)
+        a.set_averages(1.0, 0.7)
+        b.set_averages(1.0, 0.7)  # w_diff = 0.3
+        a.update_resample()
+        b.update_resample()
+        assert a.sample_count() == b.sample_count()
+        assert np.array_equal(a.samples(), b.samples())
+        assert (a.resample_sources() < 0).sum() > 0
+        assert O.port_lib().orc_drand48(C.byref(a.rng)) == O.ref_lib().ref_drand48()

@@ -76,7 +76,58 @@ __global__ void __launch_bounds__(256) k_uniform_poses(const UniformArgs a)
   a.th[s] = r2 * 2 * M_PI - M_PI;  // node.cpp:837
   a.w[s] = a.weight;
 }
+// the same generator writing packed (x, y, theta) triples: the random poses of the systematic resampler
+__global__ void __launch_bounds__(256) k_uniform_poses_aos(const UniformArgs a, double* __restrict__ out3)
+{
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= a.n)
+    return;
+  const unsigned long long gen = (unsigned long long)a.per_pose * (unsigned long long)s + (unsigned long long)(a.per_pose - 1);
+  const unsigned long long u = lcg_skip(a.state0, 2ull * gen + 1ull), v = lcg_next(u);
+  const unsigned int k = (unsigned int)((double)u * 0x1p-48 * (double)(size_t)a.free_n);
+  const int2 c = a.free_ij[k];
+  out3[3 * s] = a.origin_x + (c.x - a.size_x / 2) * a.resolution;
+  out3[3 * s + 1] = a.origin_y + (c.y - a.size_y / 2) * a.resolution;
+  out3[3 * s + 2] = (double)v * 0x1p-48 * 2 * M_PI - M_PI;
+}
 }  // namespace
+
+namespace bamcl
+{
+// n calls of the filter's registered pose function (bamcl_pf_set_random_pose_source) from generator state `state0`,
+// written to out3_dev; *state_out = the state after them. Used by the systematic resampler (particle_filter.cpp:316-324).
+int device_random_poses(bamcl_pf* pf, unsigned long long state0, int n, double* out3_dev, unsigned long long* state_out)
+{
+  bamcl_map2d* map = pf->rp_map;
+  long r = 0;
+  if (pf->rp_threshold > 0.0 && pf->rp_multiplier < 1.0 && pf->rp_multiplier >= 0.0)
+  {
+    double good = pf->rp_threshold;
+    while (1.0 < good)
+    {
+      good *= pf->rp_multiplier;
+      if (++r > 1000000)
+        return set_error(BAMCL_E_UNSUPPORTED, "resample: more than 1e6 de-weighting retries per random pose");
+    }
+  }
+  UniformArgs a;
+  memset(&a, 0, sizeof(a));
+  a.state0 = state0 & LCG_MASK;
+  a.n = n;
+  a.per_pose = (int)(1 + r);
+  a.free_ij = map->free_ij.as<int2>();
+  a.free_n = map->free_count;
+  a.size_x = map->size_x;
+  a.size_y = map->size_y;
+  a.resolution = map->resolution;
+  a.origin_x = (double)map->origin_x;
+  a.origin_y = (double)map->origin_y;
+  if (n > 0)
+    BAMCL_LAUNCH(pf->ctx, k_uniform_poses_aos, (unsigned)((n + 255) / 256), 256, 0, a, out3_dev);
+  *state_out = lcg_skip(a.state0, 2ull * (unsigned long long)(1 + r) * (unsigned long long)n);
+  return BAMCL_OK;
+}
+}  // namespace bamcl
 
 extern "C" int bamcl_map2d_update_free_space(bamcl_map2d* m, double non_free_space_radius, long* count_out)
 {

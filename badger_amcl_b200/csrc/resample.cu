@@ -803,6 +803,8 @@ static inline uint64_t drand48_next(uint64_t x) { return (0x5DEECE66DULL * x + 0
 namespace bamcl
 {
 int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res);  // multinomial.cu
+int device_random_poses(bamcl_pf* pf, unsigned long long state0, int n, double* out3_dev,
+                        unsigned long long* state_out);  // init.cu
 }
 
 extern "C" {
@@ -905,7 +907,11 @@ static int resample_impl(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
   }
   const int n_rand = w_diff * new_count;
   const int n_sys = new_count - n_rand;
-  if (n_rand > 0 && (!prm->random_poses || prm->n_random_poses < n_rand))
+  // random poses: handed over by the caller (what its random_pose_fn_ returned), or -- when none are and the node's pose
+  // function is registered (bamcl_pf_set_random_pose_source) -- generated on the device from the stream, after the
+  // start draw (:309 then :316-324)
+  const bool device_poses = n_rand > 0 && !prm->random_poses && pf->rp_map && pf->rp_map->free_count > 0;
+  if (n_rand > 0 && !device_poses && (!prm->random_poses || prm->n_random_poses < n_rand))
     return set_error(BAMCL_E_ARG, "bamcl_pf_resample: %d random poses needed, %ld supplied", n_rand, prm->n_random_poses);
   // :309-310
   const uint64_t state = drand48_next(prm->drand48_state);
@@ -924,11 +930,15 @@ static int resample_impl(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
     BAMCL_CUDA_OK(cudaMemcpyAsync(pf->seg_buf.p, pf->h_stage.p, sizeof(TargetSeg) * segs.size(), cudaMemcpyHostToDevice,
                                   ctx->stream));
   }
+  unsigned long long state_after = state;
   if (n_rand > 0)
   {
     BAMCL_TRY(pf->random_poses.reserve(sizeof(double) * 3 * (size_t)n_rand));
-    BAMCL_CUDA_OK(cudaMemcpyAsync(pf->random_poses.p, prm->random_poses, sizeof(double) * 3 * (size_t)n_rand,
-                                  cudaMemcpyHostToDevice, ctx->stream));
+    if (device_poses)
+      BAMCL_TRY(device_random_poses(pf, state, n_rand, pf->random_poses.as<double>(), &state_after));
+    else
+      BAMCL_CUDA_OK(cudaMemcpyAsync(pf->random_poses.p, prm->random_poses, sizeof(double) * 3 * (size_t)n_rand,
+                                    cudaMemcpyHostToDevice, ctx->stream));
   }
   SelectArgs a;
   a.c = pf->cdf.as<double>();
@@ -973,7 +983,7 @@ static int resample_impl(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
   res->sample_count = new_count;
   res->random_poses_used = n_rand;
   res->status_flags = flags & 1;
-  res->drand48_state = state;
+  res->drand48_state = state_after;
   return BAMCL_OK;
 }
 

@@ -352,7 +352,8 @@ int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double starting_weight
 /* random_pose_fn_ of the filter (particle_filter.h:128; the node wires in Node::uniformPoseGenerator, node.cpp:262-264):
  * registers `map`'s free-space list (bamcl_map2d_update_free_space) and the generator's two parameters, so that
  * multinomial resampling with w_diff > 0 (particle_filter.cpp:385-388) draws its random poses on the device from the
- * same drand48 stream, in the reference's order. NULL map = no source (that case is then BAMCL_E_UNSUPPORTED). The map
+ * same drand48 stream, in the reference's order; the systematic model (:309-324) does the same when
+ * bamcl_resample_params::random_poses is NULL (start draw first, then the poses). NULL map = no source (that case is then BAMCL_E_UNSUPPORTED). The map
  * must outlive the filter or be unregistered first. */
 int bamcl_pf_set_random_pose_source(bamcl_pf* pf, bamcl_map2d* map_or_null, double starting_weight_threshold,
                                     double deweight_multiplier);

@@ -263,8 +263,9 @@ def test_multinomial_resample_matches_oracle(env, n, n_min, cloud):
 @pytest.mark.parametrize("n,n_min,w_fast,thr,mult", [(3000, 100, 0.7, 0.0, 0.0), (20000, 500, 0.95, 3.0, 0.5),
                                                      (20000, 50, 0.3, 0.0, 0.0), (1, 1, 0.5, 0.0, 0.0),
                                                      (200000, 20000, 0.9, 1.5, 0.5), (5000, 100, 0.0, 0.0, 0.0)])
-def test_multinomial_with_device_pose_source_matches_oracle(env, n, n_min, w_fast, thr, mult):
-    """resampleMultinomial with w_diff = 1 - w_fast / w_slow > 0 (particle_filter.cpp:385-388) and the node's pose
+@pytest.mark.parametrize("systematic", [False, True])
+def test_resample_with_device_pose_source_matches_oracle(env, n, n_min, w_fast, thr, mult, systematic):
+    """resampleMultinomial (and resampleSystematic, :291-324: start draw, then the random poses) with w_diff = 1 - w_fast / w_slow > 0 (particle_filter.cpp:385-388) and the node's pose
     function (uniformPoseGenerator over the free-space list, node.cpp:262-264) drawing from the same drand48 stream:
     sources (-1 = random pose), poses, count, tree, clusters and the stream state, bit for bit"""
     O, cabi = env["O"], env["cabi"]
@@ -277,11 +278,11 @@ def test_multinomial_with_device_pose_source_matches_oracle(env, n, n_min, w_fas
     assert m.update_free_space(0.1) == len(fs)
     poses = synth.gaussian_poses((0.5, 0.3, 0.2), n, seed=2, sigma_xy=0.3)
     rng = np.random.default_rng(n + n_min)
-    port = O.PortPF(n_min, n, systematic=False)
+    port = O.PortPF(n_min, n, systematic=systematic)
     port.init_with_poses(poses)
     port.set_uniform_pose_source(pm, fs, thr, mult)
     port.srand48(31)
-    pf = cabi.ParticleFilter(env["ctx"], n_min, n, systematic=False)
+    pf = cabi.ParticleFilter(env["ctx"], n_min, n, systematic=systematic)
     pf.init_with_poses(poses)
     pf.set_random_pose_source(m, thr, mult)
     pf.srand48(31)
@@ -300,7 +301,7 @@ def test_multinomial_with_device_pose_source_matches_oracle(env, n, n_min, w_fas
         _assert_same_resample(pf, port, r)
         assert r.random_poses_used == int((port.resample_sources() < 0).sum())
         assert pf.drand48_state == port.rng.x
-        if w_fast < 1.0 and n > 100:
+        if 0.0 < w_fast < 1.0 and n > 100:
             assert r.random_poses_used > 0
     pf.close()
     m.close()

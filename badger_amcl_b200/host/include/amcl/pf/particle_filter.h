@@ -16,6 +16,7 @@
 
 struct bamcl_ctx;
 struct bamcl_pf;
+struct bamcl_map2d;
 
 namespace badger_amcl
 {
@@ -91,6 +92,11 @@ public:
     host_dirty_ = false;
   }
   int resampleLimit(int k);                       // particle_filter.cpp:475-502
+  // The node's pose function (Node::uniformPoseGenerator over the free-space list of `map`, node.cpp:262-264, 823-868)
+  // replayed on the device from libc's drand48 stream: random poses of updateResample (both models; the only way to
+  // run multinomial resampling with w_diff > 0 on the device) are then not requested from random_pose_fn_.
+  // map = a bamcl_map2d with a free-space list (OccupancyMap::deviceHandle + bamcl_map2d_update_free_space).
+  void setDevicePoseSource(struct ::bamcl_map2d* map, double starting_weight_threshold, double deweight_multiplier);
   double slowAverage() const { return w_slow_; }
   double fastAverage() const { return w_fast_; }
   // sources of the last resample (index into the previous set, -1 = random pose): test / diagnostics aid
@@ -110,6 +116,7 @@ private:
   double global_localization_convergence_threshold_;
   std::shared_ptr<PFSampleSet> set_;  // mirror of the CURRENT device set (the device double-buffers internally)
   bool host_valid_, host_dirty_;
+  bool device_pose_source_ = false;
 };
 }  // namespace badger_amcl
 #endif

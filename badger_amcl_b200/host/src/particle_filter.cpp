@@ -437,7 +437,11 @@ void ParticleFilter::updateResample()
   // by the same draws so that later consumers (random_pose_fn_, the motion model) see the reference's stream.
   prm.drand48_state = peekDrand48State();
   std::vector<double> random_poses;
-  if (prm.resample_systematic)
+  if (device_pose_source_ && w_diff > 0.0)
+  {
+    // both models: the device draws the start / branch values AND the random poses from the stream (bamcl.h)
+  }
+  else if (prm.resample_systematic)
   {
     // particle_filter.cpp:292-309: set size from the CURRENT set's leaf count, one draw, then the random poses
     int new_count = resampleLimit(set_->kdtree->getLeafCount());
@@ -465,9 +469,9 @@ void ParticleFilter::updateResample()
   prm.n_random_poses = (long)(random_poses.size() / 3);
   bamcl_resample_result res;
   check(bamcl_pf_resample(dev_, &prm, &res), "bamcl_pf_resample");
-  if (!prm.resample_systematic)
+  if (!prm.resample_systematic || (device_pose_source_ && w_diff > 0.0))
   {
-    // multinomial consumed draws on the device: advance libc's generator to the returned state
+    // draws were consumed on the device: advance libc's generator to the returned state
     unsigned short st[3] = {(unsigned short)(res.drand48_state & 0xFFFF), (unsigned short)((res.drand48_state >> 16) & 0xFFFF),
                             (unsigned short)((res.drand48_state >> 32) & 0xFFFF)};
     seed48(st);
@@ -479,6 +483,13 @@ void ParticleFilter::updateResample()
   installStats(&res);
   set_->converged = res.converged;
   converged_ = res.converged != 0;
+}
+
+void ParticleFilter::setDevicePoseSource(bamcl_map2d* map, double starting_weight_threshold, double deweight_multiplier)
+{
+  check(bamcl_pf_set_random_pose_source(dev_, map, starting_weight_threshold, deweight_multiplier),
+        "bamcl_pf_set_random_pose_source");
+  device_pose_source_ = map != nullptr;
 }
 
 bool ParticleFilter::getClusterStats(int cidx, double* weight, Eigen::Vector3d* mean)

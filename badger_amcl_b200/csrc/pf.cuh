@@ -106,6 +106,12 @@ struct bamcl_pf
   // temp_obs_ bookkeeping of the beam-skipping model (planar_scanner.h:160-164): rows written per slot since the last
   // clearTempData (planar_scanner.cpp:684-690); the values themselves are recomputed, never stored
   std::vector<int> skip_written;
+  // sharded beam skipping: agreement counts of ALL ranks' windows (bamcl_pf_set_skip_counts), used by the next scoring
+  // call instead of this window's own; skip_counts_out = where a counts-only pass leaves this window's counts
+  std::vector<int> skip_global_counts;
+  long skip_global_n = 0;
+  bool skip_global_set = false;
+  std::vector<int>* skip_counts_out = nullptr;
   int skip_max_obs = 0, skip_max_samples = 0;
   bool force_general_tree = false;  // keep every node's first foreign key (multinomial.cu needs t_first_at)
   int set_converged = 0;     // set->converged as handed to the last scoring entry point

@@ -556,27 +556,52 @@ int launch_score(bamcl_pf* pf, bamcl_map2d* map)
   // ---- beam skipping (planar_scanner.cpp:361-395, 480-529): only for a converged set
   if (sc.model.model_type == BAMCL_PLANAR_LF_PROB && sc.model.do_beamskip && pf->set_converged)
   {
-    if (pf->win_cnt >= 0)
-      return set_error(BAMCL_E_UNSUPPORTED, "beam skipping on a sharded filter needs an all-reduce of the agreement counts");
-    const int max_beams = sc.model.max_beams, P = a.n, nb = sc.n_beams;
+    // On a sharded set the agreement counts are over ALL ranks' windows and the ratio is against the whole set
+    // (:483-494): a counts-only pass (bamcl_pf_skip_counts) returns this window's counts, the caller sums them over
+    // the ranks and hands the sums back (bamcl_pf_set_skip_counts) before the scoring call.
+    const bool counts_only = pf->skip_counts_out != nullptr;
+    if (pf->win_cnt >= 0 && !counts_only && !pf->skip_global_set)
+      return set_error(BAMCL_E_UNSUPPORTED,
+                       "beam skipping on a sharded filter needs the agreement counts of all ranks: bamcl_pf_skip_counts, "
+                       "sum over ranks, bamcl_pf_set_skip_counts, then score");
+    const bool use_global = pf->skip_global_set && !counts_only;
+    const int max_beams = sc.model.max_beams, nb = sc.n_beams;
+    const int P = use_global ? (int)pf->skip_global_n : a.n;
+    if (use_global && (int)pf->skip_global_counts.size() != nb)
+    {
+      pf->skip_global_set = false;
+      return set_error(BAMCL_E_ARG, "bamcl_pf_set_skip_counts: %d counts supplied, the staged scan has %d beams",
+                       (int)pf->skip_global_counts.size(), nb);
+    }
     // clearTempData bookkeeping (:378-394, :684-690); temp_obs_ itself is never stored: its entries are recomputed
-    if (pf->skip_max_obs < max_beams || pf->skip_max_samples < P)
+    if (!counts_only && (pf->skip_max_obs < max_beams || pf->skip_max_samples < P))
     {
       pf->skip_max_obs = max_beams;
       pf->skip_max_samples = std::max(pf->skip_max_samples, P);
       pf->skip_written.assign((size_t)max_beams, 0);
     }
     std::vector<int> counts((size_t)std::max(nb, 1), 0);
-    if (nb > 0)
+    if (use_global)
+    {
+      for (int b = 0; b < nb; b++)
+        counts[b] = pf->skip_global_counts[b];
+      pf->skip_global_set = false;  // one scoring call per hand-over
+    }
+    else if (nb > 0 && a.n > 0)
     {
       BAMCL_TRY(sc.skip_count.reserve(sizeof(int) * (size_t)nb));
       BAMCL_CUDA_OK(cudaMemsetAsync(sc.skip_count.p, 0, sizeof(int) * (size_t)nb, ctx->stream));
-      const int cblocks = std::max(1, std::min(kNumSMs * 4, (P + 255) / 256));
+      const int cblocks = std::max(1, std::min(kNumSMs * 4, (a.n + 255) / 256));
       BAMCL_LAUNCH(ctx, k_skip_count, cblocks, 256, sizeof(int) * (size_t)nb, a, sc.agree.as<unsigned char>(),
                    sc.skip_count.as<int>(), map->layout);
       BAMCL_CUDA_OK(cudaMemcpyAsync(counts.data(), sc.skip_count.p, sizeof(int) * (size_t)nb, cudaMemcpyDeviceToHost,
                                     ctx->stream));
       BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    }
+    if (counts_only)
+    {
+      pf->skip_counts_out->assign(counts.begin(), counts.begin() + nb);
+      return BAMCL_OK;
     }
     std::vector<int> obs_count((size_t)max_beams, 0);
     std::vector<char> now((size_t)max_beams, 0);
@@ -614,7 +639,7 @@ int launch_score(bamcl_pf* pf, bamcl_map2d* map)
     }
     if (zero_all)
     {
-      BAMCL_CUDA_OK(cudaMemsetAsync(a.w, 0, sizeof(double) * (size_t)P, ctx->stream));  // w *= exp(-inf)
+      BAMCL_CUDA_OK(cudaMemsetAsync(a.w, 0, sizeof(double) * (size_t)a.n, ctx->stream));  // w *= exp(-inf)
       return BAMCL_OK;
     }
     // the beams that are integrated, in slot order
@@ -685,3 +710,39 @@ int launch_score(bamcl_pf* pf, bamcl_map2d* map)
   return BAMCL_OK;
 }
 }  // namespace bamcl
+
+// ---- sharded beam skipping (SURVEY 8e collective (2)): the per-beam agreement counts cross the ranks
+extern "C" int bamcl_pf_skip_counts(bamcl_pf* pf, bamcl_map2d* map, int converged, int* counts_out, int capacity, int* n_out)
+{
+  if (!pf || !map || !n_out || (capacity > 0 && !counts_out))
+    return set_error(BAMCL_E_ARG, "bamcl_pf_skip_counts: bad arguments");
+  *n_out = 0;
+  StagedScan& sc = pf->scan;
+  if (!sc.valid)
+    return set_error(BAMCL_E_STATE, "no scan staged");
+  if (!(sc.model.model_type == BAMCL_PLANAR_LF_PROB && sc.model.do_beamskip && converged))
+    return BAMCL_OK;  // no beam skipping in this update: nothing to exchange
+  if (sc.n_beams > capacity)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_skip_counts: %d counts, capacity %d", sc.n_beams, capacity);
+  std::vector<int> counts;
+  pf->set_converged = true;
+  pf->skip_counts_out = &counts;
+  const int rc = launch_score(pf, map);
+  pf->skip_counts_out = nullptr;
+  if (rc != BAMCL_OK)
+    return rc;
+  for (size_t b = 0; b < counts.size(); b++)
+    counts_out[b] = counts[b];
+  *n_out = (int)counts.size();
+  return BAMCL_OK;
+}
+
+extern "C" int bamcl_pf_set_skip_counts(bamcl_pf* pf, const int* counts, int n, long global_sample_count)
+{
+  if (!pf || n < 0 || (n > 0 && !counts) || global_sample_count <= 0)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_set_skip_counts: bad arguments");
+  pf->skip_global_counts.assign(counts, counts + n);
+  pf->skip_global_n = global_sample_count;
+  pf->skip_global_set = true;
+  return BAMCL_OK;
+}

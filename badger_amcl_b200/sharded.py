@@ -77,6 +77,18 @@ class CudaEngine:
         cabi._check(self.L.bamcl_pf_score_planar_staged(self.pf.h, self.map.h, int(self.pf.converged), C.byref(total)))
         return total.value
 
+    def skip_counts(self):
+        """this window's per-beam agreement counts (beam skipping), empty when the update does none"""
+        out = np.zeros(4096, np.int32)
+        n = C.c_int()
+        cabi._check(self.L.bamcl_pf_skip_counts(self.pf.h, self.map.h, int(self.pf.converged), cabi._p(out), len(out),
+                                                C.byref(n)))
+        return out[:n.value].copy()
+
+    def set_skip_counts(self, counts, total_n):
+        c = np.ascontiguousarray(counts, np.int32)
+        cabi._check(self.L.bamcl_pf_set_skip_counts(self.pf.h, cabi._p(c), len(c), total_n))
+
     def normalise(self, total):
         self.pf.normalise(total)
 
@@ -193,8 +205,22 @@ class ShardedFilter:
         return bounds
 
     # -- ParticleFilter::updateSensor (particle_filter.cpp:223-267) with PlanarScanner::applyModelToSampleSet
+    def _all_reduce_counts(self, counts):
+        if self.dist is None or self.world == 1:
+            return counts
+        import torch
+        t = torch.from_numpy(np.ascontiguousarray(counts, np.int32)).to(self.e.scalar_tensor().device)
+        parts = [torch.empty_like(t) for _ in range(self.world)]
+        self.dist.all_gather(parts, t)
+        return torch.stack(parts).sum(0).to(torch.int32).cpu().numpy()
+
     def update_sensor(self):
         self.apply_window()
+        if hasattr(self.e, "skip_counts"):
+            # beam skipping (prob model, converged set): per-beam agreement counts summed over the ranks
+            counts = self.e.skip_counts()
+            if len(counts):
+                self.e.set_skip_counts(self._all_reduce_counts(counts), self.e.sample_count())
         local = self.e.score()
         totals = self._all_gather_scalar(local)
         total = 0.0

@@ -279,6 +279,14 @@ int bamcl_pf_shard_select(bamcl_pf* pf, double start, double delta, long n_sys, 
  * then pose-bin tree, clusters, statistics, updateConverged as in bamcl_pf_resample; clears the window. */
 int bamcl_pf_shard_install(bamcl_pf* pf, const double* aos3_dev, long n, const bamcl_resample_params* params,
                            bamcl_resample_result* result);
+/* Beam skipping on a sharded set (planar_scanner.cpp:398-451, 483-494; SURVEY 8e collective (2)): the per-beam
+ * agreement counts are sums over ALL particles and the skip ratio is against the whole set. bamcl_pf_skip_counts runs
+ * the counting pass over this rank's window for the staged scan (n_out = 0 when this update does no beam skipping: model
+ * not likelihood_field_prob, do_beamskip off, or the set not converged); the caller sums the vectors over the ranks
+ * (one all-reduce of <= max_beams ints) and hands them back with the global sample count; the next scoring call
+ * (bamcl_pf_score_planar_staged / bamcl_pf_update_planar_staged) then masks and integrates with them. */
+int bamcl_pf_skip_counts(bamcl_pf* pf, bamcl_map2d* map, int converged, int* counts_out, int capacity, int* n_out);
+int bamcl_pf_set_skip_counts(bamcl_pf* pf, const int* counts, int n, long global_sample_count);
 /* host AoS <-> the samples [offset, offset + n) of the current set (a rank's window); sample_count is unchanged */
 int bamcl_pf_upload_window_samples(bamcl_pf* pf, const double* aos, long offset, long n);
 int bamcl_pf_download_window_samples(bamcl_pf* pf, double* aos, long offset, long n);

@@ -175,3 +175,65 @@ def test_sharded_update_matches_the_unsharded_device_filter(env):
     w = np.concatenate([g[3] for g in got])
     assert np.allclose(w, want, rtol=1e-12, atol=0.0)
     assert abs(w.sum() - 1.0) < 1e-9
+
+
+@pytest.mark.parametrize("case", ["mask", "error_all_beams"])
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_beam_skipping_matches_the_unsharded_device_filter(env, world, case):
+    """SURVEY 8e collective (2): per-beam agreement counts summed over the ranks' windows, the skip ratio against the
+    whole set (planar_scanner.cpp:398-451, 483-494). The unsharded device path is the one pinned to the oracle in
+    tests/test_gpu_score.py; every rank's window must carry exactly its weights (same mask => same arithmetic)."""
+    from badger_amcl_b200 import sharded
+    from sharded_support import run_ranks
+    cabi = env["cabi"]
+    n, n_beams = 6000, 180
+    cells, truth = env["cells"], env["truth"]
+    kw = dict(model_type=cabi.MODEL_LF_PROB, do_beamskip=True, beam_skip_distance=0.5, beam_skip_threshold=0.3,
+              beam_skip_error_threshold=0.9, scanner_pose=(0.1, 0.0, 0.0), max_beams=n_beams)
+    if case == "error_all_beams":
+        kw["beam_skip_threshold"] = 0.995
+        poses = synth.uniform_free_poses(cells, RES, n, seed=3)
+    else:
+        # half of the cloud sits on the true pose, half is scattered: the counts differ from window to window
+        poses = np.concatenate([synth.gaussian_poses(truth, n // 2, seed=3, sigma_xy=0.05, sigma_th=0.01),
+                                synth.uniform_free_poses(cells, RES, n - n // 2, seed=4)])
+    ranges, angles = synth.make_scan(cells, RES, truth, n_beams=n_beams)
+    rng = np.random.default_rng(9)
+    for i in rng.choice(n_beams, 25, replace=False):
+        ranges[i] = min(ranges[i], 29.0) * 0.45
+    model = cabi.planar_model(**kw)
+    one = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    one.init_with_poses(poses)
+    one.set_exact_terms(True)
+    one.converged = True
+    one.update_sensor(env["map"], model, ranges, angles, 30.0)
+    want, want_total = one.weights(), one.last_total
+    plain = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    plain.init_with_poses(poses)
+    plain.set_exact_terms(True)
+    plain.update_sensor(env["map"], cabi.planar_model(**dict(kw, do_beamskip=False)), ranges, angles, 30.0)
+    if case == "mask":
+        assert plain.last_total != want_total, "the mask must really drop beams in this case"
+    one.close()
+    plain.close()
+
+    def rank_fn(rank, dist):
+        ctx = cabi.Context(0)
+        pf = cabi.ParticleFilter(ctx, n // 10, n)
+        pf.init_with_poses(poses)
+        pf.set_exact_terms(True)
+        pf.converged = True
+        pf.stage_scan(env["map"], model, ranges, angles, 30.0)
+        f = sharded.ShardedFilter(sharded.CudaEngine(pf, env["map"], 0), rank, world, dist, n // 10, n)
+        total = f.update_sensor()
+        off, cnt = f.window()
+        w = pf.weights()[off:off + cnt]
+        pf.close()
+        ctx.close()
+        return total, w
+
+    got = run_ranks(world, rank_fn)
+    assert len(set(g[0] for g in got)) == 1
+    assert abs(got[0][0] - want_total) <= 1e-12 * abs(want_total)
+    w = np.concatenate([g[1] for g in got])
+    assert np.allclose(w, want, rtol=1e-12, atol=0.0)

@@ -72,13 +72,22 @@ class CudaEngine:
     def set_window(self, off, cnt):
         cabi._check(self.L.bamcl_pf_set_window(self.pf.h, off, cnt))
 
+    def set_cloud(self, map3d, model, points):
+        """score 3-D point clouds (PointCloudScanner, point_cloud_scanner.cpp:111-129) instead of the staged planar scan"""
+        self.cloud = (map3d, model, np.ascontiguousarray(points, np.float32))
+
     def score(self):
+        if getattr(self, "cloud", None) is not None:
+            map3d, model, pts = self.cloud
+            return self.pf.score_cloud(map3d, model, pts)  # this rank's window, un-normalised
         total = C.c_double()
         cabi._check(self.L.bamcl_pf_score_planar_staged(self.pf.h, self.map.h, int(self.pf.converged), C.byref(total)))
         return total.value
 
     def skip_counts(self):
         """this window's per-beam agreement counts (beam skipping), empty when the update does none"""
+        if getattr(self, "cloud", None) is not None:
+            return np.zeros(0, np.int32)
         out = np.zeros(4096, np.int32)
         n = C.c_int()
         cabi._check(self.L.bamcl_pf_skip_counts(self.pf.h, self.map.h, int(self.pf.converged), cabi._p(out), len(out),

@@ -144,3 +144,48 @@ def test_cloud_scoring_needs_a_cache(env):
         pf.score_cloud(m, cabi.cloud_model(), np.zeros((8, 3), np.float32))
     pf.close()
     m.close()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_cloud_update_matches_the_unsharded_device_filter(env, world):
+    """SURVEY 8e for the 3-D sensor: every rank scores its window of the one global set against the replicated OctoMap
+    cache; totals all-gathered in rank order, one global normalisation"""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from badger_amcl_b200 import sharded
+    from sharded_support import run_ranks
+    cabi = env["cabi"]
+    n = 3001
+    kw = dict(model_type=0, max_beams=512, mount_translation=(0.2, 0.0, 1.5),
+              mount_rotation=synth.rpy_quaternion(0.0, 0.1, 0.0))
+    points = synth.make_cloud(env["keys"], RES, env["truth"], n_points=512)
+    samples = _samples(env, n)
+    model = cabi.cloud_model(**kw)
+    one = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    one.upload_samples(samples)
+    assert one.update_sensor_cloud(env["m"], model, points)
+    want, want_total = one.weights(), one.last_total
+    one.close()
+
+    def rank_fn(rank, dist):
+        ctx = cabi.Context(0)
+        m = cabi.Map3D(ctx, RES, env["keys"], MAX_DIST)  # the cache is replicated: one copy per rank
+        m.upload_distances(env["pm"].dense())
+        pf = cabi.ParticleFilter(ctx, n // 10, n)
+        pf.upload_samples(samples)
+        eng = sharded.CudaEngine(pf, None, 0)
+        eng.set_cloud(m, model, points)
+        f = sharded.ShardedFilter(eng, rank, world, dist, n // 10, n)
+        total = f.update_sensor()
+        off, cnt = f.window()
+        w = pf.weights()[off:off + cnt]
+        pf.close()
+        m.close()
+        ctx.close()
+        return total, w
+
+    got = run_ranks(world, rank_fn)
+    assert len(set(g[0] for g in got)) == 1
+    assert abs(got[0][0] - want_total) <= 1e-12 * abs(want_total)
+    assert np.allclose(np.concatenate([g[1] for g in got]), want, rtol=1e-12, atol=0.0)

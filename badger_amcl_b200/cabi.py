@@ -178,6 +178,8 @@ SIGNATURES = {
     "bamcl_pf_leaf_count": (_I, [_P, _P]),
     "bamcl_pf_update_action": (_I, [_P, _P, _P, C.c_uint64, _P]),
     "bamcl_pf_max_weight_pose": (_I, [_P, _P, _P, _P]),
+    "bamcl_pf_score_planar_staged_dev": (_I, [_P, _P, _I, _P]),
+    "bamcl_pf_normalise_ranks_dev": (_I, [_P, _P, _I, _P]),
     "bamcl_pf_skip_counts": (_I, [_P, _P, _I, _P, _I, _P]),
     "bamcl_pf_set_skip_counts": (_I, [_P, _P, _I, _L]),
     "bamcl_pf_set_random_pose_source": (_I, [_P, _P, _D, _D]),

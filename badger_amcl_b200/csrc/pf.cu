@@ -101,6 +101,23 @@ __global__ void k_normalise(double* __restrict__ w, int n, const double* __restr
   else
     w[i] = 1.0 / n_set;  // the whole set's count (a sharded filter normalises only its window)
 }
+// sharded update: the ranks' window totals (rank order = sample order of the partial sums) -> global total -> normalise
+__global__ void k_normalise_ranks(double* __restrict__ w, int n, const double* __restrict__ totals, int n_ranks, int n_set,
+                                  double* __restrict__ total_out)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double total = 0.0;
+  for (int r = 0; r < n_ranks; r++)
+    total += totals[r];
+  if (i == 0)
+    *total_out = total;
+  if (i >= n)
+    return;
+  if (total > 0.0)
+    w[i] = w[i] / total;
+  else
+    w[i] = 1.0 / n_set;
+}
 }  // namespace
 
 namespace bamcl
@@ -473,6 +490,35 @@ int bamcl_pf_score_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, 
   BAMCL_TRY(launch_score(pf, map));
   BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
   return read_scalar(pf, 0, total_out);
+}
+
+int bamcl_pf_score_planar_staged_dev(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_dev)
+{
+  if (pf)
+    pf->set_converged = converged;
+  if (!pf || !map || !total_dev)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_score_planar_staged_dev: bad arguments");
+  if (pf->scan.valid && pf->scan.model.max_beams < 2)
+  {
+    BAMCL_CUDA_OK(cudaMemsetAsync(total_dev, 0, sizeof(double), pf->ctx->stream));
+    return BAMCL_OK;
+  }
+  BAMCL_TRY(launch_score(pf, map));
+  BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
+  BAMCL_CUDA_OK(cudaMemcpyAsync(total_dev, pf->scalars.as<double>(), sizeof(double), cudaMemcpyDeviceToDevice,
+                                pf->ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_pf_normalise_ranks_dev(bamcl_pf* pf, const double* totals_dev, int n_ranks, double* total_out_dev)
+{
+  if (!pf || !totals_dev || n_ranks < 1 || !total_out_dev)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_normalise_ranks_dev: bad arguments");
+  SampleSet& s = pf->sets[pf->current];
+  const int cnt = s.sample_count == 0 ? 0 : pf_win_cnt(pf);
+  BAMCL_LAUNCH(pf->ctx, k_normalise_ranks, (std::max(cnt, 1) + 255) / 256, 256, 0, s.w.as<double>() + pf_win_off(pf), cnt,
+               totals_dev, n_ranks, s.sample_count, total_out_dev);
+  return BAMCL_OK;
 }
 
 int bamcl_pf_update_planar_host(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,

@@ -84,6 +84,33 @@ class CudaEngine:
         cabi._check(self.L.bamcl_pf_score_planar_staged(self.pf.h, self.map.h, int(self.pf.converged), C.byref(total)))
         return total.value
 
+    # -- update without host round trips: score -> all-gather of the totals -> global total + normalise, one stream
+    def ext_stream(self):
+        if getattr(self, "_ext", None) is None:
+            self._ext = self.torch.cuda.ExternalStream(self.L.bamcl_ctx_stream(self.pf.ctx.h), device=self.device)
+            self._t_local = self.torch.zeros(1, dtype=self.torch.float64, device=self.device)
+            self._t_total = self.torch.zeros(1, dtype=self.torch.float64, device=self.device)
+            self._t_flat = None
+        return self._ext
+
+    def update_dev(self, dist, world):
+        """returns the global total (one device->host read at the end); None if this engine scores clouds"""
+        if getattr(self, "cloud", None) is not None:
+            return None
+        t = self.torch
+        with t.cuda.stream(self.ext_stream()):
+            if self._t_flat is None or self._t_flat.numel() != world:
+                self._t_flat = t.zeros(world, dtype=t.float64, device=self.device)
+            cabi._check(self.L.bamcl_pf_score_planar_staged_dev(self.pf.h, self.map.h, int(self.pf.converged),
+                                                                C.c_void_p(self._t_local.data_ptr())))
+            if hasattr(dist, "all_gather_into_tensor") and dist.get_backend() == "nccl":
+                dist.all_gather_into_tensor(self._t_flat, self._t_local)
+            else:
+                dist.all_gather([self._t_flat[r:r + 1] for r in range(world)], self._t_local)
+            cabi._check(self.L.bamcl_pf_normalise_ranks_dev(self.pf.h, C.c_void_p(self._t_flat.data_ptr()), world,
+                                                            C.c_void_p(self._t_total.data_ptr())))
+            return float(self._t_total.item())
+
     def skip_counts(self):
         """this window's per-beam agreement counts (beam skipping), empty when the update does none"""
         if getattr(self, "cloud", None) is not None:
@@ -230,12 +257,16 @@ class ShardedFilter:
             counts = self.e.skip_counts()
             if len(counts):
                 self.e.set_skip_counts(self._all_reduce_counts(counts), self.e.sample_count())
-        local = self.e.score()
-        totals = self._all_gather_scalar(local)
-        total = 0.0
-        for t in totals:  # rank order = sample order of the partial sums
-            total += t
-        self.e.normalise(total)
+        total = None
+        if hasattr(self.e, "update_dev") and self.dist is not None and self.world > 1:
+            total = self.e.update_dev(self.dist, self.world)
+        if total is None:
+            local = self.e.score()
+            totals = self._all_gather_scalar(local)
+            total = 0.0
+            for t in totals:  # rank order = sample order of the partial sums
+                total += t
+            self.e.normalise(total)
         if total > 0.0:
             w_avg = total / self.e.sample_count()
             self.w_slow = w_avg if self.w_slow == 0.0 else self.w_slow + self.alpha_slow * (w_avg - self.w_slow)

@@ -279,6 +279,12 @@ int bamcl_pf_shard_select(bamcl_pf* pf, double start, double delta, long n_sys, 
  * then pose-bin tree, clusters, statistics, updateConverged as in bamcl_pf_resample; clears the window. */
 int bamcl_pf_shard_install(bamcl_pf* pf, const double* aos3_dev, long n, const bamcl_resample_params* params,
                            bamcl_resample_result* result);
+/* The sharded update without host round trips: bamcl_pf_score_planar_staged with the window's total left in device
+ * memory (total_dev), and -- after the ranks' totals were all-gathered on the same stream -- the global total (summed
+ * in rank order, as ParticleFilter::updateSensor sums in sample order, particle_filter.cpp:246-252) + normalisation of
+ * the window in one launch; total_out_dev receives the global total. Nothing synchronises. */
+int bamcl_pf_score_planar_staged_dev(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_dev);
+int bamcl_pf_normalise_ranks_dev(bamcl_pf* pf, const double* totals_dev, int n_ranks, double* total_out_dev);
 /* Beam skipping on a sharded set (planar_scanner.cpp:398-451, 483-494; SURVEY 8e collective (2)): the per-beam
  * agreement counts are sums over ALL particles and the skip ratio is against the whole set. bamcl_pf_skip_counts runs
  * the counting pass over this rank's window for the staged scan (n_out = 0 when this update does no beam skipping: model

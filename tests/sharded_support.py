@@ -21,9 +21,15 @@ class ThreadDist:
 
     def all_gather(self, out, t):
         self.c.slots[self.rank] = t.clone()
+        if t.is_cuda:  # every rank thread may be on its own stream: the clone must be complete before peers read it
+            import torch
+            torch.cuda.current_stream(t.device).synchronize()
         self.c.bar.wait()
         for i in range(self.c.world):
             out[i].copy_(self.c.slots[i])
+        if t.is_cuda:
+            import torch
+            torch.cuda.current_stream(t.device).synchronize()
         self.c.bar.wait()
 
     def broadcast(self, t, src):

@@ -785,8 +785,6 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       BAMCL_CUDA_OK(cudaMemcpyAsync(h_out, out, sizeof(TreeOut), cudaMemcpyDeviceToHost, ctx->stream));
       BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     }
-    BAMCL_CUDA_OK(cudaMemcpyAsync(h_out, out, sizeof(TreeOut), cudaMemcpyDeviceToHost, ctx->stream));
-    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     if (h_out->err & 1)
       return set_error(BAMCL_E_UNSUPPORTED, "a pose is outside the kd-tree key range (|x|,|y| < 5e5 m, |theta| < 3.6e5 rad)");
     if ((h_out->err & 2) || (size_t)h_out->C > pf->t_cluster_cap)

@@ -25,11 +25,27 @@ def needs_build():
 
 
 def build(force=False, verbose=False):
-    if not force and not needs_build():
-        return OUT
+    """one object per .cu (compiled in parallel, rebuilt only when it or a header changed), then one link"""
+    from concurrent.futures import ThreadPoolExecutor
     extra = os.environ.get("BAMCL_EXTRA_NVCC", "").split()  # kernel tuning sweeps
-    cmd = [NVCC] + FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + sources()
-    subprocess.check_call(cmd)
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+    hdrs = glob.glob(os.path.join(CSRC, "*.cuh")) + [os.path.join(HERE, "..", "include", "bamcl.h")]
+    hdr_t = max(os.path.getmtime(h) for h in hdrs)
+    compile_flags = [f for f in FLAGS if f not in ("-shared", "-cudart", "static")]
+    jobs = []
+    for src in sources():
+        obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
+        stale = force or extra or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hdr_t)
+        if stale:
+            jobs.append([NVCC] + compile_flags + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, src])
+    if not jobs and os.path.exists(OUT) and not force:
+        return OUT
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 2)) as ex:
+        list(ex.map(subprocess.check_call, jobs))
+    objs = [os.path.join(objdir, os.path.basename(src)[:-3] + ".o") for src in sources()]
+    subprocess.check_call([NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-cudart", "static", "-o", OUT] + objs +
+                          ["-ldl"])
     return OUT
 
 

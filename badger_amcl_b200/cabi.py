@@ -171,15 +171,27 @@ SIGNATURES = {
     "bamcl_resample_limit": (_I, [_I, _I, _I, _D, _D]),
     "bamcl_systematic_targets": (_I, [_D, _D, _L, _P]),
     "bamcl_pf_set_window": (_I, [_P, _L, _L]),
-    "bamcl_pf_shard_cdf": (_I, [_P, _D, _P]),
     "bamcl_systematic_plan": (_I, [_D, _D, _L, _P, _I, _P, _I, _P]),
-    "bamcl_pf_shard_select": (_I, [_P, _D, _D, _L, _L, _L, _L, _P, _P]),
-    "bamcl_pf_shard_install": (_I, [_P, _P, _L, _P, _P]),
     "bamcl_pf_leaf_count": (_I, [_P, _P]),
+    "bamcl_comm_unique_id": (_I, [_P]),
+    "bamcl_comm_create": (_I, [_P, _P, _I, _I, _P]),
+    "bamcl_comm_destroy": (_I, [_P]),
+    "bamcl_comm_rank": (_I, [_P, _P, _P]),
+    "bamcl_comm_local_group": (_I, [_I, _P]),
+    "bamcl_comm_local_group_free": (_I, [_P]),
+    "bamcl_comm_create_local": (_I, [_P, _P, _I, _P]),
+    "bamcl_comm_all_reduce_sum_i32": (_I, [_P, _P, _I]),
+    "bamcl_pf_shard_attach": (_I, [_P, _P]),
+    "bamcl_pf_shard_set_count": (_I, [_P, _L, _P, _P]),
+    "bamcl_pf_shard_window": (_I, [_P, _P, _P]),
+    "bamcl_pf_shard_init_stats": (_I, [_P, _P]),
+    "bamcl_pf_shard_update_planar_staged": (_I, [_P, _P, _I, _P]),
+    "bamcl_pf_shard_update_cloud_staged": (_I, [_P, _P, _P]),
+    "bamcl_pf_shard_resample": (_I, [_P, _P, _P]),
+    "bamcl_pf_shard_bounds": (_I, [_P, _P, _I]),
+    "bamcl_shard_exchange_plan": (_I, [_P, _I, _L, _L, _I, _P, _I, _P]),
     "bamcl_pf_update_action": (_I, [_P, _P, _P, C.c_uint64, _P]),
     "bamcl_pf_max_weight_pose": (_I, [_P, _P, _P, _P]),
-    "bamcl_pf_score_planar_staged_dev": (_I, [_P, _P, _I, _P]),
-    "bamcl_pf_normalise_ranks_dev": (_I, [_P, _P, _I, _P]),
     "bamcl_pf_skip_counts": (_I, [_P, _P, _I, _P, _I, _P]),
     "bamcl_pf_set_skip_counts": (_I, [_P, _P, _I, _L]),
     "bamcl_pf_set_random_pose_source": (_I, [_P, _P, _D, _D]),
@@ -428,7 +440,11 @@ class ParticleFilter:
         _check(self.L.bamcl_pf_upload_weights(self.h, _p(w), len(w)))
 
     def weights(self):
-        out = np.empty(self.sample_count())
+        return self.weights_n(self.sample_count())
+
+    def weights_n(self, n):
+        """n = sample_count, or the window size of a distributed filter"""
+        out = np.empty(n)
         _check(self.L.bamcl_pf_download_weights(self.h, _p(out), len(out)))
         return out
 
@@ -632,12 +648,19 @@ class ParticleFilter:
         return res
 
     def resample_sources(self):
-        out = np.empty(self.sample_count(), np.int32)
+        return self.resample_sources_n(self.sample_count())
+
+    def resample_sources_n(self, n):
+        """n = sample_count, or the window size of a distributed filter"""
+        out = np.empty(n, np.int32)
         _check(self.L.bamcl_pf_resample_sources(self.h, _p(out), len(out)))
         return out
 
     def sample_clusters(self):
-        out = np.empty(self.sample_count(), np.int32)
+        return self.sample_clusters_n(self.sample_count())
+
+    def sample_clusters_n(self, n):
+        out = np.empty(n, np.int32)
         _check(self.L.bamcl_pf_sample_clusters(self.h, _p(out), len(out)))
         return out
 

@@ -227,6 +227,7 @@ extern "C" int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double star
   a.weight = 1.0 / (double)pf->max_samples;  // :152
   BAMCL_LAUNCH(ctx, k_uniform_poses, (unsigned)((n + 255) / 256), 256, 0, a);
   set.sample_count = n;
+  pf_apply_shard_window(pf);  // a distributed filter: every rank generated the whole set, and owns its window from here on
   memset(res, 0, sizeof(*res));
   BAMCL_TRY(build_tree_and_stats(pf, pf->current, 0.5, 1e300, res));
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));

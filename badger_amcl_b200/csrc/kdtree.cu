@@ -20,6 +20,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "pf.cuh"
 #include "scan.cuh"
@@ -126,6 +127,121 @@ __global__ void __launch_bounds__(256) k_make_nodes(const int* __restrict__ slot
   nfirst[id] = i;
   hnode[s] = id;
   parent[id] = id;  // union-find forest of the clustering step: every node its own root
+}
+
+// ---- 1b. the same, on a dense grid of pose bins. When the occupied bins fit a box of at most DENSE_CAP cells (a 200 m
+// map at 0.5 m x 0.5 m x 10 deg is 5.8M cells) a bin is addressed directly: no probing, no CAS, the 26 neighbour probes
+// of the clustering step are plain loads, and on a distributed filter ONE all-reduce (min) of the grid of first
+// occurrences gives every rank the global creation order.
+constexpr long DENSE_CAP = 1l << 26;
+constexpr int BOX_MARGIN = 2;
+struct Box
+{
+  int mn[3], dim[3];
+};
+__device__ __forceinline__ bool pose_key(double x, double y, double th, double cx, double cy, double ct, int* kx, int* ky, int* kt)
+{
+  // pf_kdtree.cpp:51-54
+  const double fx = floor(x / cx), fy = floor(y / cy), ft = floor(th / ct);
+  if (!(fabs(fx) < 1048575.0) || !(fabs(fy) < 1048575.0) || !(fabs(ft) < 2097151.0))
+    return false;
+  *kx = (int)fx;
+  *ky = (int)fy;
+  *kt = (int)ft;
+  return true;
+}
+// box6 = {min kx, min ky, min kt, -max kx, -max ky, -max kt}: one MIN reduction serves both ends
+__global__ void __launch_bounds__(256) k_key_bbox(const double* __restrict__ x, const double* __restrict__ y,
+                                                  const double* __restrict__ th, int n, double cx, double cy, double ct,
+                                                  int* __restrict__ box6)
+{
+  int v[6] = {INT_MAX, INT_MAX, INT_MAX, INT_MAX, INT_MAX, INT_MAX};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+  {
+    int k[3];
+    if (!pose_key(x[i], y[i], th[i], cx, cy, ct, &k[0], &k[1], &k[2]))
+      continue;
+#pragma unroll
+    for (int d = 0; d < 3; d++)
+    {
+      v[d] = min(v[d], k[d]);
+      v[3 + d] = min(v[3 + d], -k[d]);
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 6; d++)
+  {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+      v[d] = min(v[d], __shfl_xor_sync(0xffffffffu, v[d], o));
+    if ((threadIdx.x & 31) == 0 && v[d] != INT_MAX)
+      atomicMin(&box6[d], v[d]);
+  }
+}
+__global__ void __launch_bounds__(256) k_grid_first(const double* __restrict__ x, const double* __restrict__ y,
+                                                    const double* __restrict__ th, int n, long off, double cx, double cy, double ct,
+                                                    const Box box, int* __restrict__ g_first, int* __restrict__ cell_out,
+                                                    TreeOut* out)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n)
+    return;
+  int k[3];
+  if (!pose_key(x[i], y[i], th[i], cx, cy, ct, &k[0], &k[1], &k[2]))
+  {
+    atomicOr(&out->err, 1);
+    cell_out[i] = 0;
+    return;
+  }
+  const int a = k[0] - box.mn[0], b = k[1] - box.mn[1], c = k[2] - box.mn[2];
+  if ((unsigned)a >= (unsigned)box.dim[0] || (unsigned)b >= (unsigned)box.dim[1] || (unsigned)c >= (unsigned)box.dim[2])
+  {
+    atomicOr(&out->err, 4);  // outside the sticky box: the host re-fits it and repeats
+    cell_out[i] = 0;
+    return;
+  }
+  const int cell = a + box.dim[0] * (b + box.dim[1] * c);
+  atomicMin(&g_first[cell], (int)(off + i));
+  cell_out[i] = cell;
+}
+// bit f of `bits` = "global sample f is the first occurrence of its bin"
+__global__ void __launch_bounds__(256) k_grid_mark(const int* __restrict__ g_first, long cells, int n_global,
+                                                   unsigned* __restrict__ bits)
+{
+  const long c = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cells)
+    return;
+  const int f = g_first[c];
+  if (f < n_global)
+    atomicOr(&bits[f >> 5], 1u << (f & 31));
+}
+__global__ void __launch_bounds__(256) k_popc(const unsigned* __restrict__ bits, int words, int* __restrict__ cnt)
+{
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w < words)
+    cnt[w] = __popc(bits[w]);
+}
+// creation-order node id of every occupied bin = number of first occurrences before its own
+__global__ void __launch_bounds__(256) k_grid_nodes(const int* __restrict__ g_first, long cells, int n_global,
+                                                    const unsigned* __restrict__ bits, const int* __restrict__ pre, const Box box,
+                                                    int* __restrict__ g_node, unsigned long long* __restrict__ nkey,
+                                                    int* __restrict__ nfirst, int* __restrict__ parent)
+{
+  const long c = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cells)
+    return;
+  const int f = g_first[c];
+  if (f >= n_global)
+  {
+    g_node[c] = -1;
+    return;
+  }
+  const int id = pre[f >> 5] + __popc(bits[f >> 5] & ((1u << (f & 31)) - 1u));
+  g_node[c] = id;
+  const int a = (int)(c % box.dim[0]), b = (int)((c / box.dim[0]) % box.dim[1]), t = (int)(c / ((long)box.dim[0] * box.dim[1]));
+  nkey[id] = pack_key(a + box.mn[0], b + box.mn[1], t + box.mn[2]);
+  nfirst[id] = f;
+  parent[id] = id;
 }
 
 // ---- 2. the tree, one level per step
@@ -313,6 +429,26 @@ __global__ void __launch_bounds__(256) k_cc_union(const TreeOut* __restrict__ ou
   uf_union<CA>(parent, v, hnode[s]);
 }
 
+template <bool CA>
+__global__ void __launch_bounds__(256) k_cc_union_dense(const TreeOut* __restrict__ out, const unsigned long long* __restrict__ nkey,
+                                                        const Box box, const int* __restrict__ g_node, int* parent, int n_max)
+{
+  const int K = out->K;
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int v = (int)(t / 13);
+  const int o = (int)(t % 13) + 14;  // offsets 14..26 of the 27 = lexicographically after (0,0,0)
+  if (v >= K || v >= n_max)
+    return;
+  int kx, ky, kt;
+  unpack_key(nkey[v], &kx, &ky, &kt);
+  const int a = kx - box.mn[0] + (o / 9 - 1), b = ky - box.mn[1] + ((o % 9) / 3 - 1), c = kt - box.mn[2] + ((o % 9) % 3 - 1);
+  if ((unsigned)a >= (unsigned)box.dim[0] || (unsigned)b >= (unsigned)box.dim[1] || (unsigned)c >= (unsigned)box.dim[2])
+    return;
+  const int u = __ldg(&g_node[a + box.dim[0] * (b + box.dim[1] * c)]);
+  if (u >= 0)
+    uf_union<CA>(parent, v, u);
+}
+
 // Read-only find: a compressing find here would race with other threads' finds (a stale intermediate ancestor
 // written over an already final root), so the final roots go to a separate array.
 __global__ void __launch_bounds__(256) k_cc_roots(const TreeOut* __restrict__ out, const int* __restrict__ parent,
@@ -347,6 +483,7 @@ struct StatsArgs
   double* rows;  // [cap][ROW]
   int cap;
   TreeOut* out;
+  double* set_part;  // [blocks][12] per-block set sums (reduced in a fixed order by k_set_sums_final)
 };
 constexpr int ST_BLOCK = 256;
 constexpr int ST_CHUNKS = 8;  // chunks of 32 samples per warp
@@ -488,7 +625,7 @@ __global__ void __launch_bounds__(ST_BLOCK) k_labels_stats(const StatsArgs a)
       double t = 0.0;
       for (int k = 0; k < ST_BLOCK / 32; k++)
         t += s_set[k][lane];
-      atomicAdd(&a.out->set_sums[lane], t);
+      a.set_part[(size_t)blockIdx.x * 12 + lane] = t;
     }
     if (lane < ROW)
     {
@@ -515,17 +652,50 @@ __global__ void __launch_bounds__(ST_BLOCK) k_labels_stats(const StatsArgs a)
   }
 }
 
-// updateConverged (particle_filter.cpp:170-220)
-__global__ void __launch_bounds__(256) k_converged_count(const double* __restrict__ x, const double* __restrict__ y, int n,
-                                                         double dist_threshold, TreeOut* out)
+// the 12 set sums in a fixed order (run-to-run identical): warp q owns column q
+__global__ void __launch_bounds__(384) k_set_sums_final(const double* __restrict__ part, int blocks, double* __restrict__ sums12)
 {
-  const double mean_x = out->set_sums[10] / n, mean_y = out->set_sums[11] / n;
+  const int q = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double t = 0.0;
+  for (int b = lane; b < blocks; b += 32)
+    t += part[(size_t)b * 12 + q];
+  t = warp_sum(t);
+  if (lane == 0)
+    sums12[q] = t;
+}
+
+// updateConverged (particle_filter.cpp:170-220); n_set = samples of the whole set (x, y, n: this rank's window)
+__global__ void __launch_bounds__(256) k_converged_count(const double* __restrict__ x, const double* __restrict__ y, int n,
+                                                         double dist_threshold, TreeOut* out, int n_set)
+{
+  const double mean_x = out->set_sums[10] / n_set, mean_y = out->set_sums[11] / n_set;
   int cnt = 0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     cnt += (fabs(x[i] - mean_x) <= dist_threshold && fabs(y[i] - mean_y) <= dist_threshold) ? 1 : 0;
   cnt = warp_sum_i(cnt);
   if ((threadIdx.x & 31) == 0 && cnt)
     atomicAdd(&out->conv, cnt);
+}
+
+// distributed filter: the integer results that are sums over ranks (leaf count of this rank's bucket subtrees, its
+// convergence count, error bits, the resampler's "target beyond the CDF" flag) -> one all-reduce -> back
+__global__ void k_ints_pack(const TreeOut* __restrict__ out, const int* __restrict__ pf_flags, int* __restrict__ v)
+{
+  v[0] = out->leaf;
+  v[1] = out->conv;
+  v[2] = out->err & 1;
+  v[3] = (out->err >> 1) & 1;
+  v[4] = (out->err >> 2) & 1;
+  v[5] = *pf_flags & 1;
+  v[6] = (*pf_flags >> 1) & 1;
+  v[7] = 0;
+}
+__global__ void k_ints_unpack(const int* __restrict__ v, TreeOut* out, int* pf_flags)
+{
+  out->leaf = v[0];
+  out->conv = v[1];
+  out->err = (v[2] ? 1 : 0) | (v[3] ? 2 : 0) | (v[4] ? 4 : 0);
+  *pf_flags = (v[5] ? 1 : 0) | (v[6] ? 2 : 0);
 }
 
 // normalizeCluster (particle_filter.cpp:548-562) -> count, weight, mean[3], cov(0,0),(0,1),(1,0),(1,1),(2,2)
@@ -572,6 +742,8 @@ int launch_fast_tree(bamcl_pf* pf, TreeOut* out, int n)
   fa.bslot = pf->t_cur.as<int>();
   fa.bpos = pf->t_first_at.as<int>();
   fa.bids = pf->t_child.as<int>();
+  fa.part_rank = pf_rank(pf);
+  fa.part_n = pf_ranks(pf);
   const int per = 28;  // bytes of shared memory per key in k_fast_top / k_fast_bucket
   static bool attr_done = false;
   if (!attr_done)
@@ -640,23 +812,99 @@ static int coop_blocks_for(bamcl_pf* pf)
   return pf->coop_blocks;
 }
 
+// pose-bin box of the (global) set: bounding box of its keys plus a margin, identical on every rank
+static int fit_box(bamcl_pf* pf, SampleSet& set, long off, int n, double cx, double cy, double ct)
+{
+  bamcl_ctx* ctx = pf->ctx;
+  BAMCL_TRY(pf->t_ints.reserve(sizeof(int) * 32));
+  int* box6 = pf->t_ints.as<int>() + 16;
+  BAMCL_CUDA_OK(cudaMemsetAsync(box6, 0x7F, sizeof(int) * 6, ctx->stream));
+  if (n > 0)
+    BAMCL_LAUNCH(ctx, k_key_bbox, std::min((n + 255) / 256, kNumSMs * 8), 256, 0, set.x.as<double>() + off, set.y.as<double>() + off,
+                 set.th.as<double>() + off, n, cx, cy, ct, box6);
+  if (pf_ranks(pf) > 1)
+    BAMCL_TRY(comm_all_reduce(pf->comm, box6, 6, CT_I32, CO_MIN));
+  int h[6];
+  BAMCL_CUDA_OK(cudaMemcpyAsync(h, box6, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  pf->box_valid = true;
+  pf->box_dense = false;
+  pf->box_cells = 0;
+  static const bool force_hash = getenv("BAMCL_TREE_HASH") != nullptr;  // tests: exercise the hashed path
+  if (force_hash && pf_ranks(pf) == 1)
+    return BAMCL_OK;
+  long cells = 1;
+  for (int d = 0; d < 3; d++)
+  {
+    if (h[d] == 0x7F7F7F7F || h[3 + d] == 0x7F7F7F7F)
+      return BAMCL_OK;  // no representable key: the hashed path reports it
+    pf->box_min[d] = h[d] - BOX_MARGIN;
+    const long dim = (long)(-h[3 + d]) + BOX_MARGIN - pf->box_min[d] + 1;
+    if (dim <= 0 || dim > DENSE_CAP)
+      return BAMCL_OK;
+    pf->box_dim[d] = (int)dim;
+    cells *= dim;
+    if (cells > DENSE_CAP)
+      return BAMCL_OK;
+  }
+  pf->box_dense = true;
+  pf->box_cells = cells;
+  return BAMCL_OK;
+}
+
+// Distributed filter whose bins do not fit the dense grid (a very large world): every rank receives the whole set and
+// builds the tree for itself, as a single-GPU filter would. Rare; cost is proportional to the global set.
+int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, double convergence_threshold,
+                         bamcl_resample_result* res);
+static int build_replicated(bamcl_pf* pf, int set_index, double dist_threshold, double convergence_threshold,
+                            bamcl_resample_result* res)
+{
+  SampleSet& set = pf->sets[set_index];
+  bamcl_comm* comm = pf->comm;
+  const int G = comm->n_ranks, me = comm->rank;
+  const long n = set.sample_count;
+  std::vector<P2P> sends, recvs;
+  double* arr[4] = {set.x.as<double>(), set.y.as<double>(), set.th.as<double>(), set.w.as<double>()};
+  const long o0 = shard_begin(n, G, me), c0 = shard_begin(n, G, me + 1) - o0;
+  for (int q = 0; q < G; q++)
+  {
+    if (q == me)
+      continue;
+    const long o = shard_begin(n, G, q), c = shard_begin(n, G, q + 1) - o;
+    for (int k = 0; k < 4; k++)
+    {
+      sends.push_back(P2P{q, arr[k] + o0, sizeof(double) * (size_t)c0});
+      recvs.push_back(P2P{q, arr[k] + o, sizeof(double) * (size_t)c});
+    }
+  }
+  BAMCL_TRY(comm_exchange(comm, sends.data(), (int)sends.size(), recvs.data(), (int)recvs.size()));
+  const long keep_off = pf->win_off;
+  const int keep_cnt = pf->win_cnt;
+  pf->comm = nullptr;
+  pf->win_off = 0;
+  pf->win_cnt = -1;
+  pf->box_valid = false;
+  const int rc = build_tree_and_stats(pf, set_index, dist_threshold, convergence_threshold, res);
+  pf->comm = comm;
+  pf->win_off = keep_off;
+  pf->win_cnt = keep_cnt;
+  pf->box_valid = false;
+  return rc;
+}
+
 int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, double convergence_threshold,
                          bamcl_resample_result* res)
 {
   bamcl_ctx* ctx = pf->ctx;
   SampleSet& set = pf->sets[set_index];
-  const int n = set.sample_count;
+  const int G = pf_ranks(pf), me = pf_rank(pf);
+  const int n_set = set.sample_count;  // the whole (global) set
+  // the samples this rank holds: its window of a distributed set, else everything
+  const long off = G > 1 ? shard_begin(n_set, G, me) : 0;
+  const int n = G > 1 ? (int)(shard_begin(n_set, G, me + 1) - off) : n_set;
   set.leaf_count = set.node_count = set.cluster_count = 0;
-  if (n <= 0)
+  if (n_set <= 0)
     return BAMCL_OK;
-  // hash capacity: power of two >= 2n
-  size_t H = 1024;
-  while (H < (size_t)n * 2)
-    H <<= 1;
-  const unsigned hmask = (unsigned)(H - 1);
-  BAMCL_TRY(pf->t_hkeys.reserve(sizeof(unsigned long long) * H));
-  BAMCL_TRY(pf->t_hfirst.reserve(sizeof(int) * H));
-  BAMCL_TRY(pf->t_hnode.reserve(sizeof(int) * H));
   const size_t cap_n = (size_t)pf->max_samples;
   BAMCL_TRY(pf->t_slot.reserve(sizeof(int) * cap_n));
   BAMCL_TRY(pf->t_flag.reserve(sizeof(int) * cap_n));
@@ -673,6 +921,10 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
   BAMCL_TRY(pf->t_out.reserve(sizeof(TreeOut)));
   BAMCL_TRY(pf->t_hout.reserve(sizeof(TreeOut)));
   BAMCL_TRY(pf->t_root.reserve(sizeof(int) * cap_n));
+  BAMCL_TRY(pf->t_ints.reserve(sizeof(int) * 32));
+  const int per_block = ST_BLOCK * ST_CHUNKS;
+  const int stat_blocks = (n + per_block - 1) / per_block;
+  BAMCL_TRY(pf->t_setpart.reserve(sizeof(double) * 12 * (size_t)std::max(stat_blocks, 1)));
   BAMCL_TRY(pf_ensure_streams(pf));
   if (pf->t_cluster_cap == 0)
     pf->t_cluster_cap = 4096;
@@ -681,26 +933,77 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
   const int blocks_n = (n + 255) / 256;
   // cell sizes exactly as pf_kdtree.cpp:35-37 writes them
   const double cx = 0.50, cy = 0.50, ct = (10 * M_PI / 180);
+  static const bool force_general = getenv("BAMCL_TREE_GENERAL") != nullptr;  // tests: exercise k_tree_build
+  const bool general_only = force_general || pf->force_general_tree;
 
-  for (int attempt = 0; attempt < 2; attempt++)
+  for (int attempt = 0; attempt < 6; attempt++)
   {
-    BAMCL_TRY(pf->t_sums.reserve(sizeof(double) * ROW * pf->t_cluster_cap));
+    if (!pf->box_valid)
+      BAMCL_TRY(fit_box(pf, set, off, n, cx, cy, ct));
+    const bool dense = pf->box_dense;
+    if (!dense && G > 1)
+      return build_replicated(pf, set_index, dist_threshold, convergence_threshold, res);
+    pf->tree_dense = dense ? 1 : 0;
+    // node-indexed arrays hold at most k_max entries
+    const int k_max = dense ? (int)std::min<long>(n_set, pf->box_cells) : n_set;
+    const int blocks_k = (k_max + 255) / 256;
+    BAMCL_TRY(pf->t_sums.reserve(sizeof(double) * (ROW * pf->t_cluster_cap + 16)));
+    double* set_tail = pf->t_sums.as<double>() + ROW * pf->t_cluster_cap;  // the 12 set sums ride behind the cluster rows
     BAMCL_TRY(set.cluster_stats.reserve(sizeof(double) * 10 * pf->t_cluster_cap));
-    BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_hkeys.p, 0xFF, sizeof(unsigned long long) * H, ctx->stream));
-    BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_hfirst.p, 0x7F, sizeof(int) * H, ctx->stream));
     BAMCL_CUDA_OK(cudaMemsetAsync(out, 0, sizeof(TreeOut), ctx->stream));
-    BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_sums.p, 0, sizeof(double) * ROW * pf->t_cluster_cap, ctx->stream));
-    BAMCL_LAUNCH(ctx, k_hash_insert, blocks_n, 256, 0, set.x.as<double>(), set.y.as<double>(), set.th.as<double>(), n, cx, cy,
-                 ct, pf->t_hkeys.as<unsigned long long>(), pf->t_hfirst.as<int>(), hmask, pf->t_slot.as<int>(), out);
-    BAMCL_LAUNCH(ctx, k_flag_first, blocks_n, 256, 0, pf->t_slot.as<int>(), pf->t_hfirst.as<int>(), pf->t_flag.as<int>(), n);
-    BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_flag.as<int>(), pf->t_flag.as<int>(), n, pf->t_scan.as<int>(), &out->K));
-    BAMCL_LAUNCH(ctx, k_make_nodes, blocks_n, 256, 0, pf->t_slot.as<int>(), pf->t_hfirst.as<int>(), pf->t_flag.as<int>(),
-                 pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), pf->t_nkey.as<unsigned long long>(),
-                 pf->t_nfirst.as<int>(), pf->t_parent.as<int>(), n);
-    static const bool force_general = getenv("BAMCL_TREE_GENERAL") != nullptr;  // tests: exercise k_tree_build
-    const bool general_only = force_general || pf->force_general_tree;
-    // ---- fork: the cluster chain (needs only the nodes and the hash) goes to the auxiliary stream and overlaps the
-    // leaf-count chain on the main stream; both join before the result is copied back
+    BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_sums.p, 0, sizeof(double) * (ROW * pf->t_cluster_cap + 16), ctx->stream));
+    Box box;
+    unsigned hmask = 0;
+    if (dense)
+    {
+      for (int d = 0; d < 3; d++)
+      {
+        box.mn[d] = pf->box_min[d];
+        box.dim[d] = pf->box_dim[d];
+      }
+      const long cells = pf->box_cells;
+      const int words = (n_set + 31) / 32;
+      BAMCL_TRY(pf->g_first.reserve(sizeof(int) * (size_t)cells));
+      BAMCL_TRY(pf->g_node.reserve(sizeof(int) * (size_t)cells));
+      BAMCL_TRY(pf->t_bits.reserve(sizeof(unsigned) * (size_t)(words + 1)));
+      BAMCL_TRY(pf->t_bpre.reserve(sizeof(int) * (size_t)(words + 1)));
+      BAMCL_CUDA_OK(cudaMemsetAsync(pf->g_first.p, 0x7F, sizeof(int) * (size_t)cells, ctx->stream));
+      BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_bits.p, 0, sizeof(unsigned) * (size_t)words, ctx->stream));
+      if (n > 0)
+        BAMCL_LAUNCH(ctx, k_grid_first, blocks_n, 256, 0, set.x.as<double>() + off, set.y.as<double>() + off,
+                     set.th.as<double>() + off, n, off, cx, cy, ct, box, pf->g_first.as<int>(), pf->t_slot.as<int>(), out);
+      if (G > 1)  // global first occurrence of every bin
+        BAMCL_TRY(comm_all_reduce(pf->comm, pf->g_first.p, (size_t)cells, CT_I32, CO_MIN));
+      const unsigned cell_blocks = (unsigned)((cells + 255) / 256);
+      BAMCL_LAUNCH(ctx, k_grid_mark, cell_blocks, 256, 0, pf->g_first.as<int>(), cells, n_set, pf->t_bits.as<unsigned>());
+      BAMCL_LAUNCH(ctx, k_popc, (words + 255) / 256, 256, 0, pf->t_bits.as<unsigned>(), words, pf->t_bpre.as<int>());
+      BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_bpre.as<int>(), pf->t_bpre.as<int>(), words, pf->t_scan.as<int>(), &out->K));
+      BAMCL_LAUNCH(ctx, k_grid_nodes, cell_blocks, 256, 0, pf->g_first.as<int>(), cells, n_set, pf->t_bits.as<unsigned>(),
+                   pf->t_bpre.as<int>(), box, pf->g_node.as<int>(), pf->t_nkey.as<unsigned long long>(), pf->t_nfirst.as<int>(),
+                   pf->t_parent.as<int>());
+    }
+    else
+    {
+      // hash capacity: power of two >= 2n
+      size_t H = 1024;
+      while (H < (size_t)n * 2)
+        H <<= 1;
+      hmask = (unsigned)(H - 1);
+      BAMCL_TRY(pf->t_hkeys.reserve(sizeof(unsigned long long) * H));
+      BAMCL_TRY(pf->t_hfirst.reserve(sizeof(int) * H));
+      BAMCL_TRY(pf->t_hnode.reserve(sizeof(int) * H));
+      BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_hkeys.p, 0xFF, sizeof(unsigned long long) * H, ctx->stream));
+      BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_hfirst.p, 0x7F, sizeof(int) * H, ctx->stream));
+      BAMCL_LAUNCH(ctx, k_hash_insert, blocks_n, 256, 0, set.x.as<double>(), set.y.as<double>(), set.th.as<double>(), n, cx, cy,
+                   ct, pf->t_hkeys.as<unsigned long long>(), pf->t_hfirst.as<int>(), hmask, pf->t_slot.as<int>(), out);
+      BAMCL_LAUNCH(ctx, k_flag_first, blocks_n, 256, 0, pf->t_slot.as<int>(), pf->t_hfirst.as<int>(), pf->t_flag.as<int>(), n);
+      BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_flag.as<int>(), pf->t_flag.as<int>(), n, pf->t_scan.as<int>(), &out->K));
+      BAMCL_LAUNCH(ctx, k_make_nodes, blocks_n, 256, 0, pf->t_slot.as<int>(), pf->t_hfirst.as<int>(), pf->t_flag.as<int>(),
+                   pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), pf->t_nkey.as<unsigned long long>(),
+                   pf->t_nfirst.as<int>(), pf->t_parent.as<int>(), n);
+    }
+    // ---- fork: the cluster chain (needs only the nodes and the bin index) goes to the auxiliary stream and overlaps the
+    // leaf-count chain on the main stream; both join before anything is exchanged or copied back
     cudaStream_t main_stream = ctx->stream;
     BAMCL_CUDA_OK(cudaEventRecord(pf->ev_fork, main_stream));
     BAMCL_CUDA_OK(cudaStreamWaitEvent(pf->aux_stream, pf->ev_fork, 0));
@@ -712,43 +1015,49 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
         ~StreamSwap() { c->stream = keep; }
       } swap{ctx, main_stream};
       ctx->stream = pf->aux_stream;
-      const long threads = (long)n * 13;
+      const long threads = (long)k_max * 13;
       static const bool cc_volatile = getenv("BAMCL_CC_VOLATILE") != nullptr;  // A/B switch: forest reads bypass L1
       // (Measured and dropped: collecting the neighbour pairs first and uniting them in a second, dense launch. The
       // unions then all contend at once: 0.73 ms for ~1M pairs against 0.38 ms for this kernel with the unions spread
       // over the probes. Also measured and dropped: one thread per node with its 13 probes issued together and its own
       // root carried through the unions (the ECL-CC shape) -- resample 1.14 ms against 0.89 ms at 1M samples / 243k
       // bins: 13x fewer threads leave the forest walks latency-bound.)
-      if (cc_volatile)
-        BAMCL_LAUNCH(ctx, k_cc_union<false>, (unsigned)((threads + 255) / 256), 256, 0, out,
-                     pf->t_nkey.as<unsigned long long>(), pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), hmask,
-                     pf->t_parent.as<int>(), n);
+      const unsigned cc_blocks = (unsigned)((threads + 255) / 256);
+      if (dense)
+      {
+        if (cc_volatile)
+          BAMCL_LAUNCH(ctx, k_cc_union_dense<false>, cc_blocks, 256, 0, out, pf->t_nkey.as<unsigned long long>(), box,
+                       pf->g_node.as<int>(), pf->t_parent.as<int>(), k_max);
+        else
+          BAMCL_LAUNCH(ctx, k_cc_union_dense<true>, cc_blocks, 256, 0, out, pf->t_nkey.as<unsigned long long>(), box,
+                       pf->g_node.as<int>(), pf->t_parent.as<int>(), k_max);
+      }
+      else if (cc_volatile)
+        BAMCL_LAUNCH(ctx, k_cc_union<false>, cc_blocks, 256, 0, out, pf->t_nkey.as<unsigned long long>(),
+                     pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), hmask, pf->t_parent.as<int>(), k_max);
       else
-        BAMCL_LAUNCH(ctx, k_cc_union<true>, (unsigned)((threads + 255) / 256), 256, 0, out,
-                     pf->t_nkey.as<unsigned long long>(), pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), hmask,
-                     pf->t_parent.as<int>(), n);
-      BAMCL_LAUNCH(ctx, k_cc_roots, blocks_n, 256, 0, out, pf->t_parent.as<int>(), pf->t_root.as<int>(), pf->t_cid.as<int>(), n);
-      BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_cid.as<int>(), pf->t_cid.as<int>(), n, pf->t_scan.as<int>(), &out->C));
+        BAMCL_LAUNCH(ctx, k_cc_union<true>, cc_blocks, 256, 0, out, pf->t_nkey.as<unsigned long long>(),
+                     pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), hmask, pf->t_parent.as<int>(), k_max);
+      BAMCL_LAUNCH(ctx, k_cc_roots, blocks_k, 256, 0, out, pf->t_parent.as<int>(), pf->t_root.as<int>(), pf->t_cid.as<int>(), k_max);
+      BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_cid.as<int>(), pf->t_cid.as<int>(), k_max, pf->t_scan.as<int>(), &out->C));
       StatsArgs sa;
-      sa.x = set.x.as<double>();
-      sa.y = set.y.as<double>();
-      sa.th = set.th.as<double>();
-      sa.w = set.w.as<double>();
+      sa.x = set.x.as<double>() + off;
+      sa.y = set.y.as<double>() + off;
+      sa.th = set.th.as<double>() + off;
+      sa.w = set.w.as<double>() + off;
       sa.n = n;
       sa.slot = pf->t_slot.as<int>();
-      sa.hnode = pf->t_hnode.as<int>();
+      sa.hnode = dense ? pf->g_node.as<int>() : pf->t_hnode.as<int>();
       sa.parent = pf->t_root.as<int>();  // final roots (k_cc_roots)
       sa.cid = pf->t_cid.as<int>();
-      sa.label = set.label.as<int>();
+      sa.label = set.label.as<int>() + off;
       sa.rows = pf->t_sums.as<double>();
       sa.cap = (int)pf->t_cluster_cap;
       sa.out = out;
-      const int per_block = ST_BLOCK * ST_CHUNKS;
-      BAMCL_LAUNCH(ctx, k_labels_stats, (n + per_block - 1) / per_block, ST_BLOCK, 0, sa);
-      BAMCL_LAUNCH(ctx, k_converged_count, std::min(blocks_n, kNumSMs * 8), 256, 0, set.x.as<double>(), set.y.as<double>(), n,
-                   dist_threshold, out);
-      BAMCL_LAUNCH(ctx, k_cluster_finalize, (unsigned)((pf->t_cluster_cap + 255) / 256), 256, 0, out, pf->t_sums.as<double>(),
-                   (int)pf->t_cluster_cap, set.cluster_stats.as<double>());
+      sa.set_part = pf->t_setpart.as<double>();
+      if (stat_blocks > 0)
+        BAMCL_LAUNCH(ctx, k_labels_stats, stat_blocks, ST_BLOCK, 0, sa);
+      BAMCL_LAUNCH(ctx, k_set_sums_final, 1, 384, 0, pf->t_setpart.as<double>(), stat_blocks, set_tail);
       BAMCL_CUDA_OK(cudaEventRecord(pf->ev_join, pf->aux_stream));
     }
     // ---- main stream: the leaf count
@@ -760,7 +1069,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       ta.child = pf->t_child.as<int>();
       ta.first_at = pf->t_first_at.as<int>();
       ta.side = pf->t_side.as<signed char>();
-      int blocks = std::min(coop_blocks_for(pf), std::max(1, (n + 511) / 512));
+      int blocks = std::min(coop_blocks_for(pf), std::max(1, (k_max + 511) / 512));
       void* args[] = {&ta};
       BAMCL_CUDA_OK(cudaLaunchCooperativeKernel((void*)k_tree_build, dim3(blocks), dim3(256), args, 0, ctx->stream));
       ctx->launches++;
@@ -768,25 +1077,47 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
     };
     if (!general_only)
     {
-      if (n > 1500000)
-        BAMCL_TRY((launch_fast_tree<M_TOP_LARGE>(pf, out, n)));
+      if (k_max > 1500000)
+        BAMCL_TRY((launch_fast_tree<M_TOP_LARGE>(pf, out, k_max)));
       else
-        BAMCL_TRY((launch_fast_tree<M_TOP_SMALL>(pf, out, n)));
+        BAMCL_TRY((launch_fast_tree<M_TOP_SMALL>(pf, out, k_max)));
     }
     else
       BAMCL_TRY(launch_general());
     BAMCL_CUDA_OK(cudaStreamWaitEvent(main_stream, pf->ev_join, 0));
+    // ---- joined: cluster rows + set sums over all ranks, then the convergence count against the global mean
+    if (G > 1)
+      BAMCL_TRY(comm_all_reduce(pf->comm, pf->t_sums.p, ROW * pf->t_cluster_cap + 12, CT_F64, CO_SUM));
+    BAMCL_CUDA_OK(cudaMemcpyAsync(out->set_sums, set_tail, sizeof(double) * 12, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (n > 0)
+      BAMCL_LAUNCH(ctx, k_converged_count, std::min(blocks_n, kNumSMs * 8), 256, 0, set.x.as<double>() + off,
+                   set.y.as<double>() + off, n, dist_threshold, out, n_set);
+    if (G > 1)
+    {
+      int* ints = pf->t_ints.as<int>();
+      BAMCL_LAUNCH(ctx, k_ints_pack, 1, 1, 0, out, pf_flags(pf), ints);
+      BAMCL_TRY(comm_all_reduce(pf->comm, ints, 8, CT_I32, CO_SUM));
+      BAMCL_LAUNCH(ctx, k_ints_unpack, 1, 1, 0, ints, out, pf_flags(pf));
+    }
+    BAMCL_LAUNCH(ctx, k_cluster_finalize, (unsigned)((pf->t_cluster_cap + 255) / 256), 256, 0, out, pf->t_sums.as<double>(),
+                 (int)pf->t_cluster_cap, set.cluster_stats.as<double>());
     BAMCL_CUDA_OK(cudaMemcpyAsync(h_out, out, sizeof(TreeOut), cudaMemcpyDeviceToHost, ctx->stream));
     BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    if (h_out->err & 1)
+      return set_error(BAMCL_E_UNSUPPORTED, "a pose is outside the kd-tree key range (|x|,|y| < 5e5 m, |theta| < 3.6e5 rad)");
+    if (h_out->err & 4)
+    {
+      pf->box_valid = false;  // a bin outside the sticky box (the cloud moved): re-fit and repeat
+      continue;
+    }
     if (!general_only && !h_out->fast_ok)
     {
-      // a bucket outgrew shared memory (adversarial insertion order): the grid-synchronous build takes over
+      // a bucket outgrew shared memory (adversarial insertion order): the grid-synchronous build takes over. Every rank
+      // of a distributed filter sees the same flag and builds the whole tree (the partial sums above were all zero).
       BAMCL_TRY(launch_general());
       BAMCL_CUDA_OK(cudaMemcpyAsync(h_out, out, sizeof(TreeOut), cudaMemcpyDeviceToHost, ctx->stream));
       BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
     }
-    if (h_out->err & 1)
-      return set_error(BAMCL_E_UNSUPPORTED, "a pose is outside the kd-tree key range (|x|,|y| < 5e5 m, |theta| < 3.6e5 rad)");
     if ((h_out->err & 2) || (size_t)h_out->C > pf->t_cluster_cap)
     {
       // more clusters than rows: grow and redo (rare: only widely scattered sets have thousands of components)
@@ -796,8 +1127,13 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       pf->t_cluster_cap = want;
       continue;
     }
+    // a box far larger than the occupied bins (the cloud converged) costs a pass over its cells every time: re-fit next time
+    if (dense && pf->box_cells > (1l << 20) && (long)h_out->K * 64 < pf->box_cells)
+      pf->box_valid = false;
     break;
   }
+  if (h_out->err & 4)
+    return set_error(BAMCL_E_STATE, "pose-bin box could not be fitted");
   set.leaf_count = h_out->leaf;
   set.node_count = h_out->K;
   set.cluster_count = h_out->C;
@@ -818,7 +1154,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
   res->node_count = h_out->K;
   res->cluster_count = h_out->C;
   // updateConverged :206-219 (percentage in float, as the reference computes it)
-  const double percent = static_cast<float>(h_out->conv) / static_cast<float>(n) * 100;
+  const double percent = static_cast<float>(h_out->conv) / static_cast<float>(n_set) * 100;
   res->converged = percent >= convergence_threshold ? 1 : 0;
   return BAMCL_OK;
 }
@@ -828,12 +1164,15 @@ extern "C" {
 
 int bamcl_pf_sample_clusters(bamcl_pf* pf, int* labels, long n)
 {
-  if (!pf || !labels || n != pf->sets[pf->current].sample_count)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_sample_clusters: n must equal sample_count");
+  long off = 0, cnt = 0;
+  if (pf)
+    bamcl::pf_owned(pf, &off, &cnt);
+  if (!pf || !labels || n != cnt)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_sample_clusters: n must equal sample_count (a distributed filter: its window)");
   if (n == 0)
     return BAMCL_OK;
-  BAMCL_CUDA_OK(cudaMemcpyAsync(labels, pf->sets[pf->current].label.p, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost,
-                                pf->ctx->stream));
+  BAMCL_CUDA_OK(cudaMemcpyAsync(labels, pf->sets[pf->current].label.as<int>() + off, sizeof(int) * (size_t)n,
+                                cudaMemcpyDeviceToHost, pf->ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
   return BAMCL_OK;
 }

@@ -197,6 +197,32 @@ int bamcl::pf_read_scalar(bamcl_pf* pf, int slot, double* out)
   return BAMCL_OK;
 }
 
+namespace bamcl
+{
+int pf_shard_finish_update(bamcl_pf* pf, double* total_out);
+}
+
+// Distributed update, after the scoring kernel ran over this rank's window and its total sits in scalars[0]: the ranks'
+// window totals are all-gathered and summed in rank order (= the sample order in which ParticleFilter::updateSensor adds
+// up, particle_filter.cpp:246-252), every rank normalises its window by that global total. One host read at the end.
+int bamcl::pf_shard_finish_update(bamcl_pf* pf, double* total_out)
+{
+  const int G = pf_ranks(pf), me = pf_rank(pf);
+  if (G > 384)
+    return set_error(BAMCL_E_UNSUPPORTED, "more than 384 ranks");
+  SampleSet& s = pf->sets[pf->current];
+  double* sc = pf->scalars.as<double>();
+  double* totals = sc + 64;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(totals + me, sc, sizeof(double), cudaMemcpyDeviceToDevice, pf->ctx->stream));
+  BAMCL_TRY(comm_all_gather(pf->comm, totals + me, totals, sizeof(double)));
+  const int cnt = s.sample_count == 0 ? 0 : pf_win_cnt(pf);
+  BAMCL_LAUNCH(pf->ctx, k_normalise_ranks, (std::max(cnt, 1) + 255) / 256, 256, 0, s.w.as<double>() + pf_win_off(pf), cnt, totals,
+               G, s.sample_count, sc + 1);
+  if (total_out)
+    return read_scalar(pf, 1, total_out);
+  return BAMCL_OK;
+}
+
 extern "C" {
 
 int bamcl_pf_create(bamcl_ctx* ctx, int min_samples, int max_samples, bamcl_pf** out)
@@ -225,9 +251,9 @@ int bamcl_pf_create(bamcl_ctx* ctx, int min_samples, int max_samples, bamcl_pf**
   }
   BAMCL_CUDA_OK(cudaEventCreate(&pf->score_ev0));
   BAMCL_CUDA_OK(cudaEventCreate(&pf->score_ev1));
-  BAMCL_TRY(pf->scalars.reserve(sizeof(double) * 64));
-  BAMCL_TRY(pf->h_scalars.reserve(sizeof(double) * 64));
-  BAMCL_CUDA_OK(cudaMemsetAsync(pf->scalars.p, 0, sizeof(double) * 64, ctx->stream));
+  BAMCL_TRY(pf->scalars.reserve(sizeof(double) * 512));
+  BAMCL_TRY(pf->h_scalars.reserve(sizeof(double) * 512));
+  BAMCL_CUDA_OK(cudaMemsetAsync(pf->scalars.p, 0, sizeof(double) * 512, ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
   *out = pf;
   return BAMCL_OK;
@@ -271,6 +297,9 @@ int bamcl_pf_destroy(bamcl_pf* pf)
                            &pf->t_child, &pf->t_first_at, &pf->t_side, &pf->t_parent, &pf->t_cid, &pf->t_nfirst, &pf->t_root, &pf->t_scan,
                            &pf->t_out, &pf->t_sums, &pf->t_fast})
     b->release();
+  for (bamcl::DevBuf* b : {&pf->g_first, &pf->g_node, &pf->t_bits, &pf->t_bpre, &pf->t_setpart, &pf->t_ints, &pf->stage_x,
+                           &pf->stage_y, &pf->stage_th, &pf->stage_src, &pf->scan.agree, &pf->scan.skip_count, &pf->scan.beams_sel})
+    b->release();
   pf->t_hout.release();
   if (pf->aux_stream)
     cudaStreamDestroy(pf->aux_stream);
@@ -305,6 +334,9 @@ int bamcl_pf_upload_samples(bamcl_pf* pf, const double* aos, long n)
   if (!pf || !aos || n < 0 || n > pf->max_samples)
     return set_error(BAMCL_E_ARG, "bamcl_pf_upload_samples: need 0 <= n <= max_samples");
   SampleSet& s = pf->sets[pf->current];
+  if (pf_ranks(pf) > 1)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_upload_samples: a distributed filter uploads its window "
+                                    "(bamcl_pf_shard_set_count + bamcl_pf_upload_window_samples)");
   s.sample_count = (int)n;
   pf->win_cnt = -1;  // a new set: back to the whole-set window
   if (n == 0)
@@ -378,18 +410,30 @@ int bamcl_pf_sample_count(bamcl_pf* pf, int* n)
 
 int bamcl_pf_upload_weights(bamcl_pf* pf, const double* w, long n)
 {
-  if (!pf || !w || n != pf->sets[pf->current].sample_count)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_upload_weights: n must equal sample_count");
-  BAMCL_CUDA_OK(cudaMemcpyAsync(pf->sets[pf->current].w.p, w, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, pf->ctx->stream));
+  long off = 0, cnt = 0;
+  if (pf)
+    pf_owned(pf, &off, &cnt);
+  if (!pf || !w || n != cnt)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_upload_weights: n must equal sample_count (a distributed filter: its window)");
+  if (n == 0)
+    return BAMCL_OK;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(pf->sets[pf->current].w.as<double>() + off, w, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice,
+                                pf->ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
   return BAMCL_OK;
 }
 
 int bamcl_pf_download_weights(bamcl_pf* pf, double* w, long n)
 {
-  if (!pf || !w || n != pf->sets[pf->current].sample_count)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_download_weights: n must equal sample_count");
-  BAMCL_CUDA_OK(cudaMemcpyAsync(w, pf->sets[pf->current].w.p, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, pf->ctx->stream));
+  long off = 0, cnt = 0;
+  if (pf)
+    pf_owned(pf, &off, &cnt);
+  if (!pf || !w || n != cnt)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_download_weights: n must equal sample_count (a distributed filter: its window)");
+  if (n == 0)
+    return BAMCL_OK;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(w, pf->sets[pf->current].w.as<double>() + off, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost,
+                                pf->ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
   return BAMCL_OK;
 }
@@ -492,33 +536,23 @@ int bamcl_pf_score_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, 
   return read_scalar(pf, 0, total_out);
 }
 
-int bamcl_pf_score_planar_staged_dev(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_dev)
+int bamcl_pf_shard_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out)
 {
-  if (pf)
-    pf->set_converged = converged;
-  if (!pf || !map || !total_dev)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_score_planar_staged_dev: bad arguments");
-  if (pf->scan.valid && pf->scan.model.max_beams < 2)
+  if (!pf || !map)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_update_planar_staged: bad arguments");
+  if (!pf->comm)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_shard_update_planar_staged: no communicator attached");
+  pf->set_converged = converged;
+  pf_apply_shard_window(pf);
+  if (pf->scan.valid && pf->scan.model.max_beams < 2)  // updateSensor returns false on every rank, nothing happens (:128)
   {
-    BAMCL_CUDA_OK(cudaMemsetAsync(total_dev, 0, sizeof(double), pf->ctx->stream));
+    if (total_out)
+      *total_out = 0.0;
     return BAMCL_OK;
   }
   BAMCL_TRY(launch_score(pf, map));
   BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
-  BAMCL_CUDA_OK(cudaMemcpyAsync(total_dev, pf->scalars.as<double>(), sizeof(double), cudaMemcpyDeviceToDevice,
-                                pf->ctx->stream));
-  return BAMCL_OK;
-}
-
-int bamcl_pf_normalise_ranks_dev(bamcl_pf* pf, const double* totals_dev, int n_ranks, double* total_out_dev)
-{
-  if (!pf || !totals_dev || n_ranks < 1 || !total_out_dev)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_normalise_ranks_dev: bad arguments");
-  SampleSet& s = pf->sets[pf->current];
-  const int cnt = s.sample_count == 0 ? 0 : pf_win_cnt(pf);
-  BAMCL_LAUNCH(pf->ctx, k_normalise_ranks, (std::max(cnt, 1) + 255) / 256, 256, 0, s.w.as<double>() + pf_win_off(pf), cnt,
-               totals_dev, n_ranks, s.sample_count, total_out_dev);
-  return BAMCL_OK;
+  return pf_shard_finish_update(pf, total_out);
 }
 
 int bamcl_pf_update_planar_host(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,

@@ -2,6 +2,7 @@
 #pragma once
 #include <vector>
 
+#include "comm.cuh"
 #include "common.cuh"
 #include "map2d.cuh"
 
@@ -121,6 +122,19 @@ struct bamcl_pf
   // CDF work on this rank's window [win_off, win_off + win_cnt) of the current set. win_cnt < 0 = whole set.
   long win_off = 0;
   int win_cnt = -1;
+  // Distributed filter (bamcl_pf_shard_attach): every rank OWNS its window of the global set -- only those samples are
+  // valid in this rank's arrays (global indexing is kept, so sample i lives at index i on its owner).
+  bamcl_comm* comm = nullptr;
+  int cdf_slow_cap = 32;          // slow CDF tiles a rank can ship in its summary; grown on demand
+  double* cdf_bounds = nullptr;   // device, [n_ranks + 1]: exact CDF value at every rank boundary (last pf_build_cdf)
+  // Dense pose-bin grid (kdtree.cu): bins of the box [box_min, box_min + box_dim) are addressed directly instead of
+  // hashed. The box is sticky between resamples and re-fitted when a key falls outside it or it has become far too big.
+  bool box_valid = false, box_dense = false;
+  int box_min[3] = {0, 0, 0}, box_dim[3] = {0, 0, 0};
+  long box_cells = 0;
+  bamcl::DevBuf g_first, g_node, t_bits, t_bpre, t_setpart, t_ints;
+  bamcl::DevBuf stage_x, stage_y, stage_th, stage_src;  // rows this rank selected for other ranks (shard exchange)
+  int tree_dense = 0;  // the last tree build addressed the bins directly
 };
 
 namespace bamcl
@@ -130,6 +144,27 @@ inline int* pf_flags(bamcl_pf* pf) { return reinterpret_cast<int*>(pf->scalars.a
 // this rank's window of the current set
 inline long pf_win_off(const bamcl_pf* pf) { return pf->win_cnt < 0 ? 0 : pf->win_off; }
 inline int pf_win_cnt(const bamcl_pf* pf) { return pf->win_cnt < 0 ? pf->sets[pf->current].sample_count : pf->win_cnt; }
+inline int pf_ranks(const bamcl_pf* pf) { return pf->comm ? pf->comm->n_ranks : 1; }
+inline int pf_rank(const bamcl_pf* pf) { return pf->comm ? pf->comm->rank : 0; }
+// rank-major contiguous partition of n samples: rank r owns [shard_begin(n, G, r), shard_begin(n, G, r + 1))
+inline long shard_begin(long n, int n_ranks, int r) { return n * (long)r / n_ranks; }
+// the samples this rank holds: its window of a distributed set, else the whole current set
+inline void pf_owned(const bamcl_pf* pf, long* off, long* cnt)
+{
+  const long n = pf->sets[pf->current].sample_count;
+  const int G = pf_ranks(pf), r = pf_rank(pf);
+  *off = G > 1 ? shard_begin(n, G, r) : 0;
+  *cnt = G > 1 ? shard_begin(n, G, r + 1) - *off : n;
+}
+// a distributed filter works on the window it owns: set it from the current set's (global) sample count
+inline void pf_apply_shard_window(bamcl_pf* pf)
+{
+  if (pf_ranks(pf) <= 1)
+    return;
+  const long n = pf->sets[pf->current].sample_count;
+  pf->win_off = shard_begin(n, pf_ranks(pf), pf_rank(pf));
+  pf->win_cnt = (int)(shard_begin(n, pf_ranks(pf), pf_rank(pf) + 1) - pf->win_off);
+}
 }
 
 namespace bamcl
@@ -139,5 +174,5 @@ int pf_read_scalar(bamcl_pf* pf, int slot, double* out);  // device scalar slot 
 int pf_normalise_by_device_total(bamcl_pf* pf);           // w /= scalars[0] (or 1/n), particle_filter.cpp:237-266
 int pf_ensure_streams(bamcl_pf* pf);                      // side streams + events, created on first use
 int pf_download_async(bamcl_pf* pf, double* aos, long n); // current set -> host AoS on the copy stream (after the main stream's work so far)
-int pf_build_cdf(bamcl_pf* pf, double c0 = 0.0);           // exact sequential CDF of the window, starting at c0
+int pf_build_cdf(bamcl_pf* pf);  // exact sequential CDF of this rank's window (global values) + the rank bounds
 }

@@ -13,9 +13,12 @@
 //     before knowing their exact start value; the few tiles that contain a binade crossing wait for the exact
 //     start value, scan up to the crossing, take the crossing step as a real FP add, and continue.
 // The systematic targets get the same treatment on the host in closed form (<= ~100 binade segments).
+#include <algorithm>
 #include <climits>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "pf.cuh"
 #include "scan.cuh"
@@ -108,13 +111,6 @@ __device__ __forceinline__ long long mantissa_of(double s)
 }
 __device__ __forceinline__ double from_units(long long m, int e) { return scalbn((double)m, e - 52); }
 
-__device__ __forceinline__ Fn shfl_fn(const Fn& f, int src)
-{
-  Fn r;
-  r.d0 = __shfl_sync(0xffffffffu, f.d0, src);
-  r.d1 = __shfl_sync(0xffffffffu, f.d1, src);
-  return r;
-}
 __device__ __forceinline__ Fn shfl_up_fn(const Fn& f, int d)
 {
   Fn r;
@@ -181,12 +177,91 @@ __global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tile_sums(const double* __res
   }
 }
 
-// one block: approximate start value of every tile and the fast/slow decision
-__global__ void __launch_bounds__(1024) k_cdf_classify(const double* __restrict__ sums, int n_tiles, int n,
-                                                       double* __restrict__ starts, int* __restrict__ tile_e, double c0)
+// ---------------------------------------------------------------------------------------------
+// The CDF in three stream-ordered steps (no kernel ever waits for another block):
+//   k_cdf_tile_fns  every fast tile's aggregate function; slow tiles are listed (and, on a sharded set, their raw
+//                   weights copied into the summary that is all-gathered);
+//   k_cdf_resolve   ONE block walks the ranks' tile summaries in order: runs of fast tiles by a block-wide scan of the
+//                   aggregate functions, slow tiles by the sequential-rounding loop below. Out come the exact start
+//                   value of every tile of this rank and the exact CDF value at every rank boundary ("bounds": the
+//                   exclusive scan over ranks that resampleSystematic needs, particle_filter.cpp:280-285);
+//   k_cdf_apply     every tile re-derives its elements from its exact start value and writes c[].
+// ---------------------------------------------------------------------------------------------
+struct CdfHdr  // what a rank publishes before tiles can be classified
+{
+  double local_sum;  // tree-shaped (approximate) sum of the window's weights
+  long long n;       // samples in the window
+  int n_tiles;
+  int pad[11];
+};
+static_assert(sizeof(CdfHdr) == 64, "CdfHdr is exchanged as 64 bytes");
+
+// per-rank tile summary in ONE buffer (one all-gather ships it):
+//   d0[T] d1[T] | slow_w[w_cap * CDF_TILE] | tile_e[T] | slow_tile[cap] | meta[4] = {n_slow, overflow, 0, 0}
+struct CdfPack
+{
+  long long *d0, *d1;
+  double* slow_w;
+  int *tile_e, *slow_tile, *meta;
+};
+__host__ __device__ inline size_t cdf_pack_bytes(int T, int cap, int w_cap)
+{
+  const size_t b = (size_t)T * 16 + (size_t)w_cap * CDF_TILE * 8 + (size_t)T * 4 + (size_t)cap * 4 + 16;
+  return (b + 15) & ~(size_t)15;
+}
+__host__ __device__ inline CdfPack cdf_pack_at(void* base, int T, int cap, int w_cap)
+{
+  CdfPack p;
+  p.d0 = static_cast<long long*>(base);
+  p.d1 = p.d0 + T;
+  p.slow_w = reinterpret_cast<double*>(p.d1 + T);
+  p.tile_e = reinterpret_cast<int*>(p.slow_w + (size_t)w_cap * CDF_TILE);
+  p.slow_tile = p.tile_e + T;
+  p.meta = p.slow_tile + cap;
+  return p;
+}
+
+__global__ void __launch_bounds__(1024) k_cdf_hdr(const double* __restrict__ sums, int n_tiles, long long n, CdfHdr* hdr)
+{
+  __shared__ double s_part[32];
+  const int per = (n_tiles + 1023) / 1024;
+  const int lo = min(n_tiles, (int)threadIdx.x * per), hi = min(n_tiles, lo + per);
+  double acc = 0.0;
+  for (int i = lo; i < hi; i++)
+    acc += sums[i];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0)
+    s_part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32)
+  {
+    double t = warp_sum(s_part[threadIdx.x]);
+    if (threadIdx.x == 0)
+    {
+      hdr->local_sum = t;
+      hdr->n = n;
+      hdr->n_tiles = n_tiles;
+    }
+  }
+}
+
+// one block: approximate start value of every tile of THIS rank (the ranks before it enter through their published
+// sums) and the fast/slow decision; slow tiles are listed in tile order
+__global__ void __launch_bounds__(1024) k_cdf_classify(const double* __restrict__ sums, int n_tiles, const CdfHdr* __restrict__ hdrs,
+                                                       int rank, int n_ranks, double* __restrict__ starts, CdfPack pack, int cap,
+                                                       int* __restrict__ tile_slot)
 {
   __shared__ double s_part[1024];
+  __shared__ int s_cnt[1024];
   __shared__ double s_total;
+  double c0 = 0.0, total_all = 0.0, units = 64.0 + n_ranks;
+  for (int q = 0; q < n_ranks; q++)
+  {
+    if (q == rank)
+      c0 = total_all;
+    total_all += hdrs[q].local_sum;
+    units += (double)hdrs[q].n + (double)hdrs[q].n_tiles;
+  }
   // chunked serial-by-thread scan: thread t owns a contiguous run of tiles
   const int per = (n_tiles + 1023) / 1024;
   const int lo = min(n_tiles, (int)threadIdx.x * per), hi = min(n_tiles, lo + per);
@@ -197,7 +272,7 @@ __global__ void __launch_bounds__(1024) k_cdf_classify(const double* __restrict_
   __syncthreads();
   if (threadIdx.x == 0)
   {
-    double run = c0;  // value of the CDF before the first element (0 unless this is a later shard of a sharded set)
+    double run = c0;  // approximate value of the CDF before this rank's first element
     for (int i = 0; i < 1024; i++)
     {
       const double t = s_part[i];
@@ -216,179 +291,70 @@ __global__ void __launch_bounds__(1024) k_cdf_classify(const double* __restrict_
   if (threadIdx.x == 0)
     starts[n_tiles] = s_total;
   __syncthreads();
-  const double err = 2.0 * ((double)n + (double)n_tiles + 64.0) * 1.1102230246251565e-16 * s_total;
+  // every approximate value is within err of the sequentially rounded one (n roundings of at most u * total each, and
+  // as many again for the tree-shaped sums)
+  const double err = 2.0 * units * 1.1102230246251565e-16 * total_all;
+  int slow = 0;
   for (int i = lo; i < hi; i++)
   {
     const double a = starts[i] - err, b = starts[i + 1] + err;
     int e = INT_MIN;  // slow
     if (a > 2.2250738585072014e-308 && isfinite(b) && exponent_of(a) == exponent_of(b))
       e = exponent_of(a);
-    tile_e[i] = e;
+    pack.tile_e[i] = e;
+    slow += e == INT_MIN ? 1 : 0;
+  }
+  // ordered compaction of the slow tiles
+  s_cnt[threadIdx.x] = slow;
+  __syncthreads();
+  for (int o = 1; o < 1024; o <<= 1)
+  {
+    const int v = threadIdx.x >= o ? s_cnt[threadIdx.x - o] : 0;
+    __syncthreads();
+    s_cnt[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int at = s_cnt[threadIdx.x] - slow;
+  for (int i = lo; i < hi; i++)
+  {
+    int slot = -1;
+    if (pack.tile_e[i] == INT_MIN)
+    {
+      slot = at++;
+      if (slot < cap)
+        pack.slow_tile[slot] = i;
+    }
+    tile_slot[i] = slot;
+  }
+  if (threadIdx.x == 1023)
+  {
+    const int n_slow = s_cnt[1023];
+    pack.meta[0] = min(n_slow, cap);
+    pack.meta[1] = n_slow > cap ? 1 : 0;
+    pack.meta[2] = pack.meta[3] = 0;
   }
 }
 
-struct CdfArgs
+struct SlowShared
 {
-  const double* w;
-  int n;
-  double* c;  // n + 1
-  const int* tile_e;
-  int* status;
-  long long* d0;
-  long long* d1;
-  double* incl;
-  int* counter;
-  int* flags;  // bit1: unsupported value (subnormal running sum / inconsistent binade)
-  double c0;   // c[0]: 0, or the exact end value of the previous shard (sharded filter)
+  Fn warp[CDF_BLOCK / 32 + 1];
+  int first;
+  double val;
 };
 
-// exact inclusive value of tile t-1, by warp 0
-__device__ double cdf_lookback(const CdfArgs& a, int t)
+// The reference's loop c[i+1] = c[i] + w[i] over one tile whose running sum may change binade: scan to the first
+// crossing inside the current binade, take the crossing step as a real FP add, continue. Thread t holds elements
+// [t * CDF_ITEMS, (t + 1) * CDF_ITEMS) of the tile in wv. c_tile (may be null) receives c_tile[i + 1] for element i.
+// Returns the value after the last element. All CDF_BLOCK threads call it.
+__device__ double slow_tile_scan(double s, const double (&wv)[CDF_ITEMS], int tile_n, double* c_tile, SlowShared& sh, int* flags)
 {
-  const int lane = threadIdx.x & 31;
-  Fn G;
-  G.d0 = G.d1 = 0;
-  int j = t - 1;
-  for (;;)
-  {
-    const int jj = j - lane;
-    int st = ST_INCL;
-    if (jj >= 0)
-    {
-      do
-      {
-        st = *((volatile int*)&a.status[jj]);
-      } while (st == ST_EMPTY);
-    }
-    __threadfence();
-    Fn F;
-    F.d0 = F.d1 = 0;
-    double base = a.c0;  // "tile -1" ends at c[0]
-    if (jj >= 0)
-    {
-      if (st == ST_AGG)
-      {
-        F.d0 = *((volatile long long*)&a.d0[jj]);
-        F.d1 = *((volatile long long*)&a.d1[jj]);
-      }
-      else
-        base = *((volatile double*)&a.incl[jj]);
-    }
-    const unsigned incl_mask = __ballot_sync(0xffffffffu, st == ST_INCL);
-    const int L = incl_mask ? (__ffs(incl_mask) - 1) : 32;
-    Fn acc;
-    acc.d0 = acc.d1 = 0;
-    for (int k = L - 1; k >= 0; k--)
-      acc = compose(acc, shfl_fn(F, k));
-    G = compose(acc, G);
-    if (incl_mask)
-    {
-      const double b = __shfl_sync(0xffffffffu, base, L);
-      if (G.d0 == 0 && G.d1 == 0)
-        return b;
-      if (!(b >= 2.2250738585072014e-308))
-      {
-        if (lane == 0)
-          atomicOr(a.flags, 2);
-        return b;
-      }
-      const long long m = mantissa_of(b);
-      const long long m2 = m + fn_at(G, m);
-      if (m2 >= TWO53 && lane == 0)
-        atomicOr(a.flags, 2);
-      return from_units(m2, exponent_of(b));
-    }
-    j -= 32;
-  }
-}
-
-__global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tiles(const CdfArgs a)
-{
-  __shared__ Fn s_warp[CDF_BLOCK / 32 + 1];
-  __shared__ int s_tile, s_first;
-  __shared__ double s_val;
-  if (threadIdx.x == 0)
-    s_tile = atomicAdd(a.counter, 1);
-  __syncthreads();
-  const int t = s_tile;
-  const int idx0 = t * CDF_TILE + threadIdx.x * CDF_ITEMS;
-  double wv[CDF_ITEMS];
-#pragma unroll
-  for (int k = 0; k < CDF_ITEMS; k++)
-    wv[k] = (idx0 + k < a.n) ? a.w[idx0 + k] : 0.0;
-  if (t == 0 && threadIdx.x == 0)
-    a.c[0] = a.c0;
-  const int e_fast = a.tile_e[t];
-  const bool last_thread = threadIdx.x == CDF_BLOCK - 1;
-
-  if (e_fast != INT_MIN)
-  {
-    // ---- fast tile: the whole tile stays in binade e_fast
-    Fn f[CDF_ITEMS];
-    Fn mine;
-    mine.d0 = mine.d1 = 0;
-#pragma unroll
-    for (int k = 0; k < CDF_ITEMS; k++)
-    {
-      f[k] = elem_fn(wv[k], e_fast);
-      mine = compose(mine, f[k]);
-    }
-    Fn agg;
-    const Fn ex = block_scan_fn(mine, s_warp, &agg);
-    if (threadIdx.x == 0)
-    {
-      a.d0[t] = agg.d0;
-      a.d1[t] = agg.d1;
-      __threadfence();
-      *((volatile int*)&a.status[t]) = ST_AGG;
-    }
-    if (threadIdx.x < 32)
-    {
-      const double v = cdf_lookback(a, t);
-      if (threadIdx.x == 0)
-        s_val = v;
-    }
-    __syncthreads();
-    const double s_in = s_val;
-    if (exponent_of(s_in) != e_fast && threadIdx.x == 0)
-      atomicOr(a.flags, 2);
-    const long long m_in = mantissa_of(s_in);
-    long long m = m_in + fn_at(ex, m_in);
-#pragma unroll
-    for (int k = 0; k < CDF_ITEMS; k++)
-    {
-      m += fn_at(f[k], m);
-      if (idx0 + k < a.n)
-        a.c[idx0 + k + 1] = from_units(m, e_fast);
-    }
-    if (last_thread)
-    {
-      if (m >= TWO53)
-        atomicOr(a.flags, 2);
-      a.incl[t] = from_units(m, e_fast);
-      __threadfence();
-      *((volatile int*)&a.status[t]) = ST_INCL;
-    }
-    return;
-  }
-
-  // ---- slow tile: needs the exact start value first
-  if (threadIdx.x < 32)
-  {
-    const double v = (t == 0) ? a.c0 : cdf_lookback(a, t);
-    if (threadIdx.x == 0)
-      s_val = v;
-  }
-  __syncthreads();
-  double s = s_val;
   int start = 0;  // first element of the tile not yet finalised
-  const int tile_n = min(CDF_TILE, a.n - t * CDF_TILE);
   const int local0 = threadIdx.x * CDF_ITEMS;
   while (start < tile_n)
   {
     __syncthreads();
     if (threadIdx.x == 0)
-      s_first = INT_MAX;
+      sh.first = INT_MAX;
     __syncthreads();
     if (s == 0.0)
     {
@@ -399,31 +365,32 @@ __global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tiles(const CdfArgs a)
         if (local0 + k >= start && local0 + k < tile_n && wv[k] != 0.0)
           first = local0 + k;
       if (first != INT_MAX)
-        atomicMin(&s_first, first);
+        atomicMin(&sh.first, first);
       __syncthreads();
-      const int fz = min(s_first, tile_n);
+      const int fz = min(sh.first, tile_n);
 #pragma unroll
       for (int k = 0; k < CDF_ITEMS; k++)
       {
         const int li = local0 + k;
-        if (li >= start && li < fz)
-          a.c[idx0 + k + 1] = 0.0;
+        if (c_tile && li >= start && li < fz)
+          c_tile[li + 1] = 0.0;
         if (li == fz && li < tile_n)
         {
-          a.c[idx0 + k + 1] = wv[k];
-          s_val = wv[k];
+          if (c_tile)
+            c_tile[li + 1] = wv[k];
+          sh.val = wv[k];
         }
       }
       __syncthreads();
       if (fz < tile_n)
-        s = s_val;
+        s = sh.val;
       start = fz + 1;
       continue;
     }
     if (!(s >= 2.2250738585072014e-308) || !isfinite(s))
     {
       if (threadIdx.x == 0)
-        atomicOr(a.flags, 2);
+        atomicOr(flags, 2);
       break;
     }
     const int e = exponent_of(s);
@@ -440,7 +407,7 @@ __global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tiles(const CdfArgs a)
         f[k].d0 = f[k].d1 = 0;
       mine = compose(mine, f[k]);
     }
-    const Fn ex = block_scan_fn(mine, s_warp, nullptr);
+    const Fn ex = block_scan_fn(mine, sh.warp, nullptr);
     const long long m_in = mantissa_of(s);
     long long m = m_in + fn_at(ex, m_in);
     long long mk[CDF_ITEMS];
@@ -461,37 +428,207 @@ __global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tiles(const CdfArgs a)
       }
     }
     if (cross != INT_MAX)
-      atomicMin(&s_first, cross);
+      atomicMin(&sh.first, cross);
     __syncthreads();
-    const int cr = s_first;
+    const int cr = sh.first;
     const int stop = min(cr, tile_n);
 #pragma unroll
     for (int k = 0; k < CDF_ITEMS; k++)
     {
       const int li = local0 + k;
-      if (li >= start && li < stop)
-        a.c[idx0 + k + 1] = from_units(mk[k], e);
+      if (c_tile && li >= start && li < stop)
+        c_tile[li + 1] = from_units(mk[k], e);
       if (li == cr)
       {
         // the crossing add itself, as the reference does it
         const double before = from_units(mk[k], e);
         const double after = before + wv[k];
-        a.c[idx0 + k + 1] = after;
-        s_val = after;
+        if (c_tile)
+          c_tile[li + 1] = after;
+        sh.val = after;
       }
       else if (cr == INT_MAX && li == tile_n - 1)
-        s_val = from_units(mk[k], e);
+        sh.val = from_units(mk[k], e);
     }
     __syncthreads();
-    s = s_val;
+    s = sh.val;
     start = (cr == INT_MAX) ? tile_n : cr + 1;
   }
-  if (threadIdx.x == 0)
+  __syncthreads();
+  return s;
+}
+
+__global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tile_fns(const double* __restrict__ w, int n, CdfPack pack, int w_cap,
+                                                            const int* __restrict__ tile_slot)
+{
+  __shared__ Fn s_warp[CDF_BLOCK / 32 + 1];
+  const int t = blockIdx.x;
+  const int idx0 = t * CDF_TILE + threadIdx.x * CDF_ITEMS;
+  double wv[CDF_ITEMS];
+#pragma unroll
+  for (int k = 0; k < CDF_ITEMS; k++)
+    wv[k] = (idx0 + k < n) ? w[idx0 + k] : 0.0;
+  const int e = pack.tile_e[t];
+  if (e != INT_MIN)
   {
-    a.incl[t] = s;
-    __threadfence();
-    *((volatile int*)&a.status[t]) = ST_INCL;
+    Fn mine;
+    mine.d0 = mine.d1 = 0;
+#pragma unroll
+    for (int k = 0; k < CDF_ITEMS; k++)
+      mine = compose(mine, elem_fn(wv[k], e));
+    Fn agg;
+    block_scan_fn(mine, s_warp, &agg);
+    if (threadIdx.x == 0)
+    {
+      pack.d0[t] = agg.d0;
+      pack.d1[t] = agg.d1;
+    }
+    return;
   }
+  if (threadIdx.x == 0)
+    pack.d0[t] = pack.d1[t] = 0;
+  const int slot = tile_slot[t];
+  if (slot >= 0 && slot < w_cap)
+  {
+    double* dst = pack.slow_w + (size_t)slot * CDF_TILE + threadIdx.x * CDF_ITEMS;
+#pragma unroll
+    for (int k = 0; k < CDF_ITEMS; k++)
+      dst[k] = wv[k];
+  }
+}
+
+struct ResolveArgs
+{
+  int n_ranks, me, T, cap, w_cap;
+  const CdfHdr* hdrs;  // [n_ranks]
+  char* packs;         // [n_ranks] summaries, pack_bytes apart
+  size_t pack_bytes;
+  const double* w;  // this rank's window (its slow tiles are read in place)
+  double* bounds;   // [n_ranks + 1] exact CDF value at every rank boundary
+  double* starts;   // [tiles of this rank] exact start value of every tile
+  int* flags;       // bit1 unsupported running sum, bit2 a rank listed more slow tiles than fit its summary
+};
+
+__global__ void __launch_bounds__(CDF_BLOCK) k_cdf_resolve(const ResolveArgs a)
+{
+  __shared__ SlowShared sh;
+  for (int q = 0; q < a.n_ranks; q++)
+    if (cdf_pack_at(a.packs + (size_t)q * a.pack_bytes, a.T, a.cap, a.w_cap).meta[1])
+    {
+      if (threadIdx.x == 0)
+        atomicOr(a.flags, 4);
+      return;
+    }
+  double s = 0.0;  // the exact running value, identical in every thread
+  for (int q = 0; q < a.n_ranks; q++)
+  {
+    if (threadIdx.x == 0)
+      a.bounds[q] = s;
+    const CdfPack p = cdf_pack_at(a.packs + (size_t)q * a.pack_bytes, a.T, a.cap, a.w_cap);
+    const int tiles = a.hdrs[q].n_tiles;
+    const long long n_q = a.hdrs[q].n;
+    const int n_slow = p.meta[0];
+    int t = 0, k = 0;
+    while (t < tiles)
+    {
+      const int next_slow = k < n_slow ? p.slow_tile[k] : tiles;
+      while (t < next_slow)
+      {
+        // a run of fast tiles: all in the binade of s
+        const int chunk = min(CDF_BLOCK, next_slow - t);
+        Fn mine;
+        mine.d0 = mine.d1 = 0;
+        int e_t = INT_MIN;
+        if ((int)threadIdx.x < chunk)
+        {
+          mine.d0 = p.d0[t + threadIdx.x];
+          mine.d1 = p.d1[t + threadIdx.x];
+          e_t = p.tile_e[t + threadIdx.x];
+        }
+        Fn agg;
+        const Fn ex = block_scan_fn(mine, sh.warp, &agg);
+        const bool normal = s >= 2.2250738585072014e-308 && isfinite(s);
+        const int e = normal ? exponent_of(s) : 0;
+        const long long m_in = normal ? mantissa_of(s) : 0;
+        if ((int)threadIdx.x < chunk && (!normal || e_t != e))
+          atomicOr(a.flags, 2);
+        if (q == a.me && (int)threadIdx.x < chunk)
+          a.starts[t + threadIdx.x] = from_units(m_in + fn_at(ex, m_in), e);
+        const long long m_out = m_in + fn_at(agg, m_in);
+        if (m_out >= TWO53 && threadIdx.x == 0)
+          atomicOr(a.flags, 2);
+        s = normal ? from_units(m_out, e) : s;
+        t += chunk;
+      }
+      if (t < tiles)
+      {
+        // the slow tile t: sequential-rounding loop over its raw weights
+        if (q == a.me && threadIdx.x == 0)
+          a.starts[t] = s;
+        const long long base = (long long)t * CDF_TILE;
+        const int tile_n = (int)min((long long)CDF_TILE, n_q - base);
+        const double* src = q == a.me ? a.w + base : p.slow_w + (size_t)k * CDF_TILE;
+        double wv[CDF_ITEMS];
+#pragma unroll
+        for (int j = 0; j < CDF_ITEMS; j++)
+        {
+          const int li = threadIdx.x * CDF_ITEMS + j;
+          wv[j] = li < tile_n ? src[li] : 0.0;
+        }
+        s = slow_tile_scan(s, wv, tile_n, nullptr, sh, a.flags);
+        t++;
+        k++;
+      }
+    }
+  }
+  if (threadIdx.x == 0)
+    a.bounds[a.n_ranks] = s;
+}
+
+__global__ void __launch_bounds__(CDF_BLOCK) k_cdf_apply(const double* __restrict__ w, int n, double* __restrict__ c,
+                                                         const int* __restrict__ tile_e, const double* __restrict__ starts,
+                                                         int* flags)
+{
+  __shared__ SlowShared sh;
+  const int t = blockIdx.x;
+  const int idx0 = t * CDF_TILE + threadIdx.x * CDF_ITEMS;
+  double wv[CDF_ITEMS];
+#pragma unroll
+  for (int k = 0; k < CDF_ITEMS; k++)
+    wv[k] = (idx0 + k < n) ? w[idx0 + k] : 0.0;
+  const double s_in = starts[t];
+  if (t == 0 && threadIdx.x == 0)
+    c[0] = s_in;
+  const int e_fast = tile_e[t];
+  if (e_fast == INT_MIN)
+  {
+    slow_tile_scan(s_in, wv, min(CDF_TILE, n - t * CDF_TILE), c + (size_t)t * CDF_TILE, sh, flags);
+    return;
+  }
+  // ---- fast tile: the whole tile stays in binade e_fast
+  Fn f[CDF_ITEMS];
+  Fn mine;
+  mine.d0 = mine.d1 = 0;
+#pragma unroll
+  for (int k = 0; k < CDF_ITEMS; k++)
+  {
+    f[k] = elem_fn(wv[k], e_fast);
+    mine = compose(mine, f[k]);
+  }
+  const Fn ex = block_scan_fn(mine, sh.warp, nullptr);
+  if (exponent_of(s_in) != e_fast && threadIdx.x == 0)
+    atomicOr(flags, 2);
+  const long long m_in = mantissa_of(s_in);
+  long long m = m_in + fn_at(ex, m_in);
+#pragma unroll
+  for (int k = 0; k < CDF_ITEMS; k++)
+  {
+    m += fn_at(f[k], m);
+    if (idx0 + k < n)
+      c[idx0 + k + 1] = from_units(m, e_fast);
+  }
+  if (threadIdx.x == CDF_BLOCK - 1 && m >= TWO53)
+    atomicOr(flags, 2);
 }
 
 // ---- systematic selection (particle_filter.cpp:309-351)
@@ -732,50 +869,71 @@ int build_target_segments(double start, double delta, long long n, std::vector<T
 
 namespace bamcl
 {
-// c[0..n] of the current set's window -> pf->cdf (device), exact sequential rounding, c[0] = c0
-int pf_build_cdf(bamcl_pf* pf, double c0)
+// c[0..n] of this rank's window of the current set -> pf->cdf (device), exact sequential rounding with the GLOBAL
+// values (c[0] = exact end of the previous rank's window); pf->cdf_bounds = the exact value at every rank boundary.
+// Collective on a distributed filter (two all-gathers); nothing synchronises.
+int pf_build_cdf(bamcl_pf* pf)
 {
   SampleSet& set = pf->sets[pf->current];
+  bamcl_comm* comm = pf->comm;
+  const int G = pf_ranks(pf), me = pf_rank(pf);
   const int n = pf_win_cnt(pf);
   const double* w = set.w.as<double>() + pf_win_off(pf);
   bamcl_ctx* ctx = pf->ctx;
   BAMCL_TRY(pf->cdf.reserve(sizeof(double) * ((size_t)n + 1)));
-  if (n == 0)
-  {
-    BAMCL_CUDA_OK(cudaMemcpyAsync(pf->cdf.p, &c0, sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
-    return BAMCL_OK;
-  }
   const int tiles = (n + CDF_TILE - 1) / CDF_TILE;
-  // scratch layout: sums[tiles] starts[tiles+1] incl[tiles] d0[tiles] d1[tiles] | tile_e[tiles] status[tiles] counter flags
-  const size_t n8 = (size_t)tiles * 5 + 2;
-  BAMCL_TRY(pf->scratch.reserve(sizeof(double) * n8 + sizeof(int) * ((size_t)tiles * 2 + 4)));
-  double* sums = pf->scratch.as<double>();
-  double* starts = sums + tiles;
-  double* incl = starts + tiles + 1;
-  long long* d0 = reinterpret_cast<long long*>(incl + tiles);
-  long long* d1 = d0 + tiles;
-  int* tile_e = reinterpret_cast<int*>(sums + n8);
-  int* status = tile_e + tiles;
-  int* counter = status + tiles;
+  // summary geometry: identical on every rank (windows differ by at most one sample)
+  const long max_win = G > 1 ? ((long)set.sample_count + G - 1) / G : (long)n;
+  const int T = std::max(1, (int)((max_win + CDF_TILE - 1) / CDF_TILE));
+  const int cap = G > 1 ? std::min(pf->cdf_slow_cap, T) : T;
+  const int w_cap = G > 1 ? cap : 0;
+  const size_t pack_bytes = cdf_pack_bytes(T, cap, w_cap);
+  // scratch: hdrs[G] | packs[G] | sums[T] starts[T+1] exact[T] bounds[G+1] | tile_slot[T]
+  const size_t off_packs = (size_t)G * sizeof(CdfHdr);
+  const size_t off_d = off_packs + (size_t)G * pack_bytes;
+  const size_t n_d = (size_t)T * 3 + 1 + (size_t)G + 1;
+  const size_t off_i = off_d + n_d * sizeof(double);
+  BAMCL_TRY(pf->scratch.reserve(off_i + sizeof(int) * (size_t)T + 64));
+  char* base = pf->scratch.as<char>();
+  CdfHdr* hdrs = reinterpret_cast<CdfHdr*>(base);
+  char* packs = base + off_packs;
+  double* sums = reinterpret_cast<double*>(base + off_d);
+  double* starts = sums + T;
+  double* exact = starts + T + 1;
+  double* bounds = exact + T;
+  int* tile_slot = reinterpret_cast<int*>(base + off_i);
   int* flags = pf_flags(pf);
-  BAMCL_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(int) * ((size_t)tiles + 2), ctx->stream));
+  const CdfPack mine = cdf_pack_at(packs + (size_t)me * pack_bytes, T, cap, w_cap);
+  pf->cdf_bounds = bounds;
   BAMCL_CUDA_OK(cudaMemsetAsync(flags, 0, sizeof(int), ctx->stream));
-  BAMCL_LAUNCH(ctx, k_cdf_tile_sums, tiles, CDF_BLOCK, 0, w, n, sums);
-  BAMCL_LAUNCH(ctx, k_cdf_classify, 1, 1024, 0, sums, tiles, n, starts, tile_e, c0);
-  CdfArgs a;
-  a.w = w;
-  a.c0 = c0;
-  a.n = n;
-  a.c = pf->cdf.as<double>();
-  a.tile_e = tile_e;
-  a.status = status;
-  a.d0 = d0;
-  a.d1 = d1;
-  a.incl = incl;
-  a.counter = counter;
-  a.flags = flags;
-  BAMCL_LAUNCH(ctx, k_cdf_tiles, tiles, CDF_BLOCK, 0, a);
+  if (tiles > 0)
+    BAMCL_LAUNCH(ctx, k_cdf_tile_sums, tiles, CDF_BLOCK, 0, w, n, sums);
+  BAMCL_LAUNCH(ctx, k_cdf_hdr, 1, 1024, 0, sums, tiles, (long long)n, hdrs + me);
+  if (G > 1)
+    BAMCL_TRY(comm_all_gather(comm, hdrs + me, hdrs, sizeof(CdfHdr)));
+  BAMCL_LAUNCH(ctx, k_cdf_classify, 1, 1024, 0, sums, tiles, hdrs, me, G, starts, mine, cap, tile_slot);
+  if (tiles > 0)
+    BAMCL_LAUNCH(ctx, k_cdf_tile_fns, tiles, CDF_BLOCK, 0, w, n, mine, w_cap, tile_slot);
+  if (G > 1)
+    BAMCL_TRY(comm_all_gather(comm, packs + (size_t)me * pack_bytes, packs, pack_bytes));
+  ResolveArgs ra;
+  ra.n_ranks = G;
+  ra.me = me;
+  ra.T = T;
+  ra.cap = cap;
+  ra.w_cap = w_cap;
+  ra.hdrs = hdrs;
+  ra.packs = packs;
+  ra.pack_bytes = pack_bytes;
+  ra.w = w;
+  ra.bounds = bounds;
+  ra.starts = exact;
+  ra.flags = flags;
+  BAMCL_LAUNCH(ctx, k_cdf_resolve, 1, CDF_BLOCK, 0, ra);
+  if (tiles > 0)
+    BAMCL_LAUNCH(ctx, k_cdf_apply, tiles, CDF_BLOCK, 0, w, n, pf->cdf.as<double>(), mine.tile_e, exact, flags);
+  else
+    BAMCL_CUDA_OK(cudaMemcpyAsync(pf->cdf.p, bounds + me, sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
   return BAMCL_OK;
 }
 }  // namespace bamcl
@@ -830,21 +988,48 @@ int bamcl_systematic_targets(double start, double delta, long n, double* out)
   return BAMCL_OK;
 }
 
+// pf_build_cdf + the host's view of it: bounds_out[0 .. n_ranks] (may be null). A rank whose window crosses more binades
+// than its summary holds makes EVERY rank see the overflow flag; all of them grow their summaries and repeat.
+static int build_cdf_checked(bamcl_pf* pf, double* bounds_out)
+{
+  const int G = pf_ranks(pf);
+  std::vector<double> tmp((size_t)G + 1, 0.0);
+  for (int attempt = 0;; attempt++)
+  {
+    BAMCL_TRY(pf_build_cdf(pf));
+    int flags = 0;
+    BAMCL_CUDA_OK(cudaMemcpyAsync(tmp.data(), pf->cdf_bounds, sizeof(double) * (size_t)(G + 1), cudaMemcpyDeviceToHost,
+                                  pf->ctx->stream));
+    BAMCL_CUDA_OK(cudaMemcpyAsync(&flags, pf_flags(pf), sizeof(int), cudaMemcpyDeviceToHost, pf->ctx->stream));
+    BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+    if (flags & 4)
+    {
+      if (attempt >= 8)
+        return set_error(BAMCL_E_UNSUPPORTED, "CDF: the ranks' tile summaries keep overflowing");
+      pf->cdf_slow_cap *= 8;
+      continue;
+    }
+    if (flags & 2)
+      return set_error(BAMCL_E_UNSUPPORTED, "CDF: a running sum left the supported range (subnormal or non-finite weights)");
+    break;
+  }
+  if (bounds_out)
+    memcpy(bounds_out, tmp.data(), sizeof(double) * (size_t)(G + 1));
+  return BAMCL_OK;
+}
+
 int bamcl_pf_cdf(bamcl_pf* pf, double* c_out, long n_plus_1)
 {
   if (!pf || !c_out)
     return set_error(BAMCL_E_ARG, "bamcl_pf_cdf: bad arguments");
-  const int n = pf->sets[pf->current].sample_count;
-  if (n_plus_1 != (long)n + 1)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_cdf: need sample_count + 1 = %d entries", n + 1);
-  BAMCL_TRY(pf_build_cdf(pf));
-  int flags = 0;
+  long off = 0, n = 0;
+  pf_owned(pf, &off, &n);
+  if (n_plus_1 != n + 1)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_cdf: need sample_count + 1 = %ld entries (a distributed filter: its window)", n + 1);
+  pf_apply_shard_window(pf);
+  BAMCL_TRY(build_cdf_checked(pf, nullptr));
   BAMCL_CUDA_OK(cudaMemcpyAsync(c_out, pf->cdf.p, sizeof(double) * (size_t)n_plus_1, cudaMemcpyDeviceToHost, pf->ctx->stream));
-  if (n > 0)
-    BAMCL_CUDA_OK(cudaMemcpyAsync(&flags, pf_flags(pf), sizeof(int), cudaMemcpyDeviceToHost, pf->ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
-  if (flags & 2)
-    return set_error(BAMCL_E_UNSUPPORTED, "CDF: a running sum left the supported range (subnormal or non-finite weights)");
   return BAMCL_OK;
 }
 
@@ -874,8 +1059,10 @@ static int resample_impl(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
   if (!(prm->w_diff >= 0.0))  // NaN when no sensor update preceded the resample
     return set_error(BAMCL_E_STATE, "bamcl_pf_resample: w_diff is NaN/negative (updateSensor must succeed first)");
   memset(res, 0, sizeof(*res));
+  if (pf_ranks(pf) > 1)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_resample: this filter is one shard of a distributed set; use bamcl_pf_shard_resample");
   if (pf->win_cnt >= 0)
-    return set_error(BAMCL_E_STATE, "bamcl_pf_resample: a shard window is set; use the bamcl_pf_shard_* phases");
+    return set_error(BAMCL_E_STATE, "bamcl_pf_resample: a scoring window is set (bamcl_pf_set_window); clear it first");
   if (!prm->resample_systematic)
   {
     BAMCL_TRY(resample_multinomial(pf, prm, res));
@@ -959,18 +1146,15 @@ static int resample_impl(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
   // :343-346 total += 1.0 per sample, then :457-462 weight /= total
   a.weight = 1.0 / (double)new_count;
   a.flags = pf_flags(pf);
+  if (aos_out && new_count > aos_cap)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_resample_host: %d samples do not fit the output buffer", new_count);
   if (new_count > 0)
     BAMCL_LAUNCH(ctx, k_select, (new_count + 255) / 256, 256, 0, a);
   set_b.sample_count = new_count;
   pf->current = 1 - pf->current;
-  if (aos_out)
-  {
-    // the new set is final once k_select has run: its copy to the host overlaps the pose-bin tree and the clustering
-    if (new_count > aos_cap)
-      return set_error(BAMCL_E_ARG, "bamcl_pf_resample_host: %d samples do not fit the output buffer", new_count);
-    if (new_count > 0)
-      BAMCL_TRY(pf_download_async(pf, aos_out, new_count));
-  }
+  // the new set is final once k_select has run: its copy to the host overlaps the pose-bin tree and the clustering
+  if (aos_out && new_count > 0)
+    BAMCL_TRY(pf_download_async(pf, aos_out, new_count));
   // the pinned segment buffer is reused by later calls
   BAMCL_TRY(build_tree_and_stats(pf, pf->current, prm->dist_threshold, prm->convergence_threshold, res));
   if (aos_out && new_count > 0)
@@ -1001,9 +1185,15 @@ int bamcl_pf_init_stats(bamcl_pf* pf, bamcl_resample_result* res)
 
 int bamcl_pf_resample_sources(bamcl_pf* pf, int* src, long n)
 {
-  if (!pf || !src || n != pf->sets[pf->current].sample_count || pf->src.cap < sizeof(int) * (size_t)n)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_resample_sources: n must equal sample_count after a resample");
-  BAMCL_CUDA_OK(cudaMemcpyAsync(src, pf->src.p, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, pf->ctx->stream));
+  long off = 0, cnt = 0;
+  if (pf)
+    pf_owned(pf, &off, &cnt);
+  if (!pf || !src || n != cnt || pf->src.cap < sizeof(int) * (size_t)(off + n))
+    return set_error(BAMCL_E_ARG, "bamcl_pf_resample_sources: n must equal sample_count after a resample (a distributed "
+                                  "filter: its window)");
+  if (n == 0)
+    return BAMCL_OK;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(src, pf->src.as<int>() + off, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, pf->ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
   return BAMCL_OK;
 }
@@ -1011,11 +1201,9 @@ int bamcl_pf_resample_sources(bamcl_pf* pf, int* src, long n)
 }  // extern "C"
 
 // =============================================================================================
-// Sharded filter: the phases of resampleSystematic split at the points where ranks exchange data.
-// Global order is rank-major, so every order-dependent reference semantic (sequential CDF, target sequence,
-// first-occurrence order of pose bins) is the single-set one. Rank r owns the window [off, off + cnt) of the
-// current set; c_local[0] = exact end value of rank r-1's CDF, so the concatenation of the local CDFs IS the
-// reference's c[0..P].
+// Distributed filter: updateResample over ONE global set whose samples are owned rank-major by G ranks.
+// Global order is rank-major, so every order-dependent reference semantic (sequential CDF, target sequence, first
+// occurrence of pose bins) is the single-set one.
 // =============================================================================================
 namespace
 {
@@ -1025,9 +1213,9 @@ struct ShardSelArgs
   int P;            // window size
   long off;         // window offset = global index of local particle 0
   const double *ax, *ay, *ath;  // window base
-  double* out3;     // global AoS buffer, row = output slot, 3 doubles (x, y, theta)
-  int* src_out;     // optional: global source index per output slot
-  long k_begin, k_end, row0;  // outputs [k_begin, k_end) of the systematic sequence; row = row0 + k
+  double *ox, *oy, *oth;        // staging rows (SoA)
+  int* osrc;                    // global source index per row
+  long k_begin, k_end, row0;    // outputs [k_begin, k_end) of the systematic sequence; row = row0 + k
   const TargetSeg* segs;
   int n_segs;
   int* flags;
@@ -1080,23 +1268,62 @@ __global__ void __launch_bounds__(256) k_select_shard(const ShardSelArgs a)
     j = min(l2, a.P - 1);
   }
   const long long row = a.row0 + k;
-  a.out3[3 * row] = a.ax[j];
-  a.out3[3 * row + 1] = a.ay[j];
-  a.out3[3 * row + 2] = a.ath[j];
-  if (a.src_out)
-    a.src_out[row] = (int)(a.off + j);
+  a.ox[row] = a.ax[j];
+  a.oy[row] = a.ay[j];
+  a.oth[row] = a.ath[j];
+  a.osrc[row] = (int)(a.off + j);
 }
 
-__global__ void k_aos3_to_soa(const double* __restrict__ in3, double* __restrict__ x, double* __restrict__ y,
-                              double* __restrict__ th, double* __restrict__ w, double weight, int n)
+__global__ void k_fill_range(double* __restrict__ p, double v, long n)
 {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    p[i] = v;
+}
+__global__ void k_fill_range_i(int* __restrict__ p, int v, long n)
+{
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    p[i] = v;
+}
+// rows [r0, r0 + n) of packed (x, y, theta) triples -> SoA at the same global rows
+__global__ void k_rows3_to_soa(const double* __restrict__ in3, long r0, long n, double* __restrict__ x, double* __restrict__ y,
+                               double* __restrict__ th)
+{
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n)
     return;
-  x[i] = in3[3 * (size_t)i];
-  y[i] = in3[3 * (size_t)i + 1];
-  th[i] = in3[3 * (size_t)i + 2];
-  w[i] = weight;
+  x[r0 + i] = in3[3 * (r0 + i)];
+  y[r0 + i] = in3[3 * (r0 + i) + 1];
+  th[r0 + i] = in3[3 * (r0 + i) + 2];
+}
+
+struct Move
+{
+  long src, dst, kb, ke, pos;
+};
+
+// the transfers of the pose exchange, in the order both sides issue them (see bamcl_shard_exchange_plan)
+int exchange_plan(const long* runs, int n_runs, long n_random, long n, int G, std::vector<Move>& out)
+{
+  out.clear();
+  const long total = n_random + n;
+  std::vector<long> pos(G, 0);
+  for (int i = 0; i < n_runs; i++)
+  {
+    const long kb = runs[3 * i], ke = runs[3 * i + 1], s = runs[3 * i + 2];
+    if (s < 0 || s >= G || kb > ke)
+      return -1;
+    for (int d = 0; d < G; d++)
+    {
+      const long ob = shard_begin(total, G, d), oe = shard_begin(total, G, d + 1);
+      const long a = std::max(kb, ob - n_random), b = std::min(ke, oe - n_random);
+      if (a < b)
+        out.push_back(Move{s, (long)d, a, b, pos[s] + (a - kb)});
+    }
+    pos[s] += ke - kb;
+  }
+  return 0;
 }
 }  // namespace
 
@@ -1106,6 +1333,8 @@ int bamcl_pf_set_window(bamcl_pf* pf, long offset, long count)
 {
   if (!pf)
     return set_error(BAMCL_E_ARG, "bamcl_pf_set_window: null pf");
+  if (pf_ranks(pf) > 1)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_set_window: a distributed filter manages its window itself");
   const int n = pf->sets[pf->current].sample_count;
   if (count < 0)
   {
@@ -1117,24 +1346,6 @@ int bamcl_pf_set_window(bamcl_pf* pf, long offset, long count)
     return set_error(BAMCL_E_ARG, "bamcl_pf_set_window: [%ld, %ld) is outside the set of %d samples", offset, offset + count, n);
   pf->win_off = offset;
   pf->win_cnt = (int)count;
-  return BAMCL_OK;
-}
-
-int bamcl_pf_shard_cdf(bamcl_pf* pf, double c0, double* end_out)
-{
-  if (!pf || !end_out)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_cdf: bad arguments");
-  if (!(c0 >= 0.0))
-    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_cdf: c0 must be >= 0");
-  BAMCL_TRY(pf_build_cdf(pf, c0));
-  const int n = pf_win_cnt(pf);
-  int flags = 0;
-  BAMCL_CUDA_OK(cudaMemcpyAsync(end_out, pf->cdf.as<double>() + n, sizeof(double), cudaMemcpyDeviceToHost, pf->ctx->stream));
-  if (n > 0)
-    BAMCL_CUDA_OK(cudaMemcpyAsync(&flags, pf_flags(pf), sizeof(int), cudaMemcpyDeviceToHost, pf->ctx->stream));
-  BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
-  if (flags & 2)
-    return set_error(BAMCL_E_UNSUPPORTED, "CDF: a running sum left the supported range (subnormal or non-finite weights)");
   return BAMCL_OK;
 }
 
@@ -1200,67 +1411,269 @@ int bamcl_systematic_plan(double start, double delta, long n, const double* boun
   return BAMCL_OK;
 }
 
-int bamcl_pf_shard_select(bamcl_pf* pf, double start, double delta, long n_sys, long row0, long k_begin, long k_end,
-                          double* out_aos3_dev, int* src_out_dev_or_null)
+int bamcl_shard_exchange_plan(const long* runs, int n_runs, long n_random, long n, int n_ranks, long* moves, int max_moves,
+                              int* n_moves)
 {
-  if (!pf || !out_aos3_dev || k_begin < 0 || k_end > n_sys || k_begin > k_end)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_select: bad arguments");
-  if (k_begin == k_end)
-    return BAMCL_OK;
-  const int P = pf_win_cnt(pf);
-  if (P <= 0)
-    return set_error(BAMCL_E_STATE, "bamcl_pf_shard_select: this rank's window is empty but it was given outputs");
-  bamcl_ctx* ctx = pf->ctx;
-  SampleSet& set_a = pf->sets[pf->current];
-  std::vector<TargetSeg> segs;
-  if (build_target_segments(start, delta, n_sys, segs) != 0)
-    return set_error(BAMCL_E_UNSUPPORTED, "target sequence needs more than %d binade segments", MAX_SEGS);
-  BAMCL_TRY(pf->h_stage.reserve(sizeof(TargetSeg) * MAX_SEGS));
-  BAMCL_TRY(pf->seg_buf.reserve(sizeof(TargetSeg) * MAX_SEGS));
-  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));  // the pinned segment buffer may still feed an earlier copy
-  memcpy(pf->h_stage.p, segs.data(), sizeof(TargetSeg) * segs.size());
-  BAMCL_CUDA_OK(cudaMemcpyAsync(pf->seg_buf.p, pf->h_stage.p, sizeof(TargetSeg) * segs.size(), cudaMemcpyHostToDevice,
-                                ctx->stream));
-  ShardSelArgs a;
-  a.c = pf->cdf.as<double>();
-  a.P = P;
-  a.off = pf_win_off(pf);
-  a.ax = set_a.x.as<double>() + a.off;
-  a.ay = set_a.y.as<double>() + a.off;
-  a.ath = set_a.th.as<double>() + a.off;
-  a.out3 = out_aos3_dev;
-  a.src_out = src_out_dev_or_null;
-  a.k_begin = k_begin;
-  a.k_end = k_end;
-  a.row0 = row0;
-  a.segs = pf->seg_buf.as<TargetSeg>();
-  a.n_segs = (int)segs.size();
-  a.flags = pf_flags(pf);
-  const long long cnt = k_end - k_begin;
-  BAMCL_LAUNCH(ctx, k_select_shard, (unsigned)((cnt + 255) / 256), 256, 0, a);
+  if (!runs || !moves || !n_moves || n_runs < 0 || n_ranks < 1 || n_random < 0 || n < 0)
+    return set_error(BAMCL_E_ARG, "bamcl_shard_exchange_plan: bad arguments");
+  std::vector<Move> mv;
+  if (exchange_plan(runs, n_runs, n_random, n, n_ranks, mv) != 0)
+    return set_error(BAMCL_E_ARG, "bamcl_shard_exchange_plan: malformed runs");
+  if ((int)mv.size() > max_moves)
+    return set_error(BAMCL_E_ARG, "bamcl_shard_exchange_plan: %zu transfers do not fit %d", mv.size(), max_moves);
+  for (size_t i = 0; i < mv.size(); i++)
+  {
+    moves[5 * i] = mv[i].src;
+    moves[5 * i + 1] = mv[i].dst;
+    moves[5 * i + 2] = mv[i].kb;
+    moves[5 * i + 3] = mv[i].ke;
+    moves[5 * i + 4] = mv[i].pos;
+  }
+  *n_moves = (int)mv.size();
   return BAMCL_OK;
 }
 
-int bamcl_pf_shard_install(bamcl_pf* pf, const double* aos3_dev, long n, const bamcl_resample_params* prm,
-                           bamcl_resample_result* res)
+int bamcl_pf_shard_attach(bamcl_pf* pf, bamcl_comm* comm)
 {
-  if (!pf || !aos3_dev || !prm || !res || n <= 0 || n > pf->max_samples)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_install: bad arguments");
+  if (!pf)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_attach: null pf");
+  if (comm && comm->ctx != pf->ctx)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_attach: the communicator belongs to another context");
+  pf->comm = comm;
+  pf->win_off = 0;
+  pf->win_cnt = -1;
+  pf->box_valid = false;
+  if (const char* cap = getenv("BAMCL_CDF_SLOW_CAP"))  // tests: start with tiny summaries to exercise the regrow path
+    pf->cdf_slow_cap = std::max(1, atoi(cap));
+  pf_apply_shard_window(pf);
+  return BAMCL_OK;
+}
+
+int bamcl_pf_shard_window(bamcl_pf* pf, long* window_offset, long* window_count)
+{
+  if (!pf)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_window: null pf");
+  if (window_offset)
+    *window_offset = pf_win_off(pf);
+  if (window_count)
+    *window_count = pf_win_cnt(pf);
+  return BAMCL_OK;
+}
+
+int bamcl_pf_shard_set_count(bamcl_pf* pf, long n_global, long* window_offset, long* window_count)
+{
+  if (!pf || n_global < 0 || n_global > pf->max_samples)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_set_count: need 0 <= n_global <= max_samples");
+  pf->sets[pf->current].sample_count = (int)n_global;
+  pf->win_off = 0;
+  pf->win_cnt = -1;
+  pf_apply_shard_window(pf);
+  return bamcl_pf_shard_window(pf, window_offset, window_count);
+}
+
+int bamcl_pf_shard_init_stats(bamcl_pf* pf, bamcl_resample_result* res)
+{
+  if (!pf || !res)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_init_stats: bad arguments");
+  memset(res, 0, sizeof(*res));
+  pf_apply_shard_window(pf);
+  BAMCL_TRY(build_tree_and_stats(pf, pf->current, 0.5, 1e300, res));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+  res->sample_count = pf->sets[pf->current].sample_count;
+  res->converged = 0;  // initConverged, particle_filter.cpp:163-167
+  return BAMCL_OK;
+}
+
+int bamcl_pf_shard_bounds(bamcl_pf* pf, double* bounds, int n_plus_1)
+{
+  if (!pf || !bounds || n_plus_1 != pf_ranks(pf) + 1 || !pf->cdf_bounds)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_bounds: need n_ranks + 1 entries after a resample");
+  BAMCL_CUDA_OK(cudaMemcpyAsync(bounds, pf->cdf_bounds, sizeof(double) * (size_t)n_plus_1, cudaMemcpyDeviceToHost, pf->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(pf->ctx->stream));
+  return BAMCL_OK;
+}
+
+int bamcl_pf_shard_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res)
+{
+  if (!pf || !prm || !res)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_resample: bad arguments");
+  if (prm->max_samples > pf->max_samples || prm->max_samples <= 0)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_resample: max_samples exceeds the filter's capacity");
+  if (!(prm->w_diff >= 0.0))
+    return set_error(BAMCL_E_STATE, "bamcl_pf_shard_resample: w_diff is NaN/negative (updateSensor must succeed first)");
+  if (!prm->resample_systematic)
+    return set_error(BAMCL_E_UNSUPPORTED, "bamcl_pf_shard_resample: the distributed filter resamples systematically "
+                                          "(multinomial stops on a running leaf count, pf_kdtree state per output)");
   memset(res, 0, sizeof(*res));
   bamcl_ctx* ctx = pf->ctx;
+  bamcl_comm* comm = pf->comm;
+  const int G = pf_ranks(pf), me = pf_rank(pf);
+  SampleSet& set_a = pf->sets[pf->current];
   SampleSet& set_b = pf->sets[1 - pf->current];
-  BAMCL_LAUNCH(ctx, k_aos3_to_soa, (unsigned)((n + 255) / 256), 256, 0, aos3_dev, set_b.x.as<double>(), set_b.y.as<double>(),
-               set_b.th.as<double>(), set_b.w.as<double>(), 1.0 / (double)n, (int)n);
-  set_b.sample_count = (int)n;
+  if (set_a.sample_count <= 0)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_shard_resample: the current set is empty");
+  pf_apply_shard_window(pf);
+
+  // particle_filter.cpp:291-306 (host arithmetic, identical on every rank)
+  int new_count = resample_limit(set_a.leaf_count, prm->min_samples, prm->max_samples, prm->pop_err, prm->pop_z);
+  const double w_diff = prm->w_diff;
+  if (w_diff > 0.0)
+  {
+    new_count *= (1.0 + w_diff);
+    if (new_count > prm->max_samples)
+      new_count = prm->max_samples;
+  }
+  const int n_rand = w_diff * new_count;
+  const int n_sys = new_count - n_rand;
+  const bool device_poses = n_rand > 0 && !prm->random_poses && pf->rp_map && pf->rp_map->free_count > 0;
+  if (n_rand > 0 && !device_poses && (!prm->random_poses || prm->n_random_poses < n_rand))
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_resample: %d random poses needed, %ld supplied", n_rand, prm->n_random_poses);
+  // :309-310
+  const uint64_t state = drand48_next(prm->drand48_state);
+  const double start = std::ldexp((double)state, -48);
+  const double delta = 1.0 / n_sys;
+  std::vector<TargetSeg> segs;
+  if (n_sys > 0 && build_target_segments(start, delta, n_sys, segs) != 0)
+    return set_error(BAMCL_E_UNSUPPORTED, "target sequence needs more than %d binade segments", MAX_SEGS);
+
+  // ---- exact CDF of every window and the value at every rank boundary (:280-285)
+  std::vector<double> bounds(G + 1, 0.0);
+  BAMCL_TRY(build_cdf_checked(pf, bounds.data()));
+
+  // ---- who sources which output slot, and who owns it (host arithmetic, identical on every rank)
+  std::vector<long> runs((size_t)3 * (4 * G + 2 * MAX_SEGS + 16));
+  int n_runs = 0;
+  if (n_sys > 0)
+    BAMCL_TRY(bamcl_systematic_plan(start, delta, n_sys, bounds.data(), G, runs.data(), (int)(runs.size() / 3), &n_runs));
+  std::vector<Move> moves;
+  if (exchange_plan(runs.data(), n_runs, n_rand, n_sys, G, moves) != 0)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_shard_resample: malformed plan");
+  long my_rows = 0;
+  for (int i = 0; i < n_runs; i++)
+    if (runs[3 * i + 2] == me)
+      my_rows += runs[3 * i + 1] - runs[3 * i];
+  const int P = pf_win_cnt(pf);
+  if (my_rows > 0 && P <= 0)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_shard_resample: this rank's window is empty but it was given outputs");
+
+  // ---- select this rank's runs into staging rows (k order)
+  BAMCL_TRY(pf->src.reserve(sizeof(int) * (size_t)pf->max_samples));
+  const size_t rows_cap = (size_t)std::max<long>(my_rows, 1);
+  BAMCL_TRY(pf->stage_x.reserve(sizeof(double) * rows_cap));
+  BAMCL_TRY(pf->stage_y.reserve(sizeof(double) * rows_cap));
+  BAMCL_TRY(pf->stage_th.reserve(sizeof(double) * rows_cap));
+  BAMCL_TRY(pf->stage_src.reserve(sizeof(int) * rows_cap));
+  BAMCL_TRY(pf->h_stage.reserve(sizeof(TargetSeg) * MAX_SEGS));
+  BAMCL_TRY(pf->seg_buf.reserve(sizeof(TargetSeg) * MAX_SEGS));
+  if (!segs.empty())
+  {
+    memcpy(pf->h_stage.p, segs.data(), sizeof(TargetSeg) * segs.size());
+    BAMCL_CUDA_OK(cudaMemcpyAsync(pf->seg_buf.p, pf->h_stage.p, sizeof(TargetSeg) * segs.size(), cudaMemcpyHostToDevice,
+                                  ctx->stream));
+  }
+  {
+    long pos = 0;
+    for (int i = 0; i < n_runs; i++)
+    {
+      if (runs[3 * i + 2] != me)
+        continue;
+      const long kb = runs[3 * i], ke = runs[3 * i + 1];
+      if (ke == kb)
+        continue;
+      ShardSelArgs a;
+      a.c = pf->cdf.as<double>();
+      a.P = P;
+      a.off = pf_win_off(pf);
+      a.ax = set_a.x.as<double>() + a.off;
+      a.ay = set_a.y.as<double>() + a.off;
+      a.ath = set_a.th.as<double>() + a.off;
+      a.ox = pf->stage_x.as<double>();
+      a.oy = pf->stage_y.as<double>();
+      a.oth = pf->stage_th.as<double>();
+      a.osrc = pf->stage_src.as<int>();
+      a.k_begin = kb;
+      a.k_end = ke;
+      a.row0 = pos - kb;
+      a.segs = pf->seg_buf.as<TargetSeg>();
+      a.n_segs = (int)segs.size();
+      a.flags = pf_flags(pf);
+      BAMCL_LAUNCH(ctx, k_select_shard, (unsigned)((ke - kb + 255) / 256), 256, 0, a);
+      pos += ke - kb;
+    }
+  }
+
+  // ---- the exchange: selected rows -> owners of the output slots (:326-351 writes set_b in slot order)
+  double* bx = set_b.x.as<double>();
+  double* by = set_b.y.as<double>();
+  double* bth = set_b.th.as<double>();
+  int* bsrc = pf->src.as<int>();
+  std::vector<P2P> sends, recvs;
+  for (const Move& m : moves)
+  {
+    const long cnt = m.ke - m.kb, o = n_rand + m.kb;
+    if (m.src == me && m.dst == me)
+    {
+      BAMCL_CUDA_OK(cudaMemcpyAsync(bx + o, pf->stage_x.as<double>() + m.pos, sizeof(double) * cnt, cudaMemcpyDeviceToDevice, ctx->stream));
+      BAMCL_CUDA_OK(cudaMemcpyAsync(by + o, pf->stage_y.as<double>() + m.pos, sizeof(double) * cnt, cudaMemcpyDeviceToDevice, ctx->stream));
+      BAMCL_CUDA_OK(cudaMemcpyAsync(bth + o, pf->stage_th.as<double>() + m.pos, sizeof(double) * cnt, cudaMemcpyDeviceToDevice, ctx->stream));
+      BAMCL_CUDA_OK(cudaMemcpyAsync(bsrc + o, pf->stage_src.as<int>() + m.pos, sizeof(int) * cnt, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    else if (m.src == me)
+    {
+      sends.push_back(P2P{(int)m.dst, pf->stage_x.as<double>() + m.pos, sizeof(double) * (size_t)cnt});
+      sends.push_back(P2P{(int)m.dst, pf->stage_y.as<double>() + m.pos, sizeof(double) * (size_t)cnt});
+      sends.push_back(P2P{(int)m.dst, pf->stage_th.as<double>() + m.pos, sizeof(double) * (size_t)cnt});
+      sends.push_back(P2P{(int)m.dst, pf->stage_src.as<int>() + m.pos, sizeof(int) * (size_t)cnt});
+    }
+    else if (m.dst == me)
+    {
+      recvs.push_back(P2P{(int)m.src, bx + o, sizeof(double) * (size_t)cnt});
+      recvs.push_back(P2P{(int)m.src, by + o, sizeof(double) * (size_t)cnt});
+      recvs.push_back(P2P{(int)m.src, bth + o, sizeof(double) * (size_t)cnt});
+      recvs.push_back(P2P{(int)m.src, bsrc + o, sizeof(int) * (size_t)cnt});
+    }
+  }
+  if (G > 1)
+    BAMCL_TRY(comm_exchange(comm, sends.data(), (int)sends.size(), recvs.data(), (int)recvs.size()));
+
+  // ---- this rank's output window: weights 1/n (:343-346, 457-462) and the random poses among its slots (:316-324)
+  const long ob = shard_begin(new_count, G, me), oe = shard_begin(new_count, G, me + 1);
+  if (oe > ob)
+    BAMCL_LAUNCH(ctx, k_fill_range, (unsigned)((oe - ob + 255) / 256), 256, 0, set_b.w.as<double>() + ob, 1.0 / (double)new_count,
+                 oe - ob);
+  unsigned long long state_after = state;
+  if (n_rand > 0)
+  {
+    // every rank holds all n_rand poses (host-supplied, or generated from the same stream state) and keeps its own rows
+    BAMCL_TRY(pf->random_poses.reserve(sizeof(double) * 3 * (size_t)n_rand));
+    if (device_poses)
+      BAMCL_TRY(device_random_poses(pf, state, n_rand, pf->random_poses.as<double>(), &state_after));
+    else
+      BAMCL_CUDA_OK(cudaMemcpyAsync(pf->random_poses.p, prm->random_poses, sizeof(double) * 3 * (size_t)n_rand,
+                                    cudaMemcpyHostToDevice, ctx->stream));
+    const long r0 = ob, r1 = std::min<long>(oe, n_rand);
+    if (r1 > r0)
+    {
+      BAMCL_LAUNCH(ctx, k_rows3_to_soa, (unsigned)((r1 - r0 + 255) / 256), 256, 0, pf->random_poses.as<double>(), r0, r1 - r0, bx,
+                   by, bth);
+      BAMCL_LAUNCH(ctx, k_fill_range_i, (unsigned)((r1 - r0 + 255) / 256), 256, 0, bsrc + r0, -1, r1 - r0);
+    }
+  }
+  set_b.sample_count = new_count;
   pf->current = 1 - pf->current;
   pf->win_off = 0;
   pf->win_cnt = -1;
+  pf_apply_shard_window(pf);
   BAMCL_TRY(build_tree_and_stats(pf, pf->current, prm->dist_threshold, prm->convergence_threshold, res));
   int flags = 0;
   BAMCL_CUDA_OK(cudaMemcpyAsync(&flags, pf_flags(pf), sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
-  res->sample_count = (int)n;
+  // (bit0 -- a target at/after the end of the CDF, SURVEY Q10 -- is raised on the rank that selected it and was summed
+  // over the ranks with the tree's integer results)
+  res->sample_count = new_count;
+  res->random_poses_used = n_rand;
   res->status_flags = flags & 1;
+  res->drand48_state = state_after;
   return BAMCL_OK;
 }
 

@@ -403,6 +403,11 @@ int launch_score_cloud(bamcl_pf* pf, bamcl_map3d* map)
 }
 }  // namespace bamcl
 
+namespace bamcl
+{
+int pf_shard_finish_update(bamcl_pf* pf, double* total_out);  // pf.cu
+}
+
 extern "C" {
 
 int bamcl_pf_stage_cloud(bamcl_pf* pf, bamcl_map3d* map, const bamcl_cloud_model* model, const float* points_xyz,
@@ -443,6 +448,24 @@ int bamcl_pf_update_cloud_staged(bamcl_pf* pf, bamcl_map3d* map, double* total_o
   if (total_out_or_null)
     return pf_read_scalar(pf, 0, total_out_or_null);
   return BAMCL_OK;
+}
+
+int bamcl_pf_shard_update_cloud_staged(bamcl_pf* pf, bamcl_map3d* map, double* total_out)
+{
+  if (!pf || !map)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_shard_update_cloud_staged: bad arguments");
+  if (!pf->comm)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_shard_update_cloud_staged: no communicator attached");
+  pf_apply_shard_window(pf);
+  if (pf->cloud.valid && pf->cloud.model.max_beams < 2)  // updateSensor returns false (:95)
+  {
+    if (total_out)
+      *total_out = 0.0;
+    return BAMCL_OK;
+  }
+  BAMCL_TRY(launch_score_cloud(pf, map));
+  BAMCL_TRY(pf_reduce_total(pf, pf->scalars.as<double>()));
+  return pf_shard_finish_update(pf, total_out);
 }
 
 int bamcl_pf_update_cloud(bamcl_pf* pf, bamcl_map3d* map, const bamcl_cloud_model* model, const float* points_xyz,

@@ -108,6 +108,7 @@ struct FastArgs
   int* bslot;                      // [K] bucket of every key >= m
   int* bpos;                       // [K] arrival position inside the bucket
   int* bids;                       // [K] keys grouped by bucket
+  int part_rank, part_n;           // distributed filter: this rank grows the subtrees of buckets b with (b >> 1) % part_n == part_rank
 };
 
 // ---- 1. top tree (one CTA)
@@ -277,7 +278,7 @@ __global__ void __launch_bounds__(THREADS) k_fast_bucket(const FastArgs a)
   const int K = a.out->K;
   const int m = min(K, M_TOP);
   const int b = blockIdx.x, u = b >> 1, sd = b & 1;
-  if (u >= m)
+  if (u >= m || u % a.part_n != a.part_rank)
     return;
   const bool unset = a.tpivot[u] < 0;
   if (unset ? sd == 1 : a.tchild[b] != NONE)

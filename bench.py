@@ -241,19 +241,25 @@ def run_b200_arm(a):
     aos[:, 3] = 1.0 / PT
     out_aos = cabi.pinned_array((PT, 4))
     pf.srand48(12345)
-    sf = None
+    sf = comm = None
     if world > 1:
         from badger_amcl_b200 import sharded
-        sf = sharded.ShardedFilter(sharded.CudaEngine(pf, m, local_rank), rank, world, dist, PT // 10, PT)
-        sf.srand48(12345)
+        comm = sharded.Comm.nccl(ctx, rank, world, dist)  # the library's own NCCL communicator (data path)
+        sf = sharded.ShardedFilter(pf, comm, m)
     off0, cnt0 = (PT * rank) // world, (PT * (rank + 1)) // world - (PT * rank) // world
 
     def restore():
-        pf.upload_samples(aos)
-        pf.init_with_current()  # kd-tree of the set being resampled (particle_filter.cpp:292 reads its leaf count)
-        pf.w_slow = pf.w_fast = 0.0
-        if sf is not None:
-            sf.w_slow = sf.w_fast = 0.0
+        # every step resamples the SAME set with the SAME draw, so runs with different --steps / --gpus are comparable
+        if sf is None:
+            pf.upload_samples(aos)
+            pf.init_with_current()  # kd-tree of the set being resampled (particle_filter.cpp:292 reads its leaf count)
+            pf.w_slow = pf.w_fast = 0.0
+            pf.srand48(12345)
+        else:
+            cabi._check(pf.L.bamcl_pf_shard_set_count(pf.h, PT, None, None))
+            sf.upload_window(aos[off0:off0 + cnt0])  # each rank holds only the window it owns
+            sf.init_stats()
+            sf.srand48(12345)
 
     def barrier():
         ctx.sync()
@@ -296,17 +302,38 @@ def run_b200_arm(a):
         else:
             # every rank moves ITS window: upload P x 32 B, stage the scan, sharded update + resample, download its
             # share of the new set
-            cabi._check(pf.L.bamcl_pf_upload_window_samples(pf.h, cabi._p(aos[off0:off0 + cnt0]), off0, cnt0))
+            sf.upload_window(aos[off0:off0 + cnt0])
             pf.stage_scan(m, model, ranges, angles, RANGE_MAX)
             sf.update_sensor()
             r = sf.update_resample()
             n = r.sample_count
             o, c = sf.window()
-            cabi._check(pf.L.bamcl_pf_download_window_samples(pf.h, cabi._p(out_aos[o:o + c]), o, c))
+            sf.download_window(out_aos[o:o + c])
             moved = c
         ms = ctx.timer_stop_ms()
         wall = (time.perf_counter() - t0) * 1e3
         return max(ms, wall), moved
+
+    def result_hash(r):
+        """64-bit digest of (resample indices, KLD leaf count, sample count) of the last resample, independent of how
+        the set is split over ranks: sum over output slots of mix(slot, source) mod 2^64 (+ the two counts)"""
+        if sf is None:
+            o, src = 0, pf.resample_sources().astype(np.uint64)
+        else:
+            o, c = sf.window()
+            src = sf.window_sources().astype(np.uint64)
+        with np.errstate(over="ignore"):
+            z = (np.arange(o, o + len(src), dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15)) ^ (src + np.uint64(1))
+            z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+            z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+            h = int((z ^ (z >> np.uint64(31))).sum(dtype=np.uint64))
+        if dist is not None:
+            import torch
+            t = torch.tensor([h - (1 << 64) if h >= (1 << 63) else h], dtype=torch.int64, device="cuda")
+            dist.all_reduce(t)
+            h = int(t.item()) & ((1 << 64) - 1)
+        h = (h + 0x100000001B3 * int(r.leaf_count) + 0x1000193 * int(r.sample_count)) & ((1 << 64) - 1)
+        return "%016x" % h
 
     for _ in range(a.warmup):
         step_resident()
@@ -321,6 +348,7 @@ def run_b200_arm(a):
     rs = float(np.sum([r[1] for r in rows]))
     k_ms = float(np.mean([r[2] for r in rows]))
     last = rows[-1][3]
+    digest = result_hash(last)
     for _ in range(max(1, a.warmup // 2)):
         step_e2e()
     barrier()
@@ -348,6 +376,8 @@ def run_b200_arm(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms, e_total_ms, up, rs, k_ms = [float(v) for v in t.tolist()]
     if rank != 0:
+        if comm is not None:
+            comm.close()
         if dist is not None:
             dist.destroy_process_group()
         return 0
@@ -359,9 +389,10 @@ def run_b200_arm(a):
     algo_bytes = float(cnt0) * valid * 4 + float(cnt0) * 40 + B * 16   # one launch scores this rank's window
     achieved = algo_bytes / (k_ms * 1e-3) / 1e9
     par = ("single GPU" if world == 1 else
-           "ONE global set of %d particles, rank-major windows x%d; map+scan replicated; weight totals all-gathered, "
-           "exact CDF chained over ranks, systematic select by source rank, pose runs broadcast, pose-bin tree "
-           "replicated" % (PT, world))
+           "ONE global set of %d particles owned rank-major by %d ranks; map+scan replicated; NCCL inside the C library: "
+           "weight totals all-gathered, CDF tile summaries all-gathered (exact rank offsets, no chain), selected poses to "
+           "slot owners by grouped send/recv (all-to-all-v), pose-bin first occurrences all-reduced (min) on a dense grid, "
+           "bucket subtrees of the KLD tree split over ranks, cluster sums + counts all-reduced" % (PT, world))
     line = {"metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
@@ -372,7 +403,7 @@ def run_b200_arm(a):
                        "l2": "flushed (256 MiB write) before every timed step",
                        "update_ms": up / a.steps, "resample_ms": rs / a.steps, "edt_build_ms": edt_ms,
                        "resampled_count": int(last.sample_count), "kld_leaf_count": int(last.leaf_count),
-                       "clusters": int(last.cluster_count),
+                       "clusters": int(last.cluster_count), "result_hash": digest,
                        "motion_update_ms_not_in_metric": motion_ms},
             "e2e": {"value": e_value, "unit": "evals/s", "ms_per_step": e_total_ms / a.steps,
                     "h2d_bytes_per_step": int(cnt0 * 32 + 2 * B * 8) * world,
@@ -392,6 +423,8 @@ def run_b200_arm(a):
                                           % (n_cpu, P, B, cu * 1e3, cr * 1e3),
                                 "host_cores_available": os.cpu_count()}
     emit(line)
+    if comm is not None:
+        comm.close()
     if dist is not None:
         dist.destroy_process_group()
     return 0

@@ -27,11 +27,13 @@ extern "C" {
 #define BAMCL_E_ARG -2        /* invalid argument / precondition of the reference violated */
 #define BAMCL_E_UNSUPPORTED -3 /* input outside what the device path represents (e.g. non-canonical cache) */
 #define BAMCL_E_STATE -4      /* call order violated (e.g. scoring before a distance cache exists) */
+#define BAMCL_E_COMM -5       /* NCCL error, NCCL missing, or a peer rank failed */
 
 typedef struct bamcl_ctx bamcl_ctx;
 typedef struct bamcl_map2d bamcl_map2d;
 typedef struct bamcl_map3d bamcl_map3d;
 typedef struct bamcl_pf bamcl_pf;
+typedef struct bamcl_comm bamcl_comm;
 
 const char* bamcl_last_error(void);
 int bamcl_version(void);
@@ -250,47 +252,70 @@ int bamcl_systematic_targets(double start, double delta, long n, double* out);
 /* resampleLimit (particle_filter.cpp:475-502), host arithmetic exposed for parity tests */
 int bamcl_resample_limit(int k, int min_samples, int max_samples, double pop_err, double pop_z);
 
-/* ---- sharded filter (multi-GPU, one process per GPU) ------------------------------------
- * The reference resamples ONE global set (particle_filter.cpp:269-354). With G ranks the global order is
- * rank-major: rank r scores, normalises and builds the CDF of its window [offset, offset + count) of the set;
- * every rank holds the whole set (poses of foreign windows are only read by the pose-bin tree). The host layer
- * moves the scalars and poses between ranks (NCCL on bamcl_ctx_stream(); badger_amcl_b200/sharded.py):
- *   score (window) -> local totals all-gathered, summed in rank order -> bamcl_pf_normalise(global total)
- *   bamcl_pf_shard_cdf(c0 = end of rank r-1) chained over ranks -> bounds[0..G]
- *   bamcl_systematic_plan -> which rank's window holds the source of every output slot (runs of slots)
- *   bamcl_pf_shard_select for this rank's runs -> rows of a global (n x 3) device buffer; runs broadcast
- *   bamcl_pf_shard_install: buffer -> the other sample set (weights 1/n), pose-bin tree, clusters, statistics. */
-/* window of the current set this rank works on; count < 0 = whole set (single-GPU behaviour) */
+/* ---- distributed filter (multi-GPU, one process per GPU) ---------------------------------
+ * The reference resamples ONE global set (particle_filter.cpp:269-354). With G ranks the global order is rank-major:
+ * rank r OWNS the contiguous window [n*r/G, n*(r+1)/G) of the set (only its owner holds a sample; map and scan are
+ * replicated). The exchanges run inside this library, on the context's stream, with NCCL over NVLink / NVSwitch:
+ *   update    window scored locally; window totals all-gathered and summed in rank order (= sample order of the
+ *             reference's sequential sum, particle_filter.cpp:246-252); window normalised by the global total
+ *   resample  every rank summarises its window's CDF tiles as functions of an unknown start value; ONE all-gather of the
+ *             summaries lets every rank resolve the exact CDF value at every rank boundary (the exclusive scan over
+ *             ranks of particle_filter.cpp:280-285) without a chain; systematic targets are planned per source rank;
+ *             selected poses go to the owners of the output slots in one grouped send/receive (all-to-all-v);
+ *             pose bins: per-rank first occurrences on a dense bin grid, all-reduced (min) -> identical creation order
+ *             everywhere; KLD leaf count with the bucket subtrees split over the ranks (sum all-reduced); cluster sums
+ *             and the convergence count all-reduced. */
+#define BAMCL_UNIQUE_ID_BYTES 128
+/* ncclGetUniqueId on ONE rank; ship the bytes to the other ranks over any host channel */
+int bamcl_comm_unique_id(void* id_out);
+/* ncclCommInitRank on every rank (collective); n_ranks = 1 needs no id and no NCCL */
+int bamcl_comm_create(bamcl_ctx* ctx, const void* id, int rank, int n_ranks, bamcl_comm** out);
+int bamcl_comm_destroy(bamcl_comm* comm);
+int bamcl_comm_rank(bamcl_comm* comm, int* rank, int* n_ranks);
+/* TEST back end: n_ranks ranks = n_ranks threads of THIS process on one GPU (each with its own context); collectives are
+ * stream-ordered device copies. Lets a single-GPU box run the multi-rank path; never selected implicitly. */
+int bamcl_comm_local_group(int n_ranks, void** group_out);
+int bamcl_comm_local_group_free(void* group);
+int bamcl_comm_create_local(bamcl_ctx* ctx, void* group, int rank, bamcl_comm** out);
+/* small host vectors summed over the ranks (beam-skipping agreement counts, planar_scanner.cpp:448-451, 487) */
+int bamcl_comm_all_reduce_sum_i32(bamcl_comm* comm, int* host_inout, int n);
+
+/* the filter becomes rank `comm->rank`'s shard of a global set; NULL detaches. */
+int bamcl_pf_shard_attach(bamcl_pf* pf, bamcl_comm* comm);
+/* the current set holds n_global samples (this rank owns its window of them); returns the window */
+int bamcl_pf_shard_set_count(bamcl_pf* pf, long n_global, long* window_offset, long* window_count);
+int bamcl_pf_shard_window(bamcl_pf* pf, long* window_offset, long* window_count);
+/* kd-tree + statistics of the global current set (bamcl_pf_init_stats, collective) */
+int bamcl_pf_shard_init_stats(bamcl_pf* pf, bamcl_resample_result* result);
+/* PlanarScanner::updateSensor / PointCloudScanner::updateSensor over the global set with the staged scan / cloud
+ * (collective): total_out = the global total */
+int bamcl_pf_shard_update_planar_staged(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_out);
+int bamcl_pf_shard_update_cloud_staged(bamcl_pf* pf, bamcl_map3d* map, double* total_out);
+/* ParticleFilter::updateResample (systematic) over the global set (collective). result is identical on every rank.
+ * params->random_poses (host, all n_random poses on every rank) or the registered device pose source feed :316-324. */
+int bamcl_pf_shard_resample(bamcl_pf* pf, const bamcl_resample_params* params, bamcl_resample_result* result);
+/* exact CDF value at every rank boundary of the last resample, bounds[0 .. n_ranks] (parity tests) */
+int bamcl_pf_shard_bounds(bamcl_pf* pf, double* bounds, int n_plus_1);
+
+/* window of the current set the scoring / CDF entry points work on; count < 0 = whole set. (A distributed filter
+ * manages its window itself; this is for callers that score a set in pieces.) */
 int bamcl_pf_set_window(bamcl_pf* pf, long offset, long count);
-/* exact sequential CDF of the window with c[0] = c0 (particle_filter.cpp:280-285 continued from the previous
- * rank's last value); end_out = c[count] */
-int bamcl_pf_shard_cdf(bamcl_pf* pf, double c0, double* end_out);
 /* host arithmetic: for the systematic target sequence (start, delta, n) of particle_filter.cpp:309,337-341 and the
  * ranks' CDF bounds[0..n_ranks], the runs (k_begin, k_end, rank) of output slots whose source lies in each rank's
  * window; targets at/after bounds[n_ranks] go to the last rank that holds weight. */
 int bamcl_systematic_plan(double start, double delta, long n, const double* bounds, int n_ranks, long* runs, int max_runs,
                           int* n_runs);
-/* particle_filter.cpp:326-351 for outputs [k_begin, k_end) of n_sys: pose of the selected window particle ->
- * out_aos3_dev[(row0 + k) * 3 ..] (device pointer), global source index -> src_out_dev_or_null[row0 + k]. Enqueued on
- * the context's stream; needs bamcl_pf_shard_cdf first. */
-int bamcl_pf_shard_select(bamcl_pf* pf, double start, double delta, long n_sys, long row0, long k_begin, long k_end,
-                          double* out_aos3_dev, int* src_out_dev_or_null);
-/* particle_filter.cpp:343-346,448-470 on every rank: the n gathered poses become the new current set (weights 1/n),
- * then pose-bin tree, clusters, statistics, updateConverged as in bamcl_pf_resample; clears the window. */
-int bamcl_pf_shard_install(bamcl_pf* pf, const double* aos3_dev, long n, const bamcl_resample_params* params,
-                           bamcl_resample_result* result);
-/* The sharded update without host round trips: bamcl_pf_score_planar_staged with the window's total left in device
- * memory (total_dev), and -- after the ranks' totals were all-gathered on the same stream -- the global total (summed
- * in rank order, as ParticleFilter::updateSensor sums in sample order, particle_filter.cpp:246-252) + normalisation of
- * the window in one launch; total_out_dev receives the global total. Nothing synchronises. */
-int bamcl_pf_score_planar_staged_dev(bamcl_pf* pf, bamcl_map2d* map, int converged, double* total_dev);
-int bamcl_pf_normalise_ranks_dev(bamcl_pf* pf, const double* totals_dev, int n_ranks, double* total_out_dev);
-/* Beam skipping on a sharded set (planar_scanner.cpp:398-451, 483-494; SURVEY 8e collective (2)): the per-beam
+/* host arithmetic: the transfers of the pose exchange for such a plan. Output slot o = n_random + k belongs to the rank
+ * that owns it in the partition of n_random + n outputs. moves[5 * i ..] = (source rank, destination rank, k_begin,
+ * k_end, position of k_begin in the source rank's selected rows), in the order both sides issue them. */
+int bamcl_shard_exchange_plan(const long* runs, int n_runs, long n_random, long n, int n_ranks, long* moves, int max_moves,
+                              int* n_moves);
+/* Beam skipping on a distributed set (planar_scanner.cpp:398-451, 483-494; SURVEY 8e collective (2)): the per-beam
  * agreement counts are sums over ALL particles and the skip ratio is against the whole set. bamcl_pf_skip_counts runs
  * the counting pass over this rank's window for the staged scan (n_out = 0 when this update does no beam skipping: model
  * not likelihood_field_prob, do_beamskip off, or the set not converged); the caller sums the vectors over the ranks
- * (one all-reduce of <= max_beams ints) and hands them back with the global sample count; the next scoring call
- * (bamcl_pf_score_planar_staged / bamcl_pf_update_planar_staged) then masks and integrates with them. */
+ * (bamcl_comm_all_reduce_sum_i32) and hands them back with the global sample count; the next scoring call then masks
+ * and integrates with them. */
 int bamcl_pf_skip_counts(bamcl_pf* pf, bamcl_map2d* map, int converged, int* counts_out, int capacity, int* n_out);
 int bamcl_pf_set_skip_counts(bamcl_pf* pf, const int* counts, int n, long global_sample_count);
 /* host AoS <-> the samples [offset, offset + n) of the current set (a rank's window); sample_count is unchanged */

@@ -168,19 +168,21 @@ def test_sharded_cloud_update_matches_the_unsharded_device_filter(env, world):
     want, want_total = one.weights(), one.last_total
     one.close()
 
-    def rank_fn(rank, dist):
+    def rank_fn(rank, group):
         ctx = cabi.Context(0)
         m = cabi.Map3D(ctx, RES, env["keys"], MAX_DIST)  # the cache is replicated: one copy per rank
         m.upload_distances(env["pm"].dense())
         pf = cabi.ParticleFilter(ctx, n // 10, n)
-        pf.upload_samples(samples)
-        eng = sharded.CudaEngine(pf, None, 0)
-        eng.set_cloud(m, model, points)
-        f = sharded.ShardedFilter(eng, rank, world, dist, n // 10, n)
+        comm = sharded.Comm.local(ctx, group, rank, world)
+        f = sharded.ShardedFilter(pf, comm)
+        f.set_global_samples(samples)
+        pf.stage_cloud(m, model, points)
+        f.set_cloud(m)
         total = f.update_sensor()
         off, cnt = f.window()
-        w = pf.weights()[off:off + cnt]
+        w = pf.weights_n(cnt)
         pf.close()
+        comm.close()
         m.close()
         ctx.close()
         return total, w

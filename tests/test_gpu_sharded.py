@@ -1,7 +1,7 @@
-"""GPU parity of the sharded filter: G ranks (threads of this process, one filter object each, all on
-cuda:0) run the sharded update + resample through the C ABI; the result must be the single-set result -- the
-oracle's (bit-identical indices, poses, leaf / node / cluster counts; statistics to 1e-6) and the unsharded
-device filter's."""
+"""GPU parity of the distributed filter: G ranks (threads of this process, one context + filter each, all
+on cuda:0, joined by the library's in-process communicator) run the distributed update + resample of the C library;
+the result must be the single-set result -- the oracle's (bit-identical indices, poses, leaf / node / cluster counts;
+statistics to 1e-6) and the single-GPU device filter's. tests/test_gpu_nccl.py runs the same over real NCCL ranks."""
 import os
 import sys
 
@@ -23,18 +23,32 @@ def env(oracle_built):
     cells = synth.make_grid(1000, 1000, seed=7)
     m = cabi.Map2D(ctx, cells, RES)
     m.build_distances(2.0)
+    dist = m.download_distances()
     truth = synth.pick_truth_pose(cells, RES, seed=5)
-    yield dict(O=oracle_built, cabi=cabi, ctx=ctx, cells=cells, truth=truth, map=m)
+    yield dict(O=oracle_built, cabi=cabi, ctx=ctx, cells=cells, truth=truth, map=m, dist=dist)
     m.close()
     ctx.close()
 
 
+def _rank_map(env, ctx):
+    """every rank holds its own replica of the map (as one process per GPU would)"""
+    cabi = env["cabi"]
+    m = cabi.Map2D(ctx, env["cells"], RES)
+    m.upload_distances(env["dist"], 2.0)
+    return m
+
+
+@pytest.mark.parametrize("slow_cap", [None, "1"])
 @pytest.mark.parametrize("world", [2, 3, 8])
 @pytest.mark.parametrize("kind", ["uniform", "heavy", "zeros_first_rank", "dominant"])
-def test_sharded_cdf_chain_is_the_sequential_cdf(env, world, kind):
-    """particle_filter.cpp:280-285 across windows: concatenated local CDFs == the oracle's c[0..P]"""
+def test_distributed_cdf_is_the_sequential_cdf(env, world, kind, slow_cap, monkeypatch):
+    """particle_filter.cpp:280-285 across windows: concatenated window CDFs == the oracle's c[0..P], and the exact
+    value at every rank boundary; slow_cap = 1 starts with one-tile summaries and forces the regrow path"""
     from badger_amcl_b200 import sharded
+    from sharded_support import run_ranks
     O, cabi = env["O"], env["cabi"]
+    if slow_cap:
+        monkeypatch.setenv("BAMCL_CDF_SLOW_CAP", slow_cap)
     n = 50001
     rng = np.random.default_rng(world + len(kind))
     w = {"uniform": np.full(n, 1.0 / n), "heavy": np.exp(rng.normal(0.0, 6.0, n)), "zeros_first_rank": rng.random(n),
@@ -49,65 +63,74 @@ def test_sharded_cdf_chain_is_the_sequential_cdf(env, world, kind):
     port = O.PortPF(1, n)
     port.set_samples(aos)
     want = port.cdf()
-    pf = cabi.ParticleFilter(env["ctx"], 1, n)
-    pf.upload_samples(aos)
     b = sharded.shard_bounds(n, world)
-    c0 = 0.0
-    for r in range(world):
-        cabi._check(pf.L.bamcl_pf_set_window(pf.h, b[r], b[r + 1] - b[r]))
-        end = cabi.C.c_double()
-        cabi._check(pf.L.bamcl_pf_shard_cdf(pf.h, c0, cabi.C.byref(end)))
-        assert end.value == want[b[r + 1]], "rank %d end value" % r
-        c0 = end.value
-    pf.close()
+
+    def rank_fn(rank, group):
+        ctx = cabi.Context(0)
+        pf = cabi.ParticleFilter(ctx, 1, n)
+        comm = sharded.Comm.local(ctx, group, rank, world)
+        f = sharded.ShardedFilter(pf, comm)
+        f.set_global_samples(aos)
+        off, cnt = f.window()
+        c = np.empty(cnt + 1)
+        cabi._check(pf.L.bamcl_pf_cdf(pf.h, cabi._p(c), cnt + 1))
+        bounds = f.bounds()
+        pf.close()
+        comm.close()
+        ctx.close()
+        return off, cnt, c, bounds
+
+    got = run_ranks(world, rank_fn)
+    for r, (off, cnt, c, bounds) in enumerate(got):
+        assert (off, cnt) == (b[r], b[r + 1] - b[r])
+        assert np.array_equal(c, want[off:off + cnt + 1]), "rank %d window CDF" % r
+        assert np.array_equal(bounds, want[b]), "rank %d bounds" % r
 
 
-def _run_sharded(env, world, poses, weights_per_step, seed, n_min, exchange="allgather"):
+def _run_distributed(env, world, poses, weights_per_step, seed, n_min):
     from badger_amcl_b200 import sharded
     from sharded_support import run_ranks
     cabi = env["cabi"]
     n = len(poses)
+    aos0 = np.concatenate([poses, np.full((n, 1), 1.0 / n)], axis=1)
 
-    def rank_fn(rank, dist):
+    def rank_fn(rank, group):
         ctx = cabi.Context(0)  # one context (stream) per rank, as in the one-process-per-GPU deployment
         pf = cabi.ParticleFilter(ctx, n_min, n)
-        pf.init_with_poses(poses)
-        eng = sharded.CudaEngine(pf, env["map"], 0)
-        eng.want_sources()
-        f = sharded.ShardedFilter(eng, rank, world, dist, n_min, n)
+        comm = sharded.Comm.local(ctx, group, rank, world)
+        f = sharded.ShardedFilter(pf, comm)
+        f.set_global_samples(aos0)
+        init = f.init_stats()
         f.srand48(seed)
-        f.exchange = exchange
-        out = []
+        out = [dict(res=init)]
         for w in weights_per_step:
-            m = pf.sample_count()
             # staged parity: every rank installs the oracle's normalised weights of ITS window
             off, cnt = f.window()
-            full = np.zeros(m)
-            full[off:off + cnt] = w[:m][off:off + cnt]
-            pf.upload_weights(full)
+            pf.upload_weights(w[off:off + cnt])
             f.w_slow = f.w_fast = 1.0
             res = f.update_resample()
-            out.append(dict(res=res, src=eng.src[:res.sample_count].cpu().numpy(), samples=pf.samples(),
-                            labels=pf.sample_clusters(), stats=np.array(list(res.mean) + list(res.cov)),
-                            runs=list(f.last_plan), exchange=f.last_exchange))
+            off, cnt = f.window()
+            out.append(dict(res=res, off=off, cnt=cnt, src=f.window_sources(), samples=f.download_window(),
+                            labels=f.window_clusters(), stats=np.array(list(res.mean) + list(res.cov))))
         pf.close()
+        comm.close()
         ctx.close()
         return out
 
     return run_ranks(world, rank_fn)
 
 
-@pytest.mark.parametrize("exchange", ["allgather", "broadcast"])
 @pytest.mark.parametrize("world", [2, 4])
-@pytest.mark.parametrize("n,cloud", [(5000, "global"), (100000, "tracking"), (100000, "global")])
-def test_sharded_resample_equals_the_oracles_single_set(env, world, n, cloud, exchange):
+@pytest.mark.parametrize("n,cloud", [(5000, "global"), (100000, "tracking"), (100000, "global"), (7, "global")])
+def test_distributed_resample_equals_the_oracles_single_set(env, world, n, cloud):
     O = env["O"]
     cells, truth = env["cells"], env["truth"]
     poses = (synth.uniform_free_poses(cells, RES, n, seed=1) if cloud == "global"
              else synth.gaussian_poses(truth, n, seed=2))
     rng = np.random.default_rng(n + world)
-    port = O.PortPF(n // 10, n)
+    port = O.PortPF(max(1, n // 10), n)
     port.init_with_poses(poses)
+    init_want = (port.leaf_count(), port.node_count(), port.cluster_count())
     port.srand48(7)
     weights, want = [], []
     for _ in range(2):
@@ -119,28 +142,87 @@ def test_sharded_resample_equals_the_oracles_single_set(env, world, n, cloud, ex
         port.set_samples(s)
         port.set_averages(1.0, 1.0)
         port.update_resample()
-        weights.append(np.concatenate([w, np.zeros(n - m)]))
+        weights.append(w)
         want.append(dict(count=port.sample_count(), src=port.resample_sources(), samples=port.samples(),
                          leaf=port.leaf_count(), nodes=port.node_count(), clusters=port.cluster_count(),
                          labels=port.sample_clusters(), stats=port.set_stats(), conv=port.is_converged()))
-    got = _run_sharded(env, world, poses, weights, 7, n // 10, exchange)
-    assert got[0][0]["exchange"] == exchange  # balanced weights: the all-gather path is really taken when asked for
+    got = _run_distributed(env, world, poses, weights, 7, max(1, n // 10))
     for rank in range(world):
+        r0 = got[rank][0]["res"]
+        assert (r0.leaf_count, r0.node_count, r0.cluster_count) == init_want
         for step in range(2):
-            g, w_ = got[rank][step], want[step]
+            g, w_ = got[rank][step + 1], want[step]
             r = g["res"]
+            sl = slice(g["off"], g["off"] + g["cnt"])
             assert r.sample_count == w_["count"]
-            assert np.array_equal(g["src"], w_["src"])
-            assert np.array_equal(g["samples"][:, :3], w_["samples"][:, :3])
-            assert np.array_equal(g["samples"][:, 3], w_["samples"][:, 3])
+            assert np.array_equal(g["src"], w_["src"][sl])
+            assert np.array_equal(g["samples"][:, :3], w_["samples"][sl, :3])
+            assert np.array_equal(g["samples"][:, 3], w_["samples"][sl, 3])
             assert (r.leaf_count, r.node_count, r.cluster_count) == (w_["leaf"], w_["nodes"], w_["clusters"])
             assert bool(r.converged) == w_["conv"]
-            assert np.array_equal(g["labels"], w_["labels"])
+            assert np.array_equal(g["labels"], w_["labels"][sl])
             assert np.allclose(g["stats"], w_["stats"], rtol=1e-6, atol=1e-9)
-            assert len(g["runs"]) <= 2 * world + 2
+    # every sample is owned exactly once
+    for step in range(2):
+        assert sum(got[rank][step + 1]["cnt"] for rank in range(world)) == want[step]["count"]
 
 
-def test_sharded_update_matches_the_unsharded_device_filter(env):
+def test_distributed_resample_with_random_pose_injection(env):
+    """w_diff > 0 (particle_filter.cpp:297-324): the first n_rand outputs are the caller's random poses, wherever their
+    owner sits"""
+    O = env["O"]
+    n, world = 20000, 3
+    cells = env["cells"]
+    poses = synth.uniform_free_poses(cells, RES, n, seed=1)
+    rp = synth.uniform_free_poses(cells, RES, n, seed=9)
+    rng = np.random.default_rng(3)
+    w = np.exp(rng.normal(0.0, 2.0, n))
+    w /= w.sum()
+    port = O.PortPF(n // 10, n)
+    port.init_with_poses(poses)
+    port.srand48(11)
+    s = port.samples()
+    s[:, 3] = w
+    port.set_samples(s)
+    port.set_averages(1.0, 0.7)  # w_slow, w_fast -> w_diff = 0.3
+    port.set_random_poses(rp)
+    port.update_resample()
+    from badger_amcl_b200 import sharded
+    from sharded_support import run_ranks
+    cabi = env["cabi"]
+    aos0 = np.concatenate([poses, np.full((n, 1), 1.0 / n)], axis=1)
+
+    def rank_fn(rank, group):
+        ctx = cabi.Context(0)
+        pf = cabi.ParticleFilter(ctx, n // 10, n)
+        comm = sharded.Comm.local(ctx, group, rank, world)
+        f = sharded.ShardedFilter(pf, comm)
+        f.set_global_samples(aos0)
+        f.init_stats()
+        f.srand48(11)
+        f.set_random_poses(rp)
+        off, cnt = f.window()
+        pf.upload_weights(w[off:off + cnt])
+        f.w_slow, f.w_fast = 1.0, 0.7
+        res = f.update_resample()
+        off, cnt = f.window()
+        out = (res, off, cnt, f.window_sources(), f.download_window())
+        pf.close()
+        comm.close()
+        ctx.close()
+        return out
+
+    got = run_ranks(world, rank_fn)
+    want_s, want_src = port.samples(), port.resample_sources()
+    for res, off, cnt, src, smp in got:
+        assert res.sample_count == port.sample_count() and res.random_poses_used > 0
+        assert np.array_equal(src, want_src[off:off + cnt])
+        assert np.array_equal(smp, want_s[off:off + cnt])
+        assert (res.leaf_count, res.node_count, res.cluster_count) == (port.leaf_count(), port.node_count(),
+                                                                      port.cluster_count())
+
+
+def test_distributed_update_matches_the_single_gpu_filter(env):
     """score + global total + normalise over 3 windows == one filter over the whole set (weights to 1e-12: only the
     order of the partial sums of the total differs)"""
     from badger_amcl_b200 import sharded
@@ -149,6 +231,7 @@ def test_sharded_update_matches_the_unsharded_device_filter(env):
     n, world = 30000, 3
     cells, truth = env["cells"], env["truth"]
     poses = synth.uniform_free_poses(cells, RES, n, seed=4)
+    aos0 = np.concatenate([poses, np.full((n, 1), 1.0 / n)], axis=1)
     ranges, angles = synth.make_scan(cells, RES, truth, n_beams=180)
     model = cabi.planar_model(model_type=cabi.MODEL_LF, max_beams=180, scanner_pose=(0.1, 0.0, 0.0))
     one = cabi.ParticleFilter(env["ctx"], n // 10, n)
@@ -157,16 +240,20 @@ def test_sharded_update_matches_the_unsharded_device_filter(env):
     want = one.weights()
     one.close()
 
-    def rank_fn(rank, dist):
+    def rank_fn(rank, group):
         ctx = cabi.Context(0)
+        m = _rank_map(env, ctx)
         pf = cabi.ParticleFilter(ctx, n // 10, n)
-        pf.init_with_poses(poses)
-        pf.stage_scan(env["map"], model, ranges, angles, 30.0)
-        f = sharded.ShardedFilter(sharded.CudaEngine(pf, env["map"], 0), rank, world, dist, n // 10, n)
+        comm = sharded.Comm.local(ctx, group, rank, world)
+        f = sharded.ShardedFilter(pf, comm, m)
+        f.set_global_samples(aos0)
+        pf.stage_scan(m, model, ranges, angles, 30.0)
         total = f.update_sensor()
         off, cnt = f.window()
-        w = pf.weights()[off:off + cnt]
+        w = pf.weights_n(cnt)
         pf.close()
+        comm.close()
+        m.close()
         ctx.close()
         return total, off, cnt, w
 
@@ -179,9 +266,9 @@ def test_sharded_update_matches_the_unsharded_device_filter(env):
 
 @pytest.mark.parametrize("case", ["mask", "error_all_beams"])
 @pytest.mark.parametrize("world", [2, 3])
-def test_sharded_beam_skipping_matches_the_unsharded_device_filter(env, world, case):
+def test_distributed_beam_skipping_matches_the_single_gpu_filter(env, world, case):
     """SURVEY 8e collective (2): per-beam agreement counts summed over the ranks' windows, the skip ratio against the
-    whole set (planar_scanner.cpp:398-451, 483-494). The unsharded device path is the one pinned to the oracle in
+    whole set (planar_scanner.cpp:398-451, 483-494). The single-GPU device path is the one pinned to the oracle in
     tests/test_gpu_score.py; every rank's window must carry exactly its weights (same mask => same arithmetic)."""
     from badger_amcl_b200 import sharded
     from sharded_support import run_ranks
@@ -197,6 +284,7 @@ def test_sharded_beam_skipping_matches_the_unsharded_device_filter(env, world, c
         # half of the cloud sits on the true pose, half is scattered: the counts differ from window to window
         poses = np.concatenate([synth.gaussian_poses(truth, n // 2, seed=3, sigma_xy=0.05, sigma_th=0.01),
                                 synth.uniform_free_poses(cells, RES, n - n // 2, seed=4)])
+    aos0 = np.concatenate([poses, np.full((n, 1), 1.0 / n)], axis=1)
     ranges, angles = synth.make_scan(cells, RES, truth, n_beams=n_beams)
     rng = np.random.default_rng(9)
     for i in rng.choice(n_beams, 25, replace=False):
@@ -217,18 +305,22 @@ def test_sharded_beam_skipping_matches_the_unsharded_device_filter(env, world, c
     one.close()
     plain.close()
 
-    def rank_fn(rank, dist):
+    def rank_fn(rank, group):
         ctx = cabi.Context(0)
+        m = _rank_map(env, ctx)
         pf = cabi.ParticleFilter(ctx, n // 10, n)
-        pf.init_with_poses(poses)
+        comm = sharded.Comm.local(ctx, group, rank, world)
+        f = sharded.ShardedFilter(pf, comm, m)
+        f.set_global_samples(aos0)
         pf.set_exact_terms(True)
-        pf.converged = True
-        pf.stage_scan(env["map"], model, ranges, angles, 30.0)
-        f = sharded.ShardedFilter(sharded.CudaEngine(pf, env["map"], 0), rank, world, dist, n // 10, n)
+        f.converged = True
+        pf.stage_scan(m, model, ranges, angles, 30.0)
         total = f.update_sensor()
         off, cnt = f.window()
-        w = pf.weights()[off:off + cnt]
+        w = pf.weights_n(cnt)
         pf.close()
+        comm.close()
+        m.close()
         ctx.close()
         return total, w
 

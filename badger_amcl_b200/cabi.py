@@ -125,6 +125,7 @@ SIGNATURES = {
     "bamcl_timer_stop_ms": (_I, [_P, _P]),
     "bamcl_ctx_launch_count": (_L, [_P]),
     "bamcl_ctx_flush_l2": (_I, [_P]),
+    "bamcl_bench_gather": (_I, [_P, C.c_size_t, _L, _P]),
     "bamcl_host_alloc": (_I, [C.c_size_t, _P]),
     "bamcl_host_free": (_I, [_P]),
     "bamcl_pf_last_score_ms": (_I, [_P, _P]),
@@ -263,6 +264,12 @@ class Context:
 
     def flush_l2(self):
         _check(self.L.bamcl_ctx_flush_l2(self.h))
+
+    def gather_rate(self, table_bytes, n_gathers=1 << 30):
+        """random 2-byte gathers per second over a table of table_bytes (bamcl_bench_gather)"""
+        ms = C.c_float()
+        _check(self.L.bamcl_bench_gather(self.h, table_bytes, n_gathers, C.byref(ms)))
+        return n_gathers / (ms.value * 1e-3)
 
 
 def pinned_array(shape, dtype=np.float64):

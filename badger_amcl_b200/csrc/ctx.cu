@@ -1,4 +1,5 @@
 // Context, error reporting, timing helpers.
+#include <algorithm>
 #include <cstdarg>
 
 #include "common.cuh"
@@ -28,9 +29,65 @@ __global__ void k_flush(float4* __restrict__ p, size_t n)
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
     p[i] = make_float4(1.f, 2.f, 3.f, 4.f);
 }
+// measurement aid: random 2-byte gathers, 16 independent loads in flight per thread (the access pattern of the
+// likelihood-field scorer without its arithmetic)
+__global__ void __launch_bounds__(256) k_gather_bench(const unsigned short* __restrict__ table, unsigned long long n_elems,
+                                                      int iters, unsigned* __restrict__ sink)
+{
+  unsigned long long s = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * 0x9E3779B97F4A7C15ull + 12345ull;
+  unsigned acc = 0;
+  for (int it = 0; it < iters; it++)
+  {
+    unsigned v[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+    {
+      s = s * 6364136223846793005ull + 1442695040888963407ull;
+      const unsigned long long idx = ((s >> 32) * n_elems) >> 32;  // uniform in [0, n_elems), n_elems < 2^32
+      v[k] = __ldg(&table[idx]);
+    }
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+      acc += v[k];
+  }
+  if (acc == 0xFFFFFFFFu)
+    sink[0] = acc;
+}
 }  // namespace
 
 extern "C" {
+
+int bamcl_bench_gather(bamcl_ctx* ctx, size_t table_bytes, long n_gathers, float* ms_out)
+{
+  if (!ctx || !ms_out || table_bytes < 64 || n_gathers < 1)
+    return set_error(BAMCL_E_ARG, "bamcl_bench_gather: bad arguments");
+  bamcl::DevBuf table, sink;
+  BAMCL_TRY(table.reserve(table_bytes));
+  BAMCL_TRY(sink.reserve(64));
+  BAMCL_CUDA_OK(cudaMemsetAsync(table.p, 1, table_bytes, ctx->stream));
+  const int blocks = kNumSMs * 8;
+  const int iters = (int)std::max<long>(1, n_gathers / ((long)blocks * 256 * 16));
+  int rc = BAMCL_OK;
+  float best = 1e30f;
+  for (int rep = 0; rep < 4 && rc == BAMCL_OK; rep++)  // first pass warms L2
+  {
+    cudaEventRecord(ctx->ev0, ctx->stream);
+    k_gather_bench<<<blocks, 256, 0, ctx->stream>>>(table.as<unsigned short>(), table_bytes / 2, iters, sink.as<unsigned>());
+    ctx->launches++;
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    if (cudaEventSynchronize(ctx->ev1) != cudaSuccess)
+      rc = set_error(BAMCL_E_CUDA, "bamcl_bench_gather: kernel failed");
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    if (rep > 0 && ms < best)
+      best = ms;
+  }
+  table.release();
+  sink.release();
+  // report per gather actually issued
+  *ms_out = best * (float)((double)n_gathers / ((double)blocks * 256 * 16 * iters));
+  return rc;
+}
 
 const char* bamcl_last_error(void) { return g_last_error.c_str(); }
 int bamcl_version(void) { return 100; }

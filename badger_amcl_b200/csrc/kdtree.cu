@@ -265,6 +265,8 @@ __global__ void __launch_bounds__(256) k_tree_build(const TreeArgs a)
     return;
   const int K = a.out->K;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+  if (tid == 0)
+    a.out->leaf = a.out->bucket_levels = 0;  // whatever an abandoned fast build had counted
   for (int v = tid; v < K; v += nth)
   {
     a.child[2 * v] = a.child[2 * v + 1] = NONE;
@@ -447,6 +449,31 @@ __global__ void __launch_bounds__(256) k_cc_union_dense(const TreeOut* __restric
   const int u = __ldg(&g_node[a + box.dim[0] * (b + box.dim[1] * c)]);
   if (u >= 0)
     uf_union<CA>(parent, v, u);
+}
+
+// The same unions in bin order: one thread per grid cell, the 13 forward neighbours are plain (coalesced, L1-shared)
+// loads of the neighbouring rows. Used when the grid is reasonably full; the node-order kernel above serves sparse sets.
+template <bool CA>
+__global__ void __launch_bounds__(256) k_cc_union_cells(const Box box, const int* __restrict__ g_node, long cells, int* parent)
+{
+  const long c = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cells)
+    return;
+  const int v = __ldg(&g_node[c]);
+  if (v < 0)
+    return;
+  const int d0 = box.dim[0], d1 = box.dim[1], d2 = box.dim[2];
+  const int a = (int)(c % d0), b = (int)((c / d0) % d1), t = (int)(c / ((long)d0 * d1));
+#pragma unroll
+  for (int o = 14; o < 27; o++)
+  {
+    const int da = o / 9 - 1, db = (o % 9) / 3 - 1, dt = (o % 9) % 3 - 1;
+    if ((unsigned)(a + da) >= (unsigned)d0 || (unsigned)(b + db) >= (unsigned)d1 || (unsigned)(t + dt) >= (unsigned)d2)
+      continue;
+    const int u = __ldg(&g_node[c + da + (long)d0 * (db + (long)d1 * dt)]);
+    if (u >= 0)
+      uf_union<CA>(parent, v, u);
+  }
 }
 
 // Read-only find: a compressing find here would race with other threads' finds (a stale intermediate ancestor
@@ -725,50 +752,85 @@ __global__ void __launch_bounds__(256) k_cluster_finalize(const TreeOut* __restr
 
 namespace
 {
-// the bucketed shared-memory leaf count (tree_fast.cuh) with a top tree of M_TOP keys
-template <int M_TOP>
-int launch_fast_tree(bamcl_pf* pf, TreeOut* out, int n)
+// the bucketed shared-memory leaf count (tree_fast.cuh) of a tree of at most k_max keys (the device knows K)
+int launch_fast_tree(bamcl_pf* pf, TreeOut* out, int k_max)
 {
   bamcl_ctx* ctx = pf->ctx;
-  constexpr int N_BUCKETS = 2 * M_TOP;
+  const int m2 = top2_size(k_max);  // >= the device's top2_size(K)
+  const size_t n_b = 2 * (size_t)m2 + 2;
+  const size_t scan_ints = scan_scratch_ints((long)n_b);
+  // class lists: a bucket of more than c keys exists at most (keys + nodes) / c times
+  const long mass = (long)k_max + m2;
+  const int cap_s = (int)std::min<long>(2l * m2, std::max<long>(2l * M_TOP1, mass / FAST_CAP_W + 1));
+  const int cap_m = (int)std::min<long>(2l * m2, mass / FAST_CAP_S + 1), cap_l = (int)std::min<long>(2l * m2, mass / FAST_CAP_M + 1);
+  BAMCL_TRY(pf->t_fast.reserve(sizeof(TopNode) * (size_t)m2 +
+                               sizeof(int) * (n_b + scan_ints + (size_t)cap_s + cap_m + cap_l + 32)));
   FastArgs fa;
-  int* small = pf->t_fast.as<int>();
   fa.out = out;
   fa.nkey = pf->t_nkey.as<unsigned long long>();
-  fa.tpivot = small;
-  fa.tchild = small + M_TOP;
-  fa.bcount = small + 3 * M_TOP;
-  fa.boff = fa.bcount + N_BUCKETS + 1;
+  fa.top = pf->t_fast.as<TopNode>();
+  fa.bcount = reinterpret_cast<int*>(fa.top + m2);
+  int* scan_scratch = fa.bcount + n_b;
+  fa.cls = scan_scratch + scan_ints;
+  fa.lists = fa.cls + 8;
+  fa.list_m = cap_s;
+  fa.list_l = cap_s + cap_m;
   fa.bslot = pf->t_cur.as<int>();
   fa.bpos = pf->t_first_at.as<int>();
   fa.bids = pf->t_child.as<int>();
   fa.part_rank = pf_rank(pf);
   fa.part_n = pf_ranks(pf);
-  const int per = 28;  // bytes of shared memory per key in k_fast_top / k_fast_bucket
+  const int per = FAST_BYTES_PER_KEY;
   static bool attr_done = false;
   if (!attr_done)
   {
-    BAMCL_CUDA_OK(cudaFuncSetAttribute(k_fast_top<M_TOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 24 * M_TOP));
-    BAMCL_CUDA_OK(cudaFuncSetAttribute(k_fast_descend<M_TOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 17 * M_TOP));
-    BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_M, FAST_CAP_S, 512, M_TOP>),
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, per * FAST_CAP_M));
-    BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_L, FAST_CAP_M, 1024, M_TOP>),
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, per * FAST_CAP_L));
+    BAMCL_CUDA_OK(cudaFuncSetAttribute(k_fast_top, cudaFuncAttributeMaxDynamicSharedMemorySize, 24 * M_TOP1));
+    BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_M, 1, 512, false>), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       per * FAST_CAP_M));
+    BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_L, 2, 1024, false>), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       per * FAST_CAP_L));
+    BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_M, 1, 512, true>), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       per * FAST_CAP_M));
+    BAMCL_CUDA_OK(cudaFuncSetAttribute((k_fast_bucket<FAST_CAP_L, 2, 1024, true>), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       per * FAST_CAP_L));
     attr_done = true;
   }
-  const int walk_blocks = std::max(1, std::min(kNumSMs * (M_TOP > 4096 ? 1 : 8), (n + 255) / 256));
-  BAMCL_LAUNCH(ctx, k_fast_top<M_TOP>, 1, 1024, 24 * M_TOP, fa);
-  BAMCL_LAUNCH(ctx, k_fast_descend<M_TOP>, walk_blocks, 256, 17 * M_TOP, fa);
-  BAMCL_LAUNCH(ctx, k_fast_offsets<M_TOP>, 1, 1024, 0, fa);
-  if (n > M_TOP)
-    BAMCL_LAUNCH(ctx, k_fast_scatter<M_TOP>, walk_blocks, 256, 0, fa);
-  const int bucket_blocks = 2 * std::min(n, M_TOP);
-  if (n <= M_TOP + FAST_CAP_S)
+  auto walk_blocks = [](long keys) { return (unsigned)std::max<long>(1, std::min<long>((long)kNumSMs * 8, (keys + 255) / 256)); };
+  BAMCL_CUDA_OK(cudaMemsetAsync(fa.bcount, 0, sizeof(int) * n_b, ctx->stream));
+  BAMCL_CUDA_OK(cudaMemsetAsync(fa.cls, 0, sizeof(int) * 8, ctx->stream));
+  BAMCL_LAUNCH(ctx, k_fast_top, 1, 1024, 24 * M_TOP1, fa);
+  if (m2 > M_TOP1)
   {
-    BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_S, 0, 256, M_TOP>), bucket_blocks, 256, per * FAST_CAP_S, fa);
+    // ---- step B: keys [M1, M2) extend the written-out tree
+    const int nb1 = 2 * M_TOP1;
+    const long keys_b = m2 - M_TOP1;
+    BAMCL_LAUNCH(ctx, k_fast_descend<false>, walk_blocks(keys_b), 256, 0, fa);
+    BAMCL_TRY(exclusive_scan_i32(ctx, fa.bcount, fa.bcount, nb1 + 1, scan_scratch, nullptr));
+    BAMCL_LAUNCH(ctx, k_fast_scatter<false>, walk_blocks(keys_b), 256, 0, fa);
+    BAMCL_LAUNCH(ctx, k_fast_classify<false>, (nb1 + 255) / 256, 256, 0, fa);
+    BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_S, 0, 256, false>), std::min<long>(nb1, cap_s), 256, per * FAST_CAP_S, fa);
+    BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_M, 1, 512, false>), std::min<long>(cap_m, keys_b / FAST_CAP_S + 1), 512,
+                 per * FAST_CAP_M, fa);
+    BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_L, 2, 1024, false>), std::min<long>(cap_l, keys_b / FAST_CAP_M + 1), 1024,
+                 per * FAST_CAP_L, fa);
+    BAMCL_CUDA_OK(cudaMemsetAsync(fa.bcount, 0, sizeof(int) * n_b, ctx->stream));
+    BAMCL_CUDA_OK(cudaMemsetAsync(fa.cls, 0, sizeof(int) * 8, ctx->stream));
+  }
+  // ---- step C: every remaining key, leaves counted per bucket
+  const int nb2 = 2 * m2;
+  if (k_max > M_TOP1)
+  {
+    BAMCL_LAUNCH(ctx, k_fast_descend<true>, walk_blocks(k_max), 256, 0, fa);
+    BAMCL_TRY(exclusive_scan_i32(ctx, fa.bcount, fa.bcount, nb2 + 1, scan_scratch, nullptr));
+    BAMCL_LAUNCH(ctx, k_fast_scatter<true>, walk_blocks(k_max), 256, 0, fa);
+  }
+  if (k_max < M_TOP1 + FAST_CAP_W)
+  {
+    BAMCL_LAUNCH(ctx, k_fast_bucket_warp, (nb2 + FAST_W_WARPS - 1) / FAST_W_WARPS, FAST_W_WARPS * 32, 0, fa);
     return BAMCL_OK;
   }
-  // the three size classes touch disjoint buckets: large and small ones go to side streams, medium stays here
+  BAMCL_LAUNCH(ctx, k_fast_classify<true>, (nb2 + 255) / 256, 256, 0, fa);
+  // the size classes touch disjoint buckets: large and small CTA buckets go to side streams, the rest stays here
   cudaStream_t here = ctx->stream;
   BAMCL_CUDA_OK(cudaEventRecord(pf->ev_bucket_fork, here));
   {
@@ -783,13 +845,14 @@ int launch_fast_tree(bamcl_pf* pf, TreeOut* out, int n)
       BAMCL_CUDA_OK(cudaStreamWaitEvent(pf->bucket_stream[i], pf->ev_bucket_fork, 0));
       ctx->stream = pf->bucket_stream[i];
       if (i == 0)
-        BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_L, FAST_CAP_M, 1024, M_TOP>), bucket_blocks, 1024, per * FAST_CAP_L, fa);
+        BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_L, 2, 1024, true>), cap_l, 1024, per * FAST_CAP_L, fa);
       else
-        BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_S, 0, 256, M_TOP>), bucket_blocks, 256, per * FAST_CAP_S, fa);
+        BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_S, 0, 256, true>), cap_s, 256, per * FAST_CAP_S, fa);
       BAMCL_CUDA_OK(cudaEventRecord(pf->ev_bucket_join[i], pf->bucket_stream[i]));
     }
   }
-  BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_M, FAST_CAP_S, 512, M_TOP>), bucket_blocks, 512, per * FAST_CAP_M, fa);
+  BAMCL_LAUNCH(ctx, k_fast_bucket_warp, (nb2 + FAST_W_WARPS - 1) / FAST_W_WARPS, FAST_W_WARPS * 32, 0, fa);
+  BAMCL_LAUNCH(ctx, (k_fast_bucket<FAST_CAP_M, 1, 512, true>), cap_m, 512, per * FAST_CAP_M, fa);
   for (int i = 0; i < 2; i++)
     BAMCL_CUDA_OK(cudaStreamWaitEvent(here, pf->ev_bucket_join[i], 0));
   return BAMCL_OK;
@@ -830,7 +893,7 @@ static int fit_box(bamcl_pf* pf, SampleSet& set, long off, int n, double cx, dou
   pf->box_valid = true;
   pf->box_dense = false;
   pf->box_cells = 0;
-  static const bool force_hash = getenv("BAMCL_TREE_HASH") != nullptr;  // tests: exercise the hashed path
+  const bool force_hash = getenv("BAMCL_TREE_HASH") != nullptr;  // tests: exercise the hashed path
   if (force_hash && pf_ranks(pf) == 1)
     return BAMCL_OK;
   long cells = 1;
@@ -917,7 +980,6 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
   BAMCL_TRY(pf->t_cid.reserve(sizeof(int) * cap_n));
   BAMCL_TRY(pf->t_nfirst.reserve(sizeof(int) * cap_n));
   BAMCL_TRY(pf->t_scan.reserve(sizeof(int) * scan_scratch_ints((long)cap_n)));
-  BAMCL_TRY(pf->t_fast.reserve(sizeof(int) * (3 * M_TOP_LARGE + 2 * (2 * M_TOP_LARGE + 1))));
   BAMCL_TRY(pf->t_out.reserve(sizeof(TreeOut)));
   BAMCL_TRY(pf->t_hout.reserve(sizeof(TreeOut)));
   BAMCL_TRY(pf->t_root.reserve(sizeof(int) * cap_n));
@@ -972,8 +1034,10 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       if (n > 0)
         BAMCL_LAUNCH(ctx, k_grid_first, blocks_n, 256, 0, set.x.as<double>() + off, set.y.as<double>() + off,
                      set.th.as<double>() + off, n, off, cx, cy, ct, box, pf->g_first.as<int>(), pf->t_slot.as<int>(), out);
+      pf_mark(pf, "grid_first");
       if (G > 1)  // global first occurrence of every bin
         BAMCL_TRY(comm_all_reduce(pf->comm, pf->g_first.p, (size_t)cells, CT_I32, CO_MIN));
+      pf_mark(pf, "allreduce_grid");
       const unsigned cell_blocks = (unsigned)((cells + 255) / 256);
       BAMCL_LAUNCH(ctx, k_grid_mark, cell_blocks, 256, 0, pf->g_first.as<int>(), cells, n_set, pf->t_bits.as<unsigned>());
       BAMCL_LAUNCH(ctx, k_popc, (words + 255) / 256, 256, 0, pf->t_bits.as<unsigned>(), words, pf->t_bpre.as<int>());
@@ -1002,6 +1066,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
                    pf->t_hkeys.as<unsigned long long>(), pf->t_hnode.as<int>(), pf->t_nkey.as<unsigned long long>(),
                    pf->t_nfirst.as<int>(), pf->t_parent.as<int>(), n);
     }
+    pf_mark(pf, "nodes");
     // ---- fork: the cluster chain (needs only the nodes and the bin index) goes to the auxiliary stream and overlaps the
     // leaf-count chain on the main stream; both join before anything is exchanged or copied back
     cudaStream_t main_stream = ctx->stream;
@@ -1023,7 +1088,21 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       // root carried through the unions (the ECL-CC shape) -- resample 1.14 ms against 0.89 ms at 1M samples / 243k
       // bins: 13x fewer threads leave the forest walks latency-bound.)
       const unsigned cc_blocks = (unsigned)((threads + 255) / 256);
-      if (dense)
+      // (Measured and dropped as the default: one thread per grid cell with the 13 neighbours as coalesced loads,
+      // k_cc_union_cells. Neighbouring cells belong to the same component and all race for the same root at once:
+      // 0.77 ms against 0.26 ms for node order at 1M samples / 780k bins. Kept behind a switch for sparse experiments.)
+      static const bool cc_cells = getenv("BAMCL_CC_CELLS") != nullptr;
+      if (dense && cc_cells)
+      {
+        const unsigned cell_blocks = (unsigned)((pf->box_cells + 255) / 256);
+        if (cc_volatile)
+          BAMCL_LAUNCH(ctx, k_cc_union_cells<false>, cell_blocks, 256, 0, box, pf->g_node.as<int>(), pf->box_cells,
+                       pf->t_parent.as<int>());
+        else
+          BAMCL_LAUNCH(ctx, k_cc_union_cells<true>, cell_blocks, 256, 0, box, pf->g_node.as<int>(), pf->box_cells,
+                       pf->t_parent.as<int>());
+      }
+      else if (dense)
       {
         if (cc_volatile)
           BAMCL_LAUNCH(ctx, k_cc_union_dense<false>, cc_blocks, 256, 0, out, pf->t_nkey.as<unsigned long long>(), box,
@@ -1077,14 +1156,12 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
     };
     if (!general_only)
     {
-      if (k_max > 1500000)
-        BAMCL_TRY((launch_fast_tree<M_TOP_LARGE>(pf, out, k_max)));
-      else
-        BAMCL_TRY((launch_fast_tree<M_TOP_SMALL>(pf, out, k_max)));
+      BAMCL_TRY(launch_fast_tree(pf, out, k_max));
     }
     else
       BAMCL_TRY(launch_general());
     BAMCL_CUDA_OK(cudaStreamWaitEvent(main_stream, pf->ev_join, 0));
+    pf_mark(pf, "tree||clusters");
     // ---- joined: cluster rows + set sums over all ranks, then the convergence count against the global mean
     if (G > 1)
       BAMCL_TRY(comm_all_reduce(pf->comm, pf->t_sums.p, ROW * pf->t_cluster_cap + 12, CT_F64, CO_SUM));
@@ -1103,6 +1180,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
                  (int)pf->t_cluster_cap, set.cluster_stats.as<double>());
     BAMCL_CUDA_OK(cudaMemcpyAsync(h_out, out, sizeof(TreeOut), cudaMemcpyDeviceToHost, ctx->stream));
     BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    pf_mark(pf, "sums+counts");
     if (h_out->err & 1)
       return set_error(BAMCL_E_UNSUPPORTED, "a pose is outside the kd-tree key range (|x|,|y| < 5e5 m, |theta| < 3.6e5 rad)");
     if (h_out->err & 4)

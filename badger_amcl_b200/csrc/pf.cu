@@ -1,7 +1,12 @@
 // ParticleFilter device object: sample-set storage, host<->device sample exchange, weight total and
 // normalisation, and the update entry points. Reference: src/amcl/pf/particle_filter.cpp:38-98, 223-267.
+#include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <string>
+#include <utility>
+#include <vector>
 
 #include "pf.cuh"
 
@@ -120,8 +125,54 @@ __global__ void k_normalise_ranks(double* __restrict__ w, int n, const double* _
 }
 }  // namespace
 
+namespace
+{
+struct Marks
+{
+  std::vector<std::pair<std::string, double>> rows;
+  std::chrono::steady_clock::time_point last;
+  bool started = false;
+};
+thread_local Marks g_marks;
+bool marks_on()
+{
+  static const bool on = getenv("BAMCL_SHARD_TIMING") != nullptr;
+  return on;
+}
+}  // namespace
+
 namespace bamcl
 {
+void pf_mark(bamcl_pf* pf, const char* phase)
+{
+  if (!marks_on())
+    return;
+  cudaStreamSynchronize(pf->ctx->stream);
+  const auto now = std::chrono::steady_clock::now();
+  if (g_marks.started && phase)
+    g_marks.rows.emplace_back(phase, std::chrono::duration<double, std::milli>(now - g_marks.last).count());
+  g_marks.started = true;
+  g_marks.last = std::chrono::steady_clock::now();
+}
+void pf_mark_report(bamcl_pf* pf)
+{
+  if (!marks_on())
+    return;
+  if (pf_rank(pf) == 0)
+  {
+    std::string line = "[shard timing ms]";
+    char buf[96];
+    for (auto& r : g_marks.rows)
+    {
+      snprintf(buf, sizeof(buf), " %s %.3f", r.first.c_str(), r.second);
+      line += buf;
+    }
+    fprintf(stderr, "%s\n", line.c_str());
+  }
+  g_marks.rows.clear();
+  g_marks.started = false;
+}
+
 int pf_ensure_streams(bamcl_pf* pf)
 {
   if (pf->aux_stream)

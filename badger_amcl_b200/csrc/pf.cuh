@@ -169,6 +169,9 @@ inline void pf_apply_shard_window(bamcl_pf* pf)
 
 namespace bamcl
 {
+// phase timing of the distributed resample (BAMCL_SHARD_TIMING=1): synchronises at every mark, so only for diagnosis
+void pf_mark(bamcl_pf* pf, const char* phase);
+void pf_mark_report(bamcl_pf* pf);
 int pf_reduce_total(bamcl_pf* pf, double* d_total);  // deterministic sum of the current set's weights -> device scalar
 int pf_read_scalar(bamcl_pf* pf, int slot, double* out);  // device scalar slot -> host (synchronises)
 int pf_normalise_by_device_total(bamcl_pf* pf);           // w /= scalars[0] (or 1/n), particle_filter.cpp:237-266

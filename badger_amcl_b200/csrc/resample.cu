@@ -1538,7 +1538,9 @@ int bamcl_pf_shard_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamc
 
   // ---- exact CDF of every window and the value at every rank boundary (:280-285)
   std::vector<double> bounds(G + 1, 0.0);
+  pf_mark(pf, nullptr);
   BAMCL_TRY(build_cdf_checked(pf, bounds.data()));
+  pf_mark(pf, "cdf+bounds");
 
   // ---- who sources which output slot, and who owns it (host arithmetic, identical on every rank)
   std::vector<long> runs((size_t)3 * (4 * G + 2 * MAX_SEGS + 16));
@@ -1602,6 +1604,7 @@ int bamcl_pf_shard_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamc
     }
   }
 
+  pf_mark(pf, "plan+select");
   // ---- the exchange: selected rows -> owners of the output slots (:326-351 writes set_b in slot order)
   double* bx = set_b.x.as<double>();
   double* by = set_b.y.as<double>();
@@ -1636,6 +1639,7 @@ int bamcl_pf_shard_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamc
   if (G > 1)
     BAMCL_TRY(comm_exchange(comm, sends.data(), (int)sends.size(), recvs.data(), (int)recvs.size()));
 
+  pf_mark(pf, "exchange");
   // ---- this rank's output window: weights 1/n (:343-346, 457-462) and the random poses among its slots (:316-324)
   const long ob = shard_begin(new_count, G, me), oe = shard_begin(new_count, G, me + 1);
   if (oe > ob)
@@ -1674,6 +1678,7 @@ int bamcl_pf_shard_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamc
   res->random_poses_used = n_rand;
   res->status_flags = flags & 1;
   res->drand48_state = state_after;
+  pf_mark_report(pf);
   return BAMCL_OK;
 }
 

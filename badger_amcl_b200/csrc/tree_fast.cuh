@@ -2,25 +2,36 @@
 // kdtree.cu (shares TreeOut / pack_key / unpack_key / NONE).
 //
 // The level-synchronous grid kernel (k_tree_build) needs one grid-wide barrier pair per tree level (~50-60
-// levels for 1M bins). This path removes the grid barriers:
-//   1. one CTA builds the tree of the first m <= M_TOP keys in shared memory. Because the reference's tree only
-//      ever grows downwards, that is exactly the top of the final tree: every pivot it fixes and every child
-//      it links is final;
-//   2. every later key walks that top tree read-only (no synchronisation) until it falls off at an empty child
-//      slot (u, side), or reaches a node u whose pivot is still unset: its bucket;
-//   3. buckets are grouped (count, scan, scatter);
-//   4. one CTA per bucket sorts its keys by creation index and grows the bucket's subtree in shared memory
-//      with the same level-synchronous rule, using __syncthreads only. Subtrees of different buckets never
-//      interact: everything routed into a slot stays below it.
-// leaf count = childless nodes over all bucket subtrees + top nodes with an unset pivot and an empty bucket.
+// levels for 1M bins). This path has no grid barriers. Because the reference's tree only ever grows downwards, the
+// tree of the first m keys is exactly the top of the final tree: every pivot it fixes and every child it links is
+// final. So the tree is grown from the top in three steps, each an order of magnitude wider than the one before:
+//   A. one CTA builds the tree of the first M1 keys in shared memory and writes it to the global node arrays;
+//   B. keys [M1, M2) walk that top tree read-only to the empty child slot (or childless node) they fall off at --
+//      their bucket; one CTA per bucket grows the bucket's subtree in shared memory and WRITES it to the node arrays,
+//      which now hold the tree of the first M2 keys (M2 ~ K / 32, so the last step's buckets stay small);
+//   C. all remaining keys walk the M2-key tree to their bucket; one warp (<= 64 keys) or CTA per bucket grows the
+//      subtree in shared memory and only COUNTS its childless nodes. Subtrees of different buckets never interact:
+//      everything routed into a slot stays below it. On a distributed filter the ranks split the buckets of step C.
+// leaf count = childless nodes over all step-C subtrees + top nodes with an unset pivot and an empty bucket.
 // A bucket larger than FAST_CAP_L (adversarial insertion orders, e.g. spatially sorted keys) makes the fast path
-// give up (TreeOut::fast_ok stays 0) and k_tree_build does the work instead.
+// give up (TreeOut::fast_ok = 0) and k_tree_build does the work instead.
 #pragma once
 
-// keys in the top tree: the largest bucket holds about ln(M_TOP) / M_TOP of the keys, so sets beyond ~1.5M samples
-// (sharded filter: every rank builds the global tree) take the large top tree to stay inside FAST_CAP_L.
-constexpr int M_TOP_SMALL = 2048, M_TOP_LARGE = 8192;
-constexpr int FAST_CAP_S = 512, FAST_CAP_M = 2048, FAST_CAP_L = 6144;
+constexpr int M_TOP1 = 2048;         // keys of step A
+constexpr int M_TOP2_MAX = 1 << 18;  // most keys the node arrays of steps A + B hold
+constexpr int FAST_CAP_W = 64, FAST_CAP_S = 512, FAST_CAP_M = 2048, FAST_CAP_L = 6144;
+constexpr int FAST_BYTES_PER_KEY = 28;  // shared memory per key in the bucket kernels
+
+// keys in the written-out top tree for a tree of K keys (same arithmetic on host and device, monotone in K)
+__host__ __device__ inline int top2_size(int K)
+{
+  if (K <= 16 * M_TOP1)
+    return M_TOP1;  // small trees: the step-A tree is the whole top
+  int m = M_TOP1;
+  while (m < K / 32 && m < M_TOP2_MAX)
+    m <<= 1;
+  return m;
+}
 
 __device__ __forceinline__ int pivot_dim(unsigned long long ku, unsigned long long kf)
 {
@@ -46,22 +57,28 @@ __device__ __forceinline__ int key_dim(unsigned long long k, int d)
 }
 
 // Level-synchronous growth of the tree over key[0..n) (creation order, element 0 = root) in shared memory.
-// cur/child/first_at are int[n], int[2n], int[n]. Returns the number of levels. All threads of the CTA call it.
+// cur/child/first_at are int[n], int[2n], int[n]. Returns the number of levels. WARP = the caller is one warp (lanes
+// stride the keys, warp barriers); else all threads of the CTA call it.
+template <bool WARP>
 __device__ int smem_tree(const unsigned long long* key, int n, int* cur, int* child, int* first_at)
 {
-  for (int v = threadIdx.x; v < n; v += blockDim.x)
+  const int t0 = WARP ? (threadIdx.x & 31) : threadIdx.x, step = WARP ? 32 : blockDim.x;
+  for (int v = t0; v < n; v += step)
   {
     child[2 * v] = child[2 * v + 1] = NONE;
     first_at[v] = (v == 0 && n > 1) ? 1 : NONE;
     cur[v] = v == 0 ? -1 : 0;
   }
-  __syncthreads();
+  if (WARP)
+    __syncwarp();
+  else
+    __syncthreads();
   int level = 0;
   if (n < 2)
     return 0;
   for (;;)
   {
-    for (int v = threadIdx.x; v < n; v += blockDim.x)
+    for (int v = t0; v < n; v += step)
     {
       const int u = cur[v];
       if (u < 0)
@@ -72,9 +89,12 @@ __device__ int smem_tree(const unsigned long long* key, int n, int* cur, int* ch
       cur[v] = u | (sd << 30);
       atomicMin(&child[2 * u + sd], v);
     }
-    __syncthreads();
+    if (WARP)
+      __syncwarp();
+    else
+      __syncthreads();
     int any = 0;
-    for (int v = threadIdx.x; v < n; v += blockDim.x)
+    for (int v = t0; v < n; v += step)
     {
       const int cu = cur[v];
       if (cu < 0)
@@ -91,179 +111,178 @@ __device__ int smem_tree(const unsigned long long* key, int n, int* cur, int* ch
       }
     }
     level++;
-    if (!__syncthreads_or(any))
+    if (WARP)
+    {
+      __syncwarp();
+      if (!__any_sync(0xffffffffu, any))
+        break;
+    }
+    else if (!__syncthreads_or(any))
       break;
   }
   return level;
+}
+
+// A written-out node: one 16-byte load per level of the walk. c0 carries the pivot code in its top two bits
+// (0 = unset: the node is still childless; 1..3 = dimension 0..2); child ids are 30 bits, TOP_NONE = empty slot.
+struct __align__(16) TopNode
+{
+  unsigned long long key;
+  unsigned c0, c1;
+};
+constexpr unsigned TOP_NONE = 0x3FFFFFFFu;
+__device__ __forceinline__ int top_pivot(unsigned c0) { return (int)(c0 >> 30) - 1; }  // -1 = unset
+__device__ __forceinline__ unsigned top_child(const TopNode& nd, int sd) { return (sd ? nd.c1 : nd.c0) & TOP_NONE; }
+__device__ __forceinline__ TopNode top_make(unsigned long long key, int pivot, int child0, int child1)
+{
+  TopNode nd;
+  nd.key = key;
+  nd.c0 = (child0 == NONE ? TOP_NONE : (unsigned)child0) | ((unsigned)(pivot + 1) << 30);
+  nd.c1 = child1 == NONE ? TOP_NONE : (unsigned)child1;
+  return nd;
 }
 
 struct FastArgs
 {
   TreeOut* out;
   const unsigned long long* nkey;  // [K] creation order
-  int* tpivot;                     // [M_TOP] pivot dimension of a top node, -1 while unset
-  int* tchild;                     // [2 * M_TOP] children inside the top tree (NONE = empty slot)
-  int* bcount;                     // [N_BUCKETS + 1]
-  int* boff;                       // [N_BUCKETS + 1]
-  int* bslot;                      // [K] bucket of every key >= m
+  TopNode* top;                    // [M2] the written-out tree
+  int* bcount;                     // [2 * M2 + 1] keys per bucket; scanned in place into offsets
+  int* lists;                      // bucket ids by size class: S at 0, M at list_m, L at list_l; counts in cls[0..2]
+  int* cls;
+  int list_m, list_l;
+  int* bslot;                      // [K] bucket of every key routed in this step
   int* bpos;                       // [K] arrival position inside the bucket
   int* bids;                       // [K] keys grouped by bucket
-  int part_rank, part_n;           // distributed filter: this rank grows the subtrees of buckets b with (b >> 1) % part_n == part_rank
+  int part_rank, part_n;           // distributed filter: this rank counts the buckets under nodes u, u % part_n == part_rank
 };
 
-// ---- 1. top tree (one CTA)
-template <int M_TOP>
-__global__ void __launch_bounds__(1024) k_fast_top(const FastArgs a)
+// keys [lo, hi) of the step and the size m of the tree they walk: step B = [M1, M2) over M1, step C = [M2, K) over M2
+__device__ __forceinline__ void step_range(int K, bool step_c, int* lo, int* hi, int* m)
 {
-  constexpr int N_BUCKETS = 2 * M_TOP;
-  extern __shared__ __align__(16) unsigned char s_raw[];
-  unsigned long long* key = reinterpret_cast<unsigned long long*>(s_raw);
-  int* cur = reinterpret_cast<int*>(key + M_TOP);
-  int* child = cur + M_TOP;
-  int* first_at = child + 2 * M_TOP;
-  const int K = a.out->K;
-  const int m = min(K, M_TOP);
-  for (int v = threadIdx.x; v < m; v += blockDim.x)
-    key[v] = a.nkey[v];
-  for (int b = threadIdx.x; b <= N_BUCKETS; b += blockDim.x)
-    a.bcount[b] = 0;
-  __syncthreads();
-  const int levels = smem_tree(key, m, cur, child, first_at);
-  for (int v = threadIdx.x; v < M_TOP; v += blockDim.x)
+  const int m2 = min(K, top2_size(K));
+  if (step_c)
   {
-    int p = -1, c0 = NONE, c1 = NONE;
-    if (v < m)
-    {
-      c0 = child[2 * v];
-      c1 = child[2 * v + 1];
-      if (first_at[v] != NONE)
-        p = pivot_dim(key[v], key[first_at[v]]);
-    }
-    a.tpivot[v] = p;
-    a.tchild[2 * v] = c0;
-    a.tchild[2 * v + 1] = c1;
+    *lo = m2;
+    *hi = K;
+    *m = m2;
   }
-  if (threadIdx.x == 0)
-    a.out->levels = levels;
+  else
+  {
+    *lo = min(K, M_TOP1);
+    *hi = m2;
+    *m = min(K, M_TOP1);
+  }
 }
 
-// ---- 2. every later key finds its bucket
-template <int M_TOP>
+// ---- A. top tree of the first M_TOP1 keys (one CTA), written to the node arrays
+__global__ void __launch_bounds__(1024) k_fast_top(const FastArgs a)
+{
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  unsigned long long* key = reinterpret_cast<unsigned long long*>(s_raw);
+  int* cur = reinterpret_cast<int*>(key + M_TOP1);
+  int* child = cur + M_TOP1;
+  int* first_at = child + 2 * M_TOP1;
+  const int K = a.out->K;
+  const int m = min(K, M_TOP1);
+  for (int v = threadIdx.x; v < m; v += blockDim.x)
+    key[v] = a.nkey[v];
+  __syncthreads();
+  const int levels = smem_tree<false>(key, m, cur, child, first_at);
+  for (int v = threadIdx.x; v < m; v += blockDim.x)
+    a.top[v] = top_make(key[v], first_at[v] != NONE ? pivot_dim(key[v], key[first_at[v]]) : -1, child[2 * v], child[2 * v + 1]);
+  if (threadIdx.x == 0)
+  {
+    a.out->levels = levels;
+    a.out->fast_ok = 1;
+  }
+}
+
+// ---- every key of the step finds its bucket: a read-only walk down the written-out tree (L1 / L2 resident)
+template <bool STEP_C>
 __global__ void __launch_bounds__(256) k_fast_descend(const FastArgs a)
 {
-  extern __shared__ __align__(16) unsigned char s_raw[];  // 17 * M_TOP bytes
-  unsigned long long* s_key = reinterpret_cast<unsigned long long*>(s_raw);
-  int* s_child = reinterpret_cast<int*>(s_key + M_TOP);
-  signed char* s_pivot = reinterpret_cast<signed char*>(s_child + 2 * M_TOP);
-  const int K = a.out->K;
-  const int m = min(K, M_TOP);
-  if (K <= M_TOP)
-    return;
-  for (int v = threadIdx.x; v < m; v += blockDim.x)
-  {
-    s_key[v] = a.nkey[v];
-    s_pivot[v] = (signed char)a.tpivot[v];
-    s_child[2 * v] = a.tchild[2 * v];
-    s_child[2 * v + 1] = a.tchild[2 * v + 1];
-  }
-  __syncthreads();
-  for (int v = M_TOP + blockIdx.x * blockDim.x + threadIdx.x; v < K; v += gridDim.x * blockDim.x)
+  int lo, hi, m;
+  step_range(a.out->K, STEP_C, &lo, &hi, &m);
+  for (int v = lo + blockIdx.x * blockDim.x + threadIdx.x; v < hi; v += gridDim.x * blockDim.x)
   {
     const unsigned long long kv = a.nkey[v];
     int u = 0, b;
     for (;;)
     {
-      const int p = s_pivot[u];
+      const uint4 raw = __ldg(reinterpret_cast<const uint4*>(&a.top[u]));
+      const int p = top_pivot(raw.z);
       if (p < 0)
       {
-        b = 2 * u;  // a top node that is still childless: the whole bucket hangs under it
+        b = 2 * u;  // a node that is still childless: the whole bucket hangs under it
         break;
       }
-      const int sd = key_dim(kv, p) > key_dim(s_key[u], p) ? 1 : 0;
-      const int c = s_child[2 * u + sd];
-      if (c == NONE)
+      const unsigned long long ku = (unsigned long long)raw.x | ((unsigned long long)raw.y << 32);
+      const int sd = key_dim(kv, p) > key_dim(ku, p) ? 1 : 0;
+      const unsigned c = (sd ? raw.w : raw.z) & TOP_NONE;
+      if (c == TOP_NONE)
       {
         b = 2 * u + sd;
         break;
       }
-      u = c;
+      u = (int)c;
     }
     a.bslot[v] = b;
     a.bpos[v] = atomicAdd(&a.bcount[b], 1);
   }
 }
 
-// ---- 3. bucket offsets (one CTA) and the grouping scatter
-template <int M_TOP>
-__global__ void __launch_bounds__(1024) k_fast_offsets(const FastArgs a)
-{
-  constexpr int N_BUCKETS = 2 * M_TOP;
-  __shared__ int s_warp[32];
-  __shared__ int s_over;
-  constexpr int PER = N_BUCKETS / 1024;
-  if (threadIdx.x == 0)
-    s_over = 0;
-  __syncthreads();
-  int c[PER], sum = 0;
-#pragma unroll
-  for (int q = 0; q < PER; q++)
-  {
-    c[q] = a.bcount[threadIdx.x * PER + q];
-    sum += c[q];
-    if (c[q] + 1 > FAST_CAP_L)
-      s_over = 1;
-  }
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int inc = sum;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1)
-  {
-    const int t = __shfl_up_sync(0xffffffffu, inc, o);
-    if (lane >= o)
-      inc += t;
-  }
-  if (lane == 31)
-    s_warp[warp] = inc;
-  __syncthreads();
-  if (warp == 0)
-  {
-    int w = s_warp[lane], winc = w;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1)
-    {
-      const int t = __shfl_up_sync(0xffffffffu, winc, o);
-      if (lane >= o)
-        winc += t;
-    }
-    s_warp[lane] = winc - w;
-  }
-  __syncthreads();
-  int run = s_warp[warp] + inc - sum;
-#pragma unroll
-  for (int q = 0; q < PER; q++)
-  {
-    a.boff[threadIdx.x * PER + q] = run;
-    run += c[q];
-  }
-  if (threadIdx.x == 1023)
-  {
-    a.boff[N_BUCKETS] = run;
-    a.out->fast_ok = s_over ? 0 : 1;
-  }
-}
-
-template <int M_TOP>
+template <bool STEP_C>
 __global__ void __launch_bounds__(256) k_fast_scatter(const FastArgs a)
 {
-  const int K = a.out->K;
-  if (!a.out->fast_ok)
-    return;
-  for (int v = M_TOP + blockIdx.x * blockDim.x + threadIdx.x; v < K; v += gridDim.x * blockDim.x)
-    a.bids[a.boff[a.bslot[v]] + a.bpos[v]] = v;
+  int lo, hi, m;
+  step_range(a.out->K, STEP_C, &lo, &hi, &m);
+  for (int v = lo + blockIdx.x * blockDim.x + threadIdx.x; v < hi; v += gridDim.x * blockDim.x)
+    a.bids[a.bcount[a.bslot[v]] + a.bpos[v]] = v;  // bcount holds the exclusive offsets by now
 }
 
-// ---- 4. one CTA per bucket: sort by creation index, grow the subtree, count its childless nodes
-template <int CAP, int CAP_BELOW, int THREADS, int M_TOP>
+// which keys make up bucket b of a tree of m written-out nodes: returns n (0: no bucket hangs here) and (off, cnt,
+// unset). Only called between the kernels that write the tree.
+__device__ __forceinline__ int bucket_shape(const FastArgs& a, int b, int m, int* off, int* cnt, bool* unset)
+{
+  const int u = b >> 1, sd = b & 1;
+  if (u >= m)
+    return 0;
+  const TopNode nd = a.top[u];
+  *unset = top_pivot(nd.c0) < 0;
+  if (*unset ? sd == 1 : top_child(nd, sd) != TOP_NONE)
+    return 0;
+  *off = a.bcount[b];
+  *cnt = a.bcount[b + 1] - *off;
+  return *cnt + (*unset ? 1 : 0);
+}
+
+// ---- buckets by size class (a CTA of the right size per bucket, and no CTA at all for the many empty slots)
+template <bool STEP_C>
+__global__ void __launch_bounds__(256) k_fast_classify(const FastArgs a)
+{
+  int lo, hi, m;
+  step_range(a.out->K, STEP_C, &lo, &hi, &m);
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= 2 * m)
+    return;
+  if (STEP_C && (b >> 1) % a.part_n != a.part_rank)
+    return;
+  int off = 0, cnt = 0;
+  bool unset = false;
+  const int n = bucket_shape(a, b, m, &off, &cnt, &unset);
+  if (n > FAST_CAP_L)
+    a.out->fast_ok = 0;  // outgrew shared memory: the grid-synchronous build takes over
+  else if (n > FAST_CAP_M)
+    a.lists[a.list_l + atomicAdd(&a.cls[2], 1)] = b;
+  else if (n > FAST_CAP_S)
+    a.lists[a.list_m + atomicAdd(&a.cls[1], 1)] = b;
+  else if (STEP_C ? n > FAST_CAP_W : cnt > 0)
+    a.lists[atomicAdd(&a.cls[0], 1)] = b;
+}
+
+// ---- one CTA per listed bucket: sort by creation index, grow the subtree; step B writes it out, step C counts its leaves
+template <int CAP, int CLS, int THREADS, bool STEP_C>
 __global__ void __launch_bounds__(THREADS) k_fast_bucket(const FastArgs a)
 {
   extern __shared__ __align__(16) unsigned char s_raw[];
@@ -275,25 +294,16 @@ __global__ void __launch_bounds__(THREADS) k_fast_bucket(const FastArgs a)
   __shared__ int s_leaves;
   if (!a.out->fast_ok)
     return;
-  const int K = a.out->K;
-  const int m = min(K, M_TOP);
-  const int b = blockIdx.x, u = b >> 1, sd = b & 1;
-  if (u >= m || u % a.part_n != a.part_rank)
+  int lo, hi, m;
+  step_range(a.out->K, STEP_C, &lo, &hi, &m);
+  if ((int)blockIdx.x >= a.cls[CLS])
     return;
-  const bool unset = a.tpivot[u] < 0;
-  if (unset ? sd == 1 : a.tchild[b] != NONE)
-    return;  // no bucket hangs here
-  const int off = a.boff[b], cnt = a.boff[b + 1] - off;
-  const int n = cnt + (unset ? 1 : 0);
-  if (n <= CAP_BELOW || n > CAP)
-    return;  // another size class handles it
-  if (n == 1)
-  {
-    // a childless top node with an empty bucket (n == 1 && unset), or a single key in a slot: one leaf
-    if (threadIdx.x == 0)
-      atomicAdd(&a.out->leaf, 1);
-    return;
-  }
+  const int b = a.lists[(CLS == 0 ? 0 : CLS == 1 ? a.list_m : a.list_l) + blockIdx.x], u = b >> 1;
+  int off = 0, cnt = 0;
+  bool unset = false;
+  const int n = bucket_shape(a, b, m, &off, &cnt, &unset);
+  if (n > CAP || n < 1)
+    return;  // (cannot happen: the class lists are built from the same shapes)
   int np2 = 1;
   while (np2 < n)
     np2 <<= 1;
@@ -332,7 +342,26 @@ __global__ void __launch_bounds__(THREADS) k_fast_bucket(const FastArgs a)
   for (int i = threadIdx.x; i < n; i += THREADS)
     key[i] = a.nkey[ids[i]];
   __syncthreads();
-  const int levels = smem_tree(key, n, cur, child, first_at);
+  const int levels = smem_tree<false>(key, n, cur, child, first_at);
+  if (!STEP_C)
+  {
+    // the subtree joins the written-out tree: node ids[j] gets its pivot and children, the slot gets its root
+    for (int j = threadIdx.x; j < n; j += THREADS)
+      a.top[ids[j]] = top_make(key[j], first_at[j] != NONE ? pivot_dim(key[j], key[first_at[j]]) : -1,
+                               child[2 * j] == NONE ? NONE : ids[child[2 * j]],
+                               child[2 * j + 1] == NONE ? NONE : ids[child[2 * j + 1]]);
+    if (!unset && threadIdx.x == 0)
+    {
+      // the parent's pivot is final; the two slots of a node are different words, each written by its own bucket's CTA
+      if (b & 1)
+        a.top[u].c1 = (unsigned)ids[0];
+      else
+        a.top[u].c0 = (a.top[u].c0 & ~TOP_NONE) | (unsigned)ids[0];
+    }
+    if (threadIdx.x == 0)
+      atomicMax(&a.out->levels, levels);
+    return;
+  }
   int leaves = 0;
   for (int v = threadIdx.x; v < n; v += THREADS)
     leaves += (child[2 * v] == NONE && child[2 * v + 1] == NONE) ? 1 : 0;
@@ -343,6 +372,70 @@ __global__ void __launch_bounds__(THREADS) k_fast_bucket(const FastArgs a)
   if (threadIdx.x == 0)
   {
     atomicAdd(&a.out->leaf, s_leaves);
+    atomicMax(&a.out->bucket_levels, levels);
+  }
+}
+
+// ---- step C, buckets of at most FAST_CAP_W keys: one WARP per bucket, eight buckets per CTA
+constexpr int FAST_W_WARPS = 8;
+__global__ void __launch_bounds__(FAST_W_WARPS * 32) k_fast_bucket_warp(const FastArgs a)
+{
+  __shared__ unsigned long long s_key[FAST_W_WARPS][FAST_CAP_W];
+  __shared__ int s_cur[FAST_W_WARPS][FAST_CAP_W], s_first[FAST_W_WARPS][FAST_CAP_W];
+  __shared__ int s_child[FAST_W_WARPS][2 * FAST_CAP_W];
+  if (!a.out->fast_ok)
+    return;
+  int lo, hi, m;
+  step_range(a.out->K, true, &lo, &hi, &m);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * FAST_W_WARPS + warp, u = b >> 1;
+  if (u % a.part_n != a.part_rank)
+    return;
+  int off = 0, cnt = 0;
+  bool unset = false;
+  const int n = bucket_shape(a, b, m, &off, &cnt, &unset);
+  if (n == 0 || n > FAST_CAP_W)
+    return;
+  if (n == 1)
+  {
+    if (lane == 0)
+      atomicAdd(&a.out->leaf, 1);
+    return;
+  }
+  unsigned long long* key = s_key[warp];
+  // rank sort of the (distinct) creation indices, two per lane
+  int mine[2];
+#pragma unroll
+  for (int q = 0; q < 2; q++)
+  {
+    const int i = lane + 32 * q;
+    int id = INT_MAX;
+    if (i < n)
+      id = unset ? (i == 0 ? u : a.bids[off + i - 1]) : a.bids[off + i];
+    mine[q] = id;
+    s_cur[warp][i] = id;
+  }
+  __syncwarp();
+#pragma unroll
+  for (int q = 0; q < 2; q++)
+  {
+    if (lane + 32 * q < n)
+    {
+      int r = 0;
+      for (int j = 0; j < n; j++)
+        r += s_cur[warp][j] < mine[q] ? 1 : 0;
+      key[r] = a.nkey[mine[q]];
+    }
+  }
+  __syncwarp();
+  const int levels = smem_tree<true>(key, n, s_cur[warp], s_child[warp], s_first[warp]);
+  int leaves = 0;
+  for (int v = lane; v < n; v += 32)
+    leaves += (s_child[warp][2 * v] == NONE && s_child[warp][2 * v + 1] == NONE) ? 1 : 0;
+  leaves = warp_sum_i(leaves);
+  if (lane == 0)
+  {
+    atomicAdd(&a.out->leaf, leaves);
     atomicMax(&a.out->bucket_levels, levels);
   }
 }

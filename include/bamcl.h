@@ -52,6 +52,11 @@ long bamcl_ctx_launch_count(bamcl_ctx* ctx);
 /* write a buffer larger than L2 (bench hygiene between timed iterations) */
 int bamcl_ctx_flush_l2(bamcl_ctx* ctx);
 
+/* measurement aid ("L2-resident random-gather peak"): n_gathers random 2-byte loads over a table of
+ * table_bytes, 16 independent loads in flight per thread -- the likelihood-field scorer's access pattern without its
+ * arithmetic. ms_out = device time for n_gathers (best of three warm passes). */
+int bamcl_bench_gather(bamcl_ctx* ctx, size_t table_bytes, long n_gathers, float* ms_out);
+
 /* page-locked host memory for the caller's sample / scan buffers (the host mirror of PFSampleSet::samples,
  * particle_filter.h:72, lives in such a buffer so uploads and downloads run at full PCIe rate) */
 int bamcl_host_alloc(size_t bytes, void** out);

@@ -205,6 +205,21 @@ def test_kdtree_leaf_count_paths(env, n, order):
     pf.close()
 
 
+@pytest.mark.parametrize("n", [300, 5000, 150000])
+def test_kdtree_hashed_bins_path(env, n, monkeypatch):
+    """a world too large for the dense bin grid falls back to hashed bins (BAMCL_TREE_HASH forces that path here)"""
+    monkeypatch.setenv("BAMCL_TREE_HASH", "1")
+    O, cabi = env["O"], env["cabi"]
+    poses = synth.uniform_free_poses(env["cells"], RES, n, seed=13)
+    port = O.PortPF(1, n)
+    port.init_with_poses(poses)
+    pf = cabi.ParticleFilter(env["ctx"], 1, n)
+    r = pf.init_with_poses(poses)
+    assert (r.leaf_count, r.node_count, r.cluster_count) == (port.leaf_count(), port.node_count(), port.cluster_count())
+    assert np.array_equal(pf.sample_clusters(), port.sample_clusters())
+    pf.close()
+
+
 def test_kdtree_leaf_count_large_top_tree(env):
     """sets beyond 1.5M samples (a sharded filter's global set) use the 8192-key top tree of tree_fast.cuh"""
     O, cabi = env["O"], env["cabi"]

@@ -28,6 +28,7 @@ def build(force=False, verbose=False):
     """one object per .cu (compiled in parallel, rebuilt only when it or a header changed), then one link"""
     from concurrent.futures import ThreadPoolExecutor
     extra = os.environ.get("BAMCL_EXTRA_NVCC", "").split()  # kernel tuning sweeps
+    only = os.environ.get("BAMCL_EXTRA_ONLY", "").split()    # ... applied to these sources only (e.g. "score_cloud")
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     hdrs = glob.glob(os.path.join(CSRC, "*.cuh")) + [os.path.join(HERE, "..", "include", "bamcl.h")]
@@ -36,9 +37,12 @@ def build(force=False, verbose=False):
     jobs = []
     for src in sources():
         obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
-        stale = force or extra or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hdr_t)
+        name = os.path.basename(src)[:-3]
+        mine = not only or name in only
+        stale = ((force or extra) and mine) or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hdr_t)
         if stale:
-            jobs.append([NVCC] + compile_flags + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, src])
+            jobs.append([NVCC] + compile_flags + (extra if mine else []) + (["-Xptxas", "-v"] if verbose else []) +
+                        ["-c", "-o", obj, src])
     if not jobs and os.path.exists(OUT) and not force:
         return OUT
     with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 2)) as ex:

@@ -114,19 +114,59 @@ __global__ void k_index_uploaded(const float* __restrict__ dist, uint16_t* __res
   kmap[tiled_offset(i, j, tiles_x, layout)] = rank_of_k[k];
 }
 
-// ---- "not free" bit fields for the ray march: bit (i & 31) of word [j][i >> 5] (rows) and
-// bit (j & 31) of word [i][j >> 5] (columns).
-__global__ void k_blocked_bits(const int8_t* __restrict__ cells, uint32_t* __restrict__ rows, uint32_t* __restrict__ cols,
-                               int size_x, int size_y, int row_words, int col_words)
+// ---- clearance field for the ray march (score_beam.cu): per cell, floor of the Euclidean distance in cells to the
+// nearest cell a ray stops at -- any cell that is not CELL_FREE, or any cell off the grid (occupancy_map.cpp:315-358) --
+// capped at CLEAR_CAP. 0 = the cell itself stops the ray. Exact (separable) below the cap, so it never overestimates.
+constexpr int CLEAR_CAP = 64;
+// pass 1, one thread per column: distance along the column to the nearest stopping cell (grid edge included)
+__global__ void __launch_bounds__(128) k_clear_cols(const int8_t* __restrict__ cells, uint8_t* __restrict__ g, int size_x, int size_y)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int j = blockIdx.y;
-  const bool blocked = (i < size_x) ? (cells[(size_t)j * size_x + i] != -1) : true;
-  const unsigned m = __ballot_sync(0xffffffffu, blocked);
-  if ((threadIdx.x & 31) == 0 && (i >> 5) < row_words)
-    rows[(size_t)j * row_words + (i >> 5)] = m;
-  if (blocked && i < size_x)
-    atomicOr(&cols[(size_t)i * col_words + (j >> 5)], 1u << (j & 31));
+  if (i >= size_x)
+    return;
+  int run = 0;  // the cell at j = -1 stops rays
+  for (int j = 0; j < size_y; j++)
+  {
+    run = cells[(size_t)j * size_x + i] != -1 ? 0 : min(run + 1, 255);
+    g[(size_t)j * size_x + i] = (uint8_t)run;
+  }
+  run = 0;  // j = size_y
+  for (int j = size_y - 1; j >= 0; j--)
+  {
+    const int here = g[(size_t)j * size_x + i];
+    run = here == 0 ? 0 : min(run + 1, 255);
+    g[(size_t)j * size_x + i] = (uint8_t)min(here, run);
+  }
+}
+// pass 2, one thread per cell: min over the row window of dx^2 + g^2
+__global__ void __launch_bounds__(256) k_clear_rows(const uint8_t* __restrict__ g, uint8_t* __restrict__ clear, int size_x, int size_y)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+  if (i >= size_x)
+    return;
+  const uint8_t* row = g + (size_t)j * size_x;
+  int best = (int)row[i] * (int)row[i];
+  const int edge = min(i + 1, size_x - i);  // columns -1 and size_x stop rays
+  best = min(best, edge * edge);
+  for (int d = 1; d <= CLEAR_CAP && d * d < best; d++)
+  {
+    if (i - d >= 0)
+    {
+      const int v = row[i - d];
+      best = min(best, d * d + v * v);
+    }
+    if (i + d < size_x)
+    {
+      const int v = row[i + d];
+      best = min(best, d * d + v * v);
+    }
+  }
+  int r = (int)sqrtf((float)best);
+  while (r * r > best)
+    r--;
+  while ((r + 1) * (r + 1) <= best)
+    r++;
+  clear[(size_t)j * size_x + i] = (uint8_t)min(r, CLEAR_CAP);
 }
 
 // ---- calcRange (occupancy_map.cpp:257-364), one thread per ray, the reference's own cell walk.
@@ -186,17 +226,20 @@ __global__ void k_calc_range(const int8_t* __restrict__ cells, int size_x, int s
 // above tests the cell at x1 + xstep too (the reference's while condition is checked before the step, so
 // the last tested x is x1 + xstep) -- see the parity test against the oracle.
 
-static int build_blocked_bits(bamcl_map2d* m)
+static int build_clearance(bamcl_map2d* m)  // the ray march's clearance field, from the cell states
 {
   bamcl_ctx* ctx = m->ctx;
-  m->row_words = (m->size_x + 31) / 32;
-  m->col_words = (m->size_y + 31) / 32;
-  BAMCL_TRY(m->blocked_rows.reserve(sizeof(uint32_t) * (size_t)m->row_words * m->size_y));
-  BAMCL_TRY(m->blocked_cols.reserve(sizeof(uint32_t) * (size_t)m->col_words * m->size_x));
-  BAMCL_CUDA_OK(cudaMemsetAsync(m->blocked_cols.p, 0, sizeof(uint32_t) * (size_t)m->col_words * m->size_x, ctx->stream));
-  dim3 grid((m->row_words * 32 + 255) / 256, m->size_y);
-  BAMCL_LAUNCH(ctx, k_blocked_bits, grid, 256, 0, m->cells.as<int8_t>(), m->blocked_rows.as<uint32_t>(),
-               m->blocked_cols.as<uint32_t>(), m->size_x, m->size_y, m->row_words, m->col_words);
+  const size_t n = (size_t)m->size_x * m->size_y;
+  if (n == 0)
+    return BAMCL_OK;
+  bamcl::DevBuf g;
+  BAMCL_TRY(g.reserve(n));
+  BAMCL_TRY(m->clear.reserve(n));
+  BAMCL_LAUNCH(ctx, k_clear_cols, (m->size_x + 127) / 128, 128, 0, m->cells.as<int8_t>(), g.as<uint8_t>(), m->size_x, m->size_y);
+  dim3 grid((m->size_x + 255) / 256, m->size_y);
+  BAMCL_LAUNCH(ctx, k_clear_rows, grid, 256, 0, g.as<uint8_t>(), m->clear.as<uint8_t>(), m->size_x, m->size_y);
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  g.release();
   return BAMCL_OK;
 }
 
@@ -232,8 +275,7 @@ int bamcl_map2d_destroy(bamcl_map2d* m)
   m->dist.release();
   m->kmap.release();
   m->rank_of_k.release();
-  m->blocked_rows.release();
-  m->blocked_cols.release();
+  m->clear.release();
   m->free_ij.release();
   delete m;
   return BAMCL_OK;
@@ -248,7 +290,7 @@ int bamcl_map2d_set_cells(bamcl_map2d* m, const int8_t* cells, long n)
   BAMCL_TRY(m->cells.reserve((size_t)n));
   BAMCL_CUDA_OK(cudaMemcpyAsync(m->cells.p, cells, (size_t)n, cudaMemcpyHostToDevice, m->ctx->stream));
   m->has_cells = true;
-  BAMCL_TRY(build_blocked_bits(m));
+  BAMCL_TRY(build_clearance(m));
   BAMCL_CUDA_OK(cudaStreamSynchronize(m->ctx->stream));
   return BAMCL_OK;
 }
@@ -432,7 +474,7 @@ extern "C" int bamcl_map2d_from_occupancy_grid(bamcl_ctx* ctx, const int8_t* dat
                                                                            size_y, m->cells.as<signed char>());
       ctx->launches++;
       m->has_cells = true;
-      rc = build_blocked_bits(m);
+      rc = build_clearance(m);
     }
     if (rc == BAMCL_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess)
       rc = set_error(BAMCL_E_CUDA, "bamcl_map2d_from_occupancy_grid: %s", cudaGetErrorString(cudaGetLastError()));

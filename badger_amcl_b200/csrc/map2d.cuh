@@ -24,9 +24,9 @@ struct bamcl_map2d
   int cell_radius = 0;  // floor(max_distance / resolution), occupancy_map.cpp:125
   double max_distance = 0.0;
   bool has_cells = false, has_dist = false;
-  // bit field "cell is not free" for the ray march, row-major and column-major copies
-  bamcl::DevBuf blocked_rows, blocked_cols;
-  int row_words = 0, col_words = 0;
+  // ray march (score_beam.cu): u8 per cell = floor(distance in cells to the nearest cell that stops a ray -- not free, or
+  // off the grid), capped; the march jumps over the cells this proves free
+  bamcl::DevBuf clear;
   // Node2D::updateFreeSpaceIndices (node_2d.cpp:320-338): (i, j) of the free cells far enough from obstacles, i-major
   bamcl::DevBuf free_ij;
   long free_count = -1;  // -1 = not built for the current cache

@@ -114,6 +114,67 @@ static void recount(bamcl_map3d* m)
 
 static inline int world_to_voxel(double v, double res) { return (int)std::floor(v / res + 0.5); }  // octomap.cpp:98-109
 
+namespace
+{
+// one thread per brick of 4 x 4 x 2 voxels: its 32 distance bytes (255 beyond the bounds) and its "near" bits
+__global__ void __launch_bounds__(256) k3_build_bricks(const uint8_t* __restrict__ field, int W, int H, int D, int CW, int CH,
+                                                       long n_bricks, uint8_t* __restrict__ bricks, unsigned* __restrict__ bits,
+                                                       unsigned long long* __restrict__ near_count)
+{
+  const long b = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= n_bricks)
+    return;
+  const int bx = (int)(b % CW), by = (int)((b / CW) % CH), bz = (int)(b / ((long)CW * CH));
+  unsigned word = 0;
+  unsigned packed[8];
+#pragma unroll
+  for (int q = 0; q < 8; q++)
+    packed[q] = 0;
+#pragma unroll
+  for (int pos = 0; pos < 32; pos++)
+  {
+    const int i = bx * 4 + (pos & 3), j = by * 4 + ((pos >> 2) & 3), k = bz * 2 + (pos >> 4);
+    unsigned v = 255;
+    if (i < W && j < H && k < D)
+      v = field[((size_t)k * H + j) * W + i];
+    if (v < 255)
+      word |= 1u << pos;
+    packed[pos >> 2] |= v << (8 * (pos & 3));
+  }
+  uint4* dst = reinterpret_cast<uint4*>(bricks + (size_t)b * 32);
+  dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+  dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+  bits[b] = word;
+  const int cnt = warp_sum_i(__popc(word));
+  if ((threadIdx.x & 31) == 0 && cnt)
+    atomicAdd(near_count, (unsigned long long)cnt);
+}
+}  // namespace
+
+namespace bamcl
+{
+int map3d_build_bricks(bamcl_map3d* m)
+{
+  m->CW = (m->W + 3) / 4;
+  m->CH = (m->H + 3) / 4;
+  m->CD = (m->D + 1) / 2;
+  const long n_bricks = (long)m->CW * m->CH * m->CD;
+  if (n_bricks * 32 >= (1l << 32))
+    return set_error(BAMCL_E_UNSUPPORTED, "3-D map of %ld bricks exceeds the scorer's 32-bit brick addressing", n_bricks);
+  BAMCL_TRY(m->bricks.reserve((size_t)n_bricks * 32));
+  BAMCL_TRY(m->near_bits.reserve((size_t)n_bricks * 4 + 16));
+  unsigned long long* counter = reinterpret_cast<unsigned long long*>(m->near_bits.as<unsigned>() + ((n_bricks + 1) & ~1l));
+  BAMCL_CUDA_OK(cudaMemsetAsync(counter, 0, sizeof(unsigned long long), m->ctx->stream));
+  BAMCL_LAUNCH(m->ctx, k3_build_bricks, (unsigned)((n_bricks + 255) / 256), 256, 0, m->field.as<uint8_t>(), m->W, m->H, m->D, m->CW,
+               m->CH, n_bricks, m->bricks.as<uint8_t>(), m->near_bits.as<unsigned>(), counter);
+  unsigned long long near = 0;
+  BAMCL_CUDA_OK(cudaMemcpyAsync(&near, counter, sizeof(near), cudaMemcpyDeviceToHost, m->ctx->stream));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(m->ctx->stream));
+  m->near_fraction = (double)near / ((double)m->W * m->H * m->D);
+  return BAMCL_OK;
+}
+}  // namespace bamcl
+
 extern "C" {
 
 int bamcl_map3d_create(bamcl_ctx* ctx, double resolution, double max_distance, const int* keys, long n_keys,
@@ -172,6 +233,8 @@ int bamcl_map3d_destroy(bamcl_map3d* m)
   cudaStreamSynchronize(m->ctx->stream);
   m->d_src.release();
   m->field.release();
+  m->bricks.release();
+  m->near_bits.release();
   delete m;
   return BAMCL_OK;
 }
@@ -217,6 +280,7 @@ int bamcl_map3d_build_distances(bamcl_map3d* m)
   occ.release();
   g1.release();
   g2.release();
+  BAMCL_TRY(bamcl::map3d_build_bricks(m));
   m->has_dist = true;
   m->version++;
   return BAMCL_OK;
@@ -248,6 +312,7 @@ int bamcl_map3d_upload_distances(bamcl_map3d* m, const uint8_t* dense, long n)
   BAMCL_TRY(m->field.reserve((size_t)n));
   BAMCL_CUDA_OK(cudaMemcpyAsync(m->field.p, dense, (size_t)n, cudaMemcpyHostToDevice, m->ctx->stream));
   BAMCL_CUDA_OK(cudaStreamSynchronize(m->ctx->stream));
+  BAMCL_TRY(bamcl::map3d_build_bricks(m));
   m->has_dist = true;
   m->version++;
   return BAMCL_OK;

@@ -48,6 +48,61 @@ __global__ void k_fill(double* __restrict__ p, double v, int n)
     p[i] = v;
 }
 
+// ---- scoring order (pf_spatial_order): counting sort of the window by coarse-cell Morton key, 64 x 64 cells
+constexpr int ORDER_BITS = 6, ORDER_BINS = 1 << (2 * ORDER_BITS);
+__device__ __forceinline__ unsigned order_key(double x, double y, double x0, double y0, double inv_cell)
+{
+  const int cx = min(max((int)floor((x - x0) * inv_cell), 0), (1 << ORDER_BITS) - 1);
+  const int cy = min(max((int)floor((y - y0) * inv_cell), 0), (1 << ORDER_BITS) - 1);
+  unsigned k = 0;
+#pragma unroll
+  for (int b = 0; b < ORDER_BITS; b++)
+    k |= (((unsigned)cx >> b) & 1u) << (2 * b) | (((unsigned)cy >> b) & 1u) << (2 * b + 1);
+  return k;
+}
+__global__ void __launch_bounds__(256) k_order_count(const double* __restrict__ x, const double* __restrict__ y, int n, double x0,
+                                                     double y0, double inv_cell, int* __restrict__ hist)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    atomicAdd(&hist[order_key(x[i], y[i], x0, y0, inv_cell)], 1);
+}
+__global__ void __launch_bounds__(1024) k_order_scan(int* __restrict__ hist)  // exclusive scan of ORDER_BINS counts, one block
+{
+  __shared__ int s[1024];
+  constexpr int PER = ORDER_BINS / 1024;
+  int v[PER], sum = 0;
+#pragma unroll
+  for (int q = 0; q < PER; q++)
+  {
+    v[q] = hist[threadIdx.x * PER + q];
+    sum += v[q];
+  }
+  s[threadIdx.x] = sum;
+  __syncthreads();
+  for (int o = 1; o < 1024; o <<= 1)
+  {
+    const int t = threadIdx.x >= o ? s[threadIdx.x - o] : 0;
+    __syncthreads();
+    s[threadIdx.x] += t;
+    __syncthreads();
+  }
+  int run = s[threadIdx.x] - sum;
+#pragma unroll
+  for (int q = 0; q < PER; q++)
+  {
+    hist[threadIdx.x * PER + q] = run;
+    run += v[q];
+  }
+}
+__global__ void __launch_bounds__(256) k_order_scatter(const double* __restrict__ x, const double* __restrict__ y, int n, double x0,
+                                                       double y0, double inv_cell, int* __restrict__ cursor, int* __restrict__ perm)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    perm[atomicAdd(&cursor[order_key(x[i], y[i], x0, y0, inv_cell)], 1)] = i;
+}
+
 // ---- deterministic weight total: fixed-shape two-level tree (block partials, then one block).
 constexpr int RED_BLOCK = 256;
 constexpr int RED_ITEMS = 8;
@@ -210,6 +265,28 @@ int pf_download_async(bamcl_pf* pf, double* aos, long n)
   return BAMCL_OK;
 }
 
+int pf_spatial_order(bamcl_pf* pf, double x0, double y0, double cell, const int** perm_out)
+{
+  SampleSet& set = pf->sets[pf->current];
+  const int n = pf_win_cnt(pf);
+  const long off = pf_win_off(pf);
+  BAMCL_TRY(pf->order_perm.reserve(sizeof(int) * (size_t)std::max(n, 1)));
+  BAMCL_TRY(pf->order_hist.reserve(sizeof(int) * ORDER_BINS));
+  BAMCL_CUDA_OK(cudaMemsetAsync(pf->order_hist.p, 0, sizeof(int) * ORDER_BINS, pf->ctx->stream));
+  if (n > 0)
+  {
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    const double inv = 1.0 / cell;
+    BAMCL_LAUNCH(pf->ctx, k_order_count, blocks, 256, 0, set.x.as<double>() + off, set.y.as<double>() + off, n, x0, y0, inv,
+                 pf->order_hist.as<int>());
+    BAMCL_LAUNCH(pf->ctx, k_order_scan, 1, 1024, 0, pf->order_hist.as<int>());
+    BAMCL_LAUNCH(pf->ctx, k_order_scatter, blocks, 256, 0, set.x.as<double>() + off, set.y.as<double>() + off, n, x0, y0, inv,
+                 pf->order_hist.as<int>(), pf->order_perm.as<int>());
+  }
+  *perm_out = pf->order_perm.as<int>();
+  return BAMCL_OK;
+}
+
 int pf_reduce_total(bamcl_pf* pf, double* d_total)
 {
   SampleSet& set = pf->sets[pf->current];
@@ -349,7 +426,7 @@ int bamcl_pf_destroy(bamcl_pf* pf)
                            &pf->t_out, &pf->t_sums, &pf->t_fast})
     b->release();
   for (bamcl::DevBuf* b : {&pf->g_first, &pf->g_node, &pf->t_bits, &pf->t_bpre, &pf->t_setpart, &pf->t_ints, &pf->stage_x,
-                           &pf->stage_y, &pf->stage_th, &pf->stage_src, &pf->scan.agree, &pf->scan.skip_count, &pf->scan.beams_sel})
+                           &pf->stage_y, &pf->stage_th, &pf->stage_src, &pf->scan.agree, &pf->scan.skip_count, &pf->scan.beams_sel, &pf->order_perm, &pf->order_hist})
     b->release();
   pf->t_hout.release();
   if (pf->aux_stream)

@@ -51,7 +51,8 @@ struct StagedCloud
 {
   bool valid = false;
   bamcl_cloud_model model;
-  int n_points = 0;
+  int n_points = 0;   // staged (finite) points
+  int n_dropped = 0;  // points with a non-finite coordinate, left out of the staged cloud
   DevBuf xyz, px, py, pz;  // packed upload + SoA split (f32, sensor frame)
   DevBuf table;            // f64[257]: per-quantum model value, [256] = outside the map
   uint64_t map_version = 0;
@@ -135,6 +136,9 @@ struct bamcl_pf
   bamcl::DevBuf g_first, g_node, t_bits, t_bpre, t_setpart, t_ints;
   bamcl::DevBuf stage_x, stage_y, stage_th, stage_src;  // rows this rank selected for other ranks (shard exchange)
   int tree_dense = 0;  // the last tree build addressed the bins directly
+  // scoring order: particles grouped by coarse (x, y) cell along a Morton curve, so the particles a GPU works on at any
+  // moment look at the same part of the map (L2 reuse); weights are written back by original index
+  bamcl::DevBuf order_perm, order_hist;
 };
 
 namespace bamcl
@@ -172,6 +176,9 @@ namespace bamcl
 // phase timing of the distributed resample (BAMCL_SHARD_TIMING=1): synchronises at every mark, so only for diagnosis
 void pf_mark(bamcl_pf* pf, const char* phase);
 void pf_mark_report(bamcl_pf* pf);
+// perm_out (device, window-local indices) = this rank's window ordered by the Morton code of its coarse (x, y) cell;
+// cell = edge of a coarse cell in metres, (x0, y0) = lower corner of the area. Order inside a cell is arbitrary.
+int pf_spatial_order(bamcl_pf* pf, double x0, double y0, double cell, const int** perm_out);
 int pf_reduce_total(bamcl_pf* pf, double* d_total);  // deterministic sum of the current set's weights -> device scalar
 int pf_read_scalar(bamcl_pf* pf, int slot, double* out);  // device scalar slot -> host (synchronises)
 int pf_normalise_by_device_total(bamcl_pf* pf);           // w /= scalars[0] (or 1/n), particle_filter.cpp:237-266

@@ -1,9 +1,11 @@
 // K-b: beam model = per particle x beam ray march through the occupancy grid (calcRange) + the four-part
 // mixture. Reference: src/amcl/sensors/planar_scanner.cpp:168-234, src/amcl/map/occupancy_map.cpp:257-364.
 //
-// A warp owns one particle at a time; lanes take adjacent beams (adjacent rays have similar lengths and
-// touch neighbouring cells). Each lane walks the reference's own integer Bresenham sequence, so the
-// first blocked cell -- and with it the returned range -- is the reference's.
+// A warp owns one particle at a time; lanes take adjacent beams. Each lane follows the reference's own integer
+// Bresenham sequence, so the first cell that stops the ray -- and with it the returned range -- is the reference's. It
+// does not visit every cell of that sequence: the map's clearance field (map2d.cu, distance in cells to the nearest
+// stopping cell) proves the next cells free, and the walk jumps over them, landing exactly on the sequence through its
+// closed form y(t) = y0 + ystep * floor((t * 2dy + dx) / 2dx).
 #include <cmath>
 
 #include "pf.cuh"
@@ -25,8 +27,7 @@ struct BeamArgs
   int step;
   const int8_t* cells;
   const float* dist;
-  const uint32_t *blocked_rows, *blocked_cols;  // 1-bit "not free" maps (row-major / column-major)
-  int row_words, col_words;
+  const uint8_t* clear;  // clearance field: floor(distance in cells to the nearest stopping cell), capped
   int size_x, size_y;
   double resolution;
   float origin_x, origin_y;
@@ -36,23 +37,32 @@ struct BeamArgs
   double off_map_factor, non_free_space_factor, non_free_space_radius;
 };
 
-// OccupancyMap::calcRange (occupancy_map.cpp:257-364) inside the scorer: the reference's integer Bresenham walk, cell
-// by cell, so the first blocked cell -- and the returned range -- are the reference's. The cell test reads the 1-bit
-// "not free" maps (map2d.cu k_blocked_bits): bit (major & 31) of word [minor][major >> 5], the row-major copy for
-// x-major rays and the column-major copy for steep ones, so 32 consecutive steps along the major axis share one word,
-// which stays in a register until the walk leaves it.
-// State of one lane's walk along its current ray (the reference's loop variables, occupancy_map.cpp:300-360).
+// OccupancyMap::calcRange (occupancy_map.cpp:257-364) inside the scorer. The reference tests the cells of an integer
+// Bresenham walk one by one: start cell, then `x += xstep; err += dy; if (2 err >= dx) { y += ystep; err -= dx; }` until
+// x == x1 + xstep; the first cell that is off the grid or not CELL_FREE ends it. After t steps the walk is at
+// x = x0 + t xstep, y = y0 + ystep * floor((t * 2dy + dx) / 2dx) (the step rule keeps 2 err in [-dx, dx)). From a cell
+// with clearance d (true distance to the nearest stopping cell >= d) every cell within Euclidean distance < d is free;
+// the cell s steps ahead lies within s / cos(phi) + 1 of the current one (phi = the ray's angle to its major axis, +1 for
+// the rounding of y), so s < (d - 1) cos(phi) steps can be skipped untested.
+// State of one lane's walk along its current ray.
 struct RayWalk
 {
-  // the reference's loop variables (x = major axis after the steep swap); err2 = 2 * error
-  int x, y, x0, y0, err2, dx, dy2, dx2, xstep, ystep;
+  int x, y, x0, y0, t, dx, dy2, dx2, xstep, ystep;
   int left;        // cells still to test before the walk leaves the grid along x or has tested x1 + xstep
   int oob_at_end;  // running out of `left` means the next cell is off the grid (a hit) rather than "nothing hit"
-  int rowbase;     // y * words
-  int edge;        // (x & 31) value that starts a new word in walking direction
+  float fdir;      // 0.999 cos(phi)
+  double inv_dx2;
   int steep;
   int u;  // beam index, -1 = no ray
 };
+__device__ __forceinline__ int walk_y(const RayWalk& r, int t)  // y after t steps
+{
+  const int num = t * r.dy2 + r.dx;
+  int ny = (int)((double)num * r.inv_dx2);
+  ny -= ny * r.dx2 > num ? 1 : 0;
+  ny += (ny + 1) * r.dx2 <= num ? 1 : 0;
+  return r.y0 + r.ystep * ny;
+}
 
 // Warp = one particle at a time; lanes = rays. Adjacent rays can differ 30x in length (one ends on the near wall, the
 // next runs through a door), so a lane that finishes its ray scores it and takes the particle's next unassigned beam
@@ -86,7 +96,6 @@ __global__ void __launch_bounds__(256) k_score_beam(const BeamArgs a)
     bool walking = false;  // this lane is inside a walk
     double map_range = 0.0;
     bool have_result = false;  // a finished ray waits to be scored
-    uint32_t cur_word = 0;
     for (;;)
     {
       const unsigned busy = __ballot_sync(0xffffffffu, walking);
@@ -150,7 +159,6 @@ __global__ void __launch_bounds__(256) k_score_beam(const BeamArgs a)
                 t = x1; x1 = y1; y1 = t;
               }
               const int major_size = r.steep ? a.size_y : a.size_x, minor_size = r.steep ? a.size_x : a.size_y;
-              const int words = r.steep ? a.col_words : a.row_words;
               r.x0 = x0;
               r.y0 = y0;
               r.dx = abs(x1 - x0);
@@ -158,10 +166,11 @@ __global__ void __launch_bounds__(256) k_score_beam(const BeamArgs a)
               r.dx2 = 2 * r.dx;
               r.xstep = (x0 < x1) ? 1 : -1;
               r.ystep = (y0 < y1) ? 1 : -1;
-              r.edge = r.xstep > 0 ? 0 : 31;
-              r.err2 = 0;
+              r.t = 0;
               r.x = x0;
               r.y = y0;
+              r.inv_dx2 = 1.0 / (double)r.dx2;
+              r.fdir = 0.999f * (float)r.dx * rsqrtf((float)r.dx * (float)r.dx + 0.25f * (float)r.dy2 * (float)r.dy2);
               // cells x0 .. x1 + xstep are tested (dx + 2 of them); those with x off the grid count as hits
               const int to_test = r.dx + 2;
               const int in_grid = ((unsigned)x0 < (unsigned)major_size) ? (r.xstep > 0 ? major_size - x0 : x0 + 1) : 0;
@@ -173,11 +182,7 @@ __global__ void __launch_bounds__(256) k_score_beam(const BeamArgs a)
                 have_result = true;
               }
               else
-              {
-                r.rowbase = y0 * words;
-                cur_word = __ldg(&(r.steep ? a.blocked_cols : a.blocked_rows)[r.rowbase + (x0 >> 5)]);
                 walking = true;
-              }
             }
           }
         }
@@ -186,60 +191,46 @@ __global__ void __launch_bounds__(256) k_score_beam(const BeamArgs a)
           next = a.n_used;
         continue;
       }
-      // ---- one chunk of walk steps for the lanes that have a ray
+      // ---- one chunk of jumps for the lanes that have a ray
       if (walking)
       {
-        const uint32_t* __restrict__ bits = r.steep ? a.blocked_cols : a.blocked_rows;
-        const int words = r.steep ? a.col_words : a.row_words;
         const int minor_size = r.steep ? a.size_x : a.size_y;
-        int x = r.x, y = r.y, err2 = r.err2, left = r.left;
-        uint32_t word = cur_word;
-        // single-exit loop (no breaks): the lanes of a warp stay converged from one step to the next
+        int x = r.x, y = r.y, t = r.t, left = r.left;
+        // single-exit loop (no breaks): the lanes of a warp stay converged from one jump to the next
         int code = 0;  // 0 walking, 1 hit at (x, y), 2 nothing hit, 3 the next step leaves the grid along x
 #pragma unroll 1
-        for (int it = 0; it < 32 && code == 0; it++)
+        for (int it = 0; it < 8 && code == 0; it++)
         {
-          if ((word >> (x & 31)) & 1u)  // the cell is not free
+          const int d = __ldg(&a.clear[r.steep ? (size_t)x * a.size_x + y : (size_t)y * a.size_x + x]);
+          if (d == 0)  // the cell stops the ray
             code = 1;
           else if (left == 1)  // that was the last testable cell
             code = r.oob_at_end ? 3 : 2;
           else
           {
-            left--;
-            x += r.xstep;
-            err2 += r.dy2;
-            bool reload = (x & 31) == r.edge;
-            if (err2 >= r.dx)
-            {
-              y += r.ystep;
-              err2 -= r.dx2;
-              if ((unsigned)y >= (unsigned)minor_size)  // left the grid sideways: this cell is a hit
-                code = 1;
-              else
-              {
-                r.rowbase = y * words;
-                reload = true;
-              }
-            }
-            if (reload && code == 0)
-              word = __ldg(&bits[r.rowbase + (x >> 5)]);
+            int s = (int)((float)(d - 1) * r.fdir);
+            s = min(max(s, 1), left - 1);
+            t += s;
+            left -= s;
+            x += s * r.xstep;
+            y = walk_y(r, t);
+            if ((unsigned)y >= (unsigned)minor_size)  // left the grid sideways: this cell is a hit
+              code = 1;
           }
         }
         if (code == 3)
         {
           // the walk steps once more and lands off the grid: a hit there (:340-358)
+          t++;
           x += r.xstep;
-          err2 += r.dy2;
-          if (err2 >= r.dx)
-            y += r.ystep;
+          y = walk_y(r, t);
           code = 1;
         }
         const bool done = code != 0, hit = code == 1;
         r.x = x;
         r.y = y;
-        r.err2 = err2;
+        r.t = t;
         r.left = left;
-        cur_word = word;
         if (done)
         {
           const int ddx = x - r.x0, ddy = y - r.y0;
@@ -319,10 +310,7 @@ int launch_beam_model(bamcl_pf* pf, bamcl_map2d* map)
   a.step = sc.step;
   a.cells = map->cells.as<int8_t>();
   a.dist = map->dist.as<float>();
-  a.blocked_rows = map->blocked_rows.as<uint32_t>();
-  a.blocked_cols = map->blocked_cols.as<uint32_t>();
-  a.row_words = map->row_words;
-  a.col_words = map->col_words;
+  a.clear = map->clear.as<uint8_t>();
   a.size_x = map->size_x;
   a.size_y = map->size_y;
   a.resolution = map->resolution;

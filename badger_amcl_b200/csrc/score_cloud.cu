@@ -12,8 +12,17 @@
 // points of the scan = neighbouring voxels. The per-point term comes from a 257-entry f64 table (one entry per
 // quantised distance + one for "outside the map"), built on the host with glibc's exp in the reference's
 // expression order and held in shared memory in 16 interleaved copies (bank-conflict free).
+//
+// What is gathered (map3d.cuh): the volume in bricks of 4 x 4 x 2 voxels. A look-up first tests the voxel's bit in the
+// brick's "near an obstacle" word (the bit volume is 1/8 of the field and L2-resident); only voxels within max_distance of
+// an obstacle -- a minority of the evals of any cloud -- then read their distance byte from the brick's 32-byte sector.
+// The staged cloud is ordered along a Morton curve, so the 32 points of a lane group fall into a handful of bricks.
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <utility>
+#include <vector>
 
 #include "map3d.cuh"
 #include "pf.cuh"
@@ -22,9 +31,23 @@ using namespace bamcl;
 
 namespace
 {
-constexpr int PB = 16;   // particles per warp batch
-constexpr int NPL = 4;   // points per lane per pass
-constexpr int GB = 4;    // particles per gather batch
+#ifndef CLOUD_PB
+#define CLOUD_PB 16
+#endif
+#ifndef CLOUD_NPL
+#define CLOUD_NPL 2
+#endif
+#ifndef CLOUD_GB
+#define CLOUD_GB 8
+#endif
+#ifndef CLOUD_MINB
+#define CLOUD_MINB 3
+#endif
+// (swept on a B200, scripts/sweep_cloud.sh, 1M x 4096: 16/4/4/2 CTAs 48.5 ms, 8/4/4/3 29.5, 16/2/8/3 28.1, 16/2/4/4 29.4,
+// 16/1/16/4 32.2, 32/4/4/2 57.3: occupancy -- registers -- decides, three CTAs per SM is the sweet spot)
+constexpr int PB = CLOUD_PB;    // particles per warp batch
+constexpr int NPL = CLOUD_NPL;  // points per lane per pass
+constexpr int GB = CLOUD_GB;    // particles per gather batch
 constexpr int WARPS = 8;
 constexpr int PASS_POINTS = 32 * NPL;
 constexpr int TABLE_N = 257;
@@ -36,9 +59,13 @@ struct CloudArgs
   int n;
   const float *px, *py, *pz;
   int n_points;
-  const uint8_t* field;
-  int i0, j0, k0, W, H, D;
+  const uint8_t* bricks;    // [n_bricks][32]
+  const unsigned* near_bits;  // [n_bricks]
+  int i0, j0, k0, W, H, D, CW, CH;
+  const int* perm;  // scoring order (window-local particle indices), or null
+  int n_dropped;  // points with a non-finite coordinate: outside every map, removed from the staged cloud
   double resolution, inv_resolution;
+  float inv_resolution_f;
   const double* table;
   int model;
   double gompertz_a, gompertz_b, gompertz_c, input_shift, input_scale, output_shift;
@@ -62,6 +89,17 @@ __device__ __forceinline__ int world_to_voxel(float vf, double res, double inv_r
   const double fl = floor(f);
   if (f - fl < 1e-7 || fl + 1.0 - f < 1e-7)
     return (int)floor(v / res + 0.5);
+  return (int)fl;
+}
+
+// The same index from one f32 FMA when the result is clear of a rounding boundary by more than the f32 error of that
+// FMA (|f| * 1.2e-7: inv_res rounded to f32 + the FMA's own rounding); the reference's f64 expression decides the rest.
+__device__ __forceinline__ int world_to_voxel_fast(float vf, float inv_res_f, double res, double inv_res)
+{
+  const float f = __fmaf_rn(vf, inv_res_f, 0.5f);
+  const float fl = floorf(f);
+  if (fabsf((f - fl) - 0.5f) > 0.5f - (4e-7f * fabsf(f) + 1e-6f))
+    return world_to_voxel(vf, res, inv_res);
   return (int)fl;
 }
 
@@ -143,7 +181,7 @@ __device__ void particle_transform(const CloudArgs& a, double px, double py, dou
   out->t[2] = (float)o[2];
 }
 
-template <bool TAIL>
+template <bool TAIL, bool BITS>
 __device__ __forceinline__ void cloud_pass(const CloudArgs& a, const double* __restrict__ tab, const Xform* stash, int p0,
                                            int lane, double (&acc)[PB])
 {
@@ -159,10 +197,11 @@ __device__ __forceinline__ void cloud_pass(const CloudArgs& a, const double* __r
     z[q] = live[q] ? __ldg(&a.pz[t]) : 0.f;
   }
   const unsigned copy = (unsigned)(lane & 15);
+  constexpr unsigned OUTSIDE = 0xFFFFFFFFu;
 #pragma unroll
   for (int g0 = 0; g0 < PB; g0 += GB)
   {
-    unsigned kk[GB][NPL];
+    unsigned addr[GB][NPL], word[GB][NPL];
 #pragma unroll
     for (int gg = 0; gg < GB; gg++)
     {
@@ -177,13 +216,19 @@ __device__ __forceinline__ void cloud_pass(const CloudArgs& a, const double* __r
           const float m = __fadd_rn(
               __fadd_rn(__fadd_rn(__fmul_rn(T.R[r * 3], x[q]), __fmul_rn(T.R[r * 3 + 1], y[q])), __fmul_rn(T.R[r * 3 + 2], z[q])),
               T.t[r]);
-          v[r] = world_to_voxel(m, a.resolution, a.inv_resolution);
+          v[r] = world_to_voxel_fast(m, a.inv_resolution_f, a.resolution, a.inv_resolution);
         }
         const int i = v[0] - a.i0, j = v[1] - a.j0, k = v[2] - a.k0;
-        unsigned qd = 256;  // outside the (cropped) bounds: getDistanceToObject returns max_distance, :338-341
+        unsigned ad = OUTSIDE;  // outside the (cropped) bounds: getDistanceToObject returns max_distance, :338-341
+        unsigned wd = 0;
         if ((unsigned)i < (unsigned)a.W && (unsigned)j < (unsigned)a.H && (unsigned)k < (unsigned)a.D)
-          qd = __ldg(&a.field[((size_t)k * a.H + j) * a.W + i]);
-        kk[gg][q] = qd;
+        {
+          const unsigned brick = (unsigned)(((k >> 1) * a.CH + (j >> 2)) * a.CW + (i >> 2));
+          ad = (brick << 5) | (unsigned)(((k & 1) << 4) | ((j & 3) << 2) | (i & 3));
+          wd = BITS ? __ldg(&a.near_bits[brick]) : 0xFFFFFFFFu;
+        }
+        addr[gg][q] = ad;
+        word[gg][q] = wd;
       }
     }
 #pragma unroll
@@ -191,14 +236,28 @@ __device__ __forceinline__ void cloud_pass(const CloudArgs& a, const double* __r
 #pragma unroll
       for (int q = 0; q < NPL; q++)
       {
-        const double v = tab[(kk[gg][q] << 4) | copy];
+        const unsigned ad = addr[gg][q];
+        unsigned qd = ad == OUTSIDE ? 256u : 255u;  // far from every obstacle: the quantised distance saturates at 255
+        if ((word[gg][q] >> (ad & 31u)) & 1u)
+          qd = __ldg(&a.bricks[ad]);
+        addr[gg][q] = qd;
+      }
+#pragma unroll
+    for (int gg = 0; gg < GB; gg++)
+#pragma unroll
+      for (int q = 0; q < NPL; q++)
+      {
+        const double v = tab[(addr[gg][q] << 4) | copy];
         if (!TAIL || live[q])
           acc[g0 + gg] += v;
       }
   }
 }
 
-__global__ void __launch_bounds__(WARPS * 32) k_score_cloud(const CloudArgs a)
+// BITS: test the "near an obstacle" bit before touching the distance byte (pays when most of the volume is far from
+// obstacles, the usual map); maps where most voxels are near something read the byte directly
+template <bool BITS>
+__global__ void __launch_bounds__(WARPS * 32, CLOUD_MINB) k_score_cloud(const CloudArgs a)
 {
   extern __shared__ __align__(16) unsigned char s_raw[];
   double* s_tab = reinterpret_cast<double*>(s_raw);                                    // [TABLE_N][16]
@@ -214,13 +273,14 @@ __global__ void __launch_bounds__(WARPS * 32) k_score_cloud(const CloudArgs a)
 
   for (int batch = blockIdx.x * WARPS + warp; batch < n_batches; batch += warps_total)
   {
-    const int idx = batch * PB + lane;
-    const bool mine = lane < PB && idx < a.n;
+    const int slot = batch * PB + lane;
+    const bool mine = lane < PB && slot < a.n;
+    const int idx = a.perm ? a.perm[min(slot, a.n - 1)] : slot;
     double w = 0.0, factor = 1.0;
     __syncwarp();
     if (lane < PB)
     {
-      const int src = min(idx, a.n - 1);
+      const int src = a.perm ? idx : min(idx, a.n - 1);
       const double px = a.x[src], py = a.y[src], pth = a.th[src];
       w = a.w[src];
       particle_transform(a, px, py, pth, &stash[lane]);
@@ -235,9 +295,9 @@ __global__ void __launch_bounds__(WARPS * 32) k_score_cloud(const CloudArgs a)
     for (int g = 0; g < PB; g++)
       acc[g] = 0.0;
     for (int pass = 0; pass < n_full; pass++)
-      cloud_pass<false>(a, s_tab, stash, pass * PASS_POINTS, lane, acc);
+      cloud_pass<false, BITS>(a, s_tab, stash, pass * PASS_POINTS, lane, acc);
     if (n_full * PASS_POINTS < a.n_points)
-      cloud_pass<true>(a, s_tab, stash, n_full * PASS_POINTS, lane, acc);
+      cloud_pass<true, BITS>(a, s_tab, stash, n_full * PASS_POINTS, lane, acc);
     double sum = 0.0;
 #pragma unroll
     for (int g = 0; g < PB; g++)
@@ -246,6 +306,8 @@ __global__ void __launch_bounds__(WARPS * 32) k_score_cloud(const CloudArgs a)
       if (lane == g)
         sum = v;
     }
+    if (a.n_dropped)
+      sum += (double)a.n_dropped * s_tab[256 << 4];
     if (mine)
     {
       double p;
@@ -253,7 +315,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_score_cloud(const CloudArgs a)
         p = 1.0 + sum;  // :145,:161
       else
       {
-        p = sum / a.n_points;  // :197 (no zero guard in the reference: an empty cloud gives NaN)
+        p = sum / (a.n_points + a.n_dropped);  // :197 (no zero guard in the reference: an empty cloud gives NaN)
         p = p * a.input_scale + a.input_shift;  // applyGompertz :250-260
         p = a.gompertz_a * exp(-1.0 * a.gompertz_b * exp(-1.0 * a.gompertz_c * p));
         p += a.output_shift;
@@ -311,7 +373,7 @@ int stage_cloud(bamcl_pf* pf, bamcl_map3d* map, const bamcl_cloud_model* model, 
   sc.map_version = map->version;
   bamcl_ctx* ctx = pf->ctx;
   // per-quantum value table, in the reference's expression order (point_cloud_scanner.cpp:138-160, 175-193)
-  BAMCL_TRY(pf->h_stage.reserve(sizeof(double) * TABLE_N));
+  BAMCL_TRY(pf->h_stage.reserve(sizeof(double) * TABLE_N + 3 * sizeof(float) * (size_t)std::max<long>(n_points, 1)));
   double* ht = pf->h_stage.as<double>();
   const double z_hit_denom = 2 * model->sigma_hit * model->sigma_hit;
   const double z_rand_mult = 1.0 / map->max_distance;
@@ -334,16 +396,48 @@ int stage_cloud(bamcl_pf* pf, bamcl_map3d* map, const bamcl_cloud_model* model, 
   }
   BAMCL_TRY(sc.table.reserve(sizeof(double) * TABLE_N));
   BAMCL_CUDA_OK(cudaMemcpyAsync(sc.table.p, ht, sizeof(double) * TABLE_N, cudaMemcpyHostToDevice, ctx->stream));
-  if (n_points > 0)
+  // The per-particle sum over the cloud is order-free up to f64 rounding (tests: 1e-6 on weights), so the staged cloud
+  // is ordered along a Morton curve of its sensor-frame cells (0.2 m = one brick): adjacent lanes then look at adjacent
+  // voxels under any rigid transform. Points with a non-finite coordinate lie outside every map ((int)NaN is INT_MIN in
+  // the reference, octomap.cpp:98-109): they are dropped here and their constant term is added back by the kernel.
+  std::vector<std::pair<unsigned long long, int>> order;
+  order.reserve((size_t)n_points);
+  sc.n_dropped = 0;
+  for (long t = 0; t < n_points; t++)
   {
-    const size_t nb = sizeof(float) * (size_t)n_points;
+    const float* p = points_xyz + 3 * t;
+    if (!std::isfinite(p[0]) || !std::isfinite(p[1]) || !std::isfinite(p[2]))
+    {
+      sc.n_dropped++;
+      continue;
+    }
+    unsigned long long code = 0;
+    unsigned c[3];
+    for (int r = 0; r < 3; r++)
+    {
+      const double cell = std::floor((double)p[r] / 0.2) + 1048576.0;  // 21 bits per axis around the sensor
+      c[r] = (unsigned)std::min(2097151.0, std::max(0.0, cell));
+    }
+    for (int bit = 0; bit < 21; bit++)
+      for (int r = 0; r < 3; r++)
+        code |= (unsigned long long)((c[r] >> bit) & 1u) << (3 * bit + r);
+    order.emplace_back(code, (int)t);
+  }
+  std::stable_sort(order.begin(), order.end(), [](const auto& l, const auto& r) { return l.first < r.first; });
+  sc.n_points = (int)order.size();
+  if (sc.n_points > 0)
+  {
+    const size_t nb = sizeof(float) * (size_t)sc.n_points;
+    float* hx = reinterpret_cast<float*>(ht + TABLE_N);
+    for (size_t t = 0; t < order.size(); t++)
+      memcpy(hx + 3 * t, points_xyz + 3 * (size_t)order[t].second, 3 * sizeof(float));
     BAMCL_TRY(sc.xyz.reserve(3 * nb));
     BAMCL_TRY(sc.px.reserve(nb));
     BAMCL_TRY(sc.py.reserve(nb));
     BAMCL_TRY(sc.pz.reserve(nb));
-    BAMCL_CUDA_OK(cudaMemcpyAsync(sc.xyz.p, points_xyz, 3 * nb, cudaMemcpyHostToDevice, ctx->stream));
-    BAMCL_LAUNCH(ctx, k_split_points, (unsigned)((n_points + 255) / 256), 256, 0, sc.xyz.as<float>(), sc.px.as<float>(),
-                 sc.py.as<float>(), sc.pz.as<float>(), (int)n_points);
+    BAMCL_CUDA_OK(cudaMemcpyAsync(sc.xyz.p, hx, 3 * nb, cudaMemcpyHostToDevice, ctx->stream));
+    BAMCL_LAUNCH(ctx, k_split_points, (unsigned)((sc.n_points + 255) / 256), 256, 0, sc.xyz.as<float>(), sc.px.as<float>(),
+                 sc.py.as<float>(), sc.pz.as<float>(), sc.n_points);
   }
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));  // the pinned table buffer and the caller's cloud are reusable
   sc.valid = true;
@@ -371,7 +465,12 @@ int launch_score_cloud(bamcl_pf* pf, bamcl_map3d* map)
   a.py = sc.py.as<float>();
   a.pz = sc.pz.as<float>();
   a.n_points = sc.n_points;
-  a.field = map->field.as<uint8_t>();
+  a.bricks = map->bricks.as<uint8_t>();
+  a.near_bits = map->near_bits.as<unsigned>();
+  a.CW = map->CW;
+  a.CH = map->CH;
+  a.n_dropped = sc.n_dropped;
+  a.inv_resolution_f = (float)(1.0 / map->resolution);
   a.i0 = map->cmin[0];
   a.j0 = map->cmin[1];
   a.k0 = map->cmin[2];
@@ -393,10 +492,24 @@ int launch_score_cloud(bamcl_pf* pf, bamcl_map3d* map)
     a.mt[r] = sc.model.mount_translation[r];
   quat_to_basis(sc.model.mount_rotation, a.R2);
   const int n_batches = (a.n + PB - 1) / PB;
-  const int blocks = std::max(1, std::min((n_batches + WARPS - 1) / WARPS, kNumSMs * 4));
+  const int blocks = std::max(1, std::min((n_batches + WARPS - 1) / WARPS, kNumSMs * 2 * CLOUD_MINB));
   const size_t smem = sizeof(double) * TABLE_N * 16 + sizeof(Xform) * WARPS * PB;
+  // particles that sit close together look at the same part of the field: score them together (L2 reuse)
+  a.perm = nullptr;
+  static const bool no_order = getenv("BAMCL_NO_SCORE_ORDER") != nullptr;  // A/B switch
+  if (a.n >= 65536 && !no_order)
+  {
+    const double x0 = map->cmin[0] * map->resolution, y0 = map->cmin[1] * map->resolution;
+    const double extent = std::max(map->W, map->H) * map->resolution;
+    BAMCL_TRY(pf_spatial_order(pf, x0, y0, std::max(extent / 64.0, 1e-3), &a.perm));
+  }
   BAMCL_CUDA_OK(cudaEventRecord(pf->score_ev0, ctx->stream));
-  BAMCL_LAUNCH(ctx, k_score_cloud, blocks, WARPS * 32, smem, a);
+  static const char* force_bits = getenv("BAMCL_CLOUD_BITS");  // A/B switch: "0" / "1"
+  const bool bits = force_bits ? force_bits[0] == '1' : map->near_fraction < 0.5;
+  if (bits)
+    BAMCL_LAUNCH(ctx, k_score_cloud<true>, blocks, WARPS * 32, smem, a);
+  else
+    BAMCL_LAUNCH(ctx, k_score_cloud<false>, blocks, WARPS * 32, smem, a);
   BAMCL_CUDA_OK(cudaEventRecord(pf->score_ev1, ctx->stream));
   pf->score_timed = true;
   return BAMCL_OK;

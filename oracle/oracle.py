@@ -170,6 +170,10 @@ def ref_lib():
             "ref_map3d_get_bounds": (None, [P, P, P]), "ref_map3d_distance": (D, [P, I, I, I]),
             "ref_map3d_get_dense": (None, [P, P]), "ref_map3d_world_to_map": (None, [P, P, P]),
             "ref_map3d_map_to_world": (None, [P, P, P]),
+            "ref_scanner3d_create": (V, [P, I]), "ref_scanner3d_destroy": (None, [P]),
+            "ref_scanner3d_model": (None, [P, I, D, D, D, D, D, D, D, D, D]),
+            "ref_scanner3d_set_map_factors": (None, [P, D, D, D]), "ref_scanner3d_set_mount": (None, [P, P, P]),
+            "ref_scanner3d_apply": (D, [P, P, L_, P, L_]),
             "ref_kdtree_create": (V, []), "ref_kdtree_destroy": (None, [P]), "ref_kdtree_clear": (None, [P]),
             "ref_kdtree_insert": (None, [P, D, D, D, D]), "ref_kdtree_insert_many": (None, [P, P, L_, D, P]),
             "ref_kdtree_cluster": (None, [P]), "ref_kdtree_get_cluster": (I, [P, D, D, D]),
@@ -787,6 +791,26 @@ class RefMap3D:
 
     def distance(self, i, j, k):
         return self.L.ref_map3d_distance(self.h, i, j, k)
+
+    def cloud_apply(self, model, points, samples):
+        """PointCloudScanner::applyModelToSampleSet of the UNMODIFIED reference translation unit
+        (sensors/point_cloud_scanner.cpp) over this map, configured from the CloudModel struct the port uses; its tf2 / pcl
+        dependencies are the look-alikes under oracle/shim/"""
+        h = self.L.ref_scanner3d_create(self.h, model.max_beams)
+        try:
+            self.L.ref_scanner3d_model(h, int(model.model_type != 0), model.z_hit, model.z_rand, model.sigma_hit,
+                                       model.gompertz_a, model.gompertz_b, model.gompertz_c, model.input_shift,
+                                       model.input_scale, model.output_shift)
+            self.L.ref_scanner3d_set_map_factors(h, model.off_map_factor, 1.0, 0.0)
+            t = (C.c_double * 3)(*model.mount_translation)
+            q = (C.c_double * 4)(*model.mount_rotation)
+            self.L.ref_scanner3d_set_mount(h, t, q)
+            s = np.array(samples, dtype=np.float64, order="C")
+            pts = np.ascontiguousarray(points, np.float32)
+            total = self.L.ref_scanner3d_apply(h, _ptr(pts), len(pts), _ptr(s), len(s))
+            return total, s[:, 3].copy()
+        finally:
+            self.L.ref_scanner3d_destroy(h)
 
 
 def cloud_model(model_type=0, max_beams=4096, z_hit=0.95, z_rand=0.05, sigma_hit=0.2,

@@ -11,6 +11,8 @@
 //   include/amcl/pf/pf_kdtree.h:46-51           PFKDTree
 //   include/amcl/pf/particle_filter.h:96-130    ParticleFilter
 //   include/amcl/sensors/planar_scanner.h:62-96 PlanarScanner
+//   include/amcl/sensors/point_cloud_scanner.h:59-78 PointCloudScanner (its tf2 / pcl dependencies are the header-only
+//                                               look-alikes under oracle/shim/)
 #include <atomic>
 #include <cmath>
 #include <cstdint>
@@ -34,6 +36,7 @@
 #include "pf/pf_kdtree.h"
 #include "sensors/odom.h"
 #include "sensors/planar_scanner.h"
+#include "sensors/point_cloud_scanner.h"
 #undef private
 #undef protected
 
@@ -61,6 +64,10 @@ struct Map3D
 struct Scanner2D
 {
   std::shared_ptr<PlanarScanner> s;
+};
+struct Scanner3D
+{
+  std::shared_ptr<PointCloudScanner> s;
 };
 struct PF
 {
@@ -385,6 +392,65 @@ double ref_scanner2d_apply(void* h, const double* ranges, const double* angles, 
     set->samples[k].weight = samples_aos[4 * k + 3];
   }
   double total = static_cast<Scanner2D*>(h)->s->applyModelToSampleSet(make_scan(ranges, angles, n_ranges, range_max), set);
+  for (long k = 0; k < n_samples; k++)
+    samples_aos[4 * k + 3] = set->samples[k].weight;
+  return total;
+}
+
+// ---------------------------------------------------------------- PointCloudScanner
+void* ref_scanner3d_create(void* map3d, int max_beams)
+{
+  Scanner3D* h = new Scanner3D();
+  h->s = std::make_shared<PointCloudScanner>();
+  h->s->init(max_beams, static_cast<Map3D*>(map3d)->m);
+  return h;
+}
+void ref_scanner3d_destroy(void* h) { delete static_cast<Scanner3D*>(h); }
+void ref_scanner3d_model(void* h, int gompertz, double z_hit, double z_rand, double sigma, double a, double b, double c,
+                         double in_shift, double in_scale, double out_shift)
+{
+  PointCloudScanner& s = *static_cast<Scanner3D*>(h)->s;
+  if (gompertz)
+    s.setPointCloudModelGompertz(z_hit, z_rand, sigma, a, b, c, in_shift, in_scale, out_shift);
+  else
+    s.setPointCloudModel(z_hit, z_rand, sigma);
+}
+void ref_scanner3d_set_map_factors(void* h, double off_map, double non_free, double radius)
+{
+  static_cast<Scanner3D*>(h)->s->setMapFactors(off_map, non_free, radius);
+}
+void ref_scanner3d_set_mount(void* h, const double* translation3, const double* quaternion_xyzw)
+{
+  geometry_msgs::Transform t;
+  t.translation.x = translation3[0];
+  t.translation.y = translation3[1];
+  t.translation.z = translation3[2];
+  t.rotation.x = quaternion_xyzw[0];
+  t.rotation.y = quaternion_xyzw[1];
+  t.rotation.z = quaternion_xyzw[2];
+  t.rotation.w = quaternion_xyzw[3];
+  static_cast<Scanner3D*>(h)->s->setPointCloudScannerToFootprintTF(t);
+}
+// PointCloudScanner::applyModelToSampleSet (point_cloud_scanner.cpp:111-129) on a free-standing sample set
+// (AoS x, y, theta, w), no normalisation. points = packed float x, y, z in the sensor frame. Returns the model's total.
+double ref_scanner3d_apply(void* h, const float* points, long n_points, double* samples_aos, long n_samples)
+{
+  std::shared_ptr<PointCloudData> data = std::make_shared<PointCloudData>();
+  data->frame_id_ = "scanner";
+  data->points_.points.resize(n_points);
+  for (long k = 0; k < n_points; k++)
+    data->points_.points[k] = pcl::PointXYZ(points[3 * k], points[3 * k + 1], points[3 * k + 2]);
+  data->points_.width = static_cast<uint32_t>(n_points);
+  data->points_.height = 1;
+  std::shared_ptr<PFSampleSet> set = std::make_shared<PFSampleSet>();
+  set->sample_count = static_cast<int>(n_samples);
+  set->samples.resize(n_samples);
+  for (long k = 0; k < n_samples; k++)
+  {
+    set->samples[k].pose = Eigen::Vector3d(samples_aos[4 * k], samples_aos[4 * k + 1], samples_aos[4 * k + 2]);
+    set->samples[k].weight = samples_aos[4 * k + 3];
+  }
+  const double total = static_cast<Scanner3D*>(h)->s->applyModelToSampleSet(data, set);
   for (long k = 0; k < n_samples; k++)
     samples_aos[4 * k + 3] = set->samples[k].weight;
   return total;

@@ -1,0 +1,2 @@
+// oracle/shim: TEST INFRASTRUCTURE ONLY.
+#pragma once

@@ -107,6 +107,22 @@ def main():
     m3.update_distances()
     mn, mx = m3.bounds()
     np.savez_compressed(os.path.join(HERE, "octomap_3d.npz"), keys=keys, field=m3.dense(), mn=np.array(mn), mx=np.array(mx))
+    # 3-D scorer: the UNMODIFIED sensors/point_cloud_scanner.cpp (applyModelToSampleSet :111-129, calcPointCloudModel /
+    # Gompertz :132-203, recalcWeight :205-229) over that cache; its tf2 / pcl calls resolve to oracle/shim/
+    cpts = synth.make_cloud(keys, RES, (0.3, -0.2, 0.4), n_points=384)
+    rng = np.random.default_rng(5)
+    cs = np.zeros((400, 4))
+    cs[:, 0], cs[:, 1], cs[:, 2] = rng.uniform(-1.8, 1.8, 400), rng.uniform(-1.5, 1.5, 400), rng.uniform(-3.2, 3.2, 400)
+    cs[:150, :3] = np.array((0.3, -0.2, 0.4)) + rng.normal(0.0, 0.1, (150, 3))
+    cs[-5:, 0] += 40.0  # off the map: the off-map factor of recalcWeight
+    cs[:, 3] = 1.0 / len(cs)
+    cout = dict(points=cpts, samples=cs)
+    for name, mt in (("plain", 0), ("gompertz", 1)):
+        cm = O.cloud_model(model_type=mt, max_beams=384, off_map_factor=0.3, gompertz=(1.0, 2.0, 6.0, -0.2, 1.3, 0.05),
+                           mount_translation=(0.2, 0.0, 1.5), mount_rotation=synth.rpy_quaternion(0.0, 0.1, 0.0))
+        total, w = m3.cloud_apply(cm, cpts, cs)
+        cout["total_" + name], cout["w_" + name] = total, w
+    np.savez_compressed(os.path.join(HERE, "cloud_3d.npz"), **cout)
     # motion update (odom.cpp:74-311): five models x three odometry deltas on one small cloud, drand48 seeded per case;
     # `next` = the drand48() value after the update (pins the number of draws consumed)
     mposes = synth.gaussian_poses((1.5, -0.7, 0.4), 400, seed=9)

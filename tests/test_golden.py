@@ -211,3 +211,42 @@ def test_gpu_octomap_cache_vs_golden(dev):
     m.upload_distances(g["field"])
     assert np.array_equal(m.download_distances(), g["field"])
     m.close()
+
+
+def test_port_cloud_scorer_equals_golden(oracle_built):
+    """the restatement against outputs of the UNMODIFIED sensors/point_cloud_scanner.cpp (tests/golden/make_golden.py)"""
+    O = oracle_built
+    g3, gc = np.load(os.path.join(HERE, "octomap_3d.npz")), np.load(os.path.join(HERE, "cloud_3d.npz"))
+    m = O.PortMap3D(RES, g3["keys"], 0.36)
+    m.set_dense(g3["field"])
+    from badger_amcl_b200 import synth
+    for name, mt in (("plain", 0), ("gompertz", 1)):
+        cm = O.cloud_model(model_type=mt, max_beams=384, off_map_factor=0.3, gompertz=(1.0, 2.0, 6.0, -0.2, 1.3, 0.05),
+                           mount_translation=(0.2, 0.0, 1.5), mount_rotation=synth.rpy_quaternion(0.0, 0.1, 0.0))
+        total, w = m.cloud_apply(cm, gc["points"], gc["samples"])
+        assert total == float(gc["total_" + name])
+        assert np.array_equal(w, gc["w_" + name])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,mt", [("plain", 0), ("gompertz", 1)])
+def test_gpu_cloud_scorer_vs_golden(dev, name, mt):
+    """point_cloud_scanner.cpp:111-229 on the device against the compiled reference's weights (log-weights 1e-5)"""
+    from badger_amcl_b200 import synth
+    cabi = dev["cabi"]
+    g3, gc = np.load(os.path.join(HERE, "octomap_3d.npz")), np.load(os.path.join(HERE, "cloud_3d.npz"))
+    m = cabi.Map3D(dev["ctx"], RES, g3["keys"], 0.36)
+    m.upload_distances(g3["field"])
+    cm = cabi.cloud_model(model_type=mt, max_beams=384, off_map_factor=0.3, gompertz=(1.0, 2.0, 6.0, -0.2, 1.3, 0.05),
+                          mount_translation=(0.2, 0.0, 1.5), mount_rotation=synth.rpy_quaternion(0.0, 0.1, 0.0))
+    s = gc["samples"]
+    pf = cabi.ParticleFilter(dev["ctx"], len(s) // 10, len(s))
+    pf.upload_samples(s)
+    total = pf.score_cloud(m, cm, gc["points"])
+    got, want = pf.weights(), gc["w_" + name]
+    lg, lw = np.log(got), np.log(want)
+    assert (np.abs(lg - lw) <= 1e-5 * np.abs(lw)).all()
+    assert (np.abs(got - want) <= 1e-9 * want).mean() > 0.99
+    assert abs(total - float(gc["total_" + name])) <= 1e-6 * abs(float(gc["total_" + name]))
+    pf.close()
+    m.close()

@@ -259,3 +259,30 @@ def test_resample_with_the_nodes_pose_function_bit_exact(world, systematic, thr,
         assert np.array_equal(a.samples(), b.samples())
         assert (a.resample_sources() < 0).sum() > 0
         assert O.port_lib().orc_drand48(C.byref(a.rng)) == O.ref_lib().ref_drand48()
+
+
+@pytest.mark.parametrize("model_type", [0, 1])
+def test_cloud_scorer_bit_exact(world, model_type):
+    """sensors/point_cloud_scanner.cpp compiled UNMODIFIED (its tf2 / pcl calls resolve to oracle/shim) == the restatement,
+    bit for bit: applyModelToSampleSet :111-129, calcPointCloudModel / Gompertz :132-203, recalcWeight :205-229"""
+    O = world["O"]
+    from badger_amcl_b200 import synth
+    keys = synth.make_voxel_world(240, 200, 40, seed=3, wall_every=60)
+    ref = O.RefMap3D(0.05, keys, 0.36)
+    ref.update_distances()
+    port = O.PortMap3D(0.05, keys, 0.36)
+    port.set_dense(ref.dense())
+    truth = (0.3, -0.2, 0.4)
+    pts = synth.make_cloud(keys, 0.05, truth, n_points=512)
+    rng = np.random.default_rng(1)
+    n = 300
+    s = np.zeros((n, 4))
+    s[:, 0], s[:, 1], s[:, 2], s[:, 3] = rng.uniform(-6, 6, n), rng.uniform(-5, 5, n), rng.uniform(-3.2, 3.2, n), 1.0 / n
+    s[:100, :3] = np.array(truth) + rng.normal(0, 0.2, (100, 3))
+    s[-3:, 0] += 50.0  # off the map
+    m = O.cloud_model(model_type=model_type, max_beams=512, mount_translation=(0.2, 0.0, 1.5),
+                      mount_rotation=synth.rpy_quaternion(0, 0.1, 0), off_map_factor=0.7, gompertz=(1.0, 2.0, 3.0, -0.5, 1.5, 0.1))
+    t_ref, w_ref = ref.cloud_apply(m, pts, s)
+    t_port, w_port = port.cloud_apply(m, pts, s)
+    assert t_ref == t_port
+    assert np.array_equal(w_ref, w_port)

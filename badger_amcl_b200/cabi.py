@@ -128,6 +128,8 @@ SIGNATURES = {
     "bamcl_bench_gather": (_I, [_P, C.c_size_t, _L, _P]),
     "bamcl_host_alloc": (_I, [C.c_size_t, _P]),
     "bamcl_host_free": (_I, [_P]),
+    "bamcl_host_register": (_I, [_P, C.c_size_t]),
+    "bamcl_host_unregister": (_I, [_P]),
     "bamcl_pf_last_score_ms": (_I, [_P, _P]),
     "bamcl_pf_set_exact_terms": (_I, [_P, _I]),
     "bamcl_map2d_create": (_I, [_P, _I, _I, _D, _F, _F, _P]),

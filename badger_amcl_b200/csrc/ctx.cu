@@ -169,6 +169,21 @@ int bamcl_host_free(void* p)
   return BAMCL_OK;
 }
 
+int bamcl_host_register(void* p, size_t bytes)
+{
+  if (!p || bytes == 0)
+    return set_error(BAMCL_E_ARG, "bamcl_host_register: bad arguments");
+  BAMCL_CUDA_OK(cudaHostRegister(p, bytes, cudaHostRegisterDefault));
+  return BAMCL_OK;
+}
+
+int bamcl_host_unregister(void* p)
+{
+  if (p)
+    BAMCL_CUDA_OK(cudaHostUnregister(p));
+  return BAMCL_OK;
+}
+
 long bamcl_ctx_launch_count(bamcl_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
 int bamcl_ctx_flush_l2(bamcl_ctx* ctx)

@@ -556,8 +556,9 @@ __global__ void __launch_bounds__(ST_BLOCK) k_labels_stats(const StatsArgs a)
       v[q] = 0.0;
     if (live)
     {
+      // (node < 0: the sample's bin lies outside the sticky dense box; the build is flagged and repeated with a re-fitted box)
       const int node = a.hnode[a.slot[i]];
-      label = a.cid[a.parent[node]];
+      label = node >= 0 ? a.cid[a.parent[node]] : -1;
       a.label[i] = label;
       const double px = a.x[i], py = a.y[i], pt = a.th[i], pw = a.w[i];
       double sn, cs;

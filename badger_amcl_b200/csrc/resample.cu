@@ -197,16 +197,20 @@ struct CdfHdr  // what a rank publishes before tiles can be classified
 static_assert(sizeof(CdfHdr) == 64, "CdfHdr is exchanged as 64 bytes");
 
 // per-rank tile summary in ONE buffer (one all-gather ships it):
-//   d0[T] d1[T] | slow_w[w_cap * CDF_TILE] | tile_e[T] | slow_tile[cap] | meta[4] = {n_slow, overflow, 0, 0}
+//   d0[T] d1[T] s0[T] s1[T] wk[T] | slow_w[w_cap * CDF_TILE] | tile_e[T] split_e[T] | slow_tile[cap] | meta[4]
+// meta = {n_slow, overflow, 0, 0}. A tile is fast (tile_e = its binade: (d0, d1) is its aggregate function), split
+// (tile_e = INT_MIN, split_e = the binade it starts in: exactly one binade crossing at a known element -- (d0, d1) = the
+// elements before it, wk = the crossing element's weight, (s0, s1) = the elements after it, in the next binade), or slow
+// (both INT_MIN: its raw weights are walked by the sequential-rounding loop).
 struct CdfPack
 {
-  long long *d0, *d1;
-  double* slow_w;
-  int *tile_e, *slow_tile, *meta;
+  long long *d0, *d1, *s0, *s1;
+  double *wk, *slow_w;
+  int *tile_e, *split_e, *slow_tile, *meta;
 };
 __host__ __device__ inline size_t cdf_pack_bytes(int T, int cap, int w_cap)
 {
-  const size_t b = (size_t)T * 16 + (size_t)w_cap * CDF_TILE * 8 + (size_t)T * 4 + (size_t)cap * 4 + 16;
+  const size_t b = (size_t)T * 40 + (size_t)w_cap * CDF_TILE * 8 + (size_t)T * 8 + (size_t)cap * 4 + 16;
   return (b + 15) & ~(size_t)15;
 }
 __host__ __device__ inline CdfPack cdf_pack_at(void* base, int T, int cap, int w_cap)
@@ -214,9 +218,13 @@ __host__ __device__ inline CdfPack cdf_pack_at(void* base, int T, int cap, int w
   CdfPack p;
   p.d0 = static_cast<long long*>(base);
   p.d1 = p.d0 + T;
-  p.slow_w = reinterpret_cast<double*>(p.d1 + T);
+  p.s0 = p.d1 + T;
+  p.s1 = p.s0 + T;
+  p.wk = reinterpret_cast<double*>(p.s1 + T);
+  p.slow_w = p.wk + T;
   p.tile_e = reinterpret_cast<int*>(p.slow_w + (size_t)w_cap * CDF_TILE);
-  p.slow_tile = p.tile_e + T;
+  p.split_e = p.tile_e + T;
+  p.slow_tile = p.split_e + T;
   p.meta = p.slow_tile + cap;
   return p;
 }
@@ -294,6 +302,8 @@ __global__ void __launch_bounds__(1024) k_cdf_classify(const double* __restrict_
   // every approximate value is within err of the sequentially rounded one (n roundings of at most u * total each, and
   // as many again for the tree-shaped sums)
   const double err = 2.0 * units * 1.1102230246251565e-16 * total_all;
+  if (threadIdx.x == 0)
+    starts[n_tiles + 1] = err;  // k_cdf_tile_fns needs the same bound
   int slow = 0;
   for (int i = lo; i < hi; i++)
   {
@@ -459,9 +469,13 @@ __device__ double slow_tile_scan(double s, const double (&wv)[CDF_ITEMS], int ti
 }
 
 __global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tile_fns(const double* __restrict__ w, int n, CdfPack pack, int w_cap,
-                                                            const int* __restrict__ tile_slot)
+                                                            const int* __restrict__ tile_slot, const double* __restrict__ starts,
+                                                            int n_tiles)
 {
   __shared__ Fn s_warp[CDF_BLOCK / 32 + 1];
+  __shared__ double s_wsum[CDF_BLOCK / 32];
+  __shared__ int s_k;
+  __shared__ double s_pk;
   const int t = blockIdx.x;
   const int idx0 = t * CDF_TILE + threadIdx.x * CDF_ITEMS;
   double wv[CDF_ITEMS];
@@ -482,11 +496,92 @@ __global__ void __launch_bounds__(CDF_BLOCK) k_cdf_tile_fns(const double* __rest
     {
       pack.d0[t] = agg.d0;
       pack.d1[t] = agg.d1;
+      pack.split_e[t] = INT_MIN;
+    }
+    return;
+  }
+  // ---- a tile that may cross a binade. If it crosses exactly ONE boundary, at an element the approximate prefix sums
+  // place beyond doubt, it is summarised as (function before, crossing weight, function after) and costs the resolve
+  // step O(1); otherwise its raw weights go to the sequential-rounding loop.
+  const double err = starts[n_tiles + 1];
+  const double a0 = starts[t] - err, b0 = starts[t + 1] + err;
+  bool candidate = a0 > 2.2250738585072014e-308 && isfinite(b0) && exponent_of(b0) == exponent_of(a0) + 1;
+  const int e_lo = candidate ? exponent_of(a0) : 0;
+  const double boundary = candidate ? scalbn(1.0, e_lo + 1) : 0.0;
+  // approximate inclusive prefix of every element: thread-local running sums + a block scan of the thread totals
+  double run[CDF_ITEMS], tot = 0.0;
+#pragma unroll
+  for (int k = 0; k < CDF_ITEMS; k++)
+  {
+    tot += wv[k];
+    run[k] = tot;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double inc = tot;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1)
+  {
+    const double v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o)
+      inc += v;
+  }
+  if (lane == 31)
+    s_wsum[warp] = inc;
+  if (threadIdx.x == 0)
+    s_k = INT_MAX;
+  __syncthreads();
+  double base = starts[t] + (inc - tot);
+  for (int q = 0; q < warp; q++)
+    base += s_wsum[q];
+  const int tile_n = min(CDF_TILE, n - t * CDF_TILE);
+  int first = INT_MAX;
+#pragma unroll
+  for (int k = CDF_ITEMS - 1; k >= 0; k--)
+    if (threadIdx.x * CDF_ITEMS + k < tile_n && base + run[k] + err >= boundary)
+      first = threadIdx.x * CDF_ITEMS + k;
+  if (candidate && first != INT_MAX)
+    atomicMin(&s_k, first);
+  __syncthreads();
+  const int kc = s_k;
+  if (kc != INT_MAX && kc / CDF_ITEMS == (int)threadIdx.x)
+    s_pk = base + run[kc % CDF_ITEMS];
+  __syncthreads();
+  // beyond doubt: every earlier element stays below the boundary even with +err (by construction of kc), and element kc
+  // is above it even with -err
+  const bool split = candidate && kc != INT_MAX && s_pk - err >= boundary;
+  if (split)
+  {
+    Fn before, after;
+    before.d0 = before.d1 = after.d0 = after.d1 = 0;
+#pragma unroll
+    for (int k = 0; k < CDF_ITEMS; k++)
+    {
+      const int li = threadIdx.x * CDF_ITEMS + k;
+      if (li < kc)
+        before = compose(before, elem_fn(wv[k], e_lo));
+      else if (li > kc && li < tile_n)
+        after = compose(after, elem_fn(wv[k], e_lo + 1));
+    }
+    Fn agg_b, agg_a;
+    block_scan_fn(before, s_warp, &agg_b);
+    block_scan_fn(after, s_warp, &agg_a);
+    if (kc / CDF_ITEMS == (int)threadIdx.x)
+      pack.wk[t] = wv[kc % CDF_ITEMS];
+    if (threadIdx.x == 0)
+    {
+      pack.d0[t] = agg_b.d0;
+      pack.d1[t] = agg_b.d1;
+      pack.s0[t] = agg_a.d0;
+      pack.s1[t] = agg_a.d1;
+      pack.split_e[t] = e_lo;
     }
     return;
   }
   if (threadIdx.x == 0)
+  {
     pack.d0[t] = pack.d1[t] = 0;
+    pack.split_e[t] = INT_MIN;
+  }
   const int slot = tile_slot[t];
   if (slot >= 0 && slot < w_cap)
   {
@@ -560,7 +655,39 @@ __global__ void __launch_bounds__(CDF_BLOCK) k_cdf_resolve(const ResolveArgs a)
         s = normal ? from_units(m_out, e) : s;
         t += chunk;
       }
-      if (t < tiles)
+      if (t < tiles && p.split_e[t] != INT_MIN)
+      {
+        // a split tile: function before the crossing, the crossing add as a real FP add, function after it
+        if (q == a.me && threadIdx.x == 0)
+          a.starts[t] = s;
+        const int e0 = p.split_e[t];
+        bool ok = s >= 2.2250738585072014e-308 && isfinite(s) && exponent_of(s) == e0;
+        double v = s;
+        if (ok)
+        {
+          Fn fb, fa;
+          fb.d0 = p.d0[t];
+          fb.d1 = p.d1[t];
+          fa.d0 = p.s0[t];
+          fa.d1 = p.s1[t];
+          const long long m0 = mantissa_of(s);
+          const long long m1 = m0 + fn_at(fb, m0);
+          ok = m1 < TWO53;
+          const double before = from_units(m1, e0);
+          const double after = before + p.wk[t];  // the crossing step, as the reference takes it
+          ok = ok && isfinite(after) && exponent_of(after) == e0 + 1;
+          const long long m2 = mantissa_of(after);
+          const long long m3 = m2 + fn_at(fa, m2);
+          ok = ok && m3 < TWO53;
+          v = from_units(m3, e0 + 1);
+        }
+        if (!ok && threadIdx.x == 0)
+          atomicOr(a.flags, 2);  // the summary's assumptions do not hold for the exact value: report, never guess
+        s = v;
+        t++;
+        k++;
+      }
+      else if (t < tiles)
       {
         // the slow tile t: sequential-rounding loop over its raw weights
         if (q == a.me && threadIdx.x == 0)
@@ -888,10 +1015,10 @@ int pf_build_cdf(bamcl_pf* pf)
   const int cap = G > 1 ? std::min(pf->cdf_slow_cap, T) : T;
   const int w_cap = G > 1 ? cap : 0;
   const size_t pack_bytes = cdf_pack_bytes(T, cap, w_cap);
-  // scratch: hdrs[G] | packs[G] | sums[T] starts[T+1] exact[T] bounds[G+1] | tile_slot[T]
+  // scratch: hdrs[G] | packs[G] | sums[T] starts[T+2] exact[T] bounds[G+1] | tile_slot[T]
   const size_t off_packs = (size_t)G * sizeof(CdfHdr);
   const size_t off_d = off_packs + (size_t)G * pack_bytes;
-  const size_t n_d = (size_t)T * 3 + 1 + (size_t)G + 1;
+  const size_t n_d = (size_t)T * 3 + 2 + (size_t)G + 1;
   const size_t off_i = off_d + n_d * sizeof(double);
   BAMCL_TRY(pf->scratch.reserve(off_i + sizeof(int) * (size_t)T + 64));
   char* base = pf->scratch.as<char>();
@@ -899,7 +1026,7 @@ int pf_build_cdf(bamcl_pf* pf)
   char* packs = base + off_packs;
   double* sums = reinterpret_cast<double*>(base + off_d);
   double* starts = sums + T;
-  double* exact = starts + T + 1;
+  double* exact = starts + T + 2;
   double* bounds = exact + T;
   int* tile_slot = reinterpret_cast<int*>(base + off_i);
   int* flags = pf_flags(pf);
@@ -913,7 +1040,7 @@ int pf_build_cdf(bamcl_pf* pf)
     BAMCL_TRY(comm_all_gather(comm, hdrs + me, hdrs, sizeof(CdfHdr)));
   BAMCL_LAUNCH(ctx, k_cdf_classify, 1, 1024, 0, sums, tiles, hdrs, me, G, starts, mine, cap, tile_slot);
   if (tiles > 0)
-    BAMCL_LAUNCH(ctx, k_cdf_tile_fns, tiles, CDF_BLOCK, 0, w, n, mine, w_cap, tile_slot);
+    BAMCL_LAUNCH(ctx, k_cdf_tile_fns, tiles, CDF_BLOCK, 0, w, n, mine, w_cap, tile_slot, starts, tiles);
   if (G > 1)
     BAMCL_TRY(comm_all_gather(comm, packs + (size_t)me * pack_bytes, packs, pack_bytes));
   ResolveArgs ra;

@@ -135,4 +135,18 @@ private:
 }  // namespace octomap
 #endif
 
+
+// The reference's hot path raises no exceptions: updateSensor returns false, a model returns 0.0, and
+// nothing else happens. The mirror keeps that contract: a device failure on the path (updateSensor, updateResample,
+// updateAction, the lazy sample synchronisation) is recorded here and the call returns like the reference's own failure
+// paths, leaving the filter's weights untouched. Set-up calls (maps, constructors) still throw: without a CUDA device
+// there is nothing to fall back to.
+namespace badger_amcl
+{
+const char* lastDeviceError();  // "" while nothing failed since clearDeviceError()
+void clearDeviceError();
+bool deviceOk(int rc, const char* what);  // records bamcl_last_error() and returns false when rc != 0
+void deviceFail(const char* what);
+}  // namespace badger_amcl
+
 #endif  // BAMCL_AMCL_COMPAT_H

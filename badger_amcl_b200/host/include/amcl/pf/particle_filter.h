@@ -55,6 +55,7 @@ struct PFSampleSet
   int converged;
   ParticleFilter* owner;  // device port: the filter whose device set this mirrors
   bool device_scored;     // device port: a device sensor model has updated the weights since the last sync
+  bool device_failed = false;  // device port: the last sensor model call failed on the device (see lastDeviceError())
 };
 
 class SensorData;
@@ -106,6 +107,7 @@ private:
   void installStats(const void* resample_result);
   void pullToHost();
   bamcl_pf* dev_;
+  void* pinned_samples_ = nullptr;  // the samples vector's storage while it is page-locked
   int min_samples_, max_samples_;
   double pop_err_, pop_z_;
   double w_slow_, w_fast_, alpha_slow_, alpha_fast_;

@@ -7,6 +7,7 @@
 #include <stdexcept>
 #include <string>
 
+#include "amcl/compat.h"
 #include "amcl/map/occupancy_map.h"
 #include "amcl/map/octomap.h"
 #include "amcl/pf/particle_filter.h"
@@ -18,6 +19,18 @@ static void check(int rc, const char* what)
 {
   if (rc != BAMCL_OK)
     throw std::runtime_error(std::string(what) + ": " + bamcl_last_error());
+}
+
+static thread_local std::string g_device_error;
+const char* lastDeviceError() { return g_device_error.c_str(); }
+void clearDeviceError() { g_device_error.clear(); }
+void deviceFail(const char* what) { g_device_error = what; }
+bool deviceOk(int rc, const char* what)
+{
+  if (rc == BAMCL_OK)
+    return true;
+  g_device_error = std::string(what) + ": " + bamcl_last_error();
+  return false;
 }
 
 bamcl_ctx* deviceContext()

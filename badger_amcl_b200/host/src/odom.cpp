@@ -7,6 +7,7 @@
 #include <stdexcept>
 #include <string>
 
+#include "amcl/compat.h"
 #include "bamcl.h"
 
 namespace badger_amcl
@@ -59,8 +60,8 @@ bool Odom::updateAction(std::shared_ptr<ParticleFilter> pf, std::shared_ptr<Sens
   seed48(saved);
   const uint64_t state = (uint64_t)saved[0] | ((uint64_t)saved[1] << 16) | ((uint64_t)saved[2] << 32);
   uint64_t next = state;
-  if (bamcl_pf_update_action(pf->deviceHandle(), &model, &od, state, &next) != BAMCL_OK)
-    throw std::runtime_error(std::string("bamcl_pf_update_action: ") + bamcl_last_error());
+  if (!deviceOk(bamcl_pf_update_action(pf->deviceHandle(), &model, &od, state, &next), "bamcl_pf_update_action"))
+    return false;  // nothing moved, libc's generator untouched (lastDeviceError() says why)
   unsigned short st[3] = {(unsigned short)(next & 0xFFFF), (unsigned short)((next >> 16) & 0xFFFF),
                           (unsigned short)((next >> 32) & 0xFFFF)};
   seed48(st);

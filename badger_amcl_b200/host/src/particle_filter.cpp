@@ -8,6 +8,7 @@
 #include <stdexcept>
 #include <string>
 
+#include "amcl/compat.h"
 #include "amcl/pf/particle_filter.h"
 #include "amcl/pf/pdf_gaussian.h"
 #include "amcl/sensors/sensor.h"
@@ -228,6 +229,10 @@ ParticleFilter::ParticleFilter(int min_samples, int max_samples, double alpha_sl
   set_ = std::make_shared<PFSampleSet>();
   set_->sample_count = max_samples_;
   set_->samples.resize((size_t)max_samples_);
+  // the public AoS vector is the reference's type; page-locking it in place makes its lazy copies run at PCIe rate
+  // (it never reallocates: every later resize stays within max_samples)
+  if (bamcl_host_register(set_->samples.data(), sizeof(PFSample) * (size_t)max_samples_) == BAMCL_OK)
+    pinned_samples_ = set_->samples.data();
   for (int i = 0; i < max_samples_; i++)  // particle_filter.cpp:69-79 (the device set is created in the same state)
   {
     set_->samples[i].pose = Eigen::Vector3d(0.0, 0.0, 0.0);
@@ -243,6 +248,8 @@ ParticleFilter::ParticleFilter(int min_samples, int max_samples, double alpha_sl
 
 ParticleFilter::~ParticleFilter()
 {
+  if (pinned_samples_)
+    bamcl_host_unregister(pinned_samples_);
   if (dev_)
     bamcl_pf_destroy(dev_);
 }
@@ -272,8 +279,9 @@ void ParticleFilter::pushIfHostDirty()
 {
   if (!host_dirty_)
     return;
-  check(bamcl_pf_upload_samples(dev_, reinterpret_cast<const double*>(set_->samples.data()), set_->sample_count),
-        "bamcl_pf_upload_samples");
+  if (!deviceOk(bamcl_pf_upload_samples(dev_, reinterpret_cast<const double*>(set_->samples.data()), set_->sample_count),
+                "bamcl_pf_upload_samples"))
+    return;  // the host copy stays the valid one
   host_dirty_ = false;
   host_valid_ = true;
 }
@@ -283,12 +291,14 @@ void ParticleFilter::pullToHost()
   if (host_valid_)
     return;
   int n = 0;
-  check(bamcl_pf_sample_count(dev_, &n), "bamcl_pf_sample_count");
+  if (!deviceOk(bamcl_pf_sample_count(dev_, &n), "bamcl_pf_sample_count"))
+    return;
   set_->sample_count = n;
   if ((int)set_->samples.size() < n)
     set_->samples.resize((size_t)n);
-  if (n > 0)
-    check(bamcl_pf_download_samples(dev_, reinterpret_cast<double*>(set_->samples.data()), n), "bamcl_pf_download_samples");
+  if (n > 0 && !deviceOk(bamcl_pf_download_samples(dev_, reinterpret_cast<double*>(set_->samples.data()), n),
+                         "bamcl_pf_download_samples"))
+    return;
   host_valid_ = true;
   set_->device_scored = false;
 }
@@ -391,20 +401,28 @@ void ParticleFilter::updateSensor(std::function<double(std::shared_ptr<SensorDat
   // and flag it; any other functor gets the host mirror, as in the reference, and its weights are uploaded.
   pushIfHostDirty();
   set_->device_scored = false;
+  set_->device_failed = false;
   const double total = sensor_fn(sensor_data, set_);
+  if (set_->device_failed)
+    return;  // the device could not score (lastDeviceError()): weights untouched, no exception
   if (!set_->device_scored)
   {
     if (!host_valid_)
-      throw std::logic_error("ParticleFilter::updateSensor: functor neither scored on the device nor had a valid host set");
+    {
+      deviceFail("ParticleFilter::updateSensor: functor neither scored on the device nor had a valid host set");
+      return;
+    }
     host_dirty_ = true;
     pushIfHostDirty();
   }
-  check(bamcl_pf_normalise(dev_, total), "bamcl_pf_normalise");  // w /= total, or 1/n each (:237-266)
+  if (!deviceOk(bamcl_pf_normalise(dev_, total), "bamcl_pf_normalise"))  // w /= total, or 1/n each (:237-266)
+    return;
   host_valid_ = false;
   if (total > 0.0)
   {
     int n = 0;
-    check(bamcl_pf_sample_count(dev_, &n), "bamcl_pf_sample_count");
+    if (!deviceOk(bamcl_pf_sample_count(dev_, &n), "bamcl_pf_sample_count") || n <= 0)
+      return;
     const double w_avg = total / n;  // the reference's w_avg is the same sum of the un-normalised weights
     if (w_slow_ == 0.0)
       w_slow_ = w_avg;
@@ -463,12 +481,16 @@ void ParticleFilter::updateResample()
     }
   }
   else if (w_diff > 0.0)
-    throw std::runtime_error("multinomial resampling with random-pose injection interleaves drand48 with "
-                             "random_pose_fn_ per sample (particle_filter.cpp:385-393): not available on the device");
+  {
+    deviceFail("multinomial resampling with random-pose injection interleaves drand48 with random_pose_fn_ per sample "
+               "(particle_filter.cpp:385-393): register the node's pose source (setDevicePoseSource) to run it on the device");
+    return;  // the set is left as it was
+  }
   prm.random_poses = random_poses.empty() ? nullptr : random_poses.data();
   prm.n_random_poses = (long)(random_poses.size() / 3);
   bamcl_resample_result res;
-  check(bamcl_pf_resample(dev_, &prm, &res), "bamcl_pf_resample");
+  if (!deviceOk(bamcl_pf_resample(dev_, &prm, &res), "bamcl_pf_resample"))
+    return;  // the set is left as it was
   if (!prm.resample_systematic || (device_pose_source_ && w_diff > 0.0))
   {
     // draws were consumed on the device: advance libc's generator to the returned state

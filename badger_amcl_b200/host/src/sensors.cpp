@@ -8,16 +8,11 @@
 
 #include "amcl/sensors/planar_scanner.h"
 #include "amcl/sensors/point_cloud_scanner.h"
+#include "amcl/compat.h"
 #include "bamcl.h"
 
 namespace badger_amcl
 {
-static void check(int rc, const char* what)
-{
-  if (rc != BAMCL_OK)
-    throw std::runtime_error(std::string(what) + ": " + bamcl_last_error());
-}
-
 // ------------------------------------------------------------------------------------------ PlanarScanner
 PlanarScanner::PlanarScanner()
     : model_type_(PLANAR_MODEL_BEAM), planar_scanner_pose_(0.0, 0.0, 0.0), max_beams_(0), do_beamskip_(false),
@@ -121,7 +116,10 @@ double PlanarScanner::applyModelToSampleSet(std::shared_ptr<SensorData> data, st
     return 0.0;
   std::shared_ptr<PlanarData> ndata = std::dynamic_pointer_cast<PlanarData>(data);
   if (!ndata || !set || !set->owner)
-    throw std::invalid_argument("PlanarScanner::applyModelToSampleSet: need PlanarData and a set owned by a ParticleFilter");
+  {
+    deviceFail("PlanarScanner::applyModelToSampleSet: need PlanarData and a set owned by a ParticleFilter");
+    return 0.0;
+  }
   ParticleFilter* pf = set->owner;
   pf->pushIfHostDirty();
   bamcl_planar_model m;
@@ -149,9 +147,13 @@ double PlanarScanner::applyModelToSampleSet(std::shared_ptr<SensorData> data, st
   for (int i = 0; i < 3; i++)
     m.scanner_pose[i] = planar_scanner_pose_[i];
   double total = 0.0;
-  check(bamcl_pf_score_planar(pf->deviceHandle(), map_->deviceHandle(), &m, ndata->ranges_.data(), ndata->angles_.data(),
-                              ndata->range_count_, ndata->range_max_, set->converged, &total),
-        "bamcl_pf_score_planar");
+  if (!deviceOk(bamcl_pf_score_planar(pf->deviceHandle(), map_->deviceHandle(), &m, ndata->ranges_.data(), ndata->angles_.data(),
+                                      ndata->range_count_, ndata->range_max_, set->converged, &total),
+                "bamcl_pf_score_planar"))
+  {
+    set->device_failed = true;  // ParticleFilter::updateSensor leaves the weights as they were
+    return 0.0;
+  }
   set->device_scored = true;
   return total;
 }
@@ -232,7 +234,10 @@ double PointCloudScanner::applyModelToSampleSet(std::shared_ptr<SensorData> data
     return 0.0;
   std::shared_ptr<PointCloudData> ndata = std::dynamic_pointer_cast<PointCloudData>(data);
   if (!ndata || !set || !set->owner)
-    throw std::invalid_argument("PointCloudScanner::applyModelToSampleSet: need PointCloudData and a set owned by a ParticleFilter");
+  {
+    deviceFail("PointCloudScanner::applyModelToSampleSet: need PointCloudData and a set owned by a ParticleFilter");
+    return 0.0;
+  }
   ParticleFilter* pf = set->owner;
   pf->pushIfHostDirty();
   bamcl_cloud_model m;
@@ -266,7 +271,11 @@ double PointCloudScanner::applyModelToSampleSet(std::shared_ptr<SensorData> data
     xyz[3 * i + 2] = ndata->points_.points[i].z;
   }
   double total = 0.0;
-  check(bamcl_pf_score_cloud(pf->deviceHandle(), map_->deviceHandle(), &m, xyz.data(), (long)n, &total), "bamcl_pf_score_cloud");
+  if (!deviceOk(bamcl_pf_score_cloud(pf->deviceHandle(), map_->deviceHandle(), &m, xyz.data(), (long)n, &total), "bamcl_pf_score_cloud"))
+  {
+    set->device_failed = true;
+    return 0.0;
+  }
   set->device_scored = true;
   return total;
 }

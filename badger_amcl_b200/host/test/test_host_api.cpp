@@ -5,6 +5,8 @@
 // macros stand in for EXPECT_*.
 //   test_host_api kats
 //   test_host_api flow <in.bin> <out.bin>
+//   test_host_api bench <in.bin> <steps> <warmup>   the node's step through the class API, timed; one JSON line
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -14,6 +16,7 @@
 #include <string>
 #include <vector>
 
+#include "amcl/compat.h"
 #include "amcl/map/occupancy_map.h"
 #include "amcl/map/octomap.h"
 #include "amcl/pf/particle_filter.h"
@@ -46,6 +49,26 @@ static bool almostEqual(double a, double b)
   return std::llabs(ia - ib) <= 4;
 }
 #define EXPECT_DOUBLE_EQ(a, b) EXPECT_TRUE(almostEqual((a), (b)))
+
+// test/test_badger_amcl.cpp:29-49 (the reference's own known-answer test; it samples the FIRST pdf twice).
+// Must run before anything else consumes the process's unseeded drand48 stream.
+static void testPdfGaussian()
+{
+  Eigen::Vector3d x(1, 1, 1);
+  Eigen::Matrix3d cx;
+  cx(0, 0) = 1; cx(0, 1) = 0; cx(0, 2) = 0;
+  cx(1, 0) = 0; cx(1, 1) = 1; cx(1, 2) = 0;
+  cx(2, 0) = 0; cx(2, 1) = 0; cx(2, 2) = 1;
+  badger_amcl::PDFGaussian pdf_gaussian(x, cx);
+  Eigen::Vector3d sample = pdf_gaussian.sample();
+  EXPECT_DOUBLE_EQ(sample[0], 0.26562654174915334);
+  EXPECT_DOUBLE_EQ(sample[1], 0.97172090090793528);
+  EXPECT_DOUBLE_EQ(sample[2], -1.5856194295513539);
+  Eigen::Vector3d sample2 = pdf_gaussian.sample();
+  EXPECT_DOUBLE_EQ(sample2[0], 1.6262083813236745);
+  EXPECT_DOUBLE_EQ(sample2[1], 1.1142314205031041);
+  EXPECT_DOUBLE_EQ(sample2[2], 0.37407538872488655);
+}
 
 static void testPfKdtree()
 {
@@ -360,6 +383,102 @@ static int odomFlow(const char* in_path, const char* out_path)
   return g_failed ? 1 : 0;
 }
 
+// The node's step (node_2d.cpp:367-380 scan callback -> PlanarScanner::updateSensor, node.cpp:337-349 -> updateResample)
+// through the class API of libbadger_amcl.so, timed on the host. Between steps the caller writes the poses through
+// getCurrentSet()->samples, as Odom::updateAction does in the reference (odom.cpp:107-121), so the mirror's lazy
+// host <-> device synchronisation of the AoS vector is inside the timed region.
+static int benchFlow(const char* in_path, int steps, int warmup)
+{
+  Reader rd;
+  {
+    FILE* f = std::fopen(in_path, "rb");
+    if (!f)
+      return 2;
+    std::fseek(f, 0, SEEK_END);
+    rd.buf.resize((size_t)std::ftell(f));
+    std::fseek(f, 0, SEEK_SET);
+    if (std::fread(rd.buf.data(), 1, rd.buf.size(), f) != rd.buf.size())
+      return 2;
+    std::fclose(f);
+  }
+  int hdr[9];
+  double par[3];
+  rd.get(hdr, 9);
+  rd.get(par, 3);
+  const int size_x = hdr[1], size_y = hdr[2], n = hdr[3], n_beams = hdr[4], min_samples = hdr[5];
+  const double resolution = par[0], max_dist = par[1], range_max = par[2];
+  std::vector<int8_t> cells((size_t)size_x * size_y);
+  rd.get(cells.data(), cells.size());
+  auto data = std::make_shared<badger_amcl::PlanarData>();
+  data->range_count_ = n_beams;
+  data->range_max_ = range_max;
+  data->ranges_.resize(n_beams);
+  data->angles_.resize(n_beams);
+  rd.get(data->ranges_.data(), n_beams);
+  rd.get(data->angles_.data(), n_beams);
+  std::vector<double> poses((size_t)3 * n);
+  rd.get(poses.data(), poses.size());
+  auto map = std::make_shared<badger_amcl::OccupancyMap>(resolution);
+  map->setSize({size_x, size_y});
+  map->setOrigin(pcl::PointXYZ(0.0, 0.0, 0.0));
+  for (int j = 0; j < size_y; j++)
+    for (int i = 0; i < size_x; i++)
+      map->setCellState(map->computeCellIndex(i, j), (badger_amcl::MapCellState)cells[(size_t)j * size_x + i]);
+  auto scanner = std::make_shared<badger_amcl::PlanarScanner>();
+  scanner->init(n_beams, map);
+  scanner->setModelLikelihoodField(0.95, 0.05, 0.2, max_dist);  // builds the distance cache (planar_scanner.cpp:55-65)
+  scanner->setPlanarScannerPose(Eigen::Vector3d(0.1, 0.0, 0.0));
+  size_t next_pose = 0;
+  auto pose_fn = [&]() {
+    const size_t k = (next_pose++) % (size_t)n;
+    return Eigen::Vector3d(poses[3 * k], poses[3 * k + 1], poses[3 * k + 2]);
+  };
+  auto random_pose_fn = [&]() { return Eigen::Vector3d(0.0, 0.0, 0.0); };
+  auto pf = std::make_shared<badger_amcl::ParticleFilter>(min_samples, n, 0.001, 0.1, 95.0, random_pose_fn);
+  pf->setResampleModel(badger_amcl::PF_RESAMPLE_SYSTEMATIC);
+  pf->setPopulationSizeParameters(0.01, 0.99);
+  double total_ms = 0.0, sync_ms = 0.0, up_ms = 0.0, rs_ms = 0.0;
+  int last_count = 0, last_leaf = 0;
+  for (int it = 0; it < warmup + steps; it++)
+  {
+    next_pose = 0;
+    pf->initWithPoseFn(pose_fn);  // the same set every step (untimed), as bench.py restores it
+    srand48(12345);
+    const auto t0 = std::chrono::steady_clock::now();
+    {
+      // the motion update's footprint on the host mirror: read + write every pose through the public AoS vector
+      auto set = pf->getCurrentSet();
+      for (int i = 0; i < set->sample_count; i++)
+        set->samples[(size_t)i].pose[0] += 0.0;
+    }
+    const auto t1 = std::chrono::steady_clock::now();
+    scanner->updateSensor(pf, data);
+    const auto t2 = std::chrono::steady_clock::now();
+    pf->updateResample();
+    const auto t3 = std::chrono::steady_clock::now();
+    if (it >= warmup)
+    {
+      sync_ms += std::chrono::duration<double, std::milli>(t1 - t0).count();
+      up_ms += std::chrono::duration<double, std::milli>(t2 - t1).count();
+      rs_ms += std::chrono::duration<double, std::milli>(t3 - t2).count();
+      total_ms += std::chrono::duration<double, std::milli>(t3 - t0).count();
+    }
+    auto set = pf->peekCurrentSet();
+    last_count = set->sample_count;
+    last_leaf = set->kdtree->getLeafCount();
+  }
+  int valid = 0;
+  for (int i = 0; i < n_beams; i++)
+    valid += data->ranges_[(size_t)i] < range_max ? 1 : 0;
+  std::printf("{\"api\": \"badger_amcl::PlanarScanner::updateSensor + ParticleFilter::updateResample (libbadger_amcl.so)\", "
+              "\"particles\": %d, \"beams\": %d, \"valid_beams\": %d, \"steps\": %d, \"ms_per_step\": %.6f, "
+              "\"host_sample_sync_ms\": %.6f, \"update_ms\": %.6f, \"resample_ms\": %.6f, \"evals_per_s\": %.6e, "
+              "\"resampled_count\": %d, \"kld_leaf_count\": %d, \"device_error\": \"%s\"}\n",
+              n, n_beams, valid, steps, total_ms / steps, sync_ms / steps, up_ms / steps, rs_ms / steps,
+              (double)n * valid / (total_ms / steps * 1e-3), last_count, last_leaf, badger_amcl::lastDeviceError());
+  return 0;
+}
+
 int main(int argc, char** argv)
 {
   const std::string mode = argc > 1 ? argv[1] : "kats";
@@ -367,6 +486,9 @@ int main(int argc, char** argv)
   {
     if (mode == "flow" && argc == 4)
       return flow(argv[2], argv[3]);
+    if (mode == "bench" && argc == 5)
+      return benchFlow(argv[2], std::atoi(argv[3]), std::atoi(argv[4]));
+    testPdfGaussian();
     if (mode == "odom" && argc == 4)
       return odomFlow(argv[2], argv[3]);
     testPfKdtree();

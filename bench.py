@@ -353,6 +353,33 @@ def leg_c4(ctx, cabi, synth, peak):
     return out
 
 
+def leg_host_api(a, cells, ranges, angles, poses, steps=5, warmup=2):
+    """the same step through the C++ class API (libbadger_amcl.so: OccupancyMap, PlanarScanner::updateSensor,
+    ParticleFilter::updateResample, node_2d.cpp:367-380) with a host-side write of the samples between steps; the
+    standalone C++ driver badger_amcl_b200/host/test/test_host_api (mode `bench`) does the timing"""
+    import struct
+    import tempfile
+    exe = os.path.join(ROOT, "badger_amcl_b200", "host", "test", "test_host_api")
+    if not os.path.exists(exe):
+        return {"error": "host driver not built (python -c 'import __graft_entry__ as g; g.build()')"}
+    n = len(poses)
+    with tempfile.NamedTemporaryFile(suffix=".bin", delete=False) as f:
+        f.write(struct.pack("<9i", 0x414D434C, cells.shape[1], cells.shape[0], n, len(ranges), n // 10, 1, 1, 12345))
+        f.write(struct.pack("<3d", RES, 2.0, RANGE_MAX))
+        f.write(np.ascontiguousarray(cells, np.int8).tobytes())
+        f.write(np.ascontiguousarray(ranges, np.float64).tobytes())
+        f.write(np.ascontiguousarray(angles, np.float64).tobytes())
+        f.write(np.ascontiguousarray(poses[:, :3], np.float64).tobytes())
+        path = f.name
+    try:
+        r = subprocess.run([exe, "bench", path, str(steps), str(warmup)], capture_output=True, text=True, timeout=600)
+        if r.returncode != 0:
+            return {"error": "rc %d: %s" % (r.returncode, (r.stdout + r.stderr)[-400:])}
+        return json.loads(r.stdout.strip().splitlines()[-1])
+    finally:
+        os.unlink(path)
+
+
 def leg_parity(cabi, pf, m, model, cells, ranges, angles, aos, P):
     """20k particles of the bench set scored on the device against the C restatement of the reference (the checker;
     not timed, after every measurement): max relative difference of the log weight factors, default and exact mode"""
@@ -599,7 +626,7 @@ def run_b200_arm(a):
                 float(cnt0) * valid / (k_ms * 1e-3) * spr / 32.0 / g_l2)
     except Exception as e:  # noqa: BLE001
         line["roofline"]["l2_gather"] = {"error": str(e)}
-    legs = [] if a.legs == "none" else (["c2", "c3", "c4", "parity"] if a.legs == "auto" else a.legs.split(","))
+    legs = [] if a.legs == "none" else (["c2", "c3", "c4", "parity", "host"] if a.legs == "auto" else a.legs.split(","))
     if world == 1 and legs:
         from badger_amcl_b200 import synth
         cfgs = {}
@@ -610,6 +637,8 @@ def run_b200_arm(a):
         if "c2" in legs:
             cfgs["c2_beam_model"] = leg_c2(ctx, cabi, synth, m, cells, ranges, angles, peak)
         m.close()
+        if "host" in legs:
+            cfgs["host_cpp_class_api"] = leg_host_api(a, cells, ranges, angles, poses)
         if "c3" in legs:
             cfgs["c3_lf_kld_sweep"] = leg_c3(ctx, cabi, synth, peak)
         if "c4" in legs:

@@ -61,6 +61,10 @@ int bamcl_bench_gather(bamcl_ctx* ctx, size_t table_bytes, long n_gathers, float
  * particle_filter.h:72, lives in such a buffer so uploads and downloads run at full PCIe rate) */
 int bamcl_host_alloc(size_t bytes, void** out);
 int bamcl_host_free(void* p);
+/* page-lock memory the caller already owns (the host mirror's std::vector<PFSample>, particle_filter.h:72), so copies of it
+ * run at full PCIe rate and overlap kernels; the range must stay allocated until bamcl_host_unregister */
+int bamcl_host_register(void* p, size_t bytes);
+int bamcl_host_unregister(void* p);
 
 /* ---- OccupancyMap (include/amcl/map/occupancy_map.h:57-81) */
 /* ctor + setSize + setOrigin (occupancy_map.cpp:30-57) */

@@ -260,7 +260,20 @@ extern "C" int bamcl_pf_update_action(bamcl_pf* pf, const bamcl_odom_model* mode
     memcpy(&last_attempt, &h_meta[2], sizeof(long long));
   }
   ap.g = at.draws;
-  BAMCL_LAUNCH(ctx, k_apply_motion, (unsigned)((P + 255) / 256), 256, 0, ap);
+  if (pf_ranks(pf) > 1)
+  {
+    // a distributed filter: every rank replays the draw stream of the WHOLE set (the attempt flags above: the number of
+    // draws a sample consumes depends on every sample before it) and moves the window it owns
+    long off = 0, cnt = 0;
+    pf_owned(pf, &off, &cnt);
+    ap.x += off;
+    ap.y += off;
+    ap.th += off;
+    ap.g += 3 * off;
+    ap.n = (int)cnt;
+  }
+  if (ap.n > 0)
+    BAMCL_LAUNCH(ctx, k_apply_motion, (unsigned)((ap.n + 255) / 256), 256, 0, ap);
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
   *drand48_state_out = lcg_skip(at.state0, 2ull * (unsigned long long)(last_attempt + 1));
   return BAMCL_OK;

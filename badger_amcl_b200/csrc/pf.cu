@@ -708,6 +708,15 @@ int bamcl_pf_update_planar_host(bamcl_pf* pf, bamcl_map2d* map, const bamcl_plan
   BAMCL_CUDA_OK(cudaEventRecord(pf->ev_copy[CHUNKS], ctx->stream));
   BAMCL_CUDA_OK(cudaStreamWaitEvent(pf->copy_stream, pf->ev_copy[CHUNKS], 0));
   int rc = BAMCL_OK;
+  struct WindowReset  // whatever path leaves this function, the filter is back to its whole-set window
+  {
+    bamcl_pf* p;
+    ~WindowReset()
+    {
+      p->win_off = 0;
+      p->win_cnt = -1;
+    }
+  } window_reset{pf};
   for (int c = 0; c < CHUNKS && rc == BAMCL_OK; c++)
   {
     const long off = n * c / CHUNKS, cnt = n * (c + 1) / CHUNKS - off;

@@ -207,6 +207,13 @@ __global__ void SCORE_BOUNDS k_score_lf(const ScoreArgs a)
       st.y = s2;
       st.z = (sx - (double)a.origin_x) / a.resolution + 0.5 + (double)(a.size_x / 2);
       st.w = (sy - (double)a.origin_y) / a.resolution + 0.5 + (double)(a.size_y / 2);
+      // a non-finite (or absurdly distant) pose is off the map for every beam, as (int)floor(NaN) = INT_MIN makes it in
+      // the reference (occupancy_map.cpp:96-97); the magic-number floor below needs |v| < 2^31
+      if (!(fabs(st.z) < 1e9) || !(fabs(st.w) < 1e9) || !(fabs(c2) <= 1.0) || !(fabs(s2) <= 1.0))
+      {
+        st.x = st.y = 0.0;
+        st.z = st.w = -1e9;
+      }
       stash[lane] = st;
       // recalcWeight, planar_scanner.cpp:642-682 (uses the robot pose, not the scanner pose)
       const int ci = world_to_cell(px, a.origin_x, a.resolution, a.size_x);
@@ -372,10 +379,10 @@ static double lf_term(const bamcl_planar_model& m, double z, double range_max)
 int stage_scan(bamcl_pf* pf, bamcl_map2d* map, const bamcl_planar_model* model, const double* ranges,
                const double* angles, int range_count, double range_max)
 {
-  StagedScan& sc = pf->scan;
-  sc.valid = false;
   if (!pf || !map || !model || range_count < 0 || (range_count > 0 && (!ranges || !angles)))
     return set_error(BAMCL_E_ARG, "stage_scan: bad arguments");
+  StagedScan& sc = pf->scan;
+  sc.valid = false;
   if (!map->has_dist)  // every planar model reads the cache through recalcWeight
     return set_error(BAMCL_E_STATE, "the map has no distance cache (updateDistancesLUT / upload_distances first)");
   sc.model = *model;

@@ -356,7 +356,8 @@ typedef struct bamcl_odom_data /* OdomData, odom.h:43-52 */
  * attempts at once (generator skip-ahead + a prefix sum over the acceptances), so sample i gets accepted attempts
  * 3i..3i+2 exactly as in the sequential loop. *drand48_state_out = the state after the last draw consumed (hand it to
  * seed48 to keep the host stream in step). A draw of exactly 0.0 (probability 2^-48 each) would shift the pairing and is
- * reported as BAMCL_E_UNSUPPORTED. On a sharded set every rank moves its whole replicated copy. Synchronises. */
+ * reported as BAMCL_E_UNSUPPORTED. On a distributed filter every rank replays the draw stream of the whole set (the
+ * number of draws a sample consumes depends on every sample before it) and moves the window it owns. Synchronises. */
 int bamcl_pf_update_action(bamcl_pf* pf, const bamcl_odom_model* model, const bamcl_odom_data* data,
                            uint64_t drand48_state, uint64_t* drand48_state_out);
 

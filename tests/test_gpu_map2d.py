@@ -81,3 +81,47 @@ def test_calc_range_matches_oracle(env):
     assert abs(r[0] - 0.15) <= 4 * np.spacing(0.15)
     m.close()
     km.close()
+
+
+def test_drop_in_path_without_cache_upload_against_the_reference(env):
+    """The drop-in path of a user who never uploads a cache: updateDistancesLUT on the device (exact EDT) -> updateSensor,
+    against the reference chain with ITS heap-order brushfire (occupancy_map.cpp:138-242). The exact EDT
+    is <= the brushfire everywhere and equal in ~99 % of cells; the weights therefore differ: this test states by how much
+    (the same figures at the bench maps are in profiles/r02_parity.json) instead of hiding the difference behind an
+    uploaded cache. Scorer parity proper (1e-5 on log weights) is tested with the reference's cache uploaded."""
+    O, cabi = env["O"], env["cabi"]
+    cells = synth.make_grid(600, 500, seed=7, wall_every=100)
+    pm = O.PortMap2D(cells, RES)
+    brush = pm.update_distances(2.0)  # restatement of the reference brushfire, pinned bit for bit to the compiled one
+    m = cabi.Map2D(env["ctx"], cells, RES)
+    m.build_distances(2.0)
+    dev = m.download_distances()
+    assert (dev <= brush).all()
+    assert (dev == brush).mean() > 0.98
+    assert np.abs(dev - brush).max() <= 2.0 * RES * 1.5
+    truth = synth.pick_truth_pose(cells, RES, seed=5)
+    ranges, angles = synth.make_scan(cells, RES, truth, n_beams=360)
+    n = 5000
+    poses = synth.uniform_free_poses(cells, RES, n, seed=1)
+    kw = dict(model_type=1, max_beams=360, scanner_pose=(0.1, 0.0, 0.0))
+    port = O.PortPF(n // 10, n)
+    port.init_with_poses(poses)
+    port.update_sensor(pm, O.planar_model(**kw), ranges, angles, 30.0)
+    want = port.samples()[:, 3]
+    pf = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    pf.init_with_poses(poses)
+    pf.set_exact_terms(True)
+    assert pf.update_sensor(m, cabi.planar_model(**kw), ranges, angles, 30.0)
+    got = pf.weights()
+    rel = np.abs(np.log(got) - np.log(want)) / np.abs(np.log(want))
+    # a smaller distance never lowers a likelihood-field term: every un-normalised factor is >= the reference's
+    assert rel.max() < 5e-2, "the exact cache moved a log weight by more than 5 %"
+    assert np.median(rel) < 5e-3
+    # ... and with the reference's cache uploaded the same call is inside the north_star tolerance
+    m.upload_distances(brush, 2.0)
+    pf.init_with_poses(poses)
+    assert pf.update_sensor(m, cabi.planar_model(**kw), ranges, angles, 30.0)
+    got = pf.weights()
+    assert (np.abs(np.log(got) - np.log(want)) <= 1e-5 * np.abs(np.log(want))).all()
+    pf.close()
+    m.close()

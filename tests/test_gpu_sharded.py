@@ -329,3 +329,40 @@ def test_distributed_beam_skipping_matches_the_single_gpu_filter(env, world, cas
     assert abs(got[0][0] - want_total) <= 1e-12 * abs(want_total)
     w = np.concatenate([g[1] for g in got])
     assert np.allclose(w, want, rtol=1e-12, atol=0.0)
+
+
+def test_distributed_motion_update_matches_the_single_gpu_filter(env):
+    """Odom::updateAction (odom.cpp:74-311) on a distributed filter: same drand48 stream position, every window moved
+    exactly as the single-GPU filter moves those samples"""
+    from badger_amcl_b200 import sharded
+    from sharded_support import run_ranks
+    cabi = env["cabi"]
+    n, world = 20001, 3
+    poses = synth.uniform_free_poses(env["cells"], RES, n, seed=6)
+    aos0 = np.concatenate([poses, np.full((n, 1), 1.0 / n)], axis=1)
+    odo = (cabi.ODOM_DIFF_CORRECTED, [0.2, 0.3, 0.25, 0.15, 0.1], [1.0, 2.0, 0.7], [0.3, 0.1, 0.2])
+    one = cabi.ParticleFilter(env["ctx"], n // 10, n)
+    one.upload_samples(aos0)
+    one.srand48(77)
+    one.update_action(*odo)
+    want, want_state = one.samples(), one.drand48_state
+    one.close()
+
+    def rank_fn(rank, group):
+        ctx = cabi.Context(0)
+        pf = cabi.ParticleFilter(ctx, n // 10, n)
+        comm = sharded.Comm.local(ctx, group, rank, world)
+        f = sharded.ShardedFilter(pf, comm)
+        f.set_global_samples(aos0)
+        pf.srand48(77)
+        pf.update_action(*odo)
+        off, cnt = f.window()
+        out = (off, cnt, f.download_window(), pf.drand48_state)
+        pf.close()
+        comm.close()
+        ctx.close()
+        return out
+
+    for off, cnt, smp, state in run_ranks(world, rank_fn):
+        assert state == want_state
+        assert np.array_equal(smp, want[off:off + cnt])

@@ -431,9 +431,15 @@ __global__ void __launch_bounds__(256) k_cc_union(const TreeOut* __restrict__ ou
   uf_union<CA>(parent, v, hnode[s]);
 }
 
+// mode 0: every edge (single GPU). Distributed filter: the grid is cut into slabs of rows (second dimension), one per
+// rank -- mode 1: only the edges with BOTH ends in slab `me` (each rank unites its own slab); the ranks' forests are then
+// merged with an all-reduce (min) of the parent array (a rank only ever lowers the parents of its own slab's nodes, every
+// other entry still points at itself); mode 2: the edges that cross a slab boundary, united by every rank on the merged
+// forest. A root is always its component's smallest node id, so the result does not depend on the split.
 template <bool CA>
 __global__ void __launch_bounds__(256) k_cc_union_dense(const TreeOut* __restrict__ out, const unsigned long long* __restrict__ nkey,
-                                                        const Box box, const int* __restrict__ g_node, int* parent, int n_max)
+                                                        const Box box, const int* __restrict__ g_node, int* parent, int n_max,
+                                                        int mode, int me, int rows_per_slab)
 {
   const int K = out->K;
   const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -443,9 +449,18 @@ __global__ void __launch_bounds__(256) k_cc_union_dense(const TreeOut* __restric
     return;
   int kx, ky, kt;
   unpack_key(nkey[v], &kx, &ky, &kt);
-  const int a = kx - box.mn[0] + (o / 9 - 1), b = ky - box.mn[1] + ((o % 9) / 3 - 1), c = kt - box.mn[2] + ((o % 9) % 3 - 1);
+  const int b0 = ky - box.mn[1];
+  if (mode == 1 && b0 / rows_per_slab != me)
+    return;
+  const int a = kx - box.mn[0] + (o / 9 - 1), b = b0 + ((o % 9) / 3 - 1), c = kt - box.mn[2] + ((o % 9) % 3 - 1);
   if ((unsigned)a >= (unsigned)box.dim[0] || (unsigned)b >= (unsigned)box.dim[1] || (unsigned)c >= (unsigned)box.dim[2])
     return;
+  if (mode != 0)
+  {
+    const bool same = b / rows_per_slab == b0 / rows_per_slab;
+    if ((mode == 1) != same)
+      return;
+  }
   const int u = __ldg(&g_node[a + box.dim[0] * (b + box.dim[1] * c)]);
   if (u >= 0)
     uf_union<CA>(parent, v, u);
@@ -1043,6 +1058,8 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       BAMCL_LAUNCH(ctx, k_grid_mark, cell_blocks, 256, 0, pf->g_first.as<int>(), cells, n_set, pf->t_bits.as<unsigned>());
       BAMCL_LAUNCH(ctx, k_popc, (words + 255) / 256, 256, 0, pf->t_bits.as<unsigned>(), words, pf->t_bpre.as<int>());
       BAMCL_TRY(exclusive_scan_i32(ctx, pf->t_bpre.as<int>(), pf->t_bpre.as<int>(), words, pf->t_scan.as<int>(), &out->K));
+      if (G > 1)  // the parent array is all-reduced over [0, k_max): entries past K must be neutral for min
+        BAMCL_CUDA_OK(cudaMemsetAsync(pf->t_parent.p, 0x7F, sizeof(int) * (size_t)k_max, ctx->stream));
       BAMCL_LAUNCH(ctx, k_grid_nodes, cell_blocks, 256, 0, pf->g_first.as<int>(), cells, n_set, pf->t_bits.as<unsigned>(),
                    pf->t_bpre.as<int>(), box, pf->g_node.as<int>(), pf->t_nkey.as<unsigned long long>(), pf->t_nfirst.as<int>(),
                    pf->t_parent.as<int>());
@@ -1105,12 +1122,26 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       }
       else if (dense)
       {
-        if (cc_volatile)
-          BAMCL_LAUNCH(ctx, k_cc_union_dense<false>, cc_blocks, 256, 0, out, pf->t_nkey.as<unsigned long long>(), box,
-                       pf->g_node.as<int>(), pf->t_parent.as<int>(), k_max);
+        auto unite = [&](int mode, int rows_per_slab) -> int {
+          if (cc_volatile)
+            BAMCL_LAUNCH(ctx, k_cc_union_dense<false>, cc_blocks, 256, 0, out, pf->t_nkey.as<unsigned long long>(), box,
+                         pf->g_node.as<int>(), pf->t_parent.as<int>(), k_max, mode, me, rows_per_slab);
+          else
+            BAMCL_LAUNCH(ctx, k_cc_union_dense<true>, cc_blocks, 256, 0, out, pf->t_nkey.as<unsigned long long>(), box,
+                         pf->g_node.as<int>(), pf->t_parent.as<int>(), k_max, mode, me, rows_per_slab);
+          return BAMCL_OK;
+        };
+        static const bool cc_replicated = getenv("BAMCL_CC_REPLICATED") != nullptr;  // A/B switch
+        if (G > 1 && !cc_replicated && box.dim[1] >= 2 * G)
+        {
+          // every rank unites one slab of the grid; forests merged by min; slab-crossing edges united by everyone
+          const int rows_per_slab = (box.dim[1] + G - 1) / G;
+          BAMCL_TRY(unite(1, rows_per_slab));
+          BAMCL_TRY(comm_all_reduce(pf->comm, pf->t_parent.p, (size_t)k_max, CT_I32, CO_MIN));
+          BAMCL_TRY(unite(2, rows_per_slab));
+        }
         else
-          BAMCL_LAUNCH(ctx, k_cc_union_dense<true>, cc_blocks, 256, 0, out, pf->t_nkey.as<unsigned long long>(), box,
-                       pf->g_node.as<int>(), pf->t_parent.as<int>(), k_max);
+          BAMCL_TRY(unite(0, 1));
       }
       else if (cc_volatile)
         BAMCL_LAUNCH(ctx, k_cc_union<false>, cc_blocks, 256, 0, out, pf->t_nkey.as<unsigned long long>(),

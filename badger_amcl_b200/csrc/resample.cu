@@ -1425,6 +1425,42 @@ __global__ void k_rows3_to_soa(const double* __restrict__ in3, long r0, long n, 
   th[r0 + i] = in3[3 * (r0 + i) + 2];
 }
 
+// received blocks (x | y | theta | source index of `rows` rows each) -> output slots; one thread per received row
+constexpr int UNPACK_MAX = 48;
+struct UnpackArgs
+{
+  int n;
+  long prefix[UNPACK_MAX + 1];  // rows before piece i among this launch's pieces
+  const char* block[UNPACK_MAX];
+  long rows[UNPACK_MAX];  // rows of the whole block the piece sits in
+  long q[UNPACK_MAX];     // first row of the piece inside its block
+  long o[UNPACK_MAX];     // first output slot of the piece
+  double *bx, *by, *bth;
+  int* bsrc;
+};
+__global__ void __launch_bounds__(256) k_unpack_moves(const UnpackArgs a)
+{
+  const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= a.prefix[a.n])
+    return;
+  int lo = 0, hi = a.n - 1;  // last piece with prefix <= t
+  while (lo < hi)
+  {
+    const int mid = (lo + hi + 1) >> 1;
+    if (a.prefix[mid] <= t)
+      lo = mid;
+    else
+      hi = mid - 1;
+  }
+  const long r = a.q[lo] + (t - a.prefix[lo]), slot = a.o[lo] + (t - a.prefix[lo]);
+  const double* x = reinterpret_cast<const double*>(a.block[lo]);
+  const long c = a.rows[lo];
+  a.bx[slot] = x[r];
+  a.by[slot] = x[c + r];
+  a.bth[slot] = x[2 * c + r];
+  a.bsrc[slot] = reinterpret_cast<const int*>(x + 3 * c)[r];
+}
+
 struct Move
 {
   long src, dst, kb, ke, pos;
@@ -1685,13 +1721,12 @@ int bamcl_pf_shard_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamc
   if (my_rows > 0 && P <= 0)
     return set_error(BAMCL_E_STATE, "bamcl_pf_shard_resample: this rank's window is empty but it was given outputs");
 
-  // ---- select this rank's runs into staging rows (k order)
+  // ---- select + exchange (:326-351 writes set_b in slot order). Every transfer of the plan is one contiguous piece of
+  // output slots from one source rank to one owner. Pieces this rank keeps are selected straight into the new set; pieces
+  // for another rank are selected into ONE block per destination (x | y | theta | source index, SoA), so the exchange is a
+  // single send and a single receive per peer (large messages: NVLink rate instead of per-message latency), and one
+  // kernel scatters the received blocks into the new set.
   BAMCL_TRY(pf->src.reserve(sizeof(int) * (size_t)pf->max_samples));
-  const size_t rows_cap = (size_t)std::max<long>(my_rows, 1);
-  BAMCL_TRY(pf->stage_x.reserve(sizeof(double) * rows_cap));
-  BAMCL_TRY(pf->stage_y.reserve(sizeof(double) * rows_cap));
-  BAMCL_TRY(pf->stage_th.reserve(sizeof(double) * rows_cap));
-  BAMCL_TRY(pf->stage_src.reserve(sizeof(int) * rows_cap));
   BAMCL_TRY(pf->h_stage.reserve(sizeof(TargetSeg) * MAX_SEGS));
   BAMCL_TRY(pf->seg_buf.reserve(sizeof(TargetSeg) * MAX_SEGS));
   if (!segs.empty())
@@ -1700,14 +1735,34 @@ int bamcl_pf_shard_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamc
     BAMCL_CUDA_OK(cudaMemcpyAsync(pf->seg_buf.p, pf->h_stage.p, sizeof(TargetSeg) * segs.size(), cudaMemcpyHostToDevice,
                                   ctx->stream));
   }
+  double* bx = set_b.x.as<double>();
+  double* by = set_b.y.as<double>();
+  double* bth = set_b.th.as<double>();
+  int* bsrc = pf->src.as<int>();
+  std::vector<long> c_send(G, 0), c_recv(G, 0);
+  for (const Move& m : moves)
   {
-    long pos = 0;
-    for (int i = 0; i < n_runs; i++)
+    if (m.src == me && m.dst != me)
+      c_send[m.dst] += m.ke - m.kb;
+    if (m.dst == me && m.src != me)
+      c_recv[m.src] += m.ke - m.kb;
+  }
+  auto block_bytes = [](long rows) { return ((size_t)rows * 28 + 15) & ~(size_t)15; };
+  std::vector<size_t> s_off(G + 1, 0), r_off(G + 1, 0);
+  for (int q = 0; q < G; q++)
+  {
+    s_off[q + 1] = s_off[q] + block_bytes(c_send[q]);
+    r_off[q + 1] = r_off[q] + block_bytes(c_recv[q]);
+  }
+  BAMCL_TRY(pf->stage_x.reserve(std::max<size_t>(s_off[G], 16)));
+  BAMCL_TRY(pf->stage_y.reserve(std::max<size_t>(r_off[G], 16)));
+  char* send_base = pf->stage_x.as<char>();
+  char* recv_base = pf->stage_y.as<char>();
+  {
+    std::vector<long> filled(G, 0);
+    for (const Move& m : moves)
     {
-      if (runs[3 * i + 2] != me)
-        continue;
-      const long kb = runs[3 * i], ke = runs[3 * i + 1];
-      if (ke == kb)
+      if (m.src != me || m.ke == m.kb)
         continue;
       ShardSelArgs a;
       a.c = pf->cdf.as<double>();
@@ -1716,55 +1771,76 @@ int bamcl_pf_shard_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamc
       a.ax = set_a.x.as<double>() + a.off;
       a.ay = set_a.y.as<double>() + a.off;
       a.ath = set_a.th.as<double>() + a.off;
-      a.ox = pf->stage_x.as<double>();
-      a.oy = pf->stage_y.as<double>();
-      a.oth = pf->stage_th.as<double>();
-      a.osrc = pf->stage_src.as<int>();
-      a.k_begin = kb;
-      a.k_end = ke;
-      a.row0 = pos - kb;
+      if (m.dst == me)
+      {
+        a.ox = bx;
+        a.oy = by;
+        a.oth = bth;
+        a.osrc = bsrc;
+        a.row0 = n_rand;  // row = output slot
+      }
+      else
+      {
+        const long c = c_send[m.dst];
+        a.ox = reinterpret_cast<double*>(send_base + s_off[m.dst]);
+        a.oy = a.ox + c;
+        a.oth = a.ox + 2 * c;
+        a.osrc = reinterpret_cast<int*>(a.ox + 3 * c);
+        a.row0 = filled[m.dst] - m.kb;
+        filled[m.dst] += m.ke - m.kb;
+      }
+      a.k_begin = m.kb;
+      a.k_end = m.ke;
       a.segs = pf->seg_buf.as<TargetSeg>();
       a.n_segs = (int)segs.size();
       a.flags = pf_flags(pf);
-      BAMCL_LAUNCH(ctx, k_select_shard, (unsigned)((ke - kb + 255) / 256), 256, 0, a);
-      pos += ke - kb;
+      BAMCL_LAUNCH(ctx, k_select_shard, (unsigned)((m.ke - m.kb + 255) / 256), 256, 0, a);
     }
   }
-
   pf_mark(pf, "plan+select");
-  // ---- the exchange: selected rows -> owners of the output slots (:326-351 writes set_b in slot order)
-  double* bx = set_b.x.as<double>();
-  double* by = set_b.y.as<double>();
-  double* bth = set_b.th.as<double>();
-  int* bsrc = pf->src.as<int>();
-  std::vector<P2P> sends, recvs;
-  for (const Move& m : moves)
-  {
-    const long cnt = m.ke - m.kb, o = n_rand + m.kb;
-    if (m.src == me && m.dst == me)
-    {
-      BAMCL_CUDA_OK(cudaMemcpyAsync(bx + o, pf->stage_x.as<double>() + m.pos, sizeof(double) * cnt, cudaMemcpyDeviceToDevice, ctx->stream));
-      BAMCL_CUDA_OK(cudaMemcpyAsync(by + o, pf->stage_y.as<double>() + m.pos, sizeof(double) * cnt, cudaMemcpyDeviceToDevice, ctx->stream));
-      BAMCL_CUDA_OK(cudaMemcpyAsync(bth + o, pf->stage_th.as<double>() + m.pos, sizeof(double) * cnt, cudaMemcpyDeviceToDevice, ctx->stream));
-      BAMCL_CUDA_OK(cudaMemcpyAsync(bsrc + o, pf->stage_src.as<int>() + m.pos, sizeof(int) * cnt, cudaMemcpyDeviceToDevice, ctx->stream));
-    }
-    else if (m.src == me)
-    {
-      sends.push_back(P2P{(int)m.dst, pf->stage_x.as<double>() + m.pos, sizeof(double) * (size_t)cnt});
-      sends.push_back(P2P{(int)m.dst, pf->stage_y.as<double>() + m.pos, sizeof(double) * (size_t)cnt});
-      sends.push_back(P2P{(int)m.dst, pf->stage_th.as<double>() + m.pos, sizeof(double) * (size_t)cnt});
-      sends.push_back(P2P{(int)m.dst, pf->stage_src.as<int>() + m.pos, sizeof(int) * (size_t)cnt});
-    }
-    else if (m.dst == me)
-    {
-      recvs.push_back(P2P{(int)m.src, bx + o, sizeof(double) * (size_t)cnt});
-      recvs.push_back(P2P{(int)m.src, by + o, sizeof(double) * (size_t)cnt});
-      recvs.push_back(P2P{(int)m.src, bth + o, sizeof(double) * (size_t)cnt});
-      recvs.push_back(P2P{(int)m.src, bsrc + o, sizeof(int) * (size_t)cnt});
-    }
-  }
   if (G > 1)
+  {
+    std::vector<P2P> sends, recvs;
+    for (int q = 0; q < G; q++)
+    {
+      if (c_send[q] > 0)
+        sends.push_back(P2P{q, send_base + s_off[q], (size_t)c_send[q] * 28});
+      if (c_recv[q] > 0)
+        recvs.push_back(P2P{q, recv_base + r_off[q], (size_t)c_recv[q] * 28});
+    }
     BAMCL_TRY(comm_exchange(comm, sends.data(), (int)sends.size(), recvs.data(), (int)recvs.size()));
+    // received blocks -> output slots
+    UnpackArgs ua;
+    ua.bx = bx;
+    ua.by = by;
+    ua.bth = bth;
+    ua.bsrc = bsrc;
+    ua.n = 0;
+    ua.prefix[0] = 0;
+    std::vector<long> taken(G, 0);
+    auto flush = [&]() -> int {
+      if (ua.n > 0 && ua.prefix[ua.n] > 0)
+        BAMCL_LAUNCH(ctx, k_unpack_moves, (unsigned)((ua.prefix[ua.n] + 255) / 256), 256, 0, ua);
+      ua.n = 0;
+      ua.prefix[0] = 0;
+      return BAMCL_OK;
+    };
+    for (const Move& m : moves)
+    {
+      if (m.dst != me || m.src == me || m.ke == m.kb)
+        continue;
+      if (ua.n == UNPACK_MAX)
+        BAMCL_TRY(flush());
+      ua.block[ua.n] = recv_base + r_off[m.src];
+      ua.rows[ua.n] = c_recv[m.src];
+      ua.q[ua.n] = taken[m.src];
+      ua.o[ua.n] = n_rand + m.kb;
+      ua.prefix[ua.n + 1] = ua.prefix[ua.n] + (m.ke - m.kb);
+      taken[m.src] += m.ke - m.kb;
+      ua.n++;
+    }
+    BAMCL_TRY(flush());
+  }
 
   pf_mark(pf, "exchange");
   // ---- this rank's output window: weights 1/n (:343-346, 457-462) and the random poses among its slots (:316-324)

@@ -72,8 +72,16 @@ __device__ __forceinline__ int walk_y(const RayWalk& r, int t)  // y after t ste
 #define BEAM_REFILL_MIN 8
 #endif
 constexpr int REFILL_MIN = BEAM_REFILL_MIN;
+// (swept on a B200, scripts/sweep_beam2.sh, 100k x 1080: chunk 2 / 4 / 8 / 16 jumps per refill check = 11.0 / 10.0 / 9.3 / 9.1
+// ms; refill threshold 4 / 8 / 16 lanes = 9.7 / 9.3 / 9.3; 8 CTAs per SM (32 registers, spills) 8.75 against 9.3 at 4)
+#ifndef BEAM_CHUNK
+#define BEAM_CHUNK 16
+#endif
+#ifndef BEAM_MINB
+#define BEAM_MINB 8
+#endif
 
-__global__ void __launch_bounds__(256) k_score_beam(const BeamArgs a)
+__global__ void __launch_bounds__(256, BEAM_MINB) k_score_beam(const BeamArgs a)
 {
   const int lane = threadIdx.x & 31;
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -199,7 +207,7 @@ __global__ void __launch_bounds__(256) k_score_beam(const BeamArgs a)
         // single-exit loop (no breaks): the lanes of a warp stay converged from one jump to the next
         int code = 0;  // 0 walking, 1 hit at (x, y), 2 nothing hit, 3 the next step leaves the grid along x
 #pragma unroll 1
-        for (int it = 0; it < 8 && code == 0; it++)
+        for (int it = 0; it < BEAM_CHUNK && code == 0; it++)
         {
           const int d = __ldg(&a.clear[r.steep ? (size_t)x * a.size_x + y : (size_t)y * a.size_x + x]);
           if (d == 0)  // the cell stops the ray

@@ -74,6 +74,11 @@ def build_host(force=False):
     if stale(HOST_TEST, [test_src, HOST_LIB] + hdrs):
         subprocess.check_call(common + ["-o", HOST_TEST, test_src, "-L", HERE, "-lbadger_amcl", "-lbamcl_cuda",
                                         "-Wl,-rpath,$ORIGIN/../.."])
+    # the standalone C++ host of the distributed path (C ABI only)
+    dist_src, dist_exe = os.path.join(HOST, "test", "bench_dist.cpp"), os.path.join(HOST, "test", "bench_dist")
+    if stale(dist_exe, [dist_src, OUT]):
+        subprocess.check_call([CXX, "-std=c++17", "-O2", "-Wall", "-I", os.path.join(HERE, "..", "include"), "-o", dist_exe,
+                               dist_src, "-L", HERE, "-lbamcl_cuda", "-Wl,-rpath,$ORIGIN/../.."])
     return HOST_LIB
 
 

@@ -184,6 +184,8 @@ SIGNATURES = {
     "bamcl_comm_local_group_free": (_I, [_P]),
     "bamcl_comm_create_local": (_I, [_P, _P, _I, _P]),
     "bamcl_comm_all_reduce_sum_i32": (_I, [_P, _P, _I]),
+    "bamcl_comm_all_reduce_i32": (_I, [_P, _P, _I, _I]),
+    "bamcl_comm_create_file": (_I, [_P, C.c_char_p, _I, _I, _I, _P]),
     "bamcl_pf_shard_attach": (_I, [_P, _P]),
     "bamcl_pf_shard_set_count": (_I, [_P, _L, _P, _P]),
     "bamcl_pf_shard_window": (_I, [_P, _P, _P]),

@@ -8,6 +8,7 @@
 #include <cstring>
 #include <condition_variable>
 #include <mutex>
+#include <thread>
 
 #include "comm.cuh"
 
@@ -347,6 +348,74 @@ int bamcl_comm_create(bamcl_ctx* ctx, const void* id, int rank, int n_ranks, bam
   }
   *out = c;
   return BAMCL_OK;
+}
+
+int bamcl_comm_create_file(bamcl_ctx* ctx, const char* path, int rank, int n_ranks, int timeout_s, bamcl_comm** out)
+{
+  if (!ctx || !out || !path || n_ranks < 1 || rank < 0 || rank >= n_ranks)
+    return set_error(BAMCL_E_ARG, "bamcl_comm_create_file: bad arguments");
+  unsigned char id[BAMCL_UNIQUE_ID_BYTES];
+  memset(id, 0, sizeof(id));
+  if (n_ranks > 1)
+  {
+    if (rank == 0)
+    {
+      BAMCL_TRY(bamcl_comm_unique_id(id));
+      const std::string tmp = std::string(path) + ".tmp";
+      FILE* f = fopen(tmp.c_str(), "wb");
+      if (!f || fwrite(id, 1, sizeof(id), f) != sizeof(id))
+      {
+        if (f)
+          fclose(f);
+        return set_error(BAMCL_E_COMM, "bamcl_comm_create_file: cannot write %s", tmp.c_str());
+      }
+      fclose(f);
+      if (rename(tmp.c_str(), path) != 0)  // atomic: readers never see a partial id
+        return set_error(BAMCL_E_COMM, "bamcl_comm_create_file: cannot publish %s", path);
+    }
+    else
+    {
+      const auto t0 = std::chrono::steady_clock::now();
+      for (;;)
+      {
+        FILE* f = fopen(path, "rb");
+        if (f)
+        {
+          const size_t got = fread(id, 1, sizeof(id), f);
+          fclose(f);
+          if (got == sizeof(id))
+            break;
+        }
+        if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > timeout_s)
+          return set_error(BAMCL_E_COMM, "bamcl_comm_create_file: no id at %s after %d s", path, timeout_s);
+        std::this_thread::sleep_for(std::chrono::milliseconds(20));
+      }
+    }
+  }
+  const int rc = bamcl_comm_create(ctx, id, rank, n_ranks, out);
+  return rc;
+}
+
+int bamcl_comm_all_reduce_i32(bamcl_comm* c, int* host_inout, int n, int op)
+{
+  if (!c || !host_inout || n < 0 || op < 0 || op > 2)
+    return set_error(BAMCL_E_ARG, "bamcl_comm_all_reduce_i32: bad arguments");
+  if (n == 0 || c->n_ranks == 1)
+    return BAMCL_OK;
+  cudaStream_t st = c->ctx->stream;
+  bamcl::DevBuf tmp;
+  BAMCL_TRY(tmp.reserve(sizeof(int) * (size_t)n));
+  int rc = BAMCL_OK;
+  if (cudaMemcpyAsync(tmp.p, host_inout, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, st) != cudaSuccess)
+    rc = set_error(BAMCL_E_CUDA, "bamcl_comm_all_reduce_i32: upload failed");
+  if (rc == BAMCL_OK)
+    rc = comm_all_reduce(c, tmp.p, (size_t)n, CT_I32, (CommOp)op);
+  if (rc == BAMCL_OK && (cudaMemcpyAsync(host_inout, tmp.p, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+                         cudaStreamSynchronize(st) != cudaSuccess))
+    rc = set_error(BAMCL_E_CUDA, "bamcl_comm_all_reduce_i32: download failed");
+  cudaStreamSynchronize(st);
+  tmp.release();
+  return rc;
 }
 
 int bamcl_comm_local_group(int n_ranks, void** group_out)

@@ -279,6 +279,9 @@ int bamcl_resample_limit(int k, int min_samples, int max_samples, double pop_err
 int bamcl_comm_unique_id(void* id_out);
 /* ncclCommInitRank on every rank (collective); n_ranks = 1 needs no id and no NCCL */
 int bamcl_comm_create(bamcl_ctx* ctx, const void* id, int rank, int n_ranks, bamcl_comm** out);
+/* the same with the id moved through a file (a C++ host without any other channel: rank 0 writes it, the others wait for
+ * it; `path` must be fresh for every job and visible to all ranks of the node) */
+int bamcl_comm_create_file(bamcl_ctx* ctx, const char* path, int rank, int n_ranks, int timeout_s, bamcl_comm** out);
 int bamcl_comm_destroy(bamcl_comm* comm);
 int bamcl_comm_rank(bamcl_comm* comm, int* rank, int* n_ranks);
 /* TEST back end: n_ranks ranks = n_ranks threads of THIS process on one GPU (each with its own context); collectives are
@@ -288,6 +291,8 @@ int bamcl_comm_local_group_free(void* group);
 int bamcl_comm_create_local(bamcl_ctx* ctx, void* group, int rank, bamcl_comm** out);
 /* small host vectors summed over the ranks (beam-skipping agreement counts, planar_scanner.cpp:448-451, 487) */
 int bamcl_comm_all_reduce_sum_i32(bamcl_comm* comm, int* host_inout, int n);
+/* op: 0 sum, 1 min, 2 max (also serves as a barrier between ranks) */
+int bamcl_comm_all_reduce_i32(bamcl_comm* comm, int* host_inout, int n, int op);
 
 /* the filter becomes rank `comm->rank`'s shard of a global set; NULL detaches. */
 int bamcl_pf_shard_attach(bamcl_pf* pf, bamcl_comm* comm);

@@ -1175,7 +1175,11 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
           return BAMCL_OK;
         };
         static const bool cc_replicated = getenv("BAMCL_CC_REPLICATED") != nullptr;  // A/B switch
-        if (G > 1 && !cc_replicated && box.dim[1] >= 2 * G)
+        // (A/B on one 8 x B200 box, 1M particles per GPU, step ms distributed / replicated: G = 4: 3.33 / 3.47, G = 8: 3.84 /
+        // 3.74, 64M over 8: 13.9 / 13.5 -- the all-reduce of the parent array, the boundary pass and the rank skew it
+        // waits for outgrow the 1/G saving beyond four ranks)
+        static const bool cc_distributed = getenv("BAMCL_CC_DISTRIBUTED") != nullptr;
+        if (G > 1 && !cc_replicated && (G <= 4 || cc_distributed) && box.dim[1] >= 2 * G)
         {
           // every rank unites one slab of the grid; forests merged by min; slab-crossing edges united by everyone
           const int rows_per_slab = (box.dim[1] + G - 1) / G;

@@ -22,13 +22,16 @@ constexpr int M_TOP2_MAX = 1 << 18;  // most keys the node arrays of steps A + B
 constexpr int FAST_CAP_W = 64, FAST_CAP_S = 512, FAST_CAP_M = 2048, FAST_CAP_L = 6144;
 constexpr int FAST_BYTES_PER_KEY = 28;  // shared memory per key in the bucket kernels
 
+#ifndef TOP2_DIV
+#define TOP2_DIV 32
+#endif
 // keys in the written-out top tree for a tree of K keys (same arithmetic on host and device, monotone in K)
 __host__ __device__ inline int top2_size(int K)
 {
   if (K <= 16 * M_TOP1)
     return M_TOP1;  // small trees: the step-A tree is the whole top
   int m = M_TOP1;
-  while (m < K / 32 && m < M_TOP2_MAX)
+  while (m < K / TOP2_DIV && m < M_TOP2_MAX)
     m <<= 1;
   return m;
 }

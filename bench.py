@@ -353,6 +353,51 @@ def leg_c4(ctx, cabi, synth, peak):
     return out
 
 
+def leg_c5(ctx, cabi, sharded, comm, dist, m, model, cells, ranges, angles, rank, world, per_gpu=8000000, steps=3, warmup=1):
+    """config 5: global localisation, 64M particles x 1080 beams over 8 GPUs (8M per GPU): one global set, every rank
+    generates and owns its window (global-uniform free-space poses); the same step as the headline"""
+    import torch
+    from badger_amcl_b200 import synth
+    PT = per_gpu * world
+    off, cnt = (PT * rank) // world, (PT * (rank + 1)) // world - (PT * rank) // world
+    poses = synth.uniform_free_poses(cells, RES, cnt, seed=1000 + rank)
+    aos = cabi.pinned_array((cnt, 4))
+    aos[:, :3] = poses
+    aos[:, 3] = 1.0 / PT
+    del poses
+    pf = cabi.ParticleFilter(ctx, PT // 10, PT)
+    sf = sharded.ShardedFilter(pf, comm, m)
+    pf.stage_scan(m, model, ranges, angles, RANGE_MAX)
+    valid = int((ranges < RANGE_MAX).sum())
+    ups, rss = [], []
+    r = None
+    for it in range(warmup + steps):
+        cabi._check(pf.L.bamcl_pf_shard_set_count(pf.h, PT, None, None))
+        sf.upload_window(aos)
+        sf.init_stats()
+        sf.srand48(12345)
+        ctx.flush_l2()
+        ctx.sync()
+        dist.barrier()
+        ctx.timer_start()
+        sf.update_sensor()
+        u = ctx.timer_stop_ms()
+        ctx.timer_start()
+        r = sf.update_resample()
+        q = ctx.timer_stop_ms()
+        if it >= warmup:
+            ups.append(u)
+            rss.append(q)
+    t = torch.tensor([float(np.mean(ups)), float(np.mean(rss))], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    up, rs = [float(v) for v in t.tolist()]
+    pf.close()
+    return {"workload": "LF update + KLD systematic resample, ONE global set of %d particles x %d beams over %d GPUs" % (PT, len(ranges), world),
+            "global_particles": PT, "ms_per_step": up + rs, "update_ms": up, "resample_ms": rs,
+            "evals_per_s": float(PT) * valid / ((up + rs) * 1e-3), "resampled_count": int(r.sample_count),
+            "kld_leaf_count": int(r.leaf_count), "clusters": int(r.cluster_count), "steps": steps}
+
+
 def leg_host_api(a, cells, ranges, angles, poses, steps=5, warmup=2):
     """the same step through the C++ class API (libbadger_amcl.so: OccupancyMap, PlanarScanner::updateSensor,
     ParticleFilter::updateResample, node_2d.cpp:367-380) with a host-side write of the samples between steps; the
@@ -564,6 +609,14 @@ def run_b200_arm(a):
     e_ms = float(np.sum([r[0] for r in e_rows]))
     n_out = int(e_rows[-1][1])
 
+    c5 = None
+    want_c5 = (a.legs == "auto" and world == 8 and a.particles == 1000000) or (a.legs != "auto" and "c5" in a.legs.split(","))
+    if want_c5 and sf is not None:
+        per = 8000000 if world == 8 else max(1000000, 8000000 // 4)
+        try:
+            c5 = leg_c5(ctx, cabi, sharded, comm, dist, m, model, cells, ranges, angles, rank, world, per_gpu=per)
+        except Exception as e:  # noqa: BLE001  (a leg must not take the headline line down)
+            c5 = {"error": str(e)[:300]}
     total_ms, e_total_ms = up + rs, e_ms
     if dist is not None:
         import torch
@@ -626,6 +679,11 @@ def run_b200_arm(a):
                 float(cnt0) * valid / (k_ms * 1e-3) * spr / 32.0 / g_l2)
     except Exception as e:  # noqa: BLE001
         line["roofline"]["l2_gather"] = {"error": str(e)}
+    if c5 is not None:
+        line["config"].setdefault("configs", {})["c5_global_64M"] = c5
+    line["config"]["distance_cache"] = ("device-built exact EDT (OccupancyMap::updateDistancesLUT on the device); the reference's "
+                                        "heap-order brushfire equals it in 99.1 % of this map's cells and is never smaller -- "
+                                        "figures and the effect on the weights: config.parity_report / profiles/r02_parity.json")
     legs = [] if a.legs == "none" else (["c2", "c3", "c4", "parity", "host"] if a.legs == "auto" else a.legs.split(","))
     if world == 1 and legs:
         from badger_amcl_b200 import synth
@@ -643,7 +701,7 @@ def run_b200_arm(a):
             cfgs["c3_lf_kld_sweep"] = leg_c3(ctx, cabi, synth, peak)
         if "c4" in legs:
             cfgs["c4_cloud_3d"] = leg_c4(ctx, cabi, synth, peak)
-        line["config"]["configs"] = cfgs
+        line["config"].setdefault("configs", {}).update(cfgs)
         line["config"]["configs_note"] = ("config 1 (5k x 60, CPU-runnable) is the parity-test case of tests/test_golden.py; config "
                                           "5 (64M over 8 GPUs) is measured by `--gpus 8 --particles 8000000`")
     if not a.no_cpu_baseline and world == 1:

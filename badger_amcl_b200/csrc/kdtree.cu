@@ -1193,6 +1193,10 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
         }
         else
         {
+          // (Measured and dropped: unions inside 16 x 16 x 8 tiles in shared memory first (one CTA per tile, lock-free
+          // union-find over local cell indices), then only the tile-crossing edges on the global forest -- 0.19 + 0.10 ms
+          // against 0.29 ms for the single pass, resample 0.95 against 0.83 ms at 1M samples, 3.60 against 2.73 ms at 8M:
+          // the ~500 unions of a tile contend for a handful of local roots and serialise.)
           BAMCL_TRY(head_start(0, 1));
           BAMCL_TRY(unite(0, 1));
         }

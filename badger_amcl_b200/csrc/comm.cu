@@ -482,27 +482,7 @@ int bamcl_comm_destroy(bamcl_comm* c)
   return BAMCL_OK;
 }
 
-int bamcl_comm_all_reduce_sum_i32(bamcl_comm* c, int* host_inout, int n)
-{
-  if (!c || !host_inout || n < 0)
-    return set_error(BAMCL_E_ARG, "bamcl_comm_all_reduce_sum_i32: bad arguments");
-  if (n == 0 || c->n_ranks == 1)
-    return BAMCL_OK;
-  cudaStream_t st = c->ctx->stream;
-  bamcl::DevBuf tmp;  // small and rare (one call per beam-skipping update)
-  BAMCL_TRY(tmp.reserve(sizeof(int) * (size_t)n));
-  int rc = BAMCL_OK;
-  if (cudaMemcpyAsync(tmp.p, host_inout, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, st) != cudaSuccess)
-    rc = set_error(BAMCL_E_CUDA, "bamcl_comm_all_reduce_sum_i32: upload failed");
-  if (rc == BAMCL_OK)
-    rc = comm_all_reduce(c, tmp.p, (size_t)n, CT_I32, CO_SUM);
-  if (rc == BAMCL_OK && (cudaMemcpyAsync(host_inout, tmp.p, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
-                         cudaStreamSynchronize(st) != cudaSuccess))
-    rc = set_error(BAMCL_E_CUDA, "bamcl_comm_all_reduce_sum_i32: download failed");
-  cudaStreamSynchronize(st);
-  tmp.release();
-  return rc;
-}
+int bamcl_comm_all_reduce_sum_i32(bamcl_comm* c, int* host_inout, int n) { return bamcl_comm_all_reduce_i32(c, host_inout, n, 0); }
 
 int bamcl_comm_rank(bamcl_comm* c, int* rank, int* n_ranks)
 {

@@ -366,6 +366,51 @@ __device__ __forceinline__ int uf_find(int* parent, int v)
   }
   return cur;
 }
+// find(v) when parent[v] has been loaded already (the caller issued that load early, next to independent ones)
+template <bool CA>
+__device__ __forceinline__ int uf_find_from(int* parent, int v, int cur)
+{
+  if (cur != v)
+  {
+    int prev = v, next;
+    while (cur > (next = uf_load<CA>(&parent[cur])))
+    {
+      parent[prev] = next;
+      prev = cur;
+      cur = next;
+    }
+  }
+  return cur;
+}
+template <bool CA>
+__device__ __forceinline__ void uf_hook(int* parent, int ra, int rb)
+{
+  bool repeat;
+  do
+  {
+    repeat = false;
+    if (ra != rb)
+    {
+      int ret;
+      if (ra < rb)
+      {
+        if ((ret = atomicCAS(&parent[rb], rb, ra)) != rb)
+        {
+          rb = ret;
+          repeat = true;
+        }
+      }
+      else
+      {
+        if ((ret = atomicCAS(&parent[ra], ra, rb)) != ra)
+        {
+          ra = ret;
+          repeat = true;
+        }
+      }
+    }
+  } while (repeat);
+}
 template <bool CA>
 __device__ __forceinline__ void uf_union(int* parent, int a, int b)
 {
@@ -447,6 +492,7 @@ __global__ void __launch_bounds__(256) k_cc_union_dense(const TreeOut* __restric
   const int o = (int)(t % 13) + 14;  // offsets 14..26 of the 27 = lexicographically after (0,0,0)
   if (v >= K || v >= n_max)
     return;
+  const int pv = uf_load<CA>(&parent[v]);  // independent of the key: both loads travel together
   int kx, ky, kt;
   unpack_key(nkey[v], &kx, &ky, &kt);
   const int b0 = ky - box.mn[1];
@@ -462,8 +508,12 @@ __global__ void __launch_bounds__(256) k_cc_union_dense(const TreeOut* __restric
       return;
   }
   const int u = __ldg(&g_node[a + box.dim[0] * (b + box.dim[1] * c)]);
-  if (u >= 0)
-    uf_union<CA>(parent, v, u);
+  if (u < 0)
+    return;
+  // both first hops in flight together (pv was requested at the top, next to the key), then the two walks
+  const int pu = uf_load<CA>(&parent[u]);
+  const int ra = uf_find_from<CA>(parent, v, pv), rb = uf_find_from<CA>(parent, u, pu);
+  uf_hook<CA>(parent, ra, rb);
 }
 
 // Head start for the unions (the initialisation of ECL-CC): every node points at its smallest occupied neighbour with a

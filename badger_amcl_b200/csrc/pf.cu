@@ -426,7 +426,7 @@ int bamcl_pf_destroy(bamcl_pf* pf)
                            &pf->t_out, &pf->t_sums, &pf->t_fast})
     b->release();
   for (bamcl::DevBuf* b : {&pf->g_first, &pf->g_node, &pf->t_bits, &pf->t_bpre, &pf->t_setpart, &pf->t_ints, &pf->stage_x,
-                           &pf->stage_y, &pf->stage_th, &pf->stage_src, &pf->scan.agree, &pf->scan.skip_count, &pf->scan.beams_sel, &pf->order_perm, &pf->order_hist})
+                           &pf->stage_y, &pf->scan.agree, &pf->scan.skip_count, &pf->scan.beams_sel, &pf->order_perm, &pf->order_hist})
     b->release();
   pf->t_hout.release();
   if (pf->aux_stream)

@@ -134,7 +134,7 @@ struct bamcl_pf
   int box_min[3] = {0, 0, 0}, box_dim[3] = {0, 0, 0};
   long box_cells = 0;
   bamcl::DevBuf g_first, g_node, t_bits, t_bpre, t_setpart, t_ints;
-  bamcl::DevBuf stage_x, stage_y, stage_th, stage_src;  // rows this rank selected for other ranks (shard exchange)
+  bamcl::DevBuf stage_x, stage_y;  // pose exchange of the distributed resample: blocks to send / blocks received
   int tree_dense = 0;  // the last tree build addressed the bins directly
   // scoring order: particles grouped by coarse (x, y) cell along a Morton curve, so the particles a GPU works on at any
   // moment look at the same part of the map (L2 reuse); weights are written back by original index

@@ -108,6 +108,8 @@ private:
   void pullToHost();
   bamcl_pf* dev_;
   void* pinned_samples_ = nullptr;  // the samples vector's storage while it is page-locked
+  bool clusters_pending_ = false;   // set->clusters not fetched from the device yet (syncClusters)
+  void syncClusters();
   int min_samples_, max_samples_;
   double pop_err_, pop_z_;
   double w_slow_, w_fast_, alpha_slow_, alpha_fast_;

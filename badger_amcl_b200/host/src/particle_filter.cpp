@@ -303,31 +303,19 @@ void ParticleFilter::pullToHost()
   set_->device_scored = false;
 }
 
-std::shared_ptr<PFSampleSet> ParticleFilter::getCurrentSet()
+// set->clusters of the mirror <- the device's cluster table (computeClusterStatsForSet, particle_filter.cpp:505-636)
+void ParticleFilter::syncClusters()
 {
-  pullToHost();
-  host_dirty_ = true;  // the caller holds a mutable set (odom.cpp:107-121 writes the poses through it)
-  return set_;
-}
-
-std::shared_ptr<PFSampleSet> ParticleFilter::peekCurrentSet()
-{
-  pullToHost();
-  return set_;
-}
-
-// install kd-tree / cluster / set statistics of the current device set into the mirror
-void ParticleFilter::installStats(const void* result)
-{
-  const bamcl_resample_result& r = *static_cast<const bamcl_resample_result*>(result);
-  set_->sample_count = r.sample_count;
-  set_->cluster_count = r.cluster_count;
-  set_->clusters.assign((size_t)r.cluster_count, PFCluster());
-  if (r.cluster_count > 0)
+  if (!clusters_pending_)
+    return;
+  const int count = set_->cluster_count;
+  set_->clusters.assign((size_t)count, PFCluster());
+  if (count > 0)
   {
-    std::vector<double> rows((size_t)r.cluster_count * 10);
-    check(bamcl_pf_cluster_stats(dev_, rows.data(), r.cluster_count), "bamcl_pf_cluster_stats");
-    for (int c = 0; c < r.cluster_count; c++)
+    std::vector<double> rows((size_t)count * 10);
+    if (!deviceOk(bamcl_pf_cluster_stats(dev_, rows.data(), count), "bamcl_pf_cluster_stats"))
+      return;
+    for (int c = 0; c < count; c++)
     {
       const double* o = &rows[(size_t)c * 10];
       PFCluster& cl = set_->clusters[(size_t)c];
@@ -342,6 +330,31 @@ void ParticleFilter::installStats(const void* result)
       cl.cov(2, 2) = o[9];
     }
   }
+  clusters_pending_ = false;
+}
+
+std::shared_ptr<PFSampleSet> ParticleFilter::getCurrentSet()
+{
+  syncClusters();
+  pullToHost();
+  host_dirty_ = true;  // the caller holds a mutable set (odom.cpp:107-121 writes the poses through it)
+  return set_;
+}
+
+std::shared_ptr<PFSampleSet> ParticleFilter::peekCurrentSet()
+{
+  syncClusters();
+  pullToHost();
+  return set_;
+}
+
+// install kd-tree / cluster / set statistics of the current device set into the mirror
+void ParticleFilter::installStats(const void* result)
+{
+  const bamcl_resample_result& r = *static_cast<const bamcl_resample_result*>(result);
+  set_->sample_count = r.sample_count;
+  set_->cluster_count = r.cluster_count;
+  clusters_pending_ = true;  // the cluster table (176 B per cluster in the reference's type) is fetched when someone looks
   set_->mean = Eigen::Vector3d(r.mean[0], r.mean[1], r.mean[2]);
   set_->cov = Eigen::Matrix3d::Zero();
   set_->cov(0, 0) = r.cov[0];
@@ -361,8 +374,8 @@ void ParticleFilter::installStats(const void* result)
     pullToHost();
     const int n = set_->sample_count;
     std::vector<int> labels((size_t)n);
-    if (n > 0)
-      check(bamcl_pf_sample_clusters(dev_, labels.data(), n), "bamcl_pf_sample_clusters");
+    if (n > 0 && !deviceOk(bamcl_pf_sample_clusters(dev_, labels.data(), n), "bamcl_pf_sample_clusters"))
+      return;
     for (int i = 0; i < n; i++)
       tree->labels_[PFKDTree::keyOf(set_->samples[(size_t)i].pose)] = labels[(size_t)i];
   };
@@ -517,6 +530,9 @@ void ParticleFilter::setDevicePoseSource(bamcl_map2d* map, double starting_weigh
 bool ParticleFilter::getClusterStats(int cidx, double* weight, Eigen::Vector3d* mean)
 {
   if (cidx >= set_->cluster_count)
+    return false;
+  syncClusters();
+  if (cidx >= (int)set_->clusters.size())
     return false;
   *weight = set_->clusters[(size_t)cidx].weight;
   *mean = set_->clusters[(size_t)cidx].mean;

@@ -269,8 +269,31 @@ def leg_c2(ctx, cabi, synth, m, cells, ranges, angles, peak):
         steps += st
     steps_per_ray = steps / (len(sub) * len(picks))
     algo = P * len(ranges) * steps_per_ray * 1.0 + P * 40.0 + len(ranges) * 16.0
+    # sampled parity at this shape (untimed): 300 of the particles against the C restatement of calcBeamModel / calcRange
+    parity = None
+    try:
+        from oracle import oracle as O  # checker only
+        n = 300
+        idx = np.linspace(0, P - 1, n).astype(np.int64)
+        sub = np.ascontiguousarray(aos[idx])
+        sub[:, 3] = 1.0 / n
+        pm = O.PortMap2D(cells, RES)
+        pm.set_distances(m.download_distances(), 2.0)
+        port = O.PortPF(max(1, n // 10), n)
+        port.set_samples(sub)
+        port.update_sensor(pm, O.planar_model(model_type=0, max_beams=len(ranges), scanner_pose=(0.1, 0.0, 0.0)), ranges, angles,
+                           RANGE_MAX)
+        q = cabi.ParticleFilter(ctx, max(1, n // 10), n)
+        q.upload_samples(sub)
+        q.update_sensor(m, model, ranges, angles, RANGE_MAX)
+        got, want = q.weights(), port.samples()[:, 3]
+        q.close()
+        parity = {"particles": n, "max_rel_weight_diff_vs_port": float(np.abs(got / want - 1.0).max())}
+    except Exception as e:  # noqa: BLE001
+        parity = {"error": str(e)[:200]}
     pf.close()
     return {"workload": "beam model 100k x %d, 4000^2" % len(ranges), "ms": ms, "kernel": "k_score_beam", "kernel_ms": k_ms,
+            "sampled_parity": parity,
             "rays_per_s": P * len(ranges) / (ms * 1e-3), "steps_per_ray": steps_per_ray,
             "cell_steps_per_s": P * len(ranges) * steps_per_ray / (ms * 1e-3), "algorithmic_bytes": algo,
             "achieved_GBps": algo / (k_ms * 1e-3) / 1e9, "frac_of_hbm_peak": algo / (k_ms * 1e-3) / 1e9 / peak}
@@ -348,6 +371,25 @@ def leg_c4(ctx, cabi, synth, peak):
         out[cloud] = {"ms": ms, "kernel": "k_score_cloud", "kernel_ms": k_ms, "evals_per_s": P * len(pts) / (ms * 1e-3),
                       "algorithmic_bytes": algo, "achieved_GBps": algo / (k_ms * 1e-3) / 1e9,
                       "frac_of_hbm_peak": algo / (k_ms * 1e-3) / 1e9 / peak}
+        if cloud == "global":
+            # sampled parity at this shape (untimed): 64 of the particles against the C restatement over the same field
+            try:
+                from oracle import oracle as O  # checker only
+                n = 64
+                idx = np.linspace(0, P - 1, n).astype(np.int64)
+                sub = np.ascontiguousarray(aos[idx])
+                pm3 = O.PortMap3D(RES, keys, 0.36)
+                pm3.set_dense(m3.download_distances())
+                ocm = O.cloud_model(max_beams=4096, mount_translation=(0.2, 0.0, 1.5), mount_rotation=synth.rpy_quaternion(0, 0.1, 0))
+                want_total, want = pm3.cloud_apply(ocm, pts, sub)
+                q = cabi.ParticleFilter(ctx, 8, n)
+                q.upload_samples(sub)
+                q.score_cloud(m3, cm, pts)
+                got = q.weights()
+                q.close()
+                out["sampled_parity"] = {"particles": n, "max_rel_weight_diff_vs_port": float(np.abs(got / want - 1.0).max())}
+            except Exception as e:  # noqa: BLE001
+                out["sampled_parity"] = {"error": str(e)[:200]}
         pf.close()
     m3.close()
     return out

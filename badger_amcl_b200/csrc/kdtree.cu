@@ -993,7 +993,7 @@ static int fit_box(bamcl_pf* pf, SampleSet& set, long off, int n, double cx, dou
   pf->box_dense = false;
   pf->box_cells = 0;
   const bool force_hash = getenv("BAMCL_TREE_HASH") != nullptr;  // tests: exercise the hashed path
-  if (force_hash && pf_ranks(pf) == 1)
+  if (force_hash)  // (a distributed filter then takes build_replicated, as it would in a world too large for the grid)
     return BAMCL_OK;
   long cells = 1;
   for (int d = 0; d < 3; d++)

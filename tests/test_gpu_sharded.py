@@ -366,3 +366,37 @@ def test_distributed_motion_update_matches_the_single_gpu_filter(env):
     for off, cnt, smp, state in run_ranks(world, rank_fn):
         assert state == want_state
         assert np.array_equal(smp, want[off:off + cnt])
+
+
+def test_distributed_resample_falls_back_to_replicated_bins_in_a_huge_world(env, monkeypatch):
+    """a world whose pose bins do not fit the dense grid (forced here with BAMCL_TREE_HASH): every rank receives the whole
+    set and builds the hashed tree as a single GPU would -- same results"""
+    monkeypatch.setenv("BAMCL_TREE_HASH", "1")
+    O = env["O"]
+    n, world = 30000, 3
+    poses = synth.uniform_free_poses(env["cells"], RES, n, seed=1)
+    rng = np.random.default_rng(17)
+    port = O.PortPF(n // 10, n)
+    port.init_with_poses(poses)
+    init_want = (port.leaf_count(), port.node_count(), port.cluster_count())
+    port.srand48(7)
+    w = np.exp(rng.normal(0.0, 2.0, n))
+    w /= w.sum()
+    s = port.samples()
+    s[:, 3] = w
+    port.set_samples(s)
+    port.set_averages(1.0, 1.0)
+    port.update_resample()
+    got = _run_distributed(env, world, poses, [w], 7, n // 10)
+    for rank in range(world):
+        r0 = got[rank][0]["res"]
+        assert (r0.leaf_count, r0.node_count, r0.cluster_count) == init_want
+        g = got[rank][1]
+        r = g["res"]
+        sl = slice(g["off"], g["off"] + g["cnt"])
+        assert r.sample_count == port.sample_count()
+        assert np.array_equal(g["src"], port.resample_sources()[sl])
+        assert np.array_equal(g["samples"], port.samples()[sl])
+        assert (r.leaf_count, r.node_count, r.cluster_count) == (port.leaf_count(), port.node_count(), port.cluster_count())
+        assert np.array_equal(g["labels"], port.sample_clusters()[sl])
+        assert np.allclose(g["stats"], port.set_stats(), rtol=1e-6, atol=1e-9)

@@ -100,6 +100,7 @@ struct bamcl_ctx
 {
   int device = 0;
   cudaStream_t stream = nullptr;
+  int stream_priority = 0, low_priority = 0;  // the main (+ side) streams' priority and the lowest one of the device
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   long launches = 0;
   bamcl::DevBuf flush;  // > L2 scratch for bamcl_ctx_flush_l2

@@ -1,6 +1,7 @@
 // Context, error reporting, timing helpers.
 #include <algorithm>
 #include <cstdarg>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -106,7 +107,13 @@ int bamcl_ctx_create(int device, bamcl_ctx** out)
   BAMCL_CUDA_OK(cudaSetDevice(device));
   bamcl_ctx* ctx = new bamcl_ctx();
   ctx->device = device;
-  BAMCL_CUDA_OK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  // The context's stream (and the resampler's bucket side streams) run at the highest priority; the resampler's clustering
+  // chain goes to a side stream of the same or of the lowest priority, chosen per call (build_tree_and_stats, kdtree.cu).
+  int prio_lo = 0, prio_hi = 0;
+  BAMCL_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  ctx->stream_priority = prio_hi;
+  ctx->low_priority = prio_lo;
+  BAMCL_CUDA_OK(cudaStreamCreateWithPriority(&ctx->stream, cudaStreamNonBlocking, ctx->stream_priority));
   BAMCL_CUDA_OK(cudaEventCreate(&ctx->ev0));
   BAMCL_CUDA_OK(cudaEventCreate(&ctx->ev1));
   *out = ctx;

@@ -1172,7 +1172,16 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
     // leaf-count chain on the main stream; both join before anything is exchanged or copied back
     cudaStream_t main_stream = ctx->stream;
     BAMCL_CUDA_OK(cudaEventRecord(pf->ev_fork, main_stream));
-    BAMCL_CUDA_OK(cudaStreamWaitEvent(pf->aux_stream, pf->ev_fork, 0));
+    // Which side stream: with up to ~2M bins the tree chain is many short kernels, and behind the clustering pass's huge
+    // grid each of them would wait for a free slot -- the clustering chain takes the LOW-priority stream, the tree chain
+    // is served first and the two really overlap. With many more bins the tree's own kernels fill the machine and would
+    // starve the (longer) clustering chain: equal priorities there. Resample ms, low / equal priority (scripts/
+    // ab_priority.sh): 1M samples 0.78 / 0.83, 2M 1.12 / 1.17, 3M 1.75 / 1.79, 8M 2.84 / 2.72.
+    // BAMCL_PRIO_MODE = low | flat overrides.
+    static const char* prio_mode = getenv("BAMCL_PRIO_MODE");
+    const bool aux_low = prio_mode ? prio_mode[0] == 'l' : k_max <= 4000000;
+    cudaStream_t aux = aux_low ? pf->aux_stream_lo : pf->aux_stream;
+    BAMCL_CUDA_OK(cudaStreamWaitEvent(aux, pf->ev_fork, 0));
     {
       struct StreamSwap  // BAMCL_LAUNCH and the scan use ctx->stream; restored on every exit path
       {
@@ -1180,7 +1189,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
         cudaStream_t keep;
         ~StreamSwap() { c->stream = keep; }
       } swap{ctx, main_stream};
-      ctx->stream = pf->aux_stream;
+      ctx->stream = aux;
       const long threads = (long)k_max * 13;
       static const bool cc_volatile = getenv("BAMCL_CC_VOLATILE") != nullptr;  // A/B switch: forest reads bypass L1
       // (Measured and dropped: collecting the neighbour pairs first and uniting them in a second, dense launch. The
@@ -1277,7 +1286,7 @@ int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, dou
       if (stat_blocks > 0)
         BAMCL_LAUNCH(ctx, k_labels_stats, stat_blocks, ST_BLOCK, 0, sa);
       BAMCL_LAUNCH(ctx, k_set_sums_final, 1, 384, 0, pf->t_setpart.as<double>(), stat_blocks, set_tail);
-      BAMCL_CUDA_OK(cudaEventRecord(pf->ev_join, pf->aux_stream));
+      BAMCL_CUDA_OK(cudaEventRecord(pf->ev_join, aux));
     }
     // ---- main stream: the leaf count
     auto launch_general = [&]() -> int {

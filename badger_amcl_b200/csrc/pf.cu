@@ -232,13 +232,14 @@ int pf_ensure_streams(bamcl_pf* pf)
 {
   if (pf->aux_stream)
     return BAMCL_OK;
-  BAMCL_CUDA_OK(cudaStreamCreateWithFlags(&pf->aux_stream, cudaStreamNonBlocking));
+  BAMCL_CUDA_OK(cudaStreamCreateWithPriority(&pf->aux_stream, cudaStreamNonBlocking, pf->ctx->stream_priority));
+  BAMCL_CUDA_OK(cudaStreamCreateWithPriority(&pf->aux_stream_lo, cudaStreamNonBlocking, pf->ctx->low_priority));
   BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_fork, cudaEventDisableTiming));
   BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_join, cudaEventDisableTiming));
   BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_bucket_fork, cudaEventDisableTiming));
   for (int i = 0; i < 2; i++)
   {
-    BAMCL_CUDA_OK(cudaStreamCreateWithFlags(&pf->bucket_stream[i], cudaStreamNonBlocking));
+    BAMCL_CUDA_OK(cudaStreamCreateWithPriority(&pf->bucket_stream[i], cudaStreamNonBlocking, pf->ctx->stream_priority));
     BAMCL_CUDA_OK(cudaEventCreateWithFlags(&pf->ev_bucket_join[i], cudaEventDisableTiming));
   }
   BAMCL_CUDA_OK(cudaStreamCreateWithFlags(&pf->copy_stream, cudaStreamNonBlocking));
@@ -431,6 +432,8 @@ int bamcl_pf_destroy(bamcl_pf* pf)
   pf->t_hout.release();
   if (pf->aux_stream)
     cudaStreamDestroy(pf->aux_stream);
+  if (pf->aux_stream_lo)
+    cudaStreamDestroy(pf->aux_stream_lo);
   if (pf->ev_fork)
     cudaEventDestroy(pf->ev_fork);
   if (pf->ev_join)

@@ -90,7 +90,8 @@ struct bamcl_pf
   bamcl::DevBuf t_nkey, t_cur, t_child, t_first_at, t_side; // per node (creation order)
   bamcl::DevBuf t_parent, t_cid, t_nfirst, t_root;
   // the cluster chain (union-find, labels, statistics) runs on this stream next to the leaf-count chain
-  cudaStream_t aux_stream = nullptr;
+  cudaStream_t aux_stream = nullptr;     // same priority as the main stream
+  cudaStream_t aux_stream_lo = nullptr;  // lowest priority
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   // copies of host sample buffers overlap the kernels (bamcl_pf_update_planar_host / bamcl_pf_resample_host)
   cudaStream_t copy_stream = nullptr;

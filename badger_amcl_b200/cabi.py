@@ -200,7 +200,7 @@ SIGNATURES = {
     "bamcl_pf_skip_counts": (_I, [_P, _P, _I, _P, _I, _P]),
     "bamcl_pf_set_skip_counts": (_I, [_P, _P, _I, _L]),
     "bamcl_pf_set_random_pose_source": (_I, [_P, _P, _D, _D]),
-    "bamcl_map2d_from_occupancy_grid": (_I, [_P, _P, _I, _I, _D, _D, _D, _I, _P]),
+    "bamcl_map2d_from_occupancy_grid": (_I, [_P, _P, _I, _I, C.c_float, _D, _D, _I, _P]),
     "bamcl_map2d_download_cells": (_I, [_P, _P, _L]),
     "bamcl_map2d_geometry": (_I, [_P, _P, _P, _P]),
     "bamcl_scan_from_laserscan": (_I, [_P, _I, C.c_float, C.c_float, _D, _D, _D, _D, _P, _P, _P]),
@@ -208,6 +208,8 @@ SIGNATURES = {
     "bamcl_map2d_update_free_space": (_I, [_P, _D, _P]),
     "bamcl_map2d_download_free_space": (_I, [_P, _P, _L]),
     "bamcl_pf_init_uniform": (_I, [_P, _P, _D, _D, C.c_uint64, _P, _P]),
+    "bamcl_pf_init_uniform_3d": (_I, [_P, _P, _D, _D, C.c_uint64, _P, _P]),
+    "bamcl_pf_set_random_pose_source_3d": (_I, [_P, _P, _D, _D]),
     "bamcl_pose_covariance": (_I, [_P, _P]),
     "bamcl_pf_upload_window_samples": (_I, [_P, _P, _L, _L]),
     "bamcl_pf_download_window_samples": (_I, [_P, _P, _L, _L]),
@@ -306,7 +308,8 @@ class Map2D:
 
     @classmethod
     def from_occupancy_grid(cls, ctx, data, resolution, origin_xy=(0.0, 0.0), scale_up=1):
-        """Node2D::convertMap (node_2d.cpp:265-295): data = (height, width) int8 OccupancyGrid payload"""
+        """Node2D::convertMap (node_2d.cpp:265-295): data = (height, width) int8 OccupancyGrid payload; resolution is the
+        message's float32 field (narrowed here), so the map's resolution is float32(resolution) / scale_up in float"""
         data = np.ascontiguousarray(data, np.int8)
         self = cls.__new__(cls)
         self.L, self.ctx = lib(), ctx
@@ -477,11 +480,12 @@ class ParticleFilter:
 
     def init_uniform(self, map2d, threshold=0.0, multiplier=0.0):
         """initWithPoseFn(uniformPoseGenerator) on the device (particle_filter.cpp:136-162, node.cpp:823-868); the map's
-        free-space list must have been built (Map2D.update_free_space)"""
+        free-space list must have been built (Map2D.update_free_space); a Map3D draws from its cropped cell rectangle
+        (node_3d.cpp:306-318)"""
         res = ResampleResult()
         out = C.c_uint64()
-        _check(self.L.bamcl_pf_init_uniform(self.h, map2d.h, threshold, multiplier, self.drand48_state, C.byref(out),
-                                            C.byref(res)))
+        fn = self.L.bamcl_pf_init_uniform_3d if isinstance(map2d, Map3D) else self.L.bamcl_pf_init_uniform
+        _check(fn(self.h, map2d.h, threshold, multiplier, self.drand48_state, C.byref(out), C.byref(res)))
         self.drand48_state = out.value
         self.w_slow = self.w_fast = 0.0
         self.converged = False
@@ -490,7 +494,8 @@ class ParticleFilter:
 
     def set_random_pose_source(self, map2d, threshold=0.0, multiplier=0.0):
         """random_pose_fn_ = Node::uniformPoseGenerator over map2d's free-space list (node.cpp:262-264, 847-868)"""
-        _check(self.L.bamcl_pf_set_random_pose_source(self.h, map2d.h if map2d is not None else None, threshold, multiplier))
+        fn = self.L.bamcl_pf_set_random_pose_source_3d if isinstance(map2d, Map3D) else self.L.bamcl_pf_set_random_pose_source
+        _check(fn(self.h, map2d.h if map2d is not None else None, threshold, multiplier))
         self.device_pose_source = map2d is not None
 
     def init_with_current(self):

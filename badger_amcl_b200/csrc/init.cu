@@ -11,6 +11,7 @@
 #include <cstring>
 
 #include "lcg.cuh"
+#include "map3d.cuh"
 #include "pf.cuh"
 #include "scan.cuh"
 
@@ -53,10 +54,7 @@ struct UniformArgs
 {
   unsigned long long state0;
   int n, per_pose;  // per_pose = 1 + r generations per returned pose; the last one is kept
-  const int2* free_ij;
-  long free_n;
-  int size_x, size_y;
-  double resolution, origin_x, origin_y;
+  PoseSource src;
   double *x, *y, *th, *w;
   double weight;
 };
@@ -69,10 +67,8 @@ __global__ void __launch_bounds__(256) k_uniform_poses(const UniformArgs a)
   const unsigned long long gen = (unsigned long long)a.per_pose * (unsigned long long)s + (unsigned long long)(a.per_pose - 1);
   const unsigned long long u = lcg_skip(a.state0, 2ull * gen + 1ull), v = lcg_next(u);
   const double r1 = (double)u * 0x1p-48, r2 = (double)v * 0x1p-48;
-  const unsigned int k = (unsigned int)(r1 * (double)(size_t)a.free_n);  // node.cpp:831
-  const int2 c = a.free_ij[k];
-  a.x[s] = a.origin_x + (c.x - a.size_x / 2) * a.resolution;  // convertMapToWorld, occupancy_map.cpp:75-88
-  a.y[s] = a.origin_y + (c.y - a.size_y / 2) * a.resolution;
+  const unsigned int k = (unsigned int)(r1 * (double)(size_t)a.src.free_n);  // node.cpp:831
+  a.src.world(k, &a.x[s], &a.y[s]);                                            // convertMapToWorld
   a.th[s] = r2 * 2 * M_PI - M_PI;  // node.cpp:837
   a.w[s] = a.weight;
 }
@@ -84,10 +80,8 @@ __global__ void __launch_bounds__(256) k_uniform_poses_aos(const UniformArgs a, 
     return;
   const unsigned long long gen = (unsigned long long)a.per_pose * (unsigned long long)s + (unsigned long long)(a.per_pose - 1);
   const unsigned long long u = lcg_skip(a.state0, 2ull * gen + 1ull), v = lcg_next(u);
-  const unsigned int k = (unsigned int)((double)u * 0x1p-48 * (double)(size_t)a.free_n);
-  const int2 c = a.free_ij[k];
-  out3[3 * s] = a.origin_x + (c.x - a.size_x / 2) * a.resolution;
-  out3[3 * s + 1] = a.origin_y + (c.y - a.size_y / 2) * a.resolution;
+  const unsigned int k = (unsigned int)((double)u * 0x1p-48 * (double)(size_t)a.src.free_n);
+  a.src.world(k, &out3[3 * s], &out3[3 * s + 1]);
   out3[3 * s + 2] = (double)v * 0x1p-48 * 2 * M_PI - M_PI;
 }
 }  // namespace
@@ -96,9 +90,45 @@ namespace bamcl
 {
 // n calls of the filter's registered pose function (bamcl_pf_set_random_pose_source) from generator state `state0`,
 // written to out3_dev; *state_out = the state after them. Used by the systematic resampler (particle_filter.cpp:316-324).
+static void source_of_map2d(const bamcl_map2d* map, PoseSource* s)
+{
+  *s = PoseSource();
+  s->free_ij = map->free_ij.as<int2>();
+  s->free_n = map->free_count;
+  s->size_x = map->size_x;
+  s->size_y = map->size_y;
+  s->resolution = map->resolution;
+  s->origin_x = (double)map->origin_x;
+  s->origin_y = (double)map->origin_y;
+}
+// Node3D::updateFreeSpaceIndices (node_3d.cpp:306-318): for i in [min0, max0) for j in [min1, max1)
+static bool source_of_map3d(const bamcl_map3d* map, PoseSource* s)
+{
+  *s = PoseSource();
+  const long nx = (long)map->cmax[0] - map->cmin[0], ny = (long)map->cmax[1] - map->cmin[1];
+  if (nx <= 0 || ny <= 0 || nx * ny > 0x7fffffffl)
+    return false;
+  s->free_n = nx * ny;
+  s->resolution = map->resolution;
+  s->min_i = map->cmin[0];
+  s->min_j = map->cmin[1];
+  s->ny = (int)ny;
+  return true;
+}
+bool pf_pose_source(const bamcl_pf* pf, PoseSource* out)
+{
+  if (pf->rp_map && pf->rp_map->free_count > 0)
+  {
+    source_of_map2d(pf->rp_map, out);
+    return true;
+  }
+  if (pf->rp_map3d)
+    return source_of_map3d(pf->rp_map3d, out);
+  return false;
+}
+
 int device_random_poses(bamcl_pf* pf, unsigned long long state0, int n, double* out3_dev, unsigned long long* state_out)
 {
-  bamcl_map2d* map = pf->rp_map;
   long r = 0;
   if (pf->rp_threshold > 0.0 && pf->rp_multiplier < 1.0 && pf->rp_multiplier >= 0.0)
   {
@@ -110,18 +140,12 @@ int device_random_poses(bamcl_pf* pf, unsigned long long state0, int n, double* 
         return set_error(BAMCL_E_UNSUPPORTED, "resample: more than 1e6 de-weighting retries per random pose");
     }
   }
-  UniformArgs a;
-  memset(&a, 0, sizeof(a));
+  UniformArgs a{};
   a.state0 = state0 & LCG_MASK;
   a.n = n;
   a.per_pose = (int)(1 + r);
-  a.free_ij = map->free_ij.as<int2>();
-  a.free_n = map->free_count;
-  a.size_x = map->size_x;
-  a.size_y = map->size_y;
-  a.resolution = map->resolution;
-  a.origin_x = (double)map->origin_x;
-  a.origin_y = (double)map->origin_y;
+  if (!pf_pose_source(pf, &a.src))
+    return set_error(BAMCL_E_STATE, "resample: no pose source registered");
   if (n > 0)
     BAMCL_LAUNCH(pf->ctx, k_uniform_poses_aos, (unsigned)((n + 255) / 256), 256, 0, a, out3_dev);
   *state_out = lcg_skip(a.state0, 2ull * (unsigned long long)(1 + r) * (unsigned long long)n);
@@ -184,15 +208,11 @@ extern "C" int bamcl_map2d_download_free_space(bamcl_map2d* m, int* ij_out, long
   return BAMCL_OK;
 }
 
-extern "C" int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double starting_weight_threshold,
-                                     double deweight_multiplier, uint64_t drand48_state, uint64_t* drand48_state_out,
-                                     bamcl_resample_result* res)
+namespace
 {
-  if (!pf || !map || !drand48_state_out || !res)
-    return set_error(BAMCL_E_ARG, "bamcl_pf_init_uniform: null argument");
-  if (map->free_count <= 0)
-    return set_error(BAMCL_E_STATE, "bamcl_pf_init_uniform: the free-space list is empty or not built (node.cpp:826-830 "
-                                    "warns and returns an unset pose)");
+int init_uniform_from(bamcl_pf* pf, const PoseSource& src, double starting_weight_threshold, double deweight_multiplier,
+                      uint64_t drand48_state, uint64_t* drand48_state_out, bamcl_resample_result* res)
+{
   // node.cpp:849-866 with scorePose == 1.0: generations thrown away per returned pose
   long r = 0;
   if (starting_weight_threshold > 0.0 && deweight_multiplier < 1.0 && deweight_multiplier >= 0.0)
@@ -209,17 +229,11 @@ extern "C" int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double star
   pf->win_cnt = -1;
   SampleSet& set = pf->sets[pf->current];
   const int n = pf->max_samples;  // :147
-  UniformArgs a;
+  UniformArgs a{};
   a.state0 = drand48_state & LCG_MASK;
   a.n = n;
   a.per_pose = (int)(1 + r);
-  a.free_ij = map->free_ij.as<int2>();
-  a.free_n = map->free_count;
-  a.size_x = map->size_x;
-  a.size_y = map->size_y;
-  a.resolution = map->resolution;
-  a.origin_x = (double)map->origin_x;
-  a.origin_y = (double)map->origin_y;
+  a.src = src;
   a.x = set.x.as<double>();
   a.y = set.y.as<double>();
   a.th = set.th.as<double>();
@@ -235,5 +249,45 @@ extern "C" int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double star
   res->converged = 0;  // initConverged, :163-167
   *drand48_state_out = lcg_skip(a.state0, 2ull * (unsigned long long)(1 + r) * (unsigned long long)n);
   res->drand48_state = *drand48_state_out;
+  return BAMCL_OK;
+}
+}  // namespace
+
+extern "C" int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double starting_weight_threshold,
+                                     double deweight_multiplier, uint64_t drand48_state, uint64_t* drand48_state_out,
+                                     bamcl_resample_result* res)
+{
+  if (!pf || !map || !drand48_state_out || !res)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_init_uniform: null argument");
+  if (map->free_count <= 0)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_init_uniform: the free-space list is empty or not built (node.cpp:826-830 "
+                                    "warns and returns an unset pose)");
+  PoseSource src;
+  source_of_map2d(map, &src);
+  return init_uniform_from(pf, src, starting_weight_threshold, deweight_multiplier, drand48_state, drand48_state_out, res);
+}
+
+extern "C" int bamcl_pf_init_uniform_3d(bamcl_pf* pf, bamcl_map3d* map, double starting_weight_threshold,
+                                        double deweight_multiplier, uint64_t drand48_state, uint64_t* drand48_state_out,
+                                        bamcl_resample_result* res)
+{
+  if (!pf || !map || !drand48_state_out || !res)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_init_uniform_3d: null argument");
+  PoseSource src;
+  if (!source_of_map3d(map, &src))
+    return set_error(BAMCL_E_STATE, "bamcl_pf_init_uniform_3d: the map's cropped cell rectangle is empty (node.cpp:826-830 "
+                                    "warns and returns an unset pose)");
+  return init_uniform_from(pf, src, starting_weight_threshold, deweight_multiplier, drand48_state, drand48_state_out, res);
+}
+
+extern "C" int bamcl_pf_set_random_pose_source_3d(bamcl_pf* pf, bamcl_map3d* map_or_null, double starting_weight_threshold,
+                                                  double deweight_multiplier)
+{
+  if (!pf)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_set_random_pose_source_3d: null filter");
+  pf->rp_map = nullptr;
+  pf->rp_map3d = map_or_null;
+  pf->rp_threshold = starting_weight_threshold;
+  pf->rp_multiplier = deweight_multiplier;
   return BAMCL_OK;
 }

@@ -448,14 +448,14 @@ __global__ void __launch_bounds__(256) k_convert_grid(const signed char* __restr
 }
 }  // namespace
 
-extern "C" int bamcl_map2d_from_occupancy_grid(bamcl_ctx* ctx, const int8_t* data, int width, int height, double resolution,
+extern "C" int bamcl_map2d_from_occupancy_grid(bamcl_ctx* ctx, const int8_t* data, int width, int height, float resolution,
                                                double origin_x, double origin_y, int scale_up, bamcl_map2d** out)
 {
-  if (!ctx || !data || !out || width <= 0 || height <= 0 || scale_up < 1 || !(resolution > 0.0))
+  if (!ctx || !data || !out || width <= 0 || height <= 0 || scale_up < 1 || !(resolution > 0.0f))
     return set_error(BAMCL_E_ARG, "bamcl_map2d_from_occupancy_grid: bad arguments");
   if ((long)width * scale_up > 0x7fffffffl || (long)height * scale_up > 0x7fffffffl)
     return set_error(BAMCL_E_ARG, "bamcl_map2d_from_occupancy_grid: scaled size overflows int");
-  const double res = resolution / scale_up;  // :267
+  const double res = resolution / scale_up;  // :267, float / int evaluated in float, then widened
   const int size_x = width * scale_up, size_y = height * scale_up;
   const double x_origin = origin_x + (size_x / 2) * res;  // :275-276, narrowed to float by pcl::PointXYZ (:277)
   const double y_origin = origin_y + (size_y / 2) * res;

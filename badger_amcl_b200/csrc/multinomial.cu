@@ -52,10 +52,7 @@ struct MultiArgs
   const int* pos;  // null: output k starts at position 2k
   double w_diff;
   int retries;  // generations thrown away per random pose (uniformPoseGenerator's de-weighting loop)
-  const int2* free_ij;
-  long free_n;
-  int size_x, size_y;
-  double resolution, origin_x, origin_y;
+  PoseSource rp;
 };
 
 __global__ void __launch_bounds__(256) k_select_multinomial(const MultiArgs a)
@@ -69,11 +66,9 @@ __global__ void __launch_bounds__(256) k_select_multinomial(const MultiArgs a)
   {
     // random_pose_fn_() = the last of (1 + retries) randomFreeSpacePose generations (node.cpp:823-868)
     const unsigned long long u = lcg_skip(a.state0, p + 2ull + 2ull * (unsigned long long)a.retries), v = lcg_next(u);
-    const unsigned int cell = (unsigned int)((double)u * 0x1p-48 * (double)(size_t)a.free_n);
-    const int2 c = a.free_ij[cell];
+    const unsigned int cell = (unsigned int)((double)u * 0x1p-48 * (double)(size_t)a.rp.free_n);
     a.src[k] = -1;
-    a.bx[k] = a.origin_x + (c.x - a.size_x / 2) * a.resolution;
-    a.by[k] = a.origin_y + (c.y - a.size_y / 2) * a.resolution;
+    a.rp.world(cell, &a.bx[k], &a.by[k]);
     a.bth[k] = (double)v * 0x1p-48 * 2 * M_PI - M_PI;
     a.bw[k] = 1.0;
     return;
@@ -206,7 +201,8 @@ namespace bamcl
 int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res)
 {
   const bool inject = prm->w_diff > 0.0;
-  if (inject && (!pf->rp_map || pf->rp_map->free_count <= 0))
+  PoseSource rp_src;
+  if (inject && !pf_pose_source(pf, &rp_src))
     return set_error(BAMCL_E_UNSUPPORTED,
                      "multinomial resampling with w_diff > 0 interleaves random_pose_fn_() with the resampler's drand48 "
                      "draws one output at a time (particle_filter.cpp:385-387): register the node's pose function with "
@@ -248,10 +244,7 @@ int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
   a.pos = nullptr;
   a.w_diff = 0.0;
   a.retries = 0;
-  a.free_ij = nullptr;
-  a.free_n = 0;
-  a.size_x = a.size_y = 0;
-  a.resolution = a.origin_x = a.origin_y = 0.0;
+  a.rp = PoseSource();
   int* d_pos = nullptr;
   if (inject)
   {
@@ -290,13 +283,7 @@ int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
     a.pos = d_pos;
     a.w_diff = prm->w_diff;
     a.retries = (int)retries;
-    a.free_ij = pf->rp_map->free_ij.as<int2>();
-    a.free_n = pf->rp_map->free_count;
-    a.size_x = pf->rp_map->size_x;
-    a.size_y = pf->rp_map->size_y;
-    a.resolution = pf->rp_map->resolution;
-    a.origin_x = (double)pf->rp_map->origin_x;
-    a.origin_y = (double)pf->rp_map->origin_y;
+    a.rp = rp_src;
   }
   BAMCL_LAUNCH(ctx, k_select_multinomial, (n + 255) / 256, 256, 0, a);
 
@@ -365,6 +352,7 @@ extern "C" int bamcl_pf_set_random_pose_source(bamcl_pf* pf, bamcl_map2d* map_or
   if (!pf)
     return set_error(BAMCL_E_ARG, "bamcl_pf_set_random_pose_source: null filter");
   pf->rp_map = map_or_null;
+  pf->rp_map3d = nullptr;
   pf->rp_threshold = starting_weight_threshold;
   pf->rp_multiplier = deweight_multiplier;
   return BAMCL_OK;

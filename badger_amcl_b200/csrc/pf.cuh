@@ -59,6 +59,37 @@ struct StagedCloud
 };
 }  // namespace bamcl
 
+namespace bamcl
+{
+// What Node::randomFreeSpacePose (node.cpp:823-840) draws a cell from and how the cell becomes a world position.
+// 2-D (map_type 2): the list of Node2D::updateFreeSpaceIndices, OccupancyMap::convertMapToWorld (occupancy_map.cpp:75-88).
+// 3-D (map_type 3): Node3D::updateFreeSpaceIndices (node_3d.cpp:306-318) lists every (i, j) of the OctoMap's cropped cell
+// rectangle [min, max), i outer - never materialised here - and OctoMap::convertMapToWorld is i * resolution
+// (octomap.cpp:83-95).
+struct PoseSource
+{
+  const int2* free_ij = nullptr;  // null = the rectangle
+  long free_n = 0;
+  int size_x = 0, size_y = 0;
+  double resolution = 0.0, origin_x = 0.0, origin_y = 0.0;
+  int min_i = 0, min_j = 0, ny = 1;
+  __device__ __forceinline__ void world(unsigned int k, double* x, double* y) const
+  {
+    if (free_ij)
+    {
+      const int2 c = free_ij[k];
+      *x = origin_x + (c.x - size_x / 2) * resolution;
+      *y = origin_y + (c.y - size_y / 2) * resolution;
+    }
+    else
+    {
+      *x = (min_i + (int)(k / (unsigned int)ny)) * resolution;
+      *y = (min_j + (int)(k % (unsigned int)ny)) * resolution;
+    }
+  }
+};
+}  // namespace bamcl
+
 struct bamcl_pf
 {
   bamcl_ctx* ctx = nullptr;
@@ -81,8 +112,10 @@ struct bamcl_pf
   bamcl::DevBuf seg_buf;   // systematic target segments
   // multinomial resampling with random-pose injection: stream positions of the outputs + jump tables (multinomial.cu)
   bamcl::DevBuf mn_buf;
-  // random_pose_fn_ = Node::uniformPoseGenerator over this map's free-space list (bamcl_pf_set_random_pose_source)
+  // random_pose_fn_ = Node::uniformPoseGenerator over this map's free-space list (bamcl_pf_set_random_pose_source), or
+  // over the OctoMap's cropped cell rectangle (bamcl_pf_set_random_pose_source_3d)
   bamcl_map2d* rp_map = nullptr;
+  bamcl_map3d* rp_map3d = nullptr;
   double rp_threshold = 0.0, rp_multiplier = 0.0;
   // kd-tree / clustering workspace (kdtree.cu), shared by both sets
   bamcl::DevBuf t_hkeys, t_hfirst, t_hnode;                 // hash table over pose bins
@@ -179,6 +212,8 @@ void pf_mark(bamcl_pf* pf, const char* phase);
 void pf_mark_report(bamcl_pf* pf);
 // perm_out (device, window-local indices) = this rank's window ordered by the Morton code of its coarse (x, y) cell;
 // cell = edge of a coarse cell in metres, (x0, y0) = lower corner of the area. Order inside a cell is arbitrary.
+// the registered pose source (rp_map's list or rp_map3d's rectangle); false = none registered / empty (init.cu)
+bool pf_pose_source(const bamcl_pf* pf, PoseSource* out);
 int pf_spatial_order(bamcl_pf* pf, double x0, double y0, double cell, const int** perm_out);
 int pf_reduce_total(bamcl_pf* pf, double* d_total);  // deterministic sum of the current set's weights -> device scalar
 int pf_read_scalar(bamcl_pf* pf, int slot, double* out);  // device scalar slot -> host (synchronises)

@@ -1224,7 +1224,8 @@ static int resample_impl(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
   // random poses: handed over by the caller (what its random_pose_fn_ returned), or -- when none are and the node's pose
   // function is registered (bamcl_pf_set_random_pose_source) -- generated on the device from the stream, after the
   // start draw (:309 then :316-324)
-  const bool device_poses = n_rand > 0 && !prm->random_poses && pf->rp_map && pf->rp_map->free_count > 0;
+  PoseSource rp_probe;
+  const bool device_poses = n_rand > 0 && !prm->random_poses && pf_pose_source(pf, &rp_probe);
   if (n_rand > 0 && !device_poses && (!prm->random_poses || prm->n_random_poses < n_rand))
     return set_error(BAMCL_E_ARG, "bamcl_pf_resample: %d random poses needed, %ld supplied", n_rand, prm->n_random_poses);
   // :309-310
@@ -1688,7 +1689,8 @@ int bamcl_pf_shard_resample(bamcl_pf* pf, const bamcl_resample_params* prm, bamc
   }
   const int n_rand = w_diff * new_count;
   const int n_sys = new_count - n_rand;
-  const bool device_poses = n_rand > 0 && !prm->random_poses && pf->rp_map && pf->rp_map->free_count > 0;
+  PoseSource rp_probe;
+  const bool device_poses = n_rand > 0 && !prm->random_poses && pf_pose_source(pf, &rp_probe);
   if (n_rand > 0 && !device_poses && (!prm->random_poses || prm->n_random_poses < n_rand))
     return set_error(BAMCL_E_ARG, "bamcl_pf_shard_resample: %d random poses needed, %ld supplied", n_rand, prm->n_random_poses);
   // :309-310

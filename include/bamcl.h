@@ -369,9 +369,11 @@ int bamcl_pf_update_action(bamcl_pf* pf, const bamcl_odom_model* model, const ba
 /* ---- scan / map ingestion */
 /* Node2D::convertMap (node_2d.cpp:265-295): nav_msgs/OccupancyGrid (data row-major, width x height, 0 free / 100
  * occupied / anything else unknown) -> a map of (width x scale_up) x (height x scale_up) cells at resolution / scale_up
- * with the origin moved to the map centre (:275-277, narrowed to float as pcl::PointXYZ does). The message bytes are
- * uploaded once and expanded on the device. */
-int bamcl_map2d_from_occupancy_grid(bamcl_ctx* ctx, const int8_t* data, int width, int height, double resolution,
+ * with the origin moved to the map centre (:275-277, narrowed to float as pcl::PointXYZ does). `resolution` is the
+ * message's float32 field and the division by scale_up is done in float (:267: float / int), as the compiled reference
+ * does: a 0.05 m grid becomes a map of resolution 0.05000000074505806. The message bytes are uploaded once and
+ * expanded on the device. */
+int bamcl_map2d_from_occupancy_grid(bamcl_ctx* ctx, const int8_t* data, int width, int height, float resolution,
                                     double origin_x, double origin_y, int scale_up, bamcl_map2d** out);
 /* cell states back to the host (-1 free, 0 unknown, +1 occupied; index = i + j*size_x), and the map's geometry */
 int bamcl_map2d_download_cells(bamcl_map2d* m, int8_t* cells, long n);
@@ -403,6 +405,12 @@ int bamcl_map2d_download_free_space(bamcl_map2d* m, int* ij_out, long n);
 int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double starting_weight_threshold, double deweight_multiplier,
                           uint64_t drand48_state, uint64_t* drand48_state_out, bamcl_resample_result* result);
 
+/* The same with map_type 3 (Node3D): Node3D::updateFreeSpaceIndices (node_3d.cpp:306-318) lists every (i, j) of the
+ * OctoMap's cropped cell rectangle [min, max) (OctoMap::getMinMaxCells, i outer), and OctoMap::convertMapToWorld
+ * (octomap.cpp:83-95) places cell (i, j) at (i * resolution, j * resolution). The rectangle is never materialised. */
+int bamcl_pf_init_uniform_3d(bamcl_pf* pf, bamcl_map3d* map, double starting_weight_threshold, double deweight_multiplier,
+                             uint64_t drand48_state, uint64_t* drand48_state_out, bamcl_resample_result* result);
+
 /* random_pose_fn_ of the filter (particle_filter.h:128; the node wires in Node::uniformPoseGenerator, node.cpp:262-264):
  * registers `map`'s free-space list (bamcl_map2d_update_free_space) and the generator's two parameters, so that
  * multinomial resampling with w_diff > 0 (particle_filter.cpp:385-388) draws its random poses on the device from the
@@ -411,6 +419,9 @@ int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double starting_weight
  * must outlive the filter or be unregistered first. */
 int bamcl_pf_set_random_pose_source(bamcl_pf* pf, bamcl_map2d* map_or_null, double starting_weight_threshold,
                                     double deweight_multiplier);
+/* the 3-D node's pose function (the OctoMap's cropped cell rectangle); replaces a 2-D source and vice versa */
+int bamcl_pf_set_random_pose_source_3d(bamcl_pf* pf, bamcl_map3d* map_or_null, double starting_weight_threshold,
+                                       double deweight_multiplier);
 
 /* ---- pose read-out */
 /* Node2D::getMaxWeightPose (node_2d.cpp:588-617): weight and mean pose of the first cluster with the greatest weight,

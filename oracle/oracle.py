@@ -201,6 +201,25 @@ def ref_lib():
             "ref_pf_cluster_count": (I, [P]), "ref_pf_resample_limit": (I, [P, I]),
             "ref_pf_get_sample_clusters": (None, [P, P]), "ref_pf_get_cluster_stats": (None, [P, P]),
             "ref_pf_get_set_stats": (None, [P, P]),
+            "ref_gaussian_sample": (None, [P, P, L_, P]),
+            "ref_ros_reset": (None, []), "ref_ros_set_param_num": (None, [C.c_char_p, D]),
+            "ref_ros_set_param_str": (None, [C.c_char_p, C.c_char_p]), "ref_ros_set_time": (None, [D]),
+            "ref_ros_set_tf": (None, [C.c_char_p, C.c_char_p, P, P]), "ref_ros_clear_tf": (None, [C.c_char_p, C.c_char_p]),
+            "ref_ros_message_count": (L_, [C.c_char_p]), "ref_ros_call_service": (I, [C.c_char_p]),
+            "ref_ros_fire_timers": (I, []), "ref_ros_reconfigure": (I, []),
+            "ref_node_create": (V, []), "ref_node_destroy": (None, [P]),
+            "ref_ros_publish_map": (I, [P, I, I, F, D, D]), "ref_ros_publish_octomap": (I, [D, P, L_, I]),
+            "ref_ros_publish_scan": (I, [C.c_char_p, D, F, F, F, F, F, P, I]),
+            "ref_ros_publish_cloud": (I, [C.c_char_p, D, P, L_]), "ref_ros_publish_odom": (I, [D, D, D, D]),
+            "ref_ros_publish_initial_pose": (I, [C.c_char_p, D, D, D, D, P]),
+            "ref_node_pf": (V, [P]), "ref_node_map2d": (V, [P]), "ref_node_map3d": (V, [P]),
+            "ref_map2d_geometry": (None, [P, P, P, P]),
+            "ref_node_free_space_count": (L_, [P]), "ref_node_free_space": (None, [P, P]),
+            "ref_node_uniform_poses": (None, [P, L_, P]), "ref_node_scan_data": (I, [P, P, P, P, I]),
+            "ref_node_angle_stats": (I, [P, C.c_char_p, D, F, F, P]), "ref_node_cloud_data": (L_, [P, P, L_]),
+            "ref_node_max_weight_pose": (I, [P, P, P]), "ref_ros_last_pose": (L_, [P]),
+            "ref_ros_last_particlecloud": (L_, [P, L_]), "ref_node_latest_tf": (I, [P, P]),
+            "ref_node_state": (None, [P, P]), "ref_node_odom_pose": (I, [P, D, P]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)
@@ -829,10 +848,12 @@ def cloud_model(model_type=0, max_beams=4096, z_hit=0.95, z_rand=0.05, sigma_hit
 # The node translation units are ROS nodes and cannot be compiled here: these numpy restatements are PARITY UNPINNED
 # (no reference test or golden vector covers them); they follow the cited lines statement by statement.
 def convert_map(data, resolution, origin_xy, scale_up=1):
-    """Node2D::convertMap (node_2d.cpp:265-295) -> (cells (size_y, size_x) int8, resolution, (origin_x, origin_y) f32)"""
+    """Node2D::convertMap (node_2d.cpp:265-295) -> (cells (size_y, size_x) int8, resolution, (origin_x, origin_y) f32).
+    info.resolution is a float32 message field and `resolution / map_scale_up_factor_` (:267) is float / int = a float
+    division; pinned against the compiled node (tests/test_oracle_port_vs_ref.py::test_node_convert_map)."""
     data = np.asarray(data, np.int8)
     height, width = data.shape
-    res = resolution / scale_up
+    res = float(np.float32(resolution) / np.float32(scale_up))
     size_x, size_y = width * scale_up, height * scale_up
     ox = np.float32(origin_xy[0] + (size_x // 2) * res)
     oy = np.float32(origin_xy[1] + (size_y // 2) * res)
@@ -864,3 +885,215 @@ def cloud_subsample(xyz, max_beams):
     count = len(xyz)
     step = max(int((count - 1) / (max_beams - 1)), 1)  # C integer division truncates toward zero
     return xyz[0:count:step].copy()
+
+
+def uniform_poses_rect(min_ij, max_ij, resolution, rng, n, threshold=0.0, multiplier=0.0):
+    """n calls of Node::uniformPoseGenerator (node.cpp:847-868, scorePose == 1.0) with map_type 3: the free list of
+    Node3D::updateFreeSpaceIndices (node_3d.cpp:306-318) is every (i, j) of [min, max), i outer; OctoMap::convertMapToWorld
+    (octomap.cpp:83-95) puts cell (i, j) at (i * resolution, j * resolution). Draws from rng (an oracle.Rng)."""
+    L = port_lib()
+    ny = int(max_ij[1]) - int(min_ij[1])
+    size = (int(max_ij[0]) - int(min_ij[0])) * ny
+    out = np.empty((n, 3))
+
+    def generate():
+        k = int(L.orc_drand48(C.byref(rng)) * size)  # node.cpp:831
+        th = L.orc_drand48(C.byref(rng)) * 2 * np.pi - np.pi  # :837
+        return (int(min_ij[0]) + k // ny) * resolution, (int(min_ij[1]) + k % ny) * resolution, th
+
+    for s in range(n):
+        good = threshold
+        p = generate()
+        if good > 0.0 and 0.0 <= multiplier < 1.0:
+            while 1.0 < good:
+                p = generate()
+                good *= multiplier
+        out[s] = p
+    return out
+
+
+# ----------------------------------------------------------------------------------------------
+# the reference's ROS node (node/node.cpp, node_2d.cpp, node_3d.cpp compiled against oracle/shim)
+# ----------------------------------------------------------------------------------------------
+def yaw_quat(yaw):
+    """quaternion (x, y, z, w) of a rotation about z, for the tf table"""
+    return (0.0, 0.0, float(np.sin(0.5 * yaw)), float(np.cos(0.5 * yaw)))
+
+
+class RefNode:
+    """badger_amcl::Node of the reference, driven in process: `params` fill the parameter table the node reads in its
+    constructor (private names without the "~"), tf comes from set_tf, messages are delivered synchronously to the node's
+    own callbacks. One node at a time (the table is process-global)."""
+
+    def __init__(self, params=None, map_type=2):
+        self.L = ref_lib()
+        self.L.ref_ros_reset()
+        self.set_params(dict(map_type=map_type, save_pose=False))
+        self.set_params(params or {})
+        self.h = self.L.ref_node_create()
+
+    def close(self):
+        if self.h:
+            self.L.ref_node_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_params(self, params):
+        for k, v in params.items():
+            if isinstance(v, str):
+                self.L.ref_ros_set_param_str(k.encode(), v.encode())
+            else:
+                self.L.ref_ros_set_param_num(k.encode(), float(v))
+
+    def reconfigure(self, params=None):
+        """dynamic_reconfigure callback with the table's current values (Node::reconfigureCB, node.cpp:188-293)"""
+        self.set_params(params or {})
+        return self.L.ref_ros_reconfigure()
+
+    def set_time(self, t):
+        self.L.ref_ros_set_time(float(t))
+
+    def set_tf(self, target, source, xyz=(0.0, 0.0, 0.0), quat=(0.0, 0.0, 0.0, 1.0)):
+        a, q = np.array(xyz, np.float64), np.array(quat, np.float64)
+        self.L.ref_ros_set_tf(target.encode(), source.encode(), _ptr(a), _ptr(q))
+
+    def set_odom(self, x, y, yaw, odom="odom", base="base_link"):
+        """the odom -> base_link transform Node::getOdomPose looks up (node.cpp:795-821)"""
+        self.set_tf(odom, base, (x, y, 0.0), yaw_quat(yaw))
+
+    def publish_map(self, data, resolution, origin_xy=(0.0, 0.0)):
+        d = np.ascontiguousarray(data, np.int8)
+        return self.L.ref_ros_publish_map(_ptr(d), d.shape[1], d.shape[0], resolution, origin_xy[0], origin_xy[1])
+
+    def publish_octomap(self, resolution, keys, binary=True):
+        k = np.ascontiguousarray(keys, np.int32)
+        return self.L.ref_ros_publish_octomap(resolution, _ptr(k), len(k), int(binary))
+
+    def publish_scan(self, ranges, angle_min, angle_increment, range_min, range_max, stamp=0.0, frame="laser",
+                     angle_max=None):
+        r = np.ascontiguousarray(ranges, np.float32)
+        if angle_max is None:
+            angle_max = angle_min + angle_increment * (len(r) - 1)
+        return self.L.ref_ros_publish_scan(frame.encode(), stamp, angle_min, angle_max, angle_increment, range_min,
+                                           range_max, _ptr(r), len(r))
+
+    def publish_cloud(self, xyz, stamp=0.0, frame="lidar"):
+        p = np.ascontiguousarray(xyz, np.float32)
+        return self.L.ref_ros_publish_cloud(frame.encode(), stamp, _ptr(p), len(p))
+
+    def publish_odom(self, x, y, yaw, stamp=0.0):
+        return self.L.ref_ros_publish_odom(stamp, x, y, yaw)
+
+    def publish_initial_pose(self, x, y, yaw, cov36=None, frame="map", stamp=0.0):
+        c = np.zeros(36) if cov36 is None else np.ascontiguousarray(cov36, np.float64).reshape(36)
+        return self.L.ref_ros_publish_initial_pose(frame.encode(), stamp, x, y, yaw, _ptr(c))
+
+    def global_localization(self):
+        return self.L.ref_ros_call_service(b"global_localization")
+
+    def fire_timers(self):
+        return self.L.ref_ros_fire_timers()
+
+    def message_count(self, topic):
+        return self.L.ref_ros_message_count(topic.encode())
+
+    # ---- what the node holds / computed
+    def pf(self):
+        h = self.L.ref_node_pf(self.h)
+        if not h:
+            return None
+        p = RefPF.__new__(RefPF)
+        p.L, p.h, p.max_samples = self.L, h, None
+        return p
+
+    def map2d(self):
+        """(cells (size_y, size_x) int8, resolution, (origin_x, origin_y), handle-backed RefMap2D) of Node2D::map_"""
+        h = self.L.ref_node_map2d(self.h)
+        if not h:
+            return None
+        size, res, org = (C.c_int * 2)(), C.c_double(), (C.c_double * 2)()
+        self.L.ref_map2d_geometry(h, size, C.byref(res), org)
+        m = RefMap2D.__new__(RefMap2D)
+        m.L, m.h, m.size_x, m.size_y, m.resolution = self.L, h, size[0], size[1], res.value
+        m.origin = (org[0], org[1])
+        cells = np.empty((m.size_y, m.size_x), np.int8)
+        for j in range(m.size_y):
+            for i in range(m.size_x):
+                cells[j, i] = self.L.ref_map2d_get_cell(h, i, j)
+        m.cells = cells
+        return m
+
+    def map3d(self):
+        h = self.L.ref_node_map3d(self.h)
+        if not h:
+            return None
+        m = RefMap3D.__new__(RefMap3D)
+        m.L, m.h = self.L, h
+        return m
+
+    def free_space(self):
+        n = self.L.ref_node_free_space_count(self.h)
+        out = np.empty((n, 2), np.int32)
+        self.L.ref_node_free_space(self.h, _ptr(out))
+        return out
+
+    def uniform_poses(self, n):
+        out = np.empty((n, 3))
+        self.L.ref_node_uniform_poses(self.h, n, _ptr(out))
+        return out
+
+    def scan_data(self, capacity=4096):
+        r, a, m = np.empty(capacity), np.empty(capacity), C.c_double()
+        n = self.L.ref_node_scan_data(self.h, _ptr(r), _ptr(a), C.byref(m), capacity)
+        return None if n < 0 else (r[:n].copy(), a[:n].copy(), m.value)
+
+    def angle_stats(self, angle_min, angle_increment, frame="laser", stamp=0.0):
+        out = np.empty(2)
+        ok = self.L.ref_node_angle_stats(self.h, frame.encode(), stamp, angle_min, angle_increment, _ptr(out))
+        return (out[0], out[1]) if ok == 1 else None
+
+    def cloud_data(self, capacity=1 << 20):
+        out = np.empty((capacity, 3), np.float32)
+        n = self.L.ref_node_cloud_data(self.h, _ptr(out), capacity)
+        return None if n < 0 else out[:n].copy()
+
+    def max_weight_pose(self):
+        w, p = C.c_double(), np.empty(3)
+        ok = self.L.ref_node_max_weight_pose(self.h, C.byref(w), _ptr(p))
+        return (w.value, p) if ok == 1 else None
+
+    def last_pose(self):
+        """last amcl_pose message: dict(count, position, orientation (x, y, z, w), stamp, covariance (6, 6))"""
+        out = np.empty(44)
+        n = self.L.ref_ros_last_pose(_ptr(out))
+        if n == 0:
+            return None
+        return dict(count=n, position=out[0:3].copy(), orientation=out[3:7].copy(), stamp=out[7],
+                    covariance=out[8:44].reshape(6, 6).copy())
+
+    def last_particlecloud(self, capacity=1 << 20):
+        out = np.empty((capacity, 7))
+        n = self.L.ref_ros_last_particlecloud(_ptr(out), capacity)
+        return None if n < 0 else out[:n].copy()
+
+    def latest_tf(self):
+        out = np.empty(7)
+        return out if self.L.ref_node_latest_tf(self.h, _ptr(out)) else None
+
+    def odom_pose(self, stamp=0.0):
+        """Node::getOdomPose (node.cpp:795-821): (x, y, yaw) from the odom -> base_link transform, yaw through tf2"""
+        out = np.empty(3)
+        return out if self.L.ref_node_odom_pose(self.h, stamp, _ptr(out)) else None
+
+    def state(self):
+        out = np.empty(11)
+        self.L.ref_node_state(self.h, _ptr(out))
+        return dict(odom_init=bool(out[0]), global_localization_active=bool(out[1]), nd_global_localization_active=bool(out[2]),
+                    resample_count=int(out[3]), scanners=int(out[4]), pf_odom_pose=out[5:8].copy(),
+                    absolute_motion=out[8:11].copy())
+

@@ -14,7 +14,12 @@ struct ShimLeaf
   int k[3];
   bool occupied;
 };
-class OcTree
+class AbstractOcTree
+{
+public:
+  virtual ~AbstractOcTree() {}
+};
+class OcTree : public AbstractOcTree
 {
 public:
   explicit OcTree(double res) : res_(res) {}

@@ -1,0 +1,3 @@
+// oracle/shim: TEST INFRASTRUCTURE ONLY.
+#pragma once
+#include <pcl/point_cloud.h>

@@ -21,5 +21,14 @@ public:
   std::vector<T> points;
   iterator begin() { return points.begin(); }
   iterator end() { return points.end(); }
+  std::size_t size() const { return points.size(); }
+  const T& at(std::size_t n) const { return points.at(n); }
+  T& at(std::size_t n) { return points.at(n); }
+  void push_back(const T& pt)  // pcl::PointCloud::push_back
+  {
+    points.push_back(pt);
+    width = static_cast<uint32_t>(points.size());
+    height = 1;
+  }
 };
 }  // namespace pcl

@@ -9,3 +9,4 @@
 #define ROS_INFO_STREAM(x) ((void)0)
 #define ROS_WARN_STREAM(x) ((void)0)
 #define ROS_ERROR_STREAM(x) ((void)0)
+#define ROS_INFO_DELAYED_THROTTLE(...) ((void)0)

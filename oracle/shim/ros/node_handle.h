@@ -1,19 +1,3 @@
-// oracle/shim: TEST INFRASTRUCTURE ONLY. No-op NodeHandle/Publisher (only used for a debug cloud).
+// oracle/shim: TEST INFRASTRUCTURE ONLY. See ros/shim_bus.h.
 #pragma once
-#include <string>
-#include <cstdint>
-namespace ros
-{
-class Publisher
-{
-public:
-  template <typename T>
-  void publish(const T&) const {}
-};
-class NodeHandle
-{
-public:
-  template <typename T>
-  Publisher advertise(const std::string&, uint32_t, bool = false) { return Publisher(); }
-};
-}  // namespace ros
+#include <ros/shim_bus.h>

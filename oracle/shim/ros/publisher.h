@@ -1,2 +1,3 @@
+// oracle/shim: TEST INFRASTRUCTURE ONLY. See ros/shim_bus.h.
 #pragma once
-#include <ros/node_handle.h>
+#include <ros/shim_bus.h>

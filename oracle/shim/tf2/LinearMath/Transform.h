@@ -1,9 +1,9 @@
 // oracle/shim: TEST INFRASTRUCTURE ONLY. tf2::Vector3 / Quaternion / Matrix3x3 / Transform look-alikes (f64, tf2Scalar =
 // double), restating the published arithmetic of ros/geometry2 tf2/LinearMath (version unpinned by the reference's
 // package.xml:33-35, so this sequence is "parity unpinned"): Quaternion::setRPY, Matrix3x3::setRotation /
-// getRotation (Shepperd branches) / operator*, Transform::operator*. It exists so that the reference's
-// sensors/point_cloud_scanner.cpp compiles UNMODIFIED into oracle/_ref; everything that file computes itself
-// (voxel conversion, distance look-up, mixture, weights, recalcWeight) is then the reference's own code.
+// getRotation (Shepperd branches) / getEulerYPR / operator*, Quaternion product, Transform::operator* / inverse. It exists
+// so that the reference's sensors/point_cloud_scanner.cpp and node/*.cpp compile UNMODIFIED into oracle/_ref; everything
+// those files compute themselves is then the reference's own code.
 #pragma once
 #include <cmath>
 namespace tf2
@@ -18,6 +18,10 @@ public:
   double x() const { return m[0]; }
   double y() const { return m[1]; }
   double z() const { return m[2]; }
+  double getX() const { return m[0]; }
+  double getY() const { return m[1]; }
+  double getZ() const { return m[2]; }
+  Vector3 operator-() const { return Vector3(-m[0], -m[1], -m[2]); }
   double dot(const Vector3& v) const { return m[0] * v.m[0] + m[1] * v.m[1] + m[2] * v.m[2]; }
   double operator[](int i) const { return m[i]; }
 };
@@ -32,6 +36,11 @@ public:
   double z() const { return q[2]; }
   double w() const { return q[3]; }
   double length2() const { return q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]; }
+  Quaternion operator*(const Quaternion& o) const  // tf2::operator*(Quaternion, Quaternion)
+  {
+    return Quaternion(w() * o.x() + x() * o.w() + y() * o.z() - z() * o.y(), w() * o.y() + y() * o.w() + z() * o.x() - x() * o.z(),
+                      w() * o.z() + z() * o.w() + x() * o.y() - y() * o.x(), w() * o.w() - x() * o.x() - y() * o.y() - z() * o.z());
+  }
   void setRPY(double roll, double pitch, double yaw)
   {
     const double halfYaw = yaw * 0.5, halfPitch = pitch * 0.5, halfRoll = roll * 0.5;
@@ -95,6 +104,33 @@ public:
     }
     out = Quaternion(temp[0], temp[1], temp[2], temp[3]);
   }
+  // Matrix3x3::getEulerYPR, solution 1 (the default), and getRPY = the same with the outputs reordered
+  void getEulerYPR(double& yaw, double& pitch, double& roll) const
+  {
+    const double pi = 3.1415926535897932384626433832795029;  // TF2SIMD_PI
+    if (std::fabs(el[2].x()) >= 1.0)
+    {
+      yaw = 0.0;
+      const double delta = std::atan2(el[2].y(), el[2].z());
+      pitch = el[2].x() < 0.0 ? pi / 2.0 : -pi / 2.0;
+      roll = delta;
+    }
+    else
+    {
+      double a = el[2].x();  // tf2Asin clamps to [-1, 1]
+      if (a < -1.0) a = -1.0;
+      if (a > 1.0) a = 1.0;
+      pitch = -std::asin(a);
+      roll = std::atan2(el[2].y() / std::cos(pitch), el[2].z() / std::cos(pitch));
+      yaw = std::atan2(el[1].x() / std::cos(pitch), el[0].x() / std::cos(pitch));
+    }
+  }
+  void getRPY(double& roll, double& pitch, double& yaw) const { getEulerYPR(yaw, pitch, roll); }
+  Matrix3x3 transpose() const
+  {
+    return Matrix3x3(el[0].x(), el[1].x(), el[2].x(), el[0].y(), el[1].y(), el[2].y(), el[0].z(), el[1].z(), el[2].z());
+  }
+  Vector3 operator*(const Vector3& v) const { return Vector3(el[0].dot(v), el[1].dot(v), el[2].dot(v)); }
   double tdotx(const Vector3& v) const { return el[0].x() * v.x() + el[1].x() * v.y() + el[2].x() * v.z(); }
   double tdoty(const Vector3& v) const { return el[0].y() * v.x() + el[1].y() * v.y() + el[2].y() * v.z(); }
   double tdotz(const Vector3& v) const { return el[0].z() * v.x() + el[1].z() * v.y() + el[2].z() * v.z(); }
@@ -119,6 +155,18 @@ public:
   Transform operator*(const Transform& t) const { return Transform(basis * t.basis, (*this)(t.origin)); }
   const Matrix3x3& getBasis() const { return basis; }
   const Vector3& getOrigin() const { return origin; }
+  void setOrigin(const Vector3& o) { origin = o; }
+  void setRotation(const Quaternion& q) { basis.setRotation(q); }
+  void setIdentity()
+  {
+    basis = Matrix3x3();
+    origin = Vector3(0.0, 0.0, 0.0);
+  }
+  Transform inverse() const
+  {
+    const Matrix3x3 inv = basis.transpose();
+    return Transform(inv, inv * -origin);
+  }
   Quaternion getRotation() const
   {
     Quaternion q;

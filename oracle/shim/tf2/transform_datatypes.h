@@ -1,45 +1,10 @@
-// oracle/shim: TEST INFRASTRUCTURE ONLY. tf2::Stamped<T>, ros::Time, the geometry_msgs / sensor_msgs structs the 3-D scanner
-// touches (plain data, no arithmetic).
+// oracle/shim: TEST INFRASTRUCTURE ONLY. tf2::Stamped<T> (plain data, no arithmetic) + the message structs the callers
+// of this header expect to see with it.
 #pragma once
 #include <string>
 #include <vector>
 
-#include <pcl/point_types.h>
-namespace ros
-{
-struct Time
-{
-  static Time now() { return Time(); }
-};
-}  // namespace ros
-namespace geometry_msgs
-{
-struct Vector3
-{
-  double x = 0.0, y = 0.0, z = 0.0;
-};
-struct Quaternion
-{
-  double x = 0.0, y = 0.0, z = 0.0, w = 1.0;
-};
-struct Transform
-{
-  Vector3 translation;
-  Quaternion rotation;
-};
-struct TransformStamped
-{
-  std::string frame_id, child_frame_id;
-  Transform transform;
-};
-}  // namespace geometry_msgs
-namespace sensor_msgs
-{
-struct PointCloud2  // only the xyz payload the scanner moves around
-{
-  std::vector<pcl::PointXYZ> xyz;
-};
-}  // namespace sensor_msgs
+#include <ros/shim_msgs.h>
 namespace tf2
 {
 template <typename T>
@@ -50,5 +15,6 @@ public:
   std::string frame_id_;
   Stamped() {}
   Stamped(const T& input, const ros::Time& timestamp, const std::string& frame_id) : T(input), stamp_(timestamp), frame_id_(frame_id) {}
+  void setData(const T& input) { *static_cast<T*>(this) = input; }
 };
 }  // namespace tf2

@@ -1,6 +1,7 @@
 """Generate tests/golden/*.npz from the UNMODIFIED reference compiled into oracle/_ref (run in the container that has
 /root/reference; the GPU box does not). Each file holds seeded inputs and the reference's outputs for one slice of
-the hot path, small enough to commit. Usage: python tests/golden/make_golden.py"""
+the hot path, small enough to commit. Usage: python tests/golden/make_golden.py [node]  ("node": only the two runs
+through the reference's ROS node, node_2d.npz / node_3d.npz)"""
 import os
 import sys
 
@@ -35,9 +36,21 @@ def world():
     return cells, truth
 
 
+def node_runs():
+    """one localisation run through the reference's own node (node/node.cpp + node_2d.cpp / node_3d.cpp compiled against
+    oracle/shim), recorded step by step: tests/node_chain.py"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import node_chain
+    np.savez_compressed(os.path.join(HERE, "node_2d.npz"), **node_chain.record_2d(O))
+    np.savez_compressed(os.path.join(HERE, "node_3d.npz"), **node_chain.record_3d(O))
+
+
 def main():
     O.build(ref=True)
     assert O.have_ref(), "the compiled reference (oracle/_ref) is required"
+    node_runs()
+    if sys.argv[1:] == ["node"]:
+        return
     cells, truth = world()
     rm = O.RefMap2D(cells, RES)
     brushfire = rm.update_distances(2.0)  # occupancy_map.cpp:138-242, the reference's own cache

@@ -274,4 +274,182 @@ def replay_2d(backend, g, check, p=PARAMS_2D):
         leaf, clusters, labels = backend.labels()
         check("s%d_leaf" % k, leaf, g["s%d_leaf" % k])
         check("s%d_clusters" % k, clusters, g["s%d_clusters" % k])
-        check("s%d_labels" % k, labels, g["s%d_labels" % k])
+        if resampled:  # between resamplings the particles move but the tree is not rebuilt: a per-particle label is only
+            check("s%d_labels" % k, labels, g["s%d_labels" % k])  # defined right after computeClusterStats ran
+
+
+class PortBackend3D:
+    """the restated 3-D chain: OctoMap cache, getMapCloud + calcPointCloudModel(Gompertz), updateSensor, resample"""
+
+    def __init__(self, O, g, p=PARAMS_3D):
+        self.O = O
+        self.map = O.PortMap3D(0.1, g["keys"], p["laser_likelihood_max_dist"])
+        self.map.update_distances()
+        self.pf = O.PortPF(p["min_particles"], p["max_particles"], p["recovery_alpha_slow"], p["recovery_alpha_fast"], 95.0,
+                           systematic=True, pop_err=p["kld_err"], pop_z=p["kld_z"])
+        self.model = O.cloud_model(model_type=1, max_beams=p["laser_max_beams"], z_hit=p["laser_z_hit"],
+                                   z_rand=p["laser_z_rand"], sigma_hit=p["laser_sigma_hit"],
+                                   gompertz=(p["laser_gompertz_a"], p["laser_gompertz_b"], p["laser_gompertz_c"],
+                                             p["laser_gompertz_input_shift"], p["laser_gompertz_input_scale"],
+                                             p["laser_gompertz_output_shift"]),
+                                   mount_translation=CLOUD_MOUNT[:3], mount_rotation=O.yaw_quat(CLOUD_MOUNT[3]))
+
+    def field(self):
+        return self.map.dense()
+
+    def bounds(self):
+        return self.map.bounds()
+
+    def init(self, poses, state):
+        self.pf.init_with_poses(poses)
+        self.pf.rng.x = int(state)
+
+    def subsample(self, xyz, p):
+        return self.O.cloud_subsample(xyz, p["laser_max_beams"])
+
+    def action(self, alpha, pose, delta):
+        self.pf.update_action(0, alpha, pose, delta, delta)
+
+    def sensor(self, points):
+        s = self.pf.samples()
+        total, w = self.map.cloud_apply(self.model, points, s)
+        s[:, 3] = w
+        self.pf.set_samples(s)
+        self.O.port_lib().orc_pf_normalise(self.pf.h, total)  # ParticleFilter::updateSensor, particle_filter.cpp:223-266
+
+    def resample(self):
+        self.pf.update_resample()
+
+    def samples(self):
+        return self.pf.samples()
+
+    def state(self):
+        return self.pf.rng.x
+
+    def readout(self):
+        w, pose, idx = self.pf.max_weight_pose()
+        return w, pose, self.pf.pose_covariance()
+
+    def labels(self):
+        return self.pf.leaf_count(), self.pf.cluster_count(), self.pf.sample_clusters()
+
+
+def replay_3d(backend, g, check, p=PARAMS_3D):
+    """Node3D's sequence (node_3d.cpp:320-366): as replay_2d with the cloud sub-sampled instead of the scan converted"""
+    alpha = [p["odom_alpha%d" % i] for i in range(1, 6)]
+    backend.init(g["init_samples"][:, :3], g["init_state"])
+    check("init_samples", backend.samples(), g["init_samples"])
+    odom_init, update, resample_count, last = False, False, 0, None
+    for k in range(N_STEPS):
+        pose = g["s%d_odom" % k]
+        force_publication = resampled = False
+        if odom_init:
+            delta = odom_delta(pose, last)
+            update = update or should_update(delta, p)
+            if update:
+                backend.action(alpha, pose, delta)
+                last = pose
+        else:
+            last, odom_init, update, force_publication, resample_count = pose, True, True, True, 0
+        if update:
+            points = backend.subsample(g["s%d_cloud" % k], p)
+            check("s%d_points" % k, points, g["s%d_points" % k])
+            backend.sensor(points)
+            update = False
+            resample_count += 1
+            if resample_count % p["resample_interval"] == 0:
+                backend.resample()
+                resampled = True
+        check("s%d_resample_count" % k, resample_count, g["s%d_resample_count" % k])
+        check("s%d_samples" % k, backend.samples(), g["s%d_samples" % k])
+        check("s%d_state" % k, backend.state(), int(g["s%d_state" % k]))
+        if force_publication or resampled:
+            w, mean, cov = backend.readout()
+            check("s%d_max_weight" % k, np.concatenate([[w], mean]), g["s%d_max_weight" % k])
+            check("s%d_pose_xy" % k, mean[:2], g["s%d_pose" % k][:2])
+            check("s%d_cov" % k, cov, g["s%d_cov" % k])
+        leaf, clusters, labels = backend.labels()
+        check("s%d_leaf" % k, leaf, g["s%d_leaf" % k])
+        check("s%d_clusters" % k, clusters, g["s%d_clusters" % k])
+        if resampled:  # between resamplings the particles move but the tree is not rebuilt: a per-particle label is only
+            check("s%d_labels" % k, labels, g["s%d_labels" % k])  # defined right after computeClusterStats ran
+
+
+class CudaBackend2D:
+    """the CUDA library through the C ABI (badger_amcl_b200.cabi), driven in the node's order"""
+
+    def __init__(self, cabi, ctx, g, p=PARAMS_2D, reference_cache=True, exact_terms=True):
+        self.cabi = cabi
+        self.map = cabi.Map2D.from_occupancy_grid(ctx, g["data"], RES_MSG, ORIGIN, 1)
+        if reference_cache:   # the reference's brushfire, so that weights compare at scorer precision (DESIGN 4)
+            self.map.upload_distances(g["brushfire"], p["laser_likelihood_max_dist"])
+        else:
+            self.map.build_distances(p["laser_likelihood_max_dist"])
+        self.map.update_free_space(0.0)
+        self.pf = cabi.ParticleFilter(ctx, p["min_particles"], p["max_particles"], p["recovery_alpha_slow"],
+                                      p["recovery_alpha_fast"], 95.0, systematic=True, pop_err=p["kld_err"], pop_z=p["kld_z"])
+        self.pf.set_random_pose_source(self.map)
+        self.pf.set_exact_terms(exact_terms)
+        self.model = cabi.planar_model(model_type=1, max_beams=p["laser_max_beams"], z_hit=p["laser_z_hit"],
+                                       z_rand=p["laser_z_rand"], sigma_hit=p["laser_sigma_hit"],
+                                       scanner_pose=(MOUNT[0], MOUNT[1], 0.0))
+
+    def close(self):
+        self.pf.close()
+        self.map.close()
+
+    def init(self, poses, state):
+        self.pf.init_with_poses(poses)
+        self.pf.drand48_state = int(state)
+
+    def convert_scan(self, r, stats, p):
+        return self.cabi.scan_from_laserscan(r, SCAN["range_min"], SCAN["range_max"], stats[0], stats[1],
+                                             p["laser_min_range"], p["laser_max_range"])
+
+    def action(self, alpha, pose, delta):
+        self.pf.update_action(0, alpha, pose, delta, delta)
+
+    def sensor(self, ranges, angles, range_max):
+        self.pf.update_sensor(self.map, self.model, ranges, angles, range_max)
+
+    def resample(self):
+        self.pf.update_resample()
+
+    def samples(self):
+        return self.pf.samples()
+
+    def state(self):
+        return self.pf.drand48_state
+
+    def readout(self):
+        w, pose, idx = self.pf.max_weight_pose()
+        return w, pose, self.pf.pose_covariance()
+
+    def labels(self):
+        return self.pf.last.leaf_count, self.pf.last.cluster_count, self.pf.sample_clusters()
+
+
+class CudaBackend3D(CudaBackend2D):
+    def __init__(self, cabi, ctx, g, p=PARAMS_3D, reference_cache=True):
+        self.cabi = cabi
+        self.map = cabi.Map3D(ctx, 0.1, g["keys"], p["laser_likelihood_max_dist"])
+        if reference_cache:
+            self.map.upload_distances(g["field"])
+        else:
+            self.map.build_distances()
+        self.pf = cabi.ParticleFilter(ctx, p["min_particles"], p["max_particles"], p["recovery_alpha_slow"],
+                                      p["recovery_alpha_fast"], 95.0, systematic=True, pop_err=p["kld_err"], pop_z=p["kld_z"])
+        self.pf.set_random_pose_source(self.map)
+        q = (0.0, 0.0, float(np.sin(0.5 * CLOUD_MOUNT[3])), float(np.cos(0.5 * CLOUD_MOUNT[3])))
+        self.model = cabi.cloud_model(model_type=1, max_beams=p["laser_max_beams"], z_hit=p["laser_z_hit"],
+                                      z_rand=p["laser_z_rand"], sigma_hit=p["laser_sigma_hit"],
+                                      gompertz=(p["laser_gompertz_a"], p["laser_gompertz_b"], p["laser_gompertz_c"],
+                                                p["laser_gompertz_input_shift"], p["laser_gompertz_input_scale"],
+                                                p["laser_gompertz_output_shift"]),
+                                      mount_translation=CLOUD_MOUNT[:3], mount_rotation=q)
+
+    def subsample(self, xyz, p):
+        return self.cabi.cloud_subsample(xyz, p["laser_max_beams"])
+
+    def sensor(self, points):
+        self.pf.update_sensor_cloud(self.map, self.model, points)

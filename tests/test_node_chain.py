@@ -1,0 +1,169 @@
+"""A whole localisation run as the reference's ROS node sequences it (tests/node_chain.py), recorded from the compiled node
+into tests/golden/node_2d.npz / node_3d.npz and replayed here: through the restated chain on the CPU (bit-exact) and through
+the CUDA library on the GPU (bit-exact where the arithmetic is integer / copy / identical, 1e-9 where device libm differs
+from glibc in the last ulp)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+import node_chain as nc  # noqa: E402
+
+
+def golden(name):
+    return dict(np.load(os.path.join(HERE, "golden", name)))
+
+
+def exact(bad):
+    def check(name, got, want):
+        if not np.array_equal(np.asarray(got), np.asarray(want)):
+            bad.append(name)
+    return check
+
+
+def test_restated_chain_2d_is_the_node_bit_for_bit(oracle_built):
+    O, g = oracle_built, golden("node_2d.npz")
+    b = nc.PortBackend2D(O, g)
+    assert np.array_equal(b.distances(), g["brushfire"])
+    assert b.geometry == (float(g["resolution"]), (float(g["origin"][0]), float(g["origin"][1])))
+    assert np.array_equal(b.free, g["free"])
+    bad = []
+    nc.replay_2d(b, g, exact(bad))
+    assert bad == []
+
+
+def test_restated_chain_3d_is_the_node_bit_for_bit(oracle_built):
+    O, g = oracle_built, golden("node_3d.npz")
+    b = nc.PortBackend3D(O, g)
+    assert np.array_equal(b.field(), g["field"])
+    mn, mx = b.bounds()
+    assert np.array_equal(mn, g["mn"]) and np.array_equal(mx, g["mx"])
+    bad = []
+    nc.replay_3d(b, g, exact(bad))
+    assert bad == []
+
+
+@pytest.mark.parametrize("which", ["2d", "3d"])
+def test_committed_golden_is_what_the_compiled_node_produces(oracle_built, which):
+    O = oracle_built
+    if not O.have_ref():
+        pytest.skip("oracle/_ref not built (needs the reference checkout)")
+    g = golden("node_%s.npz" % which)
+    fresh = nc.record_2d(O) if which == "2d" else nc.record_3d(O)
+    assert sorted(fresh) == sorted(g)
+    for k in g:
+        assert np.array_equal(np.asarray(fresh[k]), g[k], equal_nan=np.asarray(g[k]).dtype.kind == "f"), k
+
+
+def test_the_run_exercises_motion_resampling_and_readout():
+    """the fixture is only worth something if the node actually moved, resampled and published"""
+    g = golden("node_2d.npz")
+    assert int(g["s5_resample_count"]) == 6 and int(g["s5_pose_count"]) == 4
+    assert not np.array_equal(g["s1_samples"][:, :3], g["s0_samples"][:, :3])            # updateAction moved the set
+    assert abs(g["s5_pose"][0] - nc.truth_pose(5)[0]) < 0.15 and abs(g["s5_pose"][1] - nc.truth_pose(5)[1]) < 0.15
+    assert np.unique(g["s5_samples"][:, :3], axis=0).shape[0] < len(g["s5_samples"])  # resampling duplicated particles
+
+
+# ---------------------------------------------------------------------------------------------- GPU
+@pytest.fixture(scope="module")
+def dev():
+    import torch
+    assert torch.cuda.is_available()
+    from badger_amcl_b200 import build, cabi
+    build.build()
+    return dict(cabi=cabi, ctx=cabi.Context(0))
+
+
+def tolerant(bad, weight_rtol, same_rows=1.0):
+    """same_rows: share of particles that must be the reference's particle (1.0 = every resampling index identical)"""
+    def check(name, got, want):
+        got, want = np.asarray(got), np.asarray(want)
+        if name.endswith("_samples") and name != "init_samples":
+            # poses: Odom::updateAction through device log / sincos (last ulp vs glibc); weights: scorer precision
+            ok = got.shape == want.shape
+            if ok:
+                row = (np.abs(got[:, :3] - want[:, :3]).max(axis=1) <= 1e-9) & np.isclose(got[:, 3], want[:, 3],
+                                                                                        rtol=weight_rtol, atol=1e-300)
+                ok = row.mean() >= same_rows
+        elif name.endswith("_max_weight") or name.endswith("_pose_xy") or name.endswith("_cov"):
+            ok = got.shape == want.shape and np.allclose(got, want, rtol=1e-6, atol=1e-9)
+        else:   # scan conversion, counts, labels, the generator state: exact
+            ok = np.array_equal(got, want)
+        if not ok:
+            bad.append(name)
+    return check
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("exact_terms,rtol,same_rows", [(True, 1e-9, 1.0), (False, 2e-5, 0.999)])
+def test_gpu_chain_2d_vs_the_node(dev, exact_terms, rtol, same_rows):
+    """exact_terms: f64 terms and sums, every resampling index must be the reference's; the default fixed-point table
+    (2e-5 on the weights) may move a CDF boundary past a target: at most 1 particle in 1000 may differ"""
+    g = golden("node_2d.npz")
+    b = nc.CudaBackend2D(dev["cabi"], dev["ctx"], g, exact_terms=exact_terms)
+    assert b.map.resolution == float(g["resolution"]) and tuple(np.float64(b.map.origin)) == tuple(g["origin"])
+    assert np.array_equal(b.map.free_space(), g["free"])
+    bad = []
+    nc.replay_2d(b, g, tolerant(bad, rtol, same_rows))
+    b.close()
+    assert bad == []
+
+
+@pytest.mark.gpu
+def test_gpu_chain_2d_with_the_device_built_cache(dev):
+    """the drop-in path: cache from the device's exact EDT instead of the reference's brushfire: same sequence,
+    same counts and generator state, the published pose within a few centimetres"""
+    g = golden("node_2d.npz")
+    b = nc.CudaBackend2D(dev["cabi"], dev["ctx"], g, reference_cache=False)
+    seen = {}
+
+    def check(name, got, want):
+        seen[name] = (np.asarray(got), np.asarray(want))
+    nc.replay_2d(b, g, check)
+    b.close()
+    for k in range(nc.N_STEPS):
+        assert seen["s%d_resample_count" % k][0] == seen["s%d_resample_count" % k][1]
+        assert seen["s%d_samples" % k][0].shape == seen["s%d_samples" % k][1].shape
+    got, want = seen["s5_pose_xy"]
+    assert np.abs(got - want).max() < 0.05
+
+
+@pytest.mark.gpu
+def test_gpu_chain_3d_vs_the_node(dev):
+    g = golden("node_3d.npz")
+    b = nc.CudaBackend3D(dev["cabi"], dev["ctx"], g)
+    mn, mx = b.map.bounds()
+    assert np.array_equal(mn, g["mn"]) and np.array_equal(mx, g["mx"])
+    bad = []
+    nc.replay_3d(b, g, tolerant(bad, 1e-6))
+    b.close()
+    assert bad == []
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("thr,mult", [(0.0, 0.0), (5.0, 0.4)])
+def test_gpu_init_uniform_3d_vs_oracle(oracle_built, dev, thr, mult):
+    """global localisation with map_type 3 (node_3d.cpp:306-318 + node.cpp:823-883): poses from the OctoMap's cell rectangle"""
+    import ctypes as C
+    O, cabi = oracle_built, dev["cabi"]
+    g = golden("node_3d.npz")
+    m = cabi.Map3D(dev["ctx"], 0.1, g["keys"], 0.5)
+    m.upload_distances(g["field"])
+    n = 5000
+    rng = O.Rng(0)
+    O.port_lib().orc_srand48(C.byref(rng), 123)
+    poses = O.uniform_poses_rect(g["mn"], g["mx"], 0.1, rng, n, thr, mult)
+    ref = O.PortPF(100, n)
+    ref.init_with_poses(poses)
+    pf = cabi.ParticleFilter(dev["ctx"], 100, n)
+    pf.srand48(123)
+    res = pf.init_uniform(m, thr, mult)
+    assert pf.drand48_state == rng.x
+    assert np.array_equal(pf.samples(), ref.samples())
+    assert (res.leaf_count, res.cluster_count) == (ref.leaf_count(), ref.cluster_count())
+    assert np.array_equal(pf.sample_clusters(), ref.sample_clusters())
+    pf.close()
+    m.close()

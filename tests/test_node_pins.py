@@ -238,3 +238,17 @@ def test_gaussian_pdf_shim_decomposition_is_a_decomposition(O):
     L.ref_srand48(2)
     L.ref_gaussian_sample(O._ptr(mean), O._ptr(np.ascontiguousarray(a)), len(out), O._ptr(out))
     assert np.allclose(np.cov(out.T), a, atol=6e-3)
+
+
+def test_reference_gaussian_kat_on_the_compiled_translation_unit(O):
+    """the reference's own known answers (test/test_badger_amcl.cpp:29-51: identity covariance, the process's unseeded
+    drand48 stream = glibc's all-zero initial state) reproduced by ITS pdf_gaussian.cpp compiled against the EigenSolver
+    look-alike"""
+    L = O.ref_lib()
+    L.ref_seed48((C.c_ushort * 3)(0, 0, 0))
+    out = np.empty((2, 3))
+    mean, cov = np.ones(3), np.eye(3)
+    L.ref_gaussian_sample(O._ptr(mean), O._ptr(cov), 2, O._ptr(out))
+    want = [[0.26562654174915334, 0.97172090090793528, -1.5856194295513539],
+            [1.6262083813236745, 1.1142314205031041, 0.37407538872488655]]
+    assert np.allclose(out, want, rtol=4e-16, atol=0.0)   # EXPECT_DOUBLE_EQ = 4 ulps

@@ -84,6 +84,16 @@ def scan_from_laserscan(msg_ranges, msg_range_min, msg_range_max, angle_min, ang
     return ranges, angles, rmax.value
 
 
+NOALLOC_MAX_SAMPLES = 1 << 24
+
+
+def weights_normalise_noalloc(ctx, weights_dev_ptr, n, weights_out_dev_ptr, total_out_dev_ptr):
+    """bamcl_weights_normalise_noalloc: DEVICE pointers as integers (e.g. tensor.data_ptr()); queued on the context's
+    stream, not synchronised"""
+    _check(lib().bamcl_weights_normalise_noalloc(ctx.h, C.c_void_p(weights_dev_ptr), n, C.c_void_p(weights_out_dev_ptr),
+                                                 C.c_void_p(total_out_dev_ptr)))
+
+
 def cloud_subsample(xyz, max_beams):
     """Node3D::updateLatestScanData (node_3d.cpp:467-480): stride sub-sampling of an (n, 3) float32 cloud"""
     xyz = np.ascontiguousarray(xyz, np.float32)
@@ -209,6 +219,7 @@ SIGNATURES = {
     "bamcl_map2d_download_free_space": (_I, [_P, _P, _L]),
     "bamcl_pf_init_uniform": (_I, [_P, _P, _D, _D, C.c_uint64, _P, _P]),
     "bamcl_pf_init_uniform_3d": (_I, [_P, _P, _D, _D, C.c_uint64, _P, _P]),
+    "bamcl_weights_normalise_noalloc": (_I, [_P, _P, _L, _P, _P]),
     "bamcl_pf_set_random_pose_source_3d": (_I, [_P, _P, _D, _D]),
     "bamcl_pose_covariance": (_I, [_P, _P]),
     "bamcl_pf_upload_window_samples": (_I, [_P, _P, _L, _L]),

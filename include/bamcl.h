@@ -432,6 +432,25 @@ int bamcl_pf_max_weight_pose(bamcl_pf* pf, double* max_weight, double* pose3, in
  * 6x6 of geometry_msgs/PoseWithCovariance: [0],[1],[6],[7] and [35] (COVARIANCE_AA, node.h:67); host arithmetic */
 int bamcl_pose_covariance(const bamcl_resample_result* result, double* cov36);
 
+/* ---- allocation-free variant (no counterpart in the reference)
+ * For callers that cannot call cudaMalloc - code under CUDA graph capture, tight serving loops, harnesses that forbid it:
+ * the weight total and normalisation of ParticleFilter::updateSensor (w /= total, or 1/n each where the total is not
+ * positive) over caller-owned DEVICE buffers, with the block partials of the deterministic two-level sum kept in a
+ * file-scope `static __device__` array instead of a cudaMalloc'ed buffer. Same tree shape as the filter's own total, so
+ * total and weights are bit-identical to bamcl_pf_score_planar's total followed by bamcl_pf_normalise.
+ *  - weights_dev: n doubles (device); weights_out_dev: n doubles (device, may be weights_dev itself); total_out_dev: one
+ *    double (device). Work is queued on the context's stream and NOT synchronised (bamcl_ctx_sync to wait).
+ *  - n > BAMCL_NOALLOC_MAX_SAMPLES is refused with BAMCL_E_ARG. The scratch is 64 KB per GPU, held from library load to
+ *    process exit on every GPU that loads the library.
+ *  - calls no cudaMalloc / cudaFree / allocating routine. The first call on a device looks the scratch address up
+ *    (cudaGetSymbolAddress); make that call outside stream capture.
+ *  - every call on a device shares the one scratch array, which keeps the last call's contents (nothing in it needs to
+ *    start at zero: each call writes what it reads). Two calls that overlap on the GPU - different contexts / streams on
+ *    the same device - RACE on it: serialise them. */
+#define BAMCL_NOALLOC_MAX_SAMPLES (1L << 24)
+int bamcl_weights_normalise_noalloc(bamcl_ctx* ctx, const double* weights_dev, long n, double* weights_out_dev,
+                                    double* total_out_dev);
+
 #ifdef __cplusplus
 }
 #endif

@@ -428,7 +428,7 @@ class _PFBase:
     def max_weight_pose(self):
         """Node2D::getMaxWeightPose (node_2d.cpp:588-617) restated over getClusterStats: the first cluster whose weight
         is strictly greater than every earlier one -> (weight, mean pose, index); index -1 where the reference would
-        read hyps[-1]. (node_2d.cpp is a ROS node and cannot be compiled here: parity unpinned for this helper.)"""
+        read hyps[-1]. Pinned against Node2D::getMaxWeightPose of the compiled node (tests/test_node_pins.py)."""
         st = self.cluster_stats()
         best, idx = 0.0, -1
         for c in range(len(st)):
@@ -845,8 +845,8 @@ def cloud_model(model_type=0, max_beams=4096, z_hit=0.95, z_rand=0.05, sigma_hit
 
 
 # ---------------------------------------------------------------- ingestion (node_2d.cpp / node_3d.cpp)
-# The node translation units are ROS nodes and cannot be compiled here: these numpy restatements are PARITY UNPINNED
-# (no reference test or golden vector covers them); they follow the cited lines statement by statement.
+# numpy restatements following the cited lines statement by statement; pinned bit for bit against the node translation
+# units compiled into oracle/_ref and driven in process (RefNode below, tests/test_node_pins.py).
 def convert_map(data, resolution, origin_xy, scale_up=1):
     """Node2D::convertMap (node_2d.cpp:265-295) -> (cells (size_y, size_x) int8, resolution, (origin_x, origin_y) f32).
     info.resolution is a float32 message field and `resolution / map_scale_up_factor_` (:267) is float / int = a float

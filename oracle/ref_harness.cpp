@@ -95,7 +95,7 @@ struct PF
   // queue of poses handed out by random_pose_fn_ (x, y, theta triples), consumed in order
   std::vector<double> random_poses;
   size_t random_next = 0;
-  // alternative source: Node::uniformPoseGenerator restated (node.cpp:823-868; the node sources cannot be compiled
+  // alternative source: Node::uniformPoseGenerator restated (node.cpp:823-868; kept beside the compiled node sources
   // here) over a free-space list, drawing from the process-global drand48 stream like the node's pose function does
   std::shared_ptr<OccupancyMap> uniform_map;
   std::vector<int> free_ij;

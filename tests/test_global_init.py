@@ -1,8 +1,8 @@
 """Global localisation on the device: Node2D::updateFreeSpaceIndices (node_2d.cpp:320-338) and
 initWithPoseFn(uniformPoseGenerator) (particle_filter.cpp:136-162, node.cpp:823-868).
 
-The node sources are ROS nodes and cannot be compiled here, so the oracle restates the free-space list and the pose
-generator (parity unpinned for those helpers, see oracle/amcl_oracle.h); initWithPoseFn itself runs in the compiled
+The oracle restates the free-space list and the pose generator; both are pinned against the node sources compiled into
+oracle/_ref (tests/test_node_pins.py); initWithPoseFn itself runs in the compiled
 reference (oracle/_ref) fed with the oracle's poses. GPU: free list, poses, weights, drand48 state, pose-bin tree and
 cluster labels bit-exact (integer arithmetic + one exact multiply-add per coordinate); statistics to 1e-6."""
 import os

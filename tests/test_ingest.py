@@ -1,6 +1,6 @@
 """Scan / map ingestion: Node2D::convertMap (node_2d.cpp:265-295), Node2D::updateLatestScanData
 (node_2d.cpp:534-560), Node3D::updateLatestScanData (node_3d.cpp:467-480) against the oracle's numpy restatements
-(parity unpinned: the node sources cannot be compiled here). Everything is integer / copy work or one exact expression
+(pinned against the compiled node: tests/test_node_pins.py). Everything is integer / copy work or one exact expression
 per element: bit-exact. The two scan functions are host arithmetic of the C ABI library and run without a GPU."""
 import os
 import sys

@@ -219,6 +219,7 @@ SIGNATURES = {
     "bamcl_map2d_download_free_space": (_I, [_P, _P, _L]),
     "bamcl_pf_init_uniform": (_I, [_P, _P, _D, _D, C.c_uint64, _P, _P]),
     "bamcl_pf_init_uniform_3d": (_I, [_P, _P, _D, _D, C.c_uint64, _P, _P]),
+    "bamcl_pf_init_gaussian": (_I, [_P, _P, _P, _P, C.c_uint64, _P, _P]),
     "bamcl_weights_normalise_noalloc": (_I, [_P, _P, _L, _P, _P]),
     "bamcl_pf_set_random_pose_source_3d": (_I, [_P, _P, _D, _D]),
     "bamcl_pose_covariance": (_I, [_P, _P]),
@@ -497,6 +498,20 @@ class ParticleFilter:
         out = C.c_uint64()
         fn = self.L.bamcl_pf_init_uniform_3d if isinstance(map2d, Map3D) else self.L.bamcl_pf_init_uniform
         _check(fn(self.h, map2d.h, threshold, multiplier, self.drand48_state, C.byref(out), C.byref(res)))
+        self.drand48_state = out.value
+        self.w_slow = self.w_fast = 0.0
+        self.converged = False
+        self.last = res
+        return res
+
+    def init_gaussian(self, mean, cr, cd):
+        """initWithGaussian on the device (particle_filter.cpp:105-133); cr (3, 3) rotation and cd (3,) standard deviations
+        = the decomposition PDFGaussian's constructor computes (identity / sqrt(diagonal) for a diagonal covariance)"""
+        m, r, d = (np.ascontiguousarray(v, np.float64) for v in (mean, cr, cd))
+        assert m.shape == (3,) and r.shape == (3, 3) and d.shape == (3,)
+        res = ResampleResult()
+        out = C.c_uint64()
+        _check(self.L.bamcl_pf_init_gaussian(self.h, _p(m), _p(r), _p(d), self.drand48_state, C.byref(out), C.byref(res)))
         self.drand48_state = out.value
         self.w_slow = self.w_fast = 0.0
         self.converged = False

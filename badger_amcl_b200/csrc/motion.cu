@@ -156,6 +156,60 @@ double h_rot_noise(double rot)  // odom.cpp:145-148
 }
 }  // namespace
 
+namespace
+{
+// `need` PDFGaussian::draw values from generator state `state0`, draw r with sigma[r % 3], left in pf->scratch (device);
+// *state_out = the generator state after the last attempt consumed
+int gaussian_draws(bamcl_pf* pf, uint64_t state0, const double sigma[3], long long need, const char* who, double** draws_out,
+                   uint64_t* state_out)
+{
+  bamcl_ctx* ctx = pf->ctx;
+  const long long first = (long long)std::ceil((double)need * 1.2732395447351628 * 1.01) + 4096;
+  if (first > 0x7fffff00ll)
+    return set_error(BAMCL_E_UNSUPPORTED, "%s: sample set too large for one attempt batch", who);
+  BAMCL_TRY(pf->scratch.reserve(sizeof(double) * (size_t)need));
+  BAMCL_TRY(pf->scratch2.reserve(sizeof(int) * ((size_t)first + 1 + scan_scratch_ints(first + 1) + 16)));
+  AttemptArgs at;
+  at.state0 = state0 & LCG_MASK;
+  at.meta = pf->scratch2.as<int>();
+  at.flag = at.meta + 8;
+  int* scan_scratch = at.flag + first + 1;
+  at.need = need;
+  at.draws = pf->scratch.as<double>();
+  for (int k = 0; k < 3; k++)
+    at.sigma[k] = sigma[k];
+  BAMCL_CUDA_OK(cudaMemsetAsync(at.meta, 0, sizeof(int) * 8, ctx->stream));
+  long long base = 0, j0 = 0, last_attempt = -1;
+  while (base < need)
+  {
+    const long long left = need - base;
+    long long m = (long long)std::ceil((double)left * 1.2732395447351628 * 1.01) + 4096;
+    if (m > first)
+      m = first;
+    at.j0 = j0;
+    at.m = (int)m;
+    at.base = base;
+    const unsigned blocks = (unsigned)((m + 255) / 256);
+    BAMCL_LAUNCH(ctx, k_attempt_flags, blocks, 256, 0, at);
+    BAMCL_TRY(exclusive_scan_i32(ctx, at.flag, at.flag, m, scan_scratch, at.meta));
+    BAMCL_LAUNCH(ctx, k_attempt_draws, blocks, 256, 0, at, at.flag);
+    int h_meta[4];
+    BAMCL_CUDA_OK(cudaMemcpyAsync(h_meta, at.meta, sizeof(h_meta), cudaMemcpyDeviceToHost, ctx->stream));
+    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    if (h_meta[1] & 1)
+      return set_error(BAMCL_E_UNSUPPORTED,
+                       "%s: drand48 produced exactly 0.0 inside the draw range "
+                       "(pdf_gaussian.cpp:83-92 re-draws, which shifts the pairing of the stream)", who);
+    base += h_meta[0] < left ? h_meta[0] : left;
+    j0 += m;
+    memcpy(&last_attempt, &h_meta[2], sizeof(long long));
+  }
+  *draws_out = at.draws;
+  *state_out = lcg_skip(at.state0, 2ull * (unsigned long long)(last_attempt + 1));
+  return BAMCL_OK;
+}
+}  // namespace
+
 extern "C" int bamcl_pf_update_action(bamcl_pf* pf, const bamcl_odom_model* model, const bamcl_odom_data* data,
                                       uint64_t drand48_state, uint64_t* drand48_state_out)
 {
@@ -217,49 +271,10 @@ extern "C" int bamcl_pf_update_action(bamcl_pf* pf, const bamcl_odom_model* mode
     for (int k = 0; k < 3; k++)
       sigma[k] = std::sqrt(sigma[k]);
 
-  // draws
-  const long long need = 3ll * P;
-  const long long first = (long long)std::ceil((double)need * 1.2732395447351628 * 1.01) + 4096;
-  if (first > 0x7fffff00ll)
-    return set_error(BAMCL_E_UNSUPPORTED, "bamcl_pf_update_action: sample set too large for one attempt batch");
-  BAMCL_TRY(pf->scratch.reserve(sizeof(double) * (size_t)need));
-  BAMCL_TRY(pf->scratch2.reserve(sizeof(int) * ((size_t)first + 1 + scan_scratch_ints(first + 1) + 16)));
-  AttemptArgs at;
-  at.state0 = drand48_state & LCG_MASK;
-  at.meta = pf->scratch2.as<int>();
-  at.flag = at.meta + 8;
-  int* scan_scratch = at.flag + first + 1;
-  at.need = need;
-  at.draws = pf->scratch.as<double>();
-  for (int k = 0; k < 3; k++)
-    at.sigma[k] = sigma[k];
-  BAMCL_CUDA_OK(cudaMemsetAsync(at.meta, 0, sizeof(int) * 8, ctx->stream));
-  long long base = 0, j0 = 0, last_attempt = -1;
-  while (base < need)
-  {
-    const long long left = need - base;
-    long long m = (long long)std::ceil((double)left * 1.2732395447351628 * 1.01) + 4096;
-    if (m > first)
-      m = first;
-    at.j0 = j0;
-    at.m = (int)m;
-    at.base = base;
-    const unsigned blocks = (unsigned)((m + 255) / 256);
-    BAMCL_LAUNCH(ctx, k_attempt_flags, blocks, 256, 0, at);
-    BAMCL_TRY(exclusive_scan_i32(ctx, at.flag, at.flag, m, scan_scratch, at.meta));
-    BAMCL_LAUNCH(ctx, k_attempt_draws, blocks, 256, 0, at, at.flag);
-    int h_meta[4];
-    BAMCL_CUDA_OK(cudaMemcpyAsync(h_meta, at.meta, sizeof(h_meta), cudaMemcpyDeviceToHost, ctx->stream));
-    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
-    if (h_meta[1] & 1)
-      return set_error(BAMCL_E_UNSUPPORTED,
-                       "bamcl_pf_update_action: drand48 produced exactly 0.0 inside the draw range "
-                       "(pdf_gaussian.cpp:83-92 re-draws, which shifts the pairing of the stream)");
-    base += h_meta[0] < left ? h_meta[0] : left;
-    j0 += m;
-    memcpy(&last_attempt, &h_meta[2], sizeof(long long));
-  }
-  ap.g = at.draws;
+  double* draws = nullptr;
+  uint64_t state_after = 0;
+  BAMCL_TRY(gaussian_draws(pf, drand48_state, sigma, 3ll * P, "bamcl_pf_update_action", &draws, &state_after));
+  ap.g = draws;
   if (pf_ranks(pf) > 1)
   {
     // a distributed filter: every rank replays the draw stream of the WHOLE set (the attempt flags above: the number of
@@ -275,6 +290,85 @@ extern "C" int bamcl_pf_update_action(bamcl_pf* pf, const bamcl_odom_model* mode
   if (ap.n > 0)
     BAMCL_LAUNCH(ctx, k_apply_motion, (unsigned)((ap.n + 255) / 256), 256, 0, ap);
   BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
-  *drand48_state_out = lcg_skip(at.state0, 2ull * (unsigned long long)(last_attempt + 1));
+  *drand48_state_out = state_after;
+  return BAMCL_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// ParticleFilter::initWithGaussian (particle_filter.cpp:105-133) on the device: max_samples poses, pose s =
+// PDFGaussian::sample() (pdf_gaussian.cpp:52-71): r[j] = draw(cd[j]) for j = 0, 1, 2 in this order - accepted attempts
+// 3s, 3s+1, 3s+2 of the stream, exactly the motion update's pairing - then v(i) = x[i]; v(i) += cr(i, j) * r[j] for j = 0..2.
+namespace bamcl
+{
+int build_tree_and_stats(bamcl_pf* pf, int set_index, double dist_threshold, double convergence_threshold,
+                         bamcl_resample_result* result);  // kdtree.cu
+}
+namespace
+{
+struct GaussInitArgs
+{
+  int n;
+  double *x, *y, *th, *w;
+  const double* g;
+  double mean[3], cr[9];
+  double weight;
+};
+__global__ void __launch_bounds__(256) k_gaussian_init(const GaussInitArgs a)
+{
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= a.n)
+    return;
+  const double r0 = a.g[3 * s], r1 = a.g[3 * s + 1], r2 = a.g[3 * s + 2];
+  double v[3];
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+  {
+    double t = a.mean[i];  // pdf_gaussian.cpp:65-69 (no contraction: the library is built with -fmad=false)
+    t += a.cr[3 * i] * r0;
+    t += a.cr[3 * i + 1] * r1;
+    t += a.cr[3 * i + 2] * r2;
+    v[i] = t;
+  }
+  a.x[s] = v[0];
+  a.y[s] = v[1];
+  a.th[s] = v[2];
+  a.w[s] = a.weight;
+}
+}  // namespace
+
+extern "C" int bamcl_pf_init_gaussian(bamcl_pf* pf, const double* mean3, const double* cr9, const double* cd3,
+                                      uint64_t drand48_state, uint64_t* drand48_state_out, bamcl_resample_result* res)
+{
+  if (!pf || !mean3 || !cr9 || !cd3 || !drand48_state_out || !res)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_init_gaussian: null argument");
+  bamcl_ctx* ctx = pf->ctx;
+  pf->win_cnt = -1;
+  SampleSet& set = pf->sets[pf->current];
+  const int n = pf->max_samples;  // :113
+  double* draws = nullptr;
+  uint64_t state_after = 0;
+  BAMCL_TRY(gaussian_draws(pf, drand48_state, cd3, 3ll * n, "bamcl_pf_init_gaussian", &draws, &state_after));
+  GaussInitArgs a;
+  a.n = n;
+  a.x = set.x.as<double>();
+  a.y = set.y.as<double>();
+  a.th = set.th.as<double>();
+  a.w = set.w.as<double>();
+  a.g = draws;
+  for (int k = 0; k < 3; k++)
+    a.mean[k] = mean3[k];
+  for (int k = 0; k < 9; k++)
+    a.cr[k] = cr9[k];
+  a.weight = 1.0 / (double)pf->max_samples;  // :119
+  BAMCL_LAUNCH(ctx, k_gaussian_init, (unsigned)((n + 255) / 256), 256, 0, a);
+  set.sample_count = n;
+  pf_apply_shard_window(pf);  // a distributed filter: every rank generated the whole set and owns its window from here on
+  memset(res, 0, sizeof(*res));
+  BAMCL_TRY(build_tree_and_stats(pf, pf->current, 0.5, 1e300, res));
+  BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+  res->sample_count = n;
+  res->converged = 0;  // initConverged, :132
+  *drand48_state_out = state_after;
+  res->drand48_state = state_after;
   return BAMCL_OK;
 }

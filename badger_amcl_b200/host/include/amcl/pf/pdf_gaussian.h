@@ -16,6 +16,11 @@ public:
   Eigen::Vector3d sample();
   static double draw(double sigma);
 
+  // the decomposition the constructor computed (what bamcl_pf_init_gaussian takes)
+  const Eigen::Vector3d& mean() const { return x_; }
+  const Eigen::Matrix3d& rotation() const { return cr_; }
+  const Eigen::Vector3d& sigmas() const { return cd_; }
+
 private:
   Eigen::Vector3d x_;
   Eigen::Matrix3d cr_;  // rotation (eigenvectors in columns)

@@ -403,8 +403,36 @@ void ParticleFilter::initWithPoseFn(std::function<Eigen::Vector3d()> pose_fn)
 
 void ParticleFilter::initWithGaussian(const Eigen::Vector3d& mean, const Eigen::Matrix3d& cov)
 {
+  // particle_filter.cpp:105-133 on the device: the covariance is decomposed here (PDFGaussian's constructor), the
+  // 3 * max_samples Gaussian draws and the poses are made on the device from libc's drand48 state, which is then advanced
+  // to where the reference's loop would have left it
   PDFGaussian pdf(mean, cov);
-  initWithPoseFn([&pdf]() { return pdf.sample(); });
+  double m[3], cr[9], cd[3];
+  for (int i = 0; i < 3; i++)
+  {
+    m[i] = pdf.mean()[i];
+    cd[i] = pdf.sigmas()[i];
+    for (int j = 0; j < 3; j++)
+      cr[3 * i + j] = pdf.rotation()(i, j);
+  }
+  uint64_t state_out = 0;
+  bamcl_resample_result res;
+  if (!deviceOk(bamcl_pf_init_gaussian(dev_, m, cr, cd, peekDrand48State(), &state_out, &res), "bamcl_pf_init_gaussian"))
+  {
+    // e.g. a drand48 output of exactly 0.0 inside the draw range (2^-48 per draw): the sequential loop handles it
+    clearDeviceError();
+    initWithPoseFn([&pdf]() { return pdf.sample(); });
+    return;
+  }
+  unsigned short st[3] = {(unsigned short)(state_out & 0xFFFF), (unsigned short)((state_out >> 16) & 0xFFFF),
+                          (unsigned short)((state_out >> 32) & 0xFFFF)};
+  seed48(st);
+  w_slow_ = w_fast_ = 0.0;
+  host_valid_ = false;
+  host_dirty_ = false;
+  installStats(&res);
+  set_->converged = false;  // initConverged
+  converged_ = false;
 }
 
 void ParticleFilter::updateSensor(std::function<double(std::shared_ptr<SensorData>, std::shared_ptr<PFSampleSet>)> sensor_fn,

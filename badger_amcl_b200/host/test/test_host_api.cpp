@@ -383,6 +383,37 @@ static int odomFlow(const char* in_path, const char* out_path)
   return g_failed ? 1 : 0;
 }
 
+// "gauss" mode: ParticleFilter::initWithGaussian through the mirror's class API (argv: seed n mean[3] var[3] out): writes the
+// samples, then libc's drand48 state after the call, then leaf / cluster counts
+static int gaussFlow(int argc, char** argv)
+{
+  const int seed = std::atoi(argv[2]), n = std::atoi(argv[3]);
+  Eigen::Vector3d mean(std::atof(argv[4]), std::atof(argv[5]), std::atof(argv[6]));
+  Eigen::Matrix3d cov = Eigen::Matrix3d::Zero();
+  for (int k = 0; k < 3; k++)
+    cov(k, k) = std::atof(argv[7 + k]);
+  auto pose_fn = []() { return Eigen::Vector3d(0.0, 0.0, 0.0); };
+  auto pf = std::make_shared<badger_amcl::ParticleFilter>(n / 10, n, 0.001, 0.1, 95.0, pose_fn);
+  srand48(seed);
+  pf->initWithGaussian(mean, cov);
+  EXPECT_TRUE(std::string(badger_amcl::lastDeviceError()).empty());
+  auto set = pf->peekCurrentSet();
+  EXPECT_EQ(set->sample_count, n);
+  FILE* out = std::fopen(argv[10], "wb");
+  if (!out)
+    return 2;
+  std::fwrite(set->samples.data(), sizeof(double), (size_t)4 * set->sample_count, out);
+  unsigned short zero[3] = {0, 0, 0};
+  unsigned short* prev = seed48(zero);
+  unsigned short saved[3] = {prev[0], prev[1], prev[2]};
+  seed48(saved);
+  const double tail[3] = {(double)((uint64_t)saved[0] | ((uint64_t)saved[1] << 16) | ((uint64_t)saved[2] << 32)),
+                          (double)set->kdtree->getLeafCount(), (double)set->cluster_count};
+  std::fwrite(tail, sizeof(double), 3, out);
+  std::fclose(out);
+  return g_failed ? 1 : 0;
+}
+
 // The node's step (node_2d.cpp:367-380 scan callback -> PlanarScanner::updateSensor, node.cpp:337-349 -> updateResample)
 // through the class API of libbadger_amcl.so, timed on the host. Between steps the caller writes the poses through
 // getCurrentSet()->samples, as Odom::updateAction does in the reference (odom.cpp:107-121), so the mirror's lazy
@@ -491,6 +522,8 @@ int main(int argc, char** argv)
     testPdfGaussian();
     if (mode == "odom" && argc == 4)
       return odomFlow(argv[2], argv[3]);
+    if (mode == "gauss" && argc == 11)
+      return gaussFlow(argc, argv);
     testPfKdtree();
     testOctoMapConversions();
     testOccupancyMapConversions();

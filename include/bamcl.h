@@ -411,6 +411,17 @@ int bamcl_pf_init_uniform(bamcl_pf* pf, bamcl_map2d* map, double starting_weight
 int bamcl_pf_init_uniform_3d(bamcl_pf* pf, bamcl_map3d* map, double starting_weight_threshold, double deweight_multiplier,
                              uint64_t drand48_state, uint64_t* drand48_state_out, bamcl_resample_result* result);
 
+/* ParticleFilter::initWithGaussian (particle_filter.cpp:105-133) on the device: max_samples poses, each PDFGaussian::sample()
+ * (pdf_gaussian.cpp:52-71) = mean + cr * (draw(cd[0]), draw(cd[1]), draw(cd[2])), the draws taken from the drand48 stream in
+ * the reference's order (all rejection-loop attempts evaluated at once, as in bamcl_pf_update_action), weights
+ * 1/max_samples, pose-bin tree, clusters and statistics; w_slow/w_fast reset is the caller's (:126). The caller passes the
+ * DECOMPOSED covariance PDFGaussian's constructor computes (:33-43): cr9 = the rotation (row-major, eigenvectors in
+ * columns), cd3 = the standard deviations along them - for the diagonal covariances the node passes (node.cpp:281-287,
+ * 688-701) that is the identity and sqrt of the diagonal; Eigen::EigenSolver's eigenvector order / sign for other matrices
+ * is third-party and stays with the caller. drand48_state in / out as for bamcl_pf_update_action. */
+int bamcl_pf_init_gaussian(bamcl_pf* pf, const double* mean3, const double* cr9, const double* cd3, uint64_t drand48_state,
+                           uint64_t* drand48_state_out, bamcl_resample_result* result);
+
 /* random_pose_fn_ of the filter (particle_filter.h:128; the node wires in Node::uniformPoseGenerator, node.cpp:262-264):
  * registers `map`'s free-space list (bamcl_map2d_update_free_space) and the generator's two parameters, so that
  * multinomial resampling with w_diff > 0 (particle_filter.cpp:385-388) draws its random poses on the device from the

@@ -201,7 +201,7 @@ def ref_lib():
             "ref_pf_cluster_count": (I, [P]), "ref_pf_resample_limit": (I, [P, I]),
             "ref_pf_get_sample_clusters": (None, [P, P]), "ref_pf_get_cluster_stats": (None, [P, P]),
             "ref_pf_get_set_stats": (None, [P, P]),
-            "ref_gaussian_sample": (None, [P, P, L_, P]),
+            "ref_gaussian_sample": (None, [P, P, L_, P]), "ref_pf_init_gaussian": (None, [P, P, P]),
             "ref_ros_reset": (None, []), "ref_ros_set_param_num": (None, [C.c_char_p, D]),
             "ref_ros_set_param_str": (None, [C.c_char_p, C.c_char_p]), "ref_ros_set_time": (None, [D]),
             "ref_ros_set_tf": (None, [C.c_char_p, C.c_char_p, P, P]), "ref_ros_clear_tf": (None, [C.c_char_p, C.c_char_p]),
@@ -571,6 +571,11 @@ class RefPF(_PFBase):
     def init_with_poses(self, poses):
         p = np.ascontiguousarray(poses, np.float64)
         self.L.ref_pf_init_with_poses(self.h, _ptr(p), len(p))
+
+    def init_gaussian(self, mean, cov):
+        """ParticleFilter::initWithGaussian of the compiled reference (draws from the process-global drand48 stream)"""
+        m, c = np.ascontiguousarray(mean, np.float64), np.ascontiguousarray(cov, np.float64)
+        self.L.ref_pf_init_gaussian(self.h, _ptr(m), _ptr(c))
 
     def set_uniform_pose_source(self, ref_map, free_ij, threshold=0.0, multiplier=0.0):
         f = np.ascontiguousarray(free_ij, np.int32)

@@ -544,6 +544,16 @@ void ref_pf_init_with_poses(void* h, const double* poses, long n)
     return p;
   });
 }
+// ParticleFilter::initWithGaussian (particle_filter.cpp:105-133), drawing from the process-global drand48 stream
+void ref_pf_init_gaussian(void* h, const double* mean3, const double* cov9)
+{
+  Eigen::Vector3d mean(mean3[0], mean3[1], mean3[2]);
+  Eigen::Matrix3d cov;
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++)
+      cov(i, j) = cov9[3 * i + j];
+  static_cast<PF*>(h)->pf->initWithGaussian(mean, cov);
+}
 int ref_pf_sample_count(void* h) { return static_cast<PF*>(h)->pf->getCurrentSet()->sample_count; }
 void ref_pf_get_samples(void* h, double* aos)
 {

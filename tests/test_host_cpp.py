@@ -128,3 +128,32 @@ def test_odom_update_action_through_the_class_api_matches_oracle(exe, oracle_bui
         assert np.array_equal(s[:, 3], port.samples()[:, 3])
         # continue from the device's poses so that rounding differences do not accumulate in the comparison
         port.set_samples(s)
+
+
+@pytest.mark.gpu
+def test_init_with_gaussian_through_the_class_api_matches_the_reference(exe, oracle_built, tmp_path):
+    """the mirror's ParticleFilter::initWithGaussian (-> bamcl_pf_init_gaussian) against the compiled reference's
+    (particle_filter.cpp:105-133 + pdf_gaussian.cpp): libc's drand48 state after the call bit-exact, poses to 1e-12"""
+    O = oracle_built
+    n, seed = 3000, 5
+    mean, var = [1.5, -0.5, 0.3], [0.25, 0.09, 0.0685]
+    fout = str(tmp_path / "gauss_out.bin")
+    p = subprocess.run([exe, "gauss", str(seed), str(n)] + [repr(v) for v in mean + var] + [fout], capture_output=True,
+                       text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    got = np.fromfile(fout, np.float64)
+    s, tail = got[:4 * n].reshape(n, 4), got[4 * n:]
+    ref = (O.RefPF if O.have_ref() else None)
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    pf = ref(n // 10, n)
+    pf.srand48(seed)
+    pf.init_gaussian(mean, np.diag(var))
+    want = pf.samples()
+    st = (O.C.c_ushort * 3)()
+    O.ref_lib().ref_get_seed48(st)
+    assert int(tail[0]) == st[0] | (st[1] << 16) | (st[2] << 32)
+    assert np.abs(s[:, :3] - want[:, :3]).max() <= 1e-12
+    assert np.array_equal(s[:, 3], want[:, 3])
+    assert (int(tail[1]), int(tail[2])) == (pf.leaf_count(), pf.cluster_count())
+

@@ -167,3 +167,59 @@ def test_gpu_init_uniform_3d_vs_oracle(oracle_built, dev, thr, mult):
     assert np.array_equal(pf.sample_clusters(), ref.sample_clusters())
     pf.close()
     m.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which,seed,n,cd", [("2d", 21, 1500, None), ("3d", 33, 800, None)])
+def test_gpu_init_gaussian_reproduces_the_nodes_first_particle_set(dev, which, seed, n, cd):
+    """Node::initFromNewMap -> ParticleFilter::initWithGaussian (node.cpp:670-701, particle_filter.cpp:105-133) with the
+    node's default initial pose and covariance: the set the compiled node drew from srand48(seed) is in the golden run.
+    The node draws it TWICE (initFromNewMap calls initWithGaussian, then setInitialPose -> applyInitialPose calls it again,
+    node.cpp:688-708, 980-1002): the golden set is the second one"""
+    cabi = dev["cabi"]
+    g = golden("node_%s.npz" % which)
+    pf = cabi.ParticleFilter(dev["ctx"], 100, n)
+    pf.srand48(seed)
+    sig = np.sqrt(np.array([0.5 * 0.5, 0.5 * 0.5, (np.pi / 12.0) * (np.pi / 12.0)]))   # pdf_gaussian.cpp:41-43
+    pf.init_gaussian(np.zeros(3), np.eye(3), sig)
+    res = pf.init_gaussian(np.zeros(3), np.eye(3), sig)
+    got, want = pf.samples(), g["init_samples"]
+    assert pf.drand48_state == int(g["init_state"])          # the same attempts were accepted
+    assert np.array_equal(got[:, 3], want[:, 3])
+    assert np.abs(got[:, :3] - want[:, :3]).max() <= 1e-12   # device log / sqrt vs glibc, last ulp
+    assert res.sample_count == n and res.converged == 0
+    if "init_leaf" in g:
+        assert res.leaf_count == int(g["init_leaf"])
+        assert np.array_equal(pf.sample_clusters(), g["init_labels"])
+    pf.close()
+
+
+@pytest.mark.gpu
+def test_gpu_init_gaussian_rotated_covariance_vs_reference_sampler(oracle_built, dev):
+    """a general rotation + three different sigmas, against PDFGaussian::sample of the compiled pdf_gaussian.cpp fed the
+    SAME decomposition (a covariance that is diagonal in the rotated frame is passed pre-decomposed on both sides: the
+    reference side through its diagonal path per axis, recombined here with the reference's own add order)"""
+    import ctypes as C
+    O, cabi = oracle_built, dev["cabi"]
+    n = 20000
+    cd = np.array([0.7, 0.05, 0.3])
+    a = 0.6
+    cr = np.array([[np.cos(a), -np.sin(a), 0.0], [np.sin(a), np.cos(a), 0.0], [0.0, 0.0, 1.0]])
+    mean = np.array([1.5, -2.0, 0.4])
+    # the draws r[j] = draw(cd[j]) in order, from the restated generator (pinned to pdf_gaussian.cpp's draw)
+    rng = O.Rng(0)
+    L = O.port_lib()
+    L.orc_srand48(C.byref(rng), 77)
+    r = np.array([[L.orc_gaussian_draw(C.byref(rng), cd[j]) for j in range(3)] for _ in range(n)])
+    want = np.empty((n, 3))
+    for i in range(3):   # v(i) = x[i]; v(i) += cr(i, j) * r[j], j = 0..2 (pdf_gaussian.cpp:65-69)
+        t = np.full(n, mean[i])
+        for j in range(3):
+            t = t + cr[i, j] * r[:, j]
+        want[:, i] = t
+    pf = cabi.ParticleFilter(dev["ctx"], 100, n)
+    pf.srand48(77)
+    pf.init_gaussian(mean, cr, cd)
+    assert pf.drand48_state == rng.x
+    assert np.abs(pf.samples()[:, :3] - want).max() <= 1e-12
+    pf.close()

@@ -252,3 +252,21 @@ def test_reference_gaussian_kat_on_the_compiled_translation_unit(O):
     want = [[0.26562654174915334, 0.97172090090793528, -1.5856194295513539],
             [1.6262083813236745, 1.1142314205031041, 0.37407538872488655]]
     assert np.allclose(out, want, rtol=4e-16, atol=0.0)   # EXPECT_DOUBLE_EQ = 4 ulps
+
+
+def test_node_draws_its_first_set_twice(O):
+    """Node::initFromNewMap (node.cpp:670-708): initWithGaussian with the initial pose, then setInitialPose ->
+    applyInitialPose -> initWithGaussian again; the particle set a fresh node holds is the SECOND batch of the stream"""
+    n = O.RefNode(dict(BASE))
+    O.ref_lib().ref_srand48(21)
+    n.publish_map(grid_world(), 0.05, (-4.0, -3.0))
+    got = n.pf().samples()
+    state = drand_state(O)
+    pf = O.RefPF(300, 1000)
+    pf.srand48(21)
+    cov = np.diag([0.5 * 0.5, 0.5 * 0.5, (np.pi / 12.0) * (np.pi / 12.0)])
+    pf.init_gaussian(np.zeros(3), cov)
+    assert not np.array_equal(pf.samples(), got)
+    pf.init_gaussian(np.zeros(3), cov)
+    assert np.array_equal(pf.samples(), got) and drand_state(O) == state
+    n.close()

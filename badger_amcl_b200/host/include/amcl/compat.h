@@ -52,7 +52,10 @@ struct Matrix3d
 }  // namespace Eigen
 #endif
 
-#ifndef BAMCL_HAVE_PCL
+#ifdef BAMCL_HAVE_PCL
+#include <pcl/point_cloud.h>
+#include <pcl/point_types.h>
+#else
 namespace pcl
 {
 struct PointXYZ
@@ -82,7 +85,9 @@ struct PointCloud
 }  // namespace pcl
 #endif
 
-#ifndef BAMCL_HAVE_ROS
+#ifdef BAMCL_HAVE_ROS
+#include <geometry_msgs/Transform.h>
+#else
 namespace geometry_msgs
 {
 struct Vector3
@@ -101,7 +106,9 @@ struct Transform
 }  // namespace geometry_msgs
 #endif
 
-#ifndef BAMCL_HAVE_OCTOMAP
+#ifdef BAMCL_HAVE_OCTOMAP
+#include <octomap/OcTree.h>
+#else
 namespace octomap
 {
 // The occupied leaves of an octree as integer keys (leaf centre = (key + 0.5) * resolution, octomap's

@@ -224,7 +224,21 @@ void OctoMap::initFromOctree(std::shared_ptr<octomap::OcTree> octree, double max
   if (dev_)
     bamcl_map3d_destroy(dev_);
   dev_ = nullptr;
+#ifdef BAMCL_HAVE_OCTOMAP
+  // a real octomap::OcTree: the occupied leaves through its public iterator (octomap.cpp:220-227 reads the same), leaf
+  // centre (k + 0.5) * resolution -> integer key k
+  std::vector<int> keys;
+  octree->expand();
+  for (octomap::OcTree::leaf_iterator it = octree->begin_leafs(), end = octree->end_leafs(); it != end; ++it)
+    if (octree->isNodeOccupied(*it))
+    {
+      keys.push_back((int)std::floor(it.getX() / resolution_));
+      keys.push_back((int)std::floor(it.getY() / resolution_));
+      keys.push_back((int)std::floor(it.getZ() / resolution_));
+    }
+#else
   const std::vector<int>& keys = octree->occupiedKeys();
+#endif
   check(bamcl_map3d_create(deviceContext(), resolution_, max_distance_to_object, keys.data(), (long)(keys.size() / 3), &dev_),
         "bamcl_map3d_create");
   refreshBounds();

@@ -29,6 +29,9 @@ def build(ref=True):
     subprocess.check_call(["make", "-s", "-C", HERE, "port"])
     if ref and os.path.isdir("/root/reference/src/amcl"):
         subprocess.check_call(["make", "-s", "-C", HERE, "ref"])
+        # the reference's node on top of the host mirror + CUDA library (links libbamcl_cuda.so: built once that exists)
+        if os.path.exists(os.path.join(HERE, "..", "badger_amcl_b200", "libbamcl_cuda.so")):
+            subprocess.check_call(["make", "-s", "-C", HERE, "node_gpu"])
 
 
 def _ptr(a, ty=None):
@@ -146,6 +149,64 @@ def have_ref():
     return os.path.exists(REF_SO)
 
 
+NODE_GPU_SO = os.path.join(HERE, "_ref", "libamcl_node_gpu.so")
+_node_gpu = None
+
+
+def _node_sigs(wrappers):
+    """the node-driving surface of oracle/node_harness.inc (both libraries); wrappers: the reference-only handle getters"""
+    D, I, L_, V, P, F = C.c_double, C.c_int, C.c_long, C.c_void_p, C.c_void_p, C.c_float
+    sig = {
+            "ref_ros_reset": (None, []), "ref_ros_set_param_num": (None, [C.c_char_p, D]),
+            "ref_ros_set_param_str": (None, [C.c_char_p, C.c_char_p]), "ref_ros_set_time": (None, [D]),
+            "ref_ros_set_tf": (None, [C.c_char_p, C.c_char_p, P, P]), "ref_ros_clear_tf": (None, [C.c_char_p, C.c_char_p]),
+            "ref_ros_message_count": (L_, [C.c_char_p]), "ref_ros_call_service": (I, [C.c_char_p]),
+            "ref_ros_fire_timers": (I, []), "ref_ros_reconfigure": (I, []),
+            "ref_node_create": (V, []), "ref_node_destroy": (None, [P]),
+            "ref_ros_publish_map": (I, [P, I, I, F, D, D]), "ref_ros_publish_octomap": (I, [D, P, L_, I]),
+            "ref_ros_publish_scan": (I, [C.c_char_p, D, F, F, F, F, F, P, I]),
+            "ref_ros_publish_cloud": (I, [C.c_char_p, D, P, L_]), "ref_ros_publish_odom": (I, [D, D, D, D]),
+            "ref_ros_publish_initial_pose": (I, [C.c_char_p, D, D, D, D, P]),
+            "ref_node_pf": (V, [P]), "ref_node_map2d": (V, [P]), "ref_node_map3d": (V, [P]),
+            "ref_map2d_geometry": (None, [P, P, P, P]),
+            "ref_node_free_space_count": (L_, [P]), "ref_node_free_space": (None, [P, P]),
+            "ref_node_uniform_poses": (None, [P, L_, P]), "ref_node_scan_data": (I, [P, P, P, P, I]),
+            "ref_node_angle_stats": (I, [P, C.c_char_p, D, F, F, P]), "ref_node_cloud_data": (L_, [P, P, L_]),
+            "ref_node_max_weight_pose": (I, [P, P, P]), "ref_ros_last_pose": (L_, [P]),
+            "ref_ros_last_particlecloud": (L_, [P, L_]), "ref_node_latest_tf": (I, [P, P]),
+            "ref_node_state": (None, [P, P]), "ref_node_odom_pose": (I, [P, D, P]),
+        "ref_node_sample_count": (I, [P]), "ref_node_samples": (None, [P, P]), "ref_node_filter_info": (None, [P, P]),
+        "ref_node_sample_clusters": (None, [P, P]), "ref_node_get_seed48": (None, [P]),
+    }
+    if not wrappers:
+        for k in ("ref_node_pf", "ref_node_map2d", "ref_node_map3d", "ref_map2d_geometry"):
+            del sig[k]
+    return sig
+
+
+def have_node_gpu():
+    return os.path.exists(NODE_GPU_SO)
+
+
+def node_gpu_lib():
+    """oracle/_ref/libamcl_node_gpu.so: the reference's node sources on top of the host mirror + CUDA library"""
+    global _node_gpu
+    if _node_gpu is None:
+        if not have_node_gpu():
+            raise RuntimeError("oracle/_ref/libamcl_node_gpu.so missing: run `make -C oracle node_gpu` where /root/reference exists")
+        L = C.CDLL(NODE_GPU_SO)
+        sig = _node_sigs(wrappers=False)
+        sig["ref_srand48"] = (None, [C.c_long])
+        sig["ref_node_last_device_error"] = (C.c_char_p, [])
+        sig["ref_node_install_cache_2d"] = (C.c_int, [C.c_void_p, C.c_void_p, C.c_long, C.c_double])
+        sig["ref_node_install_cache_3d"] = (C.c_int, [C.c_void_p, C.c_void_p, C.c_long])
+        for name, (res, args) in sig.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _node_gpu = L
+    return _node_gpu
+
+
 def ref_lib():
     global _ref
     if _ref is None:
@@ -202,25 +263,8 @@ def ref_lib():
             "ref_pf_get_sample_clusters": (None, [P, P]), "ref_pf_get_cluster_stats": (None, [P, P]),
             "ref_pf_get_set_stats": (None, [P, P]),
             "ref_gaussian_sample": (None, [P, P, L_, P]), "ref_pf_init_gaussian": (None, [P, P, P]),
-            "ref_ros_reset": (None, []), "ref_ros_set_param_num": (None, [C.c_char_p, D]),
-            "ref_ros_set_param_str": (None, [C.c_char_p, C.c_char_p]), "ref_ros_set_time": (None, [D]),
-            "ref_ros_set_tf": (None, [C.c_char_p, C.c_char_p, P, P]), "ref_ros_clear_tf": (None, [C.c_char_p, C.c_char_p]),
-            "ref_ros_message_count": (L_, [C.c_char_p]), "ref_ros_call_service": (I, [C.c_char_p]),
-            "ref_ros_fire_timers": (I, []), "ref_ros_reconfigure": (I, []),
-            "ref_node_create": (V, []), "ref_node_destroy": (None, [P]),
-            "ref_ros_publish_map": (I, [P, I, I, F, D, D]), "ref_ros_publish_octomap": (I, [D, P, L_, I]),
-            "ref_ros_publish_scan": (I, [C.c_char_p, D, F, F, F, F, F, P, I]),
-            "ref_ros_publish_cloud": (I, [C.c_char_p, D, P, L_]), "ref_ros_publish_odom": (I, [D, D, D, D]),
-            "ref_ros_publish_initial_pose": (I, [C.c_char_p, D, D, D, D, P]),
-            "ref_node_pf": (V, [P]), "ref_node_map2d": (V, [P]), "ref_node_map3d": (V, [P]),
-            "ref_map2d_geometry": (None, [P, P, P, P]),
-            "ref_node_free_space_count": (L_, [P]), "ref_node_free_space": (None, [P, P]),
-            "ref_node_uniform_poses": (None, [P, L_, P]), "ref_node_scan_data": (I, [P, P, P, P, I]),
-            "ref_node_angle_stats": (I, [P, C.c_char_p, D, F, F, P]), "ref_node_cloud_data": (L_, [P, P, L_]),
-            "ref_node_max_weight_pose": (I, [P, P, P]), "ref_ros_last_pose": (L_, [P]),
-            "ref_ros_last_particlecloud": (L_, [P, L_]), "ref_node_latest_tf": (I, [P, P]),
-            "ref_node_state": (None, [P, P]), "ref_node_odom_pose": (I, [P, D, P]),
         }
+        sig.update(_node_sigs(wrappers=True))
         for name, (res, args) in sig.items():
             fn = getattr(L, name)
             fn.restype, fn.argtypes = res, args
@@ -930,8 +974,8 @@ class RefNode:
     constructor (private names without the "~"), tf comes from set_tf, messages are delivered synchronously to the node's
     own callbacks. One node at a time (the table is process-global)."""
 
-    def __init__(self, params=None, map_type=2):
-        self.L = ref_lib()
+    def __init__(self, params=None, map_type=2, lib=None):
+        self.L = lib if lib is not None else ref_lib()   # lib=node_gpu_lib(): the same node on the mirror + CUDA library
         self.L.ref_ros_reset()
         self.set_params(dict(map_type=map_type, save_pose=False))
         self.set_params(params or {})
@@ -1094,6 +1138,37 @@ class RefNode:
         """Node::getOdomPose (node.cpp:795-821): (x, y, yaw) from the odom -> base_link transform, yaw through tf2"""
         out = np.empty(3)
         return out if self.L.ref_node_odom_pose(self.h, stamp, _ptr(out)) else None
+
+    def install_cache_2d(self, dist, max_dist):
+        """relinked node only: OccupancyMap::setDistancesLUT of the mirror (a cache computed by the reference)"""
+        d = np.ascontiguousarray(dist, np.float32)
+        assert self.L.ref_node_install_cache_2d(self.h, _ptr(d), d.size, max_dist) == 0
+
+    def install_cache_3d(self, dense):
+        d = np.ascontiguousarray(dense, np.uint8)
+        assert self.L.ref_node_install_cache_3d(self.h, _ptr(d), d.size) == 0
+
+    # ---- readers that work on both libraries (public API of the filter only)
+    def samples(self):
+        n = self.L.ref_node_sample_count(self.h)
+        out = np.empty((max(n, 0), 4))
+        self.L.ref_node_samples(self.h, _ptr(out))
+        return out
+
+    def filter_info(self):
+        out = np.empty(5)
+        self.L.ref_node_filter_info(self.h, _ptr(out))
+        return dict(leaf_count=int(out[0]), cluster_count=int(out[1]), converged=bool(out[2]), w_slow=out[3], w_fast=out[4])
+
+    def sample_clusters(self):
+        out = np.empty(self.L.ref_node_sample_count(self.h), np.int32)
+        self.L.ref_node_sample_clusters(self.h, _ptr(out))
+        return out
+
+    def drand48_state(self):
+        s = (C.c_ushort * 3)()
+        self.L.ref_node_get_seed48(s)
+        return s[0] | (s[1] << 16) | (s[2] << 32)
 
     def state(self):
         out = np.empty(11)

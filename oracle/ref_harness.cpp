@@ -659,132 +659,8 @@ void ref_pf_update_action(void* h, int model_type, const double* alpha, const do
   odom.updateAction(static_cast<PF*>(h)->pf, data);
 }
 
-// ---------------------------------------------------------------- the ROS node (node/node.cpp, node_2d.cpp, node_3d.cpp)
-// The node's translation units are the reference's own object code; roscpp, tf2_ros, dynamic_reconfigure, message_filters
-// and yaml-cpp are the in-process look-alikes under shim/ (parameters from a table, topics delivered synchronously, tf from
-// a table). These entry points fill the tables, publish messages into the node's callbacks and read back what the node
-// computed / published.
-void ref_ros_reset()
-{
-  ros::shim::bus().reset();
-  tf2_ros::shim::tf_table().clear();
-}
-void ref_ros_set_param_num(const char* name, double v) { ros::shim::bus().num_params[name] = v; }
-void ref_ros_set_param_str(const char* name, const char* v) { ros::shim::bus().str_params[name] = v; }
-void ref_ros_set_time(double t) { ros::shim::bus().now = t; }
-void ref_ros_set_tf(const char* target, const char* source, const double* xyz, const double* quat_xyzw)
-{
-  geometry_msgs::Transform t;
-  t.translation.x = xyz[0];
-  t.translation.y = xyz[1];
-  t.translation.z = xyz[2];
-  t.rotation.x = quat_xyzw[0];
-  t.rotation.y = quat_xyzw[1];
-  t.rotation.z = quat_xyzw[2];
-  t.rotation.w = quat_xyzw[3];
-  tf2_ros::shim::tf_table()[std::make_pair(std::string(target), std::string(source))] = t;
-}
-void ref_ros_clear_tf(const char* target, const char* source)
-{
-  tf2_ros::shim::tf_table().erase(std::make_pair(std::string(target), std::string(source)));
-}
-long ref_ros_message_count(const char* topic) { return ros::shim::bus().msg_count[topic]; }
-int ref_ros_call_service(const char* name)
-{
-  std::map<std::string, std::function<bool()>>& s = ros::shim::bus().services;
-  return s.count(name) ? (s[name]() ? 1 : 0) : -1;
-}
-int ref_ros_fire_timers()
-{
-  std::vector<ros::shim::Bus::TimerRec> t = ros::shim::bus().timers;
-  for (ros::shim::Bus::TimerRec& r : t)
-    r.fire();
-  return static_cast<int>(t.size());
-}
-int ref_ros_reconfigure()
-{
-  if (!ros::shim::bus().reconfigure)
-    return -1;
-  ros::shim::bus().reconfigure();
-  return 0;
-}
-
-void* ref_node_create() { return new Node(); }
-void ref_node_destroy(void* h) { delete static_cast<Node*>(h); }
-static Node2D* node2d(void* h) { return dynamic_cast<Node2D*>(static_cast<Node*>(h)->node_.get()); }
-static Node3D* node3d(void* h) { return dynamic_cast<Node3D*>(static_cast<Node*>(h)->node_.get()); }
-
-int ref_ros_publish_map(const int8_t* data, int width, int height, float resolution, double origin_x, double origin_y)
-{
-  std::shared_ptr<nav_msgs::OccupancyGrid> m = std::make_shared<nav_msgs::OccupancyGrid>();
-  m->header.frame_id = "map";
-  m->info.resolution = resolution;
-  m->info.width = static_cast<uint32_t>(width);
-  m->info.height = static_cast<uint32_t>(height);
-  m->info.origin.position.x = origin_x;
-  m->info.origin.position.y = origin_y;
-  m->info.origin.orientation.w = 1.0;
-  m->data.assign(data, data + static_cast<size_t>(width) * height);
-  return ros::shim::bus().deliver("map", std::shared_ptr<const nav_msgs::OccupancyGrid>(m));
-}
-int ref_ros_publish_octomap(double resolution, const int* keys, long n_keys, int binary)
-{
-  std::shared_ptr<octomap_msgs::Octomap> m = std::make_shared<octomap_msgs::Octomap>();
-  m->header.frame_id = "map";
-  m->binary = binary != 0;
-  m->resolution = resolution;
-  m->occupied_keys.assign(keys, keys + 3 * n_keys);
-  return ros::shim::bus().deliver("octomap", std::shared_ptr<const octomap_msgs::Octomap>(m));
-}
-int ref_ros_publish_scan(const char* frame_id, double stamp, float angle_min, float angle_max, float angle_increment,
-                         float range_min, float range_max, const float* ranges, int n)
-{
-  std::shared_ptr<sensor_msgs::LaserScan> m = std::make_shared<sensor_msgs::LaserScan>();
-  m->header.frame_id = frame_id;
-  m->header.stamp = ros::Time(stamp);
-  m->angle_min = angle_min;
-  m->angle_max = angle_max;
-  m->angle_increment = angle_increment;
-  m->range_min = range_min;
-  m->range_max = range_max;
-  m->ranges.assign(ranges, ranges + n);
-  return ros::shim::bus().deliver("scan", std::shared_ptr<const sensor_msgs::LaserScan>(m));
-}
-int ref_ros_publish_cloud(const char* frame_id, double stamp, const float* xyz, long n)
-{
-  std::shared_ptr<sensor_msgs::PointCloud2> m = std::make_shared<sensor_msgs::PointCloud2>();
-  m->header.frame_id = frame_id;
-  m->header.stamp = ros::Time(stamp);
-  m->xyz.resize(n);
-  for (long k = 0; k < n; k++)
-    m->xyz[k] = pcl::PointXYZ(xyz[3 * k], xyz[3 * k + 1], xyz[3 * k + 2]);
-  return ros::shim::bus().deliver("cloud", std::shared_ptr<const sensor_msgs::PointCloud2>(m));
-}
-static void fill_pose(geometry_msgs::Pose* p, double x, double y, double yaw)
-{
-  p->position.x = x;
-  p->position.y = y;
-  tf2::Quaternion q;
-  q.setRPY(0.0, 0.0, yaw);
-  p->orientation = tf2::toMsg(q);
-}
-int ref_ros_publish_odom(double stamp, double x, double y, double yaw)
-{
-  std::shared_ptr<nav_msgs::Odometry> m = std::make_shared<nav_msgs::Odometry>();
-  m->header.stamp = ros::Time(stamp);
-  fill_pose(&m->pose.pose, x, y, yaw);
-  return ros::shim::bus().deliver("odom", std::shared_ptr<const nav_msgs::Odometry>(m));
-}
-int ref_ros_publish_initial_pose(const char* frame_id, double stamp, double x, double y, double yaw, const double* cov36)
-{
-  std::shared_ptr<geometry_msgs::PoseWithCovarianceStamped> m = std::make_shared<geometry_msgs::PoseWithCovarianceStamped>();
-  m->header.frame_id = frame_id;
-  m->header.stamp = ros::Time(stamp);
-  fill_pose(&m->pose.pose, x, y, yaw);
-  for (int k = 0; k < 36; k++)
-    m->pose.covariance[k] = cov36[k];
-  return ros::shim::bus().deliver("initialpose", std::shared_ptr<const geometry_msgs::PoseWithCovarianceStamped>(m));
-}
+// ---------------------------------------------------------------- the ROS node: see node_harness.inc
+#include "node_harness.inc"  // (inside the extern "C" block)
 
 // handles onto what the node owns, usable with the ref_pf_* / ref_map2d_* / ref_map3d_* readers above (NULL if absent)
 void* ref_node_pf(void* h)
@@ -824,179 +700,5 @@ void ref_map2d_geometry(void* h, int* size_xy, double* resolution, double* origi
   pcl::PointXYZ o = m->getOrigin();
   origin_xy[0] = o.x;
   origin_xy[1] = o.y;
-}
-long ref_node_free_space_count(void* h) { return static_cast<long>(static_cast<Node*>(h)->free_space_indices_.size()); }
-void ref_node_free_space(void* h, int* ij)
-{
-  const std::vector<std::pair<int, int>>& f = static_cast<Node*>(h)->free_space_indices_;
-  for (size_t k = 0; k < f.size(); k++)
-  {
-    ij[2 * k] = f[k].first;
-    ij[2 * k + 1] = f[k].second;
-  }
-}
-// Node::uniformPoseGenerator / randomFreeSpacePose called directly (node.cpp:823-868), drawing from drand48
-void ref_node_uniform_poses(void* h, long n, double* out)
-{
-  for (long k = 0; k < n; k++)
-  {
-    Eigen::Vector3d p = static_cast<Node*>(h)->uniformPoseGenerator();
-    out[3 * k] = p[0];
-    out[3 * k + 1] = p[1];
-    out[3 * k + 2] = p[2];
-  }
-}
-// Node2D::latest_scan_data_ after a scan went through updateScanner: returns range_count_ (-1: none)
-int ref_node_scan_data(void* h, double* ranges, double* angles, double* range_max, int capacity)
-{
-  Node2D* n = node2d(h);
-  if (!n || !n->latest_scan_data_)
-    return -1;
-  const PlanarData& d = *n->latest_scan_data_;
-  for (int k = 0; k < d.range_count_ && k < capacity; k++)
-  {
-    ranges[k] = d.ranges_[k];
-    angles[k] = d.angles_[k];
-  }
-  *range_max = d.range_max_;
-  return d.range_count_;
-}
-// Node2D::getAngleStats called directly (node_2d.cpp:497-532) on a scan header; returns 0 when the tf lookup failed
-int ref_node_angle_stats(void* h, const char* frame_id, double stamp, float angle_min, float angle_increment, double* out2)
-{
-  Node2D* n = node2d(h);
-  if (!n)
-    return -1;
-  std::shared_ptr<sensor_msgs::LaserScan> m = std::make_shared<sensor_msgs::LaserScan>();
-  m->header.frame_id = frame_id;
-  m->header.stamp = ros::Time(stamp);
-  m->angle_min = angle_min;
-  m->angle_increment = angle_increment;
-  return n->getAngleStats(m, &out2[0], &out2[1]) ? 1 : 0;
-}
-// Node3D::latest_scan_data_->points_ after a cloud went through updateScanner: returns the number of points kept
-long ref_node_cloud_data(void* h, float* xyz, long capacity)
-{
-  Node3D* n = node3d(h);
-  if (!n || !n->latest_scan_data_)
-    return -1;
-  const std::vector<pcl::PointXYZ>& p = n->latest_scan_data_->points_.points;
-  for (size_t k = 0; k < p.size() && static_cast<long>(k) < capacity; k++)
-  {
-    xyz[3 * k] = p[k].x;
-    xyz[3 * k + 1] = p[k].y;
-    xyz[3 * k + 2] = p[k].z;
-  }
-  return static_cast<long>(p.size());
-}
-// Node2D/3D::getMaxWeightPose called directly; returns 0 (and leaves pose3 alone) where the reference would index hyps[-1]
-int ref_node_max_weight_pose(void* h, double* max_weight, double* pose3)
-{
-  std::shared_ptr<ParticleFilter> pf = static_cast<Node*>(h)->getPfPtr();
-  bool any = false;
-  for (int k = 0; pf && k < pf->getCurrentSet()->cluster_count; k++)
-  {
-    double w;
-    Eigen::Vector3d mean;
-    if (!pf->getClusterStats(k, &w, &mean))
-      break;
-    any = any || w > 0.0;
-  }
-  if (!any)
-    return 0;
-  Eigen::Vector3d pose;
-  if (node2d(h))
-    node2d(h)->getMaxWeightPose(max_weight, &pose);
-  else if (node3d(h))
-    node3d(h)->getMaxWeightPose(max_weight, &pose);
-  else
-    return -1;
-  pose3[0] = pose[0];
-  pose3[1] = pose[1];
-  pose3[2] = pose[2];
-  return 1;
-}
-// last geometry_msgs/PoseWithCovarianceStamped on "amcl_pose": out = x, y, z, qx, qy, qz, qw, stamp, cov[36]; returns the
-// number of poses published so far
-long ref_ros_last_pose(double* out44)
-{
-  ros::shim::Bus& b = ros::shim::bus();
-  if (!b.last_msg.count("amcl_pose"))
-    return 0;
-  const geometry_msgs::PoseWithCovarianceStamped& p =
-      *std::static_pointer_cast<const geometry_msgs::PoseWithCovarianceStamped>(b.last_msg["amcl_pose"]);
-  out44[0] = p.pose.pose.position.x;
-  out44[1] = p.pose.pose.position.y;
-  out44[2] = p.pose.pose.position.z;
-  out44[3] = p.pose.pose.orientation.x;
-  out44[4] = p.pose.pose.orientation.y;
-  out44[5] = p.pose.pose.orientation.z;
-  out44[6] = p.pose.pose.orientation.w;
-  out44[7] = p.header.stamp.toSec();
-  for (int k = 0; k < 36; k++)
-    out44[8 + k] = p.pose.covariance[k];
-  return b.msg_count["amcl_pose"];
-}
-// last geometry_msgs/PoseArray on "particlecloud": 7 doubles per pose (position, orientation); returns the pose count
-long ref_ros_last_particlecloud(double* out, long capacity)
-{
-  ros::shim::Bus& b = ros::shim::bus();
-  if (!b.last_msg.count("particlecloud"))
-    return -1;
-  const geometry_msgs::PoseArray& a = *std::static_pointer_cast<const geometry_msgs::PoseArray>(b.last_msg["particlecloud"]);
-  for (size_t k = 0; k < a.poses.size() && static_cast<long>(k) < capacity; k++)
-  {
-    out[7 * k] = a.poses[k].position.x;
-    out[7 * k + 1] = a.poses[k].position.y;
-    out[7 * k + 2] = a.poses[k].position.z;
-    out[7 * k + 3] = a.poses[k].orientation.x;
-    out[7 * k + 4] = a.poses[k].orientation.y;
-    out[7 * k + 5] = a.poses[k].orientation.z;
-    out[7 * k + 6] = a.poses[k].orientation.w;
-  }
-  return static_cast<long>(a.poses.size());
-}
-// Node::latest_tf_ (odom -> map as the node stores it, node.cpp:420-427): xyz + quaternion; returns latest_tf_valid_
-int ref_node_latest_tf(void* h, double* out7)
-{
-  Node* n = static_cast<Node*>(h);
-  if (!n->latest_tf_valid_)
-    return 0;
-  out7[0] = n->latest_tf_.getOrigin().x();
-  out7[1] = n->latest_tf_.getOrigin().y();
-  out7[2] = n->latest_tf_.getOrigin().z();
-  tf2::Quaternion q = n->latest_tf_.getRotation();
-  out7[3] = q.x();
-  out7[4] = q.y();
-  out7[5] = q.z();
-  out7[6] = q.w();
-  return 1;
-}
-// Node::getOdomPose (node.cpp:795-821): the odom -> base transform of the tf table as the (x, y, yaw) the node works with
-int ref_node_odom_pose(void* h, double stamp, double* out3)
-{
-  Eigen::Vector3d pose;
-  if (!static_cast<Node*>(h)->getOdomPose(ros::Time(stamp), &pose))
-    return 0;
-  out3[0] = pose[0];
-  out3[1] = pose[1];
-  out3[2] = pose[2];
-  return 1;
-}
-// odom_init_, Node::global_localization_active_, NodeND::global_localization_active_, resample_count_, scanner count,
-// pf_odom_pose_[3] and odom_integrator_absolute_motion_[3] as doubles: out[11]
-void ref_node_state(void* h, double* out11)
-{
-  Node* n = static_cast<Node*>(h);
-  out11[0] = n->odom_init_ ? 1.0 : 0.0;
-  out11[1] = n->global_localization_active_ ? 1.0 : 0.0;
-  out11[2] = node2d(h) ? (node2d(h)->global_localization_active_ ? 1.0 : 0.0) : node3d(h) ? (node3d(h)->global_localization_active_ ? 1.0 : 0.0) : -1.0;
-  out11[3] = node2d(h) ? node2d(h)->resample_count_ : node3d(h) ? node3d(h)->resample_count_ : -1.0;
-  out11[4] = node2d(h) ? static_cast<double>(node2d(h)->scanners_.size()) : node3d(h) ? static_cast<double>(node3d(h)->scanners_.size()) : -1.0;
-  for (int k = 0; k < 3; k++)
-  {
-    out11[5 + k] = n->pf_odom_pose_[k];
-    out11[8 + k] = n->odom_integrator_absolute_motion_[k];
-  }
 }
 }  // extern "C"

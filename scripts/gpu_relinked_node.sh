@@ -1,0 +1,5 @@
+# the reference's node sources relinked against the host mirror + CUDA library (oracle/_ref/libamcl_node_gpu.so)
+set -x
+cd $GRAFT_REPO_ROOT
+(time python -m pytest tests/test_node_chain.py -m gpu -x -q 2>&1 | tail -40) > gpurun_out/relinked_node_pytest.log 2>&1
+echo done

@@ -453,3 +453,64 @@ class CudaBackend3D(CudaBackend2D):
 
     def sensor(self, points):
         self.pf.update_sensor_cloud(self.map, self.model, points)
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+# The same scenario through a NODE (either library): oracle/_ref/libamcl_ref.so = the reference's node on the reference's
+# classes, oracle/_ref/libamcl_node_gpu.so = the reference's node on the host mirror + CUDA library. Inputs come from the
+# golden run, so nothing here needs the reference checkout.
+def run_node_2d(O, lib, g, seed=21, params=PARAMS_2D, reference_cache=False):
+    out = {}
+    lib.ref_srand48(seed)
+    n = O.RefNode(params, map_type=2, lib=lib)
+    assert n.publish_map(g["data"], RES_MSG, ORIGIN) == 1
+    if reference_cache:
+        n.install_cache_2d(g["brushfire"], params["laser_likelihood_max_dist"])
+    out["free"] = n.free_space()
+    out["init_samples"], out["init_state"] = n.samples(), n.drand48_state()
+    n.set_tf("base_link", "laser", MOUNT[:3], O.yaw_quat(MOUNT[3]))
+    for k in range(N_STEPS):
+        x, y, yaw = truth_pose(k)
+        n.set_odom(x, y, yaw)
+        assert n.publish_scan(g["s%d_ranges" % k], SCAN["angle_min"], SCAN["angle_increment"], SCAN["range_min"],
+                              SCAN["range_max"], stamp=1.0 + k) == 1
+        _read_step(n, out, k)
+        sd = n.scan_data()
+        out["s%d_scan_ranges" % k], out["s%d_scan_angles" % k], out["s%d_scan_max" % k] = sd
+    n.close()
+    return out
+
+
+def run_node_3d(O, lib, g, seed=33, params=PARAMS_3D, reference_cache=False):
+    out = {}
+    lib.ref_srand48(seed)
+    n = O.RefNode(params, map_type=3, lib=lib)
+    assert n.publish_octomap(0.1, g["keys"]) == 1
+    if reference_cache:
+        n.install_cache_3d(g["field"])
+    out["free_count"] = len(n.free_space())
+    out["init_samples"], out["init_state"] = n.samples(), n.drand48_state()
+    n.set_tf("base_link", "lidar", CLOUD_MOUNT[:3], O.yaw_quat(CLOUD_MOUNT[3]))
+    for k in range(N_STEPS):
+        x, y, yaw = truth_pose(k)
+        n.set_odom(x, y, yaw)
+        assert n.publish_cloud(g["s%d_cloud" % k], stamp=1.0 + k) == 1
+        _read_step(n, out, k)
+        out["s%d_points" % k] = n.cloud_data()
+    n.close()
+    return out
+
+
+def _read_step(n, out, k):
+    out["s%d_samples" % k] = n.samples()
+    out["s%d_state" % k] = n.drand48_state()
+    msg = n.last_pose()
+    out["s%d_pose_count" % k] = msg["count"] if msg else 0
+    if msg:
+        out["s%d_pose" % k] = np.concatenate([msg["position"], msg["orientation"]])
+        out["s%d_cov" % k] = msg["covariance"]
+    out["s%d_resample_count" % k] = n.state()["resample_count"]
+    info = n.filter_info()
+    out["s%d_leaf" % k], out["s%d_clusters" % k] = info["leaf_count"], info["cluster_count"]
+    out["s%d_averages" % k] = np.array([info["w_slow"], info["w_fast"]])
+    out["s%d_converged" % k] = int(info["converged"])

@@ -223,3 +223,79 @@ def test_gpu_init_gaussian_rotated_covariance_vs_reference_sampler(oracle_built,
     assert pf.drand48_state == rng.x
     assert np.abs(pf.samples()[:, :3] - want).max() <= 1e-12
     pf.close()
+
+
+# ------------------------------------------------------------------------------- the node itself, relinked
+def test_reference_node_replayed_from_golden_inputs_is_the_golden_run(oracle_built):
+    """run_node_2d / run_node_3d (the driver the relinked-node test below uses) on the all-reference library: bit-exact"""
+    O = oracle_built
+    if not O.have_ref():
+        pytest.skip("oracle/_ref not built (needs the reference checkout)")
+    for which, run in (("2d", nc.run_node_2d), ("3d", nc.run_node_3d)):
+        g = golden("node_%s.npz" % which)
+        out = run(O, O.ref_lib(), g)
+        for k, v in out.items():
+            if k in g:
+                assert np.array_equal(np.asarray(v), g[k], equal_nan=True), (which, k)
+        assert int(out["init_state"]) == int(g["init_state"])
+
+
+def _compare_relinked(out, g, pose_tol, same_particles):
+    assert int(out["init_state"]) == int(g["init_state"])                       # initWithGaussian x 2: same draws accepted
+    assert np.abs(out["init_samples"][:, :3] - g["init_samples"][:, :3]).max() <= 1e-12
+    for k in range(nc.N_STEPS):
+        s, w = out["s%d_samples" % k], g["s%d_samples" % k]
+        assert out["s%d_resample_count" % k] == int(g["s%d_resample_count" % k])   # the node's update / resample schedule
+        assert out["s%d_pose_count" % k] == int(g["s%d_pose_count" % k])           # ... and its publications
+        assert s.shape == w.shape
+        assert int(out["s%d_state" % k]) == int(g["s%d_state" % k])                # libc's drand48 stream stays in step
+        if same_particles is not None:
+            same = ((np.abs(s[:, :3] - w[:, :3]).max(axis=1) <= 1e-9) & np.isclose(s[:, 3], w[:, 3], rtol=2e-5, atol=1e-300)).mean()
+            assert same >= same_particles, (k, same)
+        if out["s%d_pose_count" % k]:
+            assert np.abs(out["s%d_pose" % k][:2] - g["s%d_pose" % k][:2]).max() <= pose_tol
+            if same_particles is not None:
+                assert np.allclose(out["s%d_cov" % k], g["s%d_cov" % k], rtol=1e-2, atol=1e-4)
+
+
+@pytest.mark.gpu
+def test_gpu_the_reference_node_relinked_against_the_cuda_library_2d(oracle_built, dev):
+    """The drop-in, executed: node/node.cpp + node_2d.cpp of the reference, unmodified, compiled against the mirror's
+    headers and linked with the mirror + libbamcl_cuda.so (oracle/_ref/libamcl_node_gpu.so), fed the golden run's messages.
+    Everything the node does itself (conversions, schedule) is identical; the filter underneath is the CUDA path with the
+    reference's cache installed (OccupancyMap::setDistancesLUT of the mirror): same draws, same schedule, >= 99.9 % of the
+    particles the reference's at every step (default fixed-point terms), published pose to a millimetre; and with the
+    DEVICE-built cache (exact EDT, DESIGN 4 - the plain drop-in): same draws and schedule, the pose within centimetres."""
+    O = oracle_built
+    if not O.have_node_gpu():
+        pytest.skip("oracle/_ref/libamcl_node_gpu.so not built (needs the reference checkout at build time)")
+    g = golden("node_2d.npz")
+    lib = O.node_gpu_lib()
+    out = nc.run_node_2d(O, lib, g)
+    assert lib.ref_node_last_device_error() == b""
+    assert np.array_equal(out["free"], g["free"])
+    for k in range(nc.N_STEPS):   # the node's own scan conversion (its tf2 / float arithmetic is the same object code path)
+        assert np.array_equal(out["s%d_scan_ranges" % k], g["s%d_scan_ranges" % k], equal_nan=True)
+        assert np.array_equal(out["s%d_scan_angles" % k], g["s%d_scan_angles" % k])
+    _compare_relinked(out, g, pose_tol=0.05, same_particles=None)
+    out = nc.run_node_2d(O, lib, g, reference_cache=True)
+    assert lib.ref_node_last_device_error() == b""
+    _compare_relinked(out, g, pose_tol=1e-3, same_particles=0.999)
+
+
+@pytest.mark.gpu
+def test_gpu_the_reference_node_relinked_against_the_cuda_library_3d(oracle_built, dev):
+    O = oracle_built
+    if not O.have_node_gpu():
+        pytest.skip("oracle/_ref/libamcl_node_gpu.so not built (needs the reference checkout at build time)")
+    g = golden("node_3d.npz")
+    lib = O.node_gpu_lib()
+    out = nc.run_node_3d(O, lib, g)
+    assert lib.ref_node_last_device_error() == b""
+    assert out["free_count"] == (int(g["mx"][0]) - int(g["mn"][0])) * (int(g["mx"][1]) - int(g["mn"][1]))
+    for k in range(nc.N_STEPS):
+        assert np.array_equal(out["s%d_points" % k], g["s%d_points" % k])
+    _compare_relinked(out, g, pose_tol=0.05, same_particles=None)
+    out = nc.run_node_3d(O, lib, g, reference_cache=True)
+    assert lib.ref_node_last_device_error() == b""
+    _compare_relinked(out, g, pose_tol=1e-3, same_particles=0.999)

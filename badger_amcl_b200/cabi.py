@@ -220,6 +220,7 @@ SIGNATURES = {
     "bamcl_pf_init_uniform": (_I, [_P, _P, _D, _D, C.c_uint64, _P, _P]),
     "bamcl_pf_init_uniform_3d": (_I, [_P, _P, _D, _D, C.c_uint64, _P, _P]),
     "bamcl_pf_init_gaussian": (_I, [_P, _P, _P, _P, C.c_uint64, _P, _P]),
+    "bamcl_pf_resample_multinomial_drawn": (_I, [_P, _P, _P, _P]),
     "bamcl_weights_normalise_noalloc": (_I, [_P, _P, _L, _P, _P]),
     "bamcl_pf_set_random_pose_source_3d": (_I, [_P, _P, _D, _D]),
     "bamcl_pose_covariance": (_I, [_P, _P]),
@@ -683,6 +684,25 @@ class ParticleFilter:
             _check(self.L.bamcl_pf_resample_host(self.h, C.byref(prm), C.byref(res), _p(out), len(out)))
         self.drand48_state = res.drand48_state
         self.random_next += res.random_poses_used
+        if w_diff > 0.0:
+            self.w_slow = self.w_fast = 0.0
+        self.converged = bool(res.converged)
+        self.last = res
+        return res
+
+    def update_resample_drawn(self, w_diff, draws, poses, states):
+        """multinomial updateResample with the branch loop of particle_filter.cpp:385-393 run by the caller
+        (bamcl_pf_resample_multinomial_drawn): draws[k] = second uniform of output k or -(1 + i) = poses[i]; states[k] = the
+        caller's generator state before output k (states[max_samples] = after the last): the state after the kept outputs
+        becomes this filter's drand48_state"""
+        draws = np.ascontiguousarray(draws, np.float64)
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 3)
+        assert len(draws) == self.max_samples and len(states) == self.max_samples + 1
+        prm = ResampleParams(0, self.min_samples, self.max_samples, self.pop_err, self.pop_z, w_diff, 0.5, self.conv_thresh,
+                             self.drand48_state, _p(poses) if len(poses) else None, len(poses))
+        res = ResampleResult()
+        _check(self.L.bamcl_pf_resample_multinomial_drawn(self.h, C.byref(prm), _p(draws), C.byref(res)))
+        self.drand48_state = int(states[res.sample_count])
         if w_diff > 0.0:
             self.w_slow = self.w_fast = 0.0
         self.converged = bool(res.converged)

@@ -53,6 +53,9 @@ struct MultiArgs
   double w_diff;
   int retries;  // generations thrown away per random pose (uniformPoseGenerator's de-weighting loop)
   PoseSource rp;
+  // host-drawn mode (bamcl_pf_resample_multinomial_drawn): output k's second uniform, or -(1 + i) = the i-th handed-over pose
+  const double* host_draws;
+  const double* host_poses;
 };
 
 __global__ void __launch_bounds__(256) k_select_multinomial(const MultiArgs a)
@@ -60,6 +63,23 @@ __global__ void __launch_bounds__(256) k_select_multinomial(const MultiArgs a)
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= a.n)
     return;
+  double r;
+  if (a.host_draws)
+  {
+    r = a.host_draws[k];
+    if (r < 0.0)
+    {
+      const long i = (long)(-r) - 1;  // random_pose_fn_() was called on the host for this output (:385-388)
+      a.src[k] = -1;
+      a.bx[k] = a.host_poses[3 * i];
+      a.by[k] = a.host_poses[3 * i + 1];
+      a.bth[k] = a.host_poses[3 * i + 2];
+      a.bw[k] = 1.0;
+      return;
+    }
+  }
+  else
+  {
   const unsigned long long p = a.pos ? (unsigned long long)a.pos[k] : 2ull * (unsigned long long)k;
   const unsigned long long x1 = lcg_skip(a.state0, p + 1ull);  // :385
   if (a.w_diff > 0.0 && (double)x1 * 0x1p-48 < a.w_diff)
@@ -74,7 +94,8 @@ __global__ void __launch_bounds__(256) k_select_multinomial(const MultiArgs a)
     return;
   }
   const unsigned long long x = lcg_next(x1);
-  const double r = scalbn((double)x, -48);  // drand48: X / 2^48, exact (:393)
+  r = scalbn((double)x, -48);  // drand48: X / 2^48, exact (:393)
+  }
   int L = 0, H = a.P;  // first i with c[i] <= r < c[i+1] == number of entries of c[1..P] that are <= r
   while (L < H)
   {
@@ -198,9 +219,12 @@ __global__ void k_fill_f64(double* __restrict__ p, double v, int n)
 
 namespace bamcl
 {
-int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res)
+// host_draws / host_poses (host pointers, or null): the draws were made on the host by the reference's own loop shape
+// (bamcl_pf_resample_multinomial_drawn); then nothing is drawn here and the generator state is returned unchanged
+int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res, const double* host_draws,
+                         const double* host_poses, long n_host_poses)
 {
-  const bool inject = prm->w_diff > 0.0;
+  const bool inject = prm->w_diff > 0.0 && !host_draws;
   PoseSource rp_src;
   if (inject && !pf_pose_source(pf, &rp_src))
     return set_error(BAMCL_E_UNSUPPORTED,
@@ -245,6 +269,18 @@ int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
   a.w_diff = 0.0;
   a.retries = 0;
   a.rp = PoseSource();
+  a.host_draws = a.host_poses = nullptr;
+  if (host_draws)
+  {
+    const size_t nd = (size_t)n, np3 = 3 * (size_t)std::max(n_host_poses, 0l);
+    BAMCL_TRY(pf->mn_buf.reserve(sizeof(double) * (nd + np3 + 1)));
+    double* d = pf->mn_buf.as<double>();
+    BAMCL_CUDA_OK(cudaMemcpyAsync(d, host_draws, sizeof(double) * nd, cudaMemcpyHostToDevice, ctx->stream));
+    if (np3)
+      BAMCL_CUDA_OK(cudaMemcpyAsync(d + nd, host_poses, sizeof(double) * np3, cudaMemcpyHostToDevice, ctx->stream));
+    a.host_draws = d;
+    a.host_poses = d + nd;
+  }
   int* d_pos = nullptr;
   if (inject)
   {
@@ -328,7 +364,17 @@ int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
   res->sample_count = count;
   res->random_poses_used = 0;
   res->status_flags = flags & 1;
-  unsigned long long consumed = 2ull * (unsigned long long)count;
+  unsigned long long consumed = host_draws ? 0ull : 2ull * (unsigned long long)count;
+  if (host_draws)
+  {
+    int* d_cnt = stop + 2;
+    int h = 0;
+    BAMCL_CUDA_OK(cudaMemsetAsync(d_cnt, 0, sizeof(int), ctx->stream));
+    BAMCL_LAUNCH(ctx, k_count_random, (count + 255) / 256, 256, 0, pf->src.as<int>(), count, d_cnt);
+    BAMCL_CUDA_OK(cudaMemcpyAsync(&h, d_cnt, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    BAMCL_CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    res->random_poses_used = h;
+  }
   if (inject)
   {
     int* d_cnt = stop + 2;

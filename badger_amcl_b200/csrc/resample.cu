@@ -1087,7 +1087,8 @@ static inline uint64_t drand48_next(uint64_t x) { return (0x5DEECE66DULL * x + 0
 
 namespace bamcl
 {
-int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res);  // multinomial.cu
+int resample_multinomial(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res, const double* host_draws,
+                         const double* host_poses, long n_host_poses);  // multinomial.cu
 int device_random_poses(bamcl_pf* pf, unsigned long long state0, int n, double* out3_dev,
                         unsigned long long* state_out);  // init.cu
 }
@@ -1176,6 +1177,30 @@ int bamcl_pf_resample_host(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl
   return resample_impl(pf, prm, res, aos_out, aos_capacity);
 }
 
+int bamcl_pf_resample_multinomial_drawn(bamcl_pf* pf, const bamcl_resample_params* prm, const double* draws,
+                                        bamcl_resample_result* res)
+{
+  if (!pf || !prm || !res || !draws)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_resample_multinomial_drawn: bad arguments");
+  if (prm->resample_systematic)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_resample_multinomial_drawn: the systematic model takes its random poses through "
+                                  "bamcl_resample_params::random_poses");
+  if (prm->max_samples > pf->max_samples || prm->max_samples <= 0)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_resample_multinomial_drawn: max_samples exceeds the filter's capacity");
+  if (pf_ranks(pf) > 1 || pf->win_cnt >= 0)
+    return set_error(BAMCL_E_STATE, "bamcl_pf_resample_multinomial_drawn: not available on a distributed / windowed filter");
+  if (prm->n_random_poses > 0 && !prm->random_poses)
+    return set_error(BAMCL_E_ARG, "bamcl_pf_resample_multinomial_drawn: random_poses missing");
+  for (int k = 0; k < prm->max_samples; k++)  // every -(1 + i) must name a handed-over pose
+    if (draws[k] < 0.0 && (long)(-draws[k]) - 1 >= prm->n_random_poses)
+      return set_error(BAMCL_E_ARG, "bamcl_pf_resample_multinomial_drawn: draws[%d] names pose %ld of %ld", k,
+                       (long)(-draws[k]) - 1, prm->n_random_poses);
+  memset(res, 0, sizeof(*res));
+  BAMCL_TRY(resample_multinomial(pf, prm, res, draws, prm->random_poses, prm->n_random_poses));
+  res->drand48_state = prm->drand48_state;  // nothing was drawn here
+  return BAMCL_OK;
+}
+
 static int resample_impl(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_resample_result* res, double* aos_out,
                          long aos_cap)
 {
@@ -1192,7 +1217,7 @@ static int resample_impl(bamcl_pf* pf, const bamcl_resample_params* prm, bamcl_r
     return set_error(BAMCL_E_STATE, "bamcl_pf_resample: a scoring window is set (bamcl_pf_set_window); clear it first");
   if (!prm->resample_systematic)
   {
-    BAMCL_TRY(resample_multinomial(pf, prm, res));
+    BAMCL_TRY(resample_multinomial(pf, prm, res, nullptr, nullptr, 0));
     if (aos_out)
     {
       if (res->sample_count > aos_cap)

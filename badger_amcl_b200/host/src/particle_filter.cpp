@@ -523,9 +523,44 @@ void ParticleFilter::updateResample()
   }
   else if (w_diff > 0.0)
   {
-    deviceFail("multinomial resampling with random-pose injection interleaves drand48 with random_pose_fn_ per sample "
-               "(particle_filter.cpp:385-393): register the node's pose source (setDevicePoseSource) to run it on the device");
-    return;  // the set is left as it was
+    // multinomial with an arbitrary host pose function (particle_filter.cpp:385-393): the branch loop runs here - it is the
+    // only part that cannot be replayed from the stream, the pose function draws from it too - and everything else on the
+    // device (bamcl_pf_resample_multinomial_drawn). libc's generator state is recorded before every output so that it can
+    // be put back to where the reference's loop stops (the KLD bound, :416).
+    std::vector<double> draws((size_t)max_samples_);
+    std::vector<uint64_t> state_before((size_t)max_samples_ + 1);
+    for (int k = 0; k < max_samples_; k++)
+    {
+      state_before[(size_t)k] = peekDrand48State();
+      if (drand48() < w_diff)
+      {
+        const Eigen::Vector3d p = random_pose_fn_();
+        random_poses.push_back(p[0]);
+        random_poses.push_back(p[1]);
+        random_poses.push_back(p[2]);
+        draws[(size_t)k] = -(double)(random_poses.size() / 3);
+      }
+      else
+        draws[(size_t)k] = drand48();
+    }
+    state_before[(size_t)max_samples_] = peekDrand48State();
+    prm.random_poses = random_poses.empty() ? nullptr : random_poses.data();
+    prm.n_random_poses = (long)(random_poses.size() / 3);
+    bamcl_resample_result res;
+    const bool ok = deviceOk(bamcl_pf_resample_multinomial_drawn(dev_, &prm, draws.data(), &res), "bamcl_pf_resample_multinomial_drawn");
+    const uint64_t st64 = state_before[ok ? (size_t)res.sample_count : 0];  // on failure: as if nothing had been drawn
+    unsigned short st[3] = {(unsigned short)(st64 & 0xFFFF), (unsigned short)((st64 >> 16) & 0xFFFF),
+                            (unsigned short)((st64 >> 32) & 0xFFFF)};
+    seed48(st);
+    if (!ok)
+      return;  // the set is left as it was
+    w_slow_ = w_fast_ = 0.0;
+    host_valid_ = false;
+    host_dirty_ = false;
+    installStats(&res);
+    set_->converged = res.converged;
+    converged_ = res.converged != 0;
+    return;
   }
   prm.random_poses = random_poses.empty() ? nullptr : random_poses.data();
   prm.n_random_poses = (long)(random_poses.size() / 3);

@@ -246,6 +246,17 @@ int bamcl_pf_resample(bamcl_pf* pf, const bamcl_resample_params* params, bamcl_r
  * aos_out holds aos_capacity PFSample; result->sample_count of them are written. */
 int bamcl_pf_resample_host(bamcl_pf* pf, const bamcl_resample_params* params, bamcl_resample_result* result, double* aos_out,
                            long aos_capacity);
+/* resampleMultinomial (particle_filter.cpp:356-421) with w_diff > 0 and an ARBITRARY host random_pose_fn_: the reference
+ * interleaves, per output, drand48() < w_diff ? random_pose_fn_() : drand48() (:385-393) - the pose function draws from the
+ * same stream in between, so the device cannot replay the stream on its own. The HOST runs exactly that branch loop for
+ * max_samples outputs (calling its pose function, recording libc's generator state before every output) and hands over
+ * draws[k] = the second uniform of output k (:393), or -(1 + i) when output k is the i-th pose of params->random_poses.
+ * The device does the rest in parallel: CDF, look-ups, candidate tree, the KLD stop (:416), clusters, statistics.
+ * result->sample_count = m outputs were kept: the host restores the generator state it recorded before output m, so libc's
+ * stream ends where the sequential loop would have left it; result->random_poses_used = how many of the m are random
+ * poses; result->drand48_state = params->drand48_state (nothing is drawn on the device). */
+int bamcl_pf_resample_multinomial_drawn(bamcl_pf* pf, const bamcl_resample_params* params, const double* draws,
+                                        bamcl_resample_result* result);
 /* kd-tree + cluster statistics of the CURRENT set as initWithPoseFn/initWithGaussian compute them
  * (particle_filter.cpp:106-162): fills leaf_count, node_count, cluster_count, mean, cov. */
 int bamcl_pf_init_stats(bamcl_pf* pf, bamcl_resample_result* result);
@@ -426,8 +437,9 @@ int bamcl_pf_init_gaussian(bamcl_pf* pf, const double* mean3, const double* cr9,
  * registers `map`'s free-space list (bamcl_map2d_update_free_space) and the generator's two parameters, so that
  * multinomial resampling with w_diff > 0 (particle_filter.cpp:385-388) draws its random poses on the device from the
  * same drand48 stream, in the reference's order; the systematic model (:309-324) does the same when
- * bamcl_resample_params::random_poses is NULL (start draw first, then the poses). NULL map = no source (that case is then BAMCL_E_UNSUPPORTED). The map
- * must outlive the filter or be unregistered first. */
+ * bamcl_resample_params::random_poses is NULL (start draw first, then the poses). NULL map = no source (bamcl_pf_resample then
+ * reports that case as BAMCL_E_UNSUPPORTED; a caller with an opaque host pose function uses
+ * bamcl_pf_resample_multinomial_drawn). The map must outlive the filter or be unregistered first. */
 int bamcl_pf_set_random_pose_source(bamcl_pf* pf, bamcl_map2d* map_or_null, double starting_weight_threshold,
                                     double deweight_multiplier);
 /* the 3-D node's pose function (the OctoMap's cropped cell rectangle); replaces a 2-D source and vice versa */

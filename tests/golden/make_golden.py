@@ -43,6 +43,10 @@ def node_runs():
     import node_chain
     np.savez_compressed(os.path.join(HERE, "node_2d.npz"), **node_chain.record_2d(O))
     np.savez_compressed(os.path.join(HERE, "node_3d.npz"), **node_chain.record_3d(O))
+    # the node's default resampler + recovery, a kidnapped robot: random poses injected by the node's own pose function
+    g = node_chain.record_2d(O, seed=44, params=node_chain.PARAMS_2D_MN, kidnap_from=3)
+    g.pop("brushfire")  # the same map as node_2d.npz
+    np.savez_compressed(os.path.join(HERE, "node_2d_mn.npz"), **g)
 
 
 def main():

@@ -92,13 +92,21 @@ def _record_step(n, g, k):
     g["s%d_max_weight" % k] = np.concatenate([[mw[0]], mw[1]]) if mw else np.zeros(0)
 
 
-def record_2d(O, seed=21):
+# the node's default resampler (multinomial) with augmented-MCL recovery switched on, and a robot that is carried away after
+# step 2 (the scans come from somewhere else than the odometry says): w_fast drops below w_slow and updateResample injects
+# random poses through the node's own pose function, interleaved with the resampler's draws (particle_filter.cpp:385-393)
+PARAMS_2D_MN = dict(PARAMS_2D, resample_model_type="multinomial", recovery_alpha_slow=0.05, recovery_alpha_fast=0.9,
+                    min_particles=200, max_particles=1000)
+KIDNAP = (1.6, -1.2, 0.9)   # added to the true pose the scans are taken from, steps 3..5
+
+
+def record_2d(O, seed=21, params=None, kidnap_from=None):
     """run the 2-D scenario through the compiled node; returns the golden dict"""
     L = O.ref_lib()
     data = grid_world()
     g = dict(data=data)
     L.ref_srand48(seed)
-    n = O.RefNode(PARAMS_2D, map_type=2)
+    n = O.RefNode(params or PARAMS_2D, map_type=2)
     assert n.publish_map(data, RES_MSG, ORIGIN) == 1
     m = n.map2d()
     g["brushfire"] = m.get_distances()
@@ -114,6 +122,8 @@ def record_2d(O, seed=21):
         x, y, yaw = truth_pose(k)
         n.set_odom(x, y, yaw)
         # what a laser at the true pose would see in this map, float32 like the message, a little noise, some drop-outs
+        if kidnap_from is not None and k >= kidnap_from:
+            x, y, yaw = x + KIDNAP[0], y + KIDNAP[1], yaw + KIDNAP[2]
         sx = x + MOUNT[0] * np.cos(yaw) - MOUNT[1] * np.sin(yaw)
         sy = y + MOUNT[0] * np.sin(yaw) + MOUNT[1] * np.cos(yaw)
         b = yaw + MOUNT[3] + SCAN["angle_min"] + SCAN["angle_increment"] * np.arange(SCAN["beams"])
@@ -194,7 +204,7 @@ class PortBackend2D:
         self.geometry = (res, (float(org[0]), float(org[1])))
         self.free = self.map.free_space(0.0)
         self.pf = O.PortPF(p["min_particles"], p["max_particles"], p["recovery_alpha_slow"], p["recovery_alpha_fast"], 95.0,
-                           systematic=True, pop_err=p["kld_err"], pop_z=p["kld_z"])
+                           systematic=p["resample_model_type"] == "systematic", pop_err=p["kld_err"], pop_z=p["kld_z"])
         self.pf.set_uniform_pose_source(self.map, self.free)
         self.model = O.planar_model(model_type=O.MODEL_LF, max_beams=p["laser_max_beams"], z_hit=p["laser_z_hit"],
                                     z_rand=p["laser_z_rand"], sigma_hit=p["laser_sigma_hit"],
@@ -286,7 +296,7 @@ class PortBackend3D:
         self.map = O.PortMap3D(0.1, g["keys"], p["laser_likelihood_max_dist"])
         self.map.update_distances()
         self.pf = O.PortPF(p["min_particles"], p["max_particles"], p["recovery_alpha_slow"], p["recovery_alpha_fast"], 95.0,
-                           systematic=True, pop_err=p["kld_err"], pop_z=p["kld_z"])
+                           systematic=p["resample_model_type"] == "systematic", pop_err=p["kld_err"], pop_z=p["kld_z"])
         self.model = O.cloud_model(model_type=1, max_beams=p["laser_max_beams"], z_hit=p["laser_z_hit"],
                                    z_rand=p["laser_z_rand"], sigma_hit=p["laser_sigma_hit"],
                                    gompertz=(p["laser_gompertz_a"], p["laser_gompertz_b"], p["laser_gompertz_c"],
@@ -387,7 +397,7 @@ class CudaBackend2D:
             self.map.build_distances(p["laser_likelihood_max_dist"])
         self.map.update_free_space(0.0)
         self.pf = cabi.ParticleFilter(ctx, p["min_particles"], p["max_particles"], p["recovery_alpha_slow"],
-                                      p["recovery_alpha_fast"], 95.0, systematic=True, pop_err=p["kld_err"], pop_z=p["kld_z"])
+                                      p["recovery_alpha_fast"], 95.0, systematic=p["resample_model_type"] == "systematic", pop_err=p["kld_err"], pop_z=p["kld_z"])
         self.pf.set_random_pose_source(self.map)
         self.pf.set_exact_terms(exact_terms)
         self.model = cabi.planar_model(model_type=1, max_beams=p["laser_max_beams"], z_hit=p["laser_z_hit"],
@@ -438,7 +448,7 @@ class CudaBackend3D(CudaBackend2D):
         else:
             self.map.build_distances()
         self.pf = cabi.ParticleFilter(ctx, p["min_particles"], p["max_particles"], p["recovery_alpha_slow"],
-                                      p["recovery_alpha_fast"], 95.0, systematic=True, pop_err=p["kld_err"], pop_z=p["kld_z"])
+                                      p["recovery_alpha_fast"], 95.0, systematic=p["resample_model_type"] == "systematic", pop_err=p["kld_err"], pop_z=p["kld_z"])
         self.pf.set_random_pose_source(self.map)
         q = (0.0, 0.0, float(np.sin(0.5 * CLOUD_MOUNT[3])), float(np.cos(0.5 * CLOUD_MOUNT[3])))
         self.model = cabi.cloud_model(model_type=1, max_beams=p["laser_max_beams"], z_hit=p["laser_z_hit"],
@@ -479,6 +489,10 @@ def run_node_2d(O, lib, g, seed=21, params=PARAMS_2D, reference_cache=False):
         out["s%d_scan_ranges" % k], out["s%d_scan_angles" % k], out["s%d_scan_max" % k] = sd
     n.close()
     return out
+
+
+def run_node_2d_mn(O, lib, g, reference_cache=False):
+    return run_node_2d(O, lib, g, seed=44, params=PARAMS_2D_MN, reference_cache=reference_cache)
 
 
 def run_node_3d(O, lib, g, seed=33, params=PARAMS_3D, reference_cache=False):

@@ -322,6 +322,66 @@ def test_resample_with_device_pose_source_matches_oracle(env, n, n_min, w_fast, 
     m.close()
 
 
+@pytest.mark.parametrize("n,n_min,w_fast,stream_poses", [(3000, 100, 0.7, True), (20000, 500, 0.95, True), (20000, 50, 0.3, False),
+                                                         (1, 1, 0.5, True), (5000, 100, 0.0, False)])
+def test_multinomial_with_host_drawn_branches_matches_oracle(env, n, n_min, w_fast, stream_poses):
+    """bamcl_pf_resample_multinomial_drawn: the caller runs the branch loop of particle_filter.cpp:385-393 with ITS pose
+    function - one that draws from the same drand48 stream (the node's generator) or one that does not (a queue) - and hands
+    the draws over; sources, poses, count, tree, clusters bit for bit against the sequential loop, and the generator state
+    the caller restores (recorded before the first output that was not kept) is where the sequential loop stops"""
+    O, cabi = env["O"], env["cabi"]
+    C = O.C
+    cells = synth.make_grid(300, 200, seed=7, wall_every=60)
+    pm = O.PortMap2D(cells, RES, (0.5, -0.25))
+    pm.update_distances(2.0)
+    fs = pm.free_space(0.1)
+    poses = synth.gaussian_poses((0.5, 0.3, 0.2), n, seed=2, sigma_xy=0.3)
+    queue = synth.uniform_free_poses(cells, RES, 2 * n + 8, seed=9)
+    rng = np.random.default_rng(n + n_min)
+    port = O.PortPF(n_min, n, systematic=False)
+    port.init_with_poses(poses)
+    if stream_poses:
+        port.set_uniform_pose_source(pm, fs, 0.0, 0.0)
+    port.srand48(31)
+    pf = cabi.ParticleFilter(env["ctx"], n_min, n, systematic=False)
+    pf.init_with_poses(poses)
+    pf.srand48(31)
+    L = O.port_lib()
+    used = 0
+    for _ in range(2):
+        k = port.sample_count()
+        w = np.exp(rng.normal(0.0, 1.0, k))
+        w /= w.sum()
+        s = port.samples()
+        s[:, 3] = w
+        port.set_samples(s)
+        port.set_averages(1.0, w_fast)
+        pf.upload_samples(s)
+        w_diff = max(0.0, 1.0 - w_fast / 1.0)
+        if not stream_poses:
+            port.set_random_poses(queue[used:])
+        # the caller's loop (what the host mirror does), on a copy of the generator
+        g = O.Rng(pf.drand48_state)
+        draws, rp, states = np.empty(n), [], np.empty(n + 1, np.uint64)
+        for i in range(n):
+            states[i] = g.x
+            if L.orc_drand48(C.byref(g)) < w_diff:
+                rp.append(pm.uniform_poses(fs, g, 1)[0] if stream_poses else queue[used + len(rp)])
+                draws[i] = -float(len(rp))
+            else:
+                draws[i] = L.orc_drand48(C.byref(g))
+        states[n] = g.x
+        port.update_resample()
+        r = pf.update_resample_drawn(w_diff, draws, np.array(rp).reshape(-1, 3), states)
+        _assert_same_resample(pf, port, r)
+        assert r.random_poses_used == int((port.resample_sources() < 0).sum())
+        assert pf.drand48_state == port.rng.x
+        used += r.random_poses_used
+        if 0.0 < w_fast < 1.0 and n > 100:
+            assert r.random_poses_used > 0
+    pf.close()
+
+
 def test_multinomial_with_random_injection_is_refused(env):
     cabi = env["cabi"]
     n = 1000

@@ -14,7 +14,10 @@ import node_chain as nc  # noqa: E402
 
 
 def golden(name):
-    return dict(np.load(os.path.join(HERE, "golden", name)))
+    g = dict(np.load(os.path.join(HERE, "golden", name)))
+    if name == "node_2d_mn.npz":   # the same map message as node_2d.npz: its cache is stored once
+        g["brushfire"] = np.load(os.path.join(HERE, "golden", "node_2d.npz"))["brushfire"]
+    return g
 
 
 def exact(bad):
@@ -35,6 +38,17 @@ def test_restated_chain_2d_is_the_node_bit_for_bit(oracle_built):
     assert bad == []
 
 
+def test_restated_chain_2d_multinomial_with_recovery_is_the_node_bit_for_bit(oracle_built):
+    """the node's default resampler with augmented-MCL recovery and a kidnapped robot: updateResample injects poses from
+    the node's own generator, interleaved with the resampler's draws (particle_filter.cpp:385-393)"""
+    O, g = oracle_built, golden("node_2d_mn.npz")
+    assert (g["s3_averages"] == 0.0).all() and int(g["s3_clusters"]) > 50        # the injection happened
+    b = nc.PortBackend2D(O, g, nc.PARAMS_2D_MN)
+    bad = []
+    nc.replay_2d(b, g, exact(bad), nc.PARAMS_2D_MN)
+    assert bad == []
+
+
 def test_restated_chain_3d_is_the_node_bit_for_bit(oracle_built):
     O, g = oracle_built, golden("node_3d.npz")
     b = nc.PortBackend3D(O, g)
@@ -46,13 +60,14 @@ def test_restated_chain_3d_is_the_node_bit_for_bit(oracle_built):
     assert bad == []
 
 
-@pytest.mark.parametrize("which", ["2d", "3d"])
+@pytest.mark.parametrize("which", ["2d", "3d", "2d_mn"])
 def test_committed_golden_is_what_the_compiled_node_produces(oracle_built, which):
     O = oracle_built
     if not O.have_ref():
         pytest.skip("oracle/_ref not built (needs the reference checkout)")
     g = golden("node_%s.npz" % which)
-    fresh = nc.record_2d(O) if which == "2d" else nc.record_3d(O)
+    fresh = (nc.record_2d(O) if which == "2d" else nc.record_3d(O) if which == "3d" else
+             nc.record_2d(O, seed=44, params=nc.PARAMS_2D_MN, kidnap_from=3))
     assert sorted(fresh) == sorted(g)
     for k in g:
         assert np.array_equal(np.asarray(fresh[k]), g[k], equal_nan=np.asarray(g[k]).dtype.kind == "f"), k
@@ -231,7 +246,7 @@ def test_reference_node_replayed_from_golden_inputs_is_the_golden_run(oracle_bui
     O = oracle_built
     if not O.have_ref():
         pytest.skip("oracle/_ref not built (needs the reference checkout)")
-    for which, run in (("2d", nc.run_node_2d), ("3d", nc.run_node_3d)):
+    for which, run in (("2d", nc.run_node_2d), ("3d", nc.run_node_3d), ("2d_mn", nc.run_node_2d_mn)):
         g = golden("node_%s.npz" % which)
         out = run(O, O.ref_lib(), g)
         for k, v in out.items():
@@ -281,6 +296,34 @@ def test_gpu_the_reference_node_relinked_against_the_cuda_library_2d(oracle_buil
     out = nc.run_node_2d(O, lib, g, reference_cache=True)
     assert lib.ref_node_last_device_error() == b""
     _compare_relinked(out, g, pose_tol=1e-3, same_particles=0.999)
+
+
+@pytest.mark.gpu
+def test_gpu_chain_2d_multinomial_with_recovery_vs_the_node(dev):
+    """the C ABI driven in the node's order, random poses from the registered device pose source (exact terms: every
+    resampled / injected particle the reference's, generator state exact)"""
+    g = golden("node_2d_mn.npz")
+    b = nc.CudaBackend2D(dev["cabi"], dev["ctx"], g, nc.PARAMS_2D_MN, exact_terms=True)
+    bad = []
+    nc.replay_2d(b, g, tolerant(bad, 1e-9, 1.0), nc.PARAMS_2D_MN)
+    b.close()
+    assert bad == []
+
+
+@pytest.mark.gpu
+def test_gpu_the_reference_node_relinked_multinomial_with_recovery(oracle_built, dev):
+    """the relinked node with its DEFAULT resampler and recovery on: the mirror runs the branch loop of
+    particle_filter.cpp:385-393 on the host (the node's pose function is an opaque std::function that draws from the same
+    stream) and everything else on the device (bamcl_pf_resample_multinomial_drawn)"""
+    O = oracle_built
+    if not O.have_node_gpu():
+        pytest.skip("oracle/_ref/libamcl_node_gpu.so not built (needs the reference checkout at build time)")
+    g = golden("node_2d_mn.npz")
+    lib = O.node_gpu_lib()
+    out = nc.run_node_2d_mn(O, lib, g, reference_cache=True)
+    assert lib.ref_node_last_device_error() == b""
+    assert (out["s3_averages"] == 0.0).all() and int(out["s3_clusters"]) > 50   # random poses were injected here too
+    _compare_relinked(out, g, pose_tol=2e-3, same_particles=0.995)
 
 
 @pytest.mark.gpu

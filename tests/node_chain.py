@@ -528,3 +528,56 @@ def _read_step(n, out, k):
     out["s%d_leaf" % k], out["s%d_clusters" % k] = info["leaf_count"], info["cluster_count"]
     out["s%d_averages" % k] = np.array([info["w_slow"], info["w_fast"]])
     out["s%d_converged" % k] = int(info["converged"])
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+# A second scenario for the two node builds, exercising the node's other entry points live (no golden: on the GPU box both
+# libraries are present and run the same inputs in the same process): likelihood_field_prob with beam skipping, the
+# global_localization service, an /initialpose message and a dynamic reconfigure that swaps the filter and the model.
+PARAMS_EVENTS = dict(PARAMS_2D, laser_model_type="likelihood_field_prob", do_beamskip=1, beam_skip_distance=0.5,
+                     beam_skip_threshold=0.3, min_particles=200, max_particles=1200, resample_interval=1,
+                     recovery_alpha_slow=0.001, recovery_alpha_fast=0.1)
+
+
+def run_events_2d(O, lib, g, seed=77, cache=None):
+    """g: the node_2d golden (map + scans are reused as inputs); returns a list of per-scan records"""
+    rec = []
+    lib.ref_srand48(seed)
+    n = O.RefNode(PARAMS_EVENTS, map_type=2, lib=lib)
+    assert n.publish_map(g["data"], RES_MSG, ORIGIN) == 1
+    if cache is not None:
+        n.install_cache_2d(cache, PARAMS_EVENTS["laser_likelihood_max_dist"])
+    n.set_tf("base_link", "laser", MOUNT[:3], O.yaw_quat(MOUNT[3]))
+    stamp = [1.0]
+
+    def scan(k, label):
+        x, y, yaw = truth_pose(k)
+        n.set_odom(x, y, yaw)
+        assert n.publish_scan(g["s%d_ranges" % k], SCAN["angle_min"], SCAN["angle_increment"], SCAN["range_min"],
+                              SCAN["range_max"], stamp=stamp[0]) == 1
+        stamp[0] += 1.0
+        msg, st, info = n.last_pose(), n.state(), n.filter_info()
+        rec.append(dict(label=label, samples=n.samples(), state=n.drand48_state(), pose_count=msg["count"] if msg else 0,
+                        pose=np.concatenate([msg["position"], msg["orientation"]]) if msg else None,
+                        resample_count=st["resample_count"], gl_active=st["global_localization_active"],
+                        converged=info["converged"], clusters=info["cluster_count"]))
+
+    scan(0, "start")
+    scan(1, "tracking")
+    assert n.global_localization() == 1                       # Node::globalLocalizationCallback -> initWithPoseFn
+    scan(2, "global 1")
+    scan(3, "global 2")
+    cov = np.zeros(36)
+    cov[0], cov[7], cov[35] = 0.04, 0.09, 0.01
+    tx, ty, tyaw = truth_pose(3)
+    assert n.publish_initial_pose(tx + 0.05, ty - 0.05, tyaw + 0.02, cov, stamp=stamp[0]) == 1   # -> initWithGaussian
+    scan(4, "initialpose 1")
+    scan(5, "initialpose 2")
+    assert n.reconfigure(dict(laser_model_type="likelihood_field", laser_max_beams=40, max_particles=900,
+                              update_min_d=0.1)) == 0       # Node::reconfigureCB: new filter, new model
+    if cache is not None:
+        pass                                                  # the map object (and its cache) survives a reconfigure
+    scan(4, "reconfigured 1")
+    scan(5, "reconfigured 2")
+    n.close()
+    return rec

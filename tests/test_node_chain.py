@@ -342,3 +342,29 @@ def test_gpu_the_reference_node_relinked_against_the_cuda_library_3d(oracle_buil
     out = nc.run_node_3d(O, lib, g, reference_cache=True)
     assert lib.ref_node_last_device_error() == b""
     _compare_relinked(out, g, pose_tol=1e-3, same_particles=0.999)
+
+
+@pytest.mark.gpu
+def test_gpu_relinked_node_events_against_the_reference_node_live(oracle_built, dev):
+    """both node builds in one process on the same inputs: likelihood_field_prob + beam skipping, the global_localization
+    service (initWithPoseFn through the node's generator), an /initialpose message (initWithGaussian) and a dynamic
+    reconfigure (new filter, new model). Same schedule, same set sizes, libc's drand48 stream in step after every scan,
+    nearly all particles identical, poses to millimetres."""
+    O = oracle_built
+    if not (O.have_node_gpu() and O.have_ref()):
+        pytest.skip("needs oracle/_ref/libamcl_ref.so and libamcl_node_gpu.so (built where the reference checkout exists)")
+    g = golden("node_2d.npz")
+    want = nc.run_events_2d(O, O.ref_lib(), g)
+    lib = O.node_gpu_lib()
+    got = nc.run_events_2d(O, lib, g, cache=g["brushfire"])
+    assert lib.ref_node_last_device_error() == b""
+    assert [r["label"] for r in got] == [r["label"] for r in want]
+    for a, b in zip(got, want):
+        what = a["label"]
+        assert (a["resample_count"], a["pose_count"], a["gl_active"]) == (b["resample_count"], b["pose_count"], b["gl_active"]), what
+        assert a["samples"].shape == b["samples"].shape, what
+        assert a["state"] == b["state"], what
+        same = (np.abs(a["samples"][:, :3] - b["samples"][:, :3]).max(axis=1) <= 1e-9).mean()
+        assert same >= 0.99, (what, same)
+        assert np.abs(a["pose"][:2] - b["pose"][:2]).max() <= 5e-3, what
+        assert a["converged"] == b["converged"], what

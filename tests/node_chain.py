@@ -581,3 +581,43 @@ def run_events_2d(O, lib, g, seed=77, cache=None):
     scan(5, "reconfigured 2")
     n.close()
     return rec
+
+
+PARAMS_EVENTS_3D = dict(PARAMS_3D, wait_for_occupancy_map=1, laser_model_type="likelihood_field", resample_interval=1,
+                        min_particles=150, max_particles=600)
+
+
+def run_events_3d(O, lib, g, seed=88, cache=None):
+    """3-D: the OctoMap waits for the occupancy map's bounds (Node3D::occupancyMapMsgReceived -> setMapBounds, node_3d.cpp:
+    178-197), clouds, the global_localization service over the cropped cell rectangle, clouds again. g: the node_3d golden."""
+    rec = []
+    lib.ref_srand48(seed)
+    n = O.RefNode(PARAMS_EVENTS_3D, map_type=3, lib=lib)
+    assert n.publish_octomap(0.1, g["keys"]) == 1
+    rec.append(dict(label="octomap only", free=len(n.free_space())))
+    assert n.publish_map(np.zeros((50, 60), np.int8), 0.1, (0.0, 0.0)) >= 1     # 6 m x 5 m bounds
+    rec.append(dict(label="bounds", free=len(n.free_space())))
+    if lib is O.ref_lib():
+        rec[-1]["field"] = n.map3d().dense()      # the reference's cache over the cropped volume
+    if cache is not None:
+        n.install_cache_3d(cache)
+    n.set_tf("base_link", "lidar", CLOUD_MOUNT[:3], O.yaw_quat(CLOUD_MOUNT[3]))
+    stamp = [1.0]
+
+    def cloud(k, label):
+        x, y, yaw = truth_pose(k)
+        n.set_odom(x, y, yaw)
+        assert n.publish_cloud(g["s%d_cloud" % k], stamp=stamp[0]) == 1
+        stamp[0] += 1.0
+        msg, st = n.last_pose(), n.state()
+        rec.append(dict(label=label, samples=n.samples(), state=n.drand48_state(), pose_count=msg["count"] if msg else 0,
+                        pose=np.concatenate([msg["position"], msg["orientation"]]) if msg else None,
+                        resample_count=st["resample_count"], gl_active=st["global_localization_active"]))
+
+    cloud(0, "start")
+    cloud(1, "tracking")
+    assert n.global_localization() == 1
+    cloud(2, "global 1")
+    cloud(3, "global 2")
+    n.close()
+    return rec

@@ -368,3 +368,26 @@ def test_gpu_relinked_node_events_against_the_reference_node_live(oracle_built, 
         assert same >= 0.99, (what, same)
         assert np.abs(a["pose"][:2] - b["pose"][:2]).max() <= 5e-3, what
         assert a["converged"] == b["converged"], what
+
+
+@pytest.mark.gpu
+def test_gpu_relinked_node_3d_events_against_the_reference_node_live(oracle_built, dev):
+    """3-D twin: OctoMap cropped to the occupancy map's bounds (setMapBounds), the free-space rectangle, clouds, the
+    global_localization service, clouds again - both node builds live on the same inputs"""
+    O = oracle_built
+    if not (O.have_node_gpu() and O.have_ref()):
+        pytest.skip("needs oracle/_ref/libamcl_ref.so and libamcl_node_gpu.so (built where the reference checkout exists)")
+    g = golden("node_3d.npz")
+    want = nc.run_events_3d(O, O.ref_lib(), g)
+    lib = O.node_gpu_lib()
+    got = nc.run_events_3d(O, lib, g, cache=want[1]["field"])
+    assert lib.ref_node_last_device_error() == b""
+    assert (got[0]["free"], got[1]["free"]) == (want[0]["free"], want[1]["free"])
+    for a, b in zip(got[2:], want[2:]):
+        what = a["label"]
+        assert (a["resample_count"], a["pose_count"], a["gl_active"]) == (b["resample_count"], b["pose_count"], b["gl_active"]), what
+        assert a["samples"].shape == b["samples"].shape, what
+        assert a["state"] == b["state"], what
+        same = (np.abs(a["samples"][:, :3] - b["samples"][:, :3]).max(axis=1) <= 1e-9).mean()
+        assert same >= 0.99, (what, same)
+        assert np.abs(a["pose"][:2] - b["pose"][:2]).max() <= 5e-3, what

@@ -1,8 +1,7 @@
-# full single-GPU check on the GPU box: smoke, GPU tests, the bench line with all legs, launch list
+# full single-GPU check on the GPU box: smoke, GPU tests, the bench line with all legs
 set -x
 cd $GRAFT_REPO_ROOT
 (time python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -3) > gpurun_out/check_smoke.log 2>&1
 (time python -m pytest tests -m gpu -x -q 2>&1 | tail -8) > gpurun_out/check_pytest.log 2>&1
-(time python bench.py --steps 20 --warmup 3 > gpurun_out/check_bench.json 2> gpurun_out/check_bench.err) > gpurun_out/check_bench.time 2>&1
-ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file gpurun_out/check_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --legs none > gpurun_out/check_ncu.log 2>&1
+(time python bench.py --steps 20 --warmup 3 --legs none > gpurun_out/check_bench.json 2> gpurun_out/check_bench.err) > gpurun_out/check_bench.time 2>&1
 echo done

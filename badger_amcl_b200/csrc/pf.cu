@@ -693,7 +693,15 @@ int bamcl_pf_update_planar_host(bamcl_pf* pf, bamcl_map2d* map, const bamcl_plan
   if (!pf || !aos || n < 0 || n > pf->max_samples)
     return set_error(BAMCL_E_ARG, "bamcl_pf_update_planar_host: need 0 <= n <= max_samples");
   const bool skip = model && model->model_type == BAMCL_PLANAR_LF_PROB && model->do_beamskip && converged;
-  constexpr int CHUNKS = 4;
+  // chunks of the upload pipeline (1..7; BAMCL_HOST_CHUNKS overrides). Measured at 1M x 1080 (profiles/r02_e2e_chunks.txt):
+  // update half 1.96 / 1.71 / 1.74 / 1.91 / 1.82 ms with 1 / 2 / 4 / 6 / 7 chunks - every chunk is one more launch of the
+  // scoring kernel with its table prologue. Queueing the chunk copies BEFORE the scan is staged was tried and is slower
+  // (2.06 ms): the scan's small copies then wait behind the chunks on the one host-to-device copy engine.
+  static const int CHUNKS = [] {
+    const char* e = getenv("BAMCL_HOST_CHUNKS");
+    const int v = e ? atoi(e) : 4;
+    return v < 1 ? 1 : (v > 7 ? 7 : v);
+  }();
   if (n < 4 * 65536 || skip || (model && model->model_type == BAMCL_PLANAR_BEAM) || (model && model->max_beams < 2))
   {
     // small sets, and models that look at the whole set before weighting it: upload, then update

@@ -567,6 +567,8 @@ def run_b200_arm(a):
         t_rs = ctx.timer_stop_ms()
         return t_up, t_rs, k_ms, r
 
+    e2e_split = []  # wall ms of the update half of every single-GPU e2e step
+
     def step_e2e():
         restore()
         ctx.flush_l2()
@@ -577,6 +579,7 @@ def run_b200_arm(a):
             # H2D: P x 32 B AoS from pinned host memory (chunks, scored while the next chunk is on the bus) + the scan;
             # D2H: total
             pf.update_sensor_host(m, model, ranges, angles, RANGE_MAX, aos)
+            e2e_split.append((time.perf_counter() - t0) * 1e3)  # the update call returns with the total on the host
             # D2H: result struct + n x 32 B AoS of the new set (copied while the pose-bin tree is built)
             r = pf.update_resample(out=out_aos)
             n = r.sample_count
@@ -697,7 +700,8 @@ def run_b200_arm(a):
                        "motion_update_ms_not_in_metric": motion_ms},
             "e2e": {"value": e_value, "unit": "evals/s", "ms_per_step": e_total_ms / a.steps,
                     "h2d_bytes_per_step": int(cnt0 * 32 + 2 * B * 8) * world,
-                    "d2h_bytes_per_step": int(n_out * 32 + 8 + 96) * world},
+                    "d2h_bytes_per_step": int(n_out * 32 + 8 + 96) * world,
+                    "update_ms": (float(np.mean(e2e_split[-a.steps:])) if e2e_split else None)},
             "gpu_launches": int(launches_timed),
             "roofline": {"kernel": "k_score_lf", "bound": "hbm", "bound_note": "HBM fraction as the contract asks; the kernel's "
                          "field is L2-resident and its real roof is the L2 gather rate, see l2_gather", "achieved": achieved, "peak": peak, "unit": "GB/s",

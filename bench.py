@@ -166,6 +166,47 @@ class CpuArm:
         return t1 - t0, t2 - t1
 
 
+def parallel_update_bound(a, arm, cells, threads):
+    """SURVEY 8d's "embarrassingly parallel upper bound": the reference has no threads, but its UPDATE is independent per
+    particle, so the same object code run by `threads` host threads on disjoint particle shards (each with its own map,
+    scanner and filter objects: the classes keep member scratch and are not re-entrant) bounds what a threaded port of
+    the update could reach on this host. The resample is one global sequential pass and stays single-threaded.
+    Returns the update's wall seconds for arm.n particles, or None."""
+    import threading
+    O = arm.O
+    if arm.kind != "reference" or threads < 2:
+        return None
+    cache = arm.map.get_distances()
+    shards = np.array_split(arm.poses, threads)
+    workers = []
+    for sh in shards:
+        if len(sh) == 0:
+            continue
+        m = O.RefMap2D(cells, RES)
+        m.set_distances(cache, 2.0)
+        sc = O.RefScanner2D(m, arm.model)
+        pf = O.RefPF(max(1, len(sh) // 10), len(sh))
+        pf.init_with_poses(sh)
+        workers.append((m, sc, pf))
+    gate = threading.Barrier(len(workers) + 1)
+
+    def work(w):
+        gate.wait()
+        w[2].update_sensor(w[1], arm.ranges, arm.angles, RANGE_MAX)  # ctypes releases the GIL for the call
+        gate.wait()
+
+    ts = [threading.Thread(target=work, args=(w,)) for w in workers]
+    for t in ts:
+        t.start()
+    gate.wait()
+    t0 = time.perf_counter()
+    gate.wait()
+    dt = time.perf_counter() - t0
+    for t in ts:
+        t.join()
+    return dt
+
+
 def run_reference_arm(a):
     rank, _, world = dist_env()
     if rank != 0:
@@ -183,12 +224,23 @@ def run_reference_arm(a):
     value = n_cpu * arm.valid / (up + rs)
     sample = "first %d of %d particles x %d beams (valid %d), update %.1f ms + resample %.1f ms per step" % (
         n_cpu, a.particles, a.beams, arm.valid, up * 1e3, rs * 1e3)
+    threads = os.cpu_count() or 1
+    bound = None
+    try:
+        up_par = parallel_update_bound(a, arm, cells, threads)
+        if up_par:
+            bound = {"value": n_cpu * arm.valid / (up_par + rs), "unit": "evals/s", "threads": threads,
+                     "update_ms": up_par * 1e3, "resample_ms": rs * 1e3,
+                     "note": "not the reference (it has no threads): its update object code on disjoint particle shards, "
+                             "one host thread each; the resample stays sequential"}
+    except Exception as e:  # informational leg: never fails the arm
+        bound = {"error": str(e)[:200]}
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": a.gpus, "steps": steps,
             "warmup": warm, "ms_per_step": (up + rs) * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(a), "timing": "host perf_counter, single thread"},
             "cpu_baseline": {"value": value, "unit": "evals/s", "cores": 1, "kind": arm.kind, "sample": sample,
-                             "host_cores_available": os.cpu_count()},
+                             "host_cores_available": os.cpu_count(), "parallel_update_upper_bound": bound},
             "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)

@@ -270,3 +270,38 @@ def test_node_draws_its_first_set_twice(O):
     pf.init_gaussian(np.zeros(3), cov)
     assert np.array_equal(pf.samples(), got) and drand_state(O) == state
     n.close()
+
+
+def test_tf2_look_alike_against_independent_formulas(O):
+    """the tf2 arithmetic inside oracle/shim is a restatement of published third-party code (parity unpinned); what CAN be
+    checked is that it is the mathematics it claims to be: yaw recovered through quaternion -> matrix -> getEulerYPR
+    (Node::getOdomPose), quaternion product + getYaw (Node2D::getAngleStats), and Transform inverse / compose
+    (Node::updatePose: latest_tf_ = (odom->base * (map->base)^-1), so latest_tf_^-1 * odom->base == map->base)"""
+    n = O.RefNode(dict(BASE, resample_interval=1))
+    n.publish_map(grid_world(), 0.05, (-4.0, -3.0))
+    for yaw in (-3.1, -1.5707963267948966, -0.3, 0.0, 1e-9, 0.7, 2.9, 3.14159):
+        n.set_odom(1.25, -0.5, yaw)
+        got = n.odom_pose()
+        assert abs(got[0] - 1.25) < 1e-15 and abs(got[1] + 0.5) < 1e-15 and abs(got[2] - yaw) < 1e-12
+    for mount in (-2.0, 0.1, 3.0):
+        n.set_tf("base_link", "laser", (0.2, 0.0, 0.1), O.yaw_quat(mount))
+        a0, inc = n.angle_stats(-1.2, 0.01)
+        want = np.arctan2(np.sin(-1.2 + mount), np.cos(-1.2 + mount))
+        assert abs(a0 - want) < 1e-7 and abs(inc - 0.01) < 1e-7      # message fields are float32
+    # one scan -> updatePose: map->base is the published pose; odom->base was set above
+    n.set_odom(0.5, 0.2, 0.3)
+    n.set_tf("base_link", "laser", (0.2, 0.0, 0.1), O.yaw_quat(0.1))
+    r = np.random.default_rng(3).uniform(0.5, 8.0, 181).astype(np.float32)
+    O.ref_lib().ref_srand48(3)
+    assert n.publish_scan(r, -1.5707964, 0.017453292, 0.1, 30.0, stamp=1.0) == 1
+    msg, tf = n.last_pose(), n.latest_tf()
+
+    def mat(x, y, yaw):
+        c, s = np.cos(yaw), np.sin(yaw)
+        return np.array([[c, -s, x], [s, c, y], [0.0, 0.0, 1.0]])
+    map_base = mat(msg["position"][0], msg["position"][1], 2.0 * np.arctan2(msg["orientation"][2], msg["orientation"][3]))
+    odom_base = mat(0.5, 0.2, 0.3)
+    latest = mat(tf[0], tf[1], 2.0 * np.arctan2(tf[5], tf[6]))
+    # node.cpp:404-427: latest_tf_ = T(odom<-base) applied to (map<-base)^-1, i.e. odom<-map
+    assert np.allclose(latest, odom_base @ np.linalg.inv(map_base), atol=1e-12)
+    n.close()
